@@ -1,0 +1,163 @@
+/* vrt.h — C ABI of libvrt, the B200-native (sm_100a) drop-in for the reference's voxel_volume render pass
+ * (+ denoiser). One vrt_context per process and GPU; multi-GPU = one process per GPU, each context owning an
+ * interleaved shard of image tiles (see vrt_context_set_shard), frame assembled on rank 0.
+ *
+ * Every function returns VRT_OK (0) or a negative vrt_status; nothing throws across the ABI. vrt_last_error()
+ * returns a thread-local message for the last failing call. Handles are opaque; the caller owns every host
+ * buffer it passes, the library owns all device memory. Calls on one context are not re-entrant (same as the
+ * reference, which is single-threaded: SURVEY.md §8b); independent contexts may be used from different threads.
+ *
+ * Reference interfaces replaced (paths relative to /root/reference):
+ *   vrt_camera              == ScreenQuadPush           source/voxels/resource/screen_quad_push.hpp:5-15
+ *   vrt_volume_params       == VolumeParameters         source/voxels/resource/parameters.hpp:5-9
+ *   vrt_light               == Light                    source/voxels/resource/voxel_scene.hpp:10-15
+ *   vrt_material            == Material                 source/voxels/resource/material.hpp:5-12
+ *   vrt_denoiser_settings   == DenoiserSettings         source/voxels/voxel_render_settings.hpp:21-29
+ *   vrt_scene_load_vox      == VoxelScene::VoxelScene   source/voxels/resource/voxel_scene.cpp:33-133
+ *   vrt_render              == GeometryStage::record    source/voxels/stages/geometry_stage.cpp:106-174
+ *                            + DenoiserStage::record    source/voxels/stages/denoiser_stage.cpp:156-258
+ *                              as sequenced by VoxelRenderer::recordCommands  source/voxels/voxel_renderer.cpp:55-105
+ *   vrt_frame_plane         == GeometryBuffer           source/voxels/stages/geometry_stage.hpp:19-27
+ *   vrt_camera_vectors      == CameraController::updateDirectionVectors  source/voxels/resource/camera_controller.cpp:15-28
+ */
+#ifndef VRT_H
+#define VRT_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    VRT_OK = 0,
+    VRT_E_INVALID = -1,       /* bad argument */
+    VRT_E_LFS_POINTER = -2,   /* the file is a git-LFS pointer stub, not data */
+    VRT_E_NO_INSTANCE = -3,   /* "Voxel scene does not contain an instance."  voxel_scene.cpp:49-50 */
+    VRT_E_PARSE = -4,         /* "Could not parse voxel scene"               voxel_scene.cpp:45-46 */
+    VRT_E_IO = -5,            /* "Failed to read voxel scene"                voxel_scene.cpp:40-43 */
+    VRT_E_CUDA = -6,          /* CUDA runtime error (message in vrt_last_error) */
+    VRT_E_NO_DEVICE = -7,     /* no CUDA device: there is NO CPU fallback */
+    VRT_E_UNSUPPORTED = -8,
+    VRT_E_OOM = -9
+} vrt_status;
+
+typedef struct vrt_context vrt_context;
+typedef struct vrt_scene vrt_scene;
+typedef struct vrt_frame vrt_frame;
+
+/* == ScreenQuadPush: 96 bytes, offsets 0,16,32,48,64,76,80,88 */
+typedef struct {
+    float camPos[4], camDir[4], camRight[4], camUp[4];
+    uint32_t volumeBounds[3];
+    uint32_t frame;
+    int32_t screenSize[2];
+    float cameraJitter[2];
+} vrt_camera;
+
+typedef struct { uint32_t aoSamples; float ambientIntensity; } vrt_volume_params;
+typedef struct { float direction[3]; float intensity; float color[4]; } vrt_light;
+typedef struct { float diffuse[4]; float metallic, pad1, pad2, pad3; } vrt_material;
+
+enum { VRT_DENOISE_AS_EXECUTED = 0, VRT_DENOISE_AS_INTENDED = 1 };   /* SURVEY.md F6 */
+typedef struct {
+    int32_t enable;
+    int32_t iterations;                 /* 1..10 (MAX_DENOISER_PASSES, denoiser_stage.hpp:9) */
+    float phiColor0, phiNormal0, phiPos0, stepWidth;
+    int32_t mode;
+} vrt_denoiser_settings;
+
+/* pass_mask bits (new; the reference behaves as VRT_PASS_ALL). SHADE off => colour = palette albedo. */
+enum { VRT_PASS_PRIMARY = 1, VRT_PASS_SHADOW = 2, VRT_PASS_AO = 4, VRT_PASS_REFLECT = 8, VRT_PASS_SHADE = 16, VRT_PASS_ALL = 31 };
+/* output selection bits */
+enum {
+    VRT_OUT_GBUFFER = 1,      /* depth, motion, mask, position, normal planes (the reference always writes them) */
+    VRT_OUT_INSTRUMENT = 2,   /* hit voxel + step count, palette index, float colour, per-pixel ray / fetch counts */
+};
+/* traversal back-ends (all bit-identical; for measurement). 0 = library default. */
+enum { VRT_TRAVERSAL_DEFAULT = 0, VRT_TRAVERSAL_DENSE_U8 = 1, VRT_TRAVERSAL_BRICK = 2 };
+
+typedef struct {
+    uint32_t pass_mask;
+    uint32_t out_mask;
+    uint32_t traversal;
+    uint32_t reserved;
+    vrt_volume_params vol;
+    vrt_light light;
+    vrt_denoiser_settings denoise;
+} vrt_render_settings;
+
+/* planes of a frame */
+typedef enum {
+    VRT_PLANE_COLOR_RGBA8 = 0,      /* 4 B/px, a = 0 */
+    VRT_PLANE_DENOISED_RGBA8 = 1,   /* 4 B/px (valid if denoise.enable) */
+    VRT_PLANE_DEPTH_R32F = 2,
+    VRT_PLANE_MOTION_RG32F = 3,
+    VRT_PLANE_MASK_R8 = 4,
+    VRT_PLANE_POSITION_RGBA32F = 5,
+    VRT_PLANE_NORMAL_RGBA8S = 6,
+    VRT_PLANE_HIT_XYZS_I16X4 = 7,   /* instrumented: primary-ray mapPos x,y,z at loop exit + step count */
+    VRT_PLANE_HIT_PALETTE_U8 = 8,   /* instrumented: material at loop exit */
+    VRT_PLANE_COLOR_RGB32F = 9,     /* instrumented: colour before the UNORM8 store */
+    VRT_PLANE_RAYS_U32 = 10,        /* instrumented: rays traced for the pixel */
+    VRT_PLANE_FETCHES_U32 = 11,     /* instrumented: getVoxel calls of the reference algorithm for the pixel */
+    VRT_PLANE_COUNT = 12
+} vrt_plane;
+
+typedef struct {
+    uint64_t rays;            /* rays the reference algorithm traces for this frame (this rank's pixels) */
+    uint64_t fetches;         /* getVoxel calls of the reference algorithm == algorithmic bytes of the traversal */
+    uint64_t pixels;          /* pixels rendered by this rank */
+    float ms_trace;           /* CUDA-event time of the trace+shade kernel(s) */
+    float ms_denoise;
+    float ms_total;           /* first launch to last kernel of the frame on the context stream */
+    uint32_t kernel_launches; /* kernels launched for this frame */
+    uint32_t reserved;
+} vrt_frame_stats;
+
+/* ---- context ---- */
+int vrt_context_create(int device, vrt_context** out);          /* VRT_E_NO_DEVICE when there is no GPU */
+void vrt_context_destroy(vrt_context*);
+/* tile shard of this context: tiles t with (t % world) == rank are rendered (interleaved for load balance). */
+int vrt_context_set_shard(vrt_context*, int rank, int world);
+const char* vrt_last_error(void);
+const char* vrt_version(void);
+int vrt_device_info(vrt_context*, int* sm_count, size_t* l2_bytes, size_t* hbm_bytes);
+void* vrt_context_stream(vrt_context*);                         /* cudaStream_t the context launches on */
+
+/* ---- scene ---- */
+int vrt_scene_load_vox(vrt_context*, const char* vox_path, vrt_scene** out);
+int vrt_scene_load_vox_memory(vrt_context*, const uint8_t* bytes, size_t n, vrt_scene** out);
+int vrt_scene_from_dense(vrt_context*, const uint8_t* volume, uint32_t w, uint32_t h, uint32_t d,
+                         const vrt_material palette[256], vrt_scene** out);
+/* on-GPU procedural volumes: generator 1 = noise terrain, 2 = sparse lattice shapes (DESIGN.md "synthetic volumes") */
+int vrt_scene_generate(vrt_context*, int generator, uint64_t seed, uint32_t w, uint32_t h, uint32_t d, vrt_scene** out);
+int vrt_scene_set_noise(vrt_scene*, const uint8_t* rgba8, uint32_t w, uint32_t h);      /* must be 512x512 */
+int vrt_scene_set_skybox(vrt_scene*, const float* rgba32f, uint32_t w, uint32_t h);
+int vrt_scene_bounds(const vrt_scene*, uint32_t whd[3]);
+int vrt_scene_palette(const vrt_scene*, vrt_material palette[256]);
+int vrt_scene_download_volume(const vrt_scene*, uint8_t* dst, size_t bytes);
+int vrt_scene_accel_info(const vrt_scene*, size_t* dense_bytes, size_t* brick_mask_bytes, size_t* brick_dist_bytes);
+void vrt_scene_destroy(vrt_scene*);
+
+/* ---- render ---- */
+/* Asynchronous on the context stream. If *frame is NULL a frame is allocated, otherwise it is reused
+ * (must match the screen size). cam->volumeBounds must equal the scene bounds. */
+int vrt_render(vrt_context*, const vrt_scene*, const vrt_camera*, const vrt_render_settings*, vrt_frame** frame);
+int vrt_frame_sync(vrt_frame*);
+int vrt_frame_plane(vrt_frame*, int plane, void** device_ptr, size_t* bytes);
+int vrt_frame_download(vrt_frame*, int plane, void* host_dst, size_t bytes);
+int vrt_frame_stats_get(vrt_frame*, vrt_frame_stats* out);       /* syncs */
+void vrt_frame_release(vrt_frame*);
+
+/* Stand-alone denoiser on host planes already resident on device: DenoiserStage::record. */
+int vrt_denoise(vrt_context*, const void* d_color_rgba8, const void* d_normal_rgba8s, const void* d_position_rgba32f,
+                int w, int h, const vrt_denoiser_settings*, void* d_out_rgba8);
+
+/* ---- host helpers mirroring reference host code ---- */
+void vrt_camera_vectors(float yaw_deg, float pitch_deg, float focal, float dir[3], float right[3], float up[3]);
+void vrt_default_settings(vrt_render_settings* out);            /* VoxelRenderSettings{} defaults, voxel_render_settings.hpp:15-59 */
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,101 @@
+// TEST INFRASTRUCTURE. Compiles the product's per-pixel device code (csrc/vrt_pixel.cuh, vrt_core.cuh) for the
+// HOST with g++ so that the CPU-only test tier can compare the kernel logic bit-for-bit with the oracle
+// without a GPU. This is not a product path and is not reachable from libvrt.
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+#include <algorithm>
+#include "../../voxel-raytracing_b200/csrc/vrt_pixel.cuh"
+
+using namespace vrt;
+
+// CPU restatement of the GPU brick builder (csrc/vrt_accel.cu) for the harness only.
+static void build_bricks(const uint8_t* vol, uint32_t W, uint32_t H, uint32_t D, std::vector<unsigned long long>& bmask,
+                         std::vector<uint8_t>& bdist, uint32_t& Bx, uint32_t& By, uint32_t& Bz) {
+    Bx = (W + 3) / 4; By = (H + 3) / 4; Bz = (D + 3) / 4;
+    bmask.assign((size_t)Bx * By * Bz, 0ull);
+    bdist.assign((size_t)Bx * By * Bz, 0);
+    for (uint32_t z = 0; z < D; z++) for (uint32_t y = 0; y < H; y++) for (uint32_t x = 0; x < W; x++)
+        if (vol[x + (size_t)y * W + (size_t)z * W * H]) {
+            size_t b = (size_t)(z >> 2) * By * Bx + (size_t)(y >> 2) * Bx + (x >> 2);
+            bmask[b] |= 1ull << ((x & 3) | ((y & 3) << 2) | ((z & 3) << 4));
+        }
+    std::vector<uint8_t> cur((size_t)Bx * By * Bz);
+    for (uint32_t z = 0; z < Bz; z++) for (uint32_t y = 0; y < By; y++) for (uint32_t x = 0; x < Bx; x++) {
+        size_t b = (size_t)z * By * Bx + (size_t)y * Bx + x;
+        bool straddle = (x * 4 + 4 > W) || (y * 4 + 4 > H) || (z * 4 + 4 > D);
+        cur[b] = (bmask[b] != 0 || straddle) ? 0 : VRT_DIST_CAP;
+    }
+    // Chebyshev distance by repeated 3x3x3 min (+1), outside the grid counts as distance 0
+    for (int it = 0; it < VRT_DIST_CAP; it++) {
+        std::vector<uint8_t> nxt = cur; bool changed = false;
+        for (int z = 0; z < (int)Bz; z++) for (int y = 0; y < (int)By; y++) for (int x = 0; x < (int)Bx; x++) {
+            size_t b = (size_t)z * By * Bx + (size_t)y * Bx + x;
+            int mn = 255;
+            for (int dz = -1; dz <= 1; dz++) for (int dy = -1; dy <= 1; dy++) for (int dx = -1; dx <= 1; dx++) {
+                int X = x + dx, Y = y + dy, Z = z + dz;
+                int v = (X < 0 || Y < 0 || Z < 0 || X >= (int)Bx || Y >= (int)By || Z >= (int)Bz) ? 0 : cur[(size_t)Z * By * Bx + (size_t)Y * Bx + X];
+                mn = std::min(mn, v);
+            }
+            int nv = std::min((int)cur[b], mn + 1);
+            if (nv != cur[b]) { nxt[b] = (uint8_t)nv; changed = true; }
+        }
+        cur.swap(nxt);
+        if (!changed) break;
+    }
+    bdist = cur;
+}
+
+struct HScene {
+    SceneDev dev;
+    std::vector<unsigned long long> bmask;
+    std::vector<uint8_t> bdist;
+};
+
+extern "C" void* hh_scene_create(const uint8_t* vol, uint32_t W, uint32_t H, uint32_t D, const float* palette,
+                                 const uint8_t* noise, const float* sky, uint32_t skyW, uint32_t skyH) {
+    HScene* s = new HScene();
+    memset(&s->dev, 0, sizeof(SceneDev));
+    s->dev.vol = vol; s->dev.W = W; s->dev.H = H; s->dev.D = D;
+    build_bricks(vol, W, H, D, s->bmask, s->bdist, s->dev.Bx, s->dev.By, s->dev.Bz);
+    s->dev.bmask = s->bmask.data(); s->dev.bdist = s->bdist.data();
+    s->dev.palette = reinterpret_cast<const vrt_material*>(palette);
+    s->dev.noise = noise; s->dev.sky = sky; s->dev.skyW = skyW; s->dev.skyH = skyH;
+    return s;
+}
+extern "C" void hh_scene_destroy(void* p) { delete (HScene*)p; }
+extern "C" void hh_scene_bdist(void* p, uint8_t* out) { HScene* s = (HScene*)p; memcpy(out, s->bdist.data(), s->bdist.size()); }
+extern "C" void hh_scene_bmask(void* p, unsigned long long* out) { HScene* s = (HScene*)p; memcpy(out, s->bmask.data(), 8 * s->bmask.size()); }
+
+extern "C" int hh_render(void* scene, const vrt_camera* cam, const vrt_render_settings* st, int traversal, const PlanesDev* pl,
+                         int row_begin, int row_end, int row_step) {
+    HScene* s = (HScene*)scene;
+    FrameParams fp; memset(&fp, 0, sizeof(fp));
+    fp.cam = *cam; fp.pass_mask = st->pass_mask; fp.out_mask = st->out_mask; fp.traversal = traversal;
+    fp.aoSamples = st->vol.aoSamples; fp.ambientIntensity = st->vol.ambientIntensity;
+    for (int k = 0; k < 3; k++) { fp.lightDir[k] = st->light.direction[k]; fp.lightColor[k] = st->light.color[k]; }
+    fp.lightIntensity = st->light.intensity; fp.rank = 0; fp.world = 1;
+    const int W = cam->screenSize[0], H = cam->screenSize[1];
+    if (row_end > H) row_end = H;
+#pragma omp parallel for schedule(dynamic, 4)
+    for (int py = row_begin; py < row_end; py += row_step)
+        for (int px = 0; px < W; px++) {
+            PixelOut o; memset(&o, 0, sizeof(o));
+            if (traversal == VRT_TRAVERSAL_DENSE_U8) render_pixel<VRT_TRAVERSAL_DENSE_U8>(s->dev, fp, px, py, o);
+            else render_pixel<VRT_TRAVERSAL_BRICK>(s->dev, fp, px, py, o);
+            size_t p = (size_t)py * W + px;
+            auto sat = [](int v) { return (int16_t)(v < -32768 ? -32768 : (v > 32767 ? 32767 : v)); };
+            if (pl->color) { uint8_t* q = pl->color + 4 * p; q[0] = to_unorm8(o.color.x); q[1] = to_unorm8(o.color.y); q[2] = to_unorm8(o.color.z); q[3] = 0; }
+            if (pl->depth) pl->depth[p] = o.depth;
+            if (pl->motion) { pl->motion[2 * p] = 0; pl->motion[2 * p + 1] = 0; }
+            if (pl->mask) pl->mask[p] = to_unorm8(o.mask);
+            if (pl->position) { float* q = pl->position + 4 * p; q[0] = o.pos.x; q[1] = o.pos.y; q[2] = o.pos.z; q[3] = 0; }
+            if (pl->normal) { int8_t* q = pl->normal + 4 * p; q[0] = to_snorm8(o.normal.x); q[1] = to_snorm8(o.normal.y); q[2] = to_snorm8(o.normal.z); q[3] = 0; }
+            if (pl->hit) { int16_t* q = pl->hit + 4 * p; q[0] = sat(o.hx); q[1] = sat(o.hy); q[2] = sat(o.hz); q[3] = (int16_t)o.steps; }
+            if (pl->hit_palette) pl->hit_palette[p] = (uint8_t)o.palette;
+            if (pl->color_f32) { float* q = pl->color_f32 + 3 * p; q[0] = o.color.x; q[1] = o.color.y; q[2] = o.color.z; }
+            if (pl->rays) pl->rays[p] = o.rays;
+            if (pl->fetches) pl->fetches[p] = o.fetches;
+        }
+    return 0;
+}
