@@ -137,6 +137,8 @@ int vrt_scene_bounds(const vrt_scene*, uint32_t whd[3]);
 int vrt_scene_palette(const vrt_scene*, vrt_material palette[256]);
 int vrt_scene_download_volume(const vrt_scene*, uint8_t* dst, size_t bytes);
 int vrt_scene_accel_info(const vrt_scene*, size_t* dense_bytes, size_t* brick_mask_bytes, size_t* brick_dist_bytes);
+/* brick levels back to the host (tests): bmask = 8 B per 4x4x4 brick, bdist = 1 B per brick; either may be NULL */
+int vrt_scene_download_accel(const vrt_scene*, uint64_t* bmask_dst, uint8_t* bdist_dst);
 void vrt_scene_destroy(vrt_scene*);
 
 /* ---- render ---- */
@@ -152,6 +154,10 @@ void vrt_frame_release(vrt_frame*);
 /* Stand-alone denoiser on host planes already resident on device: DenoiserStage::record. */
 int vrt_denoise(vrt_context*, const void* d_color_rgba8, const void* d_normal_rgba8s, const void* d_position_rgba32f,
                 int w, int h, const vrt_denoiser_settings*, void* d_out_rgba8);
+
+/* Multi-GPU assembly on the gathering rank: d_gathered holds `world` shard buffers back to back (rank-major), each
+ * of vrt_frame_plane() size as produced under vrt_context_set_shard(rank, world); writes a row-major w x h plane. */
+int vrt_assemble(vrt_context*, const void* d_gathered, int world, int w, int h, int plane, void* d_out);
 
 /* ---- host helpers mirroring reference host code ---- */
 void vrt_camera_vectors(float yaw_deg, float pitch_deg, float focal, float dir[3], float right[3], float up[3]);

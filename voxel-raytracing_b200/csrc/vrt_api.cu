@@ -1,0 +1,463 @@
+// vrt_api.cu — implementation of the C ABI in include/vrt.h: headless CUDA context, scene residency in HBM,
+// frame planes as device buffers (instead of Vulkan render targets), per-frame orchestration that mirrors
+// VoxelRenderer::recordCommands (voxel_renderer.cpp:55-105): geometry pass, then optional denoiser passes.
+// There is NO CPU fallback: without a CUDA device context creation fails with VRT_E_NO_DEVICE.
+#include <cuda_runtime.h>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+#include "vrt_launch.h"
+#include "vrt_vox.h"
+
+using namespace vrt;
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+#define CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(VRT_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
+
+struct vrt_context {
+    int device = 0, rank = 0, world = 1;
+    cudaStream_t stream = nullptr;
+    cudaDeviceProp prop{};
+};
+
+struct vrt_scene {
+    vrt_context* ctx = nullptr;
+    uint32_t w = 0, h = 0, d = 0, Bx = 0, By = 0, Bz = 0;
+    uint8_t* vol = nullptr; unsigned long long* bmask = nullptr; uint8_t* bdist = nullptr;
+    vrt_material* palette = nullptr; vrt_material hostPalette[256];
+    uint8_t* noise = nullptr; float* sky = nullptr; uint32_t skyW = 0, skyH = 0;
+    int accelLaunches = 0;
+};
+
+static const int kPlaneBpp[VRT_PLANE_COUNT] = {4, 4, 4, 8, 1, 16, 4, 8, 1, 12, 4, 4};
+
+struct vrt_frame {
+    vrt_context* ctx = nullptr;
+    int W = 0, H = 0;
+    size_t pixels = 0;                 // pixels stored per plane on this rank (full frame, or localTiles*1024 when sharded)
+    int tilesX = 0, tilesY = 0, localTiles = 0;
+    void* planes[VRT_PLANE_COUNT] = {};
+    void* ping[2] = {nullptr, nullptr};
+    Counters* ctr = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr;
+    bool denoised = false;
+    uint32_t launches = 0, out_mask = 0;
+};
+
+extern "C" const char* vrt_last_error(void) { return g_err.c_str(); }
+extern "C" const char* vrt_version(void) { return "vrt 0.1 (sm_100a)"; }
+
+extern "C" int vrt_context_create(int device, vrt_context** out) {
+    if (!out) return fail(VRT_E_INVALID, "out is null");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0) return fail(VRT_E_NO_DEVICE, std::string("no CUDA device (there is no CPU fallback): ") + cudaGetErrorString(e));
+    if (device < 0 || device >= n) return fail(VRT_E_INVALID, "device index out of range");
+    CU(cudaSetDevice(device));
+    vrt_context* c = new (std::nothrow) vrt_context();
+    if (!c) return fail(VRT_E_OOM, "host allocation failed");
+    c->device = device;
+    CU(cudaGetDeviceProperties(&c->prop, device));
+    CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    *out = c;
+    return VRT_OK;
+}
+extern "C" void vrt_context_destroy(vrt_context* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+extern "C" int vrt_context_set_shard(vrt_context* c, int rank, int world) {
+    if (!c || world < 1 || rank < 0 || rank >= world) return fail(VRT_E_INVALID, "bad shard");
+    c->rank = rank; c->world = world;
+    return VRT_OK;
+}
+extern "C" int vrt_device_info(vrt_context* c, int* sm_count, size_t* l2_bytes, size_t* hbm_bytes) {
+    if (!c) return fail(VRT_E_INVALID, "ctx is null");
+    if (sm_count) *sm_count = c->prop.multiProcessorCount;
+    if (l2_bytes) *l2_bytes = (size_t)c->prop.l2CacheSize;
+    if (hbm_bytes) *hbm_bytes = c->prop.totalGlobalMem;
+    return VRT_OK;
+}
+extern "C" void* vrt_context_stream(vrt_context* c) { return c ? (void*)c->stream : nullptr; }
+
+// ------------------------------------------------------------------------------------------------ scene
+extern "C" void vrt_scene_destroy(vrt_scene* s) {
+    if (!s) return;
+    cudaSetDevice(s->ctx->device);
+    cudaFree(s->vol); cudaFree(s->bmask); cudaFree(s->bdist); cudaFree(s->palette); cudaFree(s->noise); cudaFree(s->sky);
+    delete s;
+}
+
+static int scene_alloc(vrt_context* c, uint32_t w, uint32_t h, uint32_t d, vrt_scene** out) {
+    if (!c || !out) return fail(VRT_E_INVALID, "null argument");
+    if (!w || !h || !d || w > 32767 || h > 32767 || d > 32767) return fail(VRT_E_INVALID, "volume bounds must be 1..32767 per axis");
+    CU(cudaSetDevice(c->device));
+    vrt_scene* s = new (std::nothrow) vrt_scene();
+    if (!s) return fail(VRT_E_OOM, "host allocation failed");
+    s->ctx = c; s->w = w; s->h = h; s->d = d;
+    s->Bx = (w + 3) / 4; s->By = (h + 3) / 4; s->Bz = (d + 3) / 4;
+    const size_t nb = (size_t)s->Bx * s->By * s->Bz;
+    cudaError_t e = cudaMalloc(&s->vol, (size_t)w * h * d);
+    if (e == cudaSuccess) e = cudaMalloc(&s->bmask, nb * 8);
+    if (e == cudaSuccess) e = cudaMalloc(&s->bdist, nb);
+    if (e == cudaSuccess) e = cudaMalloc(&s->palette, sizeof(vrt_material) * 256);
+    if (e != cudaSuccess) { vrt_scene_destroy(s); return fail(e == cudaErrorMemoryAllocation ? VRT_E_OOM : VRT_E_CUDA, cudaGetErrorString(e)); }
+    *out = s;
+    return VRT_OK;
+}
+
+static int scene_finish(vrt_scene* s, const vrt_material palette[256]) {
+    vrt_context* c = s->ctx;
+    memcpy(s->hostPalette, palette, sizeof(vrt_material) * 256);
+    CU(cudaMemcpyAsync(s->palette, palette, sizeof(vrt_material) * 256, cudaMemcpyHostToDevice, c->stream));
+    const size_t nb = (size_t)s->Bx * s->By * s->Bz;
+    uint8_t *tmpA = nullptr, *tmpB = nullptr;
+    CU(cudaMalloc(&tmpA, nb)); CU(cudaMalloc(&tmpB, nb));
+    cudaError_t e = launch_build_accel(s->vol, s->w, s->h, s->d, s->bmask, s->bdist, tmpA, tmpB, c->stream, &s->accelLaunches);
+    cudaError_t e2 = cudaStreamSynchronize(c->stream);
+    cudaFree(tmpA); cudaFree(tmpB);
+    if (e != cudaSuccess) return fail(VRT_E_CUDA, cudaGetErrorString(e));
+    if (e2 != cudaSuccess) return fail(VRT_E_CUDA, cudaGetErrorString(e2));
+    return VRT_OK;
+}
+
+extern "C" int vrt_scene_from_dense(vrt_context* c, const uint8_t* volume, uint32_t w, uint32_t h, uint32_t d,
+                                    const vrt_material palette[256], vrt_scene** out) {
+    if (!volume || !palette) return fail(VRT_E_INVALID, "null argument");
+    vrt_scene* s = nullptr;
+    int rc = scene_alloc(c, w, h, d, &s);
+    if (rc) return rc;
+    cudaError_t e = cudaMemcpyAsync(s->vol, volume, (size_t)w * h * d, cudaMemcpyHostToDevice, c->stream);
+    if (e != cudaSuccess) { vrt_scene_destroy(s); return fail(VRT_E_CUDA, cudaGetErrorString(e)); }
+    rc = scene_finish(s, palette);
+    if (rc) { vrt_scene_destroy(s); return rc; }
+    *out = s;
+    return VRT_OK;
+}
+
+extern "C" int vrt_scene_load_vox_memory(vrt_context* c, const uint8_t* bytes, size_t n, vrt_scene** out) {
+    if (!c || !out) return fail(VRT_E_INVALID, "null argument");
+    DenseScene ds; std::string err;
+    int rc = load_vox_bytes(bytes, n, ds, err);
+    if (rc) return fail(rc, err);
+    return vrt_scene_from_dense(c, ds.volume.data(), ds.w, ds.h, ds.d, ds.palette, out);
+}
+extern "C" int vrt_scene_load_vox(vrt_context* c, const char* path, vrt_scene** out) {
+    if (!c || !out) return fail(VRT_E_INVALID, "null argument");
+    DenseScene ds; std::string err;
+    int rc = load_vox_file(path, ds, err);
+    if (rc) return fail(rc, err);
+    return vrt_scene_from_dense(c, ds.volume.data(), ds.w, ds.h, ds.d, ds.palette, out);
+}
+
+extern "C" int vrt_scene_generate(vrt_context* c, int generator, uint64_t seed, uint32_t w, uint32_t h, uint32_t d, vrt_scene** out) {
+    if (generator != 1 && generator != 2) return fail(VRT_E_INVALID, "unknown generator");
+    vrt_scene* s = nullptr;
+    int rc = scene_alloc(c, w, h, d, &s);
+    if (rc) return rc;
+    cudaError_t e = launch_generate(generator, (uint32_t)seed, s->vol, w, h, d, c->stream);
+    if (e != cudaSuccess) { vrt_scene_destroy(s); return fail(VRT_E_CUDA, cudaGetErrorString(e)); }
+    vrt_material pal[256];
+    generator_palette(generator, (uint32_t)seed, pal);
+    rc = scene_finish(s, pal);
+    if (rc) { vrt_scene_destroy(s); return rc; }
+    *out = s;
+    return VRT_OK;
+}
+
+extern "C" int vrt_scene_set_noise(vrt_scene* s, const uint8_t* rgba8, uint32_t w, uint32_t h) {
+    if (!s || !rgba8) return fail(VRT_E_INVALID, "null argument");
+    if (w != 512 || h != 512) return fail(VRT_E_INVALID, "blue-noise texture must be 512x512 (NOISE_SIZE, voxel_volume.frag:70)");
+    CU(cudaSetDevice(s->ctx->device));
+    if (!s->noise) CU(cudaMalloc(&s->noise, 512 * 512 * 4));
+    CU(cudaMemcpy(s->noise, rgba8, 512 * 512 * 4, cudaMemcpyHostToDevice));
+    return VRT_OK;
+}
+extern "C" int vrt_scene_set_skybox(vrt_scene* s, const float* rgba32f, uint32_t w, uint32_t h) {
+    if (!s || !rgba32f || !w || !h) return fail(VRT_E_INVALID, "null argument");
+    CU(cudaSetDevice(s->ctx->device));
+    if (s->sky) { cudaFree(s->sky); s->sky = nullptr; }
+    CU(cudaMalloc(&s->sky, (size_t)w * h * 16));
+    CU(cudaMemcpy(s->sky, rgba32f, (size_t)w * h * 16, cudaMemcpyHostToDevice));
+    s->skyW = w; s->skyH = h;
+    return VRT_OK;
+}
+extern "C" int vrt_scene_bounds(const vrt_scene* s, uint32_t whd[3]) {
+    if (!s || !whd) return fail(VRT_E_INVALID, "null argument");
+    whd[0] = s->w; whd[1] = s->h; whd[2] = s->d;
+    return VRT_OK;
+}
+extern "C" int vrt_scene_palette(const vrt_scene* s, vrt_material palette[256]) {
+    if (!s || !palette) return fail(VRT_E_INVALID, "null argument");
+    memcpy(palette, s->hostPalette, sizeof(vrt_material) * 256);
+    return VRT_OK;
+}
+extern "C" int vrt_scene_download_volume(const vrt_scene* s, uint8_t* dst, size_t bytes) {
+    if (!s || !dst || bytes != (size_t)s->w * s->h * s->d) return fail(VRT_E_INVALID, "bad size");
+    CU(cudaSetDevice(s->ctx->device));
+    CU(cudaMemcpy(dst, s->vol, bytes, cudaMemcpyDeviceToHost));
+    return VRT_OK;
+}
+extern "C" int vrt_scene_accel_info(const vrt_scene* s, size_t* dense_bytes, size_t* brick_mask_bytes, size_t* brick_dist_bytes) {
+    if (!s) return fail(VRT_E_INVALID, "null argument");
+    const size_t nb = (size_t)s->Bx * s->By * s->Bz;
+    if (dense_bytes) *dense_bytes = (size_t)s->w * s->h * s->d;
+    if (brick_mask_bytes) *brick_mask_bytes = nb * 8;
+    if (brick_dist_bytes) *brick_dist_bytes = nb;
+    return VRT_OK;
+}
+
+extern "C" int vrt_scene_download_accel(const vrt_scene* s, uint64_t* bmask_dst, uint8_t* bdist_dst) {
+    if (!s) return fail(VRT_E_INVALID, "null argument");
+    const size_t nb = (size_t)s->Bx * s->By * s->Bz;
+    CU(cudaSetDevice(s->ctx->device));
+    if (bmask_dst) CU(cudaMemcpy(bmask_dst, s->bmask, nb * 8, cudaMemcpyDeviceToHost));
+    if (bdist_dst) CU(cudaMemcpy(bdist_dst, s->bdist, nb, cudaMemcpyDeviceToHost));
+    return VRT_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ frames
+extern "C" void vrt_frame_release(vrt_frame* f) {
+    if (!f) return;
+    cudaSetDevice(f->ctx->device);
+    for (void* p : f->planes) cudaFree(p);
+    cudaFree(f->ping[0]); cudaFree(f->ping[1]); cudaFree(f->ctr);
+    if (f->e0) cudaEventDestroy(f->e0);
+    if (f->e1) cudaEventDestroy(f->e1);
+    if (f->e2) cudaEventDestroy(f->e2);
+    delete f;
+}
+
+static int frame_ensure_plane(vrt_frame* f, int plane) {
+    if (f->planes[plane]) return VRT_OK;
+    CU(cudaMalloc(&f->planes[plane], f->pixels * kPlaneBpp[plane]));
+    CU(cudaMemsetAsync(f->planes[plane], 0, f->pixels * kPlaneBpp[plane], f->ctx->stream));
+    return VRT_OK;
+}
+
+static int frame_create(vrt_context* c, int W, int H, vrt_frame** out) {
+    vrt_frame* f = new (std::nothrow) vrt_frame();
+    if (!f) return fail(VRT_E_OOM, "host allocation failed");
+    f->ctx = c; f->W = W; f->H = H;
+    f->tilesX = (W + VRT_TILE - 1) / VRT_TILE; f->tilesY = (H + VRT_TILE - 1) / VRT_TILE;
+    const int tiles = f->tilesX * f->tilesY;
+    f->localTiles = tiles > c->rank ? (tiles - c->rank + c->world - 1) / c->world : 0;
+    // sharded frames are padded to the same tile count on every rank so the gather is one equal-size collective
+    const int maxLocal = (tiles + c->world - 1) / c->world;
+    f->pixels = c->world == 1 ? (size_t)W * H : (size_t)maxLocal * VRT_TILE * VRT_TILE;
+    cudaError_t e = cudaMalloc(&f->ctr, sizeof(Counters));
+    if (e == cudaSuccess) e = cudaEventCreate(&f->e0);
+    if (e == cudaSuccess) e = cudaEventCreate(&f->e1);
+    if (e == cudaSuccess) e = cudaEventCreate(&f->e2);
+    if (e != cudaSuccess) { vrt_frame_release(f); return fail(VRT_E_CUDA, cudaGetErrorString(e)); }
+    *out = f;
+    return VRT_OK;
+}
+
+// Host tables of DenoiserStage (denoiser_stage.cpp:37-61) as seen by the shader under std140.
+static void denoise_taps(int mode, DenoiseTaps& t) {
+    float w[9]; float o[18]; int i = 0;
+    for (int y = -1; y <= 1; y++)
+        for (int x = -1; x <= 1; x++, i++) {
+            o[2 * i] = (float)x; o[2 * i + 1] = (float)y;
+            const float sx = ((float)x * (float)x) / (2.0f * 2.0f * 2.0f), sy = ((float)y * (float)y) / (2.0f * 2.0f * 2.0f);
+            w[i] = expf(-(sx + sy));   // glm::gauss(vec2(x,y), vec2(0), vec2(2))
+        }
+    t.n = 0;
+    for (int k = 0; k < 25; k++) {
+        float kw, ox, oy;
+        if (mode == VRT_DENOISE_AS_INTENDED) { if (k >= 9) break; kw = w[k]; ox = o[2 * k]; oy = o[2 * k + 1]; }
+        else { const int fi = 4 * k; kw = fi < 9 ? w[fi] : 0.0f; ox = fi < 18 ? o[fi] : 0.0f; oy = fi + 1 < 18 ? o[fi + 1] : 0.0f; }
+        if (kw == 0.0f) continue;   // zero-weight taps add +0 to sum and total: elided
+        t.ox[t.n] = (int)ox; t.oy[t.n] = (int)oy; t.k[t.n] = kw; t.n++;
+    }
+}
+
+static int run_denoise(vrt_context* c, const void* color, const void* normal, const void* position, int W, int H,
+                       const vrt_denoiser_settings* ds, void* ping[2], int* lastOut, uint32_t* launches) {
+    if (ds->iterations < 1 || ds->iterations > 10) return fail(VRT_E_INVALID, "denoiser iterations must be 1..10 (MAX_DENOISER_PASSES)");
+    if (ds->mode != VRT_DENOISE_AS_EXECUTED && ds->mode != VRT_DENOISE_AS_INTENDED) return fail(VRT_E_INVALID, "bad denoise mode");
+    DenoiseTaps taps; denoise_taps(ds->mode, taps);
+    const void* src = color;
+    int last = 0;
+    for (int i = 0; i < ds->iterations; i++) {   // denoiser_stage.cpp:143-154 and :203-257
+        DenoiseIter it;
+        it.phiColor = 1.0f / (float)i * ds->phiColor0;
+        it.phiNormal = 1.0f / (float)i * ds->phiNormal0;
+        it.phiPos = 1.0f / (float)i * ds->phiPos0;
+        it.stepWidth = (float)i * ds->stepWidth + 1.0f;
+        const int tgt = i % 2;
+        cudaError_t e = launch_denoise((const uint8_t*)src, (const int8_t*)normal, (const float*)position, (uint8_t*)ping[tgt], W, H, taps, it, c->stream);
+        if (e != cudaSuccess) return fail(VRT_E_CUDA, cudaGetErrorString(e));
+        if (launches) (*launches)++;
+        src = ping[tgt]; last = tgt;
+    }
+    *lastOut = last;
+    return VRT_OK;
+}
+
+extern "C" int vrt_render(vrt_context* c, const vrt_scene* s, const vrt_camera* cam, const vrt_render_settings* st, vrt_frame** frame) {
+    if (!c || !s || !cam || !st || !frame) return fail(VRT_E_INVALID, "null argument");
+    if (s->ctx != c) return fail(VRT_E_INVALID, "scene belongs to another context");
+    const int W = cam->screenSize[0], H = cam->screenSize[1];
+    if (W <= 0 || H <= 0 || W > 32768 || H > 32768) return fail(VRT_E_INVALID, "bad screenSize");
+    if (cam->volumeBounds[0] != s->w || cam->volumeBounds[1] != s->h || cam->volumeBounds[2] != s->d)
+        return fail(VRT_E_INVALID, "camera volumeBounds differ from the scene bounds");
+    if (!(st->pass_mask & VRT_PASS_PRIMARY)) return fail(VRT_E_INVALID, "pass_mask must include VRT_PASS_PRIMARY");
+    if (st->traversal > VRT_TRAVERSAL_BRICK) return fail(VRT_E_INVALID, "unknown traversal");
+    if (st->denoise.enable && c->world != 1) return fail(VRT_E_UNSUPPORTED, "denoise runs on the assembled frame: call vrt_denoise on rank 0 after the gather");
+    CU(cudaSetDevice(c->device));
+    vrt_frame* f = *frame;
+    if (f && (f->W != W || f->H != H || f->ctx != c)) return fail(VRT_E_INVALID, "frame does not match screenSize/context");
+    if (!f) { int rc = frame_create(c, W, H, &f); if (rc) return rc; }
+    uint32_t out_mask = st->out_mask;
+    if (st->denoise.enable) out_mask |= VRT_OUT_GBUFFER;
+    int rc = frame_ensure_plane(f, VRT_PLANE_COLOR_RGBA8);
+    if (!rc && (out_mask & VRT_OUT_GBUFFER))
+        for (int p : {VRT_PLANE_DEPTH_R32F, VRT_PLANE_MOTION_RG32F, VRT_PLANE_MASK_R8, VRT_PLANE_POSITION_RGBA32F, VRT_PLANE_NORMAL_RGBA8S}) if (!rc) rc = frame_ensure_plane(f, p);
+    if (!rc && (out_mask & VRT_OUT_INSTRUMENT))
+        for (int p : {VRT_PLANE_HIT_XYZS_I16X4, VRT_PLANE_HIT_PALETTE_U8, VRT_PLANE_COLOR_RGB32F, VRT_PLANE_RAYS_U32, VRT_PLANE_FETCHES_U32}) if (!rc) rc = frame_ensure_plane(f, p);
+    if (!rc && st->denoise.enable)
+        for (int k = 0; k < 2 && !rc; k++) if (!f->ping[k]) { cudaError_t e = cudaMalloc(&f->ping[k], f->pixels * 4); if (e != cudaSuccess) rc = fail(VRT_E_CUDA, cudaGetErrorString(e)); }
+    if (rc) { if (!*frame) vrt_frame_release(f); return rc; }
+
+    SceneDev sc{};
+    sc.vol = s->vol; sc.bmask = s->bmask; sc.bdist = s->bdist; sc.W = s->w; sc.H = s->h; sc.D = s->d; sc.Bx = s->Bx; sc.By = s->By; sc.Bz = s->Bz;
+    sc.palette = s->palette; sc.noise = s->noise; sc.sky = s->sky; sc.skyW = s->skyW; sc.skyH = s->skyH;
+    FrameParams fp{};
+    fp.cam = *cam; fp.pass_mask = st->pass_mask; fp.out_mask = out_mask;
+    fp.traversal = st->traversal == VRT_TRAVERSAL_DEFAULT ? VRT_TRAVERSAL_BRICK : st->traversal;
+    fp.aoSamples = st->vol.aoSamples; fp.ambientIntensity = st->vol.ambientIntensity;
+    for (int k = 0; k < 3; k++) { fp.lightDir[k] = st->light.direction[k]; fp.lightColor[k] = st->light.color[k]; }
+    fp.lightIntensity = st->light.intensity;
+    fp.rank = c->rank; fp.world = c->world; fp.tilesX = f->tilesX; fp.tilesY = f->tilesY; fp.localTiles = f->localTiles;
+    PlanesDev pl{};
+    pl.color = (uint8_t*)f->planes[VRT_PLANE_COLOR_RGBA8]; pl.depth = (float*)f->planes[VRT_PLANE_DEPTH_R32F];
+    pl.motion = (float*)f->planes[VRT_PLANE_MOTION_RG32F]; pl.mask = (uint8_t*)f->planes[VRT_PLANE_MASK_R8];
+    pl.position = (float*)f->planes[VRT_PLANE_POSITION_RGBA32F]; pl.normal = (int8_t*)f->planes[VRT_PLANE_NORMAL_RGBA8S];
+    pl.hit = (int16_t*)f->planes[VRT_PLANE_HIT_XYZS_I16X4]; pl.hit_palette = (uint8_t*)f->planes[VRT_PLANE_HIT_PALETTE_U8];
+    pl.color_f32 = (float*)f->planes[VRT_PLANE_COLOR_RGB32F]; pl.rays = (uint32_t*)f->planes[VRT_PLANE_RAYS_U32];
+    pl.fetches = (uint32_t*)f->planes[VRT_PLANE_FETCHES_U32];
+
+    f->launches = 0; f->out_mask = out_mask; f->denoised = false;
+    CU(cudaMemsetAsync(f->ctr, 0, sizeof(Counters), c->stream));
+    CU(cudaEventRecord(f->e0, c->stream));
+    cudaError_t e = launch_render(sc, fp, pl, f->ctr, c->stream);
+    if (e != cudaSuccess) { if (!*frame) vrt_frame_release(f); return fail(VRT_E_CUDA, cudaGetErrorString(e)); }
+    f->launches++;
+    CU(cudaEventRecord(f->e1, c->stream));
+    if (st->denoise.enable) {
+        int last = 0;
+        rc = run_denoise(c, pl.color, pl.normal, pl.position, W, H, &st->denoise, f->ping, &last, &f->launches);
+        if (rc) { if (!*frame) vrt_frame_release(f); return rc; }
+        // expose the final ping-pong target as the DENOISED plane without a copy
+        if (last == 1) { void* t = f->ping[0]; f->ping[0] = f->ping[1]; f->ping[1] = t; }
+        f->denoised = true;
+    }
+    CU(cudaEventRecord(f->e2, c->stream));
+    *frame = f;
+    return VRT_OK;
+}
+
+extern "C" int vrt_frame_sync(vrt_frame* f) {
+    if (!f) return fail(VRT_E_INVALID, "null frame");
+    CU(cudaSetDevice(f->ctx->device));
+    CU(cudaStreamSynchronize(f->ctx->stream));
+    return VRT_OK;
+}
+extern "C" int vrt_frame_plane(vrt_frame* f, int plane, void** device_ptr, size_t* bytes) {
+    if (!f || plane < 0 || plane >= VRT_PLANE_COUNT) return fail(VRT_E_INVALID, "bad plane");
+    void* p = plane == VRT_PLANE_DENOISED_RGBA8 ? (f->denoised ? f->ping[0] : nullptr) : f->planes[plane];
+    if (!p) return fail(VRT_E_INVALID, "plane was not produced for this frame (check out_mask / denoise.enable)");
+    if (device_ptr) *device_ptr = p;
+    if (bytes) *bytes = f->pixels * kPlaneBpp[plane];
+    return VRT_OK;
+}
+extern "C" int vrt_frame_download(vrt_frame* f, int plane, void* host_dst, size_t bytes) {
+    void* p = nullptr; size_t n = 0;
+    int rc = vrt_frame_plane(f, plane, &p, &n);
+    if (rc) return rc;
+    if (!host_dst || bytes != n) return fail(VRT_E_INVALID, "size mismatch");
+    CU(cudaSetDevice(f->ctx->device));
+    CU(cudaMemcpyAsync(host_dst, p, n, cudaMemcpyDeviceToHost, f->ctx->stream));
+    CU(cudaStreamSynchronize(f->ctx->stream));
+    return VRT_OK;
+}
+extern "C" int vrt_frame_stats_get(vrt_frame* f, vrt_frame_stats* out) {
+    if (!f || !out) return fail(VRT_E_INVALID, "null argument");
+    CU(cudaSetDevice(f->ctx->device));
+    CU(cudaStreamSynchronize(f->ctx->stream));
+    Counters h{};
+    CU(cudaMemcpy(&h, f->ctr, sizeof(h), cudaMemcpyDeviceToHost));
+    memset(out, 0, sizeof(*out));
+    out->rays = h.rays; out->fetches = h.fetches; out->pixels = h.pixels;
+    CU(cudaEventElapsedTime(&out->ms_trace, f->e0, f->e1));
+    CU(cudaEventElapsedTime(&out->ms_denoise, f->e1, f->e2));
+    CU(cudaEventElapsedTime(&out->ms_total, f->e0, f->e2));
+    out->kernel_launches = f->launches;
+    return VRT_OK;
+}
+
+extern "C" int vrt_denoise(vrt_context* c, const void* d_color, const void* d_normal, const void* d_position, int w, int h,
+                           const vrt_denoiser_settings* ds, void* d_out) {
+    if (!c || !d_color || !d_normal || !d_position || !ds || !d_out || w <= 0 || h <= 0) return fail(VRT_E_INVALID, "null argument");
+    CU(cudaSetDevice(c->device));
+    void* ping[2] = {d_out, nullptr};
+    if (ds->iterations > 1) CU(cudaMalloc(&ping[1], (size_t)w * h * 4));
+    // make the last iteration land in d_out: iteration i writes ping[i%2]; swap if the last index is odd
+    if (((ds->iterations - 1) % 2) == 1) { void* t = ping[0]; ping[0] = ping[1]; ping[1] = t; }
+    int last = 0; uint32_t n = 0;
+    int rc = run_denoise(c, d_color, d_normal, d_position, w, h, ds, ping, &last, &n);
+    cudaError_t e = cudaStreamSynchronize(c->stream);
+    void* scratch = ping[0] == d_out ? ping[1] : ping[0];
+    if (scratch) cudaFree(scratch);
+    if (rc) return rc;
+    if (e != cudaSuccess) return fail(VRT_E_CUDA, cudaGetErrorString(e));
+    return VRT_OK;
+}
+
+// Assemble a sharded plane on the gathering rank: `gathered` holds world shard buffers back to back (rank-major),
+// each of vrt_frame_plane() size; writes a row-major W x H plane.
+extern "C" int vrt_assemble(vrt_context* c, const void* d_gathered, int world, int w, int h, int plane, void* d_out) {
+    if (!c || !d_gathered || !d_out || world < 1 || plane < 0 || plane >= VRT_PLANE_COUNT) return fail(VRT_E_INVALID, "bad argument");
+    CU(cudaSetDevice(c->device));
+    const int tiles = ((w + VRT_TILE - 1) / VRT_TILE) * ((h + VRT_TILE - 1) / VRT_TILE);
+    const size_t stride = (size_t)((tiles + world - 1) / world) * VRT_TILE * VRT_TILE;
+    cudaError_t e = launch_detile(d_gathered, d_out, w, h, world, stride, kPlaneBpp[plane], c->stream);
+    if (e != cudaSuccess) return fail(VRT_E_CUDA, cudaGetErrorString(e));
+    return VRT_OK;
+}
+
+// ---- host helpers ----
+extern "C" void vrt_camera_vectors(float yaw, float pitch, float focal, float dir[3], float right[3], float up[3]) {
+    // CameraController::updateDirectionVectors (camera_controller.cpp:15-28), worldUp = (0,-1,0), glm normalize/cross
+    const float k = 0.01745329251994329576923690768489f;
+    float n[3] = {cosf(yaw * k) * cosf(pitch * k), sinf(pitch * k), sinf(yaw * k) * cosf(pitch * k)};
+    auto norm = [](float v[3]) { const float inv = 1.0f / sqrtf((v[0] * v[0] + v[1] * v[1]) + v[2] * v[2]); v[0] *= inv; v[1] *= inv; v[2] *= inv; };
+    auto cross = [](const float a[3], const float b[3], float o[3]) { o[0] = a[1] * b[2] - b[1] * a[2]; o[1] = a[2] * b[0] - b[2] * a[0]; o[2] = a[0] * b[1] - b[0] * a[1]; };
+    norm(n);
+    const float wu[3] = {0.0f, -1.0f, 0.0f};
+    float r[3], u[3];
+    cross(n, wu, r); norm(r);
+    cross(r, n, u); norm(u);
+    for (int i = 0; i < 3; i++) { dir[i] = n[i] * focal; right[i] = r[i]; up[i] = u[i]; }
+}
+
+extern "C" void vrt_default_settings(vrt_render_settings* s) {
+    if (!s) return;
+    memset(s, 0, sizeof(*s));
+    s->pass_mask = VRT_PASS_ALL; s->out_mask = VRT_OUT_GBUFFER; s->traversal = VRT_TRAVERSAL_DEFAULT;
+    s->vol.aoSamples = 4; s->vol.ambientIntensity = 1.0f;                  // AmbientOcclusionSettings
+    const float inv = 1.0f / sqrtf((1.0f * 1.0f + 1.0f * 1.0f) + 1.0f * 1.0f);   // glm::normalize(vec3(1))
+    s->light.direction[0] = s->light.direction[1] = s->light.direction[2] = 1.0f * inv;
+    s->light.intensity = 1.0f;
+    for (float& v : s->light.color) v = 1.0f;
+    s->denoise.enable = 1; s->denoise.iterations = 2; s->denoise.phiColor0 = 20.4f; s->denoise.phiNormal0 = 1E-2f;
+    s->denoise.phiPos0 = 1E-1f; s->denoise.stepWidth = 2.0f; s->denoise.mode = VRT_DENOISE_AS_EXECUTED;
+}

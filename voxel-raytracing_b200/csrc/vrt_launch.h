@@ -1,0 +1,26 @@
+// vrt_launch.h — host-callable launchers of the CUDA kernels (internal; the public surface is include/vrt.h).
+#pragma once
+#include <cuda_runtime.h>
+#include "vrt_types.h"
+
+namespace vrt {
+
+// voxel_volume pass (vrt_render.cu)
+cudaError_t launch_render(const SceneDev& sc, const FrameParams& fp, const PlanesDev& pl, Counters* ctr, cudaStream_t stream);
+cudaError_t launch_detile(const void* src, void* dst, int W, int H, int world, size_t rankStridePixels, int bpp, cudaStream_t stream);
+
+// brick acceleration build (vrt_accel.cu): bmask + bdist from the dense volume; tmpA/tmpB are scratch of Bx*By*Bz bytes
+cudaError_t launch_build_accel(const uint8_t* vol, uint32_t W, uint32_t H, uint32_t D, unsigned long long* bmask, uint8_t* bdist,
+                               uint8_t* tmpA, uint8_t* tmpB, cudaStream_t stream, int* launches);
+
+// procedural volumes (vrt_generate.cu)
+cudaError_t launch_generate(int generator, uint32_t seed, uint8_t* vol, uint32_t W, uint32_t H, uint32_t D, cudaStream_t stream);
+void generator_palette(int generator, uint32_t seed, vrt_material palette[256]);   // host
+
+// denoiser (vrt_denoise.cu)
+struct DenoiseTaps { int n; int ox[9], oy[9]; float k[9]; };   // taps with non-zero kernel weight, in loop order
+struct DenoiseIter { float phiColor, phiNormal, phiPos, stepWidth; };
+cudaError_t launch_denoise(const uint8_t* color, const int8_t* normal, const float* position, uint8_t* out, int W, int H,
+                           const DenoiseTaps& taps, const DenoiseIter& it, cudaStream_t stream);
+
+}  // namespace vrt
