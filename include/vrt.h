@@ -122,6 +122,7 @@ int vrt_context_set_shard(vrt_context*, int rank, int world);
 const char* vrt_last_error(void);
 const char* vrt_version(void);
 int vrt_device_info(vrt_context*, int* sm_count, size_t* l2_bytes, size_t* hbm_bytes);
+int vrt_context_sync(vrt_context*);                             /* wait for everything queued on the context stream */
 void* vrt_context_stream(vrt_context*);                         /* cudaStream_t the context launches on */
 
 /* ---- scene ---- */
@@ -140,6 +141,10 @@ int vrt_scene_accel_info(const vrt_scene*, size_t* dense_bytes, size_t* brick_ma
 /* brick levels back to the host (tests): bmask = 8 B per 4x4x4 brick, bdist = 1 B per brick; either may be NULL */
 int vrt_scene_download_accel(const vrt_scene*, uint64_t* bmask_dst, uint8_t* bdist_dst);
 void vrt_scene_destroy(vrt_scene*);
+/* Host-only .vox decode (no GPU involved): the dense volume + palette vrt_scene_load_vox_memory would upload.
+ * *volume_out is malloc'ed (x + y*w + z*w*h); free it with vrt_host_free. */
+int vrt_vox_decode(const uint8_t* bytes, size_t n, uint8_t** volume_out, uint32_t whd[3], vrt_material palette[256]);
+void vrt_host_free(void*);
 
 /* ---- render ---- */
 /* Asynchronous on the context stream. If *frame is NULL a frame is allocated, otherwise it is reused

@@ -1,0 +1,241 @@
+"""GPU tier (B200): the CUDA path, called through the C ABI (libvrt.so via pyvrt), against the CPU oracle on the
+same seeded inputs. Bar (BASELINE.json): hit voxel, palette index, step count bit-exact; depth / position within
+1e-5 relative (we assert bit-exact); colour within 1/255 per channel (we assert bit-exact float colour except for
+at most 1e-4 of pixels, where the binary64 atan2/asin of the sky lookup may round differently)."""
+import ctypes as C
+import numpy as np
+import pytest
+
+from vrtlib import (O, assets, TRAV_BRICK, TRAV_DENSE, harness, default_camera, look_at_camera, random_volume, random_palette,
+                    bits_equal, cached_vox, to_vrt_camera)
+import pyvrt
+import synth
+
+pytestmark = pytest.mark.gpu
+
+EXACT = ["depth", "motion", "mask", "position", "normal", "hit", "hit_palette", "rays", "fetches"]
+
+
+def vrt_settings(st: O.Settings, traversal=0, out_mask=3, denoise=None):
+    s = pyvrt.default_settings()
+    s.pass_mask, s.out_mask, s.traversal = st.pass_mask, out_mask, traversal
+    s.vol.aoSamples, s.vol.ambientIntensity = st.aoSamples, st.ambientIntensity
+    s.light.direction[:] = st.lightDir[:]; s.light.intensity = st.lightIntensity; s.light.color[:] = st.lightColor[:]
+    s.denoise.enable = 0
+    if denoise is not None:
+        s.denoise.enable, s.denoise.iterations, s.denoise.mode = 1, denoise.get("iterations", 2), denoise.get("mode", 0)
+    return s
+
+
+def cam_to_py(cam: O.Camera) -> pyvrt.Camera:
+    c = pyvrt.Camera(); C.memmove(C.byref(c), C.byref(cam), C.sizeof(cam)); return c
+
+
+def gpu_render(ctx, scene, cam, st, traversal=0, denoise=None, names=None):
+    rp = pyvrt.VoxelRenderPass(ctx, scene, vrt_settings(st, traversal, denoise=denoise))
+    fr = rp.record(cam_to_py(cam)); fr.sync()
+    names = names or [n for n, _, _ in O.PLANE_SPECS] + (["denoised"] if denoise is not None else [])
+    out = {n: fr.download(n) for n in names}
+    out["_stats"] = fr.stats()
+    fr.release()
+    return out
+
+
+def check(got, want, color_outlier_frac=1e-4):
+    for n in EXACT:
+        ok, bad = bits_equal(got[n], want[n])
+        assert ok, f"plane {n}: {bad} of {got[n].size} differ"
+    diff = np.abs(got["color"].astype(int) - want["color"].astype(int))
+    assert diff.max() <= 1, f"colour differs by {diff.max()}/255"
+    same = (got["color_f32"].view(np.uint32) == want["color_f32"].view(np.uint32)) | (np.isnan(got["color_f32"]) & np.isnan(want["color_f32"]))
+    frac = 1.0 - same.all(axis=-1).mean()
+    assert frac <= color_outlier_frac, f"float colour differs on {frac:.2e} of pixels"
+    assert int(want["rays"].sum()) == got["_stats"]["rays"] and int(want["fetches"].sum()) == got["_stats"]["fetches"]
+
+
+def make_pair(ctx, vol, pal, sky=(256, 128)):
+    noise, skyt = assets.noise_standin(), assets.sky_standin(*sky)
+    sc, keep = O.make_scene(vol, pal, noise, skyt)
+    gs = pyvrt.VoxelScene.from_dense(ctx, vol, pal); gs.set_noise(noise); gs.set_skybox(skyt)
+    return sc, keep, gs
+
+
+# ------------------------------------------------------------------------------------------- BASELINE configs
+def test_cfg1_treehouse_standin_primary_720p(gpu_ctx):
+    data = cached_vox("treehouse")
+    rc, vol, pal = O.load_vox(data)
+    gs = pyvrt.VoxelScene.from_vox_bytes(gpu_ctx, data)
+    assert gs.bounds == (126, 126, 126) and np.array_equal(gs.download_volume(), vol) and np.array_equal(gs.palette(), pal)
+    noise, sky = assets.noise_standin(), assets.sky_standin(256, 128)
+    gs.set_noise(noise); gs.set_skybox(sky)
+    sc, keep = O.make_scene(vol, pal, noise, sky)
+    cam = default_camera((126, 126, 126), (1280, 720))
+    st = O.make_settings(pass_mask=O.PASS_PRIMARY)
+    want = O.render(sc, cam, st)
+    for trav in (TRAV_DENSE, TRAV_BRICK):
+        check(gpu_render(gpu_ctx, gs, cam, st, trav), want)
+    gs.destroy()
+
+
+def test_cfg2_mandelbulb_standin_shadow_1080p(gpu_ctx):
+    data = cached_vox("mandelbulb", n=128)
+    rc, vol, pal = O.load_vox(data)
+    sc, keep, gs = make_pair(gpu_ctx, vol, pal)
+    cam = look_at_camera(gs.bounds, (1920, 1080), (-40, 150, -90), (64, 64, 64))
+    st = O.make_settings(pass_mask=O.PASS_PRIMARY | O.PASS_SHADOW | O.PASS_SHADE, ao=0)
+    check(gpu_render(gpu_ctx, gs, cam, st), O.render(sc, cam, st))
+    gs.destroy()
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+def test_cfg3_floating_standin_ao_shadow_denoise(gpu_ctx, mode):
+    rc, vol, pal = O.load_vox(cached_vox("floatingcolored"))
+    sc, keep, gs = make_pair(gpu_ctx, vol, pal, sky=(2048, 1024))
+    cam = look_at_camera(gs.bounds, (960, 540), (-60, 330, -80), (132, 132, 132), frame=3)
+    st = O.make_settings(ao=1)
+    want = O.render(sc, cam, st)
+    got = gpu_render(gpu_ctx, gs, cam, st, denoise=dict(iterations=2, mode=mode))
+    check(got, want)
+    assert want["rays"].max() > 8                           # metallic palette entries produced reflection stacks
+    # denoise the GPU's own G-buffer with the oracle: isolates the filter (expf is within 2 ulp of glibc's)
+    dn = O.denoise(got["color"], got["normal"], got["position"], iterations=2, mode=mode)
+    d = np.abs(dn.astype(int) - got["denoised"].astype(int))
+    assert d.max() <= 1 and (d != 0).mean() < 1e-3
+    gs.destroy()
+
+
+@pytest.mark.parametrize("gen,whd,pos,target", [(1, (256, 192, 256), (20.3, 150.2, 12.1), (128, 90, 128)),
+                                                (2, (256, 256, 256), (-30.5, 200.7, -40.2), (128, 128, 128))])
+def test_cfg4_cfg5_synthetic_generators_and_full_pass(gpu_ctx, gen, whd, pos, target):
+    gs = pyvrt.VoxelScene.generate(gpu_ctx, gen, 42, *whd)
+    vol = synth.GENERATORS[gen](42, *whd)
+    assert np.array_equal(gs.download_volume(), vol)
+    pal = synth.generator_palette(gen, 42)
+    assert np.array_equal(gs.palette().view(np.uint32), pal.view(np.uint32))
+    noise, sky = assets.noise_standin(), assets.sky_standin(256, 128)
+    gs.set_noise(noise); gs.set_skybox(sky)
+    sc, keep = O.make_scene(vol, pal, noise, sky)
+    cam = look_at_camera(whd, (640, 360), pos, target, frame=9)
+    st = O.make_settings()
+    want = O.render(sc, cam, st)
+    assert 0.05 < (want["hit_palette"] != 0).mean() and want["rays"].max() > 6
+    for trav in (TRAV_DENSE, TRAV_BRICK):
+        check(gpu_render(gpu_ctx, gs, cam, st, trav), want)
+    gs.destroy()
+
+
+# ------------------------------------------------------------------------------------------- structure + properties
+def test_brick_levels_match_cpu_builder(gpu_ctx):
+    rng = np.random.default_rng(21)
+    for whd in ((50, 37, 61), (64, 64, 64), (9, 130, 5)):
+        vol = random_volume(rng, whd, 0.01)
+        pal = random_palette(rng)
+        gs = pyvrt.VoxelScene.from_dense(gpu_ctx, vol, pal)
+        m, d = gs.download_accel()
+        h = harness()
+        hs = h.hh_scene_create(vol.ctypes.data_as(C.c_void_p), whd[0], whd[1], whd[2], pal.ctypes.data_as(C.c_void_p), None, None, 0, 0)
+        m2, d2 = np.zeros_like(m), np.zeros_like(d)
+        h.hh_scene_bmask(C.c_void_p(hs), m2.ctypes.data_as(C.c_void_p)); h.hh_scene_bdist(C.c_void_p(hs), d2.ctypes.data_as(C.c_void_p))
+        h.hh_scene_destroy(C.c_void_p(hs))
+        assert np.array_equal(m, m2) and np.array_equal(d, d2)
+        gs.destroy()
+
+
+def test_dense_and_brick_traversal_identical_at_4k(gpu_ctx):
+    """Size-independent property at BASELINE's full resolution: the acceleration changes no output byte."""
+    gs = pyvrt.VoxelScene.generate(gpu_ctx, 1, 42, 512, 256, 512)
+    gs.set_noise(assets.noise_standin()); gs.set_skybox(assets.sky_standin(512, 256))
+    cam = look_at_camera(gs.bounds, (3840, 2160), (30.3, 190.2, 25.1), (256, 120, 256), frame=1)
+    st = O.make_settings()
+    a = gpu_render(gpu_ctx, gs, cam, st, TRAV_DENSE); b = gpu_render(gpu_ctx, gs, cam, st, TRAV_BRICK)
+    for n, _, _ in O.PLANE_SPECS:
+        ok, bad = bits_equal(a[n], b[n]); assert ok, (n, bad)
+    hit = a["hit_palette"] != 0
+    assert 0.2 < hit.mean() < 1.0 and a["hit"][..., 3].max() <= 512
+    x, y, z = a["hit"][..., 0][hit].astype(int), a["hit"][..., 1][hit].astype(int), a["hit"][..., 2][hit].astype(int)
+    sub = slice(None, None, 997)
+    vol = gs.download_volume()
+    assert np.array_equal(vol[z[sub], y[sub], x[sub]], a["hit_palette"][hit][sub])
+    gs.destroy()
+
+
+def test_degenerate_rays_on_gpu(gpu_ctx):
+    rng = np.random.default_rng(9)
+    vol = random_volume(rng, (24, 24, 24), 0.04); pal = random_palette(rng)
+    sc, keep, gs = make_pair(gpu_ctx, vol, pal)
+    st = O.make_settings(light_dir=np.array([0, 1, 0], np.float32))     # zero components: literal inf/NaN path
+    cam = look_at_camera((24, 24, 24), (128, 96), (-8, 30, -9), (12, 12, 12))
+    check(gpu_render(gpu_ctx, gs, cam, st), O.render(sc, cam, st))
+    gs.destroy()
+    solid = np.full((12, 12, 12), 5, np.uint8)
+    sc, keep, gs = make_pair(gpu_ctx, solid, pal)
+    cam = default_camera((12, 12, 12), (64, 40), pos=(6.5, 6.5, 6.5))       # camera inside solid: step-0 hits, NaN normals
+    check(gpu_render(gpu_ctx, gs, cam, O.make_settings()), O.render(sc, cam, O.make_settings()))
+    gs.destroy()
+
+
+def test_empty_and_ragged_sizes(gpu_ctx):
+    pal = random_palette(np.random.default_rng(1))
+    sc, keep, gs = make_pair(gpu_ctx, np.zeros((5, 6, 7), np.uint8), pal)
+    cam = default_camera((7, 6, 5), (33, 17), pos=(3, 3, -10))          # not a multiple of the 8x4 warp patch or the 32x32 tile
+    got = gpu_render(gpu_ctx, gs, cam, O.make_settings())
+    check(got, O.render(sc, cam, O.make_settings()))
+    assert (got["hit_palette"] == 0).all() and got["_stats"]["pixels"] == 33 * 17
+    gs.destroy()
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_tile_sharded_frame_is_byte_identical(gpu_ctx, world):
+    """N ranks emulated one after another on one GPU (separate contexts); gather = concatenation, then vrt_assemble."""
+    import torch
+    rng = np.random.default_rng(31)
+    vol = random_volume(rng, (60, 40, 60), 0.02); pal = random_palette(rng)
+    noise, sky = assets.noise_standin(), assets.sky_standin(256, 128)
+    size = (300, 170)
+    cam = look_at_camera((60, 40, 60), size, (-20, 55, -25), (30, 20, 30))
+    st = O.make_settings()
+    gs = pyvrt.VoxelScene.from_dense(gpu_ctx, vol, pal); gs.set_noise(noise); gs.set_skybox(sky)
+    full = gpu_render(gpu_ctx, gs, cam, st, names=["color", "position", "hit", "hit_palette"])
+    gs.destroy()
+    shards = {n: [] for n in ("color", "position", "hit", "hit_palette")}
+    total = dict(rays=0, fetches=0, pixels=0)
+    for r in range(world):
+        ctx = pyvrt.Context(0, rank=r, world=world)
+        s = pyvrt.VoxelScene.from_dense(ctx, vol, pal); s.set_noise(noise); s.set_skybox(sky)
+        rp = pyvrt.VoxelRenderPass(ctx, s, vrt_settings(st)); fr = rp.record(cam_to_py(cam)); fr.sync()
+        for n in shards:
+            shards[n].append(fr.download(n))
+        stt = fr.stats()
+        for k in total:
+            total[k] += stt[k]
+        fr.release(); s.destroy(); ctx.close()
+    assert total["pixels"] == size[0] * size[1] and total["rays"] == full["_stats"]["rays"] and total["fetches"] == full["_stats"]["fetches"]
+    for n in shards:
+        gathered = torch.from_numpy(np.concatenate([x.view(np.uint8).ravel() for x in shards[n]])).cuda()
+        _, dt, ch = pyvrt.PLANES[pyvrt.PLANE_ID[n]]
+        out = torch.empty(size[0] * size[1] * ch * np.dtype(dt).itemsize, dtype=torch.uint8, device="cuda")
+        torch.cuda.synchronize()
+        pyvrt.assemble(gpu_ctx, gathered.data_ptr(), world, size, n, out.data_ptr())
+        gpu_ctx.sync()
+        res = out.cpu().numpy()
+        assert np.array_equal(res, full[n].view(np.uint8).ravel()), n
+
+
+def test_standalone_denoise_matches_oracle(gpu_ctx):
+    import torch
+    rng = np.random.default_rng(7)
+    h, w = 270, 480
+    color = rng.integers(0, 256, (h, w, 4), dtype=np.uint8); color[..., 3] = 0
+    normal = np.zeros((h, w, 4), np.int8); normal[..., :3] = rng.choice([-127, 0, 127], (h, w, 3))
+    pos = (rng.random((h, w, 4), dtype=np.float32) * 3); pos[..., 3] = 0
+    for mode in (0, 1):
+        for iters in (1, 2, 3):
+            ds = pyvrt.DenoiserSettings(1, iters, 20.4, 1e-2, 1e-1, 2.0, mode)
+            tc, tn, tp = torch.from_numpy(color).cuda(), torch.from_numpy(normal).cuda(), torch.from_numpy(pos).cuda()
+            out = torch.empty_like(tc)
+            torch.cuda.synchronize()
+            pyvrt.denoise_device(gpu_ctx, tc.data_ptr(), tn.data_ptr(), tp.data_ptr(), (w, h), ds, out.data_ptr())
+            gpu_ctx.sync()
+            want = O.denoise(color, normal, pos, iterations=iters, mode=mode)
+            d = np.abs(out.cpu().numpy().astype(int) - want.astype(int))
+            assert d.max() <= 1 and (d != 0).mean() < 2e-3, (mode, iters, d.max(), (d != 0).mean())

@@ -6,6 +6,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <new>
 #include <string>
 #include <vector>
@@ -82,6 +83,12 @@ extern "C" int vrt_device_info(vrt_context* c, int* sm_count, size_t* l2_bytes, 
     if (sm_count) *sm_count = c->prop.multiProcessorCount;
     if (l2_bytes) *l2_bytes = (size_t)c->prop.l2CacheSize;
     if (hbm_bytes) *hbm_bytes = c->prop.totalGlobalMem;
+    return VRT_OK;
+}
+extern "C" int vrt_context_sync(vrt_context* c) {
+    if (!c) return fail(VRT_E_INVALID, "ctx is null");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
     return VRT_OK;
 }
 extern "C" void* vrt_context_stream(vrt_context* c) { return c ? (void*)c->stream : nullptr; }
@@ -461,3 +468,18 @@ extern "C" void vrt_default_settings(vrt_render_settings* s) {
     s->denoise.enable = 1; s->denoise.iterations = 2; s->denoise.phiColor0 = 20.4f; s->denoise.phiNormal0 = 1E-2f;
     s->denoise.phiPos0 = 1E-1f; s->denoise.stepWidth = 2.0f; s->denoise.mode = VRT_DENOISE_AS_EXECUTED;
 }
+
+// Host-only .vox decode (no GPU needed): what vrt_scene_load_vox_memory uploads. Free *volume_out with vrt_host_free.
+extern "C" int vrt_vox_decode(const uint8_t* bytes, size_t n, uint8_t** volume_out, uint32_t whd[3], vrt_material palette[256]) {
+    if (!volume_out || !whd || !palette) return fail(VRT_E_INVALID, "null argument");
+    DenseScene ds; std::string err;
+    int rc = load_vox_bytes(bytes, n, ds, err);
+    if (rc) return fail(rc, err);
+    uint8_t* v = (uint8_t*)malloc(ds.volume.size());
+    if (!v) return fail(VRT_E_OOM, "host allocation failed");
+    memcpy(v, ds.volume.data(), ds.volume.size());
+    memcpy(palette, ds.palette, sizeof(vrt_material) * 256);
+    *volume_out = v; whd[0] = ds.w; whd[1] = ds.h; whd[2] = ds.d;
+    return VRT_OK;
+}
+extern "C" void vrt_host_free(void* p) { free(p); }

@@ -1,0 +1,269 @@
+"""ctypes binding of libvrt.so (include/vrt.h) for the bench and the tests, plus thin host-side mirrors of the
+reference's stage interface: VoxelScene (voxel_scene.hpp:18-34), GeometryStage.record -> GeometryBuffer
+(geometry_stage.hpp:19-27,53), DenoiserStage.record (denoiser_stage.hpp:45-46).
+
+The library is the product; this file only marshals arguments. If libvrt.so is missing or no CUDA device is
+present every entry point raises: there is no CPU fallback."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libvrt.so")
+
+PASS_PRIMARY, PASS_SHADOW, PASS_AO, PASS_REFLECT, PASS_SHADE, PASS_ALL = 1, 2, 4, 8, 16, 31
+OUT_GBUFFER, OUT_INSTRUMENT = 1, 2
+TRAVERSAL_DEFAULT, TRAVERSAL_DENSE_U8, TRAVERSAL_BRICK = 0, 1, 2
+DENOISE_AS_EXECUTED, DENOISE_AS_INTENDED = 0, 1
+E_LFS_POINTER, E_NO_INSTANCE, E_PARSE, E_IO, E_CUDA, E_NO_DEVICE = -2, -3, -4, -5, -6, -7
+
+# plane id -> (name, dtype, channels)
+PLANES = {0: ("color", np.uint8, 4), 1: ("denoised", np.uint8, 4), 2: ("depth", np.float32, 1), 3: ("motion", np.float32, 2),
+          4: ("mask", np.uint8, 1), 5: ("position", np.float32, 4), 6: ("normal", np.int8, 4), 7: ("hit", np.int16, 4),
+          8: ("hit_palette", np.uint8, 1), 9: ("color_f32", np.float32, 3), 10: ("rays", np.uint32, 1), 11: ("fetches", np.uint32, 1)}
+PLANE_ID = {v[0]: k for k, v in PLANES.items()}
+TILE = 32
+
+
+class Camera(C.Structure):
+    _fields_ = [("camPos", C.c_float * 4), ("camDir", C.c_float * 4), ("camRight", C.c_float * 4), ("camUp", C.c_float * 4),
+                ("volumeBounds", C.c_uint32 * 3), ("frame", C.c_uint32), ("screenSize", C.c_int32 * 2), ("cameraJitter", C.c_float * 2)]
+
+
+class VolumeParams(C.Structure):
+    _fields_ = [("aoSamples", C.c_uint32), ("ambientIntensity", C.c_float)]
+
+
+class Light(C.Structure):
+    _fields_ = [("direction", C.c_float * 3), ("intensity", C.c_float), ("color", C.c_float * 4)]
+
+
+class DenoiserSettings(C.Structure):
+    _fields_ = [("enable", C.c_int32), ("iterations", C.c_int32), ("phiColor0", C.c_float), ("phiNormal0", C.c_float),
+                ("phiPos0", C.c_float), ("stepWidth", C.c_float), ("mode", C.c_int32)]
+
+
+class RenderSettings(C.Structure):
+    _fields_ = [("pass_mask", C.c_uint32), ("out_mask", C.c_uint32), ("traversal", C.c_uint32), ("reserved", C.c_uint32),
+                ("vol", VolumeParams), ("light", Light), ("denoise", DenoiserSettings)]
+
+
+class FrameStats(C.Structure):
+    _fields_ = [("rays", C.c_uint64), ("fetches", C.c_uint64), ("pixels", C.c_uint64), ("ms_trace", C.c_float),
+                ("ms_denoise", C.c_float), ("ms_total", C.c_float), ("kernel_launches", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+class VrtError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"vrt error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise VrtError(-100, f"{LIB_PATH} is missing: build it with `make -C {HERE}` (there is no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        L.vrt_last_error.restype = C.c_char_p
+        L.vrt_version.restype = C.c_char_p
+        L.vrt_context_stream.restype = C.c_void_p
+        for fn in ("vrt_context_destroy", "vrt_scene_destroy", "vrt_frame_release", "vrt_host_free", "vrt_camera_vectors", "vrt_default_settings"):
+            getattr(L, fn).restype = None
+        _lib = L
+    return _lib
+
+
+def _ck(rc):
+    if rc != 0:
+        raise VrtError(rc, lib().vrt_last_error().decode())
+
+
+def default_settings() -> RenderSettings:
+    s = RenderSettings()
+    lib().vrt_default_settings(C.byref(s))
+    return s
+
+
+def camera_vectors(yaw, pitch, focal):
+    d, r, u = (C.c_float * 3)(), (C.c_float * 3)(), (C.c_float * 3)()
+    lib().vrt_camera_vectors(C.c_float(yaw), C.c_float(pitch), C.c_float(focal), d, r, u)
+    return np.array(d[:], np.float32), np.array(r[:], np.float32), np.array(u[:], np.float32)
+
+
+def make_camera(pos, yaw, pitch, bounds_whd, size, frame=0, jitter=(0.0, 0.0), focal=None) -> Camera:
+    """Push constants as VoxelRenderer::recordCommands fills them (voxel_renderer.cpp:72-81)."""
+    if focal is None:
+        focal = float(np.float32(1.0 / np.tan(np.radians(55.0 / 2))))   # voxel_renderer.cpp:20
+    d, r, u = camera_vectors(yaw, pitch, focal)
+    c = Camera()
+    for k in range(3):
+        c.camPos[k], c.camDir[k], c.camRight[k], c.camUp[k] = float(pos[k]), d[k], r[k], u[k]
+    c.camPos[3] = 1.0
+    c.volumeBounds[:] = [int(b) for b in bounds_whd]
+    c.frame = int(frame)
+    c.screenSize[:] = [int(size[0]), int(size[1])]
+    c.cameraJitter[:] = [float(jitter[0]), float(jitter[1])]
+    return c
+
+
+def vox_decode(data: bytes):
+    """Host-only decode of .vox bytes -> (volume[D,H,W] uint8, palette[256,8] float32). No GPU involved."""
+    buf = (C.c_uint8 * len(data)).from_buffer_copy(data)
+    vol = C.c_void_p(); whd = (C.c_uint32 * 3)(); pal = np.zeros((256, 8), np.float32)
+    _ck(lib().vrt_vox_decode(buf, C.c_size_t(len(data)), C.byref(vol), whd, pal.ctypes.data_as(C.c_void_p)))
+    w, h, d = whd[0], whd[1], whd[2]
+    arr = np.ctypeslib.as_array(C.cast(vol, C.POINTER(C.c_uint8)), shape=(d, h, w)).copy()
+    lib().vrt_host_free(vol)
+    return arr, pal
+
+
+class Context:
+    def __init__(self, device=0, rank=0, world=1):
+        self.h = C.c_void_p()
+        _ck(lib().vrt_context_create(int(device), C.byref(self.h)))
+        self.rank, self.world, self.device = rank, world, device
+        if world != 1:
+            _ck(lib().vrt_context_set_shard(self.h, rank, world))
+
+    def device_info(self):
+        sm = C.c_int(); l2 = C.c_size_t(); hbm = C.c_size_t()
+        _ck(lib().vrt_device_info(self.h, C.byref(sm), C.byref(l2), C.byref(hbm)))
+        return dict(sm_count=sm.value, l2_bytes=l2.value, hbm_bytes=hbm.value)
+
+    def sync(self):
+        _ck(lib().vrt_context_sync(self.h))
+
+    @property
+    def stream(self):
+        return lib().vrt_context_stream(self.h)
+
+    def close(self):
+        if self.h:
+            lib().vrt_context_destroy(self.h); self.h = C.c_void_p()
+
+
+class VoxelScene:
+    """Mirror of the reference's VoxelScene: width/height/depth + resident volume, palette, skybox."""
+
+    def __init__(self, ctx: Context, handle):
+        self.ctx, self.h = ctx, handle
+        whd = (C.c_uint32 * 3)()
+        _ck(lib().vrt_scene_bounds(self.h, whd))
+        self.width, self.height, self.depth = whd[0], whd[1], whd[2]
+
+    @property
+    def bounds(self):
+        return (self.width, self.height, self.depth)
+
+    @classmethod
+    def from_vox_file(cls, ctx, path):
+        h = C.c_void_p(); _ck(lib().vrt_scene_load_vox(ctx.h, path.encode(), C.byref(h))); return cls(ctx, h)
+
+    @classmethod
+    def from_vox_bytes(cls, ctx, data: bytes):
+        buf = (C.c_uint8 * len(data)).from_buffer_copy(data)
+        h = C.c_void_p(); _ck(lib().vrt_scene_load_vox_memory(ctx.h, buf, C.c_size_t(len(data)), C.byref(h))); return cls(ctx, h)
+
+    @classmethod
+    def from_dense(cls, ctx, volume, palette):
+        volume = np.ascontiguousarray(volume, np.uint8); palette = np.ascontiguousarray(palette, np.float32).reshape(256, 8)
+        d, hh, w = volume.shape
+        h = C.c_void_p()
+        _ck(lib().vrt_scene_from_dense(ctx.h, volume.ctypes.data_as(C.c_void_p), w, hh, d, palette.ctypes.data_as(C.c_void_p), C.byref(h)))
+        return cls(ctx, h)
+
+    @classmethod
+    def generate(cls, ctx, generator, seed, w, h_, d):
+        h = C.c_void_p(); _ck(lib().vrt_scene_generate(ctx.h, int(generator), C.c_uint64(seed), w, h_, d, C.byref(h))); return cls(ctx, h)
+
+    def set_noise(self, rgba8):
+        a = np.ascontiguousarray(rgba8, np.uint8); _ck(lib().vrt_scene_set_noise(self.h, a.ctypes.data_as(C.c_void_p), a.shape[1], a.shape[0]))
+
+    def set_skybox(self, rgba32f):
+        a = np.ascontiguousarray(rgba32f, np.float32); _ck(lib().vrt_scene_set_skybox(self.h, a.ctypes.data_as(C.c_void_p), a.shape[1], a.shape[0]))
+
+    def palette(self):
+        p = np.zeros((256, 8), np.float32); _ck(lib().vrt_scene_palette(self.h, p.ctypes.data_as(C.c_void_p))); return p
+
+    def download_volume(self):
+        v = np.zeros((self.depth, self.height, self.width), np.uint8)
+        _ck(lib().vrt_scene_download_volume(self.h, v.ctypes.data_as(C.c_void_p), C.c_size_t(v.size))); return v
+
+    def download_accel(self):
+        bx, by, bz = (self.width + 3) // 4, (self.height + 3) // 4, (self.depth + 3) // 4
+        m = np.zeros((bz, by, bx), np.uint64); dd = np.zeros((bz, by, bx), np.uint8)
+        _ck(lib().vrt_scene_download_accel(self.h, m.ctypes.data_as(C.c_void_p), dd.ctypes.data_as(C.c_void_p))); return m, dd
+
+    def accel_info(self):
+        a, b, c = C.c_size_t(), C.c_size_t(), C.c_size_t()
+        _ck(lib().vrt_scene_accel_info(self.h, C.byref(a), C.byref(b), C.byref(c)))
+        return dict(dense_bytes=a.value, brick_mask_bytes=b.value, brick_dist_bytes=c.value)
+
+    def destroy(self):
+        if self.h:
+            lib().vrt_scene_destroy(self.h); self.h = C.c_void_p()
+
+
+class Frame:
+    """Mirror of GeometryBuffer: named planes living in device memory."""
+
+    def __init__(self, ctx):
+        self.ctx, self.h, self.size = ctx, C.c_void_p(), None
+
+    def sync(self):
+        _ck(lib().vrt_frame_sync(self.h))
+
+    def plane_ptr(self, name):
+        p = C.c_void_p(); n = C.c_size_t()
+        _ck(lib().vrt_frame_plane(self.h, PLANE_ID[name], C.byref(p), C.byref(n))); return p.value, n.value
+
+    def download(self, name, out=None):
+        _, dt, ch = PLANES[PLANE_ID[name]]
+        _, nbytes = self.plane_ptr(name)
+        if out is None:
+            out = np.empty(nbytes // np.dtype(dt).itemsize, dt)
+        _ck(lib().vrt_frame_download(self.h, PLANE_ID[name], out.ctypes.data_as(C.c_void_p), C.c_size_t(nbytes)))
+        if self.ctx.world == 1:
+            W, H = self.size
+            return out.reshape((H, W, ch) if ch > 1 else (H, W))
+        return out
+
+    def stats(self) -> dict:
+        s = FrameStats(); _ck(lib().vrt_frame_stats_get(self.h, C.byref(s)))
+        return {k: getattr(s, k) for k, _ in FrameStats._fields_ if k != "reserved"}
+
+    def release(self):
+        if self.h:
+            lib().vrt_frame_release(self.h); self.h = C.c_void_p()
+
+
+class VoxelRenderPass:
+    """GeometryStage + DenoiserStage as one headless pass: record() launches asynchronously on the context stream
+    (the reference records a command buffer) and returns the Frame; Frame.sync() is the fence wait."""
+
+    def __init__(self, ctx: Context, scene: VoxelScene, settings: RenderSettings | None = None):
+        self.ctx, self.scene = ctx, scene
+        self.settings = settings if settings is not None else default_settings()
+        self.frame = Frame(ctx)
+
+    def record(self, camera: Camera) -> Frame:
+        size = (camera.screenSize[0], camera.screenSize[1])
+        if self.frame.size not in (None, size):
+            self.frame.release()
+        _ck(lib().vrt_render(self.ctx.h, self.scene.h, C.byref(camera), C.byref(self.settings), C.byref(self.frame.h)))
+        self.frame.size = size
+        return self.frame
+
+
+def assemble(ctx: Context, d_gathered_ptr: int, world: int, size, plane: str, d_out_ptr: int):
+    _ck(lib().vrt_assemble(ctx.h, C.c_void_p(d_gathered_ptr), world, size[0], size[1], PLANE_ID[plane], C.c_void_p(d_out_ptr)))
+
+
+def denoise_device(ctx: Context, d_color, d_normal, d_position, size, ds: DenoiserSettings, d_out):
+    _ck(lib().vrt_denoise(ctx.h, C.c_void_p(d_color), C.c_void_p(d_normal), C.c_void_p(d_position), size[0], size[1], C.byref(ds), C.c_void_p(d_out)))
