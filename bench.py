@@ -1,0 +1,355 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the voxel_volume render pass (BASELINE.json: Mrays/s and ms/frame at 4K on the
+synthetic 1024^3 volume; 1/2/4/8 B200).
+
+    python bench.py --gpus 1 --steps K --warmup W              # the CUDA path through the C ABI (libvrt.so)
+    torchrun --nproc-per-node N ... bench.py --gpus N ...      # image tiles sharded over N GPUs, frame gathered on rank 0
+    python bench.py --impl reference --steps K --warmup W      # the reference algorithm on the host cores (oracle port)
+
+A step = one frame of the camera path of the config (camera and noise frame index change every step).
+Prints ONE JSON line (rank 0). The product path never touches oracle/: only the cpu_baseline leg and the
+--impl reference arm do."""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "voxel-raytracing_b200"))
+
+METRIC, UNIT = "Mrays/s", "Mrays/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="vrt", choices=["vrt", "reference"])
+    ap.add_argument("--config", default="cfg4")
+    ap.add_argument("--whd", type=int, nargs=3, default=None, help="override the synthetic volume size (debug)")
+    ap.add_argument("--size", type=int, nargs=2, default=None, help="override the resolution (debug)")
+    ap.add_argument("--traversal", type=int, default=0, help="0 default, 1 dense u8, 2 brick")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
+    return ap.parse_args()
+
+
+# ----------------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """Samples nvidia-smi clocks and throttle reasons during the timed region (B200_PROFILING.md clocks line)."""
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, device):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(device)],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush(); self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 8:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, c[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        try:
+            os.unlink(self.f.name)
+        except OSError:
+            pass
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        # median over the upper half: samples taken between frames (idle) would drag a plain median down
+        busy = sorted(sm)[len(sm) // 2:]
+        return {"sm_mhz": float(np.median(busy)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def ncu_traffic():
+    """Per-launch DRAM traffic of the dominant kernel from the committed ncu summary, if one exists."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p)).get("render_kernel_dram_bytes_per_launch")
+        except Exception:
+            return None
+    return None
+
+
+# ----------------------------------------------------------------------------------------------- oracle legs
+def oracle_scene_for(cfg, whd):
+    """CPU-side inputs of the same workload (oracle leg only)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle as O
+    import synth
+    import assets
+    kind, what, kw = cfg["scene"]
+    if kind == "gen":
+        w, h, d = whd or kw["whd"]
+        vol = O.generate(what, kw["seed"], w, h, d)
+        pal = synth.generator_palette(what, kw["seed"])
+    else:
+        import configs
+        rc, vol, pal = O.load_vox(open(configs.standin_vox_path(what, **kw), "rb").read())
+        assert rc == 0
+    sc, keep = O.make_scene(vol, pal, assets.noise_standin(), assets.sky_standin(2048, 1024))
+    return O, sc, keep, (vol.shape[2], vol.shape[1], vol.shape[0])
+
+
+def oracle_camera(O, name, bounds, size, k):
+    import configs
+    pos, yaw, pitch, frame = configs.camera_pose(name, bounds, k)
+    focal = float(np.float32(1.0 / np.tan(np.radians(55.0 / 2))))
+    d, r, u = O.camera_vectors(yaw, pitch, focal)
+    return O.make_camera(pos, d, r, u, bounds, size, frame)
+
+
+def oracle_timed(O, sc, cam, st, row_step, nthreads=0):
+    H = cam.screenSize[1]
+    t0 = time.perf_counter()
+    out = O.render(sc, cam, st, rows=(0, H, row_step), nthreads=nthreads, planes=["color", "rays", "fetches"])
+    dt = time.perf_counter() - t0
+    return dt, int(out["rays"].sum()), int(out["fetches"].sum())
+
+
+def cpu_baseline(cfg, name, whd, size, target_s):
+    O, sc, keep, bounds = oracle_scene_for(cfg, whd)
+    st = O.make_settings(pass_mask=cfg["passes"], ao=cfg["ao"])
+    cam = oracle_camera(O, name, bounds, size, 0)
+    cores = O.lib().orc_num_threads()
+    dt, rays, _ = oracle_timed(O, sc, cam, st, 32)                       # calibration: every 32nd row
+    step = int(min(32, max(1, round(32 * dt / max(target_s, 1e-3)))))
+    if step < 32:
+        dt, rays, _ = oracle_timed(O, sc, cam, st, step)
+    return {"value": rays / dt / 1e6, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"frame 0 of the workload, every {step}th row ({size[1] // step} of {size[1]} rows), {dt:.1f} s, oracle port with OpenMP over rows"}
+
+
+def config_blob(cfg, name, whd, size, extra):
+    kind, what, kw = cfg["scene"]
+    blob = {"workload": f"{name}: {cfg['label']}", "volume": list(whd) if whd else list(kw.get("whd", [])) or what,
+            "resolution": list(size), "pass_mask": cfg["passes"], "aoSamples": cfg["ao"], "denoiser": bool(cfg["denoise"]),
+            "l2": "inputs larger than L2 (1 GiB volume + 144 MiB brick levels vs 126 MB); camera pose and noise frame index change every step"}
+    blob.update(extra)
+    return blob
+
+
+# ----------------------------------------------------------------------------------------------- reference arm
+def run_reference(args):
+    """The reference algorithm (CPU restatement of voxel_volume.frag: oracle/) on all host cores. Each step renders a
+    bounded row sample of that step's frame. Rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    import configs
+    cfg = configs.CONFIGS[args.config]
+    size = tuple(args.size) if args.size else cfg["size"]
+    O, sc, keep, bounds = oracle_scene_for(cfg, args.whd)
+    st = O.make_settings(pass_mask=cfg["passes"], ao=cfg["ao"])
+    cores = O.lib().orc_num_threads()
+    # calibrate the per-step sample to ~2 s of host work
+    dt, _, _ = oracle_timed(O, sc, oracle_camera(O, args.config, bounds, size, 0), st, 64)
+    step = int(min(64, max(1, round(64 * dt / 2.0))))
+    for k in range(args.warmup):
+        oracle_timed(O, sc, oracle_camera(O, args.config, bounds, size, k), st, step)
+    rays = fetches = 0
+    t = 0.0
+    for k in range(args.steps):
+        dt, r, f = oracle_timed(O, sc, oracle_camera(O, args.config, bounds, size, k), st, step)
+        t += dt; rays += r; fetches += f
+    val = rays / t / 1e6
+    sample = f"every {step}th row of each frame ({size[1] // step} of {size[1]} rows per step), {t:.1f} s total"
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": config_blob(cfg, args.config, args.whd, size, {"note": "reference has no CPU implementation and its Vulkan path is unavailable on this box; "
+                                                                               "this is the CPU restatement of shader/voxel_volume.frag (oracle port), OpenMP over rows"}),
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0, "algorithmic_bytes_per_s": fetches / t}
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------------------------- the CUDA arm
+class _DevBuf:
+    """Wraps a device pointer owned by libvrt so torch.distributed can move it (no copy)."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
+
+
+def run_vrt(args):
+    import torch
+    import torch.distributed as dist
+    import pyvrt
+    import configs
+
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch N>1 with torch.distributed.run")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    cfg = configs.CONFIGS[args.config]
+    size = tuple(args.size) if args.size else cfg["size"]
+    W, H = size
+
+    ctx = pyvrt.Context(local, rank=rank, world=world)       # raises without a GPU: there is no CPU fallback
+    scene = configs.build_scene(ctx, cfg, args.whd)
+    bounds = scene.bounds
+    st = configs.settings_for(cfg, gbuffer=True)
+    st.traversal = args.traversal
+    rp = pyvrt.VoxelRenderPass(ctx, scene, st)
+    ext = torch.cuda.ExternalStream(ctx.stream, device=torch.device("cuda", local))
+    final = "denoised" if cfg["denoise"] and world == 1 else "color"
+    frame_bytes = W * H * 4
+    host_frame = torch.empty(frame_bytes, dtype=torch.uint8, pin_memory=True) if rank == 0 else None
+    gathered = assembled = None
+    if world > 1 and rank == 0:
+        assembled = torch.empty(frame_bytes, dtype=torch.uint8, device="cuda")
+
+    def step(k, download=False):
+        """One frame: render this rank's tiles; N>1: gather the colour shards on rank 0 and assemble the frame."""
+        nonlocal gathered
+        cam = configs.make_camera(args.config, bounds, size, k)
+        fr = rp.record(cam)
+        launches = 1 + (cfg["denoise"] and world == 1) * st.denoise.iterations
+        if world > 1:
+            ptr, n = fr.plane_ptr("color")
+            shard = torch.as_tensor(_DevBuf(ptr, n), device=torch.device("cuda", local))
+            with torch.cuda.stream(ext):
+                if rank == 0:
+                    if gathered is None:
+                        gathered = torch.empty((world, n), dtype=torch.uint8, device="cuda")
+                    dist.gather(shard, list(gathered.unbind(0)), dst=0)
+                    pyvrt.assemble(ctx, gathered.data_ptr(), world, size, "color", assembled.data_ptr())
+                    launches += 1
+                else:
+                    dist.gather(shard, None, dst=0)
+        if download and rank == 0:
+            if world > 1:
+                with torch.cuda.stream(ext):
+                    host_frame.copy_(assembled, non_blocking=True)
+                ctx.sync()
+            else:
+                fr.download(final, out=host_frame.numpy())
+        return fr, launches
+
+    def barrier():
+        ctx.sync(); torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    # ---- warm-up, then an untimed counting pass over the K timed poses (rays / voxel visits / kernel time per frame)
+    for k in range(args.warmup):
+        step(k)
+    barrier()
+    rays = fetches = pixels = 0
+    ms_kernel = []
+    for k in range(args.steps):
+        fr, _ = step(k)
+        s = fr.stats()
+        rays += s["rays"]; fetches += s["fetches"]; pixels += s["pixels"]; ms_kernel.append(s["ms_trace"])
+    barrier()
+
+    # ---- timed region 1: K frames, inputs resident, device time on the launching stream, max over ranks
+    sampler = ClockSampler(local) if rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches = 0
+    barrier()
+    with torch.cuda.stream(ext):
+        e0.record()
+    for k in range(args.steps):
+        _, n = step(k)
+        launches += n
+    with torch.cuda.stream(ext):
+        e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if sampler else None
+
+    # ---- timed region 2 (e2e): the same K frames through the public API with the finished frame read back into
+    # pinned host memory every step; per-step inputs (camera block + settings) travel as kernel parameters
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        step(k, download=True)
+    barrier()
+    t_e2e = time.perf_counter() - t0
+
+    tot = torch.tensor([float(rays), float(fetches), float(pixels)], dtype=torch.float64, device="cuda")
+    mx = torch.tensor([ms, t_e2e], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tot); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    rays_all, fetches_all, pixels_all = [float(x) for x in tot.tolist()]
+    ms, t_e2e = [float(x) for x in mx.tolist()]
+
+    if rank == 0:
+        peak, peak_src = measured_peaks()
+        b_out = 37 if (st.out_mask & pyvrt.OUT_GBUFFER) else 4
+        alg_bytes = (fetches + pixels * b_out) / args.steps                  # this rank's render kernel, per launch
+        k_ms = float(np.mean(ms_kernel))
+        achieved = alg_bytes / (k_ms * 1e-3) / 1e9
+        line = {"metric": METRIC, "value": rays_all / (ms * 1e-3) / 1e6, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": config_blob(cfg, args.config, args.whd, size, {"parallelism": f"tiles{world}" if world > 1 else "single", "traversal": args.traversal,
+                                                                         "gathered_plane": "color RGBA8" if world > 1 else None}),
+                "rays_per_frame": rays_all / args.steps, "voxel_visits_per_frame": fetches_all / args.steps,
+                "Mrays_per_s_primary": pixels_all / (ms * 1e-3) / 1e6,
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(),
+                             "kernel": "render_kernel", "kernel_ms": k_ms, "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
+                             "note": "algorithmic bytes = getVoxel calls of the reference loop x 1 B + pixels x %d B of G-buffer; the loop is issue-bound, not bandwidth-bound (DESIGN.md)" % b_out},
+                "e2e": {"value": rays_all / t_e2e / 1e6, "unit": UNIT, "h2d_bytes_per_step": C.sizeof(pyvrt.Camera) + C.sizeof(pyvrt.RenderSettings),
+                        "d2h_bytes_per_step": frame_bytes, "ms_per_step": 1e3 * t_e2e / args.steps},
+                "gpu_launches": launches, "clocks": clocks}
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(cfg, args.config, args.whd, size, args.cpu_seconds)
+        print(json.dumps(line), flush=True)
+    barrier()
+    scene.destroy(); ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_vrt(a)

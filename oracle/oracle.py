@@ -152,6 +152,14 @@ def denoise(color, normal, position, iterations=2, phi_color=20.4, phi_normal=1e
     return out
 
 
+def generate(generator, seed, w, h, d):
+    vol = np.empty((d, h, w), np.uint8)
+    rc = lib().orc_generate(int(generator), C.c_uint32(seed & 0xFFFFFFFF), _ptr(vol), w, h, d)
+    if rc != 0:
+        raise RuntimeError(f"orc_generate failed: {rc}")
+    return vol
+
+
 def _load_vox_with(fn, data: bytes):
     buf = (C.c_uint8 * len(data)).from_buffer_copy(data)
     vol = C.c_void_p(); whd = (C.c_uint32 * 3)(); pal = np.zeros((256, 8), np.float32)

@@ -80,6 +80,8 @@ void orc_camera_vectors(float yaw_deg, float pitch_deg, float focal, float dir[3
  * Returns 0, or <0 on error (-2 = git-LFS pointer stub). Caller frees with orc_free. */
 int orc_load_vox(const uint8_t* bytes, size_t n, uint8_t** volume, uint32_t whd[3], float palette[256 * 8]);
 void orc_free(void* p);
+/* synthetic volumes of BASELINE configs 4/5: 1 = noise terrain, 2 = sparse lattice shapes */
+int orc_generate(int generator, uint32_t seed, uint8_t* vol, uint32_t W, uint32_t H, uint32_t D);
 int orc_num_threads(void);
 
 #ifdef __cplusplus
