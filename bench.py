@@ -39,6 +39,9 @@ def parse_args():
     ap.add_argument("--whd", type=int, nargs=3, default=None, help="override the synthetic volume size (debug)")
     ap.add_argument("--size", type=int, nargs=2, default=None, help="override the resolution (debug)")
     ap.add_argument("--traversal", type=int, default=0, help="0 default, 1 dense u8, 2 brick")
+    ap.add_argument("--passes", type=int, default=None, help="override the pass mask (measurement of pass subsets)")
+    ap.add_argument("--ao", type=int, default=None, help="override aoSamples")
+    ap.add_argument("--no-gbuffer", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
     return ap.parse_args()
@@ -226,14 +229,18 @@ def run_vrt(args):
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    cfg = configs.CONFIGS[args.config]
+    cfg = dict(configs.CONFIGS[args.config])
+    if args.passes is not None:
+        cfg["passes"] = args.passes
+    if args.ao is not None:
+        cfg["ao"] = args.ao
     size = tuple(args.size) if args.size else cfg["size"]
     W, H = size
 
     ctx = pyvrt.Context(local, rank=rank, world=world)       # raises without a GPU: there is no CPU fallback
     scene = configs.build_scene(ctx, cfg, args.whd)
     bounds = scene.bounds
-    st = configs.settings_for(cfg, gbuffer=True)
+    st = configs.settings_for(cfg, gbuffer=not args.no_gbuffer)
     st.traversal = args.traversal
     rp = pyvrt.VoxelRenderPass(ctx, scene, st)
     ext = torch.cuda.ExternalStream(ctx.stream, device=torch.device("cuda", local))

@@ -46,10 +46,38 @@ static void build_bricks(const uint8_t* vol, uint32_t W, uint32_t H, uint32_t D,
     bdist = cur;
 }
 
+// CPU restatement of the per-voxel safe-step field builder (csrc/vrt_accel.cu launch_build_fdist)
+static void build_fdist(const uint8_t* vol, int W, int H, int D, const std::vector<uint8_t>& bdist, uint32_t Bx, uint32_t By, uint32_t Bz,
+                        std::vector<uint8_t>& fdist) {
+    const size_t n = (size_t)W * H * D;
+    std::vector<uint8_t> a(n), nx(n);
+    for (size_t i = 0; i < n; i++) a[i] = vol[i] ? 0 : VRT_FINE_CAP;
+    auto at = [&](const std::vector<uint8_t>& v, int x, int y, int z) -> int {
+        return (x < 0 || y < 0 || z < 0 || x >= W || y >= H || z >= D) ? 0 : v[(size_t)x + (size_t)y * W + (size_t)z * W * H]; };
+    for (int r = 1; r < VRT_FINE_CAP; r++) {
+        for (int z = 0; z < D; z++) for (int y = 0; y < H; y++) for (int x = 0; x < W; x++) {
+            int mn = 255;
+            for (int dz = -1; dz <= 1; dz++) for (int dy = -1; dy <= 1; dy++) for (int dx = -1; dx <= 1; dx++) mn = std::min(mn, at(a, x + dx, y + dy, z + dz));
+            const size_t v = (size_t)x + (size_t)y * W + (size_t)z * W * H;
+            nx[v] = (uint8_t)std::min((int)a[v], mn + 1);
+        }
+        a.swap(nx);
+    }
+    fdist.assign((size_t)Bx * By * Bz * 64, 0);
+    for (int z = 0; z < D; z++) for (int y = 0; y < H; y++) for (int x = 0; x < W; x++) {
+        const uint32_t f = a[(size_t)x + (size_t)y * W + (size_t)z * W * H];
+        const size_t b = (size_t)(z >> 2) * By * Bx + (size_t)(y >> 2) * Bx + (x >> 2);
+        const uint32_t d = bdist[b];
+        uint32_t v = f;
+        if (f != 0 && d != 0) v = std::max(f, (d - 1u) * 4u + 1u);
+        fdist[b * 64 + ((x & 3) | ((y & 3) << 2) | ((z & 3) << 4))] = (uint8_t)std::min(v, 255u);
+    }
+}
+
 struct HScene {
     SceneDev dev;
     std::vector<unsigned long long> bmask;
-    std::vector<uint8_t> bdist;
+    std::vector<uint8_t> bdist, fdist;
 };
 
 extern "C" void* hh_scene_create(const uint8_t* vol, uint32_t W, uint32_t H, uint32_t D, const float* palette,
@@ -58,13 +86,15 @@ extern "C" void* hh_scene_create(const uint8_t* vol, uint32_t W, uint32_t H, uin
     memset(&s->dev, 0, sizeof(SceneDev));
     s->dev.vol = vol; s->dev.W = W; s->dev.H = H; s->dev.D = D;
     build_bricks(vol, W, H, D, s->bmask, s->bdist, s->dev.Bx, s->dev.By, s->dev.Bz);
-    s->dev.bmask = s->bmask.data(); s->dev.bdist = s->bdist.data();
+    build_fdist(vol, (int)W, (int)H, (int)D, s->bdist, s->dev.Bx, s->dev.By, s->dev.Bz, s->fdist);
+    s->dev.bmask = s->bmask.data(); s->dev.bdist = s->bdist.data(); s->dev.fdist = s->fdist.data();
     s->dev.palette = reinterpret_cast<const vrt_material*>(palette);
     s->dev.noise = noise; s->dev.sky = sky; s->dev.skyW = skyW; s->dev.skyH = skyH;
     return s;
 }
 extern "C" void hh_scene_destroy(void* p) { delete (HScene*)p; }
 extern "C" void hh_scene_bdist(void* p, uint8_t* out) { HScene* s = (HScene*)p; memcpy(out, s->bdist.data(), s->bdist.size()); }
+extern "C" void hh_scene_fdist(void* p, uint8_t* out) { HScene* s = (HScene*)p; memcpy(out, s->fdist.data(), s->fdist.size()); }
 extern "C" void hh_scene_bmask(void* p, unsigned long long* out) { HScene* s = (HScene*)p; memcpy(out, s->bmask.data(), 8 * s->bmask.size()); }
 
 extern "C" int hh_render(void* scene, const vrt_camera* cam, const vrt_render_settings* st, int traversal, const PlanesDev* pl,
@@ -82,6 +112,7 @@ extern "C" int hh_render(void* scene, const vrt_camera* cam, const vrt_render_se
         for (int px = 0; px < W; px++) {
             PixelOut o; memset(&o, 0, sizeof(o));
             if (traversal == VRT_TRAVERSAL_DENSE_U8) render_pixel<VRT_TRAVERSAL_DENSE_U8>(s->dev, fp, px, py, o);
+            else if (traversal == VRT_TRAVERSAL_FINE) render_pixel<VRT_TRAVERSAL_FINE>(s->dev, fp, px, py, o);
             else render_pixel<VRT_TRAVERSAL_BRICK>(s->dev, fp, px, py, o);
             size_t p = (size_t)py * W + px;
             auto sat = [](int v) { return (int16_t)(v < -32768 ? -32768 : (v > 32767 ? 32767 : v)); };

@@ -6,7 +6,7 @@ import ctypes as C
 import numpy as np
 import pytest
 
-from vrtlib import (O, assets, TRAV_BRICK, TRAV_DENSE, harness, default_camera, look_at_camera, random_volume, random_palette,
+from vrtlib import (O, assets, TRAV_BRICK, TRAV_DENSE, TRAV_FINE, ALL_TRAVERSALS, harness, default_camera, look_at_camera, random_volume, random_palette,
                     bits_equal, cached_vox, to_vrt_camera)
 import pyvrt
 import synth
@@ -72,7 +72,7 @@ def test_cfg1_treehouse_standin_primary_720p(gpu_ctx):
     cam = default_camera((126, 126, 126), (1280, 720))
     st = O.make_settings(pass_mask=O.PASS_PRIMARY)
     want = O.render(sc, cam, st)
-    for trav in (TRAV_DENSE, TRAV_BRICK):
+    for trav in ALL_TRAVERSALS:
         check(gpu_render(gpu_ctx, gs, cam, st, trav), want)
     gs.destroy()
 
@@ -119,7 +119,7 @@ def test_cfg4_cfg5_synthetic_generators_and_full_pass(gpu_ctx, gen, whd, pos, ta
     st = O.make_settings()
     want = O.render(sc, cam, st)
     assert 0.05 < (want["hit_palette"] != 0).mean() and want["rays"].max() > 6
-    for trav in (TRAV_DENSE, TRAV_BRICK):
+    for trav in ALL_TRAVERSALS:
         check(gpu_render(gpu_ctx, gs, cam, st, trav), want)
     gs.destroy()
 
@@ -127,7 +127,7 @@ def test_cfg4_cfg5_synthetic_generators_and_full_pass(gpu_ctx, gen, whd, pos, ta
 # ------------------------------------------------------------------------------------------- structure + properties
 def test_brick_levels_match_cpu_builder(gpu_ctx):
     rng = np.random.default_rng(21)
-    for whd in ((50, 37, 61), (64, 64, 64), (9, 130, 5)):
+    for whd in ((50, 37, 61), (64, 64, 64), (9, 130, 5), (128, 20, 36)):
         vol = random_volume(rng, whd, 0.01)
         pal = random_palette(rng)
         gs = pyvrt.VoxelScene.from_dense(gpu_ctx, vol, pal)
@@ -136,8 +136,11 @@ def test_brick_levels_match_cpu_builder(gpu_ctx):
         hs = h.hh_scene_create(vol.ctypes.data_as(C.c_void_p), whd[0], whd[1], whd[2], pal.ctypes.data_as(C.c_void_p), None, None, 0, 0)
         m2, d2 = np.zeros_like(m), np.zeros_like(d)
         h.hh_scene_bmask(C.c_void_p(hs), m2.ctypes.data_as(C.c_void_p)); h.hh_scene_bdist(C.c_void_p(hs), d2.ctypes.data_as(C.c_void_p))
+        f2 = np.zeros(m.shape + (4, 4, 4), np.uint8)
+        h.hh_scene_fdist(C.c_void_p(hs), f2.ctypes.data_as(C.c_void_p))
         h.hh_scene_destroy(C.c_void_p(hs))
         assert np.array_equal(m, m2) and np.array_equal(d, d2)
+        assert np.array_equal(gs.download_fdist(), f2)
         gs.destroy()
 
 
@@ -147,9 +150,11 @@ def test_dense_and_brick_traversal_identical_at_4k(gpu_ctx):
     gs.set_noise(assets.noise_standin()); gs.set_skybox(assets.sky_standin(512, 256))
     cam = look_at_camera(gs.bounds, (3840, 2160), (30.3, 190.2, 25.1), (256, 120, 256), frame=1)
     st = O.make_settings()
-    a = gpu_render(gpu_ctx, gs, cam, st, TRAV_DENSE); b = gpu_render(gpu_ctx, gs, cam, st, TRAV_BRICK)
-    for n, _, _ in O.PLANE_SPECS:
-        ok, bad = bits_equal(a[n], b[n]); assert ok, (n, bad)
+    a = gpu_render(gpu_ctx, gs, cam, st, TRAV_DENSE)
+    for trav in (TRAV_BRICK, TRAV_FINE):
+        b = gpu_render(gpu_ctx, gs, cam, st, trav)
+        for n, _, _ in O.PLANE_SPECS:
+            ok, bad = bits_equal(a[n], b[n]); assert ok, (trav, n, bad)
     hit = a["hit_palette"] != 0
     assert 0.2 < hit.mean() < 1.0 and a["hit"][..., 3].max() <= 512
     x, y, z = a["hit"][..., 0][hit].astype(int), a["hit"][..., 1][hit].astype(int), a["hit"][..., 2][hit].astype(int)

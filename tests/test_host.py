@@ -7,7 +7,7 @@ import re
 import numpy as np
 import pytest
 
-from vrtlib import (O, assets, ROOT, TRAV_BRICK, TRAV_DENSE, harness_render, default_camera, look_at_camera, random_volume,
+from vrtlib import (O, assets, ROOT, TRAV_BRICK, TRAV_DENSE, TRAV_FINE, ALL_TRAVERSALS, harness_render, default_camera, look_at_camera, random_volume,
                     random_palette, assert_planes_exact, cached_vox)
 import pyvrt
 
@@ -80,7 +80,7 @@ def _scene_std(vol, pal):
     return O.make_scene(vol, pal, assets.noise_standin(), assets.sky_standin(256, 128))
 
 
-@pytest.mark.parametrize("trav", [TRAV_DENSE, TRAV_BRICK])
+@pytest.mark.parametrize("trav", list(ALL_TRAVERSALS))
 def test_harness_matches_oracle_treehouse(trav):
     rc, vol, pal = O.load_vox(cached_vox("treehouse"))
     sc, keep = _scene_std(vol, pal)
@@ -99,7 +99,7 @@ def test_harness_matches_oracle_random_metallic(seed, whd):
     want = O.render(sc, cam, st)
     if min(whd) > 8:
         assert want["rays"].max() > 12                  # reflection stacks were exercised
-    for trav in (TRAV_DENSE, TRAV_BRICK):
+    for trav in ALL_TRAVERSALS:
         assert_planes_exact(harness_render(sc, cam, st, trav), want)
 
 
@@ -110,12 +110,12 @@ def test_harness_matches_oracle_degenerate_rays():
     sc, keep = _scene_std(vol, random_palette(rng))
     st = O.make_settings(light_dir=np.array([0, 1, 0], np.float32))
     cam = look_at_camera((24, 24, 24), (64, 48), (-8, 30, -9), (12, 12, 12))
-    for trav in (TRAV_DENSE, TRAV_BRICK):
+    for trav in ALL_TRAVERSALS:
         assert_planes_exact(harness_render(sc, cam, st, trav), O.render(sc, cam, st))
     solid = np.full((12, 12, 12), 5, np.uint8)
     sc2, keep2 = _scene_std(solid, random_palette(rng))
     cam2 = default_camera((12, 12, 12), (32, 20), pos=(6.5, 6.5, 6.5))
-    for trav in (TRAV_DENSE, TRAV_BRICK):
+    for trav in ALL_TRAVERSALS:
         assert_planes_exact(harness_render(sc2, cam2, O.make_settings(), trav), O.render(sc2, cam2, O.make_settings()))
 
 
@@ -126,7 +126,7 @@ def test_harness_pass_masks():
     cam = look_at_camera((40, 40, 40), (80, 60), (-10, 55, -14), (20, 20, 20))
     for pm in (O.PASS_PRIMARY, O.PASS_PRIMARY | O.PASS_SHADOW | O.PASS_SHADE, O.PASS_PRIMARY | O.PASS_AO | O.PASS_SHADE, O.PASS_ALL & ~O.PASS_REFLECT):
         st = O.make_settings(pass_mask=pm, ao=2)
-        assert_planes_exact(harness_render(sc, cam, st, TRAV_BRICK), O.render(sc, cam, st))
+        assert_planes_exact(harness_render(sc, cam, st, TRAV_FINE), O.render(sc, cam, st))
 
 
 def test_noise_constants_match_double_folding():

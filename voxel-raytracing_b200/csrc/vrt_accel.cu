@@ -64,4 +64,86 @@ cudaError_t launch_build_accel(const uint8_t* vol, uint32_t W, uint32_t H, uint3
     return cudaGetLastError();
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Per-voxel safe-step field (fdist). Fine part: Chebyshev distance to the nearest solid / out-of-bounds voxel,
+// exact up to VRT_FINE_CAP, by VRT_FINE_CAP-1 rounds of a separable 3x3x3 min (+1) over the linear volume.
+__global__ void fine_init_kernel(const uint8_t* __restrict__ vol, uint8_t* __restrict__ a, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) a[i] = vol[i] ? 0 : (uint8_t)VRT_FINE_CAP;
+}
+template <int AXIS>
+__global__ void fine_pass_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int W, int H, int D) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, z = blockIdx.z;
+    if (x >= W) return;
+    const size_t v = (size_t)x + (size_t)y * W + (size_t)z * W * H;
+    const size_t stride = AXIS == 0 ? 1 : (AXIS == 1 ? (size_t)W : (size_t)W * H);
+    const int c = AXIS == 0 ? x : (AXIS == 1 ? y : z), n = AXIS == 0 ? W : (AXIS == 1 ? H : D);
+    const int lo = c > 0 ? in[v - stride] : 0, mid = in[v], hi = c + 1 < n ? in[v + stride] : 0;
+    const int m = min(mid, min(lo, hi));
+    if (AXIS == 2) { const int cur = out[v]; out[v] = (uint8_t)min(cur, m + 1); }
+    else out[v] = (uint8_t)m;
+}
+// same passes, 4 voxels along x per thread (W % 4 == 0): byte-wise SIMD min
+template <int AXIS>
+__global__ void fine_pass4_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int W4, int H, int D) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, z = blockIdx.z;
+    if (x >= W4) return;
+    const size_t v = (size_t)x + (size_t)y * W4 + (size_t)z * W4 * H;
+    uint32_t m;
+    if (AXIS == 0) {
+        const uint32_t mid = in[v], l = x > 0 ? in[v - 1] : 0u, r = x + 1 < W4 ? in[v + 1] : 0u;
+        const uint32_t left = (mid << 8) | (l >> 24), right = (mid >> 8) | (r << 24);   // neighbours at x-1 / x+1 per byte lane
+        m = __vminu4(mid, __vminu4(left, right));
+    } else {
+        const size_t stride = AXIS == 1 ? (size_t)W4 : (size_t)W4 * H;
+        const int c = AXIS == 1 ? y : z, n = AXIS == 1 ? H : D;
+        const uint32_t lo = c > 0 ? in[v - stride] : 0u, hi = c + 1 < n ? in[v + stride] : 0u;
+        m = __vminu4(in[v], __vminu4(lo, hi));
+    }
+    if (AXIS == 2) out[v] = __vminu4(out[v], m + 0x01010101u);   // values <= VRT_FINE_CAP: no carry between bytes
+    else out[v] = m;
+}
+// merge with the far-field bound of the brick level and store 4x4x4-bricked
+__global__ void fine_merge_kernel(const uint8_t* __restrict__ fine, const uint8_t* __restrict__ bdist, uint8_t* __restrict__ fdist,
+                                  uint32_t W, uint32_t H, uint32_t D, uint32_t Bx, uint32_t By) {
+    const uint32_t x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, z = blockIdx.z;
+    if (x >= W) return;
+    const uint32_t f = fine[(size_t)x + (size_t)y * W + (size_t)z * W * H];
+    const size_t b = (size_t)(z >> 2) * By * Bx + (size_t)(y >> 2) * Bx + (x >> 2);
+    const uint32_t d = bdist[b];
+    uint32_t n = f;
+    if (f != 0 && d != 0) n = max(f, (d - 1u) * 4u + 1u);
+    fdist[b * 64u + ((x & 3u) | ((y & 3u) << 2) | ((z & 3u) << 4))] = (uint8_t)min(n, 255u);
+}
+
+cudaError_t launch_build_fdist(const uint8_t* vol, const uint8_t* bdist, uint32_t W, uint32_t H, uint32_t D, uint8_t* fdist,
+                               uint8_t* a, uint8_t* t1, uint8_t* t2, cudaStream_t stream, int* launches) {
+    const size_t n = (size_t)W * H * D;
+    const uint32_t Bx = (W + 3) / 4, By = (H + 3) / 4, Bz = (D + 3) / 4;
+    cudaError_t e = cudaMemsetAsync(fdist, 0, (size_t)Bx * By * Bz * 64u, stream);   // padding voxels of edge bricks
+    if (e != cudaSuccess) return e;
+    fine_init_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(vol, a, n);
+    int cnt = 1;
+    const bool vec = (W % 4u) == 0;
+    for (int r = 1; r < VRT_FINE_CAP; r++) {
+        if (vec) {
+            const int W4 = (int)(W / 4);
+            const dim3 block(128), grid((W4 + 127) / 128, H, D);
+            fine_pass4_kernel<0><<<grid, block, 0, stream>>>((const uint32_t*)a, (uint32_t*)t1, W4, (int)H, (int)D);
+            fine_pass4_kernel<1><<<grid, block, 0, stream>>>((const uint32_t*)t1, (uint32_t*)t2, W4, (int)H, (int)D);
+            fine_pass4_kernel<2><<<grid, block, 0, stream>>>((const uint32_t*)t2, (uint32_t*)a, W4, (int)H, (int)D);
+        } else {
+            const dim3 block(128), grid((W + 127) / 128, H, D);
+            fine_pass_kernel<0><<<grid, block, 0, stream>>>(a, t1, (int)W, (int)H, (int)D);
+            fine_pass_kernel<1><<<grid, block, 0, stream>>>(t1, t2, (int)W, (int)H, (int)D);
+            fine_pass_kernel<2><<<grid, block, 0, stream>>>(t2, a, (int)W, (int)H, (int)D);
+        }
+        cnt += 3;
+    }
+    fine_merge_kernel<<<dim3((W + 127) / 128, H, D), 128, 0, stream>>>(a, bdist, fdist, W, H, D, Bx, By);
+    cnt++;
+    if (launches) *launches += cnt;
+    return cudaGetLastError();
+}
+
 }  // namespace vrt

@@ -28,7 +28,7 @@ struct vrt_context {
 struct vrt_scene {
     vrt_context* ctx = nullptr;
     uint32_t w = 0, h = 0, d = 0, Bx = 0, By = 0, Bz = 0;
-    uint8_t* vol = nullptr; unsigned long long* bmask = nullptr; uint8_t* bdist = nullptr;
+    uint8_t* vol = nullptr; unsigned long long* bmask = nullptr; uint8_t* bdist = nullptr; uint8_t* fdist = nullptr;
     vrt_material* palette = nullptr; vrt_material hostPalette[256];
     uint8_t* noise = nullptr; float* sky = nullptr; uint32_t skyW = 0, skyH = 0;
     int accelLaunches = 0;
@@ -97,7 +97,7 @@ extern "C" void* vrt_context_stream(vrt_context* c) { return c ? (void*)c->strea
 extern "C" void vrt_scene_destroy(vrt_scene* s) {
     if (!s) return;
     cudaSetDevice(s->ctx->device);
-    cudaFree(s->vol); cudaFree(s->bmask); cudaFree(s->bdist); cudaFree(s->palette); cudaFree(s->noise); cudaFree(s->sky);
+    cudaFree(s->vol); cudaFree(s->bmask); cudaFree(s->bdist); cudaFree(s->fdist); cudaFree(s->palette); cudaFree(s->noise); cudaFree(s->sky);
     delete s;
 }
 
@@ -113,6 +113,7 @@ static int scene_alloc(vrt_context* c, uint32_t w, uint32_t h, uint32_t d, vrt_s
     cudaError_t e = cudaMalloc(&s->vol, (size_t)w * h * d);
     if (e == cudaSuccess) e = cudaMalloc(&s->bmask, nb * 8);
     if (e == cudaSuccess) e = cudaMalloc(&s->bdist, nb);
+    if (e == cudaSuccess) e = cudaMalloc(&s->fdist, nb * 64);
     if (e == cudaSuccess) e = cudaMalloc(&s->palette, sizeof(vrt_material) * 256);
     if (e != cudaSuccess) { vrt_scene_destroy(s); return fail(e == cudaErrorMemoryAllocation ? VRT_E_OOM : VRT_E_CUDA, cudaGetErrorString(e)); }
     *out = s;
@@ -130,6 +131,17 @@ static int scene_finish(vrt_scene* s, const vrt_material palette[256]) {
     cudaError_t e2 = cudaStreamSynchronize(c->stream);
     cudaFree(tmpA); cudaFree(tmpB);
     if (e != cudaSuccess) return fail(VRT_E_CUDA, cudaGetErrorString(e));
+    if (e2 != cudaSuccess) return fail(VRT_E_CUDA, cudaGetErrorString(e2));
+    // per-voxel safe-step field: three volume-sized scratch buffers, freed after the build
+    const size_t nv = (size_t)s->w * s->h * s->d;
+    uint8_t *a = nullptr, *t1 = nullptr, *t2 = nullptr;
+    e = cudaMalloc(&a, nv);
+    if (e == cudaSuccess) e = cudaMalloc(&t1, nv);
+    if (e == cudaSuccess) e = cudaMalloc(&t2, nv);
+    if (e == cudaSuccess) e = launch_build_fdist(s->vol, s->bdist, s->w, s->h, s->d, s->fdist, a, t1, t2, c->stream, &s->accelLaunches);
+    e2 = cudaStreamSynchronize(c->stream);
+    cudaFree(a); cudaFree(t1); cudaFree(t2);
+    if (e != cudaSuccess) return fail(e == cudaErrorMemoryAllocation ? VRT_E_OOM : VRT_E_CUDA, cudaGetErrorString(e));
     if (e2 != cudaSuccess) return fail(VRT_E_CUDA, cudaGetErrorString(e2));
     return VRT_OK;
 }
@@ -216,7 +228,7 @@ extern "C" int vrt_scene_accel_info(const vrt_scene* s, size_t* dense_bytes, siz
     const size_t nb = (size_t)s->Bx * s->By * s->Bz;
     if (dense_bytes) *dense_bytes = (size_t)s->w * s->h * s->d;
     if (brick_mask_bytes) *brick_mask_bytes = nb * 8;
-    if (brick_dist_bytes) *brick_dist_bytes = nb;
+    if (brick_dist_bytes) *brick_dist_bytes = nb + nb * 64;   // bdist + fdist
     return VRT_OK;
 }
 
@@ -226,6 +238,13 @@ extern "C" int vrt_scene_download_accel(const vrt_scene* s, uint64_t* bmask_dst,
     CU(cudaSetDevice(s->ctx->device));
     if (bmask_dst) CU(cudaMemcpy(bmask_dst, s->bmask, nb * 8, cudaMemcpyDeviceToHost));
     if (bdist_dst) CU(cudaMemcpy(bdist_dst, s->bdist, nb, cudaMemcpyDeviceToHost));
+    return VRT_OK;
+}
+
+extern "C" int vrt_scene_download_fdist(const vrt_scene* s, uint8_t* dst, size_t bytes) {
+    if (!s || !dst || bytes != (size_t)s->Bx * s->By * s->Bz * 64u) return fail(VRT_E_INVALID, "bad size");
+    CU(cudaSetDevice(s->ctx->device));
+    CU(cudaMemcpy(dst, s->fdist, bytes, cudaMemcpyDeviceToHost));
     return VRT_OK;
 }
 
@@ -317,7 +336,7 @@ extern "C" int vrt_render(vrt_context* c, const vrt_scene* s, const vrt_camera* 
     if (cam->volumeBounds[0] != s->w || cam->volumeBounds[1] != s->h || cam->volumeBounds[2] != s->d)
         return fail(VRT_E_INVALID, "camera volumeBounds differ from the scene bounds");
     if (!(st->pass_mask & VRT_PASS_PRIMARY)) return fail(VRT_E_INVALID, "pass_mask must include VRT_PASS_PRIMARY");
-    if (st->traversal > VRT_TRAVERSAL_BRICK) return fail(VRT_E_INVALID, "unknown traversal");
+    if (st->traversal > VRT_TRAVERSAL_FINE) return fail(VRT_E_INVALID, "unknown traversal");
     if (st->denoise.enable && c->world != 1) return fail(VRT_E_UNSUPPORTED, "denoise runs on the assembled frame: call vrt_denoise on rank 0 after the gather");
     CU(cudaSetDevice(c->device));
     vrt_frame* f = *frame;
@@ -335,11 +354,11 @@ extern "C" int vrt_render(vrt_context* c, const vrt_scene* s, const vrt_camera* 
     if (rc) { if (!*frame) vrt_frame_release(f); return rc; }
 
     SceneDev sc{};
-    sc.vol = s->vol; sc.bmask = s->bmask; sc.bdist = s->bdist; sc.W = s->w; sc.H = s->h; sc.D = s->d; sc.Bx = s->Bx; sc.By = s->By; sc.Bz = s->Bz;
+    sc.vol = s->vol; sc.bmask = s->bmask; sc.bdist = s->bdist; sc.fdist = s->fdist; sc.W = s->w; sc.H = s->h; sc.D = s->d; sc.Bx = s->Bx; sc.By = s->By; sc.Bz = s->Bz;
     sc.palette = s->palette; sc.noise = s->noise; sc.sky = s->sky; sc.skyW = s->skyW; sc.skyH = s->skyH;
     FrameParams fp{};
     fp.cam = *cam; fp.pass_mask = st->pass_mask; fp.out_mask = out_mask;
-    fp.traversal = st->traversal == VRT_TRAVERSAL_DEFAULT ? VRT_TRAVERSAL_BRICK : st->traversal;
+    fp.traversal = st->traversal == VRT_TRAVERSAL_DEFAULT ? VRT_TRAVERSAL_FINE : st->traversal;
     fp.aoSamples = st->vol.aoSamples; fp.ambientIntensity = st->vol.ambientIntensity;
     for (int k = 0; k < 3; k++) { fp.lightDir[k] = st->light.direction[k]; fp.lightColor[k] = st->light.color[k]; }
     fp.lightIntensity = st->light.intensity;

@@ -99,6 +99,21 @@ VRT_HD uint32_t dda_step_rec(Dda& s) {
     if (bz) { s.sz += s.dz; s.mz += s.stz; }
     return (bx ? 1u : 0u) | (by ? 2u : 0u) | (bz ? 4u : 0u);
 }
+// float-only steps for VRT_TRAVERSAL_FINE (mapPos is recovered from sideDist at lookups)
+VRT_HD void dda_step_f(Dda& s) {
+    float m = min3f(s.sx, s.sy, s.sz);
+    if (s.sx <= m) s.sx += s.dx;
+    if (s.sy <= m) s.sy += s.dy;
+    if (s.sz <= m) s.sz += s.dz;
+}
+VRT_HD uint32_t dda_step_f_rec(Dda& s) {
+    float m = min3f(s.sx, s.sy, s.sz);
+    bool bx = s.sx <= m, by = s.sy <= m, bz = s.sz <= m;
+    if (bx) s.sx += s.dx;
+    if (by) s.sy += s.dy;
+    if (bz) s.sz += s.dz;
+    return (bx ? 1u : 0u) | (by ? 2u : 0u) | (bz ? 4u : 0u);
+}
 VRT_HD uint32_t dda_step_literal(Dda& s) {   // exactly as written in the shader (handles inf/NaN deltaDist)
     bool bx = s.sx <= fminf(s.sy, s.sz), by = s.sy <= fminf(s.sz, s.sx), bz = s.sz <= fminf(s.sx, s.sy);
     float fx = bx ? 1.0f : 0.0f, fy = by ? 1.0f : 0.0f, fz = bz ? 1.0f : 0.0f;
@@ -146,6 +161,33 @@ VRT_HD TraceRes trace_ray(const SceneDev& sc, V3 start, V3 dir, uint32_t maxStep
             material = fetch_voxel(sc, s);
             if (material != 0) { hit = true; break; }
             mask = dda_step_rec(s);
+        }
+    } else if (TRAVERSAL == VRT_TRAVERSAL_FINE) {
+        // Per-voxel safe-step field. mapPos is not carried through the steps: it is recovered at each lookup from
+        // how far sideDist has advanced, c = rint((sideDist - sideDist0) / deltaDist) per axis. The accumulated
+        // rounding error of <= 512 float adds is < 0.02 of a step, so the rounded count is exact.
+        const float sx0 = s.sx, sy0 = s.sy, sz0 = s.sz;
+        const float ax = fabsf(dir.x), ay = fabsf(dir.y), az = fabsf(dir.z);
+        const int mx0 = s.mx, my0 = s.my, mz0 = s.mz;
+        while (i < maxSteps) {
+            s.mx = mx0 + f2i(rintf((s.sx - sx0) * ax)) * s.stx;
+            s.my = my0 + f2i(rintf((s.sy - sy0) * ay)) * s.sty;
+            s.mz = mz0 + f2i(rintf((s.sz - sz0) * az)) * s.stz;
+            if (!in_bounds(sc, s)) { oob = true; break; }
+            const uint32_t b = ((uint32_t)s.mz >> 2) * (sc.By * sc.Bx) + ((uint32_t)s.my >> 2) * sc.Bx + ((uint32_t)s.mx >> 2);
+            const uint32_t in = ((uint32_t)s.mx & 3u) | (((uint32_t)s.my & 3u) << 2) | (((uint32_t)s.mz & 3u) << 4);
+            uint32_t n = sc.fdist[(size_t)b * 64u + in];
+            if (n == 0) { material = fetch_voxel(sc, s); hit = true; break; }
+            const uint32_t left = maxSteps - i;
+            n = n < left ? n : left;
+            i += n;
+            for (uint32_t k = n - 1; k > 0; k--) dda_step_f(s);
+            mask = dda_step_f_rec(s);
+        }
+        if (!hit && !oob) {   // ran out of steps: mapPos of the exit state (instrumentation only)
+            s.mx = mx0 + f2i(rintf((s.sx - sx0) * ax)) * s.stx;
+            s.my = my0 + f2i(rintf((s.sy - sy0) * ay)) * s.sty;
+            s.mz = mz0 + f2i(rintf((s.sz - sz0) * az)) * s.stz;
         }
     } else {
         while (i < maxSteps) {

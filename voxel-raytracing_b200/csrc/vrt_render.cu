@@ -8,8 +8,12 @@
 
 namespace vrt {
 
+#ifndef VRT_MIN_BLOCKS
+#define VRT_MIN_BLOCKS 1
+#endif
+
 template <int TRAVERSAL>
-__global__ void __launch_bounds__(128) render_kernel(const SceneDev sc, const FrameParams fp, const PlanesDev pl, Counters* __restrict__ ctr) {
+__global__ void __launch_bounds__(128, VRT_MIN_BLOCKS) render_kernel(const SceneDev sc, const FrameParams fp, const PlanesDev pl, Counters* __restrict__ ctr) {
     const int W = fp.cam.screenSize[0], H = fp.cam.screenSize[1];
     const int j = blockIdx.x >> 3, sub = blockIdx.x & 7;           // local tile, 16x8 sub-block of the tile
     const int t = j * fp.world + fp.rank;                          // global tile (interleaved shard)
@@ -59,6 +63,7 @@ cudaError_t launch_render(const SceneDev& sc, const FrameParams& fp, const Plane
     if (fp.localTiles <= 0) return cudaSuccess;
     const dim3 grid((unsigned)fp.localTiles * 8u), block(128);
     if (fp.traversal == VRT_TRAVERSAL_DENSE_U8) render_kernel<VRT_TRAVERSAL_DENSE_U8><<<grid, block, 0, stream>>>(sc, fp, pl, ctr);
+    else if (fp.traversal == VRT_TRAVERSAL_FINE) render_kernel<VRT_TRAVERSAL_FINE><<<grid, block, 0, stream>>>(sc, fp, pl, ctr);
     else render_kernel<VRT_TRAVERSAL_BRICK><<<grid, block, 0, stream>>>(sc, fp, pl, ctr);
     return cudaGetLastError();
 }

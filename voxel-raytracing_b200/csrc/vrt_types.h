@@ -18,11 +18,18 @@ namespace vrt {
 //              From any voxel of a brick with bdist = n >= 1 the next (n-1)*4 positions of ANY ray are empty and
 //              in bounds, so (n-1)*4+1 DDA steps can run without looking at memory.
 constexpr int VRT_DIST_CAP = 33;      // (33-1)*4+1 = 129 unchecked steps at most per lookup
+//   fdist[v] : per-voxel "safe step count", stored 4x4x4-bricked (64 B per brick). 0 = solid voxel. Otherwise a lower
+//              bound >= 1 of the Chebyshev distance C(v) from v to the nearest solid or out-of-bounds voxel: one DDA
+//              step moves at most 1 in Chebyshev distance, so the next fdist[v]-1 positions of ANY ray through v are
+//              empty and in bounds and fdist[v] steps can run before memory is looked at again. Built as
+//              max(min(C(v), VRT_FINE_CAP) [exact near surfaces], (bdist-1)*4+1 [far field]).
+constexpr int VRT_FINE_CAP = 15;
 
 struct SceneDev {
     const uint8_t* vol;               // dense u8[W*H*D], x fastest (voxel_scene.cpp:99)
     const unsigned long long* bmask;  // [Bz][By][Bx]
     const uint8_t* bdist;             // [Bz][By][Bx]
+    const uint8_t* fdist;             // [Bz][By][Bx][4][4][4]
     uint32_t W, H, D;
     uint32_t Bx, By, Bz;
     const vrt_material* palette;      // 256 entries

@@ -11,11 +11,11 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libvrt.so")
+LIB_PATH = os.environ.get("VRT_LIB", os.path.join(HERE, "libvrt.so"))   # VRT_LIB: build variants for measurement only
 
 PASS_PRIMARY, PASS_SHADOW, PASS_AO, PASS_REFLECT, PASS_SHADE, PASS_ALL = 1, 2, 4, 8, 16, 31
 OUT_GBUFFER, OUT_INSTRUMENT = 1, 2
-TRAVERSAL_DEFAULT, TRAVERSAL_DENSE_U8, TRAVERSAL_BRICK = 0, 1, 2
+TRAVERSAL_DEFAULT, TRAVERSAL_DENSE_U8, TRAVERSAL_BRICK, TRAVERSAL_FINE = 0, 1, 2, 3
 DENOISE_AS_EXECUTED, DENOISE_AS_INTENDED = 0, 1
 E_LFS_POINTER, E_NO_INSTANCE, E_PARSE, E_IO, E_CUDA, E_NO_DEVICE = -2, -3, -4, -5, -6, -7
 
@@ -199,6 +199,11 @@ class VoxelScene:
         bx, by, bz = (self.width + 3) // 4, (self.height + 3) // 4, (self.depth + 3) // 4
         m = np.zeros((bz, by, bx), np.uint64); dd = np.zeros((bz, by, bx), np.uint8)
         _ck(lib().vrt_scene_download_accel(self.h, m.ctypes.data_as(C.c_void_p), dd.ctypes.data_as(C.c_void_p))); return m, dd
+
+    def download_fdist(self):
+        bx, by, bz = (self.width + 3) // 4, (self.height + 3) // 4, (self.depth + 3) // 4
+        f = np.zeros((bz, by, bx, 4, 4, 4), np.uint8)   # [bz][by][bx][z&3][y&3][x&3]
+        _ck(lib().vrt_scene_download_fdist(self.h, f.ctypes.data_as(C.c_void_p), C.c_size_t(f.size))); return f
 
     def accel_info(self):
         a, b, c = C.c_size_t(), C.c_size_t(), C.c_size_t()
