@@ -39,6 +39,7 @@ def parse_args():
     ap.add_argument("--whd", type=int, nargs=3, default=None, help="override the synthetic volume size (debug)")
     ap.add_argument("--size", type=int, nargs=2, default=None, help="override the resolution (debug)")
     ap.add_argument("--traversal", type=int, default=0, help="0 default, 1 dense u8, 2 brick")
+    ap.add_argument("--pipeline", type=int, default=0, help="0 default (wavefront), 1 megakernel, 2 wavefront")
     ap.add_argument("--passes", type=int, default=None, help="override the pass mask (measurement of pass subsets)")
     ap.add_argument("--ao", type=int, default=None, help="override aoSamples")
     ap.add_argument("--no-gbuffer", action="store_true")
@@ -105,12 +106,12 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def ncu_traffic():
+def ncu_traffic(kernel="render_kernel"):
     """Per-launch DRAM traffic of the dominant kernel from the committed ncu summary, if one exists."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(p):
         try:
-            return json.load(open(p)).get("render_kernel_dram_bytes_per_launch")
+            return json.load(open(p)).get(kernel.split(" ")[0] + "_dram_bytes_per_launch")
         except Exception:
             return None
     return None
@@ -242,6 +243,7 @@ def run_vrt(args):
     bounds = scene.bounds
     st = configs.settings_for(cfg, gbuffer=not args.no_gbuffer)
     st.traversal = args.traversal
+    st.pipeline = args.pipeline
     rp = pyvrt.VoxelRenderPass(ctx, scene, st)
     ext = torch.cuda.ExternalStream(ctx.stream, device=torch.device("cuda", local))
     final = "denoised" if cfg["denoise"] and world == 1 else "color"
@@ -256,7 +258,7 @@ def run_vrt(args):
         nonlocal gathered
         cam = configs.make_camera(args.config, bounds, size, k)
         fr = rp.record(cam)
-        launches = 1 + (cfg["denoise"] and world == 1) * st.denoise.iterations
+        launches = 0      # launches outside vrt_render (the library counts its own: vrt_frame_stats.kernel_launches)
         if world > 1:
             ptr, n = fr.plane_ptr("color")
             shard = torch.as_tensor(_DevBuf(ptr, n), device=torch.device("cuda", local))
@@ -287,18 +289,21 @@ def run_vrt(args):
     for k in range(args.warmup):
         step(k)
     barrier()
-    rays = fetches = pixels = 0
-    ms_kernel = []
+    rays = fetches = pixels = lib_launches = 0
+    ms_kernel, ms_stage = [], []
+    stage_rays, stage_fetches = np.zeros(3), np.zeros(3)
     for k in range(args.steps):
         fr, _ = step(k)
         s = fr.stats()
-        rays += s["rays"]; fetches += s["fetches"]; pixels += s["pixels"]; ms_kernel.append(s["ms_trace"])
+        rays += s["rays"]; fetches += s["fetches"]; pixels += s["pixels"]; ms_kernel.append(s["ms_trace"] + s["ms_denoise"])
+        ms_stage.append(s["ms_stage"]); stage_rays += s["stage_rays"]; stage_fetches += s["stage_fetches"]
+        lib_launches += s["kernel_launches"]
     barrier()
 
     # ---- timed region 1: K frames, inputs resident, device time on the launching stream, max over ranks
     sampler = ClockSampler(local) if rank == 0 else None
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    launches = 0
+    launches = lib_launches    # the timed region replays exactly the frames counted above
     barrier()
     with torch.cuda.stream(ext):
         e0.record()
@@ -330,18 +335,32 @@ def run_vrt(args):
     if rank == 0:
         peak, peak_src = measured_peaks()
         b_out = 37 if (st.out_mask & pyvrt.OUT_GBUFFER) else 4
-        alg_bytes = (fetches + pixels * b_out) / args.steps                  # this rank's render kernel, per launch
+        frame_bytes_alg = (fetches + pixels * b_out) / args.steps           # this rank, whole pass, per frame
         k_ms = float(np.mean(ms_kernel))
-        achieved = alg_bytes / (k_ms * 1e-3) / 1e9
+        # dominant kernel of the pass: per-stage CUDA-event times and per-stage getVoxel counts from the library
+        stage_ms = np.mean(np.array(ms_stage), axis=0)
+        names = ["wave_primary_kernel", "wave_bounce_kernel (x5)", "wave_anyhit_kernel", "wave_resolve_kernel"] if args.pipeline != 1 else ["render_kernel"] * 4
+        dom = int(np.argmax(stage_ms[:3]))
+        # algorithmic bytes of that kernel: 1 B per reference getVoxel call + its outputs
+        # (primary: colour + G-buffer per pixel; bounce: nothing the reference stores; any-hit: the 1-byte hit flag per ray)
+        out_bytes = [pixels * b_out, 0.0, float(stage_rays[2])][dom] if args.pipeline != 1 else pixels * b_out
+        alg_bytes = (float(stage_fetches[dom]) + out_bytes) / args.steps
+        dom_ms = float(stage_ms[dom])
+        achieved = alg_bytes / (dom_ms * 1e-3) / 1e9
         line = {"metric": METRIC, "value": rays_all / (ms * 1e-3) / 1e6, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": config_blob(cfg, args.config, args.whd, size, {"parallelism": f"tiles{world}" if world > 1 else "single", "traversal": args.traversal,
+                "config": config_blob(cfg, args.config, args.whd, size, {"parallelism": f"tiles{world}" if world > 1 else "single", "traversal": args.traversal, "pipeline": args.pipeline,
                                                                          "gathered_plane": "color RGBA8" if world > 1 else None}),
                 "rays_per_frame": rays_all / args.steps, "voxel_visits_per_frame": fetches_all / args.steps,
                 "Mrays_per_s_primary": pixels_all / (ms * 1e-3) / 1e6,
-                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(),
-                             "kernel": "render_kernel", "kernel_ms": k_ms, "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
-                             "note": "algorithmic bytes = getVoxel calls of the reference loop x 1 B + pixels x %d B of G-buffer; the loop is issue-bound, not bandwidth-bound (DESIGN.md)" % b_out},
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(names[dom]),
+                             "kernel": names[dom], "kernel_ms": dom_ms, "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
+                             "frame": {"achieved": frame_bytes_alg / (k_ms * 1e-3) / 1e9, "frac": frame_bytes_alg / (k_ms * 1e-3) / 1e9 / peak,
+                                       "algorithmic_bytes": frame_bytes_alg, "ms": k_ms},
+                             "stages_ms": {"primary": float(stage_ms[0]), "bounce": float(stage_ms[1]), "anyhit": float(stage_ms[2]), "resolve": float(stage_ms[3])},
+                             "stages_Mrays": {"primary": float(stage_rays[0] / args.steps / 1e6), "bounce": float(stage_rays[1] / args.steps / 1e6), "anyhit": float(stage_rays[2] / args.steps / 1e6)},
+                             "stages_Gvisits": {"primary": float(stage_fetches[0] / args.steps / 1e9), "bounce": float(stage_fetches[1] / args.steps / 1e9), "anyhit": float(stage_fetches[2] / args.steps / 1e9)},
+                             "note": "algorithmic bytes = getVoxel calls of the reference loop x 1 B + the kernel's outputs (primary: %d B/pixel; any-hit: 1 B/ray); the loop is issue-bound, not bandwidth-bound (DESIGN.md)" % b_out},
                 "e2e": {"value": rays_all / t_e2e / 1e6, "unit": UNIT, "h2d_bytes_per_step": C.sizeof(pyvrt.Camera) + C.sizeof(pyvrt.RenderSettings),
                         "d2h_bytes_per_step": frame_bytes, "ms_per_step": 1e3 * t_e2e / args.steps},
                 "gpu_launches": launches, "clocks": clocks}

@@ -76,11 +76,16 @@ enum {
 /* traversal back-ends (all bit-identical; for measurement). 0 = library default. */
 enum { VRT_TRAVERSAL_DEFAULT = 0, VRT_TRAVERSAL_DENSE_U8 = 1, VRT_TRAVERSAL_BRICK = 2, VRT_TRAVERSAL_FINE = 3 };
 
+/* how the pass is scheduled on the GPU (all bit-identical; for measurement). 0 = library default (wavefront).
+ *   MEGAKERNEL: one thread runs a pixel's whole ray tree (the shader's own shape).
+ *   WAVEFRONT : primary / reflection-bounce / AO+shadow / resolve kernels over compact hit records. */
+enum { VRT_PIPELINE_DEFAULT = 0, VRT_PIPELINE_MEGAKERNEL = 1, VRT_PIPELINE_WAVEFRONT = 2 };
+
 typedef struct {
     uint32_t pass_mask;
     uint32_t out_mask;
     uint32_t traversal;
-    uint32_t reserved;
+    uint32_t pipeline;
     vrt_volume_params vol;
     vrt_light light;
     vrt_denoiser_settings denoise;
@@ -112,6 +117,11 @@ typedef struct {
     float ms_total;           /* first launch to last kernel of the frame on the context stream */
     uint32_t kernel_launches; /* kernels launched for this frame */
     uint32_t reserved;
+    /* per stage of the wavefront pipeline: 0 primary, 1 reflection bounces, 2 AO + shadow (any-hit), 3 resolve.
+     * Megakernel pipeline: everything is stage 0. */
+    float ms_stage[4];
+    uint64_t stage_rays[3];
+    uint64_t stage_fetches[3];
 } vrt_frame_stats;
 
 /* ---- context ---- */

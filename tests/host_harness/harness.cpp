@@ -5,7 +5,7 @@
 #include <cstring>
 #include <vector>
 #include <algorithm>
-#include "../../voxel-raytracing_b200/csrc/vrt_pixel.cuh"
+#include "../../voxel-raytracing_b200/csrc/vrt_wave.cuh"
 
 using namespace vrt;
 
@@ -128,5 +128,90 @@ extern "C" int hh_render(void* scene, const vrt_camera* cam, const vrt_render_se
             if (pl->rays) pl->rays[p] = o.rays;
             if (pl->fetches) pl->fetches[p] = o.fetches;
         }
+    return 0;
+}
+
+// ---- wavefront pipeline (csrc/vrt_wave.cuh) run through a serial emulation of the kernels' queues ----
+template <int T>
+static void render_wave(const SceneDev& sc, const FrameParams& fp, const PlanesDev* pl, int row_begin, int row_end, int row_step) {
+    const int W = fp.cam.screenSize[0];
+    const uint32_t aoN = (fp.pass_mask & VRT_PASS_AO) ? fp.aoSamples : 0u;
+    const bool shadow = (fp.pass_mask & VRT_PASS_SHADOW) != 0;
+    std::vector<RecQ> rec; std::vector<BounceEnt> q[2]; std::vector<uint32_t> roots, sq;
+    auto sat = [](int v) { return (int16_t)(v < -32768 ? -32768 : (v > 32767 ? 32767 : v)); };
+    auto put_color = [&](size_t p, V3 c) {
+        if (pl->color) { uint8_t* d = pl->color + 4 * p; d[0] = to_unorm8(c.x); d[1] = to_unorm8(c.y); d[2] = to_unorm8(c.z); d[3] = 0; }
+        if (pl->color_f32) { float* d = pl->color_f32 + 3 * p; d[0] = c.x; d[1] = c.y; d[2] = c.z; } };
+    // primary wave
+    for (int py = row_begin; py < row_end; py += row_step)
+        for (int px = 0; px < W; px++) {
+            PixelOut o; memset(&o, 0, sizeof(o)); V3 rd;
+            const int action = wave_primary<T>(sc, fp, px, py, o, rd);
+            const size_t p = (size_t)py * W + px;
+            if (action == WAVE_PIXEL_FINAL) put_color(p, o.color);
+            if (pl->depth) pl->depth[p] = o.depth;
+            if (pl->motion) { pl->motion[2 * p] = 0; pl->motion[2 * p + 1] = 0; }
+            if (pl->mask) pl->mask[p] = to_unorm8(o.mask);
+            if (pl->position) { float* d = pl->position + 4 * p; d[0] = o.pos.x; d[1] = o.pos.y; d[2] = o.pos.z; d[3] = 0; }
+            if (pl->normal) { int8_t* d = pl->normal + 4 * p; d[0] = to_snorm8(o.normal.x); d[1] = to_snorm8(o.normal.y); d[2] = to_snorm8(o.normal.z); d[3] = 0; }
+            if (pl->hit) { int16_t* d = pl->hit + 4 * p; d[0] = sat(o.hx); d[1] = sat(o.hy); d[2] = sat(o.hz); d[3] = (int16_t)o.steps; }
+            if (pl->hit_palette) pl->hit_palette[p] = (uint8_t)o.palette;
+            if (pl->rays) pl->rays[p] = 1;
+            if (pl->fetches) pl->fetches[p] = o.fetches;
+            if (action != WAVE_PIXEL_FINAL) {
+                const uint32_t idx = (uint32_t)(rec.size() / 3);
+                rec.push_back(mkq(o.pos, (uint32_t)px | ((uint32_t)py << 16))); rec.push_back(mkq(o.normal, o.palette)); rec.push_back(mkq(rd, WAVE_NONE));
+                roots.push_back(idx);
+                if (action == WAVE_PIXEL_SHADE_AND_BOUNCE) { BounceEnt e; e.rec = idx; e.root = idx; q[0].push_back(e); }
+            }
+        }
+    auto pix = [&](uint32_t pxy) { return (size_t)(pxy >> 16) * W + (pxy & 0xffffu); };
+    // bounce waves
+    for (int w = 0; w < MAX_REFLECTIONS; w++) {
+        std::vector<BounceEnt>& in = q[w & 1]; std::vector<BounceEnt>& out = q[(w + 1) & 1]; out.clear();
+        for (const BounceEnt& ent : in) {
+            const RecQ p0 = rec[3 * (size_t)ent.rec], p1 = rec[3 * (size_t)ent.rec + 1], p2 = rec[3 * (size_t)ent.rec + 2];
+            V3 rd; const TraceRes r = wave_bounce<T>(sc, q3(p0), q3(p1), q3(p2), rd);
+            if (pl->rays) pl->rays[pix(p0.w)] += 1;
+            if (pl->fetches) pl->fetches[pix(p0.w)] += r.fetches;
+            const uint32_t child = (uint32_t)(rec.size() / 3);
+            rec.push_back(mkq(r.pos, p0.w)); rec.push_back(mkq(r.normal, r.material | ((uint32_t)w << 8))); rec.push_back(mkq(rd, ent.rec));
+            const bool terminal = r.material == 0 || sc.palette[r.material].metallic <= 0.0f;
+            if (terminal) {
+                rec[3 * (size_t)ent.root + 2].w = child;
+                if (r.material != 0) sq.push_back(child);
+                for (uint32_t k = ent.rec; k != ent.root; k = rec[3 * (size_t)k + 2].w) sq.push_back(k);
+            } else if (w + 1 < MAX_REFLECTIONS) { BounceEnt e; e.rec = child; e.root = ent.root; out.push_back(e); }
+        }
+    }
+    // any-hit wave (roots first, then queued bounce records; ray-kind-major like the kernel)
+    const uint32_t nrec = (uint32_t)(rec.size() / 3), R = aoN + (shadow ? 1u : 0u);
+    std::vector<uint8_t> res((size_t)nrec * (aoN + 1u), 0);
+    WaveBuf wb; memset(&wb, 0, sizeof(wb)); wb.rec = rec.data(); wb.res = res.data(); wb.recCap = nrec;
+    std::vector<uint32_t> todo = roots; todo.insert(todo.end(), sq.begin(), sq.end());
+    for (uint32_t i = 0; i < R; i++)
+        for (uint32_t idx : todo) {
+            const RecQ r0 = rec[3 * (size_t)idx], r1 = rec[3 * (size_t)idx + 1];
+            uint32_t f = 0;
+            res[(size_t)i * nrec + idx] = wave_anyhit<T>(sc, fp, q3(r0), q3(r1), (int)(r0.w & 0xffffu), (int)(r0.w >> 16), r1.w >> 8, i, aoN, f) ? 1 : 0;
+            if (pl->rays) pl->rays[pix(r0.w)] += 1;
+            if (pl->fetches) pl->fetches[pix(r0.w)] += f;
+        }
+    // resolve
+    for (uint32_t idx : roots) put_color(pix(rec[3 * (size_t)idx].w), wave_resolve(sc, fp, wb, idx, aoN));
+}
+
+extern "C" int hh_render_wave(void* scene, const vrt_camera* cam, const vrt_render_settings* st, int traversal, const PlanesDev* pl,
+                              int row_begin, int row_end, int row_step) {
+    HScene* s = (HScene*)scene;
+    FrameParams fp; memset(&fp, 0, sizeof(fp));
+    fp.cam = *cam; fp.pass_mask = st->pass_mask; fp.out_mask = st->out_mask; fp.traversal = traversal;
+    fp.aoSamples = st->vol.aoSamples; fp.ambientIntensity = st->vol.ambientIntensity;
+    for (int k = 0; k < 3; k++) { fp.lightDir[k] = st->light.direction[k]; fp.lightColor[k] = st->light.color[k]; }
+    fp.lightIntensity = st->light.intensity; fp.rank = 0; fp.world = 1;
+    if (row_end > cam->screenSize[1]) row_end = cam->screenSize[1];
+    if (traversal == VRT_TRAVERSAL_DENSE_U8) render_wave<VRT_TRAVERSAL_DENSE_U8>(s->dev, fp, pl, row_begin, row_end, row_step);
+    else if (traversal == VRT_TRAVERSAL_FINE) render_wave<VRT_TRAVERSAL_FINE>(s->dev, fp, pl, row_begin, row_end, row_step);
+    else render_wave<VRT_TRAVERSAL_BRICK>(s->dev, fp, pl, row_begin, row_end, row_step);
     return 0;
 }

@@ -13,12 +13,13 @@ import synth
 
 pytestmark = pytest.mark.gpu
 
+PIPELINES = (pyvrt.PIPELINE_MEGAKERNEL, pyvrt.PIPELINE_WAVEFRONT)
 EXACT = ["depth", "motion", "mask", "position", "normal", "hit", "hit_palette", "rays", "fetches"]
 
 
-def vrt_settings(st: O.Settings, traversal=0, out_mask=3, denoise=None):
+def vrt_settings(st: O.Settings, traversal=0, out_mask=3, denoise=None, pipeline=0):
     s = pyvrt.default_settings()
-    s.pass_mask, s.out_mask, s.traversal = st.pass_mask, out_mask, traversal
+    s.pass_mask, s.out_mask, s.traversal, s.pipeline = st.pass_mask, out_mask, traversal, pipeline
     s.vol.aoSamples, s.vol.ambientIntensity = st.aoSamples, st.ambientIntensity
     s.light.direction[:] = st.lightDir[:]; s.light.intensity = st.lightIntensity; s.light.color[:] = st.lightColor[:]
     s.denoise.enable = 0
@@ -31,8 +32,8 @@ def cam_to_py(cam: O.Camera) -> pyvrt.Camera:
     c = pyvrt.Camera(); C.memmove(C.byref(c), C.byref(cam), C.sizeof(cam)); return c
 
 
-def gpu_render(ctx, scene, cam, st, traversal=0, denoise=None, names=None):
-    rp = pyvrt.VoxelRenderPass(ctx, scene, vrt_settings(st, traversal, denoise=denoise))
+def gpu_render(ctx, scene, cam, st, traversal=0, denoise=None, names=None, pipeline=0):
+    rp = pyvrt.VoxelRenderPass(ctx, scene, vrt_settings(st, traversal, denoise=denoise, pipeline=pipeline))
     fr = rp.record(cam_to_py(cam)); fr.sync()
     names = names or [n for n, _, _ in O.PLANE_SPECS] + (["denoised"] if denoise is not None else [])
     out = {n: fr.download(n) for n in names}
@@ -73,7 +74,8 @@ def test_cfg1_treehouse_standin_primary_720p(gpu_ctx):
     st = O.make_settings(pass_mask=O.PASS_PRIMARY)
     want = O.render(sc, cam, st)
     for trav in ALL_TRAVERSALS:
-        check(gpu_render(gpu_ctx, gs, cam, st, trav), want)
+        for pipe in PIPELINES:
+            check(gpu_render(gpu_ctx, gs, cam, st, trav, pipeline=pipe), want)
     gs.destroy()
 
 
@@ -83,7 +85,9 @@ def test_cfg2_mandelbulb_standin_shadow_1080p(gpu_ctx):
     sc, keep, gs = make_pair(gpu_ctx, vol, pal)
     cam = look_at_camera(gs.bounds, (1920, 1080), (-40, 150, -90), (64, 64, 64))
     st = O.make_settings(pass_mask=O.PASS_PRIMARY | O.PASS_SHADOW | O.PASS_SHADE, ao=0)
-    check(gpu_render(gpu_ctx, gs, cam, st), O.render(sc, cam, st))
+    want = O.render(sc, cam, st)
+    for pipe in PIPELINES:
+        check(gpu_render(gpu_ctx, gs, cam, st, pipeline=pipe), want)
     gs.destroy()
 
 
@@ -94,6 +98,7 @@ def test_cfg3_floating_standin_ao_shadow_denoise(gpu_ctx, mode):
     cam = look_at_camera(gs.bounds, (960, 540), (-60, 330, -80), (132, 132, 132), frame=3)
     st = O.make_settings(ao=1)
     want = O.render(sc, cam, st)
+    check(gpu_render(gpu_ctx, gs, cam, st, pipeline=pyvrt.PIPELINE_MEGAKERNEL), want)
     got = gpu_render(gpu_ctx, gs, cam, st, denoise=dict(iterations=2, mode=mode))
     check(got, want)
     assert want["rays"].max() > 8                           # metallic palette entries produced reflection stacks
@@ -120,7 +125,8 @@ def test_cfg4_cfg5_synthetic_generators_and_full_pass(gpu_ctx, gen, whd, pos, ta
     want = O.render(sc, cam, st)
     assert 0.05 < (want["hit_palette"] != 0).mean() and want["rays"].max() > 6
     for trav in ALL_TRAVERSALS:
-        check(gpu_render(gpu_ctx, gs, cam, st, trav), want)
+        for pipe in PIPELINES:
+            check(gpu_render(gpu_ctx, gs, cam, st, trav, pipeline=pipe), want)
     gs.destroy()
 
 
@@ -150,11 +156,13 @@ def test_dense_and_brick_traversal_identical_at_4k(gpu_ctx):
     gs.set_noise(assets.noise_standin()); gs.set_skybox(assets.sky_standin(512, 256))
     cam = look_at_camera(gs.bounds, (3840, 2160), (30.3, 190.2, 25.1), (256, 120, 256), frame=1)
     st = O.make_settings()
-    a = gpu_render(gpu_ctx, gs, cam, st, TRAV_DENSE)
-    for trav in (TRAV_BRICK, TRAV_FINE):
-        b = gpu_render(gpu_ctx, gs, cam, st, trav)
+    a = gpu_render(gpu_ctx, gs, cam, st, TRAV_DENSE, pipeline=pyvrt.PIPELINE_MEGAKERNEL)
+    for trav, pipe in ((TRAV_BRICK, pyvrt.PIPELINE_MEGAKERNEL), (TRAV_FINE, pyvrt.PIPELINE_MEGAKERNEL), (TRAV_FINE, pyvrt.PIPELINE_WAVEFRONT),
+                       (TRAV_DENSE, pyvrt.PIPELINE_WAVEFRONT)):
+        b = gpu_render(gpu_ctx, gs, cam, st, trav, pipeline=pipe)
         for n, _, _ in O.PLANE_SPECS:
-            ok, bad = bits_equal(a[n], b[n]); assert ok, (trav, n, bad)
+            ok, bad = bits_equal(a[n], b[n]); assert ok, (trav, pipe, n, bad)
+        assert a["_stats"]["rays"] == b["_stats"]["rays"] and a["_stats"]["fetches"] == b["_stats"]["fetches"]
     hit = a["hit_palette"] != 0
     assert 0.2 < hit.mean() < 1.0 and a["hit"][..., 3].max() <= 512
     x, y, z = a["hit"][..., 0][hit].astype(int), a["hit"][..., 1][hit].astype(int), a["hit"][..., 2][hit].astype(int)
@@ -170,12 +178,14 @@ def test_degenerate_rays_on_gpu(gpu_ctx):
     sc, keep, gs = make_pair(gpu_ctx, vol, pal)
     st = O.make_settings(light_dir=np.array([0, 1, 0], np.float32))     # zero components: literal inf/NaN path
     cam = look_at_camera((24, 24, 24), (128, 96), (-8, 30, -9), (12, 12, 12))
-    check(gpu_render(gpu_ctx, gs, cam, st), O.render(sc, cam, st))
+    for pipe in PIPELINES:
+        check(gpu_render(gpu_ctx, gs, cam, st, pipeline=pipe), O.render(sc, cam, st))
     gs.destroy()
     solid = np.full((12, 12, 12), 5, np.uint8)
     sc, keep, gs = make_pair(gpu_ctx, solid, pal)
     cam = default_camera((12, 12, 12), (64, 40), pos=(6.5, 6.5, 6.5))       # camera inside solid: step-0 hits, NaN normals
-    check(gpu_render(gpu_ctx, gs, cam, O.make_settings()), O.render(sc, cam, O.make_settings()))
+    for pipe in PIPELINES:
+        check(gpu_render(gpu_ctx, gs, cam, O.make_settings(), pipeline=pipe), O.render(sc, cam, O.make_settings()))
     gs.destroy()
 
 
@@ -183,9 +193,10 @@ def test_empty_and_ragged_sizes(gpu_ctx):
     pal = random_palette(np.random.default_rng(1))
     sc, keep, gs = make_pair(gpu_ctx, np.zeros((5, 6, 7), np.uint8), pal)
     cam = default_camera((7, 6, 5), (33, 17), pos=(3, 3, -10))          # not a multiple of the 8x4 warp patch or the 32x32 tile
-    got = gpu_render(gpu_ctx, gs, cam, O.make_settings())
-    check(got, O.render(sc, cam, O.make_settings()))
-    assert (got["hit_palette"] == 0).all() and got["_stats"]["pixels"] == 33 * 17
+    for pipe in PIPELINES:
+        got = gpu_render(gpu_ctx, gs, cam, O.make_settings(), pipeline=pipe)
+        check(got, O.render(sc, cam, O.make_settings()))
+        assert (got["hit_palette"] == 0).all() and got["_stats"]["pixels"] == 33 * 17
     gs.destroy()
 
 

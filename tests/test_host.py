@@ -86,7 +86,9 @@ def test_harness_matches_oracle_treehouse(trav):
     sc, keep = _scene_std(vol, pal)
     cam = default_camera((126, 126, 126), (160, 90))
     st = O.make_settings()
-    assert_planes_exact(harness_render(sc, cam, st, trav), O.render(sc, cam, st))
+    want = O.render(sc, cam, st)
+    for wave in (False, True):
+        assert_planes_exact(harness_render(sc, cam, st, trav, wave=wave), want)
 
 
 @pytest.mark.parametrize("seed,whd", [(0, (50, 37, 61)), (1, (126, 30, 17)), (2, (8, 8, 8)), (3, (33, 65, 34))])
@@ -101,6 +103,7 @@ def test_harness_matches_oracle_random_metallic(seed, whd):
         assert want["rays"].max() > 12                  # reflection stacks were exercised
     for trav in ALL_TRAVERSALS:
         assert_planes_exact(harness_render(sc, cam, st, trav), want)
+        assert_planes_exact(harness_render(sc, cam, st, trav, wave=True), want)
 
 
 def test_harness_matches_oracle_degenerate_rays():
@@ -112,11 +115,13 @@ def test_harness_matches_oracle_degenerate_rays():
     cam = look_at_camera((24, 24, 24), (64, 48), (-8, 30, -9), (12, 12, 12))
     for trav in ALL_TRAVERSALS:
         assert_planes_exact(harness_render(sc, cam, st, trav), O.render(sc, cam, st))
+        assert_planes_exact(harness_render(sc, cam, st, trav, wave=True), O.render(sc, cam, st))
     solid = np.full((12, 12, 12), 5, np.uint8)
     sc2, keep2 = _scene_std(solid, random_palette(rng))
     cam2 = default_camera((12, 12, 12), (32, 20), pos=(6.5, 6.5, 6.5))
     for trav in ALL_TRAVERSALS:
         assert_planes_exact(harness_render(sc2, cam2, O.make_settings(), trav), O.render(sc2, cam2, O.make_settings()))
+        assert_planes_exact(harness_render(sc2, cam2, O.make_settings(), trav, wave=True), O.render(sc2, cam2, O.make_settings()))
 
 
 def test_harness_pass_masks():
@@ -127,6 +132,7 @@ def test_harness_pass_masks():
     for pm in (O.PASS_PRIMARY, O.PASS_PRIMARY | O.PASS_SHADOW | O.PASS_SHADE, O.PASS_PRIMARY | O.PASS_AO | O.PASS_SHADE, O.PASS_ALL & ~O.PASS_REFLECT):
         st = O.make_settings(pass_mask=pm, ao=2)
         assert_planes_exact(harness_render(sc, cam, st, TRAV_FINE), O.render(sc, cam, st))
+        assert_planes_exact(harness_render(sc, cam, st, TRAV_FINE, wave=True), O.render(sc, cam, st))
 
 
 def test_noise_constants_match_double_folding():

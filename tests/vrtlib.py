@@ -42,13 +42,13 @@ class VrtDenoise(C.Structure):
 
 
 class VrtSettings(C.Structure):
-    _fields_ = [("pass_mask", C.c_uint32), ("out_mask", C.c_uint32), ("traversal", C.c_uint32), ("reserved", C.c_uint32),
+    _fields_ = [("pass_mask", C.c_uint32), ("out_mask", C.c_uint32), ("traversal", C.c_uint32), ("pipeline", C.c_uint32),
                 ("vol", VrtVolParams), ("light", VrtLight), ("denoise", VrtDenoise)]
 
 
 def build_harness() -> str:
     src = os.path.join(HARNESS_DIR, "harness.cpp")
-    deps = [src] + [os.path.join(PKG, "csrc", f) for f in ("vrt_core.cuh", "vrt_pixel.cuh", "vrt_types.h")]
+    deps = [src] + [os.path.join(PKG, "csrc", f) for f in ("vrt_core.cuh", "vrt_pixel.cuh", "vrt_wave.cuh", "vrt_types.h")]
     if not os.path.exists(HARNESS_LIB) or any(os.path.getmtime(d) > os.path.getmtime(HARNESS_LIB) for d in deps):
         gxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
         subprocess.check_call([gxx, "-std=c++17", "-O2", "-ffp-contract=off", "-fno-fast-math", "-fopenmp", "-fPIC", "-shared",
@@ -65,6 +65,7 @@ def harness():
         _h = C.CDLL(build_harness())
         _h.hh_scene_create.restype = C.c_void_p
         _h.hh_render.restype = C.c_int
+        _h.hh_render_wave.restype = C.c_int
     return _h
 
 
@@ -87,7 +88,7 @@ def to_vrt_camera(cam: O.Camera) -> VrtCamera:
     return c
 
 
-def harness_render(scene: O.Scene, cam: O.Camera, st: O.Settings, traversal=TRAV_BRICK, rows=None):
+def harness_render(scene: O.Scene, cam: O.Camera, st: O.Settings, traversal=TRAV_BRICK, rows=None, wave=False):
     h = harness()
     hs = h.hh_scene_create(C.c_void_p(scene.volume), scene.w, scene.h, scene.d, C.c_void_p(scene.palette), C.c_void_p(scene.noise),
                            C.c_void_p(scene.sky), scene.skyW, scene.skyH)
@@ -98,7 +99,8 @@ def harness_render(scene: O.Scene, cam: O.Camera, st: O.Settings, traversal=TRAV
         setattr(p, n, out[n].ctypes.data_as(C.c_void_p))
     vs, vc = to_vrt_settings(st), to_vrt_camera(cam)
     rb, re, rs = rows if rows else (0, H, 1)
-    rc = h.hh_render(C.c_void_p(hs), C.byref(vc), C.byref(vs), traversal, C.byref(p), rb, re, rs)
+    fn = h.hh_render_wave if wave else h.hh_render
+    rc = fn(C.c_void_p(hs), C.byref(vc), C.byref(vs), traversal, C.byref(p), rb, re, rs)
     h.hh_scene_destroy(C.c_void_p(hs))
     assert rc == 0
     return out

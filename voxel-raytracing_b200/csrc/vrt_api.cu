@@ -45,8 +45,12 @@ struct vrt_frame {
     void* ping[2] = {nullptr, nullptr};
     Counters* ctr = nullptr;
     cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr;
+    cudaEvent_t es[3] = {nullptr, nullptr, nullptr};   // wavefront stage boundaries
+    bool staged = false;
     bool denoised = false;
     uint32_t launches = 0, out_mask = 0;
+    WaveBuf wb{};                      // wavefront pipeline buffers (allocated on first use)
+    uint32_t wbRays = 0;               // result planes allocated in wb.res
 };
 
 extern "C" const char* vrt_last_error(void) { return g_err.c_str(); }
@@ -254,9 +258,11 @@ extern "C" void vrt_frame_release(vrt_frame* f) {
     cudaSetDevice(f->ctx->device);
     for (void* p : f->planes) cudaFree(p);
     cudaFree(f->ping[0]); cudaFree(f->ping[1]); cudaFree(f->ctr);
+    cudaFree(f->wb.rec); cudaFree(f->wb.bq[0]); cudaFree(f->wb.bq[1]); cudaFree(f->wb.sq); cudaFree(f->wb.res); cudaFree(f->wb.ctr);
     if (f->e0) cudaEventDestroy(f->e0);
     if (f->e1) cudaEventDestroy(f->e1);
     if (f->e2) cudaEventDestroy(f->e2);
+    for (cudaEvent_t e : f->es) if (e) cudaEventDestroy(e);
     delete f;
 }
 
@@ -264,6 +270,29 @@ static int frame_ensure_plane(vrt_frame* f, int plane) {
     if (f->planes[plane]) return VRT_OK;
     CU(cudaMalloc(&f->planes[plane], f->pixels * kPlaneBpp[plane]));
     CU(cudaMemsetAsync(f->planes[plane], 0, f->pixels * kPlaneBpp[plane], f->ctx->stream));
+    return VRT_OK;
+}
+
+// Wavefront buffers, sized for the worst case (every pixel a hit with a full 5-bounce chain).
+static int frame_ensure_wave(vrt_frame* f, uint32_t raysPerRecord) {
+    WaveBuf& wb = f->wb;
+    if (!wb.ctr) CU(cudaMalloc(&wb.ctr, sizeof(WaveCtr)));
+    if (raysPerRecord == 0) return VRT_OK;      // no shading: the primary kernel allocates no records
+    if (f->pixels * 6 >= 0xffffffffull) return fail(VRT_E_UNSUPPORTED, "frame too large for 32-bit record indices");
+    if (!wb.rec) {
+        wb.pixCap = (uint32_t)f->pixels; wb.recCap = 6u * wb.pixCap;
+        cudaError_t e = cudaMalloc(&wb.rec, (size_t)wb.recCap * 3 * sizeof(RecQ));
+        if (e == cudaSuccess) e = cudaMalloc(&wb.bq[0], (size_t)wb.pixCap * sizeof(BounceEnt));
+        if (e == cudaSuccess) e = cudaMalloc(&wb.bq[1], (size_t)wb.pixCap * sizeof(BounceEnt));
+        if (e == cudaSuccess) e = cudaMalloc(&wb.sq, (size_t)wb.pixCap * 5 * sizeof(uint32_t));
+        if (e != cudaSuccess) return fail(e == cudaErrorMemoryAllocation ? VRT_E_OOM : VRT_E_CUDA, cudaGetErrorString(e));
+    }
+    if (raysPerRecord > f->wbRays) {
+        cudaFree(wb.res); wb.res = nullptr; f->wbRays = 0;
+        cudaError_t e = cudaMalloc(&wb.res, (size_t)wb.recCap * raysPerRecord);
+        if (e != cudaSuccess) return fail(e == cudaErrorMemoryAllocation ? VRT_E_OOM : VRT_E_CUDA, cudaGetErrorString(e));
+        f->wbRays = raysPerRecord;
+    }
     return VRT_OK;
 }
 
@@ -281,6 +310,7 @@ static int frame_create(vrt_context* c, int W, int H, vrt_frame** out) {
     if (e == cudaSuccess) e = cudaEventCreate(&f->e0);
     if (e == cudaSuccess) e = cudaEventCreate(&f->e1);
     if (e == cudaSuccess) e = cudaEventCreate(&f->e2);
+    for (int k = 0; k < 3; k++) if (e == cudaSuccess) e = cudaEventCreate(&f->es[k]);
     if (e != cudaSuccess) { vrt_frame_release(f); return fail(VRT_E_CUDA, cudaGetErrorString(e)); }
     *out = f;
     return VRT_OK;
@@ -337,6 +367,9 @@ extern "C" int vrt_render(vrt_context* c, const vrt_scene* s, const vrt_camera* 
         return fail(VRT_E_INVALID, "camera volumeBounds differ from the scene bounds");
     if (!(st->pass_mask & VRT_PASS_PRIMARY)) return fail(VRT_E_INVALID, "pass_mask must include VRT_PASS_PRIMARY");
     if (st->traversal > VRT_TRAVERSAL_FINE) return fail(VRT_E_INVALID, "unknown traversal");
+    if (st->pipeline > VRT_PIPELINE_WAVEFRONT) return fail(VRT_E_INVALID, "unknown pipeline");
+    if (st->vol.aoSamples > 255) return fail(VRT_E_INVALID, "aoSamples must be <= 255 (the reference GUI allows 0..16)");
+    const bool wavefront = st->pipeline != VRT_PIPELINE_MEGAKERNEL;
     if (st->denoise.enable && c->world != 1) return fail(VRT_E_UNSUPPORTED, "denoise runs on the assembled frame: call vrt_denoise on rank 0 after the gather");
     CU(cudaSetDevice(c->device));
     vrt_frame* f = *frame;
@@ -351,6 +384,8 @@ extern "C" int vrt_render(vrt_context* c, const vrt_scene* s, const vrt_camera* 
         for (int p : {VRT_PLANE_HIT_XYZS_I16X4, VRT_PLANE_HIT_PALETTE_U8, VRT_PLANE_COLOR_RGB32F, VRT_PLANE_RAYS_U32, VRT_PLANE_FETCHES_U32}) if (!rc) rc = frame_ensure_plane(f, p);
     if (!rc && st->denoise.enable)
         for (int k = 0; k < 2 && !rc; k++) if (!f->ping[k]) { cudaError_t e = cudaMalloc(&f->ping[k], f->pixels * 4); if (e != cudaSuccess) rc = fail(VRT_E_CUDA, cudaGetErrorString(e)); }
+    if (!rc && wavefront)
+        rc = frame_ensure_wave(f, (st->pass_mask & VRT_PASS_SHADE) ? ((st->pass_mask & VRT_PASS_AO) ? st->vol.aoSamples : 0u) + 1u : 0u);
     if (rc) { if (!*frame) vrt_frame_release(f); return rc; }
 
     SceneDev sc{};
@@ -374,9 +409,11 @@ extern "C" int vrt_render(vrt_context* c, const vrt_scene* s, const vrt_camera* 
     f->launches = 0; f->out_mask = out_mask; f->denoised = false;
     CU(cudaMemsetAsync(f->ctr, 0, sizeof(Counters), c->stream));
     CU(cudaEventRecord(f->e0, c->stream));
-    cudaError_t e = launch_render(sc, fp, pl, f->ctr, c->stream);
+    cudaError_t e;
+    f->staged = wavefront && f->localTiles > 0;
+    if (wavefront) e = launch_wavefront(sc, fp, pl, f->ctr, f->wb, c->prop.multiProcessorCount, c->stream, &f->launches, f->es);
+    else { e = launch_render(sc, fp, pl, f->ctr, c->stream); f->launches++; }
     if (e != cudaSuccess) { if (!*frame) vrt_frame_release(f); return fail(VRT_E_CUDA, cudaGetErrorString(e)); }
-    f->launches++;
     CU(cudaEventRecord(f->e1, c->stream));
     if (st->denoise.enable) {
         int last = 0;
@@ -427,6 +464,13 @@ extern "C" int vrt_frame_stats_get(vrt_frame* f, vrt_frame_stats* out) {
     CU(cudaEventElapsedTime(&out->ms_denoise, f->e1, f->e2));
     CU(cudaEventElapsedTime(&out->ms_total, f->e0, f->e2));
     out->kernel_launches = f->launches;
+    for (int k = 0; k < 3; k++) { out->stage_rays[k] = h.stageRays[k]; out->stage_fetches[k] = h.stageFetches[k]; }
+    if (f->staged) {
+        CU(cudaEventElapsedTime(&out->ms_stage[0], f->e0, f->es[0]));
+        CU(cudaEventElapsedTime(&out->ms_stage[1], f->es[0], f->es[1]));
+        CU(cudaEventElapsedTime(&out->ms_stage[2], f->es[1], f->es[2]));
+        CU(cudaEventElapsedTime(&out->ms_stage[3], f->es[2], f->e1));
+    } else out->ms_stage[0] = out->ms_trace;
     return VRT_OK;
 }
 
@@ -478,7 +522,7 @@ extern "C" void vrt_camera_vectors(float yaw, float pitch, float focal, float di
 extern "C" void vrt_default_settings(vrt_render_settings* s) {
     if (!s) return;
     memset(s, 0, sizeof(*s));
-    s->pass_mask = VRT_PASS_ALL; s->out_mask = VRT_OUT_GBUFFER; s->traversal = VRT_TRAVERSAL_DEFAULT;
+    s->pass_mask = VRT_PASS_ALL; s->out_mask = VRT_OUT_GBUFFER; s->traversal = VRT_TRAVERSAL_DEFAULT; s->pipeline = VRT_PIPELINE_DEFAULT;
     s->vol.aoSamples = 4; s->vol.ambientIntensity = 1.0f;                  // AmbientOcclusionSettings
     const float inv = 1.0f / sqrtf((1.0f * 1.0f + 1.0f * 1.0f) + 1.0f * 1.0f);   // glm::normalize(vec3(1))
     s->light.direction[0] = s->light.direction[1] = s->light.direction[2] = 1.0f * inv;

@@ -53,8 +53,8 @@ __global__ void __launch_bounds__(128, VRT_MIN_BLOCKS) render_kernel(const Scene
     const unsigned f = __reduce_add_sync(0xffffffffu, fetches);
     const unsigned n = __popc(__ballot_sync(0xffffffffu, active));
     if (lane == 0) {
-        atomicAdd(&ctr->rays, (unsigned long long)r);
-        atomicAdd(&ctr->fetches, (unsigned long long)f);
+        atomicAdd(&ctr->rays, (unsigned long long)r); atomicAdd(&ctr->stageRays[0], (unsigned long long)r);
+        atomicAdd(&ctr->fetches, (unsigned long long)f); atomicAdd(&ctr->stageFetches[0], (unsigned long long)f);
         atomicAdd(&ctr->pixels, (unsigned long long)n);
     }
 }

@@ -70,6 +70,36 @@ struct FrameParams {
     int localTiles;       // tiles owned by this rank
 };
 
-struct Counters { unsigned long long rays, fetches, pixels; };
+struct Counters { unsigned long long rays, fetches, pixels; unsigned long long stageRays[3], stageFetches[3]; };
+
+// ---- wavefront pipeline (vrt_wave.cuh / vrt_wave.cu) ----
+// The shader's per-pixel call tree (primary -> <=5 reflection bounces -> per shaded hit: aoSamples AO rays + 1
+// shadow ray) is cut into ray waves that run as separate kernels over COMPACT lists, so that every warp traces 32
+// rays of one kind. Each ray is still traced exactly as the reference does; only the order between rays changes
+// (rays are independent), so every output byte equals the per-pixel schedule's.
+//   hit record (48 B = 3 x 16 B):  q0 = {pos.xyz, px | py << 16}
+//                                  q1 = {normal.xyz, material | depth << 8}
+//                                  q2 = {dir.xyz, link}    link: primary record -> deepest record of its reflection
+//                                                          chain (lastIdx) or WAVE_NONE; bounce record -> parent record
+//   records [0, pixCap) are primary hits (allocated compactly by the primary kernel), [pixCap, 6*pixCap) bounce hits.
+struct alignas(16) RecQ { float x, y, z; uint32_t w; };
+struct alignas(8) BounceEnt { uint32_t rec, root; };
+constexpr uint32_t WAVE_NONE = 0xffffffffu;
+struct WaveCtr {
+    uint32_t n0;          // primary-hit records
+    uint32_t nb;          // bounce records
+    uint32_t nsq;         // bounce records queued for shading (AO + shadow rays)
+    uint32_t chunk;       // any-hit work distribution
+    uint32_t qn[6];       // bounce queue lengths per wave
+    uint32_t pad[2];
+};
+struct WaveBuf {
+    RecQ* rec;            // 3 per record
+    BounceEnt* bq[2];     // ping-pong bounce queues, pixCap entries each
+    uint32_t* sq;         // bounce records to shade, 5*pixCap entries
+    uint8_t* res;         // any-hit results: res[i * recCap + rec], i < aoSamples: AO ray i hit, i == aoSamples: shadowed
+    WaveCtr* ctr;
+    uint32_t pixCap, recCap;
+};
 
 }  // namespace vrt

@@ -1,0 +1,231 @@
+// vrt_wave.cu — wavefront form of the voxel_volume pass for sm_100a (default pipeline). Kernels per frame:
+//   1  wave_primary_kernel   one thread per pixel (warp = 8x4 patch): primary ray, G-buffer, compact hit records
+//   2  wave_bounce_kernel x5 reflection bounce w of every chain still alive (compact queue, ping-pong)
+//   3  wave_anyhit_kernel    all AO and shadow rays of all shaded hits: persistent warps pull 32-ray chunks of ONE
+//                            ray kind (AO sample i of 32 neighbouring hits / 32 shadow rays) from a global counter
+//   4  wave_resolve_kernel   shading + reflection sum per primary hit, colour store
+// Versus the per-pixel megakernel (vrt_render.cu): ~40 instead of 117 registers per thread (the bounce stack lives in
+// records, not registers) => 3-4x the resident warps to hide the DDA's dependent-issue latency, and warps stay full
+// because sky pixels / non-metallic pixels / finished pixels do not occupy lanes in the secondary waves.
+#include <cuda_runtime.h>
+#include "vrt_wave.cuh"
+#include "vrt_launch.h"
+
+namespace vrt {
+
+// Warp-aggregated slot allocation; must be called by all 32 lanes.
+__device__ __forceinline__ uint32_t warp_alloc(uint32_t* ctr, bool want) {
+    const unsigned m = __ballot_sync(0xffffffffu, want);
+    if (m == 0) return 0;
+    const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(ctr, (uint32_t)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return base + __popc(m & ((1u << lane) - 1u));
+}
+
+__device__ __forceinline__ void add_totals(Counters* ctr, int stage, unsigned rays, unsigned fetches, unsigned pixels) {
+    const unsigned r = __reduce_add_sync(0xffffffffu, rays);
+    const unsigned f = __reduce_add_sync(0xffffffffu, fetches);
+    const unsigned n = __reduce_add_sync(0xffffffffu, pixels);
+    if ((threadIdx.x & 31) == 0) {
+        if (r) { atomicAdd(&ctr->rays, (unsigned long long)r); atomicAdd(&ctr->stageRays[stage], (unsigned long long)r); }
+        if (f) { atomicAdd(&ctr->fetches, (unsigned long long)f); atomicAdd(&ctr->stageFetches[stage], (unsigned long long)f); }
+        if (n) atomicAdd(&ctr->pixels, (unsigned long long)n);
+    }
+}
+
+__device__ __forceinline__ void store_color(const FrameParams& fp, const PlanesDev& pl, size_t p, V3 c) {
+    reinterpret_cast<uchar4*>(pl.color)[p] = make_uchar4(to_unorm8(c.x), to_unorm8(c.y), to_unorm8(c.z), 0);
+    if (fp.out_mask & VRT_OUT_INSTRUMENT) { pl.color_f32[3 * p + 0] = c.x; pl.color_f32[3 * p + 1] = c.y; pl.color_f32[3 * p + 2] = c.z; }
+}
+
+template <int TRAVERSAL>
+__global__ void __launch_bounds__(128) wave_primary_kernel(const SceneDev sc, const FrameParams fp, const PlanesDev pl, const WaveBuf wb,
+                                                           Counters* __restrict__ ctr) {
+    const int W = fp.cam.screenSize[0], H = fp.cam.screenSize[1];
+    const int j = blockIdx.x >> 3, sub = blockIdx.x & 7;           // local tile, 16x8 sub-block of the tile
+    const int t = j * fp.world + fp.rank;                          // global tile (interleaved shard)
+    const int tx = t % fp.tilesX, ty = t / fp.tilesX;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int lx = (sub & 1) * 16 + (warp & 1) * 8 + (lane & 7);
+    const int ly = (sub >> 1) * 8 + (warp >> 1) * 4 + (lane >> 3);
+    const int px = tx * VRT_TILE + lx, py = ty * VRT_TILE + ly;
+    const bool active = px < W && py < H;
+
+    int action = WAVE_PIXEL_FINAL;
+    PixelOut o;
+    V3 rayDir = mk3(0.0f, 0.0f, 0.0f);
+    size_t p = 0;
+    if (active) {
+        action = wave_primary<TRAVERSAL>(sc, fp, px, py, o, rayDir);
+        p = fp.world == 1 ? (size_t)py * W + px : (size_t)j * (VRT_TILE * VRT_TILE) + ly * VRT_TILE + lx;
+        if (action == WAVE_PIXEL_FINAL) store_color(fp, pl, p, o.color);
+        if (fp.out_mask & VRT_OUT_GBUFFER) {
+            pl.depth[p] = o.depth;
+            reinterpret_cast<float2*>(pl.motion)[p] = make_float2(0.0f, 0.0f);
+            pl.mask[p] = to_unorm8(o.mask);
+            reinterpret_cast<float4*>(pl.position)[p] = make_float4(o.pos.x, o.pos.y, o.pos.z, 0.0f);
+            reinterpret_cast<char4*>(pl.normal)[p] = make_char4(to_snorm8(o.normal.x), to_snorm8(o.normal.y), to_snorm8(o.normal.z), 0);
+        }
+        if (fp.out_mask & VRT_OUT_INSTRUMENT) {
+            auto sat = [](int v) { return (short)(v < -32768 ? -32768 : (v > 32767 ? 32767 : v)); };
+            reinterpret_cast<short4*>(pl.hit)[p] = make_short4(sat(o.hx), sat(o.hy), sat(o.hz), (short)o.steps);
+            pl.hit_palette[p] = (uint8_t)o.palette;
+            pl.rays[p] = 1u;
+            pl.fetches[p] = o.fetches;
+        }
+    }
+    const bool shade = action != WAVE_PIXEL_FINAL, bounce = action == WAVE_PIXEL_SHADE_AND_BOUNCE;
+    const uint32_t idx = warp_alloc(&wb.ctr->n0, shade);
+    if (shade) {
+        RecQ* r = wb.rec + 3 * (size_t)idx;
+        r[0] = mkq(o.pos, (uint32_t)px | ((uint32_t)py << 16));
+        r[1] = mkq(o.normal, o.palette);                           // depth 0
+        r[2] = mkq(rayDir, WAVE_NONE);
+    }
+    const uint32_t qi = warp_alloc(&wb.ctr->qn[0], bounce);
+    if (bounce) { BounceEnt e; e.rec = idx; e.root = idx; wb.bq[0][qi] = e; }
+    add_totals(ctr, 0, active ? 1u : 0u, active ? o.fetches : 0u, active ? 1u : 0u);
+}
+
+template <int TRAVERSAL>
+__global__ void __launch_bounds__(128) wave_bounce_kernel(const SceneDev sc, const FrameParams fp, const PlanesDev pl, const WaveBuf wb,
+                                                          Counters* __restrict__ ctr, const int w) {
+    const uint32_t n = wb.ctr->qn[w];
+    const BounceEnt* __restrict__ qin = wb.bq[w & 1];
+    BounceEnt* __restrict__ qout = wb.bq[(w + 1) & 1];
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t gwarp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+    unsigned rays = 0, fetches = 0;
+    for (uint32_t e0 = gwarp * 32u; e0 < n; e0 += nwarps * 32u) {
+        const uint32_t e = e0 + lane;
+        const bool valid = e < n;
+        BounceEnt ent; ent.rec = 0; ent.root = 0;
+        TraceRes r; r.material = 0; r.fetches = 0; r.pos = r.normal = mk3(0.0f, 0.0f, 0.0f);
+        V3 rd = mk3(0.0f, 0.0f, 0.0f);
+        uint32_t pxy = 0;
+        if (valid) {
+            ent = qin[e];
+            const RecQ* pr = wb.rec + 3 * (size_t)ent.rec;
+            const RecQ p0 = pr[0], p1 = pr[1], p2 = pr[2];
+            pxy = p0.w;
+            r = wave_bounce<TRAVERSAL>(sc, q3(p0), q3(p1), q3(p2), rd);
+            rays++; fetches += r.fetches;
+            if (fp.out_mask & VRT_OUT_INSTRUMENT) {
+                const size_t p = plane_index(fp, (int)(pxy & 0xffffu), (int)(pxy >> 16));
+                atomicAdd(pl.rays + p, 1u); atomicAdd(pl.fetches + p, r.fetches);
+            }
+        }
+        const uint32_t child = wb.pixCap + warp_alloc(&wb.ctr->nb, valid);
+        bool cont = false;
+        if (valid) {
+            RecQ* cr = wb.rec + 3 * (size_t)child;
+            cr[0] = mkq(r.pos, pxy);
+            cr[1] = mkq(r.normal, r.material | ((uint32_t)w << 8));
+            cr[2] = mkq(rd, ent.rec);
+            const bool terminal = r.material == 0 || sc.palette[r.material].metallic <= 0.0f;   // :289-292 lastIdx = w
+            if (terminal) {
+                wb.rec[3 * (size_t)ent.root + 2].w = child;
+                // every record of the chain below the primary hit that is a hit gets its AO + shadow rays
+                const uint32_t cnt = (uint32_t)w + (r.material != 0 ? 1u : 0u);
+                if (cnt) {
+                    uint32_t s = atomicAdd(&wb.ctr->nsq, cnt);
+                    if (r.material != 0) wb.sq[s++] = child;
+                    for (uint32_t k = ent.rec; k != ent.root; k = wb.rec[3 * (size_t)k + 2].w) wb.sq[s++] = k;
+                }
+            } else if (w + 1 < MAX_REFLECTIONS) cont = true;        // else: 5 metallic bounces, lastIdx stays -1 (:298)
+        }
+        const uint32_t qi = warp_alloc(&wb.ctr->qn[w + 1], cont);
+        if (cont) { BounceEnt o; o.rec = child; o.root = ent.root; qout[qi] = o; }
+    }
+    add_totals(ctr, 1, rays, fetches, 0u);
+}
+
+constexpr uint32_t ANYHIT_CHUNK = 8;   // 32-ray groups per work-counter atomic
+
+template <int TRAVERSAL>
+__global__ void __launch_bounds__(256) wave_anyhit_kernel(const SceneDev sc, const FrameParams fp, const PlanesDev pl, const WaveBuf wb,
+                                                          Counters* __restrict__ ctr) {
+    const uint32_t n0 = wb.ctr->n0, S = n0 + wb.ctr->nsq;
+    const uint32_t aoN = (fp.pass_mask & VRT_PASS_AO) ? fp.aoSamples : 0u;
+    const uint32_t R = aoN + ((fp.pass_mask & VRT_PASS_SHADOW) ? 1u : 0u);
+    const unsigned long long total = (unsigned long long)S * R;
+    const uint32_t lane = threadIdx.x & 31;
+    unsigned rays = 0, fetches = 0;
+    for (;;) {
+        uint32_t c = 0;
+        if (lane == 0) c = atomicAdd(&wb.ctr->chunk, 1u);
+        c = __shfl_sync(0xffffffffu, c, 0);
+        const unsigned long long t0 = (unsigned long long)c * (32u * ANYHIT_CHUNK);
+        if (t0 >= total) break;
+        const uint32_t i0 = (uint32_t)(t0 / S);                     // warp-uniform; lanes only add and wrap
+        const uint32_t q0 = (uint32_t)(t0 - (unsigned long long)i0 * S);
+        for (uint32_t g = 0; g < ANYHIT_CHUNK; g++) {
+            if (t0 + g * 32u + lane >= total) break;
+            uint32_t i = i0;
+            unsigned long long qq = (unsigned long long)q0 + g * 32u + lane;
+            while (qq >= S) { qq -= S; i++; }
+            const uint32_t q = (uint32_t)qq;
+            const uint32_t idx = q < n0 ? q : wb.sq[q - n0];
+            const RecQ r0 = wb.rec[3 * (size_t)idx], r1 = wb.rec[3 * (size_t)idx + 1];
+            const int px = (int)(r0.w & 0xffffu), py = (int)(r0.w >> 16);
+            uint32_t f = 0;
+            const bool hit = wave_anyhit<TRAVERSAL>(sc, fp, q3(r0), q3(r1), px, py, r1.w >> 8, i, aoN, f);
+            wb.res[(size_t)i * wb.recCap + idx] = hit ? 1 : 0;
+            rays++; fetches += f;
+            if (fp.out_mask & VRT_OUT_INSTRUMENT) {
+                const size_t p = plane_index(fp, px, py);
+                atomicAdd(pl.rays + p, 1u); atomicAdd(pl.fetches + p, f);
+            }
+        }
+    }
+    add_totals(ctr, 2, rays, fetches, 0u);
+}
+
+__global__ void __launch_bounds__(256) wave_resolve_kernel(const SceneDev sc, const FrameParams fp, const PlanesDev pl, const WaveBuf wb) {
+    const uint32_t n0 = wb.ctr->n0;
+    const uint32_t aoN = (fp.pass_mask & VRT_PASS_AO) ? fp.aoSamples : 0u;
+    for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n0; idx += gridDim.x * blockDim.x) {
+        const uint32_t pxy = wb.rec[3 * (size_t)idx].w;
+        const V3 c = wave_resolve(sc, fp, wb, idx, aoN);
+        store_color(fp, pl, plane_index(fp, (int)(pxy & 0xffffu), (int)(pxy >> 16)), c);
+    }
+}
+
+template <int T>
+static cudaError_t launch_wave_t(const SceneDev& sc, const FrameParams& fp, const PlanesDev& pl, Counters* ctr, const WaveBuf& wb, int sms,
+                                 cudaStream_t stream, uint32_t* launches, cudaEvent_t* ev) {
+    cudaError_t e = cudaMemsetAsync(wb.ctr, 0, sizeof(WaveCtr), stream);
+    if (e != cudaSuccess) return e;
+    static int occAny = 0, occBounce = 0;
+    if (!occAny) {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occAny, wave_anyhit_kernel<T>, 256, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occBounce, wave_bounce_kernel<T>, 128, 0);
+        if (occAny < 1) occAny = 1;
+        if (occBounce < 1) occBounce = 1;
+    }
+    wave_primary_kernel<T><<<(unsigned)fp.localTiles * 8u, 128, 0, stream>>>(sc, fp, pl, wb, ctr);
+    uint32_t n = 1;
+    if (ev) cudaEventRecord(ev[0], stream);
+    const bool shade = (fp.pass_mask & VRT_PASS_SHADE) != 0;
+    if (shade && (fp.pass_mask & VRT_PASS_REFLECT))
+        for (int w = 0; w < MAX_REFLECTIONS; w++) { wave_bounce_kernel<T><<<(unsigned)(sms * occBounce), 128, 0, stream>>>(sc, fp, pl, wb, ctr, w); n++; }
+    if (ev) cudaEventRecord(ev[1], stream);
+    const uint32_t aoN = (fp.pass_mask & VRT_PASS_AO) ? fp.aoSamples : 0u;
+    if (shade && (aoN || (fp.pass_mask & VRT_PASS_SHADOW))) { wave_anyhit_kernel<T><<<(unsigned)(sms * occAny), 256, 0, stream>>>(sc, fp, pl, wb, ctr); n++; }
+    if (ev) cudaEventRecord(ev[2], stream);
+    if (shade) { wave_resolve_kernel<<<(unsigned)(sms * 8), 256, 0, stream>>>(sc, fp, pl, wb); n++; }
+    if (launches) *launches += n;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_wavefront(const SceneDev& sc, const FrameParams& fp, const PlanesDev& pl, Counters* ctr, const WaveBuf& wb, int sms,
+                             cudaStream_t stream, uint32_t* launches, cudaEvent_t* ev) {
+    if (fp.localTiles <= 0) return cudaSuccess;
+    if (fp.traversal == VRT_TRAVERSAL_DENSE_U8) return launch_wave_t<VRT_TRAVERSAL_DENSE_U8>(sc, fp, pl, ctr, wb, sms, stream, launches, ev);
+    if (fp.traversal == VRT_TRAVERSAL_FINE) return launch_wave_t<VRT_TRAVERSAL_FINE>(sc, fp, pl, ctr, wb, sms, stream, launches, ev);
+    return launch_wave_t<VRT_TRAVERSAL_BRICK>(sc, fp, pl, ctr, wb, sms, stream, launches, ev);
+}
+
+}  // namespace vrt

@@ -16,6 +16,7 @@ LIB_PATH = os.environ.get("VRT_LIB", os.path.join(HERE, "libvrt.so"))   # VRT_LI
 PASS_PRIMARY, PASS_SHADOW, PASS_AO, PASS_REFLECT, PASS_SHADE, PASS_ALL = 1, 2, 4, 8, 16, 31
 OUT_GBUFFER, OUT_INSTRUMENT = 1, 2
 TRAVERSAL_DEFAULT, TRAVERSAL_DENSE_U8, TRAVERSAL_BRICK, TRAVERSAL_FINE = 0, 1, 2, 3
+PIPELINE_DEFAULT, PIPELINE_MEGAKERNEL, PIPELINE_WAVEFRONT = 0, 1, 2
 DENOISE_AS_EXECUTED, DENOISE_AS_INTENDED = 0, 1
 E_LFS_POINTER, E_NO_INSTANCE, E_PARSE, E_IO, E_CUDA, E_NO_DEVICE = -2, -3, -4, -5, -6, -7
 
@@ -46,13 +47,14 @@ class DenoiserSettings(C.Structure):
 
 
 class RenderSettings(C.Structure):
-    _fields_ = [("pass_mask", C.c_uint32), ("out_mask", C.c_uint32), ("traversal", C.c_uint32), ("reserved", C.c_uint32),
+    _fields_ = [("pass_mask", C.c_uint32), ("out_mask", C.c_uint32), ("traversal", C.c_uint32), ("pipeline", C.c_uint32),
                 ("vol", VolumeParams), ("light", Light), ("denoise", DenoiserSettings)]
 
 
 class FrameStats(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("fetches", C.c_uint64), ("pixels", C.c_uint64), ("ms_trace", C.c_float),
-                ("ms_denoise", C.c_float), ("ms_total", C.c_float), ("kernel_launches", C.c_uint32), ("reserved", C.c_uint32)]
+                ("ms_denoise", C.c_float), ("ms_total", C.c_float), ("kernel_launches", C.c_uint32), ("reserved", C.c_uint32),
+                ("ms_stage", C.c_float * 4), ("stage_rays", C.c_uint64 * 3), ("stage_fetches", C.c_uint64 * 3)]
 
 
 class VrtError(RuntimeError):
@@ -241,7 +243,7 @@ class Frame:
 
     def stats(self) -> dict:
         s = FrameStats(); _ck(lib().vrt_frame_stats_get(self.h, C.byref(s)))
-        return {k: getattr(s, k) for k, _ in FrameStats._fields_ if k != "reserved"}
+        return {k: (list(getattr(s, k)) if k.startswith(("ms_stage", "stage_")) else getattr(s, k)) for k, _ in FrameStats._fields_ if k != "reserved"}
 
     def release(self):
         if self.h:
