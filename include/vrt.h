@@ -74,7 +74,7 @@ enum {
     VRT_OUT_INSTRUMENT = 2,   /* hit voxel + step count, palette index, float colour, per-pixel ray / fetch counts */
 };
 /* traversal back-ends (all bit-identical; for measurement). 0 = library default. */
-enum { VRT_TRAVERSAL_DEFAULT = 0, VRT_TRAVERSAL_DENSE_U8 = 1, VRT_TRAVERSAL_BRICK = 2, VRT_TRAVERSAL_FINE = 3 };
+enum { VRT_TRAVERSAL_DEFAULT = 0, VRT_TRAVERSAL_DENSE_U8 = 1, VRT_TRAVERSAL_BRICK = 2, VRT_TRAVERSAL_FINE = 3, VRT_TRAVERSAL_LINEAR = 4 };
 
 /* how the pass is scheduled on the GPU (all bit-identical; for measurement). 0 = library default (wavefront).
  *   MEGAKERNEL: one thread runs a pixel's whole ray tree (the shader's own shape).

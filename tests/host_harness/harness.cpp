@@ -48,7 +48,7 @@ static void build_bricks(const uint8_t* vol, uint32_t W, uint32_t H, uint32_t D,
 
 // CPU restatement of the per-voxel safe-step field builder (csrc/vrt_accel.cu launch_build_fdist)
 static void build_fdist(const uint8_t* vol, int W, int H, int D, const std::vector<uint8_t>& bdist, uint32_t Bx, uint32_t By, uint32_t Bz,
-                        std::vector<uint8_t>& fdist) {
+                        std::vector<uint8_t>& fdist, std::vector<uint8_t>& ldist) {
     const size_t n = (size_t)W * H * D;
     std::vector<uint8_t> a(n), nx(n);
     for (size_t i = 0; i < n; i++) a[i] = vol[i] ? 0 : VRT_FINE_CAP;
@@ -64,20 +64,22 @@ static void build_fdist(const uint8_t* vol, int W, int H, int D, const std::vect
         a.swap(nx);
     }
     fdist.assign((size_t)Bx * By * Bz * 64, 0);
+    ldist.assign((size_t)(W + 2) * (H + 2) * (D + 2), (uint8_t)VRT_LIN_OOB);
     for (int z = 0; z < D; z++) for (int y = 0; y < H; y++) for (int x = 0; x < W; x++) {
         const uint32_t f = a[(size_t)x + (size_t)y * W + (size_t)z * W * H];
         const size_t b = (size_t)(z >> 2) * By * Bx + (size_t)(y >> 2) * Bx + (x >> 2);
         const uint32_t d = bdist[b];
         uint32_t v = f;
         if (f != 0 && d != 0) v = std::max(f, (d - 1u) * 4u + 1u);
-        fdist[b * 64 + ((x & 3) | ((y & 3) << 2) | ((z & 3) << 4))] = (uint8_t)std::min(v, 255u);
+        fdist[b * 64 + ((x & 3) | ((y & 3) << 2) | ((z & 3) << 4))] = (uint8_t)std::min(v, 254u);
+        ldist[(size_t)(x + 1) + (size_t)(y + 1) * (W + 2) + (size_t)(z + 1) * (W + 2) * (H + 2)] = (uint8_t)std::min(v, 254u);
     }
 }
 
 struct HScene {
     SceneDev dev;
     std::vector<unsigned long long> bmask;
-    std::vector<uint8_t> bdist, fdist;
+    std::vector<uint8_t> bdist, fdist, ldist;
 };
 
 extern "C" void* hh_scene_create(const uint8_t* vol, uint32_t W, uint32_t H, uint32_t D, const float* palette,
@@ -86,8 +88,8 @@ extern "C" void* hh_scene_create(const uint8_t* vol, uint32_t W, uint32_t H, uin
     memset(&s->dev, 0, sizeof(SceneDev));
     s->dev.vol = vol; s->dev.W = W; s->dev.H = H; s->dev.D = D;
     build_bricks(vol, W, H, D, s->bmask, s->bdist, s->dev.Bx, s->dev.By, s->dev.Bz);
-    build_fdist(vol, (int)W, (int)H, (int)D, s->bdist, s->dev.Bx, s->dev.By, s->dev.Bz, s->fdist);
-    s->dev.bmask = s->bmask.data(); s->dev.bdist = s->bdist.data(); s->dev.fdist = s->fdist.data();
+    build_fdist(vol, (int)W, (int)H, (int)D, s->bdist, s->dev.Bx, s->dev.By, s->dev.Bz, s->fdist, s->ldist);
+    s->dev.bmask = s->bmask.data(); s->dev.bdist = s->bdist.data(); s->dev.fdist = s->fdist.data(); s->dev.ldist = s->ldist.data();
     s->dev.palette = reinterpret_cast<const vrt_material*>(palette);
     s->dev.noise = noise; s->dev.sky = sky; s->dev.skyW = skyW; s->dev.skyH = skyH;
     return s;
@@ -113,6 +115,7 @@ extern "C" int hh_render(void* scene, const vrt_camera* cam, const vrt_render_se
             PixelOut o; memset(&o, 0, sizeof(o));
             if (traversal == VRT_TRAVERSAL_DENSE_U8) render_pixel<VRT_TRAVERSAL_DENSE_U8>(s->dev, fp, px, py, o);
             else if (traversal == VRT_TRAVERSAL_FINE) render_pixel<VRT_TRAVERSAL_FINE>(s->dev, fp, px, py, o);
+            else if (traversal == VRT_TRAVERSAL_LINEAR) render_pixel<VRT_TRAVERSAL_LINEAR>(s->dev, fp, px, py, o);
             else render_pixel<VRT_TRAVERSAL_BRICK>(s->dev, fp, px, py, o);
             size_t p = (size_t)py * W + px;
             auto sat = [](int v) { return (int16_t)(v < -32768 ? -32768 : (v > 32767 ? 32767 : v)); };
@@ -212,6 +215,7 @@ extern "C" int hh_render_wave(void* scene, const vrt_camera* cam, const vrt_rend
     if (row_end > cam->screenSize[1]) row_end = cam->screenSize[1];
     if (traversal == VRT_TRAVERSAL_DENSE_U8) render_wave<VRT_TRAVERSAL_DENSE_U8>(s->dev, fp, pl, row_begin, row_end, row_step);
     else if (traversal == VRT_TRAVERSAL_FINE) render_wave<VRT_TRAVERSAL_FINE>(s->dev, fp, pl, row_begin, row_end, row_step);
+    else if (traversal == VRT_TRAVERSAL_LINEAR) render_wave<VRT_TRAVERSAL_LINEAR>(s->dev, fp, pl, row_begin, row_end, row_step);
     else render_wave<VRT_TRAVERSAL_BRICK>(s->dev, fp, pl, row_begin, row_end, row_step);
     return 0;
 }

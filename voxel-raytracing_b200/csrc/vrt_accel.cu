@@ -105,7 +105,7 @@ __global__ void fine_pass4_kernel(const uint32_t* __restrict__ in, uint32_t* __r
 }
 // merge with the far-field bound of the brick level and store 4x4x4-bricked
 __global__ void fine_merge_kernel(const uint8_t* __restrict__ fine, const uint8_t* __restrict__ bdist, uint8_t* __restrict__ fdist,
-                                  uint32_t W, uint32_t H, uint32_t D, uint32_t Bx, uint32_t By) {
+                                  uint8_t* __restrict__ ldist, uint32_t W, uint32_t H, uint32_t D, uint32_t Bx, uint32_t By) {
     const uint32_t x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, z = blockIdx.z;
     if (x >= W) return;
     const uint32_t f = fine[(size_t)x + (size_t)y * W + (size_t)z * W * H];
@@ -113,14 +113,18 @@ __global__ void fine_merge_kernel(const uint8_t* __restrict__ fine, const uint8_
     const uint32_t d = bdist[b];
     uint32_t n = f;
     if (f != 0 && d != 0) n = max(f, (d - 1u) * 4u + 1u);
-    fdist[b * 64u + ((x & 3u) | ((y & 3u) << 2) | ((z & 3u) << 4))] = (uint8_t)min(n, 255u);
+    n = min(n, 254u);
+    fdist[b * 64u + ((x & 3u) | ((y & 3u) << 2) | ((z & 3u) << 4))] = (uint8_t)n;
+    ldist[(size_t)(x + 1u) + (size_t)(y + 1u) * (W + 2u) + (size_t)(z + 1u) * (W + 2u) * (H + 2u)] = (uint8_t)n;
 }
 
-cudaError_t launch_build_fdist(const uint8_t* vol, const uint8_t* bdist, uint32_t W, uint32_t H, uint32_t D, uint8_t* fdist,
+cudaError_t launch_build_fdist(const uint8_t* vol, const uint8_t* bdist, uint32_t W, uint32_t H, uint32_t D, uint8_t* fdist, uint8_t* ldist,
                                uint8_t* a, uint8_t* t1, uint8_t* t2, cudaStream_t stream, int* launches) {
     const size_t n = (size_t)W * H * D;
     const uint32_t Bx = (W + 3) / 4, By = (H + 3) / 4, Bz = (D + 3) / 4;
     cudaError_t e = cudaMemsetAsync(fdist, 0, (size_t)Bx * By * Bz * 64u, stream);   // padding voxels of edge bricks
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(ldist, (int)VRT_LIN_OOB, (size_t)(W + 2u) * (H + 2u) * (D + 2u), stream);               // apron
     if (e != cudaSuccess) return e;
     fine_init_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(vol, a, n);
     int cnt = 1;
@@ -140,7 +144,7 @@ cudaError_t launch_build_fdist(const uint8_t* vol, const uint8_t* bdist, uint32_
         }
         cnt += 3;
     }
-    fine_merge_kernel<<<dim3((W + 127) / 128, H, D), 128, 0, stream>>>(a, bdist, fdist, W, H, D, Bx, By);
+    fine_merge_kernel<<<dim3((W + 127) / 128, H, D), 128, 0, stream>>>(a, bdist, fdist, ldist, W, H, D, Bx, By);
     cnt++;
     if (launches) *launches += cnt;
     return cudaGetLastError();

@@ -28,7 +28,7 @@ struct vrt_context {
 struct vrt_scene {
     vrt_context* ctx = nullptr;
     uint32_t w = 0, h = 0, d = 0, Bx = 0, By = 0, Bz = 0;
-    uint8_t* vol = nullptr; unsigned long long* bmask = nullptr; uint8_t* bdist = nullptr; uint8_t* fdist = nullptr;
+    uint8_t* vol = nullptr; unsigned long long* bmask = nullptr; uint8_t* bdist = nullptr; uint8_t* fdist = nullptr; uint8_t* ldist = nullptr;
     vrt_material* palette = nullptr; vrt_material hostPalette[256];
     uint8_t* noise = nullptr; float* sky = nullptr; uint32_t skyW = 0, skyH = 0;
     int accelLaunches = 0;
@@ -101,7 +101,7 @@ extern "C" void* vrt_context_stream(vrt_context* c) { return c ? (void*)c->strea
 extern "C" void vrt_scene_destroy(vrt_scene* s) {
     if (!s) return;
     cudaSetDevice(s->ctx->device);
-    cudaFree(s->vol); cudaFree(s->bmask); cudaFree(s->bdist); cudaFree(s->fdist); cudaFree(s->palette); cudaFree(s->noise); cudaFree(s->sky);
+    cudaFree(s->vol); cudaFree(s->bmask); cudaFree(s->bdist); cudaFree(s->fdist); cudaFree(s->ldist); cudaFree(s->palette); cudaFree(s->noise); cudaFree(s->sky);
     delete s;
 }
 
@@ -118,6 +118,7 @@ static int scene_alloc(vrt_context* c, uint32_t w, uint32_t h, uint32_t d, vrt_s
     if (e == cudaSuccess) e = cudaMalloc(&s->bmask, nb * 8);
     if (e == cudaSuccess) e = cudaMalloc(&s->bdist, nb);
     if (e == cudaSuccess) e = cudaMalloc(&s->fdist, nb * 64);
+    if (e == cudaSuccess) e = cudaMalloc(&s->ldist, (size_t)(w + 2) * (h + 2) * (d + 2));
     if (e == cudaSuccess) e = cudaMalloc(&s->palette, sizeof(vrt_material) * 256);
     if (e != cudaSuccess) { vrt_scene_destroy(s); return fail(e == cudaErrorMemoryAllocation ? VRT_E_OOM : VRT_E_CUDA, cudaGetErrorString(e)); }
     *out = s;
@@ -142,7 +143,7 @@ static int scene_finish(vrt_scene* s, const vrt_material palette[256]) {
     e = cudaMalloc(&a, nv);
     if (e == cudaSuccess) e = cudaMalloc(&t1, nv);
     if (e == cudaSuccess) e = cudaMalloc(&t2, nv);
-    if (e == cudaSuccess) e = launch_build_fdist(s->vol, s->bdist, s->w, s->h, s->d, s->fdist, a, t1, t2, c->stream, &s->accelLaunches);
+    if (e == cudaSuccess) e = launch_build_fdist(s->vol, s->bdist, s->w, s->h, s->d, s->fdist, s->ldist, a, t1, t2, c->stream, &s->accelLaunches);
     e2 = cudaStreamSynchronize(c->stream);
     cudaFree(a); cudaFree(t1); cudaFree(t2);
     if (e != cudaSuccess) return fail(e == cudaErrorMemoryAllocation ? VRT_E_OOM : VRT_E_CUDA, cudaGetErrorString(e));
@@ -232,7 +233,7 @@ extern "C" int vrt_scene_accel_info(const vrt_scene* s, size_t* dense_bytes, siz
     const size_t nb = (size_t)s->Bx * s->By * s->Bz;
     if (dense_bytes) *dense_bytes = (size_t)s->w * s->h * s->d;
     if (brick_mask_bytes) *brick_mask_bytes = nb * 8;
-    if (brick_dist_bytes) *brick_dist_bytes = nb + nb * 64;   // bdist + fdist
+    if (brick_dist_bytes) *brick_dist_bytes = nb + nb * 64 + (size_t)(s->w + 2) * (s->h + 2) * (s->d + 2);   // bdist + fdist + ldist
     return VRT_OK;
 }
 
@@ -366,7 +367,7 @@ extern "C" int vrt_render(vrt_context* c, const vrt_scene* s, const vrt_camera* 
     if (cam->volumeBounds[0] != s->w || cam->volumeBounds[1] != s->h || cam->volumeBounds[2] != s->d)
         return fail(VRT_E_INVALID, "camera volumeBounds differ from the scene bounds");
     if (!(st->pass_mask & VRT_PASS_PRIMARY)) return fail(VRT_E_INVALID, "pass_mask must include VRT_PASS_PRIMARY");
-    if (st->traversal > VRT_TRAVERSAL_FINE) return fail(VRT_E_INVALID, "unknown traversal");
+    if (st->traversal > VRT_TRAVERSAL_LINEAR) return fail(VRT_E_INVALID, "unknown traversal");
     if (st->pipeline > VRT_PIPELINE_WAVEFRONT) return fail(VRT_E_INVALID, "unknown pipeline");
     if (st->vol.aoSamples > 255) return fail(VRT_E_INVALID, "aoSamples must be <= 255 (the reference GUI allows 0..16)");
     const bool wavefront = st->pipeline != VRT_PIPELINE_MEGAKERNEL;
@@ -389,7 +390,7 @@ extern "C" int vrt_render(vrt_context* c, const vrt_scene* s, const vrt_camera* 
     if (rc) { if (!*frame) vrt_frame_release(f); return rc; }
 
     SceneDev sc{};
-    sc.vol = s->vol; sc.bmask = s->bmask; sc.bdist = s->bdist; sc.fdist = s->fdist; sc.W = s->w; sc.H = s->h; sc.D = s->d; sc.Bx = s->Bx; sc.By = s->By; sc.Bz = s->Bz;
+    sc.vol = s->vol; sc.bmask = s->bmask; sc.bdist = s->bdist; sc.fdist = s->fdist; sc.ldist = s->ldist; sc.W = s->w; sc.H = s->h; sc.D = s->d; sc.Bx = s->Bx; sc.By = s->By; sc.Bz = s->Bz;
     sc.palette = s->palette; sc.noise = s->noise; sc.sky = s->sky; sc.skyW = s->skyW; sc.skyH = s->skyH;
     FrameParams fp{};
     fp.cam = *cam; fp.pass_mask = st->pass_mask; fp.out_mask = out_mask;

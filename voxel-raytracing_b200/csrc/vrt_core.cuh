@@ -4,6 +4,7 @@
 // compile with -fmad=false (nvcc) / -ffp-contract=off (g++); never -use_fast_math; IEEE div/sqrt.
 #pragma once
 #include <math.h>
+#include <string.h>
 #include "vrt_types.h"
 
 namespace vrt {
@@ -129,13 +130,96 @@ VRT_HD uint32_t fetch_voxel(const SceneDev& sc, const Dda& s) {   // getVoxel :7
     return sc.vol[(size_t)s.mx + (size_t)s.my * sc.W + (size_t)s.mz * sc.W * (size_t)sc.H];
 }
 
+// ---- VRT_TRAVERSAL_LINEAR: resumable ray over the aproned linear safe-step field (ldist) ----
+// Look-up = 3 x (FADD, FFMA) + 3 integer multiply-adds + one byte load. The per-axis step count since entry is
+// recovered as rint((sideDist - sideDist0) * |dir|) by adding 1.5*2^23 inside the FFMA: the sum's low mantissa bits are
+// the integer (error of <= 512 accumulated adds < 0.02 step, so the rounding is exact). No coordinates, no bounds test
+// (apron), no brick address arithmetic.
+constexpr float VRT_LIN_MAGIC = 12582912.0f;
+constexpr int VRT_LIN_MAGIC_BITS = 0x4B400000;
+VRT_HD int lin_count(float s, float s0, float a) {
+#if defined(__CUDA_ARCH__)
+    return __float_as_int(__fmaf_rn(s - s0, a, VRT_LIN_MAGIC)) - VRT_LIN_MAGIC_BITS;
+#else
+    const float r = fmaf(s - s0, a, VRT_LIN_MAGIC);
+    int b; memcpy(&b, &r, 4); return b - VRT_LIN_MAGIC_BITS;
+#endif
+}
+VRT_HD int lin_bits(float s, float s0, float a) {   // VRT_LIN_MAGIC_BITS + count
+#if defined(__CUDA_ARCH__)
+    return __float_as_int(__fmaf_rn(s - s0, a, VRT_LIN_MAGIC));
+#else
+    const float r = fmaf(s - s0, a, VRT_LIN_MAGIC);
+    int b; memcpy(&b, &r, 4); return b;
+#endif
+}
+struct LinRay {
+    float sx, sy, sz;          // sideDist
+    float dx, dy, dz;          // deltaDist
+    float sx0, sy0, sz0;       // sideDist at entry
+    float ax, ay, az;          // |dir|
+    const uint8_t* p0;         // &ldist[entry voxel]
+    int SX, SY, SZ;            // signed ldist strides of one step per axis (|SZ| <= (W+2)(H+2) < 2^31)
+    int T0;                    // -MAGIC_BITS * (SX + SY), 32-bit wrap-around
+    uint32_t i, maxSteps;
+    uint32_t mask;             // axes advanced by the last step
+    int mx0, my0, mz0, stx, sty, stz;
+};
+enum { LIN_CONTINUE = 0, LIN_HIT = 1, LIN_OOB = 2, LIN_EXHAUSTED = 3 };
+
+// Entry state from the DDA set-up of traceRayInt (:131-150). Returns LIN_OOB when mapPos starts outside the volume.
+VRT_HD int lin_begin(const SceneDev& sc, const Dda& s, V3 dir, uint32_t maxSteps, LinRay& r) {
+    r.sx = r.sx0 = s.sx; r.sy = r.sy0 = s.sy; r.sz = r.sz0 = s.sz;
+    r.dx = s.dx; r.dy = s.dy; r.dz = s.dz;
+    r.ax = fabsf(dir.x); r.ay = fabsf(dir.y); r.az = fabsf(dir.z);
+    r.mx0 = s.mx; r.my0 = s.my; r.mz0 = s.mz; r.stx = s.stx; r.sty = s.sty; r.stz = s.stz;
+    r.i = 0; r.maxSteps = maxSteps; r.mask = 0;
+    if (!in_bounds(sc, s)) return LIN_OOB;
+    const int LW = (int)sc.W + 2, LWH = LW * ((int)sc.H + 2);
+    r.p0 = sc.ldist + ((size_t)(s.mx + 1) + (size_t)(s.my + 1) * (size_t)LW + (size_t)(s.mz + 1) * (size_t)LWH);
+    r.SX = s.stx; r.SY = s.sty * LW; r.SZ = s.stz * LWH;
+    r.T0 = (int)(0u - (uint32_t)VRT_LIN_MAGIC_BITS * (uint32_t)(r.SX + r.SY));
+#if defined(__CUDA_ARCH__)
+    // keep the strides in registers: without this ptxas re-derives them from W and H (64-bit multiplies) at every look-up
+    asm volatile("" : "+r"(r.SX), "+r"(r.SY), "+r"(r.SZ), "+r"(r.T0), "+l"(r.p0));
+#endif
+    return LIN_CONTINUE;
+}
+// One look-up and the steps it allows. STEP_REC: keep the mask of the last step (needed for the hit normal).
+template <bool STEP_REC>
+VRT_HD int lin_round(const SceneDev& sc, LinRay& r) {
+    const int bx = lin_bits(r.sx, r.sx0, r.ax), by = lin_bits(r.sy, r.sy0, r.ay), bz = lin_bits(r.sz, r.sz0, r.az);
+    const int t = (int)((uint32_t)bx * (uint32_t)r.SX + (uint32_t)by * (uint32_t)r.SY + (uint32_t)r.T0);   // cx*SX + cy*SY
+    const long long off = (long long)(bz - VRT_LIN_MAGIC_BITS) * (long long)r.SZ + (long long)t;
+#if defined(__CUDA_ARCH__)
+    uint32_t n;
+    asm("ld.global.nc.u8 %0, [%1];" : "=r"(n) : "l"(r.p0 + off));   // p0 went through an asm barrier: say "global" again
+#else
+    uint32_t n = r.p0[off];
+#endif
+    if (n == 0) return LIN_HIT;
+    if (n == VRT_LIN_OOB) return LIN_OOB;
+    const uint32_t left = r.maxSteps - r.i;
+    n = n < left ? n : left;
+    r.i += n;
+    Dda d; d.sx = r.sx; d.sy = r.sy; d.sz = r.sz; d.dx = r.dx; d.dy = r.dy; d.dz = r.dz;
+    for (uint32_t k = n - 1; k > 0; k--) dda_step_f(d);
+    if (STEP_REC) r.mask = dda_step_f_rec(d); else dda_step_f(d);
+    r.sx = d.sx; r.sy = d.sy; r.sz = d.sz;
+    return r.i >= r.maxSteps ? LIN_EXHAUSTED : LIN_CONTINUE;
+}
+// mapPos of the current state
+VRT_HD void lin_map_pos(const LinRay& r, int& mx, int& my, int& mz) {
+    mx = r.mx0 + lin_count(r.sx, r.sx0, r.ax) * r.stx;
+    my = r.my0 + lin_count(r.sy, r.sy0, r.ay) * r.sty;
+    mz = r.mz0 + lin_count(r.sz, r.sz0, r.az) * r.stz;
+}
+
 // traceRayInt + traceRay (:127-196). TRAVERSAL selects how voxel emptiness is learned; the float/int DDA state
 // evolves identically in every variant (one dda_step per reference iteration).
-template <int TRAVERSAL>
-VRT_HD TraceRes trace_ray(const SceneDev& sc, V3 start, V3 dir, uint32_t maxSteps) {
-    TraceRes r;
-    V3 pos = box_intersection(sc, start, dir);
-    Dda s;
+// DDA set-up of traceRayInt (:131-150). Returns whether the fast select-form step may be used (finite deltaDist).
+VRT_HD bool dda_begin(const SceneDev& sc, V3 start, V3 dir, V3& pos, Dda& s) {
+    pos = box_intersection(sc, start, dir);
     s.mx = f2i(floorf(pos.x)); s.my = f2i(floorf(pos.y)); s.mz = f2i(floorf(pos.z));
     s.dx = fabsf(1.0f / dir.x); s.dy = fabsf(1.0f / dir.y); s.dz = fabsf(1.0f / dir.z);
     const float gx = signf(dir.x), gy = signf(dir.y), gz = signf(dir.z);
@@ -143,10 +227,22 @@ VRT_HD TraceRes trace_ray(const SceneDev& sc, V3 start, V3 dir, uint32_t maxStep
     s.sx = ((gx * ((float)s.mx - pos.x) + (gx * 0.5f)) + 0.5f) * s.dx;
     s.sy = ((gy * ((float)s.my - pos.y) + (gy * 0.5f)) + 0.5f) * s.dy;
     s.sz = ((gz * ((float)s.mz - pos.z) + (gz * 0.5f)) + 0.5f) * s.dz;
+    return finitef(s.dx) && finitef(s.dy) && finitef(s.dz);
+}
+// LINEAR additionally needs a finite start (see trace_ray)
+VRT_HD bool lin_usable(bool fast, const Dda& s) { return fast && finitef(s.sx) && finitef(s.sy) && finitef(s.sz); }
+
+template <int TRAVERSAL>
+VRT_HD TraceRes trace_ray(const SceneDev& sc, V3 start, V3 dir, uint32_t maxSteps) {
+    TraceRes r;
+    V3 pos;
+    Dda s;
+    bool fast = dda_begin(sc, start, dir, pos, s);
 
     uint32_t i = 0, mask = 0, material = 0;
     bool hit = false, oob = false;
-    const bool fast = finitef(s.dx) && finitef(s.dy) && finitef(s.dz);
+    // a NaN / infinite start (origin built from a NaN normal) never moves: the literal loop replays that too
+    if (TRAVERSAL == VRT_TRAVERSAL_LINEAR) fast = lin_usable(fast, s);
     if (!fast) {
         // literal loop: rays with a zero / denormal / NaN direction component
         for (; i < maxSteps; i++) {
@@ -162,6 +258,15 @@ VRT_HD TraceRes trace_ray(const SceneDev& sc, V3 start, V3 dir, uint32_t maxStep
             if (material != 0) { hit = true; break; }
             mask = dda_step_rec(s);
         }
+    } else if (TRAVERSAL == VRT_TRAVERSAL_LINEAR) {
+        LinRay lr;
+        int st = lin_begin(sc, s, dir, maxSteps, lr);
+        while (st == LIN_CONTINUE) st = lin_round<true>(sc, lr);
+        lin_map_pos(lr, s.mx, s.my, s.mz);
+        s.sx = lr.sx; s.sy = lr.sy; s.sz = lr.sz;
+        i = lr.i; mask = lr.mask;
+        if (st == LIN_HIT) { material = fetch_voxel(sc, s); hit = true; }
+        else if (st == LIN_OOB) oob = true;
     } else if (TRAVERSAL == VRT_TRAVERSAL_FINE) {
         // Per-voxel safe-step field. mapPos is not carried through the steps: it is recovered at each lookup from
         // how far sideDist has advanced, c = rint((sideDist - sideDist0) / deltaDist) per axis. The accumulated

@@ -16,8 +16,8 @@ cudaError_t launch_detile(const void* src, void* dst, int W, int H, int world, s
 cudaError_t launch_build_accel(const uint8_t* vol, uint32_t W, uint32_t H, uint32_t D, unsigned long long* bmask, uint8_t* bdist,
                                uint8_t* tmpA, uint8_t* tmpB, cudaStream_t stream, int* launches);
 
-// per-voxel safe-step field (bricked) from the volume and bdist; a/t1/t2 are scratch of W*H*D bytes each
-cudaError_t launch_build_fdist(const uint8_t* vol, const uint8_t* bdist, uint32_t W, uint32_t H, uint32_t D, uint8_t* fdist,
+// per-voxel safe-step field (bricked fdist + linear aproned ldist) from the volume and bdist; a/t1/t2 are scratch of W*H*D bytes each
+cudaError_t launch_build_fdist(const uint8_t* vol, const uint8_t* bdist, uint32_t W, uint32_t H, uint32_t D, uint8_t* fdist, uint8_t* ldist,
                                uint8_t* a, uint8_t* t1, uint8_t* t2, cudaStream_t stream, int* launches);
 
 // procedural volumes (vrt_generate.cu)

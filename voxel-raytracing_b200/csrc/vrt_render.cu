@@ -64,6 +64,7 @@ cudaError_t launch_render(const SceneDev& sc, const FrameParams& fp, const Plane
     const dim3 grid((unsigned)fp.localTiles * 8u), block(128);
     if (fp.traversal == VRT_TRAVERSAL_DENSE_U8) render_kernel<VRT_TRAVERSAL_DENSE_U8><<<grid, block, 0, stream>>>(sc, fp, pl, ctr);
     else if (fp.traversal == VRT_TRAVERSAL_FINE) render_kernel<VRT_TRAVERSAL_FINE><<<grid, block, 0, stream>>>(sc, fp, pl, ctr);
+    else if (fp.traversal == VRT_TRAVERSAL_LINEAR) render_kernel<VRT_TRAVERSAL_LINEAR><<<grid, block, 0, stream>>>(sc, fp, pl, ctr);
     else render_kernel<VRT_TRAVERSAL_BRICK><<<grid, block, 0, stream>>>(sc, fp, pl, ctr);
     return cudaGetLastError();
 }

@@ -24,12 +24,18 @@ constexpr int VRT_DIST_CAP = 33;      // (33-1)*4+1 = 129 unchecked steps at mos
 //              empty and in bounds and fdist[v] steps can run before memory is looked at again. Built as
 //              max(min(C(v), VRT_FINE_CAP) [exact near surfaces], (bdist-1)*4+1 [far field]).
 constexpr int VRT_FINE_CAP = 15;
+//   ldist[v] : the same safe-step values stored LINEARLY with a one-voxel apron: ldist[(x+1) + (y+1)*LW + (z+1)*LW*LH],
+//              LW = W+2, LH = H+2; apron voxels (the layer just outside the volume) hold VRT_LIN_OOB. A ray that does its
+//              look-ups every fdist steps can be at most one voxel outside the volume when it looks again, so the
+//              traversal needs no bounds test and no coordinates: one byte load at entry_offset + sum(count_axis * stride_axis).
+constexpr uint32_t VRT_LIN_OOB = 255;
 
 struct SceneDev {
     const uint8_t* vol;               // dense u8[W*H*D], x fastest (voxel_scene.cpp:99)
     const unsigned long long* bmask;  // [Bz][By][Bx]
     const uint8_t* bdist;             // [Bz][By][Bx]
     const uint8_t* fdist;             // [Bz][By][Bx][4][4][4]
+    const uint8_t* ldist;             // [D+2][H+2][W+2]
     uint32_t W, H, D;
     uint32_t Bx, By, Bz;
     const vrt_material* palette;      // 256 entries

@@ -225,6 +225,7 @@ cudaError_t launch_wavefront(const SceneDev& sc, const FrameParams& fp, const Pl
     if (fp.localTiles <= 0) return cudaSuccess;
     if (fp.traversal == VRT_TRAVERSAL_DENSE_U8) return launch_wave_t<VRT_TRAVERSAL_DENSE_U8>(sc, fp, pl, ctr, wb, sms, stream, launches, ev);
     if (fp.traversal == VRT_TRAVERSAL_FINE) return launch_wave_t<VRT_TRAVERSAL_FINE>(sc, fp, pl, ctr, wb, sms, stream, launches, ev);
+    if (fp.traversal == VRT_TRAVERSAL_LINEAR) return launch_wave_t<VRT_TRAVERSAL_LINEAR>(sc, fp, pl, ctr, wb, sms, stream, launches, ev);
     return launch_wave_t<VRT_TRAVERSAL_BRICK>(sc, fp, pl, ctr, wb, sms, stream, launches, ev);
 }
 

@@ -70,10 +70,8 @@ VRT_HD TraceRes wave_bounce(const SceneDev& sc, V3 pos, V3 normal, V3 dir, V3& r
 }
 
 // ray i of a shaded hit: i < aoN -> AO ray i (:214-223, 64 steps), i == aoN -> shadow ray (:230-233, 512 steps)
-template <int TRAVERSAL>
-VRT_HD bool wave_anyhit(const SceneDev& sc, const FrameParams& fp, V3 pos, V3 normal, int px, int py, uint32_t depth, uint32_t i,
-                        uint32_t aoN, uint32_t& fetches) {
-    V3 rs, rd; uint32_t maxSteps;
+VRT_HD void wave_anyhit_ray(const SceneDev& sc, const FrameParams& fp, V3 pos, V3 normal, int px, int py, uint32_t depth, uint32_t i,
+                            uint32_t aoN, V3& rs, V3& rd, uint32_t& maxSteps) {
     if (i < aoN) {
         const V3 dir = normal + random_dir(sc, fp.cam.frame, px, py, i + depth * aoN);
         rs = pos + dir * 0.01f; rd = dir; maxSteps = 64;
@@ -81,6 +79,12 @@ VRT_HD bool wave_anyhit(const SceneDev& sc, const FrameParams& fp, V3 pos, V3 no
         rd = mk3(fp.lightDir[0], fp.lightDir[1], fp.lightDir[2]);
         rs = pos + normal * 0.01f; maxSteps = MAX_RAY_STEPS;
     }
+}
+template <int TRAVERSAL>
+VRT_HD bool wave_anyhit(const SceneDev& sc, const FrameParams& fp, V3 pos, V3 normal, int px, int py, uint32_t depth, uint32_t i,
+                        uint32_t aoN, uint32_t& fetches) {
+    V3 rs, rd; uint32_t maxSteps;
+    wave_anyhit_ray(sc, fp, pos, normal, px, py, depth, i, aoN, rs, rd, maxSteps);
     const TraceRes r = trace_ray<TRAVERSAL>(sc, rs, rd, maxSteps);
     fetches = r.fetches;
     return r.material != 0;

@@ -15,7 +15,7 @@ LIB_PATH = os.environ.get("VRT_LIB", os.path.join(HERE, "libvrt.so"))   # VRT_LI
 
 PASS_PRIMARY, PASS_SHADOW, PASS_AO, PASS_REFLECT, PASS_SHADE, PASS_ALL = 1, 2, 4, 8, 16, 31
 OUT_GBUFFER, OUT_INSTRUMENT = 1, 2
-TRAVERSAL_DEFAULT, TRAVERSAL_DENSE_U8, TRAVERSAL_BRICK, TRAVERSAL_FINE = 0, 1, 2, 3
+TRAVERSAL_DEFAULT, TRAVERSAL_DENSE_U8, TRAVERSAL_BRICK, TRAVERSAL_FINE, TRAVERSAL_LINEAR = 0, 1, 2, 3, 4
 PIPELINE_DEFAULT, PIPELINE_MEGAKERNEL, PIPELINE_WAVEFRONT = 0, 1, 2
 DENOISE_AS_EXECUTED, DENOISE_AS_INTENDED = 0, 1
 E_LFS_POINTER, E_NO_INSTANCE, E_PARSE, E_IO, E_CUDA, E_NO_DEVICE = -2, -3, -4, -5, -6, -7
