@@ -368,9 +368,17 @@ def run_vrt(args):
             line["cpu_baseline"] = cpu_baseline(cfg, args.config, args.whd, size, args.cpu_seconds)
         print(json.dumps(line), flush=True)
     barrier()
-    scene.destroy(); ctx.close()
+    # tensors that were used on the context's stream must be returned to torch's allocator while that stream still exists
+    gathered = assembled = host_frame = None
+    del step
+    import gc
+    gc.collect()
+    torch.cuda.synchronize()
+    torch.cuda.empty_cache()
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
+    scene.destroy(); ctx.close()
 
 
 if __name__ == "__main__":

@@ -134,6 +134,10 @@ const char* vrt_version(void);
 int vrt_device_info(vrt_context*, int* sm_count, size_t* l2_bytes, size_t* hbm_bytes);
 int vrt_context_sync(vrt_context*);                             /* wait for everything queued on the context stream */
 void* vrt_context_stream(vrt_context*);                         /* cudaStream_t the context launches on */
+/* device scratch owned by the caller (outputs of vrt_denoise / vrt_assemble, gather staging) */
+int vrt_buffer_alloc(vrt_context*, size_t bytes, void** d_ptr);
+void vrt_buffer_free(vrt_context*, void* d_ptr);
+int vrt_buffer_download(vrt_context*, const void* d_src, void* host_dst, size_t bytes);   /* on the context stream; syncs */
 
 /* ---- scene ---- */
 int vrt_scene_load_vox(vrt_context*, const char* vox_path, vrt_scene** out);

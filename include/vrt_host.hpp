@@ -1,0 +1,231 @@
+// vrt_host.hpp — C++ host side above the C ABI (include/vrt.h), header-only. It mirrors the reference's own operator
+// surface for this path so that a caller of the reference's classes finds the same names, argument meaning and error
+// behaviour (exceptions: the reference throws std::runtime_error from VoxelScene and lets vk::resultCheck throw;
+// /root/reference/source/voxels/resource/voxel_scene.cpp:42,46,50):
+//
+//   vrt::VoxelRenderSettings  == VoxelRenderSettings           source/voxels/voxel_render_settings.hpp:15-59
+//   vrt::VoxelScene           == VoxelScene                    source/voxels/resource/voxel_scene.hpp:18-34
+//   vrt::CameraController     == CameraController              source/voxels/resource/camera_controller.cpp:15-28
+//   vrt::GeometryStage        == GeometryStage                 source/voxels/stages/geometry_stage.hpp:30-56
+//   vrt::GeometryBuffer       == GeometryBuffer                source/voxels/stages/geometry_stage.hpp:19-27
+//   vrt::DenoiserStage        == DenoiserStage                 source/voxels/stages/denoiser_stage.hpp:21-47
+//   vrt::VoxelRenderer        == VoxelRenderer::recordCommands source/voxels/voxel_renderer.cpp:55-105 (geometry -> denoise)
+//
+// What differs, deliberately: there is no vk::CommandBuffer / flightFrame (the context's CUDA stream plays the role of
+// the command buffer; record() is asynchronous exactly like the reference's, results are valid after sync()), render
+// targets are device pointers instead of RenderImage, and FSR / blit / swapchain are out of scope.
+#pragma once
+#include <cmath>
+#include <cstring>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+#include "vrt.h"
+
+namespace vrt {
+
+inline void check(int rc, const char* what) {
+    if (rc != VRT_OK) throw std::runtime_error(std::string(what) + ": " + vrt_last_error() + " (vrt_status " + std::to_string(rc) + ")");
+}
+
+// The reference's Engine owns the device and queue; here: one CUDA device + stream (+ the tile shard of this process).
+class Engine {
+public:
+    explicit Engine(int device = 0, int rank = 0, int world = 1) {
+        check(vrt_context_create(device, &_ctx), "vrt_context_create");   // throws when there is no GPU: no CPU fallback
+        if (world > 1) check(vrt_context_set_shard(_ctx, rank, world), "vrt_context_set_shard");
+    }
+    ~Engine() { vrt_context_destroy(_ctx); }
+    Engine(const Engine&) = delete;
+    Engine& operator=(const Engine&) = delete;
+    vrt_context* handle() const { return _ctx; }
+    void waitIdle() const { check(vrt_context_sync(_ctx), "vrt_context_sync"); }   // == device.waitIdle()
+    void* stream() const { return vrt_context_stream(_ctx); }
+private:
+    vrt_context* _ctx = nullptr;
+};
+
+// voxel_render_settings.hpp:21-59 (FSR settings omitted: out of scope; render resolution == target resolution)
+struct DenoiserSettings { bool enable = true; int iterations = 2; float phiColor0 = 20.4f, phiNormal0 = 1E-2f, phiPos0 = 1E-1f, stepWidth = 2.0f; };
+struct AmbientOcclusionSettings { int numSamples = 4; float intensity = 1.0f; };
+struct LightSettings {
+    float direction[3] = {0.57735026f, 0.57735026f, 0.57735026f};   // overwritten by the constructor below (glm::normalize(vec3(1)))
+    float color[4] = {1.0f, 1.0f, 1.0f, 1.0f};
+    float intensity = 1.0f;
+};
+class VoxelRenderSettings {
+public:
+    uint32_t targetResolution[2] = {1920, 1080};
+    DenoiserSettings denoiserSettings = {};
+    AmbientOcclusionSettings occlusionSettings = {};
+    LightSettings lightSettings = {};
+    std::string voxPath = "../resource/treehouse.vox";
+    std::string skyboxPath = "../resource/rustig_koppie.hdr";
+    // additions of this build (the reference behaves as VRT_PASS_ALL / G-buffer on / AS_EXECUTED)
+    uint32_t passMask = VRT_PASS_ALL, outMask = VRT_OUT_GBUFFER, traversal = VRT_TRAVERSAL_DEFAULT, pipeline = VRT_PIPELINE_DEFAULT;
+    int denoiseMode = VRT_DENOISE_AS_EXECUTED;
+
+    VoxelRenderSettings() {
+        vrt_render_settings d; vrt_default_settings(&d);
+        std::memcpy(lightSettings.direction, d.light.direction, sizeof(lightSettings.direction));
+    }
+    const uint32_t* renderResolution() const { return targetResolution; }
+    vrt_render_settings lower(bool withDenoiser) const {
+        vrt_render_settings s; vrt_default_settings(&s);
+        s.pass_mask = passMask; s.out_mask = outMask; s.traversal = traversal; s.pipeline = pipeline;
+        s.vol.aoSamples = (uint32_t)occlusionSettings.numSamples; s.vol.ambientIntensity = occlusionSettings.intensity;   // geometry_stage.cpp:135-137
+        std::memcpy(s.light.direction, lightSettings.direction, sizeof(s.light.direction));                               // geometry_stage.cpp:138-142
+        s.light.intensity = lightSettings.intensity; std::memcpy(s.light.color, lightSettings.color, sizeof(s.light.color));
+        s.denoise.enable = withDenoiser && denoiserSettings.enable; s.denoise.iterations = denoiserSettings.iterations;
+        s.denoise.phiColor0 = denoiserSettings.phiColor0; s.denoise.phiNormal0 = denoiserSettings.phiNormal0;
+        s.denoise.phiPos0 = denoiserSettings.phiPos0; s.denoise.stepWidth = denoiserSettings.stepWidth; s.denoise.mode = denoiseMode;
+        return s;
+    }
+};
+
+// A complete voxel scene: dense volume + palette (+ noise + skybox) resident on the GPU. voxel_scene.hpp:18-34.
+class VoxelScene {
+public:
+    uint32_t width = 0, height = 0, depth = 0;
+    // VoxelScene(engine, filename, skyboxFilename): the skybox/noise decoders (stb) are outside the path; pass pixels.
+    VoxelScene(const std::shared_ptr<Engine>& engine, const std::string& filename) : _engine(engine) {
+        check(vrt_scene_load_vox(engine->handle(), filename.c_str(), &_scene), "VoxelScene");   // messages of voxel_scene.cpp:42,46,50
+        bounds();
+    }
+    VoxelScene(const std::shared_ptr<Engine>& engine, const uint8_t* dense, uint32_t w, uint32_t h, uint32_t d, const vrt_material palette[256])
+        : _engine(engine) {
+        check(vrt_scene_from_dense(engine->handle(), dense, w, h, d, palette, &_scene), "VoxelScene(dense)");
+        bounds();
+    }
+    VoxelScene(const std::shared_ptr<Engine>& engine, int generator, uint64_t seed, uint32_t w, uint32_t h, uint32_t d) : _engine(engine) {
+        check(vrt_scene_generate(engine->handle(), generator, seed, w, h, d, &_scene), "VoxelScene(generate)");
+        bounds();
+    }
+    ~VoxelScene() { destroy(); }
+    VoxelScene(const VoxelScene&) = delete;
+    VoxelScene& operator=(const VoxelScene&) = delete;
+    void destroy() { if (_scene) { vrt_scene_destroy(_scene); _scene = nullptr; } }   // == AResource::destroy()
+    void setNoise(const uint8_t* rgba8, uint32_t w, uint32_t h) { check(vrt_scene_set_noise(_scene, rgba8, w, h), "setNoise"); }
+    void setSkybox(const float* rgba32f, uint32_t w, uint32_t h) { check(vrt_scene_set_skybox(_scene, rgba32f, w, h), "setSkybox"); }
+    vrt_scene* handle() const { return _scene; }
+    const std::shared_ptr<Engine>& engine() const { return _engine; }
+private:
+    void bounds() { uint32_t b[3]; check(vrt_scene_bounds(_scene, b), "vrt_scene_bounds"); width = b[0]; height = b[1]; depth = b[2]; }
+    std::shared_ptr<Engine> _engine;
+    vrt_scene* _scene = nullptr;
+};
+
+// camera_controller.cpp:15-28 + the push-constant fill of voxel_renderer.cpp:72-83
+class CameraController {
+public:
+    float position[3] = {8.0f, 8.0f, -50.0f};
+    float yaw = 90.0f, pitch = 0.0f, focalLength = 1.920982f;    // voxel_renderer.cpp:20 (fov 55 degrees)
+    float direction[3], right[3], up[3];
+    CameraController() { updateDirectionVectors(); }
+    void updateDirectionVectors() { vrt_camera_vectors(yaw, pitch, focalLength, direction, right, up); }
+    vrt_camera push(const VoxelScene& scene, const uint32_t res[2], uint32_t frame, float jx = 0.0f, float jy = 0.0f) const {
+        vrt_camera c; std::memset(&c, 0, sizeof(c));
+        for (int i = 0; i < 3; i++) { c.camPos[i] = position[i]; c.camDir[i] = direction[i]; c.camRight[i] = right[i]; c.camUp[i] = up[i]; }
+        c.camPos[3] = 1.0f;
+        c.volumeBounds[0] = scene.width; c.volumeBounds[1] = scene.height; c.volumeBounds[2] = scene.depth;
+        c.frame = frame; c.screenSize[0] = (int32_t)res[0]; c.screenSize[1] = (int32_t)res[1];
+        c.cameraJitter[0] = jx; c.cameraJitter[1] = jy;
+        return c;
+    }
+};
+
+// One render target on the device (RenderImage stand-in).
+struct RenderImage { void* devicePtr = nullptr; size_t bytes = 0; int plane = -1; };
+
+struct GeometryBuffer { RenderImage color, depth, motion, mask, normal, position; };   // geometry_stage.hpp:19-27
+
+class GeometryStage {
+public:
+    GeometryStage(const std::shared_ptr<Engine>& engine, const std::shared_ptr<VoxelRenderSettings>& settings, const std::shared_ptr<VoxelScene>& scene)
+        : _engine(engine), _settings(settings), _scene(scene) {}
+    ~GeometryStage() { vrt_frame_release(_frame); }
+    GeometryStage(const GeometryStage&) = delete;
+    GeometryStage& operator=(const GeometryStage&) = delete;
+    // Records the pass on the engine's stream with the LIVE settings (geometry_stage.cpp:135-141) and the pushed camera block
+    // (the reference's caller pushes ScreenQuadPush before record: voxel_renderer.cpp:72-83). Asynchronous.
+    GeometryBuffer record(const vrt_camera& push) {
+        const vrt_render_settings s = _settings->lower(false);
+        check(vrt_render(_engine->handle(), _scene->handle(), &push, &s, &_frame), "GeometryStage::record");
+        GeometryBuffer g;
+        g.color = image(VRT_PLANE_COLOR_RGBA8);
+        if (s.out_mask & VRT_OUT_GBUFFER) {
+            g.depth = image(VRT_PLANE_DEPTH_R32F); g.motion = image(VRT_PLANE_MOTION_RG32F); g.mask = image(VRT_PLANE_MASK_R8);
+            g.normal = image(VRT_PLANE_NORMAL_RGBA8S); g.position = image(VRT_PLANE_POSITION_RGBA32F);
+        }
+        return g;
+    }
+    RenderImage image(int plane) const {
+        RenderImage r; r.plane = plane;
+        check(vrt_frame_plane(_frame, plane, &r.devicePtr, &r.bytes), "vrt_frame_plane");
+        return r;
+    }
+    void download(const RenderImage& img, void* host) const { check(vrt_frame_download(_frame, img.plane, host, img.bytes), "vrt_frame_download"); }
+    vrt_frame_stats stats() const { vrt_frame_stats s; check(vrt_frame_stats_get(_frame, &s), "vrt_frame_stats_get"); return s; }
+    vrt_frame* frame() const { return _frame; }
+private:
+    std::shared_ptr<Engine> _engine;
+    std::shared_ptr<VoxelRenderSettings> _settings;
+    std::shared_ptr<VoxelScene> _scene;
+    vrt_frame* _frame = nullptr;
+};
+
+class DenoiserStage {
+public:
+    DenoiserStage(const std::shared_ptr<Engine>& engine, const std::shared_ptr<VoxelRenderSettings>& settings) : _engine(engine), _settings(settings) {}
+    ~DenoiserStage() { vrt_buffer_free(_engine->handle(), _out.devicePtr); }
+    DenoiserStage(const DenoiserStage&) = delete;
+    DenoiserStage& operator=(const DenoiserStage&) = delete;
+    // denoiser_stage.hpp:45-46. The output target is owned by the stage (re-created when the resolution changes, like the
+    // reference's RENDER_RESIZE handling); ping-pong scratch lives in the library. Runs with the LIVE settings.
+    const RenderImage& record(const RenderImage& colorInput, const RenderImage& normalInput, const RenderImage& posInput, int w, int h) {
+        const size_t bytes = (size_t)w * (size_t)h * 4u;
+        if (_out.bytes != bytes) {
+            vrt_buffer_free(_engine->handle(), _out.devicePtr); _out = RenderImage();
+            check(vrt_buffer_alloc(_engine->handle(), bytes, &_out.devicePtr), "DenoiserStage target");
+            _out.bytes = bytes; _out.plane = VRT_PLANE_DENOISED_RGBA8;
+        }
+        const vrt_render_settings s = _settings->lower(true);
+        check(vrt_denoise(_engine->handle(), colorInput.devicePtr, normalInput.devicePtr, posInput.devicePtr, w, h, &s.denoise, _out.devicePtr),
+              "DenoiserStage::record");
+        return _out;
+    }
+    void download(void* host) const { check(vrt_buffer_download(_engine->handle(), _out.devicePtr, host, _out.bytes), "vrt_buffer_download"); }
+private:
+    std::shared_ptr<Engine> _engine;
+    std::shared_ptr<VoxelRenderSettings> _settings;
+    RenderImage _out;
+};
+
+// VoxelRenderer::recordCommands (voxel_renderer.cpp:55-105) without the upscaler and blit: push constants -> geometry
+// stage -> denoiser stage (when enabled, voxel_renderer.cpp:87-92) -> the image the blit would present.
+class VoxelRenderer {
+public:
+    CameraController camera;
+    VoxelRenderer(const std::shared_ptr<Engine>& engine, const std::shared_ptr<VoxelRenderSettings>& settings, const std::shared_ptr<VoxelScene>& scene)
+        : _engine(engine), _settings(settings), _scene(scene), _geometry(engine, settings, scene), _denoiser(engine, settings) {}
+    // one frame; returns the final colour image (denoised when the denoiser is enabled)
+    RenderImage recordCommands(uint32_t frameCount, float jitterX = 0.0f, float jitterY = 0.0f) {
+        const uint32_t* res = _settings->renderResolution();
+        const vrt_camera push = camera.push(*_scene, res, frameCount, jitterX, jitterY);
+        const GeometryBuffer g = _geometry.record(push);
+        if (_settings->denoiserSettings.enable && (_settings->outMask & VRT_OUT_GBUFFER))
+            return _denoiser.record(g.color, g.normal, g.position, (int)res[0], (int)res[1]);
+        return g.color;
+    }
+    GeometryStage& geometryStage() { return _geometry; }
+    DenoiserStage& denoiserStage() { return _denoiser; }
+private:
+    std::shared_ptr<Engine> _engine;
+    std::shared_ptr<VoxelRenderSettings> _settings;
+    std::shared_ptr<VoxelScene> _scene;
+    GeometryStage _geometry;
+    DenoiserStage _denoiser;
+};
+
+}  // namespace vrt

@@ -219,3 +219,41 @@ extern "C" int hh_render_wave(void* scene, const vrt_camera* cam, const vrt_rend
     else render_wave<VRT_TRAVERSAL_BRICK>(s->dev, fp, pl, row_begin, row_end, row_step);
     return 0;
 }
+
+// ---- tile-sharded rendering (N>1 ranks): this rank's interleaved tiles into a compact tile-major colour buffer, exactly
+// the layout vrt_render produces under vrt_context_set_shard (plane_index), and the assembly of vrt_assemble ----
+extern "C" int hh_render_shard(void* scene, const vrt_camera* cam, const vrt_render_settings* st, int traversal, int rank, int world,
+                               uint8_t* color_tiles, size_t shard_pixels) {
+    HScene* s = (HScene*)scene;
+    FrameParams fp; memset(&fp, 0, sizeof(fp));
+    fp.cam = *cam; fp.pass_mask = st->pass_mask; fp.out_mask = st->out_mask; fp.traversal = traversal;
+    fp.aoSamples = st->vol.aoSamples; fp.ambientIntensity = st->vol.ambientIntensity;
+    for (int k = 0; k < 3; k++) { fp.lightDir[k] = st->light.direction[k]; fp.lightColor[k] = st->light.color[k]; }
+    fp.lightIntensity = st->light.intensity; fp.rank = rank; fp.world = world;
+    const int W = cam->screenSize[0], H = cam->screenSize[1];
+    fp.tilesX = (W + VRT_TILE - 1) / VRT_TILE; fp.tilesY = (H + VRT_TILE - 1) / VRT_TILE;
+    const int tiles = fp.tilesX * fp.tilesY;
+    fp.localTiles = tiles > rank ? (tiles - rank + world - 1) / world : 0;
+    if ((size_t)((tiles + world - 1) / world) * VRT_TILE * VRT_TILE != shard_pixels) return -1;
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int j = 0; j < fp.localTiles; j++) {
+        const int t = j * world + rank, tx = t % fp.tilesX, ty = t / fp.tilesX;
+        for (int ly = 0; ly < VRT_TILE; ly++)
+            for (int lx = 0; lx < VRT_TILE; lx++) {
+                const int px = tx * VRT_TILE + lx, py = ty * VRT_TILE + ly;
+                if (px >= W || py >= H) continue;
+                PixelOut o; memset(&o, 0, sizeof(o));
+                if (traversal == VRT_TRAVERSAL_LINEAR) render_pixel<VRT_TRAVERSAL_LINEAR>(s->dev, fp, px, py, o);
+                else render_pixel<VRT_TRAVERSAL_FINE>(s->dev, fp, px, py, o);
+                uint8_t* q = color_tiles + 4 * plane_index(fp, px, py);
+                q[0] = to_unorm8(o.color.x); q[1] = to_unorm8(o.color.y); q[2] = to_unorm8(o.color.z); q[3] = 0;
+            }
+    }
+    return 0;
+}
+extern "C" void hh_assemble(const uint8_t* gathered, int world, int W, int H, size_t shard_pixels, uint8_t* out) {
+    const int tilesX = (W + VRT_TILE - 1) / VRT_TILE;
+    for (int py = 0; py < H; py++)
+        for (int px = 0; px < W; px++)
+            memcpy(out + 4 * ((size_t)py * W + px), gathered + 4 * gathered_index(px, py, tilesX, world, shard_pixels), 4);
+}

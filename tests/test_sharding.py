@@ -1,0 +1,70 @@
+"""N>1 path on CPU (gloo, world size 2 and 3): every rank renders its interleaved tile shard with the product's own
+per-pixel code and layout functions (host-compiled: tests/host_harness), the colour shards are gathered on rank 0 with
+torch.distributed exactly as bench.py gathers them over NCCL, assembled, and must be byte-identical to the 1-rank frame."""
+import ctypes as C
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from vrtlib import O, assets, harness, harness_render, look_at_camera, random_volume, random_palette, to_vrt_camera, to_vrt_settings, TRAV_FINE
+
+TILE = 32
+
+
+def _inputs():
+    rng = np.random.default_rng(11)
+    whd = (40, 36, 44)
+    vol, pal = random_volume(rng, whd, 0.03), random_palette(rng, metallic_every=4)
+    cam = look_at_camera(whd, (200, 120), (-15, 50, -20), (20, 18, 22), frame=5)   # ragged: 200x120 is not a multiple of 32
+    return vol, pal, cam, O.make_settings(ao=2)
+
+
+def _worker(rank, world, port, outdir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        vol, pal, cam, st = _inputs()
+        noise, sky = assets.noise_standin(), assets.sky_standin(64, 32)
+        sc, keep = O.make_scene(vol, pal, noise, sky)
+        h = harness()
+        hs = h.hh_scene_create(C.c_void_p(sc.volume), sc.w, sc.h, sc.d, C.c_void_p(sc.palette), C.c_void_p(sc.noise), C.c_void_p(sc.sky), sc.skyW, sc.skyH)
+        W, H = cam.screenSize[0], cam.screenSize[1]
+        tiles = ((W + TILE - 1) // TILE) * ((H + TILE - 1) // TILE)
+        shard_px = ((tiles + world - 1) // world) * TILE * TILE
+        shard = np.zeros(shard_px * 4, np.uint8)
+        vs, vc = to_vrt_settings(st), to_vrt_camera(cam)
+        h.hh_render_shard.restype = C.c_int
+        rc = h.hh_render_shard(C.c_void_p(hs), C.byref(vc), C.byref(vs), TRAV_FINE, rank, world, shard.ctypes.data_as(C.c_void_p), C.c_size_t(shard_px))
+        assert rc == 0
+        t = torch.from_numpy(shard)
+        if rank == 0:
+            parts = [torch.empty_like(t) for _ in range(world)]
+            dist.gather(t, parts, dst=0)
+            gathered = torch.cat(parts).numpy()
+            out = np.zeros((H, W, 4), np.uint8)
+            h.hh_assemble(gathered.ctypes.data_as(C.c_void_p), world, W, H, C.c_size_t(shard_px), out.ctypes.data_as(C.c_void_p))
+            np.save(os.path.join(outdir, "frame.npy"), out)
+        else:
+            dist.gather(t, None, dst=0)
+        h.hh_scene_destroy(C.c_void_p(hs))
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_gloo_sharded_frame_is_byte_identical(world, tmp_path):
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]
+    mp.spawn(_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    got = np.load(tmp_path / "frame.npy")
+    vol, pal, cam, st = _inputs()
+    sc, keep = O.make_scene(vol, pal, assets.noise_standin(), assets.sky_standin(64, 32))
+    want = harness_render(sc, cam, st, traversal=TRAV_FINE)["color"]
+    assert np.array_equal(got, want)
+    assert np.array_equal(want, O.render(sc, cam, st)["color"]) or np.abs(want.astype(int) - O.render(sc, cam, st)["color"].astype(int)).max() <= 1

@@ -98,6 +98,26 @@ extern "C" int vrt_context_sync(vrt_context* c) {
 extern "C" void* vrt_context_stream(vrt_context* c) { return c ? (void*)c->stream : nullptr; }
 
 // ------------------------------------------------------------------------------------------------ scene
+extern "C" int vrt_buffer_alloc(vrt_context* c, size_t bytes, void** d_ptr) {
+    if (!c || !d_ptr || bytes == 0) return fail(VRT_E_INVALID, "bad argument");
+    CU(cudaSetDevice(c->device));
+    const cudaError_t e = cudaMalloc(d_ptr, bytes);
+    if (e != cudaSuccess) return fail(e == cudaErrorMemoryAllocation ? VRT_E_OOM : VRT_E_CUDA, cudaGetErrorString(e));
+    return VRT_OK;
+}
+extern "C" void vrt_buffer_free(vrt_context* c, void* d_ptr) {
+    if (!c || !d_ptr) return;
+    cudaSetDevice(c->device);
+    cudaFree(d_ptr);
+}
+extern "C" int vrt_buffer_download(vrt_context* c, const void* d_src, void* host_dst, size_t bytes) {
+    if (!c || !d_src || !host_dst) return fail(VRT_E_INVALID, "null argument");
+    CU(cudaSetDevice(c->device));
+    CU(cudaMemcpyAsync(host_dst, d_src, bytes, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return VRT_OK;
+}
+
 extern "C" void vrt_scene_destroy(vrt_scene* s) {
     if (!s) return;
     cudaSetDevice(s->ctx->device);

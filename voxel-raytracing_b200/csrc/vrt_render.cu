@@ -74,9 +74,7 @@ __global__ void detile_kernel(const uint8_t* __restrict__ src, uint8_t* __restri
                               size_t rankStridePixels, int bpp) {
     const int px = blockIdx.x * blockDim.x + threadIdx.x, py = blockIdx.y * blockDim.y + threadIdx.y;
     if (px >= W || py >= H) return;
-    const int t = (py / VRT_TILE) * tilesX + (px / VRT_TILE);
-    const int rank = t % world, j = t / world;
-    const size_t sp = (size_t)rank * rankStridePixels + (size_t)j * (VRT_TILE * VRT_TILE) + (py % VRT_TILE) * VRT_TILE + (px % VRT_TILE);
+    const size_t sp = gathered_index(px, py, tilesX, world, rankStridePixels);
     const size_t dp = (size_t)py * W + px;
     if (bpp == 4) reinterpret_cast<uint32_t*>(dst)[dp] = reinterpret_cast<const uint32_t*>(src)[sp];
     else if (bpp == 16) reinterpret_cast<uint4*>(dst)[dp] = reinterpret_cast<const uint4*>(src)[sp];

@@ -26,6 +26,13 @@ VRT_HD size_t plane_index(const FrameParams& fp, int px, int py) {
     return (size_t)(t / fp.world) * (VRT_TILE * VRT_TILE) + (py % VRT_TILE) * VRT_TILE + (px % VRT_TILE);
 }
 
+// where pixel (px,py) of the assembled frame lies in the gathered buffer (world shard buffers back to back, rank-major,
+// each rankStridePixels long): the inverse of plane_index over all ranks (vrt_assemble / detile_kernel)
+VRT_HD size_t gathered_index(int px, int py, int tilesX, int world, size_t rankStridePixels) {
+    const int t = (py / VRT_TILE) * tilesX + (px / VRT_TILE);
+    return (size_t)(t % world) * rankStridePixels + (size_t)(t / world) * (VRT_TILE * VRT_TILE) + (py % VRT_TILE) * VRT_TILE + (px % VRT_TILE);
+}
+
 enum { WAVE_PIXEL_FINAL = 0, WAVE_PIXEL_SHADE = 1, WAVE_PIXEL_SHADE_AND_BOUNCE = 2 };
 
 // main :309-345 up to the first colorMainRay decision. Fills the G-buffer fields of `o`; `o.color` only when the
