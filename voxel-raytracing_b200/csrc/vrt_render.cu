@@ -3,7 +3,7 @@
 // covers an 8x4 pixel patch (ray coherence: at 4K adjacent primary rays walk the same bricks), a 128-thread
 // block covers 16x8 pixels, 8 blocks cover one 32x32 shard tile.
 #include <cuda_runtime.h>
-#include "vrt_pixel.cuh"
+#include "vrt_wave.cuh"
 #include "vrt_launch.h"
 
 namespace vrt {
