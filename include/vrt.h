@@ -74,7 +74,7 @@ enum {
     VRT_OUT_INSTRUMENT = 2,   /* hit voxel + step count, palette index, float colour, per-pixel ray / fetch counts */
 };
 /* traversal back-ends (all bit-identical; for measurement). 0 = library default. */
-enum { VRT_TRAVERSAL_DEFAULT = 0, VRT_TRAVERSAL_DENSE_U8 = 1, VRT_TRAVERSAL_BRICK = 2, VRT_TRAVERSAL_FINE = 3, VRT_TRAVERSAL_LINEAR = 4 };
+enum { VRT_TRAVERSAL_DEFAULT = 0, VRT_TRAVERSAL_DENSE_U8 = 1, VRT_TRAVERSAL_BRICK = 2, VRT_TRAVERSAL_FINE = 3, VRT_TRAVERSAL_LINEAR = 4, VRT_TRAVERSAL_OCTANT = 5 };
 
 /* how the pass is scheduled on the GPU (all bit-identical; for measurement). 0 = library default (wavefront).
  *   MEGAKERNEL: one thread runs a pixel's whole ray tree (the shader's own shape).
@@ -156,6 +156,8 @@ int vrt_scene_accel_info(const vrt_scene*, size_t* dense_bytes, size_t* brick_ma
 int vrt_scene_download_accel(const vrt_scene*, uint64_t* bmask_dst, uint8_t* bdist_dst);
 /* per-voxel safe-step field (1 B per voxel, 4x4x4-bricked: 64 B per brick, (x&3) + (y&3)*4 + (z&3)*16 inside) */
 int vrt_scene_download_fdist(const vrt_scene*, uint8_t* dst, size_t bytes);
+/* directional safe-step field of one direction octant (0..7), aproned linear: (w+2)*(h+2)*(d+2) bytes; built on first use */
+int vrt_scene_download_odist(const vrt_scene*, int octant, uint8_t* dst, size_t bytes);
 void vrt_scene_destroy(vrt_scene*);
 /* Host-only .vox decode (no GPU involved): the dense volume + palette vrt_scene_load_vox_memory would upload.
  * *volume_out is malloc'ed (x + y*w + z*w*h); free it with vrt_host_free. */

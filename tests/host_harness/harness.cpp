@@ -71,15 +71,43 @@ static void build_fdist(const uint8_t* vol, int W, int H, int D, const std::vect
         const uint32_t d = bdist[b];
         uint32_t v = f;
         if (f != 0 && d != 0) v = std::max(f, (d - 1u) * 4u + 1u);
-        fdist[b * 64 + ((x & 3) | ((y & 3) << 2) | ((z & 3) << 4))] = (uint8_t)std::min(v, 254u);
-        ldist[(size_t)(x + 1) + (size_t)(y + 1) * (W + 2) + (size_t)(z + 1) * (W + 2) * (H + 2)] = (uint8_t)std::min(v, 254u);
+        fdist[b * 64 + ((x & 3) | ((y & 3) << 2) | ((z & 3) << 4))] = (uint8_t)std::min(v, VRT_SAFE_MAX);
+        ldist[(size_t)(x + 1) + (size_t)(y + 1) * (W + 2) + (size_t)(z + 1) * (W + 2) * (H + 2)] = (uint8_t)std::min(v, VRT_SAFE_MAX);
+    }
+}
+
+// CPU restatement of the directional safe-step fields (csrc/vrt_octant.cu): exact largest empty cube anchored at v towards
+// the octant (7-neighbour dynamic programme), rounded down to a level of VRT_OCT_LEVEL_LIST
+static void build_odist(const uint8_t* vol, int W, int H, int D, std::vector<uint8_t> odist[8]) {
+    static const int lv[VRT_OCT_NLEVELS] = VRT_OCT_LEVEL_LIST;
+    const size_t n = (size_t)W * H * D;
+    std::vector<int> e(n);
+    auto at = [&](int x, int y, int z) -> int { return (x < 0 || y < 0 || z < 0 || x >= W || y >= H || z >= D) ? 0 : e[(size_t)x + (size_t)y * W + (size_t)z * W * H]; };
+    for (int o = 0; o < 8; o++) {
+        const int sx = (o & 1) ? -1 : 1, sy = (o & 2) ? -1 : 1, sz = (o & 4) ? -1 : 1;
+        odist[o].assign((size_t)(W + 2) * (H + 2) * (D + 2), (uint8_t)VRT_LIN_OOB);
+        for (int kz = 0; kz < D; kz++) for (int ky = 0; ky < H; ky++) for (int kx = 0; kx < W; kx++) {
+            const int x = sx > 0 ? W - 1 - kx : kx, y = sy > 0 ? H - 1 - ky : ky, z = sz > 0 ? D - 1 - kz : kz;   // far end of the octant first
+            int v = 0;
+            if (vol[(size_t)x + (size_t)y * W + (size_t)z * W * H] == 0) {
+                int m = at(x + sx, y, z);
+                m = std::min(m, at(x, y + sy, z)); m = std::min(m, at(x, y, z + sz));
+                m = std::min(m, at(x + sx, y + sy, z)); m = std::min(m, at(x + sx, y, z + sz)); m = std::min(m, at(x, y + sy, z + sz));
+                m = std::min(m, at(x + sx, y + sy, z + sz));
+                v = std::min(1 + m, (int)VRT_SAFE_MAX);
+            }
+            e[(size_t)x + (size_t)y * W + (size_t)z * W * H] = v;
+            int q = 0;
+            for (int l = 0; l < VRT_OCT_NLEVELS; l++) if (lv[l] <= v) q = lv[l];
+            odist[o][(size_t)(x + 1) + (size_t)(y + 1) * (W + 2) + (size_t)(z + 1) * (W + 2) * (H + 2)] = (uint8_t)q;
+        }
     }
 }
 
 struct HScene {
     SceneDev dev;
     std::vector<unsigned long long> bmask;
-    std::vector<uint8_t> bdist, fdist, ldist;
+    std::vector<uint8_t> bdist, fdist, ldist, odist[8];
 };
 
 extern "C" void* hh_scene_create(const uint8_t* vol, uint32_t W, uint32_t H, uint32_t D, const float* palette,
@@ -90,6 +118,8 @@ extern "C" void* hh_scene_create(const uint8_t* vol, uint32_t W, uint32_t H, uin
     build_bricks(vol, W, H, D, s->bmask, s->bdist, s->dev.Bx, s->dev.By, s->dev.Bz);
     build_fdist(vol, (int)W, (int)H, (int)D, s->bdist, s->dev.Bx, s->dev.By, s->dev.Bz, s->fdist, s->ldist);
     s->dev.bmask = s->bmask.data(); s->dev.bdist = s->bdist.data(); s->dev.fdist = s->fdist.data(); s->dev.ldist = s->ldist.data();
+    build_odist(vol, (int)W, (int)H, (int)D, s->odist);
+    for (int o = 0; o < 8; o++) s->dev.odist[o] = s->odist[o].data();
     s->dev.palette = reinterpret_cast<const vrt_material*>(palette);
     s->dev.noise = noise; s->dev.sky = sky; s->dev.skyW = skyW; s->dev.skyH = skyH;
     return s;
@@ -116,6 +146,7 @@ extern "C" int hh_render(void* scene, const vrt_camera* cam, const vrt_render_se
             if (traversal == VRT_TRAVERSAL_DENSE_U8) render_pixel<VRT_TRAVERSAL_DENSE_U8>(s->dev, fp, px, py, o);
             else if (traversal == VRT_TRAVERSAL_FINE) render_pixel<VRT_TRAVERSAL_FINE>(s->dev, fp, px, py, o);
             else if (traversal == VRT_TRAVERSAL_LINEAR) render_pixel<VRT_TRAVERSAL_LINEAR>(s->dev, fp, px, py, o);
+            else if (traversal == VRT_TRAVERSAL_OCTANT) render_pixel<VRT_TRAVERSAL_OCTANT>(s->dev, fp, px, py, o);
             else render_pixel<VRT_TRAVERSAL_BRICK>(s->dev, fp, px, py, o);
             size_t p = (size_t)py * W + px;
             auto sat = [](int v) { return (int16_t)(v < -32768 ? -32768 : (v > 32767 ? 32767 : v)); };
@@ -216,6 +247,7 @@ extern "C" int hh_render_wave(void* scene, const vrt_camera* cam, const vrt_rend
     if (traversal == VRT_TRAVERSAL_DENSE_U8) render_wave<VRT_TRAVERSAL_DENSE_U8>(s->dev, fp, pl, row_begin, row_end, row_step);
     else if (traversal == VRT_TRAVERSAL_FINE) render_wave<VRT_TRAVERSAL_FINE>(s->dev, fp, pl, row_begin, row_end, row_step);
     else if (traversal == VRT_TRAVERSAL_LINEAR) render_wave<VRT_TRAVERSAL_LINEAR>(s->dev, fp, pl, row_begin, row_end, row_step);
+    else if (traversal == VRT_TRAVERSAL_OCTANT) render_wave<VRT_TRAVERSAL_OCTANT>(s->dev, fp, pl, row_begin, row_end, row_step);
     else render_wave<VRT_TRAVERSAL_BRICK>(s->dev, fp, pl, row_begin, row_end, row_step);
     return 0;
 }
@@ -244,6 +276,7 @@ extern "C" int hh_render_shard(void* scene, const vrt_camera* cam, const vrt_ren
                 if (px >= W || py >= H) continue;
                 PixelOut o; memset(&o, 0, sizeof(o));
                 if (traversal == VRT_TRAVERSAL_LINEAR) render_pixel<VRT_TRAVERSAL_LINEAR>(s->dev, fp, px, py, o);
+                else if (traversal == VRT_TRAVERSAL_OCTANT) render_pixel<VRT_TRAVERSAL_OCTANT>(s->dev, fp, px, py, o);
                 else render_pixel<VRT_TRAVERSAL_FINE>(s->dev, fp, px, py, o);
                 uint8_t* q = color_tiles + 4 * plane_index(fp, px, py);
                 q[0] = to_unorm8(o.color.x); q[1] = to_unorm8(o.color.y); q[2] = to_unorm8(o.color.z); q[3] = 0;
@@ -257,3 +290,5 @@ extern "C" void hh_assemble(const uint8_t* gathered, int world, int W, int H, si
         for (int px = 0; px < W; px++)
             memcpy(out + 4 * ((size_t)py * W + px), gathered + 4 * gathered_index(px, py, tilesX, world, shard_pixels), 4);
 }
+
+extern "C" void hh_scene_odist(void* p, int octant, uint8_t* out) { HScene* s = (HScene*)p; memcpy(out, s->odist[octant].data(), s->odist[octant].size()); }

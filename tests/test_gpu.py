@@ -144,9 +144,13 @@ def test_brick_levels_match_cpu_builder(gpu_ctx):
         h.hh_scene_bmask(C.c_void_p(hs), m2.ctypes.data_as(C.c_void_p)); h.hh_scene_bdist(C.c_void_p(hs), d2.ctypes.data_as(C.c_void_p))
         f2 = np.zeros(m.shape + (4, 4, 4), np.uint8)
         h.hh_scene_fdist(C.c_void_p(hs), f2.ctypes.data_as(C.c_void_p))
-        h.hh_scene_destroy(C.c_void_p(hs))
         assert np.array_equal(m, m2) and np.array_equal(d, d2)
         assert np.array_equal(gs.download_fdist(), f2)
+        for o in range(8):                                    # directional fields: bit-volume build == the CPU dynamic programme
+            o2 = np.zeros((whd[2] + 2, whd[1] + 2, whd[0] + 2), np.uint8)
+            h.hh_scene_odist(C.c_void_p(hs), o, o2.ctypes.data_as(C.c_void_p))
+            assert np.array_equal(gs.download_odist(o), o2), f"odist octant {o} differs for {whd}"
+        h.hh_scene_destroy(C.c_void_p(hs))
         gs.destroy()
 
 
@@ -158,7 +162,7 @@ def test_dense_and_brick_traversal_identical_at_4k(gpu_ctx):
     st = O.make_settings()
     a = gpu_render(gpu_ctx, gs, cam, st, TRAV_DENSE, pipeline=pyvrt.PIPELINE_MEGAKERNEL)
     for trav, pipe in ((TRAV_BRICK, pyvrt.PIPELINE_MEGAKERNEL), (TRAV_FINE, pyvrt.PIPELINE_MEGAKERNEL), (TRAV_FINE, pyvrt.PIPELINE_WAVEFRONT),
-                       (TRAV_DENSE, pyvrt.PIPELINE_WAVEFRONT)):
+                       (TRAV_DENSE, pyvrt.PIPELINE_WAVEFRONT), (4, pyvrt.PIPELINE_WAVEFRONT), (5, pyvrt.PIPELINE_WAVEFRONT), (5, pyvrt.PIPELINE_MEGAKERNEL)):
         b = gpu_render(gpu_ctx, gs, cam, st, trav, pipeline=pipe)
         for n, _, _ in O.PLANE_SPECS:
             ok, bad = bits_equal(a[n], b[n]); assert ok, (trav, pipe, n, bad)

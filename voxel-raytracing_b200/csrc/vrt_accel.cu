@@ -113,7 +113,7 @@ __global__ void fine_merge_kernel(const uint8_t* __restrict__ fine, const uint8_
     const uint32_t d = bdist[b];
     uint32_t n = f;
     if (f != 0 && d != 0) n = max(f, (d - 1u) * 4u + 1u);
-    n = min(n, 254u);
+    n = min(n, VRT_SAFE_MAX);
     fdist[b * 64u + ((x & 3u) | ((y & 3u) << 2) | ((z & 3u) << 4))] = (uint8_t)n;
     ldist[(size_t)(x + 1u) + (size_t)(y + 1u) * (W + 2u) + (size_t)(z + 1u) * (W + 2u) * (H + 2u)] = (uint8_t)n;
 }

@@ -29,6 +29,7 @@ struct vrt_scene {
     vrt_context* ctx = nullptr;
     uint32_t w = 0, h = 0, d = 0, Bx = 0, By = 0, Bz = 0;
     uint8_t* vol = nullptr; unsigned long long* bmask = nullptr; uint8_t* bdist = nullptr; uint8_t* fdist = nullptr; uint8_t* ldist = nullptr;
+    uint8_t* odist[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // built on first use (scene_ensure_octant)
     vrt_material* palette = nullptr; vrt_material hostPalette[256];
     uint8_t* noise = nullptr; float* sky = nullptr; uint32_t skyW = 0, skyH = 0;
     int accelLaunches = 0;
@@ -121,7 +122,7 @@ extern "C" int vrt_buffer_download(vrt_context* c, const void* d_src, void* host
 extern "C" void vrt_scene_destroy(vrt_scene* s) {
     if (!s) return;
     cudaSetDevice(s->ctx->device);
-    cudaFree(s->vol); cudaFree(s->bmask); cudaFree(s->bdist); cudaFree(s->fdist); cudaFree(s->ldist); cudaFree(s->palette); cudaFree(s->noise); cudaFree(s->sky);
+    cudaFree(s->vol); cudaFree(s->bmask); cudaFree(s->bdist); cudaFree(s->fdist); cudaFree(s->ldist); for (uint8_t* p : s->odist) cudaFree(p); cudaFree(s->palette); cudaFree(s->noise); cudaFree(s->sky);
     delete s;
 }
 
@@ -273,6 +274,34 @@ extern "C" int vrt_scene_download_fdist(const vrt_scene* s, uint8_t* dst, size_t
     return VRT_OK;
 }
 
+// Directional safe-step fields, built the first time a frame asks for VRT_TRAVERSAL_OCTANT (8 fields of one byte per voxel).
+static int scene_ensure_octant(vrt_scene* s) {
+    if (s->odist[0]) return VRT_OK;
+    vrt_context* c = s->ctx;
+    const size_t fieldBytes = (size_t)(s->w + 2) * (s->h + 2) * (s->d + 2);
+    uint32_t* scratch = nullptr;
+    cudaError_t e = cudaMalloc(&scratch, octant_scratch_bytes(s->w, s->h, s->d));
+    for (int o = 0; o < 8 && e == cudaSuccess; o++) e = cudaMalloc(&s->odist[o], fieldBytes);
+    if (e == cudaSuccess) e = launch_build_odist(s->vol, s->w, s->h, s->d, s->odist, scratch, c->stream, &s->accelLaunches);
+    const cudaError_t e2 = cudaStreamSynchronize(c->stream);
+    cudaFree(scratch);
+    if (e == cudaSuccess) e = e2;
+    if (e != cudaSuccess) {
+        for (uint8_t*& p : s->odist) { cudaFree(p); p = nullptr; }
+        return fail(e == cudaErrorMemoryAllocation ? VRT_E_OOM : VRT_E_CUDA, cudaGetErrorString(e));
+    }
+    return VRT_OK;
+}
+
+extern "C" int vrt_scene_download_odist(const vrt_scene* s, int octant, uint8_t* dst, size_t bytes) {
+    if (!s || !dst || octant < 0 || octant > 7 || bytes != (size_t)(s->w + 2) * (s->h + 2) * (s->d + 2)) return fail(VRT_E_INVALID, "bad argument");
+    CU(cudaSetDevice(s->ctx->device));
+    const int rc = scene_ensure_octant(const_cast<vrt_scene*>(s));
+    if (rc) return rc;
+    CU(cudaMemcpy(dst, s->odist[octant], bytes, cudaMemcpyDeviceToHost));
+    return VRT_OK;
+}
+
 // ------------------------------------------------------------------------------------------------ frames
 extern "C" void vrt_frame_release(vrt_frame* f) {
     if (!f) return;
@@ -387,7 +416,7 @@ extern "C" int vrt_render(vrt_context* c, const vrt_scene* s, const vrt_camera* 
     if (cam->volumeBounds[0] != s->w || cam->volumeBounds[1] != s->h || cam->volumeBounds[2] != s->d)
         return fail(VRT_E_INVALID, "camera volumeBounds differ from the scene bounds");
     if (!(st->pass_mask & VRT_PASS_PRIMARY)) return fail(VRT_E_INVALID, "pass_mask must include VRT_PASS_PRIMARY");
-    if (st->traversal > VRT_TRAVERSAL_LINEAR) return fail(VRT_E_INVALID, "unknown traversal");
+    if (st->traversal > VRT_TRAVERSAL_OCTANT) return fail(VRT_E_INVALID, "unknown traversal");
     if (st->pipeline > VRT_PIPELINE_WAVEFRONT) return fail(VRT_E_INVALID, "unknown pipeline");
     if (st->vol.aoSamples > 255) return fail(VRT_E_INVALID, "aoSamples must be <= 255 (the reference GUI allows 0..16)");
     const bool wavefront = st->pipeline != VRT_PIPELINE_MEGAKERNEL;
@@ -409,12 +438,15 @@ extern "C" int vrt_render(vrt_context* c, const vrt_scene* s, const vrt_camera* 
         rc = frame_ensure_wave(f, (st->pass_mask & VRT_PASS_SHADE) ? ((st->pass_mask & VRT_PASS_AO) ? st->vol.aoSamples : 0u) + 1u : 0u);
     if (rc) { if (!*frame) vrt_frame_release(f); return rc; }
 
+    const uint32_t traversal = st->traversal == VRT_TRAVERSAL_DEFAULT ? VRT_TRAVERSAL_OCTANT : st->traversal;
+    if (traversal == VRT_TRAVERSAL_OCTANT) { rc = scene_ensure_octant(const_cast<vrt_scene*>(s)); if (rc) { if (!*frame) vrt_frame_release(f); return rc; } }
     SceneDev sc{};
+    for (int o = 0; o < 8; o++) sc.odist[o] = s->odist[o];
     sc.vol = s->vol; sc.bmask = s->bmask; sc.bdist = s->bdist; sc.fdist = s->fdist; sc.ldist = s->ldist; sc.W = s->w; sc.H = s->h; sc.D = s->d; sc.Bx = s->Bx; sc.By = s->By; sc.Bz = s->Bz;
     sc.palette = s->palette; sc.noise = s->noise; sc.sky = s->sky; sc.skyW = s->skyW; sc.skyH = s->skyH;
     FrameParams fp{};
     fp.cam = *cam; fp.pass_mask = st->pass_mask; fp.out_mask = out_mask;
-    fp.traversal = st->traversal == VRT_TRAVERSAL_DEFAULT ? VRT_TRAVERSAL_FINE : st->traversal;
+    fp.traversal = traversal;
     fp.aoSamples = st->vol.aoSamples; fp.ambientIntensity = st->vol.ambientIntensity;
     for (int k = 0; k < 3; k++) { fp.lightDir[k] = st->light.direction[k]; fp.lightColor[k] = st->light.color[k]; }
     fp.lightIntensity = st->light.intensity;

@@ -167,8 +167,12 @@ struct LinRay {
 };
 enum { LIN_CONTINUE = 0, LIN_HIT = 1, LIN_OOB = 2, LIN_EXHAUSTED = 3 };
 
+// the directional field of the ray's octant (rayStep components are +-1 here: zero components take the literal loop)
+VRT_HD const uint8_t* octant_field(const SceneDev& sc, const Dda& s) {
+    return sc.odist[(s.stx < 0 ? 1 : 0) | (s.sty < 0 ? 2 : 0) | (s.stz < 0 ? 4 : 0)];
+}
 // Entry state from the DDA set-up of traceRayInt (:131-150). Returns LIN_OOB when mapPos starts outside the volume.
-VRT_HD int lin_begin(const SceneDev& sc, const Dda& s, V3 dir, uint32_t maxSteps, LinRay& r) {
+VRT_HD int lin_begin(const SceneDev& sc, const uint8_t* field, const Dda& s, V3 dir, uint32_t maxSteps, LinRay& r) {
     r.sx = r.sx0 = s.sx; r.sy = r.sy0 = s.sy; r.sz = r.sz0 = s.sz;
     r.dx = s.dx; r.dy = s.dy; r.dz = s.dz;
     r.ax = fabsf(dir.x); r.ay = fabsf(dir.y); r.az = fabsf(dir.z);
@@ -176,7 +180,7 @@ VRT_HD int lin_begin(const SceneDev& sc, const Dda& s, V3 dir, uint32_t maxSteps
     r.i = 0; r.maxSteps = maxSteps; r.mask = 0;
     if (!in_bounds(sc, s)) return LIN_OOB;
     const int LW = (int)sc.W + 2, LWH = LW * ((int)sc.H + 2);
-    r.p0 = sc.ldist + ((size_t)(s.mx + 1) + (size_t)(s.my + 1) * (size_t)LW + (size_t)(s.mz + 1) * (size_t)LWH);
+    r.p0 = field + ((size_t)(s.mx + 1) + (size_t)(s.my + 1) * (size_t)LW + (size_t)(s.mz + 1) * (size_t)LWH);
     r.SX = s.stx; r.SY = s.sty * LW; r.SZ = s.stz * LWH;
     r.T0 = (int)(0u - (uint32_t)VRT_LIN_MAGIC_BITS * (uint32_t)(r.SX + r.SY));
 #if defined(__CUDA_ARCH__)
@@ -242,7 +246,7 @@ VRT_HD TraceRes trace_ray(const SceneDev& sc, V3 start, V3 dir, uint32_t maxStep
     uint32_t i = 0, mask = 0, material = 0;
     bool hit = false, oob = false;
     // a NaN / infinite start (origin built from a NaN normal) never moves: the literal loop replays that too
-    if (TRAVERSAL == VRT_TRAVERSAL_LINEAR) fast = lin_usable(fast, s);
+    if (TRAVERSAL == VRT_TRAVERSAL_LINEAR || TRAVERSAL == VRT_TRAVERSAL_OCTANT) fast = lin_usable(fast, s);
     if (!fast) {
         // literal loop: rays with a zero / denormal / NaN direction component
         for (; i < maxSteps; i++) {
@@ -258,9 +262,9 @@ VRT_HD TraceRes trace_ray(const SceneDev& sc, V3 start, V3 dir, uint32_t maxStep
             if (material != 0) { hit = true; break; }
             mask = dda_step_rec(s);
         }
-    } else if (TRAVERSAL == VRT_TRAVERSAL_LINEAR) {
+    } else if (TRAVERSAL == VRT_TRAVERSAL_LINEAR || TRAVERSAL == VRT_TRAVERSAL_OCTANT) {
         LinRay lr;
-        int st = lin_begin(sc, s, dir, maxSteps, lr);
+        int st = lin_begin(sc, TRAVERSAL == VRT_TRAVERSAL_OCTANT ? octant_field(sc, s) : sc.ldist, s, dir, maxSteps, lr);
         while (st == LIN_CONTINUE) st = lin_round<true>(sc, lr);
         lin_map_pos(lr, s.mx, s.my, s.mz);
         s.sx = lr.sx; s.sy = lr.sy; s.sz = lr.sz;

@@ -1,0 +1,113 @@
+// vrt_engine.cuh — persistent-warp ray engine (device only; sm_100a): lane refill + fixed-length lock-step rounds.
+//
+// Why (ncu r1c/r1d/r1e, profiles/): a warp that traces 32 rays to completion with the per-ray loop of trace_ray runs at 9-15 of
+// 32 lanes although it is issue-bound, for two reasons: rays END after very different step counts (AO: 1..64, shadow /
+// reflection: 1..512), and within one look-up round every lane runs a different number of steps (the unrolled step loop held 55 %
+// of all issued instructions at 5-9 active lanes; it runs max-over-lanes iterations). The engine removes both:
+//   * ray set-up (record load, direction, box entry, DDA set-up, IEEE divisions: ~270 instructions) always runs with all 32 lanes,
+//     32 rays at a time, and pushes the resulting traversal states into a per-warp shared-memory stash;
+//   * a refill event happens when >= refillT lanes are idle: those lanes first retire the result of their finished ray (so the
+//     retire code also runs with >= refillT lanes), then pop a prepared state (LDS.128, conflict-free);
+//   * a round = [lanes whose safe-step budget is spent look the field up] + a FIXED number of DDA steps for the whole warp
+//     (ENGINE_NEAR_STEPS, or ENGINE_FAR_STEPS when every live lane has that much budget), fully unrolled, each step predicated
+//     on the lane's remaining budget (the predicate rides on the FSETPs: 9 instructions per step).
+// Every ray still performs exactly the float operations of traceRayInt in the same order (the select form of
+// voxel_volume.frag:164-170) and looks the field up through the same lin_bits() offset recovery as trace_ray<LINEAR/OCTANT>, so
+// results are bit-identical (tests/test_gpu.py runs every back-end against the oracle).
+#pragma once
+#include "vrt_wave.cuh"
+
+namespace vrt {
+
+constexpr int ENGINE_WARPS = 8;          // warps per block
+constexpr int ENGINE_STASH = 64;         // prepared rays per warp (a refill asks for <= 32 more while < 32 are left)
+constexpr int ENGINE_NEAR_STEPS = 4;
+constexpr int ENGINE_FAR_STEPS = 16;
+
+// Traversal state of one ray: LinRay (vrt_core.cuh) + the step budget
+struct EngRay {
+    LinRay l;                            // l.i is not used here
+    int rem;                             // steps that may still run before the field must be looked at again
+    uint32_t left;                       // maxSteps - steps taken - rem
+};
+
+// SoA of 16-byte quads: lanes popping consecutive entries read consecutive quads
+struct alignas(16) EngineStash {
+    float4 s[ENGINE_STASH];              // sideDist at entry (== sideDist0);  w: flags = maxSteps << 8 | sign bits (1: step -1) x,y,z
+    float4 d[ENGINE_STASH];              // deltaDist;                         w: user word 0
+    float4 a[ENGINE_STASH];              // |dir|;                             w: user word 1
+    uint2 p[ENGINE_STASH];               // entry pointer into the ray's safe-step field
+};
+
+__device__ __forceinline__ void engine_push(EngineStash& st, uint32_t slot, const LinRay& r, uint32_t u0, uint32_t u1) {
+    const uint32_t flags = (r.maxSteps << 8) | (r.SX < 0 ? 1u : 0u) | (r.SY < 0 ? 2u : 0u) | (r.SZ < 0 ? 4u : 0u);
+    st.s[slot] = make_float4(r.sx, r.sy, r.sz, __uint_as_float(flags));
+    st.d[slot] = make_float4(r.dx, r.dy, r.dz, __uint_as_float(u0));
+    st.a[slot] = make_float4(r.ax, r.ay, r.az, __uint_as_float(u1));
+    const unsigned long long p = (unsigned long long)r.p0;
+    st.p[slot] = make_uint2((uint32_t)p, (uint32_t)(p >> 32));
+}
+
+__device__ __forceinline__ void engine_pop(const EngineStash& st, uint32_t slot, EngRay& e, int LW, int LWH, uint32_t& u0, uint32_t& u1) {
+    const float4 s = st.s[slot], d = st.d[slot], a = st.a[slot];
+    const uint2 p = st.p[slot];
+    const uint32_t flags = __float_as_uint(s.w);
+    LinRay& r = e.l;
+    r.sx = r.sx0 = s.x; r.sy = r.sy0 = s.y; r.sz = r.sz0 = s.z;
+    r.dx = d.x; r.dy = d.y; r.dz = d.z;
+    r.ax = a.x; r.ay = a.y; r.az = a.z;
+    u0 = __float_as_uint(d.w); u1 = __float_as_uint(a.w);
+    r.maxSteps = flags >> 8;
+    r.SX = (flags & 1u) ? -1 : 1; r.SY = (flags & 2u) ? -LW : LW; r.SZ = (flags & 4u) ? -LWH : LWH;
+    r.T0 = (int)(0u - (uint32_t)VRT_LIN_MAGIC_BITS * (uint32_t)(r.SX + r.SY));
+    r.p0 = reinterpret_cast<const uint8_t*>((unsigned long long)p.x | ((unsigned long long)p.y << 32));
+    e.rem = 0; e.left = r.maxSteps;
+}
+
+enum { ENG_GO = 0, ENG_HIT = 1, ENG_OOB = 2, ENG_EXHAUSTED = 3 };
+
+// Look-up for a lane whose budget is spent (rem == 0). Mirrors the loop head of traceRayInt (:152-162): i < maxSteps, bounds
+// test, getVoxel != 0. On ENG_GO the budget is re-armed with min(safe steps, steps left).
+__device__ __forceinline__ int engine_lookup(EngRay& e) {
+    if (e.left == 0u) return ENG_EXHAUSTED;
+    const LinRay& r = e.l;
+    const int bx = lin_bits(r.sx, r.sx0, r.ax), by = lin_bits(r.sy, r.sy0, r.ay), bz = lin_bits(r.sz, r.sz0, r.az);
+    const int t = (int)((uint32_t)bx * (uint32_t)r.SX + (uint32_t)by * (uint32_t)r.SY + (uint32_t)r.T0);
+    const long long off = (long long)(bz - VRT_LIN_MAGIC_BITS) * (long long)r.SZ + (long long)t;
+    int n;
+    asm("ld.global.nc.s8 %0, [%1];" : "=r"(n) : "l"(r.p0 + off));
+    if (n <= 0) return n == 0 ? ENG_HIT : ENG_OOB;
+    e.rem = n < (int)e.left ? n : (int)e.left;
+    e.left -= (uint32_t)e.rem;
+    return ENG_GO;
+}
+
+// DDA step number k of a round (:164-170, select form) for lanes whose budget at the start of the round exceeds k.
+// Written in PTX so that the budget predicate rides on the three compares and the adds stay predicated (8 instructions).
+__device__ __forceinline__ void engine_step(LinRay& r, int rem, int k) {
+    asm("{\n\t.reg .pred pa, px, py, pz;\n\t.reg .f32 m;\n\t"
+        "setp.gt.s32 pa, %6, %8;\n\t"
+        "min.f32 m, %0, %1, %2;\n\t"
+        "setp.le.and.f32 px, %0, m, pa;\n\t"
+        "setp.le.and.f32 py, %1, m, pa;\n\t"
+        "setp.le.and.f32 pz, %2, m, pa;\n\t"
+        "@px add.f32 %0, %0, %3;\n\t"
+        "@py add.f32 %1, %1, %4;\n\t"
+        "@pz add.f32 %2, %2, %5;\n\t}"
+        : "+f"(r.sx), "+f"(r.sy), "+f"(r.sz) : "f"(r.dx), "f"(r.dy), "f"(r.dz), "r"(rem), "n"(0) , "r"(k));
+}
+__device__ __forceinline__ uint32_t engine_steps_taken(const EngRay& e) { return e.l.maxSteps - e.left - (uint32_t)e.rem; }
+
+// literal loop of traceRayInt for rays the select-form DDA cannot replay (zero / denormal / NaN components): any-hit form
+__device__ __forceinline__ bool engine_anyhit_literal(const SceneDev& sc, Dda s, uint32_t maxSteps, uint32_t& fetches) {
+    uint32_t i = 0; bool hit = false;
+    for (; i < maxSteps; i++) {
+        if (!in_bounds(sc, s)) break;
+        if (fetch_voxel(sc, s) != 0) { hit = true; break; }
+        dda_step_literal(s);
+    }
+    fetches = hit ? i + 1 : i;
+    return hit;
+}
+
+}  // namespace vrt

@@ -20,6 +20,11 @@ cudaError_t launch_build_accel(const uint8_t* vol, uint32_t W, uint32_t H, uint3
 cudaError_t launch_build_fdist(const uint8_t* vol, const uint8_t* bdist, uint32_t W, uint32_t H, uint32_t D, uint8_t* fdist, uint8_t* ldist,
                                uint8_t* a, uint8_t* t1, uint8_t* t2, cudaStream_t stream, int* launches);
 
+// directional safe-step fields (vrt_octant.cu): odist[0..7] of (W+2)(H+2)(D+2) bytes each, scratch of octant_scratch_bytes()
+size_t octant_scratch_bytes(uint32_t W, uint32_t H, uint32_t D);
+cudaError_t launch_build_odist(const uint8_t* vol, uint32_t W, uint32_t H, uint32_t D, uint8_t* const odist[8], uint32_t* scratch,
+                               cudaStream_t stream, int* launches);
+
 // procedural volumes (vrt_generate.cu)
 cudaError_t launch_generate(int generator, uint32_t seed, uint8_t* vol, uint32_t W, uint32_t H, uint32_t D, cudaStream_t stream);
 void generator_palette(int generator, uint32_t seed, vrt_material palette[256]);   // host

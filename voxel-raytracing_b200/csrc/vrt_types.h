@@ -28,7 +28,17 @@ constexpr int VRT_FINE_CAP = 15;
 //              LW = W+2, LH = H+2; apron voxels (the layer just outside the volume) hold VRT_LIN_OOB. A ray that does its
 //              look-ups every fdist steps can be at most one voxel outside the volume when it looks again, so the
 //              traversal needs no bounds test and no coordinates: one byte load at entry_offset + sum(count_axis * stride_axis).
+//              Read as a SIGNED byte the field is: 0 solid, -1 outside, 1..VRT_SAFE_MAX safe steps (one compare ends a ray).
 constexpr uint32_t VRT_LIN_OOB = 255;
+constexpr uint32_t VRT_SAFE_MAX = 127;
+//   odist[o][v] : DIRECTIONAL safe-step fields, one per direction octant o = (dir.x<0) | (dir.y<0)<<1 | (dir.z<0)<<2, same aproned
+//              linear layout and value coding as ldist. A ray of octant o only ever moves by 0 or sign_o(axis) per axis and step,
+//              so after k steps it is inside the cube [0,k]^3 (in octant direction) anchored at its voxel: odist[o][v] = n means the
+//              cube of side n anchored at v (offsets 0..n-1 per axis towards o) holds no solid and no out-of-bounds voxel, hence n
+//              steps can run before the field is looked at again. What lies behind or beside the ray no longer shortens its steps
+//              (a ray LEAVING a surface gets its full budget at once). n is rounded down to a level of VRT_OCT_LEVELS.
+constexpr int VRT_OCT_NLEVELS = 24;
+#define VRT_OCT_LEVEL_LIST {1, 2, 3, 4, 5, 6, 7, 8, 10, 12, 14, 16, 20, 24, 28, 32, 40, 48, 56, 64, 80, 96, 112, 127}
 
 struct SceneDev {
     const uint8_t* vol;               // dense u8[W*H*D], x fastest (voxel_scene.cpp:99)
@@ -36,6 +46,7 @@ struct SceneDev {
     const uint8_t* bdist;             // [Bz][By][Bx]
     const uint8_t* fdist;             // [Bz][By][Bx][4][4][4]
     const uint8_t* ldist;             // [D+2][H+2][W+2]
+    const uint8_t* odist[8];          // per direction octant, [D+2][H+2][W+2] each
     uint32_t W, H, D;
     uint32_t Bx, By, Bz;
     const vrt_material* palette;      // 256 entries

@@ -8,7 +8,9 @@
 // records, not registers) => 3-4x the resident warps to hide the DDA's dependent-issue latency, and warps stay full
 // because sky pixels / non-metallic pixels / finished pixels do not occupy lanes in the secondary waves.
 #include <cuda_runtime.h>
+#include <stdlib.h>
 #include "vrt_wave.cuh"
+#include "vrt_engine.cuh"
 #include "vrt_launch.h"
 
 namespace vrt {
@@ -183,6 +185,117 @@ __global__ void __launch_bounds__(256) wave_anyhit_kernel(const SceneDev sc, con
     add_totals(ctr, 2, rays, fetches, 0u);
 }
 
+// ---- any-hit wave on the ray engine (vrt_engine.cuh): LINEAR (isotropic field) or OCTANT (directional fields) ----
+template <int TRAVERSAL, int NEAR_STEPS, int FAR_STEPS>
+__global__ void __launch_bounds__(ENGINE_WARPS * 32) wave_anyhit_engine_kernel(const SceneDev sc, const FrameParams fp, const PlanesDev pl, const WaveBuf wb,
+                                                                                Counters* __restrict__ ctr, const uint32_t refillT, const uint32_t farShare) {
+    __shared__ EngineStash stashAll[ENGINE_WARPS];
+    EngineStash& st = stashAll[threadIdx.x >> 5];
+    const uint32_t lane = threadIdx.x & 31, ltMask = (1u << lane) - 1u;
+    const uint32_t n0 = wb.ctr->n0, S = n0 + wb.ctr->nsq;
+    const uint32_t aoN = (fp.pass_mask & VRT_PASS_AO) ? fp.aoSamples : 0u;
+    const uint32_t R = aoN + ((fp.pass_mask & VRT_PASS_SHADOW) ? 1u : 0u);
+    const unsigned long long total = (unsigned long long)S * R;
+    const int LW = (int)sc.W + 2, LWH = LW * ((int)sc.H + 2);
+    const bool instrument = (fp.out_mask & VRT_OUT_INSTRUMENT) != 0;
+
+    // warp-uniform work range [cur, end) and the (ray kind, record slot) of item `cur`
+    unsigned long long cur = 0, end = 0;
+    uint32_t ci = 0, cq = 0, stashN = 0;
+    bool exhausted = total == 0;
+    // lane state
+    EngRay er; er.rem = 0; er.left = 0;
+    er.l.sx = er.l.sy = er.l.sz = er.l.dx = er.l.dy = er.l.dz = er.l.sx0 = er.l.sy0 = er.l.sz0 = er.l.ax = er.l.ay = er.l.az = 0.0f;
+    er.l.p0 = sc.ldist; er.l.SX = er.l.SY = er.l.SZ = er.l.T0 = 0; er.l.maxSteps = 0;
+    bool alive = false, pending = false, hitRes = false;
+    uint32_t idx = 0, kind = 0, fetchRes = 0;
+    unsigned rays = 0, fetches = 0;
+
+    auto retire = [&](uint32_t rIdx, uint32_t rKind, bool hit, uint32_t f) {
+        wb.res[(size_t)rKind * wb.recCap + rIdx] = hit ? 1 : 0;
+        rays++; fetches += f;
+        if (instrument) {
+            const uint32_t pxy = wb.rec[3 * (size_t)rIdx].w;
+            const size_t p = plane_index(fp, (int)(pxy & 0xffffu), (int)(pxy >> 16));
+            atomicAdd(pl.rays + p, 1u); atomicAdd(pl.fetches + p, f);
+        }
+    };
+
+    for (;;) {
+        // ---- refill: idle lanes retire their finished ray and pop a prepared one
+        const unsigned idleMask = __ballot_sync(0xffffffffu, !alive);
+        const uint32_t nIdle = __popc(idleMask);
+        const bool canRefill = stashN > 0 || !exhausted;
+        if (nIdle == 32u && !canRefill) break;
+        if (canRefill && (nIdle >= refillT || nIdle == 32u)) {
+            if (!alive && pending) { retire(idx, kind, hitRes, fetchRes); pending = false; }
+            // produce prepared rays, 32 at a time with all lanes, until the idle lanes can be served
+            while (stashN < nIdle && !exhausted) {
+                if (cur >= end) {
+                    uint32_t c = 0;
+                    if (lane == 0) c = atomicAdd(&wb.ctr->chunk, 1u);
+                    c = __shfl_sync(0xffffffffu, c, 0);
+                    const unsigned long long t0 = (unsigned long long)c * 256u;
+                    if (t0 >= total) { exhausted = true; break; }
+                    cur = t0; end = t0 + 256u < total ? t0 + 256u : total;
+                    ci = (uint32_t)(t0 / S); cq = (uint32_t)(t0 - (unsigned long long)ci * S);
+                }
+                const bool valid = cur + lane < end;
+                bool push = false;
+                LinRay nr = er.l;
+                uint32_t nIdx = 0, i = ci;
+                if (valid) {
+                    unsigned long long qq = (unsigned long long)cq + lane;
+                    while (qq >= S) { qq -= S; i++; }
+                    const uint32_t q = (uint32_t)qq;
+                    nIdx = q < n0 ? q : wb.sq[q - n0];
+                    const RecQ r0 = wb.rec[3 * (size_t)nIdx], r1 = wb.rec[3 * (size_t)nIdx + 1];
+                    V3 rs, rd, pos; uint32_t maxSteps; Dda s;
+                    wave_anyhit_ray(sc, fp, q3(r0), q3(r1), (int)(r0.w & 0xffffu), (int)(r0.w >> 16), r1.w >> 8, i, aoN, rs, rd, maxSteps);
+                    if (!lin_usable(dda_begin(sc, rs, rd, pos, s), s)) {
+                        uint32_t f; const bool hit = engine_anyhit_literal(sc, s, maxSteps, f);
+                        retire(nIdx, i, hit, f);
+                    } else if (lin_begin(sc, TRAVERSAL == VRT_TRAVERSAL_OCTANT ? octant_field(sc, s) : sc.ldist, s, rd, maxSteps, nr) == LIN_OOB)
+                        retire(nIdx, i, false, 0u);
+                    else push = true;
+                }
+                const unsigned pm = __ballot_sync(0xffffffffu, push);
+                if (push) engine_push(st, stashN + __popc(pm & ltMask), nr, nIdx, i);
+                stashN += __popc(pm);
+                cur += 32u; cq += 32u;
+                while (cq >= S) { cq -= S; ci++; }
+            }
+            __syncwarp();
+            const uint32_t take = nIdle < stashN ? nIdle : stashN;
+            const uint32_t r = __popc(idleMask & ltMask);
+            if (!alive && r < take) { engine_pop(st, stashN - 1u - r, er, LW, LWH, idx, kind); alive = true; }
+            stashN -= take;
+            __syncwarp();
+        }
+        // ---- look-up for lanes whose budget is spent
+        if (alive && er.rem == 0) {
+            const int stt = engine_lookup(er);
+            if (stt != ENG_GO) {
+                alive = false; pending = true; hitRes = stt == ENG_HIT; fetchRes = engine_steps_taken(er) + (hitRes ? 1u : 0u);
+            }
+        }
+        // ---- lock-step DDA steps: a long round when every live lane can use it
+        // a long round when at least farShare/8 of the live lanes can use all of it
+        const uint32_t nFar = __popc(__ballot_sync(0xffffffffu, alive && er.rem >= FAR_STEPS));
+        if (nFar * 8u >= (32u - nIdle) * farShare && nFar) {
+#pragma unroll
+            for (int k = 0; k < FAR_STEPS; k++) engine_step(er.l, er.rem, k);
+            er.rem = max(er.rem - FAR_STEPS, 0);
+        } else {
+#pragma unroll
+            for (int k = 0; k < NEAR_STEPS; k++) engine_step(er.l, er.rem, k);
+            er.rem = max(er.rem - NEAR_STEPS, 0);
+        }
+    }
+    if (pending) retire(idx, kind, hitRes, fetchRes);
+    add_totals(ctr, 2, rays, fetches, 0u);
+}
+
 __global__ void __launch_bounds__(256) wave_resolve_kernel(const SceneDev sc, const FrameParams fp, const PlanesDev pl, const WaveBuf wb) {
     const uint32_t n0 = wb.ctr->n0;
     const uint32_t aoN = (fp.pass_mask & VRT_PASS_AO) ? fp.aoSamples : 0u;
@@ -191,6 +304,13 @@ __global__ void __launch_bounds__(256) wave_resolve_kernel(const SceneDev sc, co
         const V3 c = wave_resolve(sc, fp, wb, idx, aoN);
         store_color(fp, pl, plane_index(fp, (int)(pxy & 0xffffu), (int)(pxy >> 16)), c);
     }
+}
+
+// refill threshold of the ray engine (idle lanes that trigger a refill); VRT_ENGINE_T=0 selects the run-to-completion kernels
+static int engineT() {
+    static int t = -1;
+    if (t < 0) { const char* e = getenv("VRT_ENGINE_T"); t = e ? atoi(e) : 8; if (t > 32) t = 32; }
+    return t;
 }
 
 template <int T>
@@ -213,7 +333,22 @@ static cudaError_t launch_wave_t(const SceneDev& sc, const FrameParams& fp, cons
         for (int w = 0; w < MAX_REFLECTIONS; w++) { wave_bounce_kernel<T><<<(unsigned)(sms * occBounce), 128, 0, stream>>>(sc, fp, pl, wb, ctr, w); n++; }
     if (ev) cudaEventRecord(ev[1], stream);
     const uint32_t aoN = (fp.pass_mask & VRT_PASS_AO) ? fp.aoSamples : 0u;
-    if (shade && (aoN || (fp.pass_mask & VRT_PASS_SHADOW))) { wave_anyhit_kernel<T><<<(unsigned)(sms * occAny), 256, 0, stream>>>(sc, fp, pl, wb, ctr); n++; }
+    if (shade && (aoN || (fp.pass_mask & VRT_PASS_SHADOW))) {
+        if ((T == VRT_TRAVERSAL_LINEAR || T == VRT_TRAVERSAL_OCTANT) && engineT() > 0) {
+            static const int variant = getenv("VRT_ENGINE_VARIANT") ? atoi(getenv("VRT_ENGINE_VARIANT")) : 0;
+            auto launch = [&](auto kernel) {
+                int occ = 0;
+                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, ENGINE_WARPS * 32, 0);
+                if (occ < 1) occ = 1;
+                static const int farShare = getenv("VRT_ENGINE_FARSHARE") ? atoi(getenv("VRT_ENGINE_FARSHARE")) : 4;
+                kernel<<<(unsigned)(sms * occ), ENGINE_WARPS * 32, 0, stream>>>(sc, fp, pl, wb, ctr, (uint32_t)engineT(), (uint32_t)farShare);
+            };
+            if (variant == 1) launch(wave_anyhit_engine_kernel<T, 4, 16>);
+            else if (variant == 2) launch(wave_anyhit_engine_kernel<T, 8, 16>);
+            else launch(wave_anyhit_engine_kernel<T, 8, 32>);
+        } else wave_anyhit_kernel<T><<<(unsigned)(sms * occAny), 256, 0, stream>>>(sc, fp, pl, wb, ctr);
+        n++;
+    }
     if (ev) cudaEventRecord(ev[2], stream);
     if (shade) { wave_resolve_kernel<<<(unsigned)(sms * 8), 256, 0, stream>>>(sc, fp, pl, wb); n++; }
     if (launches) *launches += n;
@@ -226,6 +361,7 @@ cudaError_t launch_wavefront(const SceneDev& sc, const FrameParams& fp, const Pl
     if (fp.traversal == VRT_TRAVERSAL_DENSE_U8) return launch_wave_t<VRT_TRAVERSAL_DENSE_U8>(sc, fp, pl, ctr, wb, sms, stream, launches, ev);
     if (fp.traversal == VRT_TRAVERSAL_FINE) return launch_wave_t<VRT_TRAVERSAL_FINE>(sc, fp, pl, ctr, wb, sms, stream, launches, ev);
     if (fp.traversal == VRT_TRAVERSAL_LINEAR) return launch_wave_t<VRT_TRAVERSAL_LINEAR>(sc, fp, pl, ctr, wb, sms, stream, launches, ev);
+    if (fp.traversal == VRT_TRAVERSAL_OCTANT) return launch_wave_t<VRT_TRAVERSAL_OCTANT>(sc, fp, pl, ctr, wb, sms, stream, launches, ev);
     return launch_wave_t<VRT_TRAVERSAL_BRICK>(sc, fp, pl, ctr, wb, sms, stream, launches, ev);
 }
 

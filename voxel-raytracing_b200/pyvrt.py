@@ -15,7 +15,7 @@ LIB_PATH = os.environ.get("VRT_LIB", os.path.join(HERE, "libvrt.so"))   # VRT_LI
 
 PASS_PRIMARY, PASS_SHADOW, PASS_AO, PASS_REFLECT, PASS_SHADE, PASS_ALL = 1, 2, 4, 8, 16, 31
 OUT_GBUFFER, OUT_INSTRUMENT = 1, 2
-TRAVERSAL_DEFAULT, TRAVERSAL_DENSE_U8, TRAVERSAL_BRICK, TRAVERSAL_FINE, TRAVERSAL_LINEAR = 0, 1, 2, 3, 4
+TRAVERSAL_DEFAULT, TRAVERSAL_DENSE_U8, TRAVERSAL_BRICK, TRAVERSAL_FINE, TRAVERSAL_LINEAR, TRAVERSAL_OCTANT = 0, 1, 2, 3, 4, 5
 PIPELINE_DEFAULT, PIPELINE_MEGAKERNEL, PIPELINE_WAVEFRONT = 0, 1, 2
 DENOISE_AS_EXECUTED, DENOISE_AS_INTENDED = 0, 1
 E_LFS_POINTER, E_NO_INSTANCE, E_PARSE, E_IO, E_CUDA, E_NO_DEVICE = -2, -3, -4, -5, -6, -7
@@ -206,6 +206,10 @@ class VoxelScene:
         bx, by, bz = (self.width + 3) // 4, (self.height + 3) // 4, (self.depth + 3) // 4
         f = np.zeros((bz, by, bx, 4, 4, 4), np.uint8)   # [bz][by][bx][z&3][y&3][x&3]
         _ck(lib().vrt_scene_download_fdist(self.h, f.ctypes.data_as(C.c_void_p), C.c_size_t(f.size))); return f
+
+    def download_odist(self, octant):
+        f = np.zeros((self.depth + 2, self.height + 2, self.width + 2), np.uint8)   # aproned, [z+1][y+1][x+1]
+        _ck(lib().vrt_scene_download_odist(self.h, int(octant), f.ctypes.data_as(C.c_void_p), C.c_size_t(f.size))); return f
 
     def accel_info(self):
         a, b, c = C.c_size_t(), C.c_size_t(), C.c_size_t()
