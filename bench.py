@@ -43,6 +43,8 @@ def parse_args():
     ap.add_argument("--passes", type=int, default=None, help="override the pass mask (measurement of pass subsets)")
     ap.add_argument("--ao", type=int, default=None, help="override aoSamples")
     ap.add_argument("--no-gbuffer", action="store_true")
+    ap.add_argument("--shard", type=int, nargs=2, default=None, metavar=("RANK", "WORLD"),
+                    help="debug: render only the tile shard RANK of WORLD on one GPU (what one rank of an N-GPU run does), no gather")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
     return ap.parse_args()
@@ -238,7 +240,10 @@ def run_vrt(args):
     size = tuple(args.size) if args.size else cfg["size"]
     W, H = size
 
-    ctx = pyvrt.Context(local, rank=rank, world=world)       # raises without a GPU: there is no CPU fallback
+    if args.shard and world == 1:
+        ctx = pyvrt.Context(local, rank=args.shard[0], world=args.shard[1])
+    else:
+        ctx = pyvrt.Context(local, rank=rank, world=world)   # raises without a GPU: there is no CPU fallback
     scene = configs.build_scene(ctx, cfg, args.whd)
     bounds = scene.bounds
     st = configs.settings_for(cfg, gbuffer=not args.no_gbuffer)

@@ -94,12 +94,12 @@ static void build_odist(const uint8_t* vol, int W, int H, int D, std::vector<uin
                 m = std::min(m, at(x, y + sy, z)); m = std::min(m, at(x, y, z + sz));
                 m = std::min(m, at(x + sx, y + sy, z)); m = std::min(m, at(x + sx, y, z + sz)); m = std::min(m, at(x, y + sy, z + sz));
                 m = std::min(m, at(x + sx, y + sy, z + sz));
-                v = std::min(1 + m, (int)VRT_SAFE_MAX);
+                v = std::min(1 + m, 1 << 20);
             }
             e[(size_t)x + (size_t)y * W + (size_t)z * W * H] = v;
             int q = 0;
             for (int l = 0; l < VRT_OCT_NLEVELS; l++) if (lv[l] <= v) q = lv[l];
-            odist[o][(size_t)(x + 1) + (size_t)(y + 1) * (W + 2) + (size_t)(z + 1) * (W + 2) * (H + 2)] = (uint8_t)q;
+            odist[o][(size_t)(x + 1) + (size_t)(y + 1) * (W + 2) + (size_t)(z + 1) * (W + 2) * (H + 2)] = (uint8_t)safe_encode((uint32_t)q);
         }
     }
 }

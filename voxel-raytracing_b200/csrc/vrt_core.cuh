@@ -190,8 +190,11 @@ VRT_HD int lin_begin(const SceneDev& sc, const uint8_t* field, const Dda& s, V3 
     return LIN_CONTINUE;
 }
 // One look-up and the steps it allows. STEP_REC: keep the mask of the last step (needed for the hit normal).
+// ANYHIT: the caller only wants to know whether the ray hits (traceRayHit :198-202). Once the field grants at least as many
+// steps as the ray has left, the loop of traceRayInt provably runs out of steps over empty in-bounds voxels (maxSteps getVoxel
+// calls, no hit): the remaining steps need not be executed because their only product, the DDA state, is discarded.
 template <bool STEP_REC>
-VRT_HD int lin_round(const SceneDev& sc, LinRay& r) {
+VRT_HD int lin_round(const SceneDev& sc, LinRay& r, const bool ANYHIT = false) {
     const int bx = lin_bits(r.sx, r.sx0, r.ax), by = lin_bits(r.sy, r.sy0, r.ay), bz = lin_bits(r.sz, r.sz0, r.az);
     const int t = (int)((uint32_t)bx * (uint32_t)r.SX + (uint32_t)by * (uint32_t)r.SY + (uint32_t)r.T0);   // cx*SX + cy*SY
     const long long off = (long long)(bz - VRT_LIN_MAGIC_BITS) * (long long)r.SZ + (long long)t;
@@ -203,7 +206,9 @@ VRT_HD int lin_round(const SceneDev& sc, LinRay& r) {
 #endif
     if (n == 0) return LIN_HIT;
     if (n == VRT_LIN_OOB) return LIN_OOB;
+    n = safe_decode(n);
     const uint32_t left = r.maxSteps - r.i;
+    if (ANYHIT && n >= left) { r.i = r.maxSteps; return LIN_EXHAUSTED; }
     n = n < left ? n : left;
     r.i += n;
     Dda d; d.sx = r.sx; d.sy = r.sy; d.sz = r.sz; d.dx = r.dx; d.dy = r.dy; d.dz = r.dz;
@@ -237,7 +242,7 @@ VRT_HD bool dda_begin(const SceneDev& sc, V3 start, V3 dir, V3& pos, Dda& s) {
 VRT_HD bool lin_usable(bool fast, const Dda& s) { return fast && finitef(s.sx) && finitef(s.sy) && finitef(s.sz); }
 
 template <int TRAVERSAL>
-VRT_HD TraceRes trace_ray(const SceneDev& sc, V3 start, V3 dir, uint32_t maxSteps) {
+VRT_HD TraceRes trace_ray(const SceneDev& sc, V3 start, V3 dir, uint32_t maxSteps, const bool anyhit = false) {
     TraceRes r;
     V3 pos;
     Dda s;
@@ -265,7 +270,7 @@ VRT_HD TraceRes trace_ray(const SceneDev& sc, V3 start, V3 dir, uint32_t maxStep
     } else if (TRAVERSAL == VRT_TRAVERSAL_LINEAR || TRAVERSAL == VRT_TRAVERSAL_OCTANT) {
         LinRay lr;
         int st = lin_begin(sc, TRAVERSAL == VRT_TRAVERSAL_OCTANT ? octant_field(sc, s) : sc.ldist, s, dir, maxSteps, lr);
-        while (st == LIN_CONTINUE) st = lin_round<true>(sc, lr);
+        while (st == LIN_CONTINUE) st = lin_round<true>(sc, lr, anyhit);
         lin_map_pos(lr, s.mx, s.my, s.mz);
         s.sx = lr.sx; s.sy = lr.sy; s.sz = lr.sz;
         i = lr.i; mask = lr.mask;

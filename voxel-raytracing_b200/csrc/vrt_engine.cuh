@@ -20,6 +20,7 @@
 namespace vrt {
 
 constexpr int ENGINE_WARPS = 8;          // warps per block
+constexpr uint32_t ENGINE_CHUNK = 64;    // rays per claim of the global work counter (small: the tail of a sharded frame is short)
 constexpr int ENGINE_STASH = 64;         // prepared rays per warp (a refill asks for <= 32 more while < 32 are left)
 constexpr int ENGINE_NEAR_STEPS = 4;
 constexpr int ENGINE_FAR_STEPS = 16;
@@ -74,11 +75,14 @@ __device__ __forceinline__ int engine_lookup(EngRay& e) {
     const int bx = lin_bits(r.sx, r.sx0, r.ax), by = lin_bits(r.sy, r.sy0, r.ay), bz = lin_bits(r.sz, r.sz0, r.az);
     const int t = (int)((uint32_t)bx * (uint32_t)r.SX + (uint32_t)by * (uint32_t)r.SY + (uint32_t)r.T0);
     const long long off = (long long)(bz - VRT_LIN_MAGIC_BITS) * (long long)r.SZ + (long long)t;
-    int n;
-    asm("ld.global.nc.s8 %0, [%1];" : "=r"(n) : "l"(r.p0 + off));
-    if (n <= 0) return n == 0 ? ENG_HIT : ENG_OOB;
-    e.rem = n < (int)e.left ? n : (int)e.left;
-    e.left -= (uint32_t)e.rem;
+    uint32_t n;
+    asm("ld.global.nc.u8 %0, [%1];" : "=r"(n) : "l"(r.p0 + off));
+    if (n - 1u >= 254u) return n == 0u ? ENG_HIT : ENG_OOB;
+    n = safe_decode(n);
+    // any-hit: a budget that covers all remaining steps ends the ray as a miss after maxSteps getVoxel calls (see lin_round)
+    if (n >= e.left) { e.left = 0u; return ENG_EXHAUSTED; }
+    e.rem = (int)n;
+    e.left -= n;
     return ENG_GO;
 }
 

@@ -16,8 +16,8 @@ __constant__ uint8_t c_octLevels[VRT_OCT_NLEVELS + 1];
 
 // level 0: emptiness bits
 __global__ void oct_init_kernel(const uint8_t* __restrict__ vol, uint32_t* __restrict__ bits, uint32_t W, uint32_t H, uint32_t WW) {
-    const uint32_t wx = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, z = blockIdx.z;
-    if (wx >= WW) return;
+    const uint32_t wx = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y, z = blockIdx.z;
+    if (wx >= WW || y >= H) return;
     const uint8_t* row = vol + (size_t)y * W + (size_t)z * W * H;
     uint32_t m = 0;
     const uint32_t x0 = wx * 32u;
@@ -50,8 +50,8 @@ __device__ __forceinline__ uint32_t oct_shifted(const uint32_t* __restrict__ row
 
 // next = level m+d from prev = level m
 __global__ void oct_level_kernel(const uint32_t* __restrict__ prev, uint32_t* __restrict__ next, int WW, int H, int D, int d, int sx, int sy, int sz) {
-    const int wx = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, z = blockIdx.z;
-    if (wx >= WW) return;
+    const int wx = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y, z = blockIdx.z;
+    if (wx >= WW || y >= H) return;
     uint32_t acc = 0xffffffffu;
 #pragma unroll
     for (int c = 0; c < 2; c++) {
@@ -69,8 +69,8 @@ __global__ void oct_level_kernel(const uint32_t* __restrict__ prev, uint32_t* __
 
 // count the levels each voxel satisfies (levels are nested: E_n subset of E_m for n > m) and write the aproned byte field
 __global__ void oct_final_kernel(const uint32_t* __restrict__ levels, size_t levelWords, uint8_t* __restrict__ out, uint32_t W, uint32_t H, uint32_t WW) {
-    const uint32_t wx = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, z = blockIdx.z;
-    if (wx >= WW) return;
+    const uint32_t wx = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y, z = blockIdx.z;
+    if (wx >= WW || y >= H) return;
     const size_t i = (size_t)wx + (size_t)y * WW + (size_t)z * WW * H;
     uint32_t c0 = 0, c1 = 0, c2 = 0, c3 = 0, c4 = 0;
     for (int l = 0; l < VRT_OCT_NLEVELS; l++) {
@@ -99,12 +99,12 @@ cudaError_t launch_build_odist(const uint8_t* vol, uint32_t W, uint32_t H, uint3
     static const int lv[VRT_OCT_NLEVELS] = VRT_OCT_LEVEL_LIST;
     uint8_t table[VRT_OCT_NLEVELS + 1];
     table[0] = 0;
-    for (int l = 0; l < VRT_OCT_NLEVELS; l++) table[l + 1] = (uint8_t)lv[l];
+    for (int l = 0; l < VRT_OCT_NLEVELS; l++) table[l + 1] = (uint8_t)safe_encode((uint32_t)lv[l]);
     cudaError_t e = cudaMemcpyToSymbolAsync(c_octLevels, table, sizeof(table), 0, cudaMemcpyHostToDevice, stream);
     if (e != cudaSuccess) return e;
     const uint32_t WW = (W + 31u) / 32u;
     const size_t levelWords = (size_t)WW * H * D;
-    const dim3 block(64), grid((WW + 63u) / 64u, H, D);
+    const dim3 block(32, 8), grid((WW + 31u) / 32u, (H + 7u) / 8u, D);
     oct_init_kernel<<<grid, block, 0, stream>>>(vol, scratch, W, H, WW);
     int cnt = 1;
     for (int o = 0; o < 8; o++) {

@@ -37,8 +37,12 @@ constexpr uint32_t VRT_SAFE_MAX = 127;
 //              cube of side n anchored at v (offsets 0..n-1 per axis towards o) holds no solid and no out-of-bounds voxel, hence n
 //              steps can run before the field is looked at again. What lies behind or beside the ray no longer shortens its steps
 //              (a ray LEAVING a surface gets its full budget at once). n is rounded down to a level of VRT_OCT_LEVELS.
-constexpr int VRT_OCT_NLEVELS = 24;
-#define VRT_OCT_LEVEL_LIST {1, 2, 3, 4, 5, 6, 7, 8, 10, 12, 14, 16, 20, 24, 28, 32, 40, 48, 56, 64, 80, 96, 112, 127}
+//              Byte coding of every safe-step field: 0 solid, 255 outside, 1..127 that many steps, 128..254 -> 4*code - 384
+//              steps (128, 132, .. 632): safe_decode(). Levels above 127 are multiples of 4.
+constexpr int VRT_OCT_NLEVELS = 31;
+#define VRT_OCT_LEVEL_LIST {1, 2, 3, 4, 5, 6, 7, 8, 10, 12, 14, 16, 20, 24, 28, 32, 40, 48, 56, 64, 80, 96, 112, 128, 160, 192, 256, 320, 384, 448, 512}
+VRT_HD uint32_t safe_decode(uint32_t code) { return code < 128u ? code : code * 4u - 384u; }
+VRT_HD uint32_t safe_encode(uint32_t n) { return n < 128u ? n : (n + 384u) / 4u; }
 
 struct SceneDev {
     const uint8_t* vol;               // dense u8[W*H*D], x fastest (voxel_scene.cpp:99)
@@ -109,6 +113,7 @@ struct WaveCtr {
     uint32_t chunk;       // any-hit work distribution
     uint32_t qn[6];       // bounce queue lengths per wave
     uint32_t pad[2];
+    uint32_t bcur[8];     // bounce work distribution per wave (32-ray groups are handed out dynamically: ray lengths differ by 500x)
 };
 struct WaveBuf {
     RecQ* rec;            // 3 per record

@@ -98,9 +98,12 @@ __global__ void __launch_bounds__(128) wave_bounce_kernel(const SceneDev sc, con
     const BounceEnt* __restrict__ qin = wb.bq[w & 1];
     BounceEnt* __restrict__ qout = wb.bq[(w + 1) & 1];
     const uint32_t lane = threadIdx.x & 31;
-    const uint32_t gwarp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
     unsigned rays = 0, fetches = 0;
-    for (uint32_t e0 = gwarp * 32u; e0 < n; e0 += nwarps * 32u) {
+    for (;;) {
+        uint32_t e0 = 0;
+        if (lane == 0) e0 = atomicAdd(&wb.ctr->bcur[w], 32u);
+        e0 = __shfl_sync(0xffffffffu, e0, 0);
+        if (e0 >= n) break;
         const uint32_t e = e0 + lane;
         const bool valid = e < n;
         BounceEnt ent; ent.rec = 0; ent.root = 0;
@@ -235,9 +238,9 @@ __global__ void __launch_bounds__(ENGINE_WARPS * 32) wave_anyhit_engine_kernel(c
                     uint32_t c = 0;
                     if (lane == 0) c = atomicAdd(&wb.ctr->chunk, 1u);
                     c = __shfl_sync(0xffffffffu, c, 0);
-                    const unsigned long long t0 = (unsigned long long)c * 256u;
+                    const unsigned long long t0 = (unsigned long long)c * ENGINE_CHUNK;
                     if (t0 >= total) { exhausted = true; break; }
-                    cur = t0; end = t0 + 256u < total ? t0 + 256u : total;
+                    cur = t0; end = t0 + ENGINE_CHUNK < total ? t0 + ENGINE_CHUNK : total;
                     ci = (uint32_t)(t0 / S); cq = (uint32_t)(t0 - (unsigned long long)ci * S);
                 }
                 const bool valid = cur + lane < end;
@@ -318,13 +321,16 @@ static cudaError_t launch_wave_t(const SceneDev& sc, const FrameParams& fp, cons
                                  cudaStream_t stream, uint32_t* launches, cudaEvent_t* ev) {
     cudaError_t e = cudaMemsetAsync(wb.ctr, 0, sizeof(WaveCtr), stream);
     if (e != cudaSuccess) return e;
-    static int occAny = 0, occBounce = 0;
+    static int occAny = 0, occBounce = 0, occEngine = 0;
     if (!occAny) {
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occAny, wave_anyhit_kernel<T>, 256, 0);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occBounce, wave_bounce_kernel<T>, 128, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occEngine, wave_anyhit_engine_kernel<T, 8, 32>, ENGINE_WARPS * 32, 0);
         if (occAny < 1) occAny = 1;
         if (occBounce < 1) occBounce = 1;
+        if (occEngine < 1) occEngine = 1;
     }
+    static const int farShare = getenv("VRT_ENGINE_FARSHARE") ? atoi(getenv("VRT_ENGINE_FARSHARE")) : 4;
     wave_primary_kernel<T><<<(unsigned)fp.localTiles * 8u, 128, 0, stream>>>(sc, fp, pl, wb, ctr);
     uint32_t n = 1;
     if (ev) cudaEventRecord(ev[0], stream);
@@ -334,19 +340,10 @@ static cudaError_t launch_wave_t(const SceneDev& sc, const FrameParams& fp, cons
     if (ev) cudaEventRecord(ev[1], stream);
     const uint32_t aoN = (fp.pass_mask & VRT_PASS_AO) ? fp.aoSamples : 0u;
     if (shade && (aoN || (fp.pass_mask & VRT_PASS_SHADOW))) {
-        if ((T == VRT_TRAVERSAL_LINEAR || T == VRT_TRAVERSAL_OCTANT) && engineT() > 0) {
-            static const int variant = getenv("VRT_ENGINE_VARIANT") ? atoi(getenv("VRT_ENGINE_VARIANT")) : 0;
-            auto launch = [&](auto kernel) {
-                int occ = 0;
-                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, ENGINE_WARPS * 32, 0);
-                if (occ < 1) occ = 1;
-                static const int farShare = getenv("VRT_ENGINE_FARSHARE") ? atoi(getenv("VRT_ENGINE_FARSHARE")) : 4;
-                kernel<<<(unsigned)(sms * occ), ENGINE_WARPS * 32, 0, stream>>>(sc, fp, pl, wb, ctr, (uint32_t)engineT(), (uint32_t)farShare);
-            };
-            if (variant == 1) launch(wave_anyhit_engine_kernel<T, 4, 16>);
-            else if (variant == 2) launch(wave_anyhit_engine_kernel<T, 8, 16>);
-            else launch(wave_anyhit_engine_kernel<T, 8, 32>);
-        } else wave_anyhit_kernel<T><<<(unsigned)(sms * occAny), 256, 0, stream>>>(sc, fp, pl, wb, ctr);
+        // the ray engine needs a linear safe-step field; the other back-ends keep the run-to-completion kernel (VRT_ENGINE_T=0 forces it)
+        if ((T == VRT_TRAVERSAL_LINEAR || T == VRT_TRAVERSAL_OCTANT) && engineT() > 0)
+            wave_anyhit_engine_kernel<T, 8, 32><<<(unsigned)(sms * occEngine), ENGINE_WARPS * 32, 0, stream>>>(sc, fp, pl, wb, ctr, (uint32_t)engineT(), (uint32_t)farShare);
+        else wave_anyhit_kernel<T><<<(unsigned)(sms * occAny), 256, 0, stream>>>(sc, fp, pl, wb, ctr);
         n++;
     }
     if (ev) cudaEventRecord(ev[2], stream);

@@ -92,7 +92,7 @@ VRT_HD bool wave_anyhit(const SceneDev& sc, const FrameParams& fp, V3 pos, V3 no
                         uint32_t aoN, uint32_t& fetches) {
     V3 rs, rd; uint32_t maxSteps;
     wave_anyhit_ray(sc, fp, pos, normal, px, py, depth, i, aoN, rs, rd, maxSteps);
-    const TraceRes r = trace_ray<TRAVERSAL>(sc, rs, rd, maxSteps);
+    const TraceRes r = trace_ray<TRAVERSAL>(sc, rs, rd, maxSteps, true);
     fetches = r.fetches;
     return r.material != 0;
 }
