@@ -176,6 +176,41 @@ def test_dense_and_brick_traversal_identical_at_4k(gpu_ctx):
     gs.destroy()
 
 
+def test_production_frames_early_termination(gpu_ctx):
+    """Frames without VRT_OUT_INSTRUMENT end rays as a miss as soon as the safe-step field shows no solid within reach (EARLY_ALWAYS):
+    colour and every G-buffer plane must still equal the oracle's / the instrumented frame's, on every pipeline."""
+    gs = pyvrt.VoxelScene.generate(gpu_ctx, 1, 42, 256, 192, 256)
+    noise, sky = assets.noise_standin(), assets.sky_standin(512, 256)
+    gs.set_noise(noise); gs.set_skybox(sky)
+    vol = O.generate(1, 42, 256, 192, 256)
+    sc, keep = O.make_scene(vol, synth.generator_palette(1, 42), noise, sky)
+    cam = look_at_camera(gs.bounds, (640, 360), (20.3, 150.2, 12.1), (128, 90, 128), frame=7)
+    st = O.make_settings()
+    want = O.render(sc, cam, st)
+    names = ["color", "depth", "motion", "mask", "position", "normal"]
+    for trav in (4, 5):
+        for pipe in PIPELINES:
+            rp = pyvrt.VoxelRenderPass(gpu_ctx, gs, vrt_settings(st, trav, out_mask=pyvrt.OUT_GBUFFER, pipeline=pipe))
+            fr = rp.record(cam_to_py(cam)); fr.sync()
+            got = {n: fr.download(n) for n in names}
+            stats = fr.stats(); fr.release()
+            for n in names[1:]:
+                ok, bad = bits_equal(got[n], want[n]); assert ok, (trav, pipe, n, bad)
+            assert np.array_equal(got["color"], want["color"]) or np.abs(got["color"].astype(int) - want["color"].astype(int)).max() <= 1
+            assert stats["rays"] == int(want["rays"].sum())
+            assert stats["fetches"] >= int(want["fetches"].sum())         # early-terminated rays are booked with their full budget
+    # full resolution, sharp edge: production frame == instrumented frame, byte for byte
+    big = pyvrt.VoxelScene.generate(gpu_ctx, 1, 42, 512, 256, 512)
+    big.set_noise(noise); big.set_skybox(sky)
+    cam = look_at_camera(big.bounds, (3840, 2160), (30.3, 190.2, 25.1), (256, 120, 256), frame=1)
+    a = gpu_render(gpu_ctx, big, cam, st, names=names)
+    rp = pyvrt.VoxelRenderPass(gpu_ctx, big, vrt_settings(st, 0, out_mask=pyvrt.OUT_GBUFFER))
+    fr = rp.record(cam_to_py(cam)); fr.sync()
+    for n in names:
+        ok, bad = bits_equal(a[n], fr.download(n)); assert ok, (n, bad)
+    fr.release(); gs.destroy(); big.destroy()
+
+
 def test_degenerate_rays_on_gpu(gpu_ctx):
     rng = np.random.default_rng(9)
     vol = random_volume(rng, (24, 24, 24), 0.04); pal = random_palette(rng)

@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 
 from vrtlib import (O, assets, ROOT, TRAV_BRICK, TRAV_DENSE, TRAV_FINE, ALL_TRAVERSALS, harness_render, default_camera, look_at_camera, random_volume,
-                    random_palette, assert_planes_exact, cached_vox)
+                    random_palette, assert_planes_exact, cached_vox, bits_equal)
 import pyvrt
 
 GOLD = os.path.join(ROOT, "tests", "golden")
@@ -139,3 +139,23 @@ def test_noise_constants_match_double_folding():
     g = 1.22074408460575947536
     a = np.array([1 / g, 1 / (g * g), 1 / (g * g * g)]).astype(np.float32)
     assert [float.hex(float(x)) for x in a] == ["0x1.a36a940000000p-1", "0x1.5793080000000p-1", "0x1.1972580000000p-1"]
+
+
+@pytest.mark.parametrize("trav", [4, 5])
+@pytest.mark.parametrize("wave", [False, True])
+def test_harness_production_mode_early_termination(trav, wave):
+    """Frames without VRT_OUT_INSTRUMENT let rays stop as a miss as soon as the safe-step field shows no solid within reach
+    (EARLY_ALWAYS, vrt_core.cuh): every reference output (colour + G-buffer) must still equal the oracle's."""
+    rng = np.random.default_rng(5)
+    whd = (70, 40, 55)
+    vol, pal = random_volume(rng, whd, 0.004), random_palette(rng, metallic_every=3)
+    vol[:, :6, :] = 3                                        # a floor: long unobstructed shadow / reflection / AO rays above it
+    sc, keep = _scene_std(vol, pal)
+    for pos, target in (((-30, 60, -25), (35, 5, 27)), ((35, 20, 27), (60, 0, 50)), ((200, 90, 140), (35, 10, 27))):
+        cam = look_at_camera(whd, (160, 96), pos, target, frame=4)
+        st = O.make_settings(ao=3)
+        want = O.render(sc, cam, st)
+        got = harness_render(sc, cam, st, traversal=trav, wave=wave, out_mask=1)
+        assert_planes_exact(got, want, names=["depth", "motion", "mask", "position", "normal"])
+        assert np.abs(got["color"].astype(int) - want["color"].astype(int)).max() <= 1
+        ok, bad = bits_equal(got["color_f32"], want["color_f32"]); assert ok, bad

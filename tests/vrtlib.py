@@ -88,7 +88,7 @@ def to_vrt_camera(cam: O.Camera) -> VrtCamera:
     return c
 
 
-def harness_render(scene: O.Scene, cam: O.Camera, st: O.Settings, traversal=TRAV_BRICK, rows=None, wave=False):
+def harness_render(scene: O.Scene, cam: O.Camera, st: O.Settings, traversal=TRAV_BRICK, rows=None, wave=False, out_mask=3):
     h = harness()
     hs = h.hh_scene_create(C.c_void_p(scene.volume), scene.w, scene.h, scene.d, C.c_void_p(scene.palette), C.c_void_p(scene.noise),
                            C.c_void_p(scene.sky), scene.skyW, scene.skyH)
@@ -97,7 +97,7 @@ def harness_render(scene: O.Scene, cam: O.Camera, st: O.Settings, traversal=TRAV
     for n, dt, ch in O.PLANE_SPECS:
         out[n] = np.zeros((H, W, ch) if ch > 1 else (H, W), dt)
         setattr(p, n, out[n].ctypes.data_as(C.c_void_p))
-    vs, vc = to_vrt_settings(st), to_vrt_camera(cam)
+    vs, vc = to_vrt_settings(st, out_mask=out_mask), to_vrt_camera(cam)
     rb, re, rs = rows if rows else (0, H, 1)
     fn = h.hh_render_wave if wave else h.hh_render
     rc = fn(C.c_void_p(hs), C.byref(vc), C.byref(vs), traversal, C.byref(p), rb, re, rs)
