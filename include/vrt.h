@@ -171,6 +171,12 @@ int vrt_render(vrt_context*, const vrt_scene*, const vrt_camera*, const vrt_rend
 int vrt_frame_sync(vrt_frame*);
 int vrt_frame_plane(vrt_frame*, int plane, void** device_ptr, size_t* bytes);
 int vrt_frame_download(vrt_frame*, int plane, void* host_dst, size_t bytes);
+/* Read-back that overlaps the NEXT frame (the reference keeps 2 frames in flight, source/engine/engine.hpp:19): the copy is
+ * queued on the context's copy stream behind this frame's kernels and the call returns at once; host_dst should be pinned
+ * memory and must stay untouched until vrt_frame_download_wait returns. Rendering into the same frame again waits for the
+ * copy on the device by itself, so alternate between two frames to keep the GPU busy. */
+int vrt_frame_download_async(vrt_frame*, int plane, void* host_dst, size_t bytes);
+int vrt_frame_download_wait(vrt_frame*);
 int vrt_frame_stats_get(vrt_frame*, vrt_frame_stats* out);       /* syncs */
 void vrt_frame_release(vrt_frame*);
 

@@ -211,6 +211,32 @@ def test_production_frames_early_termination(gpu_ctx):
     fr.release(); gs.destroy(); big.destroy()
 
 
+def test_two_frames_in_flight_readback(gpu_ctx):
+    """vrt_frame_download_async: frame k is read back on the copy stream while frame k+1 renders; bytes equal the blocking download."""
+    import torch
+    gs = pyvrt.VoxelScene.generate(gpu_ctx, 2, 1234, 192, 192, 192)
+    gs.set_noise(assets.noise_standin()); gs.set_skybox(assets.sky_standin(256, 128))
+    st = pyvrt.default_settings(); st.denoise.enable = 0
+    passes = [pyvrt.VoxelRenderPass(gpu_ctx, gs, st) for _ in range(2)]
+    host = [torch.empty(480 * 270 * 4, dtype=torch.uint8, pin_memory=True) for _ in range(2)]
+    cams = [cam_to_py(look_at_camera(gs.bounds, (480, 270), (-40 + 9 * k, 230, -60), (96, 96, 96), frame=k)) for k in range(6)]
+    want = []
+    for c in cams:
+        fr = passes[0].record(c); want.append(fr.download("color").copy())
+    got = []
+    for k, c in enumerate(cams):
+        fr = passes[k & 1].record(c)
+        fr.download_async("color", host[k & 1].numpy())
+        if k > 0:
+            passes[(k - 1) & 1].frame.download_wait(); got.append(host[(k - 1) & 1].numpy().reshape(270, 480, 4).copy())
+    passes[(len(cams) - 1) & 1].frame.download_wait(); got.append(host[(len(cams) - 1) & 1].numpy().reshape(270, 480, 4).copy())
+    for a, b in zip(got, want):
+        assert np.array_equal(a, b)
+    for p in passes:
+        p.frame.release()
+    gs.destroy()
+
+
 def test_degenerate_rays_on_gpu(gpu_ctx):
     rng = np.random.default_rng(9)
     vol = random_volume(rng, (24, 24, 24), 0.04); pal = random_palette(rng)

@@ -22,6 +22,7 @@ static int fail(int code, const std::string& msg) { g_err = msg; return code; }
 struct vrt_context {
     int device = 0, rank = 0, world = 1;
     cudaStream_t stream = nullptr;
+    cudaStream_t copyStream = nullptr;   // asynchronous read-backs (vrt_frame_download_async)
     cudaDeviceProp prop{};
 };
 
@@ -47,6 +48,8 @@ struct vrt_frame {
     Counters* ctr = nullptr;
     cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr;
     cudaEvent_t es[3] = {nullptr, nullptr, nullptr};   // wavefront stage boundaries
+    cudaEvent_t rendered = nullptr, copied = nullptr;  // asynchronous read-back: frame complete on the main stream / copy complete
+    bool copyPending = false;
     bool staged = false;
     bool denoised = false;
     uint32_t launches = 0, out_mask = 0;
@@ -69,6 +72,7 @@ extern "C" int vrt_context_create(int device, vrt_context** out) {
     c->device = device;
     CU(cudaGetDeviceProperties(&c->prop, device));
     CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&c->copyStream, cudaStreamNonBlocking));
     *out = c;
     return VRT_OK;
 }
@@ -76,6 +80,7 @@ extern "C" void vrt_context_destroy(vrt_context* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->copyStream) cudaStreamDestroy(c->copyStream);
     delete c;
 }
 extern "C" int vrt_context_set_shard(vrt_context* c, int rank, int world) {
@@ -313,6 +318,9 @@ extern "C" void vrt_frame_release(vrt_frame* f) {
     if (f->e1) cudaEventDestroy(f->e1);
     if (f->e2) cudaEventDestroy(f->e2);
     for (cudaEvent_t e : f->es) if (e) cudaEventDestroy(e);
+    if (f->copyPending) cudaEventSynchronize(f->copied);
+    if (f->rendered) cudaEventDestroy(f->rendered);
+    if (f->copied) cudaEventDestroy(f->copied);
     delete f;
 }
 
@@ -361,6 +369,8 @@ static int frame_create(vrt_context* c, int W, int H, vrt_frame** out) {
     if (e == cudaSuccess) e = cudaEventCreate(&f->e1);
     if (e == cudaSuccess) e = cudaEventCreate(&f->e2);
     for (int k = 0; k < 3; k++) if (e == cudaSuccess) e = cudaEventCreate(&f->es[k]);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&f->rendered, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&f->copied, cudaEventDisableTiming);
     if (e != cudaSuccess) { vrt_frame_release(f); return fail(VRT_E_CUDA, cudaGetErrorString(e)); }
     *out = f;
     return VRT_OK;
@@ -459,6 +469,7 @@ extern "C" int vrt_render(vrt_context* c, const vrt_scene* s, const vrt_camera* 
     pl.color_f32 = (float*)f->planes[VRT_PLANE_COLOR_RGB32F]; pl.rays = (uint32_t*)f->planes[VRT_PLANE_RAYS_U32];
     pl.fetches = (uint32_t*)f->planes[VRT_PLANE_FETCHES_U32];
 
+    if (f->copyPending) { CU(cudaStreamWaitEvent(c->stream, f->copied, 0)); f->copyPending = false; }   // a read-back of the previous content
     f->launches = 0; f->out_mask = out_mask; f->denoised = false;
     CU(cudaMemsetAsync(f->ctr, 0, sizeof(Counters), c->stream));
     CU(cudaEventRecord(f->e0, c->stream));
@@ -503,6 +514,27 @@ extern "C" int vrt_frame_download(vrt_frame* f, int plane, void* host_dst, size_
     CU(cudaSetDevice(f->ctx->device));
     CU(cudaMemcpyAsync(host_dst, p, n, cudaMemcpyDeviceToHost, f->ctx->stream));
     CU(cudaStreamSynchronize(f->ctx->stream));
+    return VRT_OK;
+}
+extern "C" int vrt_frame_download_async(vrt_frame* f, int plane, void* host_dst, size_t bytes) {
+    void* p = nullptr; size_t n = 0;
+    int rc = vrt_frame_plane(f, plane, &p, &n);
+    if (rc) return rc;
+    if (!host_dst || bytes != n) return fail(VRT_E_INVALID, "size mismatch");
+    vrt_context* c = f->ctx;
+    CU(cudaSetDevice(c->device));
+    CU(cudaEventRecord(f->rendered, c->stream));
+    CU(cudaStreamWaitEvent(c->copyStream, f->rendered, 0));
+    CU(cudaMemcpyAsync(host_dst, p, n, cudaMemcpyDeviceToHost, c->copyStream));
+    CU(cudaEventRecord(f->copied, c->copyStream));
+    f->copyPending = true;
+    return VRT_OK;
+}
+extern "C" int vrt_frame_download_wait(vrt_frame* f) {
+    if (!f) return fail(VRT_E_INVALID, "null frame");
+    if (!f->copyPending) return VRT_OK;
+    CU(cudaSetDevice(f->ctx->device));
+    CU(cudaEventSynchronize(f->copied));
     return VRT_OK;
 }
 extern "C" int vrt_frame_stats_get(vrt_frame* f, vrt_frame_stats* out) {

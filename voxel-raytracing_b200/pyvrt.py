@@ -230,6 +230,16 @@ class Frame:
     def sync(self):
         _ck(lib().vrt_frame_sync(self.h))
 
+    def download_async(self, name, out):
+        """Queue the read-back behind this frame's kernels on the copy stream (out: pinned uint8 buffer); pair with download_wait()."""
+        _, nbytes = self.plane_ptr(name)
+        assert out.nbytes == nbytes
+        _ck(lib().vrt_frame_download_async(self.h, PLANE_ID[name], out.ctypes.data_as(C.c_void_p), C.c_size_t(nbytes)))
+
+    def download_wait(self):
+        if self.h:
+            _ck(lib().vrt_frame_download_wait(self.h))
+
     def plane_ptr(self, name):
         p = C.c_void_p(); n = C.c_size_t()
         _ck(lib().vrt_frame_plane(self.h, PLANE_ID[name], C.byref(p), C.byref(n))); return p.value, n.value
