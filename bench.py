@@ -367,16 +367,19 @@ def run_vrt(args):
         elif copied_pending[slot]:
             ev_copied[slot].synchronize()
 
-    step_e2e(0); wait_e2e(0); step_e2e(1); wait_e2e(1)      # allocate the second frame outside the timed region
-    barrier()
-    t0 = time.perf_counter()
-    for k in range(args.steps):
-        step_e2e(k)
-        if k > 0:
-            wait_e2e((k - 1) & 1)
-    wait_e2e((args.steps - 1) & 1)
-    barrier()
-    t_e2e = time.perf_counter() - t0
+    if args.shard and world == 1:                           # debug mode: a shard is not a frame, there is nothing to read back
+        t_e2e = ms * 1e-3
+    else:
+        step_e2e(0); wait_e2e(0); step_e2e(1); wait_e2e(1)  # allocate the second frame outside the timed region
+        barrier()
+        t0 = time.perf_counter()
+        for k in range(args.steps):
+            step_e2e(k)
+            if k > 0:
+                wait_e2e((k - 1) & 1)
+        wait_e2e((args.steps - 1) & 1)
+        barrier()
+        t_e2e = time.perf_counter() - t0
 
     tot = torch.tensor([float(rays), float(fetches), float(pixels)], dtype=torch.float64, device="cuda")
     mx = torch.tensor([ms, t_e2e], dtype=torch.float64, device="cuda")

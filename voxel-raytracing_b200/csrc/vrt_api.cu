@@ -23,6 +23,7 @@ struct vrt_context {
     int device = 0, rank = 0, world = 1;
     cudaStream_t stream = nullptr;
     cudaStream_t copyStream = nullptr;   // asynchronous read-backs (vrt_frame_download_async)
+    WaveSide side{};                     // low-priority stream + fork/join events (launch_wavefront)
     cudaDeviceProp prop{};
 };
 
@@ -71,7 +72,12 @@ extern "C" int vrt_context_create(int device, vrt_context** out) {
     if (!c) return fail(VRT_E_OOM, "host allocation failed");
     c->device = device;
     CU(cudaGetDeviceProperties(&c->prop, device));
-    CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    int prLow = 0, prHigh = 0;
+    CU(cudaDeviceGetStreamPriorityRange(&prLow, &prHigh));
+    CU(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prHigh));
+    CU(cudaStreamCreateWithPriority(&c->side.stream, cudaStreamNonBlocking, prLow));
+    CU(cudaEventCreateWithFlags(&c->side.fork, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&c->side.join, cudaEventDisableTiming));
     CU(cudaStreamCreateWithFlags(&c->copyStream, cudaStreamNonBlocking));
     *out = c;
     return VRT_OK;
@@ -81,6 +87,9 @@ extern "C" void vrt_context_destroy(vrt_context* c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamDestroy(c->stream);
     if (c->copyStream) cudaStreamDestroy(c->copyStream);
+    if (c->side.stream) cudaStreamDestroy(c->side.stream);
+    if (c->side.fork) cudaEventDestroy(c->side.fork);
+    if (c->side.join) cudaEventDestroy(c->side.join);
     delete c;
 }
 extern "C" int vrt_context_set_shard(vrt_context* c, int rank, int world) {
@@ -475,7 +484,7 @@ extern "C" int vrt_render(vrt_context* c, const vrt_scene* s, const vrt_camera* 
     CU(cudaEventRecord(f->e0, c->stream));
     cudaError_t e;
     f->staged = wavefront && f->localTiles > 0;
-    if (wavefront) e = launch_wavefront(sc, fp, pl, f->ctr, f->wb, c->prop.multiProcessorCount, c->stream, &f->launches, f->es);
+    if (wavefront) e = launch_wavefront(sc, fp, pl, f->ctr, f->wb, c->prop.multiProcessorCount, c->stream, &c->side, &f->launches, f->es);
     else { e = launch_render(sc, fp, pl, f->ctr, c->stream); f->launches++; }
     if (e != cudaSuccess) { if (!*frame) vrt_frame_release(f); return fail(VRT_E_CUDA, cudaGetErrorString(e)); }
     CU(cudaEventRecord(f->e1, c->stream));

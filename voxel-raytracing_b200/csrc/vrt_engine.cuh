@@ -21,6 +21,7 @@ namespace vrt {
 
 constexpr int ENGINE_WARPS = 8;          // warps per block
 constexpr uint32_t ENGINE_CHUNK = 64;    // rays per claim of the global work counter (small: the tail of a sharded frame is short)
+constexpr uint32_t ENGINE_BLOCK_QUOTA = ENGINE_WARPS * 256u;   // rays per block when the kernel runs as many short-lived blocks
 constexpr int ENGINE_STASH = 64;         // prepared rays per warp (a refill asks for <= 32 more while < 32 are left)
 constexpr int ENGINE_NEAR_STEPS = 4;
 constexpr int ENGINE_FAR_STEPS = 16;

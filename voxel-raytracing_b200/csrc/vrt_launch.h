@@ -8,8 +8,12 @@ namespace vrt {
 // voxel_volume pass (vrt_render.cu)
 cudaError_t launch_render(const SceneDev& sc, const FrameParams& fp, const PlanesDev& pl, Counters* ctr, cudaStream_t stream);
 // the same pass as ray waves over compact hit records (vrt_wave.cu); `sms` sizes the persistent grids
+// `side` (may be null): a low-priority stream + two untimed events. The AO / shadow rays of the PRIMARY hits do not depend on the
+// reflection waves, so they run beside them as many short-lived blocks that fill the latency-bound tails of those launches.
+struct WaveSide { cudaStream_t stream; cudaEvent_t fork, join; };
 cudaError_t launch_wavefront(const SceneDev& sc, const FrameParams& fp, const PlanesDev& pl, Counters* ctr, const WaveBuf& wb, int sms,
-                             cudaStream_t stream, uint32_t* launches, cudaEvent_t* stageEvents /* 3: after primary, bounces, any-hit; or null */);
+                             cudaStream_t stream, const WaveSide* side, uint32_t* launches,
+                             cudaEvent_t* stageEvents /* 3: after primary, bounces, any-hit; or null */);
 cudaError_t launch_detile(const void* src, void* dst, int W, int H, int world, size_t rankStridePixels, int bpp, cudaStream_t stream);
 
 // brick acceleration build (vrt_accel.cu): bmask + bdist from the dense volume; tmpA/tmpB are scratch of Bx*By*Bz bytes

@@ -191,14 +191,23 @@ __global__ void __launch_bounds__(256) wave_anyhit_kernel(const SceneDev sc, con
 // ---- any-hit wave on the ray engine (vrt_engine.cuh): LINEAR (isotropic field) or OCTANT (directional fields) ----
 template <int TRAVERSAL, int NEAR_STEPS, int FAR_STEPS>
 __global__ void __launch_bounds__(ENGINE_WARPS * 32) wave_anyhit_engine_kernel(const SceneDev sc, const FrameParams fp, const PlanesDev pl, const WaveBuf wb,
-                                                                                Counters* __restrict__ ctr, const uint32_t refillT, const uint32_t farShare) {
+                                                                                Counters* __restrict__ ctr, const uint32_t refillT, const uint32_t farShare, const int part) {
     __shared__ EngineStash stashAll[ENGINE_WARPS];
+    __shared__ uint32_t blockChunk;
     EngineStash& st = stashAll[threadIdx.x >> 5];
     const uint32_t lane = threadIdx.x & 31, ltMask = (1u << lane) - 1u;
-    const uint32_t n0 = wb.ctr->n0, S = n0 + wb.ctr->nsq;
+    // part 0: the rays of every shaded record, persistent grid, chunks from a global counter
+    // part 1: the rays of the primary-hit records only, short-lived blocks: block b owns items [b, b+1) * ENGINE_BLOCK_QUOTA
+    // part 2: the rays of the queued bounce records only, persistent grid
+    const uint32_t n0 = wb.ctr->n0, qBase = part == 2 ? n0 : 0u, S = part == 1 ? n0 : (part == 2 ? wb.ctr->nsq : n0 + wb.ctr->nsq);
     const uint32_t aoN = (fp.pass_mask & VRT_PASS_AO) ? fp.aoSamples : 0u;
     const uint32_t R = aoN + ((fp.pass_mask & VRT_PASS_SHADOW) ? 1u : 0u);
     const unsigned long long total = (unsigned long long)S * R;
+    if (part == 1) {
+        if ((unsigned long long)blockIdx.x * ENGINE_BLOCK_QUOTA >= total) return;     // the grid is sized for the worst case
+        if (threadIdx.x == 0) blockChunk = 0;
+        __syncthreads();
+    }
     const int LW = (int)sc.W + 2, LWH = LW * ((int)sc.H + 2);
     const bool instrument = (fp.out_mask & VRT_OUT_INSTRUMENT) != 0;
 
@@ -236,9 +245,10 @@ __global__ void __launch_bounds__(ENGINE_WARPS * 32) wave_anyhit_engine_kernel(c
             while (stashN < nIdle && !exhausted) {
                 if (cur >= end) {
                     uint32_t c = 0;
-                    if (lane == 0) c = atomicAdd(&wb.ctr->chunk, 1u);
+                    if (lane == 0) c = part == 1 ? atomicAdd(&blockChunk, 1u) : atomicAdd(part == 2 ? &wb.ctr->pad[0] : &wb.ctr->chunk, 1u);
                     c = __shfl_sync(0xffffffffu, c, 0);
-                    const unsigned long long t0 = (unsigned long long)c * ENGINE_CHUNK;
+                    if (part == 1 && c >= ENGINE_BLOCK_QUOTA / ENGINE_CHUNK) { exhausted = true; break; }
+                    const unsigned long long t0 = (unsigned long long)c * ENGINE_CHUNK + (part == 1 ? (unsigned long long)blockIdx.x * ENGINE_BLOCK_QUOTA : 0ull);
                     if (t0 >= total) { exhausted = true; break; }
                     cur = t0; end = t0 + ENGINE_CHUNK < total ? t0 + ENGINE_CHUNK : total;
                     ci = (uint32_t)(t0 / S); cq = (uint32_t)(t0 - (unsigned long long)ci * S);
@@ -250,7 +260,7 @@ __global__ void __launch_bounds__(ENGINE_WARPS * 32) wave_anyhit_engine_kernel(c
                 if (valid) {
                     unsigned long long qq = (unsigned long long)cq + lane;
                     while (qq >= S) { qq -= S; i++; }
-                    const uint32_t q = (uint32_t)qq;
+                    const uint32_t q = qBase + (uint32_t)qq;
                     nIdx = q < n0 ? q : wb.sq[q - n0];
                     const RecQ r0 = wb.rec[3 * (size_t)nIdx], r1 = wb.rec[3 * (size_t)nIdx + 1];
                     V3 rs, rd, pos; uint32_t maxSteps; Dda s;
@@ -318,7 +328,7 @@ static int engineT() {
 
 template <int T>
 static cudaError_t launch_wave_t(const SceneDev& sc, const FrameParams& fp, const PlanesDev& pl, Counters* ctr, const WaveBuf& wb, int sms,
-                                 cudaStream_t stream, uint32_t* launches, cudaEvent_t* ev) {
+                                 cudaStream_t stream, const WaveSide* side, uint32_t* launches, cudaEvent_t* ev) {
     cudaError_t e = cudaMemsetAsync(wb.ctr, 0, sizeof(WaveCtr), stream);
     if (e != cudaSuccess) return e;
     static int occAny = 0, occBounce = 0, occEngine = 0;
@@ -331,20 +341,39 @@ static cudaError_t launch_wave_t(const SceneDev& sc, const FrameParams& fp, cons
         if (occEngine < 1) occEngine = 1;
     }
     static const int farShare = getenv("VRT_ENGINE_FARSHARE") ? atoi(getenv("VRT_ENGINE_FARSHARE")) : 4;
+    // measured (profiles/r1_overlap.log): beside-the-waves scheduling pays when the frame (or this rank's shard of it) is small and
+    // the launches are tail-bound (1/8 of a 4K frame: -12 %), and costs ~1 % on a full 4K frame. VRT_OVERLAP=0/1 overrides.
+    static const int overlapEnv = getenv("VRT_OVERLAP") ? atoi(getenv("VRT_OVERLAP")) : -1;
+    const bool smallFrame = (size_t)fp.localTiles * (VRT_TILE * VRT_TILE) <= (size_t)1 << 21;
     wave_primary_kernel<T><<<(unsigned)fp.localTiles * 8u, 128, 0, stream>>>(sc, fp, pl, wb, ctr);
     uint32_t n = 1;
     if (ev) cudaEventRecord(ev[0], stream);
     const bool shade = (fp.pass_mask & VRT_PASS_SHADE) != 0;
-    if (shade && (fp.pass_mask & VRT_PASS_REFLECT))
+    const bool reflect = shade && (fp.pass_mask & VRT_PASS_REFLECT);
+    const uint32_t aoN = (fp.pass_mask & VRT_PASS_AO) ? fp.aoSamples : 0u;
+    const uint32_t R = aoN + ((fp.pass_mask & VRT_PASS_SHADOW) ? 1u : 0u);
+    const bool anyhit = shade && R;
+    // the ray engine needs a linear safe-step field; the other back-ends keep the run-to-completion kernel (VRT_ENGINE_T=0 forces it)
+    const bool engine = (T == VRT_TRAVERSAL_LINEAR || T == VRT_TRAVERSAL_OCTANT) && engineT() > 0;
+    const bool overlap = anyhit && reflect && engine && side && (overlapEnv < 0 ? smallFrame : overlapEnv != 0);
+    auto launch_engine = [&](cudaStream_t s, int part, unsigned grid) {
+        wave_anyhit_engine_kernel<T, 8, 32><<<grid, ENGINE_WARPS * 32, 0, s>>>(sc, fp, pl, wb, ctr, (uint32_t)engineT(), (uint32_t)farShare, part);
+        n++;
+    };
+    if (overlap) {
+        const unsigned long long worst = (unsigned long long)fp.localTiles * (VRT_TILE * VRT_TILE) * R;       // every pixel a hit
+        cudaEventRecord(side->fork, stream);
+        cudaStreamWaitEvent(side->stream, side->fork, 0);
+        launch_engine(side->stream, 1, (unsigned)((worst + ENGINE_BLOCK_QUOTA - 1) / ENGINE_BLOCK_QUOTA));
+        cudaEventRecord(side->join, side->stream);
+    }
+    if (reflect)
         for (int w = 0; w < MAX_REFLECTIONS; w++) { wave_bounce_kernel<T><<<(unsigned)(sms * occBounce), 128, 0, stream>>>(sc, fp, pl, wb, ctr, w); n++; }
     if (ev) cudaEventRecord(ev[1], stream);
-    const uint32_t aoN = (fp.pass_mask & VRT_PASS_AO) ? fp.aoSamples : 0u;
-    if (shade && (aoN || (fp.pass_mask & VRT_PASS_SHADOW))) {
-        // the ray engine needs a linear safe-step field; the other back-ends keep the run-to-completion kernel (VRT_ENGINE_T=0 forces it)
-        if ((T == VRT_TRAVERSAL_LINEAR || T == VRT_TRAVERSAL_OCTANT) && engineT() > 0)
-            wave_anyhit_engine_kernel<T, 8, 32><<<(unsigned)(sms * occEngine), ENGINE_WARPS * 32, 0, stream>>>(sc, fp, pl, wb, ctr, (uint32_t)engineT(), (uint32_t)farShare);
-        else wave_anyhit_kernel<T><<<(unsigned)(sms * occAny), 256, 0, stream>>>(sc, fp, pl, wb, ctr);
-        n++;
+    if (anyhit) {
+        if (overlap) { launch_engine(stream, 2, (unsigned)(sms * occEngine)); cudaStreamWaitEvent(stream, side->join, 0); }
+        else if (engine) launch_engine(stream, 0, (unsigned)(sms * occEngine));
+        else { wave_anyhit_kernel<T><<<(unsigned)(sms * occAny), 256, 0, stream>>>(sc, fp, pl, wb, ctr); n++; }
     }
     if (ev) cudaEventRecord(ev[2], stream);
     if (shade) { wave_resolve_kernel<<<(unsigned)(sms * 8), 256, 0, stream>>>(sc, fp, pl, wb); n++; }
@@ -353,13 +382,13 @@ static cudaError_t launch_wave_t(const SceneDev& sc, const FrameParams& fp, cons
 }
 
 cudaError_t launch_wavefront(const SceneDev& sc, const FrameParams& fp, const PlanesDev& pl, Counters* ctr, const WaveBuf& wb, int sms,
-                             cudaStream_t stream, uint32_t* launches, cudaEvent_t* ev) {
+                             cudaStream_t stream, const WaveSide* side, uint32_t* launches, cudaEvent_t* ev) {
     if (fp.localTiles <= 0) return cudaSuccess;
-    if (fp.traversal == VRT_TRAVERSAL_DENSE_U8) return launch_wave_t<VRT_TRAVERSAL_DENSE_U8>(sc, fp, pl, ctr, wb, sms, stream, launches, ev);
-    if (fp.traversal == VRT_TRAVERSAL_FINE) return launch_wave_t<VRT_TRAVERSAL_FINE>(sc, fp, pl, ctr, wb, sms, stream, launches, ev);
-    if (fp.traversal == VRT_TRAVERSAL_LINEAR) return launch_wave_t<VRT_TRAVERSAL_LINEAR>(sc, fp, pl, ctr, wb, sms, stream, launches, ev);
-    if (fp.traversal == VRT_TRAVERSAL_OCTANT) return launch_wave_t<VRT_TRAVERSAL_OCTANT>(sc, fp, pl, ctr, wb, sms, stream, launches, ev);
-    return launch_wave_t<VRT_TRAVERSAL_BRICK>(sc, fp, pl, ctr, wb, sms, stream, launches, ev);
+    if (fp.traversal == VRT_TRAVERSAL_DENSE_U8) return launch_wave_t<VRT_TRAVERSAL_DENSE_U8>(sc, fp, pl, ctr, wb, sms, stream, side, launches, ev);
+    if (fp.traversal == VRT_TRAVERSAL_FINE) return launch_wave_t<VRT_TRAVERSAL_FINE>(sc, fp, pl, ctr, wb, sms, stream, side, launches, ev);
+    if (fp.traversal == VRT_TRAVERSAL_LINEAR) return launch_wave_t<VRT_TRAVERSAL_LINEAR>(sc, fp, pl, ctr, wb, sms, stream, side, launches, ev);
+    if (fp.traversal == VRT_TRAVERSAL_OCTANT) return launch_wave_t<VRT_TRAVERSAL_OCTANT>(sc, fp, pl, ctr, wb, sms, stream, side, launches, ev);
+    return launch_wave_t<VRT_TRAVERSAL_BRICK>(sc, fp, pl, ctr, wb, sms, stream, side, launches, ev);
 }
 
 }  // namespace vrt
