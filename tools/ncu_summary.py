@@ -1,23 +1,54 @@
-"""Print the key counters of every kernel in an .ncu-rep: usage: ncu_summary.py file.ncu-rep"""
-import csv, subprocess, sys
+"""Summarise an .ncu-rep for profiles/: per kernel launch the counters BASELINE.json asks for (L2 hit rate, achieved L2 / HBM GB/s,
+warp execution efficiency, issue-slot utilisation) plus occupancy, stall reasons and DRAM traffic.
+usage: ncu_summary.py file.ncu-rep [--json traffic.json]"""
+import csv, json, subprocess, sys
+
 out = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
-h = rows[0]
-keys = [("Kernel Name", "kernel"), ("gpu__time_duration.sum", "ms"), ("smsp__inst_executed.sum", "warp_inst"),
-        ("smsp__issue_active.avg.pct_of_peak_sustained_active", "issue%"), ("sm__warps_active.avg.pct_of_peak_sustained_active", "occ%"),
-        ("smsp__thread_inst_executed_per_inst_executed.ratio", "lanes"), ("l1tex__t_sector_hit_rate.pct", "L1hit%"),
-        ("lts__t_sector_hit_rate.pct", "L2hit%"), ("dram__bytes_read.sum", "dramR"), ("dram__bytes_write.sum", "dramW"),
-        ("lts__t_sectors_op_read.sum", "L2rdSect"), ("l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum", "L1ldSect"),
-        ("launch__registers_per_thread", "regs"),
-        ("smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio", "st_long"),
-        ("smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio", "st_short"),
-        ("smsp__average_warps_issue_stalled_wait_per_issue_active.ratio", "st_wait"),
-        ("smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio", "st_notsel"),
-        ("smsp__average_warps_issue_stalled_branch_resolving_per_issue_active.ratio", "st_branch"),
-        ("smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio", "st_bar"),
-        ("smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio", "st_math"),
-        ("smsp__average_warps_issue_stalled_no_instruction_per_issue_active.ratio", "st_noinst"),
-        ("smsp__average_warps_issue_stalled_lg_throttle_per_issue_active.ratio", "st_lg"),
-        ("smsp__average_warps_issue_stalled_dispatch_stall_per_issue_active.ratio", "st_disp")]
+h, units = rows[0], rows[1]
+SCALE = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12, "ns": 1e-9, "us": 1e-6, "ms": 1e-3, "s": 1.0, "usecond": 1e-6, "msecond": 1e-3, "nsecond": 1e-9, "second": 1.0,
+         "byte/second": 1, "Kbyte/second": 1e3, "Mbyte/second": 1e6, "Gbyte/second": 1e9, "Tbyte/second": 1e12}
+
+
+def val(r, k):
+    if k not in h:
+        return None
+    i = h.index(k)
+    try:
+        v = float(r[i].replace(",", ""))
+    except ValueError:
+        return None
+    return v * SCALE.get(units[i], 1)
+
+
+per = {}
 for r in rows[2:]:
-    print(" ".join(f"{n}={r[h.index(k)][:44]}" for k, n in keys if k in h))
+    name = r[h.index("Kernel Name")].split("(")[0].replace("void ", "")
+    t = val(r, "gpu__time_duration.sum")
+    d = dict(
+        ms=t * 1e3, warp_inst=val(r, "smsp__inst_executed.sum"),
+        issue_active_pct=val(r, "smsp__issue_active.avg.pct_of_peak_sustained_active"),
+        occupancy_pct=val(r, "sm__warps_active.avg.pct_of_peak_sustained_active"),
+        active_lanes=val(r, "smsp__thread_inst_executed_per_inst_executed.ratio"),
+        l1_hit_pct=val(r, "l1tex__t_sector_hit_rate.pct"), l2_hit_pct=val(r, "lts__t_sector_hit_rate.pct"),
+        l2_gbs=(val(r, "lts__t_sectors.sum") or 0) * 32 / t / 1e9, l2_throughput_pct=val(r, "lts__throughput.avg.pct_of_peak_sustained_elapsed"),
+        l1_gbs=(val(r, "l1tex__t_bytes_pipe_lsu_mem_global_op_ldgsts_cache_access.sum") or 0) / t / 1e9,
+        dram_read_bytes=val(r, "dram__bytes_read.sum"), dram_write_bytes=val(r, "dram__bytes_write.sum"),
+        dram_gbs=((val(r, "dram__bytes_read.sum") or 0) + (val(r, "dram__bytes_write.sum") or 0)) / t / 1e9,
+        regs=val(r, "launch__registers_per_thread"),
+        stall_long_scoreboard=val(r, "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio"),
+        stall_wait=val(r, "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio"),
+        stall_not_selected=val(r, "smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio"),
+        stall_math_throttle=val(r, "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio"),
+        stall_branch=val(r, "smsp__average_warps_issue_stalled_branch_resolving_per_issue_active.ratio"))
+    per.setdefault(name, []).append(d)
+    print(name)
+    print("   " + "  ".join(f"{k}={v:.4g}" if isinstance(v, float) else f"{k}={v}" for k, v in d.items()))
+if "--json" in sys.argv:
+    # per-launch DRAM traffic of each kernel (mean over the captured launches; reflection waves: the first = largest wave)
+    tr = {}
+    for name, ds in per.items():
+        key = name.split("<")[0]
+        big = ds if "bounce" not in key else ds[:1]
+        tr[key + "_dram_bytes_per_launch"] = sum((d["dram_read_bytes"] or 0) + (d["dram_write_bytes"] or 0) for d in big) / len(big)
+    json.dump(tr, open(sys.argv[sys.argv.index("--json") + 1], "w"), indent=1)

@@ -190,11 +190,12 @@ VRT_HD int lin_begin(const SceneDev& sc, const uint8_t* field, const Dda& s, V3 
     return LIN_CONTINUE;
 }
 // One look-up and the steps it allows. STEP_REC: keep the mask of the last step (needed for the hit normal).
-// ANYHIT: the caller only wants to know whether the ray hits (traceRayHit :198-202). Once the field grants at least as many
-// steps as the ray has left, the loop of traceRayInt provably runs out of steps over empty in-bounds voxels (maxSteps getVoxel
-// calls, no hit): the remaining steps need not be executed because their only product, the DDA state, is discarded.
+// ANYHIT: the caller does not use the DDA state of a ray that misses (traceRayHit :198-202 returns a bool; traceRay :180-195 fills
+// RayHit only on a hit). Once the field grants at least as many steps as the ray has left, the loop of traceRayInt provably runs
+// out of steps over empty in-bounds voxels (exactly maxSteps getVoxel calls, no hit): the remaining steps need not be executed
+// because their only product, the DDA state, is discarded. Primary rays never use this (their exit state is instrumented).
 template <bool STEP_REC>
-VRT_HD int lin_round(const SceneDev& sc, LinRay& r, const bool ANYHIT = false) {
+VRT_HD int lin_round(const SceneDev& sc, LinRay& r, const bool ANYHIT = false, const uint32_t roundCap = 512u) {
     const int bx = lin_bits(r.sx, r.sx0, r.ax), by = lin_bits(r.sy, r.sy0, r.ay), bz = lin_bits(r.sz, r.sz0, r.az);
     const int t = (int)((uint32_t)bx * (uint32_t)r.SX + (uint32_t)by * (uint32_t)r.SY + (uint32_t)r.T0);   // cx*SX + cy*SY
     const long long off = (long long)(bz - VRT_LIN_MAGIC_BITS) * (long long)r.SZ + (long long)t;
@@ -210,6 +211,7 @@ VRT_HD int lin_round(const SceneDev& sc, LinRay& r, const bool ANYHIT = false) {
     const uint32_t left = r.maxSteps - r.i;
     if (ANYHIT && n >= left) { r.i = r.maxSteps; return LIN_EXHAUSTED; }
     n = n < left ? n : left;
+    n = n < roundCap ? n : roundCap;
     r.i += n;
     Dda d; d.sx = r.sx; d.sy = r.sy; d.sz = r.sz; d.dx = r.dx; d.dy = r.dy; d.dz = r.dz;
     for (uint32_t k = n - 1; k > 0; k--) dda_step_f(d);
@@ -241,8 +243,9 @@ VRT_HD bool dda_begin(const SceneDev& sc, V3 start, V3 dir, V3& pos, Dda& s) {
 // LINEAR additionally needs a finite start (see trace_ray)
 VRT_HD bool lin_usable(bool fast, const Dda& s) { return fast && finitef(s.sx) && finitef(s.sy) && finitef(s.sz); }
 
+constexpr uint32_t ROUND_CAP_PRIMARY = 128u, ROUND_CAP_SECONDARY = 32u;   // profiles/r1_round_cap.log
 template <int TRAVERSAL>
-VRT_HD TraceRes trace_ray(const SceneDev& sc, V3 start, V3 dir, uint32_t maxSteps, const bool anyhit = false) {
+VRT_HD TraceRes trace_ray(const SceneDev& sc, V3 start, V3 dir, uint32_t maxSteps, const bool anyhit = false, const uint32_t roundCap = ROUND_CAP_PRIMARY) {
     TraceRes r;
     V3 pos;
     Dda s;
@@ -270,7 +273,7 @@ VRT_HD TraceRes trace_ray(const SceneDev& sc, V3 start, V3 dir, uint32_t maxStep
     } else if (TRAVERSAL == VRT_TRAVERSAL_LINEAR || TRAVERSAL == VRT_TRAVERSAL_OCTANT) {
         LinRay lr;
         int st = lin_begin(sc, TRAVERSAL == VRT_TRAVERSAL_OCTANT ? octant_field(sc, s) : sc.ldist, s, dir, maxSteps, lr);
-        while (st == LIN_CONTINUE) st = lin_round<true>(sc, lr, anyhit);
+        while (st == LIN_CONTINUE) st = lin_round<true>(sc, lr, anyhit, roundCap);
         lin_map_pos(lr, s.mx, s.my, s.mz);
         s.sx = lr.sx; s.sy = lr.sy; s.sz = lr.sz;
         i = lr.i; mask = lr.mask;

@@ -84,7 +84,7 @@ VRT_HD void render_pixel(const SceneDev& sc, const FrameParams& fp, int px, int 
     o.rays = 0; o.fetches = 0;
 
     for (;;) {
-        const TraceRes r = trace_ray<TRAVERSAL>(sc, rs, rd, maxSteps, phase == PH_AO || phase == PH_SHADOW);   // the only call site
+        const TraceRes r = trace_ray<TRAVERSAL>(sc, rs, rd, maxSteps, phase != PH_PRIMARY, phase != PH_PRIMARY ? ROUND_CAP_SECONDARY : ROUND_CAP_PRIMARY);   // the only call site
         o.rays++; o.fetches += r.fetches;
         bool done = false, need_ray = false;
 

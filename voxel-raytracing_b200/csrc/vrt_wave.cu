@@ -190,7 +190,7 @@ __global__ void __launch_bounds__(256) wave_anyhit_kernel(const SceneDev sc, con
 
 // ---- any-hit wave on the ray engine (vrt_engine.cuh): LINEAR (isotropic field) or OCTANT (directional fields) ----
 template <int TRAVERSAL, int NEAR_STEPS, int FAR_STEPS>
-__global__ void __launch_bounds__(ENGINE_WARPS * 32) wave_anyhit_engine_kernel(const SceneDev sc, const FrameParams fp, const PlanesDev pl, const WaveBuf wb,
+__global__ void __launch_bounds__(ENGINE_WARPS * 32, 4) wave_anyhit_engine_kernel(const SceneDev sc, const FrameParams fp, const PlanesDev pl, const WaveBuf wb,
                                                                                 Counters* __restrict__ ctr, const uint32_t refillT, const uint32_t farShare, const int part) {
     __shared__ EngineStash stashAll[ENGINE_WARPS];
     __shared__ uint32_t blockChunk;

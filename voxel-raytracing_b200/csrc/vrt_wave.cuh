@@ -73,7 +73,7 @@ template <int TRAVERSAL>
 VRT_HD TraceRes wave_bounce(const SceneDev& sc, V3 pos, V3 normal, V3 dir, V3& rd) {
     rd = reflect3(dir, normal);
     const V3 rs = pos + normal * 0.01f;
-    return trace_ray<TRAVERSAL>(sc, rs, rd, MAX_RAY_STEPS);
+    return trace_ray<TRAVERSAL>(sc, rs, rd, MAX_RAY_STEPS, true, ROUND_CAP_SECONDARY);   // a miss carries no state (traceRay :180-195): see lin_round ANYHIT
 }
 
 // ray i of a shaded hit: i < aoN -> AO ray i (:214-223, 64 steps), i == aoN -> shadow ray (:230-233, 512 steps)
@@ -92,7 +92,7 @@ VRT_HD bool wave_anyhit(const SceneDev& sc, const FrameParams& fp, V3 pos, V3 no
                         uint32_t aoN, uint32_t& fetches) {
     V3 rs, rd; uint32_t maxSteps;
     wave_anyhit_ray(sc, fp, pos, normal, px, py, depth, i, aoN, rs, rd, maxSteps);
-    const TraceRes r = trace_ray<TRAVERSAL>(sc, rs, rd, maxSteps, true);
+    const TraceRes r = trace_ray<TRAVERSAL>(sc, rs, rd, maxSteps, true, ROUND_CAP_SECONDARY);
     fetches = r.fetches;
     return r.material != 0;
 }
