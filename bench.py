@@ -108,6 +108,19 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def l2_block(primary_alg_bytes, primary_ms):
+    """BASELINE's target is quoted against the L2 roofline for PRIMARY rays: algorithmic bytes of the primary kernel (1 B per reference
+    getVoxel call + its per-pixel outputs) / its CUDA-event time, against the L2 read bandwidth measured by tools/l2peak.cu."""
+    p = os.path.join(ROOT, "profiles", "r1_l2_peak.json")
+    try:
+        peak = float(json.load(open(p))["l2_read_gbs"])
+    except Exception:
+        return None
+    ach = primary_alg_bytes / (primary_ms * 1e-3) / 1e9 if primary_ms > 0 else 0.0
+    return {"kernel": "wave_primary_kernel", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+            "peak_source": "measured (tools/l2peak.cu, 64 MiB read-only stream, profiles/r1_l2_peak.json)"}
+
+
 def ncu_traffic(kernel="render_kernel"):
     """Per-launch DRAM traffic of the dominant kernel from the committed ncu summary, if one exists."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
@@ -395,7 +408,9 @@ def run_vrt(args):
         k_ms = float(np.mean(ms_kernel))
         # dominant kernel of the pass: per-stage CUDA-event times and per-stage getVoxel counts from the library
         stage_ms = np.mean(np.array(ms_stage), axis=0)
-        names = ["wave_primary_kernel", "wave_bounce_kernel (x5)", "wave_anyhit_kernel", "wave_resolve_kernel"] if args.pipeline != 1 else ["render_kernel"] * 4
+        engine = args.traversal in (0, 4, 5) and os.environ.get("VRT_ENGINE_T", "8") != "0"
+        names = ["wave_primary_kernel", "wave_bounce_kernel (x5)", "wave_anyhit_engine_kernel" if engine else "wave_anyhit_kernel",
+                 "wave_resolve_kernel"] if args.pipeline != 1 else ["render_kernel"] * 4
         dom = int(np.argmax(stage_ms[:3]))
         # algorithmic bytes of that kernel: 1 B per reference getVoxel call + its outputs
         # (primary: colour + G-buffer per pixel; bounce: nothing the reference stores; any-hit: the 1-byte hit flag per ray)
@@ -413,6 +428,7 @@ def run_vrt(args):
                              "kernel": names[dom], "kernel_ms": dom_ms, "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
                              "frame": {"achieved": frame_bytes_alg / (k_ms * 1e-3) / 1e9, "frac": frame_bytes_alg / (k_ms * 1e-3) / 1e9 / peak,
                                        "algorithmic_bytes": frame_bytes_alg, "ms": k_ms},
+                             "l2": l2_block(float(stage_fetches[0]) / args.steps + pixels / args.steps * b_out, float(stage_ms[0])),
                              "stages_ms": {"primary": float(stage_ms[0]), "bounce": float(stage_ms[1]), "anyhit": float(stage_ms[2]), "resolve": float(stage_ms[3])},
                              "stages_Mrays": {"primary": float(stage_rays[0] / args.steps / 1e6), "bounce": float(stage_rays[1] / args.steps / 1e6), "anyhit": float(stage_rays[2] / args.steps / 1e6)},
                              "stages_Gvisits": {"primary": float(stage_fetches[0] / args.steps / 1e9), "bounce": float(stage_fetches[1] / args.steps / 1e9), "anyhit": float(stage_fetches[2] / args.steps / 1e9)},
