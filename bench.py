@@ -262,117 +262,77 @@ def run_vrt(args):
     st = configs.settings_for(cfg, gbuffer=not args.no_gbuffer)
     st.traversal = args.traversal
     st.pipeline = args.pipeline
-    rp = pyvrt.VoxelRenderPass(ctx, scene, st)
-    ext = torch.cuda.ExternalStream(ctx.stream, device=torch.device("cuda", local))
+    # Two frames in flight (as in the reference, source/engine/engine.hpp:19): two render passes used alternately.
+    rp, rp2 = pyvrt.VoxelRenderPass(ctx, scene, st), pyvrt.VoxelRenderPass(ctx, scene, st)
+    passes = (rp, rp2)
+    dev = torch.device("cuda", local)
+    ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
     final = "denoised" if cfg["denoise"] and world == 1 else "color"
     frame_bytes = W * H * 4
-    host_frame = torch.empty(frame_bytes, dtype=torch.uint8, pin_memory=True) if rank == 0 else None
-    gathered = assembled = None
-    if world > 1 and rank == 0:
-        assembled = torch.empty(frame_bytes, dtype=torch.uint8, device="cuda")
-
-    def step(k, download=False):
-        """One frame: render this rank's tiles; N>1: gather the colour shards on rank 0 and assemble the frame."""
-        nonlocal gathered
-        cam = configs.make_camera(args.config, bounds, size, k)
-        fr = rp.record(cam)
-        launches = 0      # launches outside vrt_render (the library counts its own: vrt_frame_stats.kernel_launches)
-        if world > 1:
-            ptr, n = fr.plane_ptr("color")
-            shard = torch.as_tensor(_DevBuf(ptr, n), device=torch.device("cuda", local))
-            with torch.cuda.stream(ext):
-                if rank == 0:
-                    if gathered is None:
-                        gathered = torch.empty((world, n), dtype=torch.uint8, device="cuda")
-                    dist.gather(shard, list(gathered.unbind(0)), dst=0)
-                    pyvrt.assemble(ctx, gathered.data_ptr(), world, size, "color", assembled.data_ptr())
-                    launches += 1
-                else:
-                    dist.gather(shard, None, dst=0)
-        if download and rank == 0:
-            if world > 1:
-                with torch.cuda.stream(ext):
-                    host_frame.copy_(assembled, non_blocking=True)
-                ctx.sync()
-            else:
-                fr.download(final, out=host_frame.numpy())
-        return fr, launches
-
-    def barrier():
-        ctx.sync(); torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-
-    # ---- warm-up, then an untimed counting pass over the K timed poses (rays / voxel visits / kernel time per frame)
-    for k in range(args.warmup):
-        step(k)
-    barrier()
-    rays = fetches = pixels = lib_launches = 0
-    ms_kernel, ms_stage = [], []
-    stage_rays, stage_fetches = np.zeros(3), np.zeros(3)
-    for k in range(args.steps):
-        fr, _ = step(k)
-        s = fr.stats()
-        rays += s["rays"]; fetches += s["fetches"]; pixels += s["pixels"]; ms_kernel.append(s["ms_trace"] + s["ms_denoise"])
-        ms_stage.append(s["ms_stage"]); stage_rays += s["stage_rays"]; stage_fetches += s["stage_fetches"]
-        lib_launches += s["kernel_launches"]
-    barrier()
-
-    # ---- timed region 1: K frames, inputs resident, device time on the launching stream, max over ranks
-    sampler = ClockSampler(local) if rank == 0 else None
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    launches = lib_launches    # the timed region replays exactly the frames counted above
-    barrier()
-    with torch.cuda.stream(ext):
-        e0.record()
-    for k in range(args.steps):
-        _, n = step(k)
-        launches += n
-    with torch.cuda.stream(ext):
-        e1.record()
-    barrier()
-    ms = e0.elapsed_time(e1)
-    clocks = sampler.stop() if sampler else None
-
-    # ---- timed region 2 (e2e): the same K frames through the public API with the finished frame read back into pinned host
-    # memory EVERY step; per-step inputs (camera block + settings) travel as kernel parameters. Two frames are in flight (as in
-    # the reference, source/engine/engine.hpp:19): the read-back of frame k runs on the copy stream beside the kernels of frame
-    # k+1, and the host waits for frame k-1 before it queues frame k+1. All K read-backs complete inside the timed region.
-    rp2 = pyvrt.VoxelRenderPass(ctx, scene, st)
-    passes = (rp, rp2)
     host2 = [torch.empty(frame_bytes, dtype=torch.uint8, pin_memory=True) for _ in range(2)] if rank == 0 else None
-    asm2 = [torch.empty(frame_bytes, dtype=torch.uint8, device="cuda") for _ in range(2)] if (world > 1 and rank == 0) else None
-    copy_stream = torch.cuda.Stream(device=torch.device("cuda", local)) if (world > 1 and rank == 0) else None
+    # N>1: the colour shards of frame k travel to rank 0 (NCCL gather) on a communication stream while the context stream already
+    # traces frame k+1; rank 0 assembles frame k (detile kernel, same communication stream) once its shards are in.
+    gathered, asm2, comm, copy_stream = [None, None], None, None, None
+    if world > 1:
+        comm = torch.cuda.Stream(device=dev, priority=-1)
+        if rank == 0:
+            asm2 = [torch.empty(frame_bytes, dtype=torch.uint8, device="cuda") for _ in range(2)]
+            copy_stream = torch.cuda.Stream(device=dev)
+    ev_rendered = [torch.cuda.Event() for _ in range(2)]
+    ev_gathered = [torch.cuda.Event() for _ in range(2)]
     ev_ready = [torch.cuda.Event() for _ in range(2)]
     ev_copied = [torch.cuda.Event() for _ in range(2)]
-    copied_pending = [False, False]
+    sent, copied_pending = [False, False], [False, False]
+    last_slot = None
 
-    def step_e2e(k):
-        """Render frame k (+ gather / assemble for N>1) and queue its read-back; returns the slot used."""
+    def submit(k, readback=False):
+        """Queue frame k: render this rank's tiles (+ N>1: gather and assemble; + readback: copy the finished frame to pinned host
+        memory). Returns the frame and the kernels launched outside vrt_render (the library counts its own)."""
+        nonlocal last_slot
         slot = k & 1
-        fr = passes[slot].record(configs.make_camera(args.config, bounds, size, k))
+        cam = configs.make_camera(args.config, bounds, size, k)
         if world == 1:
-            fr.download_async(final, host2[slot].numpy())
-            return slot
+            fr = passes[slot].record(cam)
+            if readback:
+                fr.download_async(final, host2[slot].numpy())
+            return fr, 0
+        if sent[slot]:
+            ext.wait_event(ev_gathered[slot])                # this slot's shard buffer is still being sent
+        fr = passes[slot].record(cam)
+        ev_rendered[slot].record(ext)
         ptr, n = fr.plane_ptr("color")
-        shard = torch.as_tensor(_DevBuf(ptr, n), device=torch.device("cuda", local))
-        with torch.cuda.stream(ext):
+        shard = torch.as_tensor(_DevBuf(ptr, n), device=dev)
+        if rank == 0 and gathered[slot] is None:
+            gathered[slot] = torch.empty((world, n), dtype=torch.uint8, device="cuda")
+        launches = 0
+        comm.wait_event(ev_rendered[slot])
+        with torch.cuda.stream(comm):
+            dist.gather(shard, list(gathered[slot].unbind(0)) if rank == 0 else None, dst=0)
             if rank == 0:
                 if copied_pending[slot]:
-                    ext.wait_event(ev_copied[slot])              # asm2[slot] is still being read back
-                dist.gather(shard, list(gathered.unbind(0)), dst=0)
-                pyvrt.assemble(ctx, gathered.data_ptr(), world, size, "color", asm2[slot].data_ptr())
-                ev_ready[slot].record(ext)
-                copy_stream.wait_event(ev_ready[slot])
-                with torch.cuda.stream(copy_stream):
-                    host2[slot].copy_(asm2[slot], non_blocking=True)
-                    ev_copied[slot].record(copy_stream)
-                copied_pending[slot] = True
-            else:
-                dist.gather(shard, None, dst=0)
-        return slot
+                    comm.wait_event(ev_copied[slot])         # asm2[slot] is still being read back
+                pyvrt.assemble(ctx, gathered[slot].data_ptr(), world, size, "color", asm2[slot].data_ptr(), stream=comm.cuda_stream)
+                launches = 1
+                if readback:
+                    ev_ready[slot].record(comm)
+                    copy_stream.wait_event(ev_ready[slot])
+                    with torch.cuda.stream(copy_stream):
+                        host2[slot].copy_(asm2[slot], non_blocking=True)
+                        ev_copied[slot].record(copy_stream)
+                    copied_pending[slot] = True
+            ev_gathered[slot].record(comm)                   # shards sent / frame assembled
+        sent[slot] = True
+        last_slot = slot
+        return fr, launches
 
-    def wait_e2e(slot):
+    def drain():
+        """Join the communication stream into the context stream (the timed region ends on the context stream)."""
+        if world > 1 and last_slot is not None:
+            ext.wait_event(ev_gathered[last_slot])
+        return 0
+
+    def wait_readback(k):
+        slot = k & 1
         if rank != 0:
             return
         if world == 1:
@@ -380,17 +340,64 @@ def run_vrt(args):
         elif copied_pending[slot]:
             ev_copied[slot].synchronize()
 
+    def barrier():
+        ctx.sync(); torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    # ---- warm-up, then an untimed counting pass over the K timed poses (rays / voxel visits / kernel time per frame)
+    for k in range(max(args.warmup, 2)):
+        submit(k)
+    drain()
+    barrier()
+    rays = fetches = pixels = lib_launches = 0
+    ms_kernel, ms_stage = [], []
+    stage_rays, stage_fetches = np.zeros(3), np.zeros(3)
+    for k in range(args.steps):
+        fr, _ = submit(k)
+        s = fr.stats()
+        rays += s["rays"]; fetches += s["fetches"]; pixels += s["pixels"]; ms_kernel.append(s["ms_trace"] + s["ms_denoise"])
+        ms_stage.append(s["ms_stage"]); stage_rays += s["stage_rays"]; stage_fetches += s["stage_fetches"]
+        lib_launches += s["kernel_launches"]
+    drain()
+    barrier()
+
+    # ---- timed region 1: K frames, inputs resident, device time on the launching stream, max over ranks. The region ends when the
+    # last frame is assembled on rank 0 (every gather and detile kernel is inside it).
+    sampler = ClockSampler(local) if rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches = lib_launches    # the timed region replays exactly the frames counted above
+    barrier()
+    with torch.cuda.stream(ext):
+        e0.record()
+    for k in range(args.steps):
+        _, n = submit(k)
+        launches += n
+    launches += drain()
+    with torch.cuda.stream(ext):
+        e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if sampler else None
+
+    # ---- timed region 2 (e2e): the same K frames through the public API with the finished frame read back into pinned host
+    # memory EVERY step; per-step inputs (camera block + settings) travel as kernel parameters. The read-back of frame k runs on
+    # the copy stream beside the kernels of frame k+1, and the host waits for frame k-1 before it queues frame k+1. All K
+    # read-backs complete inside the timed region.
     if args.shard and world == 1:                           # debug mode: a shard is not a frame, there is nothing to read back
         t_e2e = ms * 1e-3
     else:
-        step_e2e(0); wait_e2e(0); step_e2e(1); wait_e2e(1)  # allocate the second frame outside the timed region
+        for k in range(2):
+            submit(k, True)
+        drain(); wait_readback(0); wait_readback(1)
         barrier()
         t0 = time.perf_counter()
         for k in range(args.steps):
-            step_e2e(k)
+            submit(k, True)
             if k > 0:
-                wait_e2e((k - 1) & 1)
-        wait_e2e((args.steps - 1) & 1)
+                wait_readback(k - 1)
+        drain()
+        wait_readback(args.steps - 1)
         barrier()
         t_e2e = time.perf_counter() - t0
 
@@ -421,7 +428,8 @@ def run_vrt(args):
         line = {"metric": METRIC, "value": rays_all / (ms * 1e-3) / 1e6, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": config_blob(cfg, args.config, args.whd, size, {"parallelism": f"tiles{world}" if world > 1 else "single", "traversal": args.traversal, "pipeline": args.pipeline,
-                                                                         "gathered_plane": "color RGBA8" if world > 1 else None}),
+                                                                         "gathered_plane": "color RGBA8" if world > 1 else None, "frames_in_flight": 2,
+                                                                         "exchange": "NCCL gather of frame k on a communication stream beside the tracing of frame k+1, detile on rank 0" if world > 1 else None}),
                 "rays_per_frame": rays_all / args.steps, "voxel_visits_per_frame": fetches_all / args.steps,
                 "Mrays_per_s_primary": pixels_all / (ms * 1e-3) / 1e6,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(names[dom]),
@@ -441,9 +449,9 @@ def run_vrt(args):
         print(json.dumps(line), flush=True)
     barrier()
     # tensors that were used on the context's stream must be returned to torch's allocator while that stream still exists
-    gathered = assembled = host_frame = host2 = asm2 = None
+    gathered = host2 = asm2 = None
     rp2.frame.release()
-    del step, step_e2e
+    del submit
     import gc
     gc.collect()
     torch.cuda.synchronize()

@@ -187,6 +187,8 @@ int vrt_denoise(vrt_context*, const void* d_color_rgba8, const void* d_normal_rg
 /* Multi-GPU assembly on the gathering rank: d_gathered holds `world` shard buffers back to back (rank-major), each
  * of vrt_frame_plane() size as produced under vrt_context_set_shard(rank, world); writes a row-major w x h plane. */
 int vrt_assemble(vrt_context*, const void* d_gathered, int world, int w, int h, int plane, void* d_out);
+/* the same on a cudaStream_t of the caller's (the stream its gather runs on), leaving the context stream free for the next frame */
+int vrt_assemble_on(vrt_context*, const void* d_gathered, int world, int w, int h, int plane, void* d_out, void* stream);
 
 /* ---- host helpers mirroring reference host code ---- */
 void vrt_camera_vectors(float yaw_deg, float pitch_deg, float focal, float dir[3], float right[3], float up[3]);

@@ -9,3 +9,6 @@ try:
 except Exception as e: print("parse failed", e)
 PY
 done
+# cfg5: BASELINE's 8-GPU line — 2048^3 volume replicated per GPU, 7680x4320, 256-frame camera path, colour shards gathered on rank 0
+python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29533 bench.py --config cfg5 --gpus 8 --steps 256 --warmup 3 > gpurun_out/scale_cfg5_8.json 2> gpurun_out/scale_cfg5_8.err
+echo "cfg5 N=8 rc=$?"; cut -c1-400 gpurun_out/scale_cfg5_8.json; tail -2 gpurun_out/scale_cfg5_8.err

@@ -559,6 +559,13 @@ extern "C" int vrt_frame_stats_get(vrt_frame* f, vrt_frame_stats* out) {
     CU(cudaEventElapsedTime(&out->ms_total, f->e0, f->e2));
     out->kernel_launches = f->launches;
     for (int k = 0; k < 3; k++) { out->stage_rays[k] = h.stageRays[k]; out->stage_fetches[k] = h.stageFetches[k]; }
+#ifdef VRT_ENGINE_STATS
+    if (getenv("VRT_DEBUG_STATS")) {
+        fprintf(stderr, "engine stats:");
+        for (int k = 0; k < 24; k++) fprintf(stderr, " %llu", h.dbg[k]);
+        fprintf(stderr, "\n");
+    }
+#endif
     if (f->staged) {
         CU(cudaEventElapsedTime(&out->ms_stage[0], f->e0, f->es[0]));
         CU(cudaEventElapsedTime(&out->ms_stage[1], f->es[0], f->es[1]));
@@ -588,12 +595,17 @@ extern "C" int vrt_denoise(vrt_context* c, const void* d_color, const void* d_no
 
 // Assemble a sharded plane on the gathering rank: `gathered` holds world shard buffers back to back (rank-major),
 // each of vrt_frame_plane() size; writes a row-major W x H plane.
+extern "C" int vrt_assemble_on(vrt_context* c, const void* d_gathered, int world, int w, int h, int plane, void* d_out, void* stream);
 extern "C" int vrt_assemble(vrt_context* c, const void* d_gathered, int world, int w, int h, int plane, void* d_out) {
+    return vrt_assemble_on(c, d_gathered, world, w, h, plane, d_out, c ? (void*)c->stream : nullptr);
+}
+// the same on a stream of the caller's (e.g. the one its gather runs on, so that the context stream can trace the next frame)
+extern "C" int vrt_assemble_on(vrt_context* c, const void* d_gathered, int world, int w, int h, int plane, void* d_out, void* stream) {
     if (!c || !d_gathered || !d_out || world < 1 || plane < 0 || plane >= VRT_PLANE_COUNT) return fail(VRT_E_INVALID, "bad argument");
     CU(cudaSetDevice(c->device));
     const int tiles = ((w + VRT_TILE - 1) / VRT_TILE) * ((h + VRT_TILE - 1) / VRT_TILE);
     const size_t stride = (size_t)((tiles + world - 1) / world) * VRT_TILE * VRT_TILE;
-    cudaError_t e = launch_detile(d_gathered, d_out, w, h, world, stride, kPlaneBpp[plane], c->stream);
+    cudaError_t e = launch_detile(d_gathered, d_out, w, h, world, stride, kPlaneBpp[plane], (cudaStream_t)stream);
     if (e != cudaSuccess) return fail(VRT_E_CUDA, cudaGetErrorString(e));
     return VRT_OK;
 }

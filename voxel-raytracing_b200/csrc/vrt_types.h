@@ -91,7 +91,7 @@ struct FrameParams {
     int localTiles;       // tiles owned by this rank
 };
 
-struct Counters { unsigned long long rays, fetches, pixels; unsigned long long stageRays[3], stageFetches[3]; };
+struct Counters { unsigned long long rays, fetches, pixels; unsigned long long stageRays[3], stageFetches[3]; unsigned long long dbg[24]; };   // dbg: -DVRT_ENGINE_STATS builds only
 
 // ---- wavefront pipeline (vrt_wave.cuh / vrt_wave.cu) ----
 // The shader's per-pixel call tree (primary -> <=5 reflection bounces -> per shaded hit: aoSamples AO rays + 1

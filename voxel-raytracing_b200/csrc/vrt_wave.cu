@@ -91,9 +91,12 @@ __global__ void __launch_bounds__(128) wave_primary_kernel(const SceneDev sc, co
     add_totals(ctr, 0, active ? 1u : 0u, active ? o.fetches : 0u, active ? 1u : 0u);
 }
 
+// Reflection wave w: bounce w of every chain still alive. With `chain` set the wave also runs all LATER bounces of its rays in
+// place (the lanes whose chain goes on keep going, the others idle): the last waves hold a few thousand rays each and cost a
+// launch + a latency-bound tail apiece, which is more than their idle lanes cost.
 template <int TRAVERSAL>
 __global__ void __launch_bounds__(128) wave_bounce_kernel(const SceneDev sc, const FrameParams fp, const PlanesDev pl, const WaveBuf wb,
-                                                          Counters* __restrict__ ctr, const int w) {
+                                                          Counters* __restrict__ ctr, const int w, const bool chain) {
     const uint32_t n = wb.ctr->qn[w];
     const BounceEnt* __restrict__ qin = wb.bq[w & 1];
     BounceEnt* __restrict__ qout = wb.bq[(w + 1) & 1];
@@ -105,44 +108,54 @@ __global__ void __launch_bounds__(128) wave_bounce_kernel(const SceneDev sc, con
         e0 = __shfl_sync(0xffffffffu, e0, 0);
         if (e0 >= n) break;
         const uint32_t e = e0 + lane;
-        const bool valid = e < n;
+        bool act = e < n;
         BounceEnt ent; ent.rec = 0; ent.root = 0;
-        TraceRes r; r.material = 0; r.fetches = 0; r.pos = r.normal = mk3(0.0f, 0.0f, 0.0f);
-        V3 rd = mk3(0.0f, 0.0f, 0.0f);
+        V3 pos = mk3(0.0f, 0.0f, 0.0f), normal = pos, dir = pos;
         uint32_t pxy = 0;
-        if (valid) {
+        if (act) {
             ent = qin[e];
             const RecQ* pr = wb.rec + 3 * (size_t)ent.rec;
             const RecQ p0 = pr[0], p1 = pr[1], p2 = pr[2];
-            pxy = p0.w;
-            r = wave_bounce<TRAVERSAL>(sc, q3(p0), q3(p1), q3(p2), rd);
-            rays++; fetches += r.fetches;
-            if (fp.out_mask & VRT_OUT_INSTRUMENT) {
-                const size_t p = plane_index(fp, (int)(pxy & 0xffffu), (int)(pxy >> 16));
-                atomicAdd(pl.rays + p, 1u); atomicAdd(pl.fetches + p, r.fetches);
-            }
+            pxy = p0.w; pos = q3(p0); normal = q3(p1); dir = q3(p2);
         }
-        const uint32_t child = wb.pixCap + warp_alloc(&wb.ctr->nb, valid);
-        bool cont = false;
-        if (valid) {
-            RecQ* cr = wb.rec + 3 * (size_t)child;
-            cr[0] = mkq(r.pos, pxy);
-            cr[1] = mkq(r.normal, r.material | ((uint32_t)w << 8));
-            cr[2] = mkq(rd, ent.rec);
-            const bool terminal = r.material == 0 || sc.palette[r.material].metallic <= 0.0f;   // :289-292 lastIdx = w
-            if (terminal) {
-                wb.rec[3 * (size_t)ent.root + 2].w = child;
-                // every record of the chain below the primary hit that is a hit gets its AO + shadow rays
-                const uint32_t cnt = (uint32_t)w + (r.material != 0 ? 1u : 0u);
-                if (cnt) {
-                    uint32_t s = atomicAdd(&wb.ctr->nsq, cnt);
-                    if (r.material != 0) wb.sq[s++] = child;
-                    for (uint32_t k = ent.rec; k != ent.root; k = wb.rec[3 * (size_t)k + 2].w) wb.sq[s++] = k;
+        for (uint32_t wl = (uint32_t)w;; wl++) {                    // warp-uniform depth of this bounce
+            TraceRes r; r.material = 0; r.fetches = 0; r.pos = r.normal = mk3(0.0f, 0.0f, 0.0f);
+            V3 rd = mk3(0.0f, 0.0f, 0.0f);
+            if (act) {
+                r = wave_bounce<TRAVERSAL>(sc, pos, normal, dir, rd);
+                rays++; fetches += r.fetches;
+                if (fp.out_mask & VRT_OUT_INSTRUMENT) {
+                    const size_t p = plane_index(fp, (int)(pxy & 0xffffu), (int)(pxy >> 16));
+                    atomicAdd(pl.rays + p, 1u); atomicAdd(pl.fetches + p, r.fetches);
                 }
-            } else if (w + 1 < MAX_REFLECTIONS) cont = true;        // else: 5 metallic bounces, lastIdx stays -1 (:298)
+            }
+            const uint32_t child = wb.pixCap + warp_alloc(&wb.ctr->nb, act);
+            bool cont = false;
+            if (act) {
+                RecQ* cr = wb.rec + 3 * (size_t)child;
+                cr[0] = mkq(r.pos, pxy);
+                cr[1] = mkq(r.normal, r.material | (wl << 8));
+                cr[2] = mkq(rd, ent.rec);
+                const bool terminal = r.material == 0 || sc.palette[r.material].metallic <= 0.0f;   // :289-292 lastIdx = w
+                if (terminal) {
+                    wb.rec[3 * (size_t)ent.root + 2].w = child;
+                    // every record of the chain below the primary hit that is a hit gets its AO + shadow rays
+                    const uint32_t cnt = wl + (r.material != 0 ? 1u : 0u);
+                    if (cnt) {
+                        uint32_t s = atomicAdd(&wb.ctr->nsq, cnt);
+                        if (r.material != 0) wb.sq[s++] = child;
+                        for (uint32_t k = ent.rec; k != ent.root; k = wb.rec[3 * (size_t)k + 2].w) wb.sq[s++] = k;
+                    }
+                } else if (wl + 1 < MAX_REFLECTIONS) cont = true;    // else: 5 metallic bounces, lastIdx stays -1 (:298)
+            }
+            if (!chain) {
+                const uint32_t qi = warp_alloc(&wb.ctr->qn[w + 1], cont);
+                if (cont) { BounceEnt o; o.rec = child; o.root = ent.root; qout[qi] = o; }
+                break;
+            }
+            if (!__any_sync(0xffffffffu, cont)) break;
+            act = cont; ent.rec = child; pos = r.pos; normal = r.normal; dir = rd;
         }
-        const uint32_t qi = warp_alloc(&wb.ctr->qn[w + 1], cont);
-        if (cont) { BounceEnt o; o.rec = child; o.root = ent.root; qout[qi] = o; }
     }
     add_totals(ctr, 1, rays, fetches, 0u);
 }
@@ -191,7 +204,7 @@ __global__ void __launch_bounds__(256) wave_anyhit_kernel(const SceneDev sc, con
 // ---- any-hit wave on the ray engine (vrt_engine.cuh): LINEAR (isotropic field) or OCTANT (directional fields) ----
 template <int TRAVERSAL, int NEAR_STEPS, int FAR_STEPS>
 __global__ void __launch_bounds__(ENGINE_WARPS * 32, 4) wave_anyhit_engine_kernel(const SceneDev sc, const FrameParams fp, const PlanesDev pl, const WaveBuf wb,
-                                                                                Counters* __restrict__ ctr, const uint32_t refillT, const uint32_t farShare, const int part) {
+                                                                                Counters* __restrict__ ctr, const uint32_t refillT, const uint32_t farShare, const int part, const uint32_t quota) {
     __shared__ EngineStash stashAll[ENGINE_WARPS];
     __shared__ uint32_t blockChunk;
     EngineStash& st = stashAll[threadIdx.x >> 5];
@@ -204,7 +217,7 @@ __global__ void __launch_bounds__(ENGINE_WARPS * 32, 4) wave_anyhit_engine_kerne
     const uint32_t R = aoN + ((fp.pass_mask & VRT_PASS_SHADOW) ? 1u : 0u);
     const unsigned long long total = (unsigned long long)S * R;
     if (part == 1) {
-        if ((unsigned long long)blockIdx.x * ENGINE_BLOCK_QUOTA >= total) return;     // the grid is sized for the worst case
+        if ((unsigned long long)blockIdx.x * quota >= total) return;     // the grid is sized for the worst case
         if (threadIdx.x == 0) blockChunk = 0;
         __syncthreads();
     }
@@ -222,6 +235,12 @@ __global__ void __launch_bounds__(ENGINE_WARPS * 32, 4) wave_anyhit_engine_kerne
     bool alive = false, pending = false, hitRes = false;
     uint32_t idx = 0, kind = 0, fetchRes = 0;
     unsigned rays = 0, fetches = 0;
+#ifdef VRT_ENGINE_STATS
+    unsigned long long dbg[20] = {};
+#define ENG_STAT(k, v) dbg[k] += (v)
+#else
+#define ENG_STAT(k, v)
+#endif
 
     auto retire = [&](uint32_t rIdx, uint32_t rKind, bool hit, uint32_t f) {
         wb.res[(size_t)rKind * wb.recCap + rIdx] = hit ? 1 : 0;
@@ -240,6 +259,7 @@ __global__ void __launch_bounds__(ENGINE_WARPS * 32, 4) wave_anyhit_engine_kerne
         const bool canRefill = stashN > 0 || !exhausted;
         if (nIdle == 32u && !canRefill) break;
         if (canRefill && (nIdle >= refillT || nIdle == 32u)) {
+            ENG_STAT(7, lane == 0);
             if (!alive && pending) { retire(idx, kind, hitRes, fetchRes); pending = false; }
             // produce prepared rays, 32 at a time with all lanes, until the idle lanes can be served
             while (stashN < nIdle && !exhausted) {
@@ -247,8 +267,8 @@ __global__ void __launch_bounds__(ENGINE_WARPS * 32, 4) wave_anyhit_engine_kerne
                     uint32_t c = 0;
                     if (lane == 0) c = part == 1 ? atomicAdd(&blockChunk, 1u) : atomicAdd(part == 2 ? &wb.ctr->pad[0] : &wb.ctr->chunk, 1u);
                     c = __shfl_sync(0xffffffffu, c, 0);
-                    if (part == 1 && c >= ENGINE_BLOCK_QUOTA / ENGINE_CHUNK) { exhausted = true; break; }
-                    const unsigned long long t0 = (unsigned long long)c * ENGINE_CHUNK + (part == 1 ? (unsigned long long)blockIdx.x * ENGINE_BLOCK_QUOTA : 0ull);
+                    if (part == 1 && c >= quota / ENGINE_CHUNK) { exhausted = true; break; }
+                    const unsigned long long t0 = (unsigned long long)c * ENGINE_CHUNK + (part == 1 ? (unsigned long long)blockIdx.x * quota : 0ull);
                     if (t0 >= total) { exhausted = true; break; }
                     cur = t0; end = t0 + ENGINE_CHUNK < total ? t0 + ENGINE_CHUNK : total;
                     ci = (uint32_t)(t0 / S); cq = (uint32_t)(t0 - (unsigned long long)ci * S);
@@ -288,6 +308,11 @@ __global__ void __launch_bounds__(ENGINE_WARPS * 32, 4) wave_anyhit_engine_kerne
         // ---- look-up for lanes whose budget is spent
         if (alive && er.rem == 0) {
             const int stt = engine_lookup(er);
+            ENG_STAT(6, 1);
+            ENG_STAT(8, stt == ENG_EXHAUSTED);
+#ifdef VRT_ENGINE_STATS
+            if (stt == ENG_GO) { const int n = er.rem; dbg[9 + (n <= 1 ? 0 : n <= 2 ? 1 : n <= 4 ? 2 : n <= 8 ? 3 : n <= 16 ? 4 : n <= 32 ? 5 : n <= 64 ? 6 : 7)]++; }
+#endif
             if (stt != ENG_GO) {
                 alive = false; pending = true; hitRes = stt == ENG_HIT; fetchRes = engine_steps_taken(er) + (hitRes ? 1u : 0u);
             }
@@ -296,10 +321,12 @@ __global__ void __launch_bounds__(ENGINE_WARPS * 32, 4) wave_anyhit_engine_kerne
         // a long round when at least farShare/8 of the live lanes can use all of it
         const uint32_t nFar = __popc(__ballot_sync(0xffffffffu, alive && er.rem >= FAR_STEPS));
         if (nFar * 8u >= (32u - nIdle) * farShare && nFar) {
+            ENG_STAT(1, lane == 0); ENG_STAT(3, alive); ENG_STAT(5, alive ? min(er.rem, FAR_STEPS) : 0);
 #pragma unroll
             for (int k = 0; k < FAR_STEPS; k++) engine_step(er.l, er.rem, k);
             er.rem = max(er.rem - FAR_STEPS, 0);
         } else {
+            ENG_STAT(0, lane == 0); ENG_STAT(2, alive); ENG_STAT(4, alive ? min(er.rem, NEAR_STEPS) : 0);
 #pragma unroll
             for (int k = 0; k < NEAR_STEPS; k++) engine_step(er.l, er.rem, k);
             er.rem = max(er.rem - NEAR_STEPS, 0);
@@ -307,6 +334,9 @@ __global__ void __launch_bounds__(ENGINE_WARPS * 32, 4) wave_anyhit_engine_kerne
     }
     if (pending) retire(idx, kind, hitRes, fetchRes);
     add_totals(ctr, 2, rays, fetches, 0u);
+#ifdef VRT_ENGINE_STATS
+    for (int k = 0; k < 20; k++) if (dbg[k]) atomicAdd(&ctr->dbg[k], dbg[k]);
+#endif
 }
 
 __global__ void __launch_bounds__(256) wave_resolve_kernel(const SceneDev sc, const FrameParams fp, const PlanesDev pl, const WaveBuf wb) {
@@ -340,6 +370,9 @@ static cudaError_t launch_wave_t(const SceneDev& sc, const FrameParams& fp, cons
         if (occBounce < 1) occBounce = 1;
         if (occEngine < 1) occEngine = 1;
     }
+    static const uint32_t quota = getenv("VRT_ENGINE_QUOTA") ? (uint32_t)atoi(getenv("VRT_ENGINE_QUOTA")) / ENGINE_CHUNK * ENGINE_CHUNK : ENGINE_BLOCK_QUOTA;
+    // the wave from which the rest of every reflection chain runs in place (MAX_REFLECTIONS - 1: one launch per bounce)
+    static const int bounceChain = getenv("VRT_BOUNCE_CHAIN") ? min(max(atoi(getenv("VRT_BOUNCE_CHAIN")), 0), MAX_REFLECTIONS - 1) : 2;
     static const int farShare = getenv("VRT_ENGINE_FARSHARE") ? atoi(getenv("VRT_ENGINE_FARSHARE")) : 4;
     // measured (profiles/r1_overlap.log): beside-the-waves scheduling pays when the frame (or this rank's shard of it) is small and
     // the launches are tail-bound (1/8 of a 4K frame: -12 %), and costs ~1 % on a full 4K frame. VRT_OVERLAP=0/1 overrides.
@@ -357,18 +390,26 @@ static cudaError_t launch_wave_t(const SceneDev& sc, const FrameParams& fp, cons
     const bool engine = (T == VRT_TRAVERSAL_LINEAR || T == VRT_TRAVERSAL_OCTANT) && engineT() > 0;
     const bool overlap = anyhit && reflect && engine && side && (overlapEnv < 0 ? smallFrame : overlapEnv != 0);
     auto launch_engine = [&](cudaStream_t s, int part, unsigned grid) {
-        wave_anyhit_engine_kernel<T, 8, 32><<<grid, ENGINE_WARPS * 32, 0, s>>>(sc, fp, pl, wb, ctr, (uint32_t)engineT(), (uint32_t)farShare, part);
+        // part 1 shares the SMs with the reflection waves: padding its shared memory caps its blocks per SM so that the waves'
+        // blocks find registers at once instead of waiting for a side block to retire
+        static const int sidePad = getenv("VRT_SIDE_PAD_KB") ? atoi(getenv("VRT_SIDE_PAD_KB")) * 1024 : 0;
+        const size_t dyn = part == 1 ? (size_t)sidePad : 0;
+        if (dyn) cudaFuncSetAttribute(wave_anyhit_engine_kernel<T, 8, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+        wave_anyhit_engine_kernel<T, 8, 32><<<grid, ENGINE_WARPS * 32, dyn, s>>>(sc, fp, pl, wb, ctr, (uint32_t)engineT(), (uint32_t)farShare, part, quota);
         n++;
     };
     if (overlap) {
         const unsigned long long worst = (unsigned long long)fp.localTiles * (VRT_TILE * VRT_TILE) * R;       // every pixel a hit
         cudaEventRecord(side->fork, stream);
         cudaStreamWaitEvent(side->stream, side->fork, 0);
-        launch_engine(side->stream, 1, (unsigned)((worst + ENGINE_BLOCK_QUOTA - 1) / ENGINE_BLOCK_QUOTA));
+        launch_engine(side->stream, 1, (unsigned)((worst + quota - 1) / quota));
         cudaEventRecord(side->join, side->stream);
     }
     if (reflect)
-        for (int w = 0; w < MAX_REFLECTIONS; w++) { wave_bounce_kernel<T><<<(unsigned)(sms * occBounce), 128, 0, stream>>>(sc, fp, pl, wb, ctr, w); n++; }
+        for (int w = 0; w <= bounceChain; w++) {
+            wave_bounce_kernel<T><<<(unsigned)(sms * occBounce), 128, 0, stream>>>(sc, fp, pl, wb, ctr, w, w == bounceChain && w + 1 < MAX_REFLECTIONS);
+            n++;
+        }
     if (ev) cudaEventRecord(ev[1], stream);
     if (anyhit) {
         if (overlap) { launch_engine(stream, 2, (unsigned)(sms * occEngine)); cudaStreamWaitEvent(stream, side->join, 0); }

@@ -282,8 +282,11 @@ class VoxelRenderPass:
         return self.frame
 
 
-def assemble(ctx: Context, d_gathered_ptr: int, world: int, size, plane: str, d_out_ptr: int):
-    _ck(lib().vrt_assemble(ctx.h, C.c_void_p(d_gathered_ptr), world, size[0], size[1], PLANE_ID[plane], C.c_void_p(d_out_ptr)))
+def assemble(ctx: Context, d_gathered_ptr: int, world: int, size, plane: str, d_out_ptr: int, stream: int = None):
+    if stream is None:
+        _ck(lib().vrt_assemble(ctx.h, C.c_void_p(d_gathered_ptr), world, size[0], size[1], PLANE_ID[plane], C.c_void_p(d_out_ptr)))
+    else:
+        _ck(lib().vrt_assemble_on(ctx.h, C.c_void_p(d_gathered_ptr), world, size[0], size[1], PLANE_ID[plane], C.c_void_p(d_out_ptr), C.c_void_p(stream)))
 
 
 def denoise_device(ctx: Context, d_color, d_normal, d_position, size, ds: DenoiserSettings, d_out):
