@@ -40,7 +40,17 @@ for r in rows[2:]:
         stall_wait=val(r, "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio"),
         stall_not_selected=val(r, "smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio"),
         stall_math_throttle=val(r, "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio"),
-        stall_branch=val(r, "smsp__average_warps_issue_stalled_branch_resolving_per_issue_active.ratio"))
+        stall_branch=val(r, "smsp__average_warps_issue_stalled_branch_resolving_per_issue_active.ratio"),
+        stall_short_scoreboard=val(r, "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio"),
+        stall_barrier=val(r, "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio"),
+        stall_dispatch=val(r, "smsp__average_warps_issue_stalled_dispatch_stall_per_issue_active.ratio"),
+        stall_no_inst=val(r, "smsp__average_warps_issue_stalled_no_instruction_per_issue_active.ratio"),
+        pipe_alu_pct=val(r, "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active"),
+        pipe_fma_pct=val(r, "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active"),
+        pipe_fmaheavy_pct=val(r, "sm__inst_executed_pipe_fmaheavy.avg.pct_of_peak_sustained_active"),
+        pipe_lsu_pct=val(r, "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active"),
+        pipe_xu_pct=val(r, "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active"),
+        pred_on_lanes=val(r, "smsp__thread_inst_executed_pred_on_per_inst_executed.ratio"))
     per.setdefault(name, []).append(d)
     print(name)
     print("   " + "  ".join(f"{k}={v:.4g}" if isinstance(v, float) else f"{k}={v}" for k, v in d.items()))

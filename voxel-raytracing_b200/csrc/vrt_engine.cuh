@@ -8,9 +8,9 @@
 //     32 rays at a time, and pushes the resulting traversal states into a per-warp shared-memory stash;
 //   * a refill event happens when >= refillT lanes are idle: those lanes first retire the result of their finished ray (so the
 //     retire code also runs with >= refillT lanes), then pop a prepared state (LDS.128, conflict-free);
-//   * a round = [lanes whose safe-step budget is spent look the field up] + a FIXED number of DDA steps for the whole warp
-//     (ENGINE_NEAR_STEPS, or ENGINE_FAR_STEPS when every live lane has that much budget), fully unrolled, each step predicated
-//     on the lane's remaining budget (the predicate rides on the FSETPs: 9 instructions per step).
+//   * a round = [lanes whose safe-step budget is spent look the field up] + a FIXED block sequence of DDA steps for the whole
+//     warp (up to 7 steps, or up to 31 when enough live lanes have that much budget), fully unrolled; a lane runs the binary
+//     blocks of its own budget (engine_round): 7 instructions per step.
 // Every ray still performs exactly the float operations of traceRayInt in the same order (the select form of
 // voxel_volume.frag:164-170) and looks the field up through the same lin_bits() offset recovery as trace_ray<LINEAR/OCTANT>, so
 // results are bit-identical (tests/test_gpu.py runs every back-end against the oracle).
@@ -22,9 +22,13 @@ namespace vrt {
 constexpr int ENGINE_WARPS = 8;          // warps per block
 constexpr uint32_t ENGINE_CHUNK = 64;    // rays per claim of the global work counter (small: the tail of a sharded frame is short)
 constexpr uint32_t ENGINE_BLOCK_QUOTA = ENGINE_WARPS * 256u;   // rays per block when the kernel runs as many short-lived blocks
+#ifndef ENGINE_NEAR_TOP
+#define ENGINE_NEAR_TOP 4              // near round: up to 7 steps (blocks 4,2,1)
+#endif
+#ifndef ENGINE_FAR_TOP
+#define ENGINE_FAR_TOP 16              // far round: up to 31 steps (blocks 16,8,4,2,1)
+#endif
 constexpr int ENGINE_STASH = 64;         // prepared rays per warp (a refill asks for <= 32 more while < 32 are left)
-constexpr int ENGINE_NEAR_STEPS = 4;
-constexpr int ENGINE_FAR_STEPS = 16;
 
 // Traversal state of one ray: LinRay (vrt_core.cuh) + the step budget
 struct EngRay {
@@ -87,19 +91,37 @@ __device__ __forceinline__ int engine_lookup(EngRay& e) {
     return ENG_GO;
 }
 
-// DDA step number k of a round (:164-170, select form) for lanes whose budget at the start of the round exceeds k.
-// Written in PTX so that the budget predicate rides on the three compares and the adds stay predicated (8 instructions).
-__device__ __forceinline__ void engine_step(LinRay& r, int rem, int k) {
-    asm("{\n\t.reg .pred pa, px, py, pz;\n\t.reg .f32 m;\n\t"
-        "setp.gt.s32 pa, %6, %8;\n\t"
-        "min.f32 m, %0, %1, %2;\n\t"
-        "setp.le.and.f32 px, %0, m, pa;\n\t"
-        "setp.le.and.f32 py, %1, m, pa;\n\t"
-        "setp.le.and.f32 pz, %2, m, pa;\n\t"
-        "@px add.f32 %0, %0, %3;\n\t"
-        "@py add.f32 %1, %1, %4;\n\t"
-        "@pz add.f32 %2, %2, %5;\n\t}"
-        : "+f"(r.sx), "+f"(r.sy), "+f"(r.sz) : "f"(r.dx), "f"(r.dy), "f"(r.dz), "r"(rem), "n"(0) , "r"(k));
+// A block of N DDA steps (:164-170, select form) for the lanes with `on` set; the other lanes keep their state. Written in PTX so
+// that the guard rides on the three compares (FSETP.LE.AND) and the adds stay predicated: 7 instructions per step (FMNMX3,
+// 3 FSETP, 3 FADD) + one ISETP per block. The step is bound by the ALU pipe (min + compares: 4 of the 7 run there at half rate), so
+// a per-step budget compare would cost a fifth ALU slot: a round runs its lanes' budgets as binary blocks instead (16+8+4+2+1).
+#define VRT_STEP1 "min.f32 m, %0, %1, %2;\n\tsetp.le.and.f32 px, %0, m, pa;\n\tsetp.le.and.f32 py, %1, m, pa;\n\tsetp.le.and.f32 pz, %2, m, pa;\n\t" \
+                  "@px add.f32 %0, %0, %3;\n\t@py add.f32 %1, %1, %4;\n\t@pz add.f32 %2, %2, %5;\n\t"
+#define VRT_STEP2 VRT_STEP1 VRT_STEP1
+#define VRT_STEP4 VRT_STEP2 VRT_STEP2
+#define VRT_STEP8 VRT_STEP4 VRT_STEP4
+#define VRT_STEP16 VRT_STEP8 VRT_STEP8
+#define VRT_BLOCK_ASM(STEPS) asm("{\n\t.reg .pred pa, px, py, pz;\n\t.reg .f32 m;\n\tsetp.ne.s32 pa, %6, 0;\n\t" STEPS "}" \
+        : "+f"(r.sx), "+f"(r.sy), "+f"(r.sz) : "f"(r.dx), "f"(r.dy), "f"(r.dz), "r"(on))
+template <int N>
+__device__ __forceinline__ void engine_block(LinRay& r, int on) {
+    static_assert(N == 1 || N == 2 || N == 4 || N == 8 || N == 16, "block sizes are powers of two");
+    if (N == 1) VRT_BLOCK_ASM(VRT_STEP1);
+    else if (N == 2) VRT_BLOCK_ASM(VRT_STEP2);
+    else if (N == 4) VRT_BLOCK_ASM(VRT_STEP4);
+    else if (N == 8) VRT_BLOCK_ASM(VRT_STEP8);
+    else VRT_BLOCK_ASM(VRT_STEP16);
+}
+// A round of up to 2*TOP-1 steps: every lane runs min(rem, 2*TOP-1) of them, as the binary blocks TOP, TOP/2, .., 1
+template <int TOP>
+__device__ __forceinline__ void engine_round(LinRay& r, int& rem) {
+    const int n = min(rem, 2 * TOP - 1);
+    if (TOP >= 16) engine_block<16>(r, n & 16);
+    if (TOP >= 8) engine_block<8>(r, n & 8);
+    if (TOP >= 4) engine_block<4>(r, n & 4);
+    if (TOP >= 2) engine_block<2>(r, n & 2);
+    engine_block<1>(r, n & 1);
+    rem -= n;
 }
 __device__ __forceinline__ uint32_t engine_steps_taken(const EngRay& e) { return e.l.maxSteps - e.left - (uint32_t)e.rem; }
 

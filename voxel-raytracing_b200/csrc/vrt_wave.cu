@@ -96,17 +96,24 @@ __global__ void __launch_bounds__(128) wave_primary_kernel(const SceneDev sc, co
 // launch + a latency-bound tail apiece, which is more than their idle lanes cost.
 template <int TRAVERSAL>
 __global__ void __launch_bounds__(128) wave_bounce_kernel(const SceneDev sc, const FrameParams fp, const PlanesDev pl, const WaveBuf wb,
-                                                          Counters* __restrict__ ctr, const int w, const bool chain) {
+                                                          Counters* __restrict__ ctr, const int w, const bool chain, const uint32_t roundCap) {
     const uint32_t n = wb.ctr->qn[w];
     const BounceEnt* __restrict__ qin = wb.bq[w & 1];
     BounceEnt* __restrict__ qout = wb.bq[(w + 1) & 1];
-    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t lane = threadIdx.x & 31, ltMask = (1u << lane) - 1u;
+    // Every queued ray yields exactly one record, so its index needs no allocation: records of wave w start after those of the
+    // earlier waves. Only the in-place continuation bounces (chain) allocate, behind this wave's block.
+    uint32_t recBase = wb.pixCap;
+    for (int v = 0; v < w; v++) recBase += wb.ctr->qn[v];
+    const uint32_t recBase2 = recBase + n;
     unsigned rays = 0, fetches = 0;
+    // 32-ray groups are claimed one ahead: the counter's round trip overlaps the tracing of the current group
+    uint32_t nextE0 = 0;
+    if (lane == 0) nextE0 = atomicAdd(&wb.ctr->bcur[w], 32u);
     for (;;) {
-        uint32_t e0 = 0;
-        if (lane == 0) e0 = atomicAdd(&wb.ctr->bcur[w], 32u);
-        e0 = __shfl_sync(0xffffffffu, e0, 0);
+        const uint32_t e0 = __shfl_sync(0xffffffffu, nextE0, 0);
         if (e0 >= n) break;
+        if (lane == 0) nextE0 = atomicAdd(&wb.ctr->bcur[w], 32u);
         const uint32_t e = e0 + lane;
         bool act = e < n;
         BounceEnt ent; ent.rec = 0; ent.root = 0;
@@ -121,36 +128,50 @@ __global__ void __launch_bounds__(128) wave_bounce_kernel(const SceneDev sc, con
         for (uint32_t wl = (uint32_t)w;; wl++) {                    // warp-uniform depth of this bounce
             TraceRes r; r.material = 0; r.fetches = 0; r.pos = r.normal = mk3(0.0f, 0.0f, 0.0f);
             V3 rd = mk3(0.0f, 0.0f, 0.0f);
+            bool cont = false, terminal = false;
+            uint32_t cnt = 0;           // records of this chain that get AO + shadow rays now (the chain ends here)
             if (act) {
-                r = wave_bounce<TRAVERSAL>(sc, pos, normal, dir, rd);
+                r = wave_bounce<TRAVERSAL>(sc, pos, normal, dir, rd, roundCap);
                 rays++; fetches += r.fetches;
                 if (fp.out_mask & VRT_OUT_INSTRUMENT) {
                     const size_t p = plane_index(fp, (int)(pxy & 0xffffu), (int)(pxy >> 16));
                     atomicAdd(pl.rays + p, 1u); atomicAdd(pl.fetches + p, r.fetches);
                 }
+                terminal = r.material == 0 || sc.palette[r.material].metallic <= 0.0f;   // :289-292 lastIdx = w
+                if (terminal) cnt = wl + (r.material != 0 ? 1u : 0u);   // every hit record below the primary hit
+                else if (wl + 1 < MAX_REFLECTIONS) cont = true;          // else: 5 metallic bounces, lastIdx stays -1 (:298)
             }
-            const uint32_t child = wb.pixCap + warp_alloc(&wb.ctr->nb, act);
-            bool cont = false;
+            // all allocations of this bounce with ONE exposed round trip: lane 0 issues the (independent) atomics back to back
+            const bool first = wl == (uint32_t)w;
+            const unsigned mRec = first ? 0u : __ballot_sync(0xffffffffu, act), mQ = chain ? 0u : __ballot_sync(0xffffffffu, cont);
+            uint32_t incl = cnt;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d); if ((int)lane >= d) incl += t; }
+            const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+            uint32_t aRec = 0, aSq = 0, aQ = 0;
+            if (lane == 0) {
+                if (mRec) aRec = atomicAdd(&wb.ctr->nb, (uint32_t)__popc(mRec));
+                if (total) aSq = atomicAdd(&wb.ctr->nsq, total);
+                if (mQ) aQ = atomicAdd(&wb.ctr->qn[w + 1], (uint32_t)__popc(mQ));
+            }
+            aRec = __shfl_sync(0xffffffffu, aRec, 0); aSq = __shfl_sync(0xffffffffu, aSq, 0); aQ = __shfl_sync(0xffffffffu, aQ, 0);
+            const uint32_t child = first ? recBase + e : recBase2 + aRec + __popc(mRec & ltMask);
             if (act) {
                 RecQ* cr = wb.rec + 3 * (size_t)child;
                 cr[0] = mkq(r.pos, pxy);
                 cr[1] = mkq(r.normal, r.material | (wl << 8));
                 cr[2] = mkq(rd, ent.rec);
-                const bool terminal = r.material == 0 || sc.palette[r.material].metallic <= 0.0f;   // :289-292 lastIdx = w
                 if (terminal) {
                     wb.rec[3 * (size_t)ent.root + 2].w = child;
-                    // every record of the chain below the primary hit that is a hit gets its AO + shadow rays
-                    const uint32_t cnt = wl + (r.material != 0 ? 1u : 0u);
+                    uint32_t s = aSq + incl - cnt;
                     if (cnt) {
-                        uint32_t s = atomicAdd(&wb.ctr->nsq, cnt);
                         if (r.material != 0) wb.sq[s++] = child;
                         for (uint32_t k = ent.rec; k != ent.root; k = wb.rec[3 * (size_t)k + 2].w) wb.sq[s++] = k;
                     }
-                } else if (wl + 1 < MAX_REFLECTIONS) cont = true;    // else: 5 metallic bounces, lastIdx stays -1 (:298)
+                }
             }
             if (!chain) {
-                const uint32_t qi = warp_alloc(&wb.ctr->qn[w + 1], cont);
-                if (cont) { BounceEnt o; o.rec = child; o.root = ent.root; qout[qi] = o; }
+                if (cont) { BounceEnt o; o.rec = child; o.root = ent.root; qout[aQ + __popc(mQ & ltMask)] = o; }
                 break;
             }
             if (!__any_sync(0xffffffffu, cont)) break;
@@ -202,7 +223,7 @@ __global__ void __launch_bounds__(256) wave_anyhit_kernel(const SceneDev sc, con
 }
 
 // ---- any-hit wave on the ray engine (vrt_engine.cuh): LINEAR (isotropic field) or OCTANT (directional fields) ----
-template <int TRAVERSAL, int NEAR_STEPS, int FAR_STEPS>
+template <int TRAVERSAL, int NEAR_TOP, int FAR_TOP>
 __global__ void __launch_bounds__(ENGINE_WARPS * 32, 4) wave_anyhit_engine_kernel(const SceneDev sc, const FrameParams fp, const PlanesDev pl, const WaveBuf wb,
                                                                                 Counters* __restrict__ ctr, const uint32_t refillT, const uint32_t farShare, const int part, const uint32_t quota) {
     __shared__ EngineStash stashAll[ENGINE_WARPS];
@@ -319,17 +340,13 @@ __global__ void __launch_bounds__(ENGINE_WARPS * 32, 4) wave_anyhit_engine_kerne
         }
         // ---- lock-step DDA steps: a long round when every live lane can use it
         // a long round when at least farShare/8 of the live lanes can use all of it
-        const uint32_t nFar = __popc(__ballot_sync(0xffffffffu, alive && er.rem >= FAR_STEPS));
+        const uint32_t nFar = __popc(__ballot_sync(0xffffffffu, alive && er.rem >= 2 * FAR_TOP - 1));
         if (nFar * 8u >= (32u - nIdle) * farShare && nFar) {
-            ENG_STAT(1, lane == 0); ENG_STAT(3, alive); ENG_STAT(5, alive ? min(er.rem, FAR_STEPS) : 0);
-#pragma unroll
-            for (int k = 0; k < FAR_STEPS; k++) engine_step(er.l, er.rem, k);
-            er.rem = max(er.rem - FAR_STEPS, 0);
+            ENG_STAT(1, lane == 0); ENG_STAT(3, alive); ENG_STAT(5, alive ? min(er.rem, 2 * FAR_TOP - 1) : 0);
+            engine_round<FAR_TOP>(er.l, er.rem);
         } else {
-            ENG_STAT(0, lane == 0); ENG_STAT(2, alive); ENG_STAT(4, alive ? min(er.rem, NEAR_STEPS) : 0);
-#pragma unroll
-            for (int k = 0; k < NEAR_STEPS; k++) engine_step(er.l, er.rem, k);
-            er.rem = max(er.rem - NEAR_STEPS, 0);
+            ENG_STAT(0, lane == 0); ENG_STAT(2, alive); ENG_STAT(4, alive ? min(er.rem, 2 * NEAR_TOP - 1) : 0);
+            engine_round<NEAR_TOP>(er.l, er.rem);
         }
     }
     if (pending) retire(idx, kind, hitRes, fetchRes);
@@ -365,7 +382,7 @@ static cudaError_t launch_wave_t(const SceneDev& sc, const FrameParams& fp, cons
     if (!occAny) {
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occAny, wave_anyhit_kernel<T>, 256, 0);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occBounce, wave_bounce_kernel<T>, 128, 0);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occEngine, wave_anyhit_engine_kernel<T, 8, 32>, ENGINE_WARPS * 32, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occEngine, wave_anyhit_engine_kernel<T, ENGINE_NEAR_TOP, ENGINE_FAR_TOP>, ENGINE_WARPS * 32, 0);
         if (occAny < 1) occAny = 1;
         if (occBounce < 1) occBounce = 1;
         if (occEngine < 1) occEngine = 1;
@@ -373,6 +390,7 @@ static cudaError_t launch_wave_t(const SceneDev& sc, const FrameParams& fp, cons
     static const uint32_t quota = getenv("VRT_ENGINE_QUOTA") ? (uint32_t)atoi(getenv("VRT_ENGINE_QUOTA")) / ENGINE_CHUNK * ENGINE_CHUNK : ENGINE_BLOCK_QUOTA;
     // the wave from which the rest of every reflection chain runs in place (MAX_REFLECTIONS - 1: one launch per bounce)
     static const int bounceChain = getenv("VRT_BOUNCE_CHAIN") ? min(max(atoi(getenv("VRT_BOUNCE_CHAIN")), 0), MAX_REFLECTIONS - 1) : 2;
+    static const uint32_t bounceCapLate = getenv("VRT_BOUNCE_CAP_LATE") ? (uint32_t)atoi(getenv("VRT_BOUNCE_CAP_LATE")) : ROUND_CAP_SECONDARY;
     static const int farShare = getenv("VRT_ENGINE_FARSHARE") ? atoi(getenv("VRT_ENGINE_FARSHARE")) : 4;
     // measured (profiles/r1_overlap.log): beside-the-waves scheduling pays when the frame (or this rank's shard of it) is small and
     // the launches are tail-bound (1/8 of a 4K frame: -12 %), and costs ~1 % on a full 4K frame. VRT_OVERLAP=0/1 overrides.
@@ -394,8 +412,8 @@ static cudaError_t launch_wave_t(const SceneDev& sc, const FrameParams& fp, cons
         // blocks find registers at once instead of waiting for a side block to retire
         static const int sidePad = getenv("VRT_SIDE_PAD_KB") ? atoi(getenv("VRT_SIDE_PAD_KB")) * 1024 : 0;
         const size_t dyn = part == 1 ? (size_t)sidePad : 0;
-        if (dyn) cudaFuncSetAttribute(wave_anyhit_engine_kernel<T, 8, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
-        wave_anyhit_engine_kernel<T, 8, 32><<<grid, ENGINE_WARPS * 32, dyn, s>>>(sc, fp, pl, wb, ctr, (uint32_t)engineT(), (uint32_t)farShare, part, quota);
+        if (dyn) cudaFuncSetAttribute(wave_anyhit_engine_kernel<T, ENGINE_NEAR_TOP, ENGINE_FAR_TOP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+        wave_anyhit_engine_kernel<T, ENGINE_NEAR_TOP, ENGINE_FAR_TOP><<<grid, ENGINE_WARPS * 32, dyn, s>>>(sc, fp, pl, wb, ctr, (uint32_t)engineT(), (uint32_t)farShare, part, quota);
         n++;
     };
     if (overlap) {
@@ -407,7 +425,7 @@ static cudaError_t launch_wave_t(const SceneDev& sc, const FrameParams& fp, cons
     }
     if (reflect)
         for (int w = 0; w <= bounceChain; w++) {
-            wave_bounce_kernel<T><<<(unsigned)(sms * occBounce), 128, 0, stream>>>(sc, fp, pl, wb, ctr, w, w == bounceChain && w + 1 < MAX_REFLECTIONS);
+            wave_bounce_kernel<T><<<(unsigned)(sms * occBounce), 128, 0, stream>>>(sc, fp, pl, wb, ctr, w, w == bounceChain && w + 1 < MAX_REFLECTIONS, w == 0 ? ROUND_CAP_SECONDARY : bounceCapLate);
             n++;
         }
     if (ev) cudaEventRecord(ev[1], stream);

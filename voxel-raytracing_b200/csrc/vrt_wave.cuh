@@ -70,10 +70,10 @@ VRT_HD int wave_primary(const SceneDev& sc, const FrameParams& fp, int px, int p
 
 // one reflection bounce :282-297 from the hit (pos, normal, dir)
 template <int TRAVERSAL>
-VRT_HD TraceRes wave_bounce(const SceneDev& sc, V3 pos, V3 normal, V3 dir, V3& rd) {
+VRT_HD TraceRes wave_bounce(const SceneDev& sc, V3 pos, V3 normal, V3 dir, V3& rd, uint32_t roundCap = ROUND_CAP_SECONDARY) {
     rd = reflect3(dir, normal);
     const V3 rs = pos + normal * 0.01f;
-    return trace_ray<TRAVERSAL>(sc, rs, rd, MAX_RAY_STEPS, true, ROUND_CAP_SECONDARY);   // a miss carries no state (traceRay :180-195): see lin_round ANYHIT
+    return trace_ray<TRAVERSAL>(sc, rs, rd, MAX_RAY_STEPS, true, roundCap);   // a miss carries no state (traceRay :180-195): see lin_round ANYHIT
 }
 
 // ray i of a shaded hit: i < aoN -> AO ray i (:214-223, 64 steps), i == aoN -> shadow ray (:230-233, 512 steps)
