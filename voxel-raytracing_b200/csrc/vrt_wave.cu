@@ -108,12 +108,16 @@ __global__ void __launch_bounds__(128) wave_bounce_kernel(const SceneDev sc, con
     const uint32_t recBase2 = recBase + n;
     unsigned rays = 0, fetches = 0;
     // 32-ray groups are claimed one ahead: the counter's round trip overlaps the tracing of the current group
+    // (only while plenty of groups are left: near the end a group held in reserve by a busy warp would lengthen the tail)
+    const uint32_t reserve = 2u * 32u * (gridDim.x * (blockDim.x >> 5));
+    bool have = false;
     uint32_t nextE0 = 0;
-    if (lane == 0) nextE0 = atomicAdd(&wb.ctr->bcur[w], 32u);
     for (;;) {
+        if (!have && lane == 0) nextE0 = atomicAdd(&wb.ctr->bcur[w], 32u);
         const uint32_t e0 = __shfl_sync(0xffffffffu, nextE0, 0);
         if (e0 >= n) break;
-        if (lane == 0) nextE0 = atomicAdd(&wb.ctr->bcur[w], 32u);
+        have = e0 + reserve < n;
+        if (have && lane == 0) nextE0 = atomicAdd(&wb.ctr->bcur[w], 32u);
         const uint32_t e = e0 + lane;
         bool act = e < n;
         BounceEnt ent; ent.rec = 0; ent.root = 0;
