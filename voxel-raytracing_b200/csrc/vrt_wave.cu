@@ -361,11 +361,17 @@ __global__ void __launch_bounds__(ENGINE_WARPS * 32, 4) wave_anyhit_engine_kerne
 }
 
 __global__ void __launch_bounds__(256) wave_resolve_kernel(const SceneDev sc, const FrameParams fp, const PlanesDev pl, const WaveBuf wb) {
+    __shared__ float skyTab[64 * 3];          // skyColor of the 64 axis-code vectors (sky_of_normal)
+    if (threadIdx.x < 64) {
+        const V3 c = sky_color(sc, sky_axis_vector(threadIdx.x));
+        skyTab[3 * threadIdx.x] = c.x; skyTab[3 * threadIdx.x + 1] = c.y; skyTab[3 * threadIdx.x + 2] = c.z;
+    }
+    __syncthreads();
     const uint32_t n0 = wb.ctr->n0;
     const uint32_t aoN = (fp.pass_mask & VRT_PASS_AO) ? fp.aoSamples : 0u;
     for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n0; idx += gridDim.x * blockDim.x) {
         const uint32_t pxy = wb.rec[3 * (size_t)idx].w;
-        const V3 c = wave_resolve(sc, fp, wb, idx, aoN);
+        const V3 c = wave_resolve(sc, fp, wb, idx, aoN, skyTab);
         store_color(fp, pl, plane_index(fp, (int)(pxy & 0xffffu), (int)(pxy >> 16)), c);
     }
 }

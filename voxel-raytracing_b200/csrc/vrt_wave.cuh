@@ -106,12 +106,30 @@ VRT_HD float wave_ambient(uint32_t aoN, uint32_t hits) {
     return ambient;
 }
 
+// skyColor of a surface normal. Normals are normalize(mask * -step): almost always an axis vector whose components are exactly
+// +-0 or +-1 (the sign of a zero matters to atan2), so the resolve kernel tabulates skyColor for the 64 such vectors once per block
+// (skyTab, 3 floats each, computed by sky_color itself) instead of two binary64 inverse-trig calls per shaded record. Any other
+// normal (two axes stepped at once on a tie) goes through sky_color directly.
+VRT_HD uint32_t sky_axis_code(float c) { const uint32_t b = f2u(c); return (b >> 31 << 1) | ((b & 0x7fffffffu) == 0x3f800000u ? 1u : 0u); }
+VRT_HD bool sky_axis_ok(float c) { const uint32_t a = f2u(c) & 0x7fffffffu; return a == 0u || a == 0x3f800000u; }
+VRT_HD V3 sky_of_normal(const SceneDev& sc, V3 n, const float* skyTab) {
+    if (skyTab && sky_axis_ok(n.x) && sky_axis_ok(n.y) && sky_axis_ok(n.z)) {
+        const float* t = skyTab + 3u * (sky_axis_code(n.x) | (sky_axis_code(n.y) << 2) | (sky_axis_code(n.z) << 4));
+        return mk3(t[0], t[1], t[2]);
+    }
+    return sky_color(sc, n);
+}
+VRT_HD V3 sky_axis_vector(uint32_t code) {
+    const float v[4] = {0.0f, 1.0f, -0.0f, -1.0f};
+    return mk3(v[code & 3u], v[(code >> 2) & 3u], v[(code >> 4) & 3u]);
+}
+
 // colorHit :252-264 (+ color :236-248) of one record
 VRT_HD V3 wave_shade(const SceneDev& sc, const FrameParams& fp, uint32_t material, V3 normal, V3 dir, float ambient, bool shadowed,
-                     V3 reflection, uint32_t depth) {
+                     V3 reflection, uint32_t depth, const float* skyTab = nullptr) {
     if (material == 0) return sky_color(sc, dir);
     const V3 lightDir = mk3(fp.lightDir[0], fp.lightDir[1], fp.lightDir[2]);
-    const V3 ambientVec = (ambient * fp.ambientIntensity) * sky_color(sc, normal);
+    const V3 ambientVec = (ambient * fp.ambientIntensity) * sky_of_normal(sc, normal, skyTab);
     const vrt_material& mat = sc.palette[material];
     V3 diffuse = mk3(0.0f, 0.0f, 0.0f);
     if (!shadowed) {
@@ -132,7 +150,7 @@ VRT_HD void wave_results(const WaveBuf& wb, const FrameParams& fp, uint32_t idx,
 }
 
 // colorMainRay :298-306 for the primary record `root`: walk the reflection chain from its deepest record up
-VRT_HD V3 wave_resolve(const SceneDev& sc, const FrameParams& fp, const WaveBuf& wb, uint32_t root, uint32_t aoN) {
+VRT_HD V3 wave_resolve(const SceneDev& sc, const FrameParams& fp, const WaveBuf& wb, uint32_t root, uint32_t aoN, const float* skyTab = nullptr) {
     const RecQ r1 = wb.rec[3 * (size_t)root + 1], r2 = wb.rec[3 * (size_t)root + 2];
     V3 reflection = mk3(0.0f, 0.0f, 0.0f);
     uint32_t k = r2.w;
@@ -141,12 +159,12 @@ VRT_HD V3 wave_resolve(const SceneDev& sc, const FrameParams& fp, const WaveBuf&
         const uint32_t material = b1.w & 0xffu, depth = b1.w >> 8;
         float ambient = 0.0f; bool shadowed = false;
         if (material != 0) wave_results(wb, fp, k, aoN, ambient, shadowed);
-        reflection = reflection + wave_shade(sc, fp, material, q3(b1), q3(b2), ambient, shadowed, reflection, depth);
+        reflection = reflection + wave_shade(sc, fp, material, q3(b1), q3(b2), ambient, shadowed, reflection, depth, skyTab);
         k = b2.w;
     }
     float ambient; bool shadowed;
     wave_results(wb, fp, root, aoN, ambient, shadowed);
-    return wave_shade(sc, fp, r1.w & 0xffu, q3(r1), q3(r2), ambient, shadowed, reflection, 0u);
+    return wave_shade(sc, fp, r1.w & 0xffu, q3(r1), q3(r2), ambient, shadowed, reflection, 0u, skyTab);
 }
 
 }  // namespace vrt
