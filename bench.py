@@ -46,6 +46,8 @@ def parse_args():
     ap.add_argument("--shard", type=int, nargs=2, default=None, metavar=("RANK", "WORLD"),
                     help="debug: render only the tile shard RANK of WORLD on one GPU (what one rank of an N-GPU run does), no gather")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--frames-in-flight", type=int, default=3, help="frame objects used round-robin (>= 2)")
+    ap.add_argument("--serial-frames", action="store_true", help="one stream: frame k+1 starts when frame k has finished (default: two frames in flight on their own streams)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
     return ap.parse_args()
 
@@ -262,34 +264,38 @@ def run_vrt(args):
     st = configs.settings_for(cfg, gbuffer=not args.no_gbuffer)
     st.traversal = args.traversal
     st.pipeline = args.pipeline
-    # Two frames in flight (as in the reference, source/engine/engine.hpp:19): two render passes used alternately.
-    rp, rp2 = pyvrt.VoxelRenderPass(ctx, scene, st), pyvrt.VoxelRenderPass(ctx, scene, st)
-    passes = (rp, rp2)
+    # Two frames in flight (as in the reference, source/engine/engine.hpp:19): two render passes used alternately, each frame on
+    # a stream of its own so that the kernels of frame k+1 fill the tails of frame k's (--serial-frames: one stream, back to back).
+    if not args.serial_frames:
+        ctx.set_concurrent_frames(True)
+    F = max(2, args.frames_in_flight)
+    passes = tuple(pyvrt.VoxelRenderPass(ctx, scene, st) for _ in range(F))
     dev = torch.device("cuda", local)
     ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
     final = "denoised" if cfg["denoise"] and world == 1 else "color"
     frame_bytes = W * H * 4
-    host2 = [torch.empty(frame_bytes, dtype=torch.uint8, pin_memory=True) for _ in range(2)] if rank == 0 else None
+    host2 = [torch.empty(frame_bytes, dtype=torch.uint8, pin_memory=True) for _ in range(F)] if rank == 0 else None
     # N>1: the colour shards of frame k travel to rank 0 (NCCL gather) on a communication stream while the context stream already
     # traces frame k+1; rank 0 assembles frame k (detile kernel, same communication stream) once its shards are in.
-    gathered, asm2, comm, copy_stream = [None, None], None, None, None
+    gathered, asm2, comm, copy_stream = [None] * F, None, None, None
     if world > 1:
         comm = torch.cuda.Stream(device=dev, priority=-1)
         if rank == 0:
-            asm2 = [torch.empty(frame_bytes, dtype=torch.uint8, device="cuda") for _ in range(2)]
+            asm2 = [torch.empty(frame_bytes, dtype=torch.uint8, device="cuda") for _ in range(F)]
             copy_stream = torch.cuda.Stream(device=dev)
-    ev_rendered = [torch.cuda.Event() for _ in range(2)]
-    ev_gathered = [torch.cuda.Event() for _ in range(2)]
-    ev_ready = [torch.cuda.Event() for _ in range(2)]
-    ev_copied = [torch.cuda.Event() for _ in range(2)]
-    sent, copied_pending = [False, False], [False, False]
+    ev_rendered = [torch.cuda.Event() for _ in range(F)]
+    ev_gathered = [torch.cuda.Event() for _ in range(F)]
+    ev_ready = [torch.cuda.Event() for _ in range(F)]
+    ev_copied = [torch.cuda.Event() for _ in range(F)]
+    sent, copied_pending = [False] * F, [False] * F
+    fstream = [None] * F                                   # the stream each frame object renders on
     last_slot = None
 
     def submit(k, readback=False):
         """Queue frame k: render this rank's tiles (+ N>1: gather and assemble; + readback: copy the finished frame to pinned host
         memory). Returns the frame and the kernels launched outside vrt_render (the library counts its own)."""
         nonlocal last_slot
-        slot = k & 1
+        slot = k % F
         cam = configs.make_camera(args.config, bounds, size, k)
         if world == 1:
             fr = passes[slot].record(cam)
@@ -297,9 +303,11 @@ def run_vrt(args):
                 fr.download_async(final, host2[slot].numpy())
             return fr, 0
         if sent[slot]:
-            ext.wait_event(ev_gathered[slot])                # this slot's shard buffer is still being sent
+            fstream[slot].wait_event(ev_gathered[slot])      # this slot's shard buffer is still being sent
         fr = passes[slot].record(cam)
-        ev_rendered[slot].record(ext)
+        if fstream[slot] is None:
+            fstream[slot] = torch.cuda.ExternalStream(fr.stream, device=dev)
+        ev_rendered[slot].record(fstream[slot])
         ptr, n = fr.plane_ptr("color")
         shard = torch.as_tensor(_DevBuf(ptr, n), device=dev)
         if rank == 0 and gathered[slot] is None:
@@ -326,13 +334,14 @@ def run_vrt(args):
         return fr, launches
 
     def drain():
-        """Join the communication stream into the context stream (the timed region ends on the context stream)."""
+        """Join the frames' streams and the communication stream into the context stream (the timed region ends there)."""
+        ctx.join()
         if world > 1 and last_slot is not None:
             ext.wait_event(ev_gathered[last_slot])
         return 0
 
     def wait_readback(k):
-        slot = k & 1
+        slot = k % F
         if rank != 0:
             return
         if world == 1:
@@ -346,7 +355,7 @@ def run_vrt(args):
             dist.barrier()
 
     # ---- warm-up, then an untimed counting pass over the K timed poses (rays / voxel visits / kernel time per frame)
-    for k in range(max(args.warmup, 2)):
+    for k in range(max(args.warmup, F)):
         submit(k)
     drain()
     barrier()
@@ -382,22 +391,25 @@ def run_vrt(args):
 
     # ---- timed region 2 (e2e): the same K frames through the public API with the finished frame read back into pinned host
     # memory EVERY step; per-step inputs (camera block + settings) travel as kernel parameters. The read-back of frame k runs on
-    # the copy stream beside the kernels of frame k+1, and the host waits for frame k-1 before it queues frame k+1. All K
-    # read-backs complete inside the timed region.
+    # the copy stream beside the kernels of the following frames, and the host waits for frame k-(F-1) before it queues frame
+    # k+1 (F frame objects in flight). All K read-backs complete inside the timed region.
     if args.shard and world == 1:                           # debug mode: a shard is not a frame, there is nothing to read back
         t_e2e = ms * 1e-3
     else:
-        for k in range(2):
+        for k in range(F):
             submit(k, True)
-        drain(); wait_readback(0); wait_readback(1)
+        drain()
+        for k in range(F):
+            wait_readback(k)
         barrier()
         t0 = time.perf_counter()
         for k in range(args.steps):
             submit(k, True)
-            if k > 0:
-                wait_readback(k - 1)
+            if k >= F - 1:
+                wait_readback(k - (F - 1))            # the host runs at most F-1 frames ahead of the finished read-backs
         drain()
-        wait_readback(args.steps - 1)
+        for k in range(max(0, args.steps - (F - 1)), args.steps):
+            wait_readback(k)
         barrier()
         t_e2e = time.perf_counter() - t0
 
@@ -428,7 +440,7 @@ def run_vrt(args):
         line = {"metric": METRIC, "value": rays_all / (ms * 1e-3) / 1e6, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": config_blob(cfg, args.config, args.whd, size, {"parallelism": f"tiles{world}" if world > 1 else "single", "traversal": args.traversal, "pipeline": args.pipeline,
-                                                                         "gathered_plane": "color RGBA8" if world > 1 else None, "frames_in_flight": 2,
+                                                                         "gathered_plane": "color RGBA8" if world > 1 else None, "frames_in_flight": F, "frame_streams": "one" if args.serial_frames else "per frame",
                                                                          "exchange": "NCCL gather of frame k on a communication stream beside the tracing of frame k+1, detile on rank 0" if world > 1 else None}),
                 "rays_per_frame": rays_all / args.steps, "voxel_visits_per_frame": fetches_all / args.steps,
                 "Mrays_per_s_primary": pixels_all / (ms * 1e-3) / 1e6,
@@ -450,7 +462,8 @@ def run_vrt(args):
     barrier()
     # tensors that were used on the context's stream must be returned to torch's allocator while that stream still exists
     gathered = host2 = asm2 = None
-    rp2.frame.release()
+    for p_ in passes[1:]:
+        p_.frame.release()
     del submit
     import gc
     gc.collect()

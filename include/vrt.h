@@ -134,6 +134,12 @@ const char* vrt_version(void);
 int vrt_device_info(vrt_context*, int* sm_count, size_t* l2_bytes, size_t* hbm_bytes);
 int vrt_context_sync(vrt_context*);                             /* wait for everything queued on the context stream */
 void* vrt_context_stream(vrt_context*);                         /* cudaStream_t the context launches on */
+/* Frames in flight (the reference keeps two: source/engine/engine.hpp:19). With this on, every frame object created afterwards
+ * renders on a stream of its own, forked from the context stream at each vrt_render, so the kernels of one frame fill the tails
+ * of another's. vrt_context_join: the context stream waits for everything queued on the frames' streams so far;
+ * vrt_context_sync waits on the host for all of it; vrt_frame_stream: the cudaStream_t a frame's work is queued on. */
+int vrt_context_set_concurrent_frames(vrt_context*, int on);
+int vrt_context_join(vrt_context*);
 /* device scratch owned by the caller (outputs of vrt_denoise / vrt_assemble, gather staging) */
 int vrt_buffer_alloc(vrt_context*, size_t bytes, void** d_ptr);
 void vrt_buffer_free(vrt_context*, void* d_ptr);
@@ -178,6 +184,7 @@ int vrt_frame_download(vrt_frame*, int plane, void* host_dst, size_t bytes);
 int vrt_frame_download_async(vrt_frame*, int plane, void* host_dst, size_t bytes);
 int vrt_frame_download_wait(vrt_frame*);
 int vrt_frame_stats_get(vrt_frame*, vrt_frame_stats* out);       /* syncs */
+void* vrt_frame_stream(vrt_frame*);
 void vrt_frame_release(vrt_frame*);
 
 /* Stand-alone denoiser on host planes already resident on device: DenoiserStage::record. */

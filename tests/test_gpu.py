@@ -237,6 +237,36 @@ def test_two_frames_in_flight_readback(gpu_ctx):
     gs.destroy()
 
 
+def test_concurrent_frames_are_byte_identical(gpu_ctx):
+    """vrt_context_set_concurrent_frames: two frame objects render on streams of their own and overlap on the GPU; every frame
+    must equal the frame rendered alone (per-frame buffers, counters and side streams: nothing is shared between frames)."""
+    gs = pyvrt.VoxelScene.generate(gpu_ctx, 1, 42, 160, 160, 160)
+    gs.set_noise(assets.noise_standin()); gs.set_skybox(assets.sky_standin(256, 128))
+    st = pyvrt.default_settings(); st.denoise.enable = 0
+    cams = [cam_to_py(look_at_camera(gs.bounds, (512, 288), (-30 + 7 * k, 200, -50), (80, 80, 80), frame=k)) for k in range(8)]
+    solo = pyvrt.VoxelRenderPass(gpu_ctx, gs, st)
+    want = [solo.record(c).download("color").copy() for c in cams]
+    stats = solo.frame.stats()
+    gpu_ctx.set_concurrent_frames(True)
+    try:
+        passes = [pyvrt.VoxelRenderPass(gpu_ctx, gs, st) for _ in range(2)]
+        got = []
+        for k in range(0, len(cams), 2):
+            frames = [passes[j].record(cams[k + j]) for j in range(2)]           # both queued before either is read
+            assert frames[0].stream != frames[1].stream and frames[0].stream != gpu_ctx.stream
+            got += [frames[0].download("color").copy(), frames[1].download("color").copy()]
+        gpu_ctx.join(); gpu_ctx.sync()
+        assert passes[(len(cams) - 1) & 1].frame.stats()["rays"] == stats["rays"]
+        for p in passes:
+            p.frame.release()
+    finally:
+        gpu_ctx.set_concurrent_frames(False)
+    assert len(got) == len(want)
+    for a, b in zip(got, want):
+        assert np.array_equal(a, b)
+    solo.frame.release(); gs.destroy()
+
+
 def test_degenerate_rays_on_gpu(gpu_ctx):
     rng = np.random.default_rng(9)
     vol = random_volume(rng, (24, 24, 24), 0.04); pal = random_palette(rng)

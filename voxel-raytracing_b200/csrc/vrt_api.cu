@@ -25,6 +25,8 @@ struct vrt_context {
     cudaStream_t copyStream = nullptr;   // asynchronous read-backs (vrt_frame_download_async)
     WaveSide side{};                     // low-priority stream + fork/join events (launch_wavefront)
     cudaDeviceProp prop{};
+    bool concurrent = false;             // frames created from now on render on their own streams (vrt_context_set_concurrent_frames)
+    std::vector<struct vrt_frame*> frames;
 };
 
 struct vrt_scene {
@@ -54,6 +56,11 @@ struct vrt_frame {
     bool staged = false;
     bool denoised = false;
     uint32_t launches = 0, out_mask = 0;
+    cudaStream_t stream = nullptr;     // the stream this frame's work is queued on: the context's, or its own (concurrent frames)
+    WaveSide side{};
+    cudaEvent_t fork = nullptr;        // own stream: orders the frame after what the context stream held when vrt_render was called
+    cudaEvent_t joined = nullptr;      // own stream: vrt_context_join
+    bool own = false;
     WaveBuf wb{};                      // wavefront pipeline buffers (allocated on first use)
     uint32_t wbRays = 0;               // result planes allocated in wb.res
 };
@@ -108,9 +115,24 @@ extern "C" int vrt_context_sync(vrt_context* c) {
     if (!c) return fail(VRT_E_INVALID, "ctx is null");
     CU(cudaSetDevice(c->device));
     CU(cudaStreamSynchronize(c->stream));
+    for (vrt_frame* f : c->frames) if (f->own) CU(cudaStreamSynchronize(f->stream));
     return VRT_OK;
 }
 extern "C" void* vrt_context_stream(vrt_context* c) { return c ? (void*)c->stream : nullptr; }
+// Frames in flight: with this on, every frame object created afterwards renders on a stream of its own (forked from the context
+// stream at each vrt_render), so that the kernels of one frame fill the tails of another's. vrt_context_join makes the context
+// stream wait for everything queued on the frames' streams so far; vrt_context_sync waits on the host for all of it.
+extern "C" int vrt_context_set_concurrent_frames(vrt_context* c, int on) {
+    if (!c) return fail(VRT_E_INVALID, "ctx is null");
+    c->concurrent = on != 0;
+    return VRT_OK;
+}
+extern "C" int vrt_context_join(vrt_context* c) {
+    if (!c) return fail(VRT_E_INVALID, "ctx is null");
+    CU(cudaSetDevice(c->device));
+    for (vrt_frame* f : c->frames) if (f->own) { CU(cudaEventRecord(f->joined, f->stream)); CU(cudaStreamWaitEvent(c->stream, f->joined, 0)); }
+    return VRT_OK;
+}
 
 // ------------------------------------------------------------------------------------------------ scene
 extern "C" int vrt_buffer_alloc(vrt_context* c, size_t bytes, void** d_ptr) {
@@ -330,13 +352,19 @@ extern "C" void vrt_frame_release(vrt_frame* f) {
     if (f->copyPending) cudaEventSynchronize(f->copied);
     if (f->rendered) cudaEventDestroy(f->rendered);
     if (f->copied) cudaEventDestroy(f->copied);
+    if (f->own) {
+        if (f->stream) { cudaStreamSynchronize(f->stream); cudaStreamDestroy(f->stream); }
+        if (f->fork) cudaEventDestroy(f->fork);
+        if (f->joined) cudaEventDestroy(f->joined);
+    }
+    if (f->ctx) { auto& v = f->ctx->frames; for (size_t i = 0; i < v.size(); i++) if (v[i] == f) { v.erase(v.begin() + i); break; } }
     delete f;
 }
 
 static int frame_ensure_plane(vrt_frame* f, int plane) {
     if (f->planes[plane]) return VRT_OK;
     CU(cudaMalloc(&f->planes[plane], f->pixels * kPlaneBpp[plane]));
-    CU(cudaMemsetAsync(f->planes[plane], 0, f->pixels * kPlaneBpp[plane], f->ctx->stream));
+    CU(cudaMemsetAsync(f->planes[plane], 0, f->pixels * kPlaneBpp[plane], f->stream));
     return VRT_OK;
 }
 
@@ -380,7 +408,16 @@ static int frame_create(vrt_context* c, int W, int H, vrt_frame** out) {
     for (int k = 0; k < 3; k++) if (e == cudaSuccess) e = cudaEventCreate(&f->es[k]);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&f->rendered, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&f->copied, cudaEventDisableTiming);
+    if (c->concurrent) {
+        f->own = true;
+        int prLow = 0, prHigh = 0;
+        if (e == cudaSuccess) e = cudaDeviceGetStreamPriorityRange(&prLow, &prHigh);
+        if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&f->stream, cudaStreamNonBlocking, prHigh);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&f->fork, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&f->joined, cudaEventDisableTiming);
+    } else { f->stream = c->stream; f->side = c->side; }
     if (e != cudaSuccess) { vrt_frame_release(f); return fail(VRT_E_CUDA, cudaGetErrorString(e)); }
+    c->frames.push_back(f);
     *out = f;
     return VRT_OK;
 }
@@ -404,7 +441,7 @@ static void denoise_taps(int mode, DenoiseTaps& t) {
     }
 }
 
-static int run_denoise(vrt_context* c, const void* color, const void* normal, const void* position, int W, int H,
+static int run_denoise(vrt_context* c, cudaStream_t stream, const void* color, const void* normal, const void* position, int W, int H,
                        const vrt_denoiser_settings* ds, void* ping[2], int* lastOut, uint32_t* launches) {
     if (ds->iterations < 1 || ds->iterations > 10) return fail(VRT_E_INVALID, "denoiser iterations must be 1..10 (MAX_DENOISER_PASSES)");
     if (ds->mode != VRT_DENOISE_AS_EXECUTED && ds->mode != VRT_DENOISE_AS_INTENDED) return fail(VRT_E_INVALID, "bad denoise mode");
@@ -418,7 +455,7 @@ static int run_denoise(vrt_context* c, const void* color, const void* normal, co
         it.phiPos = 1.0f / (float)i * ds->phiPos0;
         it.stepWidth = (float)i * ds->stepWidth + 1.0f;
         const int tgt = i % 2;
-        cudaError_t e = launch_denoise((const uint8_t*)src, (const int8_t*)normal, (const float*)position, (uint8_t*)ping[tgt], W, H, taps, it, c->stream);
+        cudaError_t e = launch_denoise((const uint8_t*)src, (const int8_t*)normal, (const float*)position, (uint8_t*)ping[tgt], W, H, taps, it, stream);
         if (e != cudaSuccess) return fail(VRT_E_CUDA, cudaGetErrorString(e));
         if (launches) (*launches)++;
         src = ping[tgt]; last = tgt;
@@ -478,25 +515,28 @@ extern "C" int vrt_render(vrt_context* c, const vrt_scene* s, const vrt_camera* 
     pl.color_f32 = (float*)f->planes[VRT_PLANE_COLOR_RGB32F]; pl.rays = (uint32_t*)f->planes[VRT_PLANE_RAYS_U32];
     pl.fetches = (uint32_t*)f->planes[VRT_PLANE_FETCHES_U32];
 
-    if (f->copyPending) { CU(cudaStreamWaitEvent(c->stream, f->copied, 0)); f->copyPending = false; }   // a read-back of the previous content
+    const cudaStream_t fs = f->stream;
+    if (f->own) { CU(cudaEventRecord(f->fork, c->stream)); CU(cudaStreamWaitEvent(fs, f->fork, 0)); }
+    if (f->copyPending) { CU(cudaStreamWaitEvent(fs, f->copied, 0)); f->copyPending = false; }   // a read-back of the previous content
     f->launches = 0; f->out_mask = out_mask; f->denoised = false;
-    CU(cudaMemsetAsync(f->ctr, 0, sizeof(Counters), c->stream));
-    CU(cudaEventRecord(f->e0, c->stream));
+    CU(cudaMemsetAsync(f->ctr, 0, sizeof(Counters), fs));
+    CU(cudaEventRecord(f->e0, fs));
     cudaError_t e;
     f->staged = wavefront && f->localTiles > 0;
-    if (wavefront) e = launch_wavefront(sc, fp, pl, f->ctr, f->wb, c->prop.multiProcessorCount, c->stream, &c->side, &f->launches, f->es);
-    else { e = launch_render(sc, fp, pl, f->ctr, c->stream); f->launches++; }
+    // frames on their own streams fill each other's tails: the any-hit side stream (launch_wave_t) is for a frame that runs alone
+    if (wavefront) e = launch_wavefront(sc, fp, pl, f->ctr, f->wb, c->prop.multiProcessorCount, fs, f->own ? nullptr : &f->side, &f->launches, f->es);
+    else { e = launch_render(sc, fp, pl, f->ctr, fs); f->launches++; }
     if (e != cudaSuccess) { if (!*frame) vrt_frame_release(f); return fail(VRT_E_CUDA, cudaGetErrorString(e)); }
-    CU(cudaEventRecord(f->e1, c->stream));
+    CU(cudaEventRecord(f->e1, fs));
     if (st->denoise.enable) {
         int last = 0;
-        rc = run_denoise(c, pl.color, pl.normal, pl.position, W, H, &st->denoise, f->ping, &last, &f->launches);
+        rc = run_denoise(c, fs, pl.color, pl.normal, pl.position, W, H, &st->denoise, f->ping, &last, &f->launches);
         if (rc) { if (!*frame) vrt_frame_release(f); return rc; }
         // expose the final ping-pong target as the DENOISED plane without a copy
         if (last == 1) { void* t = f->ping[0]; f->ping[0] = f->ping[1]; f->ping[1] = t; }
         f->denoised = true;
     }
-    CU(cudaEventRecord(f->e2, c->stream));
+    CU(cudaEventRecord(f->e2, fs));
     *frame = f;
     return VRT_OK;
 }
@@ -504,9 +544,10 @@ extern "C" int vrt_render(vrt_context* c, const vrt_scene* s, const vrt_camera* 
 extern "C" int vrt_frame_sync(vrt_frame* f) {
     if (!f) return fail(VRT_E_INVALID, "null frame");
     CU(cudaSetDevice(f->ctx->device));
-    CU(cudaStreamSynchronize(f->ctx->stream));
+    CU(cudaStreamSynchronize(f->stream));
     return VRT_OK;
 }
+extern "C" void* vrt_frame_stream(vrt_frame* f) { return f ? (void*)f->stream : nullptr; }
 extern "C" int vrt_frame_plane(vrt_frame* f, int plane, void** device_ptr, size_t* bytes) {
     if (!f || plane < 0 || plane >= VRT_PLANE_COUNT) return fail(VRT_E_INVALID, "bad plane");
     void* p = plane == VRT_PLANE_DENOISED_RGBA8 ? (f->denoised ? f->ping[0] : nullptr) : f->planes[plane];
@@ -521,8 +562,8 @@ extern "C" int vrt_frame_download(vrt_frame* f, int plane, void* host_dst, size_
     if (rc) return rc;
     if (!host_dst || bytes != n) return fail(VRT_E_INVALID, "size mismatch");
     CU(cudaSetDevice(f->ctx->device));
-    CU(cudaMemcpyAsync(host_dst, p, n, cudaMemcpyDeviceToHost, f->ctx->stream));
-    CU(cudaStreamSynchronize(f->ctx->stream));
+    CU(cudaMemcpyAsync(host_dst, p, n, cudaMemcpyDeviceToHost, f->stream));
+    CU(cudaStreamSynchronize(f->stream));
     return VRT_OK;
 }
 extern "C" int vrt_frame_download_async(vrt_frame* f, int plane, void* host_dst, size_t bytes) {
@@ -532,7 +573,7 @@ extern "C" int vrt_frame_download_async(vrt_frame* f, int plane, void* host_dst,
     if (!host_dst || bytes != n) return fail(VRT_E_INVALID, "size mismatch");
     vrt_context* c = f->ctx;
     CU(cudaSetDevice(c->device));
-    CU(cudaEventRecord(f->rendered, c->stream));
+    CU(cudaEventRecord(f->rendered, f->stream));
     CU(cudaStreamWaitEvent(c->copyStream, f->rendered, 0));
     CU(cudaMemcpyAsync(host_dst, p, n, cudaMemcpyDeviceToHost, c->copyStream));
     CU(cudaEventRecord(f->copied, c->copyStream));
@@ -549,7 +590,7 @@ extern "C" int vrt_frame_download_wait(vrt_frame* f) {
 extern "C" int vrt_frame_stats_get(vrt_frame* f, vrt_frame_stats* out) {
     if (!f || !out) return fail(VRT_E_INVALID, "null argument");
     CU(cudaSetDevice(f->ctx->device));
-    CU(cudaStreamSynchronize(f->ctx->stream));
+    CU(cudaStreamSynchronize(f->stream));
     Counters h{};
     CU(cudaMemcpy(&h, f->ctr, sizeof(h), cudaMemcpyDeviceToHost));
     memset(out, 0, sizeof(*out));
@@ -584,7 +625,7 @@ extern "C" int vrt_denoise(vrt_context* c, const void* d_color, const void* d_no
     // make the last iteration land in d_out: iteration i writes ping[i%2]; swap if the last index is odd
     if (((ds->iterations - 1) % 2) == 1) { void* t = ping[0]; ping[0] = ping[1]; ping[1] = t; }
     int last = 0; uint32_t n = 0;
-    int rc = run_denoise(c, d_color, d_normal, d_position, w, h, ds, ping, &last, &n);
+    int rc = run_denoise(c, c->stream, d_color, d_normal, d_position, w, h, ds, ping, &last, &n);
     cudaError_t e = cudaStreamSynchronize(c->stream);
     void* scratch = ping[0] == d_out ? ping[1] : ping[0];
     if (scratch) cudaFree(scratch);

@@ -75,6 +75,7 @@ def lib():
         L.vrt_last_error.restype = C.c_char_p
         L.vrt_version.restype = C.c_char_p
         L.vrt_context_stream.restype = C.c_void_p
+        L.vrt_frame_stream.restype = C.c_void_p
         for fn in ("vrt_context_destroy", "vrt_scene_destroy", "vrt_frame_release", "vrt_host_free", "vrt_camera_vectors", "vrt_default_settings"):
             getattr(L, fn).restype = None
         _lib = L
@@ -144,6 +145,14 @@ class Context:
     @property
     def stream(self):
         return lib().vrt_context_stream(self.h)
+
+    def set_concurrent_frames(self, on=True):
+        """Frame objects created afterwards render on streams of their own (frames in flight overlap on the GPU)."""
+        _ck(lib().vrt_context_set_concurrent_frames(self.h, 1 if on else 0))
+
+    def join(self):
+        """The context stream waits for everything queued on the frames' own streams so far."""
+        _ck(lib().vrt_context_join(self.h))
 
     def close(self):
         if self.h:
@@ -229,6 +238,11 @@ class Frame:
 
     def sync(self):
         _ck(lib().vrt_frame_sync(self.h))
+
+    @property
+    def stream(self):
+        """cudaStream_t this frame's work is queued on (the context's unless frames are concurrent)."""
+        return lib().vrt_frame_stream(self.h)
 
     def download_async(self, name, out):
         """Queue the read-back behind this frame's kernels on the copy stream (out: pinned uint8 buffer); pair with download_wait()."""
