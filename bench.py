@@ -47,6 +47,8 @@ def parse_args():
                     help="debug: render only the tile shard RANK of WORLD on one GPU (what one rank of an N-GPU run does), no gather")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--frames-in-flight", type=int, default=3, help="frame objects used round-robin (>= 2)")
+    ap.add_argument("--exchange", choices=["gather", "push"], default="gather",
+                    help="N>1: NCCL gather + de-tile on rank 0, or every rank stores its tiles straight into rank 0's frame over NVLink (symmetric memory)")
     ap.add_argument("--serial-frames", action="store_true", help="one stream: frame k+1 starts when frame k has finished (default: two frames in flight on their own streams)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
     return ap.parse_args()
@@ -278,11 +280,21 @@ def run_vrt(args):
     # N>1: the colour shards of frame k travel to rank 0 (NCCL gather) on a communication stream while the context stream already
     # traces frame k+1; rank 0 assembles frame k (detile kernel, same communication stream) once its shards are in.
     gathered, asm2, comm, copy_stream = [None] * F, None, None, None
+    sym = hdl = None
     if world > 1:
         comm = torch.cuda.Stream(device=dev, priority=-1)
         if rank == 0:
-            asm2 = [torch.empty(frame_bytes, dtype=torch.uint8, device="cuda") for _ in range(F)]
             copy_stream = torch.cuda.Stream(device=dev)
+        if args.exchange == "push":
+            # rank 0's buffer holds the F assembled frames; every rank maps it (peer memory over NVLink / NVSwitch)
+            import torch.distributed._symmetric_memory as symm_mem
+            sym = symm_mem.empty(F * frame_bytes, dtype=torch.uint8, device=dev)
+            hdl = symm_mem.rendezvous(sym, dist.group.WORLD)
+            frame0_ptr = int(hdl.buffer_ptrs[0])
+            if rank == 0:
+                asm2 = [sym[k * frame_bytes:(k + 1) * frame_bytes] for k in range(F)]
+        elif rank == 0:
+            asm2 = [torch.empty(frame_bytes, dtype=torch.uint8, device="cuda") for _ in range(F)]
     ev_rendered = [torch.cuda.Event() for _ in range(F)]
     ev_gathered = [torch.cuda.Event() for _ in range(F)]
     ev_ready = [torch.cuda.Event() for _ in range(F)]
@@ -310,24 +322,31 @@ def run_vrt(args):
         ev_rendered[slot].record(fstream[slot])
         ptr, n = fr.plane_ptr("color")
         shard = torch.as_tensor(_DevBuf(ptr, n), device=dev)
-        if rank == 0 and gathered[slot] is None:
-            gathered[slot] = torch.empty((world, n), dtype=torch.uint8, device="cuda")
         launches = 0
         comm.wait_event(ev_rendered[slot])
         with torch.cuda.stream(comm):
-            dist.gather(shard, list(gathered[slot].unbind(0)) if rank == 0 else None, dst=0)
-            if rank == 0:
-                if copied_pending[slot]:
-                    comm.wait_event(ev_copied[slot])         # asm2[slot] is still being read back
-                pyvrt.assemble(ctx, gathered[slot].data_ptr(), world, size, "color", asm2[slot].data_ptr(), stream=comm.cuda_stream)
-                launches = 1
+            if rank == 0 and copied_pending[slot]:
+                comm.wait_event(ev_copied[slot])             # asm2[slot] is still being read back
+            if args.exchange == "push":
                 if readback:
-                    ev_ready[slot].record(comm)
-                    copy_stream.wait_event(ev_ready[slot])
-                    with torch.cuda.stream(copy_stream):
-                        host2[slot].copy_(asm2[slot], non_blocking=True)
-                        ev_copied[slot].record(copy_stream)
-                    copied_pending[slot] = True
+                    hdl.barrier(channel=0)                   # rank 0 has finished with what this slot held
+                fr.push_tiles("color", frame0_ptr + slot * frame_bytes, stream=comm.cuda_stream)
+                hdl.barrier(channel=1)                       # every rank's tiles of frame k are in rank 0's buffer
+                launches = 1
+            else:
+                if rank == 0 and gathered[slot] is None:
+                    gathered[slot] = torch.empty((world, n), dtype=torch.uint8, device="cuda")
+                dist.gather(shard, list(gathered[slot].unbind(0)) if rank == 0 else None, dst=0)
+                if rank == 0:
+                    pyvrt.assemble(ctx, gathered[slot].data_ptr(), world, size, "color", asm2[slot].data_ptr(), stream=comm.cuda_stream)
+                    launches = 1
+            if rank == 0 and readback:
+                ev_ready[slot].record(comm)
+                copy_stream.wait_event(ev_ready[slot])
+                with torch.cuda.stream(copy_stream):
+                    host2[slot].copy_(asm2[slot], non_blocking=True)
+                    ev_copied[slot].record(copy_stream)
+                copied_pending[slot] = True
             ev_gathered[slot].record(comm)                   # shards sent / frame assembled
         sent[slot] = True
         last_slot = slot
@@ -354,6 +373,22 @@ def run_vrt(args):
         if world > 1:
             dist.barrier()
 
+    if world > 1 and args.exchange == "push":
+        # self-check of the peer-memory plumbing (outside every timed region): frame 0 assembled by push must equal the same frame
+        # assembled by NCCL gather + de-tile
+        fr0, _ = submit(0)
+        drain(); barrier()
+        ptr, n = fr0.plane_ptr("color")
+        g = torch.empty((world, n), dtype=torch.uint8, device="cuda") if rank == 0 else None
+        dist.gather(torch.as_tensor(_DevBuf(ptr, n), device=dev), list(g.unbind(0)) if rank == 0 else None, dst=0)
+        if rank == 0:
+            ref = torch.empty(frame_bytes, dtype=torch.uint8, device="cuda")
+            pyvrt.assemble(ctx, g.data_ptr(), world, size, "color", ref.data_ptr(), stream=torch.cuda.current_stream().cuda_stream)
+            torch.cuda.synchronize()
+            if not torch.equal(ref, asm2[0]):
+                raise SystemExit("push exchange: assembled frame differs from the gathered one")
+        barrier()
+
     # ---- warm-up, then an untimed counting pass over the K timed poses (rays / voxel visits / kernel time per frame)
     for k in range(max(args.warmup, F)):
         submit(k)
@@ -379,10 +414,12 @@ def run_vrt(args):
     barrier()
     with torch.cuda.stream(ext):
         e0.record()
+    t_host = time.perf_counter()
     for k in range(args.steps):
         _, n = submit(k)
         launches += n
     launches += drain()
+    t_host = time.perf_counter() - t_host        # host time to QUEUE the K frames (must stay below the device time, else the GPU starves)
     with torch.cuda.stream(ext):
         e1.record()
     barrier()
@@ -441,7 +478,7 @@ def run_vrt(args):
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": config_blob(cfg, args.config, args.whd, size, {"parallelism": f"tiles{world}" if world > 1 else "single", "traversal": args.traversal, "pipeline": args.pipeline,
                                                                          "gathered_plane": "color RGBA8" if world > 1 else None, "frames_in_flight": F, "frame_streams": "one" if args.serial_frames else "per frame",
-                                                                         "exchange": "NCCL gather of frame k on a communication stream beside the tracing of frame k+1, detile on rank 0" if world > 1 else None}),
+                                                                         "exchange": ("NCCL gather of frame k on a communication stream beside the tracing of the next frames, detile on rank 0" if args.exchange == "gather" else "every rank stores its tiles of frame k straight into rank 0's frame (symmetric memory over NVLink) on a communication stream; device-side barriers") if world > 1 else None}),
                 "rays_per_frame": rays_all / args.steps, "voxel_visits_per_frame": fetches_all / args.steps,
                 "Mrays_per_s_primary": pixels_all / (ms * 1e-3) / 1e6,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(names[dom]),
@@ -455,13 +492,13 @@ def run_vrt(args):
                              "note": "algorithmic bytes = getVoxel calls of the reference loop x 1 B + the kernel's outputs (primary: %d B/pixel; any-hit: 1 B/ray); the loop is issue-bound, not bandwidth-bound (DESIGN.md)" % b_out},
                 "e2e": {"value": rays_all / t_e2e / 1e6, "unit": UNIT, "h2d_bytes_per_step": C.sizeof(pyvrt.Camera) + C.sizeof(pyvrt.RenderSettings),
                         "d2h_bytes_per_step": frame_bytes, "ms_per_step": 1e3 * t_e2e / args.steps},
-                "gpu_launches": launches, "clocks": clocks}
+                "gpu_launches": launches, "clocks": clocks, "host_submit_ms_per_step": 1e3 * t_host / args.steps}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(cfg, args.config, args.whd, size, args.cpu_seconds)
         print(json.dumps(line), flush=True)
     barrier()
     # tensors that were used on the context's stream must be returned to torch's allocator while that stream still exists
-    gathered = host2 = asm2 = None
+    gathered = host2 = asm2 = sym = hdl = None
     for p_ in passes[1:]:
         p_.frame.release()
     del submit

@@ -197,6 +197,11 @@ int vrt_assemble(vrt_context*, const void* d_gathered, int world, int w, int h, 
 /* the same on a cudaStream_t of the caller's (the stream its gather runs on), leaving the context stream free for the next frame */
 int vrt_assemble_on(vrt_context*, const void* d_gathered, int world, int w, int h, int plane, void* d_out, void* stream);
 
+/* Assembly without a collective: this rank's tiles of `plane` are stored straight into the row-major w x h frame at d_frame, which
+ * may be peer memory (another GPU's buffer mapped into this process over NVLink). On `stream` (NULL: the frame's own stream); the
+ * caller orders the stores against the consumer (device-side barrier / signal). With world == 1 it is a plain de-tile copy. */
+int vrt_frame_push_tiles(vrt_frame*, int plane, void* d_frame, void* stream);
+
 /* ---- host helpers mirroring reference host code ---- */
 void vrt_camera_vectors(float yaw_deg, float pitch_deg, float focal, float dir[3], float right[3], float up[3]);
 void vrt_default_settings(vrt_render_settings* out);            /* VoxelRenderSettings{} defaults, voxel_render_settings.hpp:15-59 */

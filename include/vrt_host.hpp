@@ -42,6 +42,11 @@ public:
     vrt_context* handle() const { return _ctx; }
     void waitIdle() const { check(vrt_context_sync(_ctx), "vrt_context_sync"); }   // == device.waitIdle()
     void* stream() const { return vrt_context_stream(_ctx); }
+    // MAX_FRAMES_IN_FLIGHT of the reference (source/engine/engine.hpp:19): GeometryStage objects created after this call record
+    // into frames that run on streams of their own, so that consecutive frames overlap on the GPU; joinFrames() makes the
+    // engine's stream wait for all of them (a queue-level fence), waitIdle() waits on the host.
+    void setFramesInFlight(bool concurrent) const { check(vrt_context_set_concurrent_frames(_ctx, concurrent ? 1 : 0), "vrt_context_set_concurrent_frames"); }
+    void joinFrames() const { check(vrt_context_join(_ctx), "vrt_context_join"); }
 private:
     vrt_context* _ctx = nullptr;
 };

@@ -310,6 +310,8 @@ def test_tile_sharded_frame_is_byte_identical(gpu_ctx, world):
     gs.destroy()
     shards = {n: [] for n in ("color", "position", "hit", "hit_palette")}
     total = dict(rays=0, fetches=0, pixels=0)
+    pushed = {n: torch.zeros(full[n].nbytes, dtype=torch.uint8, device="cuda") for n in shards}
+    torch.cuda.synchronize()
     for r in range(world):
         ctx = pyvrt.Context(0, rank=r, world=world)
         s = pyvrt.VoxelScene.from_dense(ctx, vol, pal); s.set_noise(noise); s.set_skybox(sky)
@@ -319,8 +321,14 @@ def test_tile_sharded_frame_is_byte_identical(gpu_ctx, world):
         stt = fr.stats()
         for k in total:
             total[k] += stt[k]
+        # the collective-free assembly: every rank stores its tiles straight into the (here: same-GPU) row-major frame
+        for n in pushed:
+            fr.push_tiles(n, pushed[n].data_ptr())
+        fr.sync()
         fr.release(); s.destroy(); ctx.close()
     assert total["pixels"] == size[0] * size[1] and total["rays"] == full["_stats"]["rays"] and total["fetches"] == full["_stats"]["fetches"]
+    for n in pushed:
+        assert np.array_equal(pushed[n].cpu().numpy(), full[n].view(np.uint8).ravel()), "push " + n
     for n in shards:
         gathered = torch.from_numpy(np.concatenate([x.view(np.uint8).ravel() for x in shards[n]])).cuda()
         _, dt, ch = pyvrt.PLANES[pyvrt.PLANE_ID[n]]

@@ -651,6 +651,20 @@ extern "C" int vrt_assemble_on(vrt_context* c, const void* d_gathered, int world
     return VRT_OK;
 }
 
+// Multi-GPU assembly without a collective: this rank's tiles of `plane` go straight into a row-major w x h frame at d_frame, which
+// may be PEER memory (another GPU's buffer mapped into this process: CUDA IPC / symmetric memory over NVLink). Runs on `stream`
+// (null: the frame's stream); the caller orders it against the consumer (a device-side barrier or signal).
+extern "C" int vrt_frame_push_tiles(vrt_frame* f, int plane, void* d_frame, void* stream) {
+    if (!f || !d_frame || plane < 0 || plane >= VRT_PLANE_COUNT || plane == VRT_PLANE_DENOISED_RGBA8) return fail(VRT_E_INVALID, "bad argument");
+    if (!f->planes[plane]) return fail(VRT_E_INVALID, "plane was not produced for this frame");
+    vrt_context* c = f->ctx;
+    CU(cudaSetDevice(c->device));
+    const cudaError_t e = launch_push_tiles(f->planes[plane], d_frame, f->W, f->H, c->rank, c->world, f->localTiles, kPlaneBpp[plane],
+                                            stream ? (cudaStream_t)stream : f->stream);
+    if (e != cudaSuccess) return fail(VRT_E_CUDA, cudaGetErrorString(e));
+    return VRT_OK;
+}
+
 // ---- host helpers ----
 extern "C" void vrt_camera_vectors(float yaw, float pitch, float focal, float dir[3], float right[3], float up[3]) {
     // CameraController::updateDirectionVectors (camera_controller.cpp:15-28), worldUp = (0,-1,0), glm normalize/cross

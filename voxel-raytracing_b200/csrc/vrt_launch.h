@@ -15,6 +15,7 @@ cudaError_t launch_wavefront(const SceneDev& sc, const FrameParams& fp, const Pl
                              cudaStream_t stream, const WaveSide* side, uint32_t* launches,
                              cudaEvent_t* stageEvents /* 3: after primary, bounces, any-hit; or null */);
 cudaError_t launch_detile(const void* src, void* dst, int W, int H, int world, size_t rankStridePixels, int bpp, cudaStream_t stream);
+cudaError_t launch_push_tiles(const void* src, void* dst, int W, int H, int rank, int world, int localTiles, int bpp, cudaStream_t stream);
 
 // brick acceleration build (vrt_accel.cu): bmask + bdist from the dense volume; tmpA/tmpB are scratch of Bx*By*Bz bytes
 cudaError_t launch_build_accel(const uint8_t* vol, uint32_t W, uint32_t H, uint32_t D, unsigned long long* bmask, uint8_t* bdist,

@@ -90,4 +90,30 @@ cudaError_t launch_detile(const void* src, void* dst, int W, int H, int world, s
     return cudaGetLastError();
 }
 
+// ---- push: this rank's tile-major shard -> its pixels of a row-major frame that may live on ANOTHER GPU (peer memory over
+// NVLink: plain stores, 128-byte rows of a tile are contiguous in both layouts). Replaces gather + de-tile on the assembling rank.
+__global__ void push_tiles_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int W, int H, int tilesX, int rank, int world,
+                                  int localTiles, int bpp) {
+    const int j = blockIdx.x, lx = threadIdx.x, ly0 = threadIdx.y;
+    if (j >= localTiles) return;
+    const int t = rank + j * world, px = (t % tilesX) * VRT_TILE + lx;
+    if (px >= W) return;
+    for (int ly = ly0; ly < VRT_TILE; ly += blockDim.y) {
+        const int py = (t / tilesX) * VRT_TILE + ly;
+        if (py >= H) break;
+        const size_t sp = (size_t)j * (VRT_TILE * VRT_TILE) + ly * VRT_TILE + lx, dp = (size_t)py * W + px;
+        if (bpp == 4) reinterpret_cast<uint32_t*>(dst)[dp] = reinterpret_cast<const uint32_t*>(src)[sp];
+        else if (bpp == 16) reinterpret_cast<uint4*>(dst)[dp] = reinterpret_cast<const uint4*>(src)[sp];
+        else if (bpp == 8) reinterpret_cast<uint2*>(dst)[dp] = reinterpret_cast<const uint2*>(src)[sp];
+        else for (int k = 0; k < bpp; k++) dst[dp * bpp + k] = src[sp * bpp + k];
+    }
+}
+
+cudaError_t launch_push_tiles(const void* src, void* dst, int W, int H, int rank, int world, int localTiles, int bpp, cudaStream_t stream) {
+    if (localTiles <= 0) return cudaSuccess;
+    const int tilesX = (W + VRT_TILE - 1) / VRT_TILE;
+    push_tiles_kernel<<<(unsigned)localTiles, dim3(VRT_TILE, 8), 0, stream>>>((const uint8_t*)src, (uint8_t*)dst, W, H, tilesX, rank, world, localTiles, bpp);
+    return cudaGetLastError();
+}
+
 }  // namespace vrt

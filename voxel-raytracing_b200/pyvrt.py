@@ -244,6 +244,10 @@ class Frame:
         """cudaStream_t this frame's work is queued on (the context's unless frames are concurrent)."""
         return lib().vrt_frame_stream(self.h)
 
+    def push_tiles(self, name, d_frame_ptr, stream=None):
+        """Store this rank's tiles of a plane into a row-major frame that may be peer memory (vrt_frame_push_tiles)."""
+        _ck(lib().vrt_frame_push_tiles(self.h, PLANE_ID[name], C.c_void_p(d_frame_ptr), C.c_void_p(stream) if stream else None))
+
     def download_async(self, name, out):
         """Queue the read-back behind this frame's kernels on the copy stream (out: pinned uint8 buffer); pair with download_wait()."""
         _, nbytes = self.plane_ptr(name)
