@@ -19,6 +19,11 @@
  *                              as sequenced by VoxelRenderer::recordCommands  source/voxels/voxel_renderer.cpp:55-105
  *   vrt_frame_plane         == GeometryBuffer           source/voxels/stages/geometry_stage.hpp:19-27
  *   vrt_camera_vectors      == CameraController::updateDirectionVectors  source/voxels/resource/camera_controller.cpp:15-28
+ *   vrt_blit                == BlitStage::record + shader/blit.frag      source/voxels/stages/blit_stage.cpp:25-57, shader/blit.frag:14-22
+ *   vrt_upscaler_update     == UpscalerStage::update (jitter + frame counter only; FSR2 itself is closed source and out of scope)
+ *                                                       source/voxels/stages/upscaler_stage.cpp:59-70
+ *   vrt_jitter_phase_count / vrt_jitter_offset == ffxFsr2GetJitterPhaseCount / ffxFsr2GetJitterOffset  thirdparty/fsr2/include/ffx_fsr2.h:356,395
+ *   vrt_render_resolution   == VoxelRenderSettings::renderResolution     source/voxels/voxel_render_settings.cpp:3-13
  */
 #ifndef VRT_H
 #define VRT_H
@@ -201,6 +206,28 @@ int vrt_assemble_on(vrt_context*, const void* d_gathered, int world, int w, int 
  * may be peer memory (another GPU's buffer mapped into this process over NVLink). On `stream` (NULL: the frame's own stream); the
  * caller orders the stores against the consumer (device-side barrier / signal). With world == 1 it is a plain de-tile copy. */
 int vrt_frame_push_tiles(vrt_frame*, int plane, void* d_frame, void* stream);
+
+/* ---- output stage (the step downstream of the pass): BlitStage::record running blit.frag, headless ----
+ * d_src: sw x sh RGBA8 on the device (the colour or denoised plane of a full frame, or any RGBA8 image); d_dst: tw x th RGBA8 device
+ * buffer standing in for the swap-chain image. Sampling is the reference's: LINEAR, CLAMP_TO_EDGE; the source is scaled to fill
+ * the target and centre-cropped (blit.frag:17-19). VRT_BLIT_SRGB: encode rgb linear -> sRGB on store, as the reference's swap chain
+ * does (vk-bootstrap default format B8G8R8A8_SRGB, source/engine/swapchain.cpp:15); VRT_BLIT_BGRA: that format's byte order.
+ * vrt_blit runs on the context stream and returns without synchronising (vrt_context_sync / vrt_buffer_download order after it). */
+enum { VRT_BLIT_SRGB = 1, VRT_BLIT_BGRA = 2 };
+int vrt_blit(vrt_context*, const void* d_src_rgba8, int sw, int sh, void* d_dst_rgba8, int tw, int th, uint32_t flags);
+int vrt_blit_on(vrt_context*, const void* d_src_rgba8, int sw, int sh, void* d_dst_rgba8, int tw, int th, uint32_t flags, void* stream);
+/* image files for the headless path (host memory in, RGBA8 row-major): binary PPM (rgb), PNG rgb (tagged sRGB) or PNG rgba */
+enum { VRT_IMAGE_PPM = 0, VRT_IMAGE_PNG_RGB = 1, VRT_IMAGE_PNG_RGBA = 2 };
+int vrt_image_write(const char* path, const void* rgba8, int w, int h, int format);
+
+/* ---- frame driver (the caller of the pass): jitter sequence and frame counter of UpscalerStage::update ----
+ * Pure host functions, usable without a GPU. vrt_upscaler_update: jitter of this frame from *frameCount, then advances it the way the
+ * reference does (wraps to 0 only once it exceeds the phase count); the values go to vrt_camera.cameraJitter / .frame. */
+int vrt_jitter_phase_count(int renderWidth, int displayWidth);
+int vrt_jitter_offset(int index, int phaseCount, float* outX, float* outY);
+int vrt_upscaler_update(int renderWidth, int targetWidth, int* frameCount, float* jitterX, float* jitterY);
+/* scaling = FsrScaling (10 NONE, 15 QUALITY, 17 BALANCED, 20 PERFORMANCE, 30 ULTRA_PERFORMANCE; voxel_render_settings.hpp:6-13) */
+void vrt_render_resolution(int fsrEnable, uint32_t scaling, const uint32_t target[2], uint32_t out[2]);
 
 /* ---- host helpers mirroring reference host code ---- */
 void vrt_camera_vectors(float yaw_deg, float pitch_deg, float focal, float dir[3], float right[3], float up[3]);

@@ -9,11 +9,15 @@
 //   vrt::GeometryStage        == GeometryStage                 source/voxels/stages/geometry_stage.hpp:30-56
 //   vrt::GeometryBuffer       == GeometryBuffer                source/voxels/stages/geometry_stage.hpp:19-27
 //   vrt::DenoiserStage        == DenoiserStage                 source/voxels/stages/denoiser_stage.hpp:21-47
-//   vrt::VoxelRenderer        == VoxelRenderer::recordCommands source/voxels/voxel_renderer.cpp:55-105 (geometry -> denoise)
+//   vrt::UpscalerStage        == UpscalerStage::update         source/voxels/stages/upscaler_stage.cpp:59-70 (jitter + frame counter)
+//   vrt::BlitStage            == BlitStage::record             source/voxels/stages/blit_stage.cpp:25-57 (+ shader/blit.frag)
+//   vrt::VoxelRenderer        == VoxelRenderer::update / recordCommands  source/voxels/voxel_renderer.cpp:33-105
 //
 // What differs, deliberately: there is no vk::CommandBuffer / flightFrame (the context's CUDA stream plays the role of
 // the command buffer; record() is asynchronous exactly like the reference's, results are valid after sync()), render
-// targets are device pointers instead of RenderImage, and FSR / blit / swapchain are out of scope.
+// targets are device pointers instead of RenderImage, the "window" of the blit is a device buffer, and FSR2's upscaling pass is out
+// of scope (closed source) — with fsrSetttings.enable the pass renders at the reduced resolution with FSR2's jitter
+// sequence and the blit's LINEAR sampler does the enlarging.
 #pragma once
 #include <cmath>
 #include <cstring>
@@ -51,7 +55,9 @@ private:
     vrt_context* _ctx = nullptr;
 };
 
-// voxel_render_settings.hpp:21-59 (FSR settings omitted: out of scope; render resolution == target resolution)
+// voxel_render_settings.hpp:6-59. FsrSettings::enable defaults to false here (true in the reference): see the note above.
+enum class FsrScaling : uint32_t { NONE = 10, QUALITY = 15, BALANCED = 17, PERFORMANCE = 20, ULTRA_PERFORMANCE = 30 };
+struct FsrSettings { bool enable = false; FsrScaling scaling = FsrScaling::BALANCED; };
 struct DenoiserSettings { bool enable = true; int iterations = 2; float phiColor0 = 20.4f, phiNormal0 = 1E-2f, phiPos0 = 1E-1f, stepWidth = 2.0f; };
 struct AmbientOcclusionSettings { int numSamples = 4; float intensity = 1.0f; };
 struct LightSettings {
@@ -62,6 +68,7 @@ struct LightSettings {
 class VoxelRenderSettings {
 public:
     uint32_t targetResolution[2] = {1920, 1080};
+    FsrSettings fsrSetttings = {};                       // (sic) the reference's spelling, voxel_render_settings.hpp:49
     DenoiserSettings denoiserSettings = {};
     AmbientOcclusionSettings occlusionSettings = {};
     LightSettings lightSettings = {};
@@ -75,7 +82,11 @@ public:
         vrt_render_settings d; vrt_default_settings(&d);
         std::memcpy(lightSettings.direction, d.light.direction, sizeof(lightSettings.direction));
     }
-    const uint32_t* renderResolution() const { return targetResolution; }
+    // voxel_render_settings.cpp:8-13; the pointer stays valid until the next call
+    const uint32_t* renderResolution() const {
+        vrt_render_resolution(fsrSetttings.enable ? 1 : 0, (uint32_t)fsrSetttings.scaling, targetResolution, _render);
+        return _render;
+    }
     vrt_render_settings lower(bool withDenoiser) const {
         vrt_render_settings s; vrt_default_settings(&s);
         s.pass_mask = passMask; s.out_mask = outMask; s.traversal = traversal; s.pipeline = pipeline;
@@ -87,6 +98,8 @@ public:
         s.denoise.phiPos0 = denoiserSettings.phiPos0; s.denoise.stepWidth = denoiserSettings.stepWidth; s.denoise.mode = denoiseMode;
         return s;
     }
+private:
+    mutable uint32_t _render[2] = {0, 0};
 };
 
 // A complete voxel scene: dense volume + palette (+ noise + skybox) resident on the GPU. voxel_scene.hpp:18-34.
@@ -156,6 +169,8 @@ public:
     // (the reference's caller pushes ScreenQuadPush before record: voxel_renderer.cpp:72-83). Asynchronous.
     GeometryBuffer record(const vrt_camera& push) {
         const vrt_render_settings s = _settings->lower(false);
+        if (_frame && (push.screenSize[0] != _w || push.screenSize[1] != _h)) { vrt_frame_release(_frame); _frame = nullptr; }   // RENDER_RESIZE
+        _w = push.screenSize[0]; _h = push.screenSize[1];
         check(vrt_render(_engine->handle(), _scene->handle(), &push, &s, &_frame), "GeometryStage::record");
         GeometryBuffer g;
         g.color = image(VRT_PLANE_COLOR_RGBA8);
@@ -178,6 +193,7 @@ private:
     std::shared_ptr<VoxelRenderSettings> _settings;
     std::shared_ptr<VoxelScene> _scene;
     vrt_frame* _frame = nullptr;
+    int32_t _w = 0, _h = 0;
 };
 
 class DenoiserStage {
@@ -207,13 +223,64 @@ private:
     RenderImage _out;
 };
 
-// VoxelRenderer::recordCommands (voxel_renderer.cpp:55-105) without the upscaler and blit: push constants -> geometry
-// stage -> denoiser stage (when enabled, voxel_renderer.cpp:87-92) -> the image the blit would present.
+// The frame-driver half of UpscalerStage (upscaler_stage.cpp:59-70): update() once per frame computes this frame's jitter from
+// frameCount and advances it; VoxelRenderer pushes both (voxel_renderer.cpp:80-82). record() — FSR2 itself — does not exist here.
+class UpscalerStage {
+public:
+    float jitterX = 0.0f, jitterY = 0.0f;
+    int frameCount = 0;
+    explicit UpscalerStage(const std::shared_ptr<VoxelRenderSettings>& settings) : _settings(settings) {}
+    void update(float /*delta*/) {
+        check(vrt_upscaler_update((int)_settings->renderResolution()[0], (int)_settings->targetResolution[0], &frameCount, &jitterX, &jitterY),
+              "UpscalerStage::update");
+    }
+private:
+    std::shared_ptr<VoxelRenderSettings> _settings;
+};
+
+// BlitStage::record (blit_stage.cpp:25-57): the final image, sampled LINEAR / CLAMP_TO_EDGE, scaled to fill the window and centre-cropped
+// (blit.frag:14-22), stored sRGB-encoded like the reference's swap-chain format. The window is a device buffer owned by the stage.
+class BlitStage {
+public:
+    uint32_t flags = VRT_BLIT_SRGB;
+    explicit BlitStage(const std::shared_ptr<Engine>& engine) : _engine(engine) {}
+    ~BlitStage() { vrt_buffer_free(_engine->handle(), _window.devicePtr); }
+    BlitStage(const BlitStage&) = delete;
+    BlitStage& operator=(const BlitStage&) = delete;
+    const RenderImage& record(const RenderImage& image, const uint32_t sourceSize[2], const uint32_t windowSize[2]) {
+        const size_t bytes = (size_t)windowSize[0] * windowSize[1] * 4u;
+        if (_window.bytes != bytes) {
+            vrt_buffer_free(_engine->handle(), _window.devicePtr); _window = RenderImage();
+            check(vrt_buffer_alloc(_engine->handle(), bytes, &_window.devicePtr), "BlitStage window");
+            _window.bytes = bytes;
+        }
+        check(vrt_blit(_engine->handle(), image.devicePtr, (int)sourceSize[0], (int)sourceSize[1], _window.devicePtr, (int)windowSize[0], (int)windowSize[1], flags),
+              "BlitStage::record");
+        return _window;
+    }
+    void download(void* host) const { check(vrt_buffer_download(_engine->handle(), _window.devicePtr, host, _window.bytes), "vrt_buffer_download"); }
+private:
+    std::shared_ptr<Engine> _engine;
+    RenderImage _window;
+};
+
+// VoxelRenderer::update / recordCommands (voxel_renderer.cpp:33-105) without FSR2's pass: push constants -> geometry stage -> denoiser
+// stage (when enabled, voxel_renderer.cpp:87-92) -> blit into the window.
 class VoxelRenderer {
 public:
     CameraController camera;
     VoxelRenderer(const std::shared_ptr<Engine>& engine, const std::shared_ptr<VoxelRenderSettings>& settings, const std::shared_ptr<VoxelScene>& scene)
-        : _engine(engine), _settings(settings), _scene(scene), _geometry(engine, settings, scene), _denoiser(engine, settings) {}
+        : _engine(engine), _settings(settings), _scene(scene), _geometry(engine, settings, scene), _denoiser(engine, settings), _upscaler(settings),
+          _blit(engine) {}
+    // voxel_renderer.cpp:33-39: per-frame host update (the camera controller's input handling has no headless counterpart)
+    void update(float delta) { _upscaler.update(delta); }
+    // one whole frame as the reference records it: frame counter and jitter from the upscaler stage, final image blitted into a window
+    // of windowSize (engine->windowSize in the reference). Returns the window image (RGBA8, sRGB-encoded).
+    const RenderImage& recordCommands(const uint32_t windowSize[2]) {
+        const RenderImage img = recordCommands((uint32_t)_upscaler.frameCount, _upscaler.jitterX, _upscaler.jitterY);
+        uint32_t src[2] = {_settings->renderResolution()[0], _settings->renderResolution()[1]};
+        return _blit.record(img, src, windowSize);
+    }
     // one frame; returns the final colour image (denoised when the denoiser is enabled)
     RenderImage recordCommands(uint32_t frameCount, float jitterX = 0.0f, float jitterY = 0.0f) {
         const uint32_t* res = _settings->renderResolution();
@@ -225,12 +292,16 @@ public:
     }
     GeometryStage& geometryStage() { return _geometry; }
     DenoiserStage& denoiserStage() { return _denoiser; }
+    UpscalerStage& upscalerStage() { return _upscaler; }
+    BlitStage& blitStage() { return _blit; }
 private:
     std::shared_ptr<Engine> _engine;
     std::shared_ptr<VoxelRenderSettings> _settings;
     std::shared_ptr<VoxelScene> _scene;
     GeometryStage _geometry;
     DenoiserStage _denoiser;
+    UpscalerStage _upscaler;
+    BlitStage _blit;
 };
 
 }  // namespace vrt

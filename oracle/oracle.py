@@ -64,6 +64,8 @@ def lib():
         _lib.orc_load_vox.restype = C.c_int
         _lib.orc_trace_one.restype = C.c_int
         _lib.orc_num_threads.restype = C.c_int
+        _lib.orc_jitter_phase_count.restype = C.c_int
+        _lib.orc_blit.restype = C.c_int
     return _lib
 
 
@@ -149,6 +151,39 @@ def denoise(color, normal, position, iterations=2, phi_color=20.4, phi_normal=1e
     rc = lib().orc_denoise(_ptr(color), _ptr(normal), _ptr(position), w, h, C.byref(ds), _ptr(out), nthreads)
     if rc != 0:
         raise RuntimeError(f"orc_denoise failed: {rc}")
+    return out
+
+
+def jitter_phase_count(render_width, display_width):
+    return lib().orc_jitter_phase_count(int(render_width), int(display_width))
+
+
+def jitter_offset(index, phase_count):
+    x, y = C.c_float(), C.c_float()
+    lib().orc_jitter_offset(C.byref(x), C.byref(y), int(index), int(phase_count))
+    return np.float32(x.value), np.float32(y.value)
+
+
+def upscaler_update(render_width, target_width, frame_count):
+    """UpscalerStage::update: returns (jitterX, jitterY, next frameCount)."""
+    fc, x, y = C.c_int(frame_count), C.c_float(), C.c_float()
+    lib().orc_upscaler_update(int(render_width), int(target_width), C.byref(fc), C.byref(x), C.byref(y))
+    return np.float32(x.value), np.float32(y.value), fc.value
+
+
+def render_resolution(fsr_enable, scaling, target):
+    t = (C.c_uint32 * 2)(*target); o = (C.c_uint32 * 2)()
+    lib().orc_render_resolution(int(bool(fsr_enable)), int(scaling), t, o)
+    return o[0], o[1]
+
+
+def blit(src, target_size, srgb=True):
+    """BlitStage: src (h, w, 4) u8 -> (th, tw, 4) u8; target_size = (tw, th)."""
+    src = np.ascontiguousarray(src, np.uint8); sh, sw = src.shape[:2]
+    out = np.zeros((target_size[1], target_size[0], 4), np.uint8)
+    rc = lib().orc_blit(_ptr(src), sw, sh, _ptr(out), target_size[0], target_size[1], 1 if srgb else 0, 0)
+    if rc != 0:
+        raise RuntimeError(f"orc_blit failed: {rc}")
     return out
 
 

@@ -84,6 +84,17 @@ void orc_free(void* p);
 int orc_generate(int generator, uint32_t seed, uint8_t* vol, uint32_t W, uint32_t H, uint32_t D);
 int orc_num_threads(void);
 
+/* ---- the steps either side of the pass (orc_output.cpp) ---- */
+/* ffxFsr2GetJitterPhaseCount / ffxFsr2GetJitterOffset (FSR2 v2.1.0, thirdparty/fsr2/include/ffx_fsr2.h:356,395) */
+int orc_jitter_phase_count(int renderWidth, int displayWidth);
+void orc_jitter_offset(float* outX, float* outY, int index, int phaseCount);
+/* UpscalerStage::update, upscaler_stage.cpp:59-70 (jitter of this frame; advances *frameCount) */
+void orc_upscaler_update(int renderWidth, int targetWidth, int* frameCount, float* jitterX, float* jitterY);
+/* VoxelRenderSettings::renderResolution, voxel_render_settings.cpp:3-13 */
+void orc_render_resolution(int fsrEnable, uint32_t scaling, const uint32_t target[2], uint32_t out[2]);
+/* blit.frag:14-22 through a LINEAR / CLAMP_TO_EDGE sampler; RGBA8 in and out; flags bit 0: sRGB-encode rgb on store */
+int orc_blit(const uint8_t* src, int sw, int sh, uint8_t* dst, int tw, int th, int flags, int nthreads);
+
 #ifdef __cplusplus
 }
 #endif

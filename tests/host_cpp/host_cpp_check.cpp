@@ -14,6 +14,12 @@ static void dump(const std::string& path, const void* p, size_t n) {
     fclose(f);
 }
 
+static void check_image_file(const std::string& path, const vrt::RenderImage& win, vrt::VoxelRenderer& renderer, int W, int H) {
+    std::vector<uint8_t> host(win.bytes);
+    renderer.blitStage().download(host.data());
+    vrt::check(vrt_image_write(path.c_str(), host.data(), W, H, VRT_IMAGE_PNG_RGB), "vrt_image_write");
+}
+
 int main(int argc, char** argv) {
     if (argc == 2 && !strcmp(argv[1], "--link-only")) { printf("%s\n", vrt_version()); return 0; }
     if (argc == 2 && !strcmp(argv[1], "--no-gpu")) {   // error behaviour without a device: an exception, never a fallback
@@ -53,6 +59,21 @@ int main(int argc, char** argv) {
         }
         buf.resize(final.bytes); renderer.denoiserStage().download(buf.data());
         dump(std::string(argv[4]) + "_denoised.bin", buf.data(), buf.size());
+        // the whole frame as the reference records it: upscaler-stage jitter + frame counter, FSR render resolution, blit into a window
+        settings->fsrSetttings.enable = true; settings->fsrSetttings.scaling = vrt::FsrScaling::QUALITY;
+        renderer.update(0.016f); renderer.update(0.016f);
+        const uint32_t window[2] = {(uint32_t)W, (uint32_t)H};
+        const vrt::RenderImage& win = renderer.recordCommands(window);
+        engine->waitIdle();
+        buf.resize(win.bytes); renderer.blitStage().download(buf.data());
+        dump(std::string(argv[4]) + "_window.bin", buf.data(), buf.size());
+        const uint32_t* rr = settings->renderResolution();
+        const vrt_camera push2 = renderer.camera.push(*scene, rr, (uint32_t)renderer.upscalerStage().frameCount, renderer.upscalerStage().jitterX, renderer.upscalerStage().jitterY);
+        dump(std::string(argv[4]) + "_camera2.bin", &push2, sizeof(push2));
+        buf.resize((size_t)rr[0] * rr[1] * 4); renderer.denoiserStage().download(buf.data());   // the image the blit sampled
+        dump(std::string(argv[4]) + "_final2.bin", buf.data(), buf.size());
+        check_image_file(std::string(argv[4]) + "_window.png", win, renderer, W, H);
+        settings->fsrSetttings.enable = false;
         const vrt_frame_stats st = gs.stats();
         const vrt_camera push = renderer.camera.push(*scene, settings->renderResolution(), 3);
         dump(std::string(argv[4]) + "_camera.bin", &push, sizeof(push));

@@ -6,6 +6,7 @@
 #include <vector>
 #include <algorithm>
 #include "../../voxel-raytracing_b200/csrc/vrt_wave.cuh"
+#include "../../voxel-raytracing_b200/csrc/vrt_output.cuh"
 
 using namespace vrt;
 
@@ -292,3 +293,27 @@ extern "C" void hh_assemble(const uint8_t* gathered, int world, int W, int H, si
 }
 
 extern "C" void hh_scene_odist(void* p, int octant, uint8_t* out) { HScene* s = (HScene*)p; memcpy(out, s->odist[octant].data(), s->odist[octant].size()); }
+
+// the output stage's per-pixel code (csrc/vrt_output.cuh) in the loop structure of blit_kernel
+extern "C" void hh_blit(const uint8_t* src, int sw, int sh, uint8_t* dst, int tw, int th, uint32_t flags) {
+    BlitParams p; p.sw = sw; p.sh = sh; p.tw = tw; p.th = th; p.flags = flags;
+    float thr[256]; srgb_thresholds(thr);
+    float lutU[256]; for (int i = 0; i < 256; i++) lutU[i] = (float)i / 255.0f;
+    const float scale = blit_scale(p);
+    for (int py = 0; py < th; py++) {
+        const BlitAxis ry = blit_axis(py, sh, th, scale);
+        for (int px = 0; px < tw; px++) {
+            const BlitAxis cx = blit_axis(px, sw, tw, scale);
+            const BlitTap t = blit_weights(cx.a, ry.a);
+            const uint8_t* c00 = src + 4 * ((size_t)ry.i0 * sw + cx.i0); const uint8_t* c10 = src + 4 * ((size_t)ry.i0 * sw + cx.i1);
+            const uint8_t* c01 = src + 4 * ((size_t)ry.i1 * sw + cx.i0); const uint8_t* c11 = src + 4 * ((size_t)ry.i1 * sw + cx.i1);
+            uint8_t o[4];
+            for (int c = 0; c < 4; c++) {
+                const float v = blit_mix(t, lutU[c00[c]], lutU[c10[c]], lutU[c01[c]], lutU[c11[c]]);
+                o[c] = ((flags & VRT_BLIT_SRGB) && c < 3) ? srgb8_lookup(thr, v) : to_unorm8(v);
+            }
+            if (flags & VRT_BLIT_BGRA) std::swap(o[0], o[2]);
+            memcpy(dst + 4 * ((size_t)py * tw + px), o, 4);
+        }
+    }
+}

@@ -3,6 +3,7 @@ same seeded inputs. Bar (BASELINE.json): hit voxel, palette index, step count bi
 1e-5 relative (we assert bit-exact); colour within 1/255 per channel (we assert bit-exact float colour except for
 at most 1e-4 of pixels, where the binary64 atan2/asin of the sky lookup may round differently)."""
 import ctypes as C
+import os
 import numpy as np
 import pytest
 
@@ -358,3 +359,61 @@ def test_standalone_denoise_matches_oracle(gpu_ctx):
             want = O.denoise(color, normal, pos, iterations=iters, mode=mode)
             d = np.abs(out.cpu().numpy().astype(int) - want.astype(int))
             assert d.max() <= 1 and (d != 0).mean() < 2e-3, (mode, iters, d.max(), (d != 0).mean())
+
+
+@pytest.mark.parametrize("sizes", [(480, 270, 480, 270), (1129, 635, 1920, 1080), (1920, 1080, 1280, 720), (333, 217, 1001, 64), (1, 1, 50, 40),
+                                   (3840, 2160, 2560, 1440)])
+def test_blit_matches_oracle_bit_exact(gpu_ctx, sizes):
+    """Output stage (BlitStage::record / blit.frag) through the C ABI against the oracle: every byte equal, UNORM and sRGB stores."""
+    import torch
+    sw, sh, tw, th = sizes
+    rng = np.random.default_rng(sw + 7 * tw)
+    src = rng.integers(0, 256, (sh, sw, 4), dtype=np.uint8)
+    tsrc = torch.from_numpy(src).cuda()
+    for flags in (0, pyvrt.BLIT_SRGB, pyvrt.BLIT_SRGB | pyvrt.BLIT_BGRA):
+        out = torch.zeros((th, tw, 4), dtype=torch.uint8, device="cuda")
+        torch.cuda.synchronize()
+        pyvrt.blit_device(gpu_ctx, tsrc.data_ptr(), (sw, sh), out.data_ptr(), (tw, th), flags)
+        gpu_ctx.sync()
+        want = O.blit(src, (tw, th), srgb=bool(flags & pyvrt.BLIT_SRGB))
+        if flags & pyvrt.BLIT_BGRA:
+            want = want[..., [2, 1, 0, 3]]
+        got = out.cpu().numpy()
+        assert np.array_equal(got, want), (sizes, flags, int((got != want).sum()))
+
+
+def test_frame_to_window_jittered_sequence(gpu_ctx, tmp_path):
+    """The callers either side of the pass, end to end on the device: UpscalerStage.update drives frame / cameraJitter, the pass renders at
+    the FSR render resolution, the blit presents at the target resolution; every stage equals the oracle's."""
+    import torch
+    rng = np.random.default_rng(11)
+    whd = (40, 36, 44)
+    vol, pal = random_volume(rng, whd, 0.03), random_palette(rng, metallic_every=4)
+    noise, sky = assets.noise_standin(), assets.sky_standin(128, 64)
+    target = (320, 180)
+    rres = pyvrt.render_resolution(True, pyvrt.FSR_BALANCED, target)
+    assert rres == O.render_resolution(True, 17, target)
+    sc, keep = O.make_scene(vol, pal, noise, sky)
+    st = O.make_settings()
+    gs = pyvrt.VoxelScene.from_dense(gpu_ctx, vol, pal); gs.set_noise(noise); gs.set_skybox(sky)
+    s = pyvrt.default_settings(); s.out_mask = pyvrt.OUT_GBUFFER; s.denoise.enable = 0
+    s.light.direction[:] = st.lightDir[:]
+    rp = pyvrt.VoxelRenderPass(gpu_ctx, gs, s)
+    up = pyvrt.UpscalerStage(rres[0], target[0])
+    for k in range(3):
+        up.update(0.016)
+        cam = look_at_camera(whd, rres, (-15, 45, -20), (20, 18, 22), frame=up.frameCount)
+        cam.cameraJitter[:] = [float(up.jitterX), float(up.jitterY)]
+        want = O.render(sc, cam, st)
+        c = pyvrt.Camera(); C.memmove(C.byref(c), C.byref(cam), C.sizeof(cam))
+        fr = rp.record(c); fr.sync()
+        color = fr.download("color")
+        assert np.abs(color.astype(int) - want["color"].astype(int)).max() <= 1
+        out = torch.zeros((target[1], target[0], 4), dtype=torch.uint8, device="cuda")
+        torch.cuda.synchronize()
+        pyvrt.blit_device(gpu_ctx, fr.plane_ptr("color"), rres, out.data_ptr(), target, pyvrt.BLIT_SRGB)
+        gpu_ctx.sync()
+        assert np.array_equal(out.cpu().numpy(), O.blit(color, target, srgb=True))
+    pyvrt.image_write(str(tmp_path / "frame.png"), out.cpu().numpy(), pyvrt.IMAGE_PNG_RGB)
+    assert os.path.getsize(str(tmp_path / "frame.png")) > target[0] * target[1] * 3
+    fr.release(); gs.destroy()

@@ -159,3 +159,74 @@ def test_harness_production_mode_early_termination(trav, wave):
         assert_planes_exact(got, want, names=["depth", "motion", "mask", "position", "normal"])
         assert np.abs(got["color"].astype(int) - want["color"].astype(int)).max() <= 1
         ok, bad = bits_equal(got["color_f32"], want["color_f32"]); assert ok, bad
+
+
+# ---- the steps either side of the pass: frame driver (host functions of libvrt) and output stage (csrc/vrt_output.cuh on the host) ----
+def test_frame_driver_matches_oracle():
+    for scaling in (10, 15, 17, 20, 30):
+        for target in ((1920, 1080), (3840, 2160), (1280, 720), (7680, 4320), (1001, 333)):
+            for en in (0, 1):
+                assert pyvrt.render_resolution(en, scaling, target) == O.render_resolution(en, scaling, target)
+            rw = pyvrt.render_resolution(1, scaling, target)[0]
+            n = pyvrt.jitter_phase_count(rw, target[0])
+            assert n == O.jitter_phase_count(rw, target[0])
+            for idx in range(0, n + 2):
+                a, b = pyvrt.jitter_offset(idx, n), O.jitter_offset(idx, n)
+                assert bits_equal(np.array(a), np.array(b))[0], (scaling, target, idx)
+    up, fc = pyvrt.UpscalerStage(1129, 1920), 0
+    for _ in range(60):
+        x, y, fc = O.upscaler_update(1129, 1920, fc)
+        up.update(0.016)
+        assert up.frameCount == fc and bits_equal(np.array([up.jitterX, up.jitterY]), np.array([x, y]))[0]
+    with pytest.raises(pyvrt.VrtError):
+        pyvrt.jitter_offset(0, 0)
+
+
+@pytest.mark.parametrize("sizes", [(16, 9, 16, 9), (16, 9, 32, 18), (33, 17, 20, 31), (64, 36, 7, 5), (5, 7, 64, 36), (1, 1, 9, 9),
+                                   (127, 61, 128, 64), (1129, 635, 1920, 1080), (480, 270, 479, 271)])
+def test_harness_blit_matches_oracle(sizes):
+    from vrtlib import harness
+    sw, sh, tw, th = sizes
+    rng = np.random.default_rng(sw * 131 + tw)
+    src = rng.integers(0, 256, (sh, sw, 4), dtype=np.uint8)
+    for flags in (0, pyvrt.BLIT_SRGB, pyvrt.BLIT_SRGB | pyvrt.BLIT_BGRA):
+        want = O.blit(src, (tw, th), srgb=bool(flags & pyvrt.BLIT_SRGB))
+        if flags & pyvrt.BLIT_BGRA:
+            want = want[..., [2, 1, 0, 3]]
+        got = np.zeros((th, tw, 4), np.uint8)
+        harness().hh_blit(src.ctypes.data_as(C.c_void_p), sw, sh, got.ctypes.data_as(C.c_void_p), tw, th, C.c_uint32(flags))
+        assert np.array_equal(got, want), (sizes, flags, int((got != want).sum()))
+
+
+def test_image_writers_round_trip(tmp_path):
+    import zlib, struct
+    rng = np.random.default_rng(5)
+    for (w, h) in ((1, 1), (37, 11), (300, 200)):                     # 300x200x4 > 65535: several stored blocks
+        img = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+        for fmt, ch in ((pyvrt.IMAGE_PNG_RGB, 3), (pyvrt.IMAGE_PNG_RGBA, 4)):
+            path = str(tmp_path / f"t{w}_{fmt}.png")
+            pyvrt.image_write(path, img, fmt)
+            data = open(path, "rb").read()
+            assert data[:8] == b"\x89PNG\r\n\x1a\n"
+            at, idat, ihdr = 8, b"", None
+            while at < len(data):
+                n, typ = struct.unpack(">I4s", data[at:at + 8]); body = data[at + 8:at + 8 + n]
+                assert struct.unpack(">I", data[at + 8 + n:at + 12 + n])[0] == zlib.crc32(typ + body)
+                if typ == b"IHDR": ihdr = struct.unpack(">IIBBBBB", body)
+                if typ == b"IDAT": idat += body
+                at += 12 + n
+            assert ihdr == (w, h, 8, 6 if ch == 4 else 2, 0, 0, 0)
+            raw = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(h, 1 + w * ch)
+            assert (raw[:, 0] == 0).all() and np.array_equal(raw[:, 1:].reshape(h, w, ch), img[..., :ch])
+        path = str(tmp_path / f"t{w}.ppm")
+        pyvrt.image_write(path, img, pyvrt.IMAGE_PPM)
+        data = open(path, "rb").read()
+        head = f"P6\n{w} {h}\n255\n".encode()
+        assert data.startswith(head) and np.array_equal(np.frombuffer(data[len(head):], np.uint8).reshape(h, w, 3), img[..., :3])
+    try:
+        from PIL import Image
+        assert np.array_equal(np.asarray(Image.open(str(tmp_path / "t300_2.png"))), img)
+    except ImportError:
+        pass
+    with pytest.raises(pyvrt.VrtError):
+        pyvrt.image_write(str(tmp_path / "no_such_dir" / "x.png"), img)

@@ -64,3 +64,16 @@ def test_cpp_renderer_matches_oracle(tmp_path):
     dn = np.fromfile(prefix + "_denoised.bin", np.uint8).reshape(H, W, 4)
     ref = O.denoise(got["color"], got["normal"], got["position"])
     assert np.abs(dn.astype(int) - ref.astype(int)).max() <= 1
+    # the whole frame: FSR QUALITY render resolution, two upscaler updates (frameCount 2, Halton index 1), blit into a W x H sRGB window
+    cam2 = O.Camera(); raw = open(prefix + "_camera2.bin", "rb").read(); C.memmove(C.byref(cam2), raw, len(raw))
+    rw, rh = O.render_resolution(True, 15, (W, H))
+    assert (cam2.screenSize[0], cam2.screenSize[1]) == (rw, rh) and cam2.frame == 2
+    jx, jy = O.jitter_offset(1, O.jitter_phase_count(rw, W))
+    assert bits_equal(np.array(cam2.cameraJitter[:], np.float32), np.array([jx, jy], np.float32))[0]
+    final2 = np.fromfile(prefix + "_final2.bin", np.uint8).reshape(rh, rw, 4)
+    want2 = O.render(sc, cam2, O.make_settings())
+    ref2 = O.denoise(want2["color"], want2["normal"], want2["position"])
+    assert np.abs(final2.astype(int) - ref2.astype(int)).max() <= 2      # colour within 1/255, then the denoiser within 1/255
+    window = np.fromfile(prefix + "_window.bin", np.uint8).reshape(H, W, 4)
+    assert np.array_equal(window, O.blit(final2, (W, H), srgb=True))      # the blit itself is exact on the same input
+    assert os.path.getsize(prefix + "_window.png") > W * H * 3

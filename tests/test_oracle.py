@@ -242,3 +242,64 @@ def test_denoiser_modes_and_iteration0_is_edge_blind():
     flat = np.zeros((h, w, 4), np.uint8); flat[..., :3] = (10, 200, 77)
     for mode in (0, 1):
         assert np.array_equal(O.denoise(flat, normal, pos * 0, iterations=3, mode=mode), flat)
+
+
+# ---- the steps either side of the pass (oracle/orc_output.cpp) ----
+def test_jitter_phase_counts_pinned_by_reference_header():
+    # the reference's own table, thirdparty/fsr2/include/ffx_fsr2.h:341-347: scale factor -> phase count
+    for scaling, want in ((15, 18), (17, 23), (20, 32), (30, 72)):
+        rw, _ = O.render_resolution(True, scaling, (1920, 1080))       # voxel_render_settings.cpp:3-13
+        assert O.jitter_phase_count(rw, 1920) == want, (scaling, rw)
+    assert O.render_resolution(True, 17, (1920, 1080)) == (1129, 635)   # uint32((10.0f/17)*1920)
+    assert O.render_resolution(False, 17, (1920, 1080)) == (1920, 1080)
+    assert O.jitter_phase_count(1920, 1920) == 8
+
+
+def test_jitter_is_halton_2_3_exact_fractions():
+    from fractions import Fraction
+    def halton(i, b):
+        f, r = Fraction(1), Fraction(0)
+        while i > 0:
+            f /= b; r += f * (i % b); i //= b
+        return r
+    for phases in (8, 18, 23, 32, 72):
+        for idx in range(phases + 3):
+            x, y = O.jitter_offset(idx, phases)
+            k = idx % phases + 1
+            assert abs(Fraction(float(x)) - (halton(k, 2) - Fraction(1, 2))) < Fraction(1, 1 << 22)
+            assert abs(Fraction(float(y)) - (halton(k, 3) - Fraction(1, 2))) < Fraction(1, 1 << 22)
+            assert -0.5 <= x < 0.5 and -0.5 <= y < 0.5
+    # base 2 is exact in binary32
+    assert [float(O.jitter_offset(i, 8)[0]) for i in range(4)] == [0.0, -0.25, 0.25, -0.375]
+
+
+def test_upscaler_update_wraps_one_frame_late():
+    fc, seen = 0, []
+    for _ in range(20):
+        x, y, nfc = O.upscaler_update(1920, 1920, fc)        # 8 phases
+        seen.append((fc, float(x), float(y))); fc = nfc
+    assert [s[0] for s in seen] == [0, 1, 2, 3, 4, 5, 6, 7, 8, 0, 1, 2, 3, 4, 5, 6, 7, 8, 0, 1]   # upscaler_stage.cpp:67-69: '>' not '>='
+    assert seen[8][1:] == seen[0][1:] == seen[9][1:]         # frameCount 8 % 8 == index 0 again
+
+
+def test_blit_known_answers():
+    rng = np.random.default_rng(3)
+    a = rng.integers(0, 256, (36, 64, 4), dtype=np.uint8)
+    assert np.array_equal(O.blit(a, (64, 36), srgb=False), a)                    # same size: texel centres, weights (1,0,0,0)
+    flat = np.full((7, 5, 4), 77, np.uint8)
+    assert (O.blit(flat, (33, 21), srgb=False) == 77).all()                      # partition of unity
+    up = O.blit(a, (128, 72), srgb=False)                                        # 2x: taps at +-1/4 texel -> weights 9/16, 3/16, 3/16, 1/16
+    p = a.astype(np.float64)
+    want = (9 * p[1, 1] + 3 * p[1, 2] + 3 * p[2, 1] + 1 * p[2, 2]) / 16
+    assert np.abs(up[3, 3].astype(np.float64) - want).max() <= 0.5 + 1e-4
+    assert np.array_equal(up[0, 0], a[0, 0])                                     # CLAMP_TO_EDGE at the corner
+    # fill + centre crop (blit.frag:17-19): a wider target shows the source's middle rows only
+    tall = np.zeros((100, 10, 4), np.uint8); tall[:, :, 0] = np.arange(100)[:, None]
+    wide = O.blit(tall, (40, 40), srgb=False)                                    # scale = 10/40; rows 45..55 of the source
+    assert 44 <= wide[0, 0, 0] <= 46 and 54 <= wide[-1, 0, 0] <= 56
+    # sRGB store: closed-form codes of the transfer function; alpha stays linear
+    grey = np.zeros((2, 2, 4), np.uint8); grey[...] = (0, 1, 128, 128)
+    enc = O.blit(grey, (2, 2), srgb=True)[0, 0]
+    assert tuple(enc) == (0, 13, 188, 128)                                       # 1/255 -> 12.71 -> 13; 128/255 -> 187.85 -> 188
+    full = np.full((1, 1, 4), 255, np.uint8)
+    assert tuple(O.blit(full, (3, 3), srgb=True)[1, 1]) == (255, 255, 255, 255)

@@ -48,7 +48,7 @@ class VrtSettings(C.Structure):
 
 def build_harness() -> str:
     src = os.path.join(HARNESS_DIR, "harness.cpp")
-    deps = [src] + [os.path.join(PKG, "csrc", f) for f in ("vrt_core.cuh", "vrt_pixel.cuh", "vrt_wave.cuh", "vrt_types.h")]
+    deps = [src] + [os.path.join(PKG, "csrc", f) for f in ("vrt_core.cuh", "vrt_pixel.cuh", "vrt_wave.cuh", "vrt_output.cuh", "vrt_types.h")]
     if not os.path.exists(HARNESS_LIB) or any(os.path.getmtime(d) > os.path.getmtime(HARNESS_LIB) for d in deps):
         gxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
         subprocess.check_call([gxx, "-std=c++17", "-O2", "-ffp-contract=off", "-fno-fast-math", "-fopenmp", "-fPIC", "-shared",

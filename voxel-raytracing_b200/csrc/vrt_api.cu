@@ -634,6 +634,19 @@ extern "C" int vrt_denoise(vrt_context* c, const void* d_color, const void* d_no
     return VRT_OK;
 }
 
+// BlitStage::record (blit_stage.cpp:25-57): source image -> "window" buffer through blit.frag. Asynchronous on the given stream.
+extern "C" int vrt_blit_on(vrt_context* c, const void* d_src, int sw, int sh, void* d_dst, int tw, int th, uint32_t flags, void* stream) {
+    if (!c || !d_src || !d_dst || sw <= 0 || sh <= 0 || tw <= 0 || th <= 0 || (flags & ~(uint32_t)(VRT_BLIT_SRGB | VRT_BLIT_BGRA)))
+        return fail(VRT_E_INVALID, "bad argument");
+    CU(cudaSetDevice(c->device));
+    cudaError_t e = launch_blit(d_src, sw, sh, d_dst, tw, th, flags, (cudaStream_t)stream);
+    if (e != cudaSuccess) return fail(VRT_E_CUDA, cudaGetErrorString(e));
+    return VRT_OK;
+}
+extern "C" int vrt_blit(vrt_context* c, const void* d_src, int sw, int sh, void* d_dst, int tw, int th, uint32_t flags) {
+    return vrt_blit_on(c, d_src, sw, sh, d_dst, tw, th, flags, c ? (void*)c->stream : nullptr);
+}
+
 // Assemble a sharded plane on the gathering rank: `gathered` holds world shard buffers back to back (rank-major),
 // each of vrt_frame_plane() size; writes a row-major W x H plane.
 extern "C" int vrt_assemble_on(vrt_context* c, const void* d_gathered, int world, int w, int h, int plane, void* d_out, void* stream);

@@ -40,4 +40,7 @@ struct DenoiseIter { float phiColor, phiNormal, phiPos, stepWidth; };
 cudaError_t launch_denoise(const uint8_t* color, const int8_t* normal, const float* position, uint8_t* out, int W, int H,
                            const DenoiseTaps& taps, const DenoiseIter& it, cudaStream_t stream);
 
+// output stage (vrt_output.cu): blit.frag; flags = VRT_BLIT_*
+cudaError_t launch_blit(const void* src, int sw, int sh, void* dst, int tw, int th, uint32_t flags, cudaStream_t stream);
+
 }  // namespace vrt

@@ -1,0 +1,65 @@
+// vrt_output.cu — the output stage: BlitStage::record (source/voxels/stages/blit_stage.cpp:25-57) running shader/blit.frag as a CUDA
+// kernel, headless: the "window" is a device buffer of the target size. HBM-streaming: algorithmically 4 B read per source pixel the
+// footprints cover + 4 B written per target pixel; the four taps of neighbouring pixels overlap and are served by L1/L2.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <mutex>
+#include "vrt_output.cuh"
+#include "vrt_launch.h"
+
+namespace vrt {
+
+__global__ void __launch_bounds__(256) blit_kernel(const uchar4* __restrict__ src, uchar4* __restrict__ dst, const BlitParams p,
+                                                   const float* __restrict__ srgbThr) {
+    __shared__ float lutU[256], thr[256];
+    __shared__ BlitAxis col[32], row[8];
+    lutU[threadIdx.x] = (float)threadIdx.x / 255.0f;       // exact UNORM8 decode without a division per tap (as in denoise_kernel)
+    thr[threadIdx.x] = srgbThr[threadIdx.x];
+    // the block's 32 column taps and 8 row taps, once: 4 IEEE divisions per tap instead of per pixel
+    const float scale = blit_scale(p);
+    if (threadIdx.x < 32) col[threadIdx.x] = blit_axis(min((int)(blockIdx.x * 32 + threadIdx.x), p.tw - 1), p.sw, p.tw, scale);
+    else if (threadIdx.x < 40) row[threadIdx.x - 32] = blit_axis(min((int)(blockIdx.y * 8 + threadIdx.x - 32), p.th - 1), p.sh, p.th, scale);
+    __syncthreads();
+    const int px = blockIdx.x * 32 + (threadIdx.x & 31), py = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (px >= p.tw || py >= p.th) return;
+    const BlitAxis cx = col[threadIdx.x & 31], ry = row[threadIdx.x >> 5];
+    const BlitTap t = blit_weights(cx.a, ry.a);
+    const uchar4* r0 = src + (size_t)ry.i0 * p.sw; const uchar4* r1 = src + (size_t)ry.i1 * p.sw;
+    const uchar4 c00 = __ldg(r0 + cx.i0), c10 = __ldg(r0 + cx.i1), c01 = __ldg(r1 + cx.i0), c11 = __ldg(r1 + cx.i1);
+    const float r = blit_mix(t, lutU[c00.x], lutU[c10.x], lutU[c01.x], lutU[c11.x]);
+    const float g = blit_mix(t, lutU[c00.y], lutU[c10.y], lutU[c01.y], lutU[c11.y]);
+    const float b = blit_mix(t, lutU[c00.z], lutU[c10.z], lutU[c01.z], lutU[c11.z]);
+    const float a = blit_mix(t, lutU[c00.w], lutU[c10.w], lutU[c01.w], lutU[c11.w]);
+    uchar4 o;
+    if (p.flags & VRT_BLIT_SRGB) { o.x = srgb8_lookup(thr, r); o.y = srgb8_lookup(thr, g); o.z = srgb8_lookup(thr, b); }
+    else { o.x = to_unorm8(r); o.y = to_unorm8(g); o.z = to_unorm8(b); }
+    o.w = to_unorm8(a);                                      // alpha of an sRGB format is linear
+    if (p.flags & VRT_BLIT_BGRA) { const unsigned char s = o.x; o.x = o.z; o.z = s; }
+    dst[(size_t)py * p.tw + px] = o;
+}
+
+static std::mutex g_thrLock;
+static float* g_thrDev[64] = {};
+
+cudaError_t launch_blit(const void* src, int sw, int sh, void* dst, int tw, int th, uint32_t flags, cudaStream_t stream) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    {
+        std::lock_guard<std::mutex> lk(g_thrLock);
+        if (!g_thrDev[dev]) {
+            float h[256]; srgb_thresholds(h);
+            float* d = nullptr;
+            if ((e = cudaMalloc(&d, sizeof(h))) != cudaSuccess) return e;
+            if ((e = cudaMemcpy(d, h, sizeof(h), cudaMemcpyHostToDevice)) != cudaSuccess) { cudaFree(d); return e; }
+            g_thrDev[dev] = d;
+        }
+    }
+    BlitParams p; p.sw = sw; p.sh = sh; p.tw = tw; p.th = th; p.flags = flags;
+    dim3 grid((tw + 31) / 32, (th + 7) / 8);
+    blit_kernel<<<grid, 256, 0, stream>>>((const uchar4*)src, (uchar4*)dst, p, g_thrDev[dev]);
+    return cudaGetLastError();
+}
+
+}  // namespace vrt

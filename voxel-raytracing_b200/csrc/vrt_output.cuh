@@ -1,0 +1,77 @@
+// vrt_output.cuh — per-pixel arithmetic of the output stage (the step downstream of the render pass), written for
+// the device and compilable for the host (tests/host_harness). Follows /root/reference/shader/blit.frag:14-22 sampled through
+// RenderImage's LINEAR / CLAMP_TO_EDGE sampler (source/engine/resource/render_image.cpp:59-67). Same exactness rules as vrt_core.cuh.
+#pragma once
+#include "vrt_core.cuh"
+
+namespace vrt {
+
+VRT_HD int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+
+struct BlitParams { int sw, sh, tw, th; uint32_t flags; };
+
+// The footprint is separable: column taps depend on px only, row taps on py only (blit.frag's vec2 arithmetic never mixes the axes
+// except through the scalar `scale`). One axis: the two clamped texel coordinates and alpha (Vulkan texel filtering: i0 = floor(u - 0.5),
+// alpha = frac(u - 0.5)).
+struct BlitAxis { int i0, i1; float a; };
+
+VRT_HD float blit_scale(const BlitParams& p) { return fminf((float)p.sw / (float)p.tw, (float)p.sh / (float)p.th); }   // blit.frag:17
+
+VRT_HD BlitAxis blit_axis(int pix, int srcN, int tgtN, float scale) {
+    const float fs = (float)srcN, ft = (float)tgtN;
+    const float screen = ((float)pix + 0.5f) / ft;                // vScreenPos (screen_quad.vert:16-32)
+    const float target = screen * ft;                             // blit.frag:16
+    const float scaled = ft * scale;                              // :18
+    const float source = target * scale + (fs - scaled) / 2.0f;   // :19
+    const float u = (source / fs) * fs - 0.5f;                    // :20 + un-normalisation by the sampler
+    const float fi = floorf(u);
+    const int i = f2i(fi);
+    BlitAxis t;
+    t.a = u - fi; t.i0 = clampi(i, 0, srcN - 1); t.i1 = clampi(i + 1, 0, srcN - 1);
+    return t;
+}
+
+// weights as products, applied in the order 00, 10, 01, 11
+struct BlitTap { float w00, w10, w01, w11; };
+VRT_HD BlitTap blit_weights(float a, float b) {
+    BlitTap t;
+    t.w00 = (1.0f - a) * (1.0f - b); t.w10 = a * (1.0f - b); t.w01 = (1.0f - a) * b; t.w11 = a * b;
+    return t;
+}
+
+VRT_HD float blit_mix(const BlitTap& t, float c00, float c10, float c01, float c11) {
+    return ((t.w00 * c00 + t.w10 * c10) + t.w01 * c01) + t.w11 * c11;
+}
+
+// sRGB store: thr[k] (k = 1..255) is the smallest binary32 value whose encoded UNORM8 code is >= k (built on the host by bisection over
+// the exact transfer function, vrt_output.cu), so the code of L is the number of thresholds <= L: 8 compares instead of a powf whose
+// last bit would differ between libraries. thr[0] is unused.
+VRT_HD uint8_t srgb8_lookup(const float* thr, float L) {
+    if (!(L == L)) return 0;
+    int code = 0;
+#pragma unroll
+    for (int step = 128; step > 0; step >>= 1) if (L >= thr[code + step]) code += step;
+    return (uint8_t)code;
+}
+
+// ---- sRGB thresholds (host). encode(L) = round-half-even(255 * E(L)), E = the sRGB transfer function in binary64; it is monotone in L,
+// so the smallest binary32 L with encode(L) >= k is found by bisection over the (ordered) bit patterns of [0, 1].
+inline int srgb_code(float L) {
+    const double l = (double)L;
+    const double e = l <= 0.0031308 ? 12.92 * l : 1.055 * pow(l, 1.0 / 2.4) - 0.055;
+    return (int)rint(e * 255.0);
+}
+inline void srgb_thresholds(float thr[256]) {
+    thr[0] = 0.0f;
+    for (int k = 1; k < 256; k++) {
+        uint32_t lo = 0u, hi = 0x3f800000u;                 // code(lo) < k <= code(hi); positive floats order like their bit patterns
+        while (hi - lo > 1u) {
+            const uint32_t mid = lo + (hi - lo) / 2u;
+            float f; memcpy(&f, &mid, 4);
+            if (srgb_code(f) >= k) hi = mid; else lo = mid;
+        }
+        memcpy(&thr[k], &hi, 4);
+    }
+}
+
+}  // namespace vrt

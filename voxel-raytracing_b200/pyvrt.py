@@ -76,7 +76,7 @@ def lib():
         L.vrt_version.restype = C.c_char_p
         L.vrt_context_stream.restype = C.c_void_p
         L.vrt_frame_stream.restype = C.c_void_p
-        for fn in ("vrt_context_destroy", "vrt_scene_destroy", "vrt_frame_release", "vrt_host_free", "vrt_camera_vectors", "vrt_default_settings"):
+        for fn in ("vrt_context_destroy", "vrt_scene_destroy", "vrt_frame_release", "vrt_host_free", "vrt_camera_vectors", "vrt_default_settings", "vrt_render_resolution"):
             getattr(L, fn).restype = None
         _lib = L
     return _lib
@@ -305,6 +305,55 @@ def assemble(ctx: Context, d_gathered_ptr: int, world: int, size, plane: str, d_
         _ck(lib().vrt_assemble(ctx.h, C.c_void_p(d_gathered_ptr), world, size[0], size[1], PLANE_ID[plane], C.c_void_p(d_out_ptr)))
     else:
         _ck(lib().vrt_assemble_on(ctx.h, C.c_void_p(d_gathered_ptr), world, size[0], size[1], PLANE_ID[plane], C.c_void_p(d_out_ptr), C.c_void_p(stream)))
+
+
+BLIT_SRGB, BLIT_BGRA = 1, 2
+IMAGE_PPM, IMAGE_PNG_RGB, IMAGE_PNG_RGBA = 0, 1, 2
+FSR_NONE, FSR_QUALITY, FSR_BALANCED, FSR_PERFORMANCE, FSR_ULTRA_PERFORMANCE = 10, 15, 17, 20, 30   # FsrScaling, voxel_render_settings.hpp:6-13
+
+
+def blit_device(ctx: Context, d_src, src_size, d_dst, dst_size, flags=BLIT_SRGB, stream: int = None):
+    """BlitStage::record: src_size / dst_size are (w, h); device pointers to RGBA8 images. Asynchronous."""
+    if stream is None:
+        _ck(lib().vrt_blit(ctx.h, C.c_void_p(d_src), src_size[0], src_size[1], C.c_void_p(d_dst), dst_size[0], dst_size[1], C.c_uint32(flags)))
+    else:
+        _ck(lib().vrt_blit_on(ctx.h, C.c_void_p(d_src), src_size[0], src_size[1], C.c_void_p(d_dst), dst_size[0], dst_size[1], C.c_uint32(flags), C.c_void_p(stream)))
+
+
+def image_write(path: str, rgba8, fmt=IMAGE_PNG_RGB):
+    a = np.ascontiguousarray(rgba8, np.uint8)
+    assert a.ndim == 3 and a.shape[2] == 4
+    _ck(lib().vrt_image_write(path.encode(), a.ctypes.data_as(C.c_void_p), a.shape[1], a.shape[0], fmt))
+
+
+def jitter_phase_count(render_width, display_width) -> int:
+    return lib().vrt_jitter_phase_count(int(render_width), int(display_width))
+
+
+def jitter_offset(index, phase_count):
+    x, y = C.c_float(), C.c_float()
+    _ck(lib().vrt_jitter_offset(int(index), int(phase_count), C.byref(x), C.byref(y)))
+    return np.float32(x.value), np.float32(y.value)
+
+
+def render_resolution(fsr_enable, scaling, target):
+    t = (C.c_uint32 * 2)(*target); o = (C.c_uint32 * 2)()
+    lib().vrt_render_resolution(int(bool(fsr_enable)), C.c_uint32(scaling), t, o)
+    return o[0], o[1]
+
+
+class UpscalerStage:
+    """The frame-driver half of UpscalerStage (upscaler_stage.cpp:59-70): update() once per frame sets jitterX / jitterY for this
+    frame and advances frameCount; both feed the camera block (voxel_renderer.cpp:80-82). FSR2's upscaling itself is out of scope."""
+
+    def __init__(self, render_width, target_width):
+        self.render_width, self.target_width = int(render_width), int(target_width)
+        self.frameCount, self.jitterX, self.jitterY = 0, np.float32(0), np.float32(0)
+
+    def update(self, delta=0.0):
+        fc, x, y = C.c_int(self.frameCount), C.c_float(), C.c_float()
+        _ck(lib().vrt_upscaler_update(self.render_width, self.target_width, C.byref(fc), C.byref(x), C.byref(y)))
+        self.frameCount, self.jitterX, self.jitterY = fc.value, np.float32(x.value), np.float32(y.value)
 
 
 def denoise_device(ctx: Context, d_color, d_normal, d_position, size, ds: DenoiserSettings, d_out):
