@@ -72,6 +72,11 @@ int main(int argc, char** argv) {
         dump(std::string(argv[4]) + "_camera2.bin", &push2, sizeof(push2));
         buf.resize((size_t)rr[0] * rr[1] * 4); renderer.denoiserStage().download(buf.data());   // the image the blit sampled
         dump(std::string(argv[4]) + "_final2.bin", buf.data(), buf.size());
+        for (int plane : {VRT_PLANE_COLOR_RGBA8, VRT_PLANE_POSITION_RGBA32F, VRT_PLANE_NORMAL_RGBA8S}) {
+            const vrt::RenderImage img = gs.image(plane);
+            buf.resize(img.bytes); gs.download(img, buf.data());
+            dump(std::string(argv[4]) + "_fsr_plane" + std::to_string(plane) + ".bin", buf.data(), buf.size());
+        }
         check_image_file(std::string(argv[4]) + "_window.png", win, renderer, W, H);
         settings->fsrSetttings.enable = false;
         const vrt_frame_stats st = gs.stats();

@@ -411,7 +411,7 @@ def test_frame_to_window_jittered_sequence(gpu_ctx, tmp_path):
         assert np.abs(color.astype(int) - want["color"].astype(int)).max() <= 1
         out = torch.zeros((target[1], target[0], 4), dtype=torch.uint8, device="cuda")
         torch.cuda.synchronize()
-        pyvrt.blit_device(gpu_ctx, fr.plane_ptr("color"), rres, out.data_ptr(), target, pyvrt.BLIT_SRGB)
+        pyvrt.blit_device(gpu_ctx, fr.plane_ptr("color")[0], rres, out.data_ptr(), target, pyvrt.BLIT_SRGB)
         gpu_ctx.sync()
         assert np.array_equal(out.cpu().numpy(), O.blit(color, target, srgb=True))
     pyvrt.image_write(str(tmp_path / "frame.png"), out.cpu().numpy(), pyvrt.IMAGE_PNG_RGB)

@@ -72,8 +72,12 @@ def test_cpp_renderer_matches_oracle(tmp_path):
     assert bits_equal(np.array(cam2.cameraJitter[:], np.float32), np.array([jx, jy], np.float32))[0]
     final2 = np.fromfile(prefix + "_final2.bin", np.uint8).reshape(rh, rw, 4)
     want2 = O.render(sc, cam2, O.make_settings())
-    ref2 = O.denoise(want2["color"], want2["normal"], want2["position"])
-    assert np.abs(final2.astype(int) - ref2.astype(int)).max() <= 2      # colour within 1/255, then the denoiser within 1/255
+    col2 = np.fromfile(prefix + "_fsr_plane0.bin", np.uint8).reshape(rh, rw, 4)
+    pos2 = np.fromfile(prefix + "_fsr_plane5.bin", np.float32).reshape(rh, rw, 4)
+    nrm2 = np.fromfile(prefix + "_fsr_plane6.bin", np.int8).reshape(rh, rw, 4)
+    assert bits_equal(pos2, want2["position"])[0] and bits_equal(nrm2, want2["normal"])[0]     # the jittered frame, bit for bit
+    assert np.abs(col2.astype(int) - want2["color"].astype(int)).max() <= 1
+    assert np.abs(final2.astype(int) - O.denoise(col2, nrm2, pos2).astype(int)).max() <= 1
     window = np.fromfile(prefix + "_window.bin", np.uint8).reshape(H, W, 4)
     assert np.array_equal(window, O.blit(final2, (W, H), srgb=True))      # the blit itself is exact on the same input
     assert os.path.getsize(prefix + "_window.png") > W * H * 3
