@@ -44,6 +44,17 @@ main = stripped.find(b"MAIN")
 stripped = stripped[:main + 8] + struct.pack("<I", len(stripped) - (main + 12)) + stripped[main + 12:]
 save("nopalette.vox", stripped)
 
+# nine instances of three models under all the rotation kinds, overlapping on purpose: the flatten's instance order decides the result
+# (the device flatten of csrc/vrt_flatten.cu must reproduce it)
+rng = np.random.default_rng(21)
+rots = [I3, rz, [[-1, 0, 0], [0, -1, 0], [0, 0, 1]], [[0, 0, 1], [0, 1, 0], [-1, 0, 0]], [[1, 0, 0], [0, 0, -1], [0, 1, 0]], [[0, -1, 0], [0, 0, 1], [-1, 0, 0]]]
+ms = []
+for k, shape in enumerate(((13, 9, 7), (6, 11, 10), (17, 5, 12))):
+    mm = ((rng.random(shape) < 0.6) * rng.integers(1, 200, shape)).astype(np.uint8); mm.flat[0] = 10 + k
+    ms.append(mm)
+inst = [(int(i % 3), np.array(rots[int(rng.integers(0, len(rots)))], np.float32), tuple(int(t) for t in rng.integers(-7, 8, 3))) for i in range(9)]
+save("overlap9.vox", O.ref_write_vox(ms, inst, pal, {12: 0.5}))
+
 # small oracle render (self-generated)
 rc, vol, p = O.load_vox(open(os.path.join(HERE, "twoinst.vox"), "rb").read())
 sc, keep = O.make_scene(vol, p, assets.noise_standin(), assets.sky_standin(64, 32))

@@ -40,7 +40,7 @@ def test_no_gpu_fails_loudly_no_cpu_fallback():
     assert e.value.code == pyvrt.E_NO_DEVICE and "no CPU fallback" in str(e.value)
 
 
-@pytest.mark.parametrize("name", ["lshape", "twoinst", "nopalette"])
+@pytest.mark.parametrize("name", ["lshape", "twoinst", "nopalette", "overlap9"])
 def test_vox_decode_matches_reference_golden(name):
     data = open(os.path.join(GOLD, name + ".vox"), "rb").read()
     ref = np.load(os.path.join(GOLD, name + "_ref.npz"))

@@ -18,7 +18,7 @@ def _gold(name):
 
 
 # ---------------------------------------------------------------- scene loader vs the reference's ogt_vox (golden)
-@pytest.mark.parametrize("name", ["lshape", "twoinst", "nopalette"])
+@pytest.mark.parametrize("name", ["lshape", "twoinst", "nopalette", "overlap9"])
 def test_loader_matches_reference_golden(name):
     data, vol, pal = _gold(name)
     rc, v, p = O.load_vox(data)

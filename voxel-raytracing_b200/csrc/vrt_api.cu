@@ -222,19 +222,56 @@ extern "C" int vrt_scene_from_dense(vrt_context* c, const uint8_t* volume, uint3
     return VRT_OK;
 }
 
+// VoxelScene::VoxelScene (voxel_scene.cpp:33-133): parse on the host, flatten on the device. Every model is uploaded once and each
+// instance is one kernel launch, in the reference's order. A scene with a non-permutation transform (an invalid _r yields a zero row,
+// as in the reference's parser) can collide inside one instance, where the reference's sequential loop order decides: such a scene
+// is flattened by the host loop and uploaded, like vrt_scene_from_dense.
+static int scene_from_layout(vrt_context* c, const VoxLayout& lay, vrt_scene** out) {
+    bool device = true;
+    for (const VoxLayout::Instance& in : lay.instances) device = device && in.permutation;
+    if (!device) {
+        std::vector<uint8_t> vol((size_t)lay.w * lay.h * lay.d);
+        flatten_host(lay, vol.data());
+        return vrt_scene_from_dense(c, vol.data(), lay.w, lay.h, lay.d, lay.palette, out);
+    }
+    vrt_scene* s = nullptr;
+    int rc = scene_alloc(c, lay.w, lay.h, lay.d, &s);
+    if (rc) return rc;
+    std::vector<uint8_t*> dmodels(lay.models.size(), nullptr);
+    cudaError_t e = cudaMemsetAsync(s->vol, 0, (size_t)lay.w * lay.h * lay.d, c->stream);
+    for (size_t i = 0; i < lay.instances.size() && e == cudaSuccess; i++) {
+        const uint32_t mi = lay.instances[i].model;
+        const VoxLayout::Model& m = lay.models[mi];
+        if (m.cells.empty()) continue;
+        if (!dmodels[mi]) {
+            e = cudaMalloc(&dmodels[mi], m.cells.size());
+            if (e == cudaSuccess) e = cudaMemcpyAsync(dmodels[mi], m.cells.data(), m.cells.size(), cudaMemcpyHostToDevice, c->stream);
+        }
+        if (e == cudaSuccess) e = launch_flatten_instance(dmodels[mi], s->vol, flatten_instance_params(lay, i), c->stream);
+        if (e == cudaSuccess) s->accelLaunches++;
+    }
+    const cudaError_t e2 = cudaStreamSynchronize(c->stream);   // lay's host buffers are pageable: the copies must be done before they go away
+    for (uint8_t* p : dmodels) cudaFree(p);
+    if (e != cudaSuccess || e2 != cudaSuccess) { vrt_scene_destroy(s); return fail(e == cudaErrorMemoryAllocation ? VRT_E_OOM : VRT_E_CUDA, cudaGetErrorString(e != cudaSuccess ? e : e2)); }
+    rc = scene_finish(s, lay.palette);
+    if (rc) { vrt_scene_destroy(s); return rc; }
+    *out = s;
+    return VRT_OK;
+}
+
 extern "C" int vrt_scene_load_vox_memory(vrt_context* c, const uint8_t* bytes, size_t n, vrt_scene** out) {
     if (!c || !out) return fail(VRT_E_INVALID, "null argument");
-    DenseScene ds; std::string err;
-    int rc = load_vox_bytes(bytes, n, ds, err);
+    VoxLayout lay; std::string err;
+    int rc = parse_vox_bytes(bytes, n, lay, err);
     if (rc) return fail(rc, err);
-    return vrt_scene_from_dense(c, ds.volume.data(), ds.w, ds.h, ds.d, ds.palette, out);
+    return scene_from_layout(c, lay, out);
 }
 extern "C" int vrt_scene_load_vox(vrt_context* c, const char* path, vrt_scene** out) {
     if (!c || !out) return fail(VRT_E_INVALID, "null argument");
-    DenseScene ds; std::string err;
-    int rc = load_vox_file(path, ds, err);
+    VoxLayout lay; std::string err;
+    int rc = parse_vox_file(path, lay, err);
     if (rc) return fail(rc, err);
-    return vrt_scene_from_dense(c, ds.volume.data(), ds.w, ds.h, ds.d, ds.palette, out);
+    return scene_from_layout(c, lay, out);
 }
 
 extern "C" int vrt_scene_generate(vrt_context* c, int generator, uint64_t seed, uint32_t w, uint32_t h, uint32_t d, vrt_scene** out) {

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include "vrt_types.h"
+#include "vrt_flatten.h"
 
 namespace vrt {
 
@@ -39,6 +40,9 @@ struct DenoiseTaps { int n; int ox[9], oy[9]; float k[9]; };   // taps with non-
 struct DenoiseIter { float phiColor, phiNormal, phiPos, stepWidth; };
 cudaError_t launch_denoise(const uint8_t* color, const int8_t* normal, const float* position, uint8_t* out, int W, int H,
                            const DenoiseTaps& taps, const DenoiseIter& it, cudaStream_t stream);
+
+// scene ingestion (vrt_flatten.cu): one instance of a .vox scene into the dense volume (cells: the model's voxels on the device)
+cudaError_t launch_flatten_instance(const uint8_t* cells, uint8_t* vol, const FlattenInstance& f, cudaStream_t stream);
 
 // output stage (vrt_output.cu): blit.frag; flags = VRT_BLIT_*
 cudaError_t launch_blit(const void* src, int sw, int sh, void* dst, int tw, int th, uint32_t flags, cudaStream_t stream);

@@ -9,33 +9,50 @@
 
 namespace vrt {
 
+// One block = a 32 x 32 tile of the target, 256 threads, 4 rows per thread (rows ty, ty+8, ty+16, ty+24): the tables and the tile's
+// 32 column + 32 row taps are set up once per 1024 pixels, and a thread keeps its column tap in registers.
+#define VRT_BLIT_TILE 32
 __global__ void __launch_bounds__(256) blit_kernel(const uchar4* __restrict__ src, uchar4* __restrict__ dst, const BlitParams p,
                                                    const float* __restrict__ srgbThr) {
-    __shared__ float lutU[256], thr[256];
-    __shared__ BlitAxis col[32], row[8];
+    __shared__ float lutU[256], thr[257];
+    __shared__ BlitAxis col[VRT_BLIT_TILE], row[VRT_BLIT_TILE];
     lutU[threadIdx.x] = (float)threadIdx.x / 255.0f;       // exact UNORM8 decode without a division per tap (as in denoise_kernel)
     thr[threadIdx.x] = srgbThr[threadIdx.x];
-    // the block's 32 column taps and 8 row taps, once: 4 IEEE divisions per tap instead of per pixel
+    // the tile's column and row taps, once: 4 IEEE divisions per tap instead of per pixel (warp 0: columns, warp 1: rows)
     const float scale = blit_scale(p);
-    if (threadIdx.x < 32) col[threadIdx.x] = blit_axis(min((int)(blockIdx.x * 32 + threadIdx.x), p.tw - 1), p.sw, p.tw, scale);
-    else if (threadIdx.x < 40) row[threadIdx.x - 32] = blit_axis(min((int)(blockIdx.y * 8 + threadIdx.x - 32), p.th - 1), p.sh, p.th, scale);
+    if (threadIdx.x < 32) col[threadIdx.x] = blit_axis(min((int)(blockIdx.x * VRT_BLIT_TILE + threadIdx.x), p.tw - 1), p.sw, p.tw, scale);
+    else if (threadIdx.x < 64) row[threadIdx.x - 32] = blit_axis(min((int)(blockIdx.y * VRT_BLIT_TILE + threadIdx.x - 32), p.th - 1), p.sh, p.th, scale);
     __syncthreads();
-    const int px = blockIdx.x * 32 + (threadIdx.x & 31), py = blockIdx.y * 8 + (threadIdx.x >> 5);
-    if (px >= p.tw || py >= p.th) return;
-    const BlitAxis cx = col[threadIdx.x & 31], ry = row[threadIdx.x >> 5];
-    const BlitTap t = blit_weights(cx.a, ry.a);
-    const uchar4* r0 = src + (size_t)ry.i0 * p.sw; const uchar4* r1 = src + (size_t)ry.i1 * p.sw;
-    const uchar4 c00 = __ldg(r0 + cx.i0), c10 = __ldg(r0 + cx.i1), c01 = __ldg(r1 + cx.i0), c11 = __ldg(r1 + cx.i1);
-    const float r = blit_mix(t, lutU[c00.x], lutU[c10.x], lutU[c01.x], lutU[c11.x]);
-    const float g = blit_mix(t, lutU[c00.y], lutU[c10.y], lutU[c01.y], lutU[c11.y]);
-    const float b = blit_mix(t, lutU[c00.z], lutU[c10.z], lutU[c01.z], lutU[c11.z]);
-    const float a = blit_mix(t, lutU[c00.w], lutU[c10.w], lutU[c01.w], lutU[c11.w]);
-    uchar4 o;
-    if (p.flags & VRT_BLIT_SRGB) { o.x = srgb8_lookup(thr, r); o.y = srgb8_lookup(thr, g); o.z = srgb8_lookup(thr, b); }
-    else { o.x = to_unorm8(r); o.y = to_unorm8(g); o.z = to_unorm8(b); }
-    o.w = to_unorm8(a);                                      // alpha of an sRGB format is linear
-    if (p.flags & VRT_BLIT_BGRA) { const unsigned char s = o.x; o.x = o.z; o.z = s; }
-    dst[(size_t)py * p.tw + px] = o;
+    const int lx = threadIdx.x & 31, px = blockIdx.x * VRT_BLIT_TILE + lx;
+    if (px >= p.tw) return;
+    const BlitAxis cx = col[lx];
+    const bool srgb = (p.flags & VRT_BLIT_SRGB) != 0, bgra = (p.flags & VRT_BLIT_BGRA) != 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int ly = (threadIdx.x >> 5) + 8 * k, py = blockIdx.y * VRT_BLIT_TILE + ly;
+        if (py >= p.th) break;
+        const BlitAxis ry = row[ly];
+        const uchar4* r0 = src + (size_t)ry.i0 * p.sw; const uchar4* r1 = src + (size_t)ry.i1 * p.sw;
+        const uchar4 c00 = __ldg(r0 + cx.i0);
+        float r, g, b, a;
+        if (__all_sync(__activemask(), cx.a == 0.0f && ry.a == 0.0f)) {
+            // sample points on texel centres (equal sizes): the weights are (1, 0, 0, 0) and the mix returns c00's values bit for bit
+            r = lutU[c00.x]; g = lutU[c00.y]; b = lutU[c00.z]; a = lutU[c00.w];
+        } else {
+            const uchar4 c10 = __ldg(r0 + cx.i1), c01 = __ldg(r1 + cx.i0), c11 = __ldg(r1 + cx.i1);
+            const BlitTap t = blit_weights(cx.a, ry.a);
+            r = blit_mix(t, lutU[c00.x], lutU[c10.x], lutU[c01.x], lutU[c11.x]);
+            g = blit_mix(t, lutU[c00.y], lutU[c10.y], lutU[c01.y], lutU[c11.y]);
+            b = blit_mix(t, lutU[c00.z], lutU[c10.z], lutU[c01.z], lutU[c11.z]);
+            a = blit_mix(t, lutU[c00.w], lutU[c10.w], lutU[c01.w], lutU[c11.w]);
+        }
+        uchar4 o;
+        if (srgb) { o.x = srgb8_lookup(thr, r); o.y = srgb8_lookup(thr, g); o.z = srgb8_lookup(thr, b); }
+        else { o.x = to_unorm8(r); o.y = to_unorm8(g); o.z = to_unorm8(b); }
+        o.w = to_unorm8(a);                                      // alpha of an sRGB format is linear
+        if (bgra) { const unsigned char sw = o.x; o.x = o.z; o.z = sw; }
+        dst[(size_t)py * p.tw + px] = o;
+    }
 }
 
 static std::mutex g_thrLock;
@@ -57,7 +74,7 @@ cudaError_t launch_blit(const void* src, int sw, int sh, void* dst, int tw, int 
         }
     }
     BlitParams p; p.sw = sw; p.sh = sh; p.tw = tw; p.th = th; p.flags = flags;
-    dim3 grid((tw + 31) / 32, (th + 7) / 8);
+    dim3 grid((tw + VRT_BLIT_TILE - 1) / VRT_BLIT_TILE, (th + VRT_BLIT_TILE - 1) / VRT_BLIT_TILE);
     blit_kernel<<<grid, 256, 0, stream>>>((const uchar4*)src, (uchar4*)dst, p, g_thrDev[dev]);
     return cudaGetLastError();
 }

@@ -48,10 +48,20 @@ VRT_HD float blit_mix(const BlitTap& t, float c00, float c10, float c01, float c
 // last bit would differ between libraries. thr[0] is unused.
 VRT_HD uint8_t srgb8_lookup(const float* thr, float L) {
     if (!(L == L)) return 0;
+#if defined(__CUDA_ARCH__)
+    // a guess from the fast transfer function (2 MUFU), then moved onto the exact code by the thresholds: the result is defined by
+    // thr[] alone, whatever the guess was (usually 0 or 1 corrections instead of 8 dependent look-ups)
+    const float l = fminf(fmaxf(L, 0.0f), 1.0f);
+    const float e = l <= 0.0031308f ? 12.92f * l : 1.055f * __powf(l, 1.0f / 2.4f) - 0.055f;
+    int code = min(max(__float2int_rn(e * 255.0f), 0), 255);
+    while (code > 0 && L < thr[code]) code--;
+    while (code < 255 && L >= thr[code + 1]) code++;
+    return (uint8_t)code;
+#else
     int code = 0;
-#pragma unroll
     for (int step = 128; step > 0; step >>= 1) if (L >= thr[code + step]) code += step;
     return (uint8_t)code;
+#endif
 }
 
 // ---- sRGB thresholds (host). encode(L) = round-half-even(255 * E(L)), E = the sRGB transfer function in binary64; it is monotone in L,

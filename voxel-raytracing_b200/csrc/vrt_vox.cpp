@@ -1,6 +1,7 @@
 // vrt_vox.cpp — see vrt_vox.h. Three stages: (1) chunk scan of the RIFF-like .vox container, (2) scene-graph walk
 // producing flattened instance transforms, (3) the reference's flatten into one dense volume with the Y/Z swap.
 #include "vrt_vox.h"
+#include "vrt_flatten.h"
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -104,7 +105,7 @@ constexpr uint32_t tag(char a, char b, char c, char d) { return (uint32_t)(uint8
 
 }  // namespace
 
-int load_vox_bytes(const uint8_t* bytes, size_t n, DenseScene& out, std::string& err) {
+int parse_vox_bytes(const uint8_t* bytes, size_t n, VoxLayout& out, std::string& err) {
     static const char lfs[] = "version https://git-lfs";
     if (bytes && n >= sizeof(lfs) - 1 && memcmp(bytes, lfs, sizeof(lfs) - 1) == 0) {
         err = "file is a git-LFS pointer stub, not .vox data"; return VRT_E_LFS_POINTER;
@@ -210,38 +211,36 @@ int load_vox_bytes(const uint8_t* bytes, size_t n, DenseScene& out, std::string&
 
     if (placed.empty()) { err = "Voxel scene does not contain an instance."; return VRT_E_NO_INSTANCE; }
 
-    // (3) flatten (voxel_scene.cpp:9-105)
-    auto pivot = [](const VoxModel& m, int p[3]) { p[0] = (int)floorf(m.nx / 2.0f); p[1] = (int)floorf(m.ny / 2.0f); p[2] = (int)floorf(m.nz / 2.0f); };
-    auto xform = [](const Mat4& t, const int p[3], int x, int y, int z, int o[3]) {
-        const float v0 = ((float)x + 0.5f) - (float)p[0], v1 = ((float)y + 0.5f) - (float)p[1], v2 = ((float)z + 0.5f) - (float)p[2];
-        for (int k = 0; k < 3; k++) {
-            const float s = (t.e[k] * v0 + t.e[4 + k] * v1) + (t.e[8 + k] * v2 + t.e[12 + k] * 1.0f);
-            const float fl = floorf(s);
-            o[k] = (fl != fl) ? 0 : (fl >= 2147483648.0f ? 2147483647 : (fl <= -2147483648.0f ? (-2147483647 - 1) : (int)fl));
-        }
-    };
+    // (3) bounds of the flatten (voxel_scene.cpp:53-76); the copy itself is flatten_host / the device flatten
+    out.models.clear(); out.instances.clear();
+    for (const VoxModel& m : models) { VoxLayout::Model o; o.nx = m.nx; o.ny = m.ny; o.nz = m.nz; o.cells = m.cells; out.models.push_back(std::move(o)); }
     int lo[3] = {100000, 100000, 100000}, hi[3] = {-100000, -100000, -100000};
     for (const Placed& pl : placed) {
         const VoxModel& m = models[pl.model];
-        int pv[3], a[3], b[3]; pivot(m, pv);
-        xform(pl.xf, pv, 0, 0, 0, a); xform(pl.xf, pv, (int)m.nx, (int)m.ny, (int)m.nz, b);
+        VoxLayout::Instance in; in.model = pl.model; memcpy(in.xf, pl.xf.e, sizeof(in.xf));
+        in.pivot[0] = (int)floorf(m.nx / 2.0f); in.pivot[1] = (int)floorf(m.ny / 2.0f); in.pivot[2] = (int)floorf(m.nz / 2.0f);
+        // a signed permutation in the rotation part maps distinct voxels to distinct cells; anything else (the zero row an invalid _r yields)
+        // can collide inside one instance, where the reference's loop order decides
+        bool perm = true;
+        for (int r = 0; r < 3 && perm; r++) {
+            int nzRow = 0, nzCol = 0;
+            for (int k = 0; k < 3; k++) {
+                const float a = in.xf[4 * r + k], b = in.xf[4 * k + r];
+                if (a != 0.0f) { nzRow++; if (a != 1.0f && a != -1.0f) perm = false; }
+                if (b != 0.0f) nzCol++;
+            }
+            if (nzRow != 1 || nzCol != 1) perm = false;
+        }
+        in.permutation = perm;
+        int a[3], b[3];
+        vox_transform(in.xf, in.pivot, 0, 0, 0, a); vox_transform(in.xf, in.pivot, (int)m.nx, (int)m.ny, (int)m.nz, b);
         for (int k = 0; k < 3; k++) { lo[k] = std::min(lo[k], std::min(a[k], b[k])); hi[k] = std::max(hi[k], std::max(a[k], b[k])); }
+        out.instances.push_back(in);
     }
+    for (int k = 0; k < 3; k++) out.lo[k] = lo[k];
     out.w = (uint32_t)(hi[0] - lo[0]); out.h = (uint32_t)(hi[2] - lo[2]); out.d = (uint32_t)(hi[1] - lo[1]);
     const size_t total = (size_t)out.w * out.h * out.d;
     if (total == 0 || total > ((size_t)1 << 34)) { err = "degenerate scene bounds"; return VRT_E_PARSE; }
-    out.volume.assign(total, 0);
-    for (const Placed& pl : placed) {
-        const VoxModel& m = models[pl.model];
-        int pv[3]; pivot(m, pv);
-        for (uint32_t x = 0; x < m.nx; x++) for (uint32_t y = 0; y < m.ny; y++) for (uint32_t z = 0; z < m.nz; z++) {
-            const uint8_t v = m.cells[x + (size_t)y * m.nx + (size_t)z * m.nx * m.ny];
-            if (!v) continue;
-            int t[3]; xform(pl.xf, pv, (int)x, (int)y, (int)z, t);
-            const long long at = (long long)(t[0] - lo[0]) + (long long)(t[2] - lo[2]) * out.w + (long long)(t[1] - lo[1]) * out.w * out.h;
-            if (at >= 0 && (size_t)at < total) out.volume[(size_t)at] = v;   // the reference writes unchecked (UB past the end); dropped here
-        }
-    }
     for (int i = 0; i < 256; i++) {   // voxel_scene.cpp:107-117
         vrt_material& m = out.palette[i];
         for (int k = 0; k < 4; k++) m.diffuse[k] = powf((float)pal[4 * i + k] / 255.0f, 2.2f);
@@ -250,17 +249,62 @@ int load_vox_bytes(const uint8_t* bytes, size_t n, DenseScene& out, std::string&
     return VRT_OK;
 }
 
-int load_vox_file(const char* path, DenseScene& out, std::string& err) {
+static FlattenInstance flatten_params(const VoxLayout& lay, const VoxLayout::Instance& in) {
+    const VoxLayout::Model& m = lay.models[in.model];
+    FlattenInstance f;
+    memcpy(f.xf, in.xf, sizeof(f.xf));
+    for (int k = 0; k < 3; k++) { f.pivot[k] = in.pivot[k]; f.lo[k] = lay.lo[k]; }
+    f.nx = m.nx; f.ny = m.ny; f.nz = m.nz; f.W = lay.w; f.H = lay.h; f.D = lay.d;
+    return f;
+}
+FlattenInstance flatten_instance_params(const VoxLayout& lay, size_t i) { return flatten_params(lay, lay.instances[i]); }
+
+// voxel_scene.cpp:83-105, loop order included (x outermost, z innermost; instances in order)
+void flatten_host(const VoxLayout& lay, uint8_t* volume) {
+    memset(volume, 0, (size_t)lay.w * lay.h * lay.d);
+    for (const VoxLayout::Instance& in : lay.instances) {
+        const VoxLayout::Model& m = lay.models[in.model];
+        const FlattenInstance f = flatten_params(lay, in);
+        for (uint32_t x = 0; x < m.nx; x++) for (uint32_t y = 0; y < m.ny; y++) for (uint32_t z = 0; z < m.nz; z++) {
+            const uint8_t v = m.cells[x + (size_t)y * m.nx + (size_t)z * m.nx * m.ny];
+            if (!v) continue;
+            const long long at = flatten_cell(f, (int)x, (int)y, (int)z);
+            if (at >= 0) volume[(size_t)at] = v;
+        }
+    }
+}
+
+int load_vox_bytes(const uint8_t* bytes, size_t n, DenseScene& out, std::string& err) {
+    VoxLayout lay;
+    const int rc = parse_vox_bytes(bytes, n, lay, err);
+    if (rc) return rc;
+    out.w = lay.w; out.h = lay.h; out.d = lay.d;
+    out.volume.resize((size_t)lay.w * lay.h * lay.d);
+    flatten_host(lay, out.volume.data());
+    memcpy(out.palette, lay.palette, sizeof(out.palette));
+    return VRT_OK;
+}
+
+static int read_file(const char* path, std::vector<uint8_t>& buf, std::string& err) {
     FILE* f = path ? fopen(path, "rb") : nullptr;
     if (!f) { err = "Failed to read voxel scene"; return VRT_E_IO; }
-    std::vector<uint8_t> buf;
     fseek(f, 0, SEEK_END); long sz = ftell(f); fseek(f, 0, SEEK_SET);
     if (sz < 0) { fclose(f); err = "Failed to read voxel scene"; return VRT_E_IO; }
     buf.resize((size_t)sz);
     const size_t got = sz ? fread(buf.data(), 1, (size_t)sz, f) : 0;
     fclose(f);
     if (got != (size_t)sz) { err = "Failed to read voxel scene"; return VRT_E_IO; }
-    return load_vox_bytes(buf.data(), buf.size(), out, err);
+    return VRT_OK;
+}
+int load_vox_file(const char* path, DenseScene& out, std::string& err) {
+    std::vector<uint8_t> buf;
+    const int rc = read_file(path, buf, err);
+    return rc ? rc : load_vox_bytes(buf.data(), buf.size(), out, err);
+}
+int parse_vox_file(const char* path, VoxLayout& out, std::string& err) {
+    std::vector<uint8_t> buf;
+    const int rc = read_file(path, buf, err);
+    return rc ? rc : parse_vox_bytes(buf.data(), buf.size(), out, err);
 }
 
 }  // namespace vrt
