@@ -33,18 +33,19 @@ __global__ void __launch_bounds__(256) blit_kernel(const uchar4* __restrict__ sr
         if (py >= p.th) break;
         const BlitAxis ry = row[ly];
         const uchar4* r0 = src + (size_t)ry.i0 * p.sw; const uchar4* r1 = src + (size_t)ry.i1 * p.sw;
-        const uchar4 c00 = __ldg(r0 + cx.i0);
+        const uint32_t* w0 = reinterpret_cast<const uint32_t*>(r0); const uint32_t* w1 = reinterpret_cast<const uint32_t*>(r1);
+        const uint32_t c00 = __ldg(w0 + cx.i0);
         float r, g, b, a;
         if (__all_sync(__activemask(), cx.a == 0.0f && ry.a == 0.0f)) {
-            // sample points on texel centres (equal sizes): the weights are (1, 0, 0, 0) and the mix returns c00's values bit for bit
-            r = lutU[c00.x]; g = lutU[c00.y]; b = lutU[c00.z]; a = lutU[c00.w];
+            // sample points on texel centres: the weights are (1, 0, 0, 0) and the mix returns c00's values bit for bit
+            r = lut_byte(lutU, c00, 0); g = lut_byte(lutU, c00, 1); b = lut_byte(lutU, c00, 2); a = lut_byte(lutU, c00, 3);
         } else {
-            const uchar4 c10 = __ldg(r0 + cx.i1), c01 = __ldg(r1 + cx.i0), c11 = __ldg(r1 + cx.i1);
+            const uint32_t c10 = __ldg(w0 + cx.i1), c01 = __ldg(w1 + cx.i0), c11 = __ldg(w1 + cx.i1);
             const BlitTap t = blit_weights(cx.a, ry.a);
-            r = blit_mix(t, lutU[c00.x], lutU[c10.x], lutU[c01.x], lutU[c11.x]);
-            g = blit_mix(t, lutU[c00.y], lutU[c10.y], lutU[c01.y], lutU[c11.y]);
-            b = blit_mix(t, lutU[c00.z], lutU[c10.z], lutU[c01.z], lutU[c11.z]);
-            a = blit_mix(t, lutU[c00.w], lutU[c10.w], lutU[c01.w], lutU[c11.w]);
+            r = blit_mix(t, lut_byte(lutU, c00, 0), lut_byte(lutU, c10, 0), lut_byte(lutU, c01, 0), lut_byte(lutU, c11, 0));
+            g = blit_mix(t, lut_byte(lutU, c00, 1), lut_byte(lutU, c10, 1), lut_byte(lutU, c01, 1), lut_byte(lutU, c11, 1));
+            b = blit_mix(t, lut_byte(lutU, c00, 2), lut_byte(lutU, c10, 2), lut_byte(lutU, c01, 2), lut_byte(lutU, c11, 2));
+            a = blit_mix(t, lut_byte(lutU, c00, 3), lut_byte(lutU, c10, 3), lut_byte(lutU, c01, 3), lut_byte(lutU, c11, 3));
         }
         uchar4 o;
         if (srgb) { o.x = srgb8_lookup(thr, r); o.y = srgb8_lookup(thr, g); o.z = srgb8_lookup(thr, b); }

@@ -46,22 +46,41 @@ VRT_HD float blit_mix(const BlitTap& t, float c00, float c10, float c01, float c
 // sRGB store: thr[k] (k = 1..255) is the smallest binary32 value whose encoded UNORM8 code is >= k (built on the host by bisection over
 // the exact transfer function, vrt_output.cu), so the code of L is the number of thresholds <= L: 8 compares instead of a powf whose
 // last bit would differ between libraries. thr[0] is unused.
-VRT_HD uint8_t srgb8_lookup(const float* thr, float L) {
-    if (!(L == L)) return 0;
-#if defined(__CUDA_ARCH__)
-    // a guess from the fast transfer function (2 MUFU), then moved onto the exact code by the thresholds: the result is defined by
-    // thr[] alone, whatever the guess was (usually 0 or 1 corrections instead of 8 dependent look-ups)
-    const float l = fminf(fmaxf(L, 0.0f), 1.0f);
-    const float e = l <= 0.0031308f ? 12.92f * l : 1.055f * __powf(l, 1.0f / 2.4f) - 0.055f;
-    int code = min(max(__float2int_rn(e * 255.0f), 0), 255);
-    while (code > 0 && L < thr[code]) code--;
-    while (code < 255 && L >= thr[code + 1]) code++;
-    return (uint8_t)code;
-#else
+VRT_HD uint8_t srgb8_search(const float* thr, float L) {
     int code = 0;
     for (int step = 128; step > 0; step >>= 1) if (L >= thr[code + step]) code += step;
     return (uint8_t)code;
+}
+#if defined(__CUDACC__)
+static __device__ __noinline__ uint8_t srgb8_search_cold(const float* thr, float L) { return srgb8_search(thr, L); }
 #endif
+VRT_HD uint8_t srgb8_lookup(const float* thr, float L) {
+#if defined(__CUDA_ARCH__)
+    // a guess from the fast transfer function (lg2.approx / ex2.approx, no branches), moved by at most one onto the exact code by the two
+    // thresholds around it; the result is defined by thr[] alone: if the guess had to move, the new interval is checked and the search runs
+    // when it does not hold. NaN clamps to 0 (fmaxf returns the other operand), like the NaN -> 0 rule of the UNORM store.
+    const float l = fminf(fmaxf(L, 0.0f), 1.0f);
+    float lg, p;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(lg) : "f"(l));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(p) : "f"(lg * (1.0f / 2.4f)));
+    const float e = l <= 0.0031308f ? 12.92f * l : 1.055f * p - 0.055f;
+    const int guess = min(max(__float2int_rn(e * 255.0f), 1), 254);          // thr[guess - 1 .. guess + 2] are all in the table
+    int code = guess + (l >= thr[guess + 1] ? 1 : 0) - (l < thr[guess] ? 1 : 0);
+    if (code != guess) {
+        const bool ok = (code == 0 || l >= thr[code]) && (code == 255 || l < thr[code + 1]);
+        if (!ok) code = srgb8_search_cold(thr, l);
+    }
+    return (uint8_t)code;
+#else
+    if (!(L == L)) return 0;
+    return srgb8_search(thr, L);
+#endif
+}
+
+// lut[(word >> 8k) & 255] with the byte turned into a byte offset by one shift + mask (instead of extract, scale, add)
+VRT_HD float lut_byte(const float* lut, uint32_t word, int k) {
+    const uint32_t off = (k == 0 ? word << 2 : word >> (8 * k - 2)) & 0x3FCu;
+    return *reinterpret_cast<const float*>(reinterpret_cast<const char*>(lut) + off);
 }
 
 // ---- sRGB thresholds (host). encode(L) = round-half-even(255 * E(L)), E = the sRGB transfer function in binary64; it is monotone in L,
