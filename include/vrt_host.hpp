@@ -134,14 +134,44 @@ private:
     vrt_scene* _scene = nullptr;
 };
 
-// camera_controller.cpp:15-28 + the push-constant fill of voxel_renderer.cpp:72-83
+// camera_controller.cpp:15-71 + the push-constant fill of voxel_renderer.cpp:72-83. The reference polls GLFW; headless, the caller passes
+// the key state and cursor events in (same arithmetic, same order of operations).
 class CameraController {
 public:
+    enum Key : unsigned { KEY_W = 1, KEY_S = 2, KEY_A = 4, KEY_D = 8 };
     float position[3] = {8.0f, 8.0f, -50.0f};
     float yaw = 90.0f, pitch = 0.0f, focalLength = 1.920982f;    // voxel_renderer.cpp:20 (fov 55 degrees)
-    float direction[3], right[3], up[3];
+    float direction[3], right[3], up[3], normalDir[3];
     CameraController() { updateDirectionVectors(); }
-    void updateDirectionVectors() { vrt_camera_vectors(yaw, pitch, focalLength, direction, right, up); }
+    void updateDirectionVectors() {
+        float r2[3], u2[3];
+        vrt_camera_vectors(yaw, pitch, 1.0f, normalDir, r2, u2);          // normalDir * 1.0f == normalDir
+        vrt_camera_vectors(yaw, pitch, focalLength, direction, right, up);
+    }
+    // CameraController::update, camera_controller.cpp:30-44: cameraSpeed 50; W/S along normalDir, A/D along right
+    void update(float delta, unsigned keys) {
+        const float cameraSpeed = 50.0f;
+        for (int k = 0; k < 3; k++) {
+            if (keys & KEY_W) position[k] += (cameraSpeed * normalDir[k]) * delta;
+            if (keys & KEY_S) position[k] -= (cameraSpeed * normalDir[k]) * delta;
+            if (keys & KEY_A) position[k] -= (right[k] * cameraSpeed) * delta;
+            if (keys & KEY_D) position[k] += (right[k] * cameraSpeed) * delta;
+        }
+        updateDirectionVectors();
+    }
+    // CameraController::mouseCallback, camera_controller.cpp:46-71: drag with the right button held; one degree per pixel
+    void mouseCallback(double cursorX, double cursorY, bool rightButton) {
+        if (rightButton) {
+            if (_lastCursorX > 0 && _lastCursorY > 0) {
+                const float offsetX = static_cast<float>(cursorX - _lastCursorX), offsetY = static_cast<float>(cursorY - _lastCursorY);
+                yaw -= offsetX;
+                const float p = pitch - offsetY;
+                pitch = p < -90.0f ? -90.0f : (p > 90.0f ? 90.0f : p);
+                updateDirectionVectors();
+            }
+            _lastCursorX = cursorX; _lastCursorY = cursorY;
+        } else { _lastCursorX = -1; _lastCursorY = -1; }
+    }
     vrt_camera push(const VoxelScene& scene, const uint32_t res[2], uint32_t frame, float jx = 0.0f, float jy = 0.0f) const {
         vrt_camera c; std::memset(&c, 0, sizeof(c));
         for (int i = 0; i < 3; i++) { c.camPos[i] = position[i]; c.camDir[i] = direction[i]; c.camRight[i] = right[i]; c.camUp[i] = up[i]; }
@@ -151,6 +181,8 @@ public:
         c.cameraJitter[0] = jx; c.cameraJitter[1] = jy;
         return c;
     }
+private:
+    double _lastCursorX = -1, _lastCursorY = -1;
 };
 
 // One render target on the device (RenderImage stand-in).
@@ -273,7 +305,7 @@ public:
         : _engine(engine), _settings(settings), _scene(scene), _geometry(engine, settings, scene), _denoiser(engine, settings), _upscaler(settings),
           _blit(engine) {}
     // voxel_renderer.cpp:33-39: per-frame host update (the camera controller's input handling has no headless counterpart)
-    void update(float delta) { _upscaler.update(delta); }
+    void update(float delta, unsigned keys = 0) { camera.update(delta, keys); _upscaler.update(delta); }
     // one whole frame as the reference records it: frame counter and jitter from the upscaler stage, final image blitted into a window
     // of windowSize (engine->windowSize in the reference). Returns the window image (RGBA8, sRGB-encoded).
     const RenderImage& recordCommands(const uint32_t windowSize[2]) {

@@ -26,6 +26,20 @@ int main(int argc, char** argv) {
         try { vrt::Engine e(0); } catch (const std::runtime_error& ex) { printf("threw: %s\n", ex.what()); return 0; }
         return 3;
     }
+    if (argc == 2 && !strcmp(argv[1], "--camera")) {   // CameraController input handling: host arithmetic only, no device
+        vrt::CameraController cam;
+        using K = vrt::CameraController;
+        const struct { int kind; float delta; unsigned keys; double x, y; int button; } script[] = {
+            {0, 0.016f, K::KEY_W, 0, 0, 0}, {0, 0.016f, K::KEY_W | K::KEY_D, 0, 0, 0}, {1, 0, 0, 400.0, 300.0, 1}, {1, 0, 0, 417.5, 288.25, 1},
+            {0, 0.033f, K::KEY_S | K::KEY_A, 0, 0, 0}, {1, 0, 0, 10.0, 500.0, 1}, {1, 0, 0, 0, 0, 0}, {1, 0, 0, 90.0, 90.0, 1}, {1, 0, 0, 95.0, 700.0, 1},
+            {0, 0.5f, K::KEY_A, 0, 0, 0}, {0, 0.25f, K::KEY_W, 0, 0, 0}};
+        for (const auto& st : script) {
+            if (st.kind == 0) cam.update(st.delta, st.keys); else cam.mouseCallback(st.x, st.y, st.button != 0);
+            printf("%a %a %a %a %a %a %a %a %a %a %a %a %a %a\n", cam.position[0], cam.position[1], cam.position[2], cam.yaw, cam.pitch, cam.direction[0], cam.direction[1],
+                   cam.direction[2], cam.right[0], cam.right[1], cam.right[2], cam.up[0], cam.up[1], cam.up[2]);
+        }
+        return 0;
+    }
     if (argc != 5) { fprintf(stderr, "usage: %s scene.vox W H out_prefix\n", argv[0]); return 1; }
     try {
         auto engine = std::make_shared<vrt::Engine>(0);

@@ -35,6 +35,39 @@ def test_cpp_host_throws_without_gpu():
     assert "threw" in out and "no CPU fallback" in out
 
 
+def test_cpp_camera_controller_matches_reference_arithmetic():
+    """CameraController::update / mouseCallback (camera_controller.cpp:30-71) in the C++ mirror against a binary32 restatement here,
+    direction vectors against the oracle's camera_vectors (camera_controller.cpp:15-28): bit for bit over a scripted input sequence."""
+    out = subprocess.check_output([build_check(), "--camera"], text=True).strip().splitlines()
+    f32 = np.float32
+    pos = np.array([8.0, 8.0, -50.0], f32); yaw, pitch, focal = f32(90.0), f32(0.0), f32(1.920982)
+    last = [-1.0, -1.0]
+    W, S, A, D = 1, 2, 4, 8
+    script = [(0, 0.016, W), (0, 0.016, W | D), (1, 400.0, 300.0, 1), (1, 417.5, 288.25, 1), (0, 0.033, S | A), (1, 10.0, 500.0, 1), (1, 0, 0, 0),
+              (1, 90.0, 90.0, 1), (1, 95.0, 700.0, 1), (0, 0.5, A), (0, 0.25, W)]
+    assert len(out) == len(script)
+    for line, st in zip(out, script):
+        nd, right, _ = O.camera_vectors(float(yaw), float(pitch), 1.0)
+        if st[0] == 0:
+            delta, keys = f32(st[1]), st[2]
+            if keys & W: pos = (pos + (f32(50.0) * nd) * delta).astype(f32)
+            if keys & S: pos = (pos - (f32(50.0) * nd) * delta).astype(f32)
+            if keys & A: pos = (pos - (right * f32(50.0)) * delta).astype(f32)
+            if keys & D: pos = (pos + (right * f32(50.0)) * delta).astype(f32)
+        else:
+            _, x, y, button = st
+            if button:
+                if last[0] > 0 and last[1] > 0:
+                    yaw = f32(yaw - f32(x - last[0])); pitch = f32(min(max(f32(pitch - f32(y - last[1])), f32(-90.0)), f32(90.0)))
+                last = [x, y]
+            else:
+                last = [-1.0, -1.0]
+        d, r, u = O.camera_vectors(float(yaw), float(pitch), float(focal))
+        want = np.concatenate([pos, [yaw, pitch], d, r, u]).astype(f32)
+        got = np.array([float.fromhex(t) for t in line.split()], f32)
+        assert bits_equal(got, want)[0], (st, got, want)
+
+
 @pytest.mark.gpu
 def test_cpp_renderer_matches_oracle(tmp_path):
     data = cached_vox("treehouse")
