@@ -441,3 +441,45 @@ def test_device_flatten_multi_instance_standin(gpu_ctx):
     gs = pyvrt.VoxelScene.from_vox_bytes(gpu_ctx, data)
     assert np.array_equal(gs.download_volume(), vol) and np.array_equal(gs.palette(), pal)
     gs.destroy()
+
+
+def test_sharded_frame_denoised_on_assembling_rank_is_byte_identical(gpu_ctx):
+    """SURVEY 8(e), denoiser under sharding, route (a): the ranks trace their tiles, colour / normal / position are assembled on rank 0
+    (here by direct tile stores, as over NVLink), and the denoiser runs there on the whole frame: same bytes as the single-GPU frame."""
+    import torch
+    rng = np.random.default_rng(77)
+    whd = (56, 44, 52)
+    vol = random_volume(rng, whd, 0.03); pal = random_palette(rng, metallic_every=4)
+    noise, sky = assets.noise_standin(), assets.sky_standin(128, 64)
+    size = (200, 150)                                    # ragged in 32 x 32 tiles
+    cam = look_at_camera(whd, size, (-18, 50, -22), (28, 20, 26), frame=4)
+    st = O.make_settings()
+    gs = pyvrt.VoxelScene.from_dense(gpu_ctx, vol, pal); gs.set_noise(noise); gs.set_skybox(sky)
+    single = gpu_render(gpu_ctx, gs, cam, st, denoise=dict(iterations=2, mode=0), names=["color", "normal", "position", "denoised"])
+    gs.destroy()
+    world = 4
+    names = ("color", "normal", "position")
+    frame = {n: torch.zeros(single[n].nbytes, dtype=torch.uint8, device="cuda") for n in names}
+    torch.cuda.synchronize()
+    for r in range(world):
+        ctx = pyvrt.Context(0, rank=r, world=world)
+        s = pyvrt.VoxelScene.from_dense(ctx, vol, pal); s.set_noise(noise); s.set_skybox(sky)
+        rp = pyvrt.VoxelRenderPass(ctx, s, vrt_settings(st, out_mask=pyvrt.OUT_GBUFFER)); fr = rp.record(cam_to_py(cam))
+        for n in names:
+            fr.push_tiles(n, frame[n].data_ptr())
+        fr.sync(); fr.release(); s.destroy(); ctx.close()
+    for n in names:
+        assert np.array_equal(frame[n].cpu().numpy(), single[n].view(np.uint8).ravel()), n
+    out = torch.zeros(size[0] * size[1] * 4, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    ds = pyvrt.DenoiserSettings(1, 2, 20.4, 1e-2, 1e-1, 2.0, 0)
+    pyvrt.denoise_device(gpu_ctx, frame["color"].data_ptr(), frame["normal"].data_ptr(), frame["position"].data_ptr(), size, ds, out.data_ptr())
+    gpu_ctx.sync()
+    assert np.array_equal(out.cpu().numpy(), single["denoised"].view(np.uint8).ravel())
+    # a sharded context refuses to denoise its own shard (taps cross tile borders): the error says where the denoiser belongs
+    ctx = pyvrt.Context(0, rank=1, world=2)
+    s = pyvrt.VoxelScene.from_dense(ctx, vol, pal); s.set_noise(noise); s.set_skybox(sky)
+    with pytest.raises(pyvrt.VrtError) as e:
+        pyvrt.VoxelRenderPass(ctx, s, vrt_settings(st, denoise=dict(iterations=2))).record(cam_to_py(cam))
+    assert "rank 0" in str(e.value)
+    s.destroy(); ctx.close()
