@@ -483,3 +483,25 @@ def test_sharded_frame_denoised_on_assembling_rank_is_byte_identical(gpu_ctx):
         pyvrt.VoxelRenderPass(ctx, s, vrt_settings(st, denoise=dict(iterations=2))).record(cam_to_py(cam))
     assert "rank 0" in str(e.value)
     s.destroy(); ctx.close()
+
+
+def test_denoiser_iteration0_edge_blind_kernel_is_exact(gpu_ctx):
+    """Iteration 0 (phi = +inf) runs the edge-blind kernel: no exp, so the result equals the oracle's byte for byte, also where the
+    G-buffer holds inf / NaN / huge positions (whose weights are 1 all the same)."""
+    import torch
+    from vrtlib import blind_blur
+    rng = np.random.default_rng(23)
+    h, w = 270, 481
+    color = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+    normal = rng.integers(-127, 128, (h, w, 4)).astype(np.int8)
+    pos = (rng.random((h, w, 4), dtype=np.float32) * 1e3).astype(np.float32)
+    pos[3, 4, 0] = np.inf; pos[10, 11, 1] = np.nan; pos[20, 30, 2] = 3e38; pos[21, 30, 2] = -3e38; pos[0, 0, :] = -np.inf
+    tc, tn, tp = torch.from_numpy(color).cuda(), torch.from_numpy(normal).cuda(), torch.from_numpy(pos).cuda()
+    for mode in (0, 1):
+        out = torch.zeros_like(tc)
+        torch.cuda.synchronize()
+        pyvrt.denoise_device(gpu_ctx, tc.data_ptr(), tn.data_ptr(), tp.data_ptr(), (w, h), pyvrt.DenoiserSettings(1, 1, 20.4, 1e-2, 1e-1, 2.0, mode), out.data_ptr())
+        gpu_ctx.sync()
+        got = out.cpu().numpy()
+        assert np.array_equal(got, O.denoise(color, normal, pos, iterations=1, mode=mode)), mode
+        assert np.array_equal(got, blind_blur(color, mode)), mode

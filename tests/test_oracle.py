@@ -303,3 +303,16 @@ def test_blit_known_answers():
     assert tuple(enc) == (0, 13, 188, 128)                                       # 1/255 -> 12.71 -> 13; 128/255 -> 187.85 -> 188
     full = np.full((1, 1, 4), 255, np.uint8)
     assert tuple(O.blit(full, (3, 3), srgb=True)[1, 1]) == (255, 255, 255, 255)
+
+
+def test_iteration0_is_a_plain_blur_whatever_the_gbuffer_holds():
+    from vrtlib import blind_blur
+    rng = np.random.default_rng(17)
+    h, w = 37, 53
+    color = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+    normal = rng.integers(-127, 128, (h, w, 4)).astype(np.int8)
+    pos = (rng.random((h, w, 4), dtype=np.float32) * 1e3).astype(np.float32)
+    pos[3, 4, 0] = np.inf; pos[10, 11, 1] = np.nan; pos[20, 30, 2] = 3e38; pos[21, 30, 2] = -3e38; pos[0, 0, :] = -np.inf
+    for mode in (0, 1):
+        got = O.denoise(color, normal, pos, iterations=1, mode=mode)
+        assert np.array_equal(got, blind_blur(color, mode)), mode

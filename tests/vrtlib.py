@@ -178,3 +178,23 @@ def assert_planes_exact(got, want, names=None, rows=None):
             g, w = g[rows[0]:rows[1]:rows[2]], w[rows[0]:rows[1]:rows[2]]
         ok, bad = bits_equal(g, w)
         assert ok, f"plane {n}: {bad} of {g.size} elements differ"
+
+
+def blind_blur(color, mode):
+    """Iteration 0 of the denoiser as a plain kernel-weighted blur, in the oracle's float operations and order (what the product's
+    edge-blind kernel computes): taps clamped to the edge, (c * k) summed left to right, divided by the summed k, UNORM8 store."""
+    f32 = np.float32
+    h, w = color.shape[:2]
+    c = color.astype(f32) / f32(255)
+    g = lambda x, y: f32(np.exp(f32(-(f32(x * x) / f32(8) + f32(y * y) / f32(8)))))
+    if mode == 0:      # AS_EXECUTED (SURVEY F6): the shader's stride-16 view of the tables
+        taps = [(-1, -1, g(-1, -1)), (1, -1, g(0, 0)), (0, 0, g(1, 1))]
+    else:
+        taps = [(x, y, g(x, y)) for y in (-1, 0, 1) for x in (-1, 0, 1)]
+    ys, xs = np.mgrid[0:h, 0:w]
+    acc = np.zeros((h, w, 4), f32); tot = f32(0)
+    for dx, dy, k in taps:
+        acc = (acc + c[np.clip(ys + dy, 0, h - 1), np.clip(xs + dx, 0, w - 1)] * k).astype(f32)
+        tot = f32(tot + k)
+    v = np.clip(acc / tot, 0, 1).astype(f32)
+    return np.rint(v * f32(255)).astype(np.uint8)

@@ -24,44 +24,68 @@ __device__ __forceinline__ float dot4d(float4 a, float4 b) {   // t = a - b; dot
     return ((x * x + y * y) + z * z) + w * w;
 }
 
+// BLIND: all three phi are +inf, which is what the reference's host code produces for iteration 0 (1.0f / float(0) * phi0,
+// denoiser_stage.cpp:143-154). Then every edge-stopping weight is exactly 1 whatever the inputs are — x / inf is +-0 for finite x and
+// NaN for x = inf / NaN, exp gives 1 or NaN, and min(NaN, 1) = 1 — so the iteration is a plain weighted blur of the colour plane:
+// normals and positions are not read, no exp, no division (the IEEE divisions by inf all took the slow path). The sums are the same
+// float operations in the same order ((c * 1) * k == c * k, 1 * k == k), so the bytes are those of the general kernel.
+template <bool BLIND>
 __global__ void __launch_bounds__(256) denoise_kernel(const uint8_t* __restrict__ color, const int8_t* __restrict__ normal,
                                                       const float* __restrict__ position, uint8_t* __restrict__ out, int W, int H,
                                                       const DenoiseTaps taps, const DenoiseIter it) {
     __shared__ float lutU[256], lutS[256];
     lutU[threadIdx.x] = (float)threadIdx.x / 255.0f;
-    lutS[threadIdx.x] = snorm((signed char)threadIdx.x);          // indexed by the byte pattern
+    if (!BLIND) lutS[threadIdx.x] = snorm((signed char)threadIdx.x);          // indexed by the byte pattern
     __syncthreads();
     const int px = blockIdx.x * 32 + (threadIdx.x & 31), py = blockIdx.y * 8 + (threadIdx.x >> 5);
     if (px >= W || py >= H) return;
     const size_t p = (size_t)py * W + px;
-    const float4 sc = ld_color(color, p, lutU), sn = ld_normal(normal, p, lutS), sp = reinterpret_cast<const float4*>(position)[p];
     float4 sum = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     float total = 0.0f;
-    const float sw2 = it.stepWidth * it.stepWidth;
+    if (BLIND) {
 #pragma unroll 1
-    for (int i = 0; i < taps.n; i++) {
-        // uv = vScreenPos + offset*step*stepWidth under LINEAR/CLAMP = the texel holding the sample point
-        int tx = px + f2i(floorf(0.5f + (float)taps.ox[i] * it.stepWidth));
-        int ty = py + f2i(floorf(0.5f + (float)taps.oy[i] * it.stepWidth));
-        tx = min(max(tx, 0), W - 1); ty = min(max(ty, 0), H - 1);
-        const size_t q = (size_t)ty * W + tx;
-        const float4 oc = ld_color(color, q, lutU);
-        const float cw = fminf(expf(-(dot4d(sc, oc)) / it.phiColor), 1.0f);
-        const float4 on = ld_normal(normal, q, lutS);
-        const float nw = fminf(expf(-(fmaxf(dot4d(sn, on) / sw2, 0.0f)) / it.phiNormal), 1.0f);
-        const float4 op = reinterpret_cast<const float4*>(position)[q];
-        const float pw = fminf(expf(-(dot4d(sp, op)) / it.phiPos), 1.0f);
-        const float weight = (cw * nw) * pw;
-        const float k = taps.k[i];
-        sum.x += (oc.x * weight) * k; sum.y += (oc.y * weight) * k; sum.z += (oc.z * weight) * k; sum.w += (oc.w * weight) * k;
-        total += weight * k;
+        for (int i = 0; i < taps.n; i++) {
+            const int tx = min(max(px + taps.dx[i], 0), W - 1), ty = min(max(py + taps.dy[i], 0), H - 1);
+            const float4 oc = ld_color(color, (size_t)ty * W + tx, lutU);
+            const float k = taps.k[i];
+            sum.x += oc.x * k; sum.y += oc.y * k; sum.z += oc.z * k; sum.w += oc.w * k;
+            total += k;
+        }
+    } else {
+        const float4 sc = ld_color(color, p, lutU), sn = ld_normal(normal, p, lutS), sp = reinterpret_cast<const float4*>(position)[p];
+        const float sw2 = it.stepWidth * it.stepWidth;
+#pragma unroll 1
+        for (int i = 0; i < taps.n; i++) {
+            // uv = vScreenPos + offset*step*stepWidth under LINEAR/CLAMP = the texel holding the sample point; the texel offsets
+            // floor(0.5 + offset*stepWidth) are per-iteration constants (taps.dx / dy, computed on the host with the same float operations)
+            const int tx = min(max(px + taps.dx[i], 0), W - 1), ty = min(max(py + taps.dy[i], 0), H - 1);
+            const size_t q = (size_t)ty * W + tx;
+            const float4 oc = ld_color(color, q, lutU);
+            const float cw = fminf(expf(-(dot4d(sc, oc)) / it.phiColor), 1.0f);
+            const float4 on = ld_normal(normal, q, lutS);
+            const float nw = fminf(expf(-(fmaxf(dot4d(sn, on) / sw2, 0.0f)) / it.phiNormal), 1.0f);
+            const float4 op = reinterpret_cast<const float4*>(position)[q];
+            const float pw = fminf(expf(-(dot4d(sp, op)) / it.phiPos), 1.0f);
+            const float weight = (cw * nw) * pw;
+            const float k = taps.k[i];
+            sum.x += (oc.x * weight) * k; sum.y += (oc.y * weight) * k; sum.z += (oc.z * weight) * k; sum.w += (oc.w * weight) * k;
+            total += weight * k;
+        }
     }
     reinterpret_cast<uchar4*>(out)[p] = make_uchar4(to_unorm8(sum.x / total), to_unorm8(sum.y / total), to_unorm8(sum.z / total), to_unorm8(sum.w / total));
 }
 
 cudaError_t launch_denoise(const uint8_t* color, const int8_t* normal, const float* position, uint8_t* out, int W, int H,
                            const DenoiseTaps& taps, const DenoiseIter& it, cudaStream_t stream) {
-    denoise_kernel<<<dim3((W + 31) / 32, (H + 7) / 8), 256, 0, stream>>>(color, normal, position, out, W, H, taps, it);
+    DenoiseTaps t = taps;
+    for (int i = 0; i < t.n; i++) {   // the texel offsets of this iteration (the kernel used to compute them per tap and pixel)
+        t.dx[i] = f2i(floorf(0.5f + (float)t.ox[i] * it.stepWidth));
+        t.dy[i] = f2i(floorf(0.5f + (float)t.oy[i] * it.stepWidth));
+    }
+    const float inf = INFINITY;
+    const dim3 grid((W + 31) / 32, (H + 7) / 8);
+    if (it.phiColor == inf && it.phiNormal == inf && it.phiPos == inf) denoise_kernel<true><<<grid, 256, 0, stream>>>(color, normal, position, out, W, H, t, it);
+    else denoise_kernel<false><<<grid, 256, 0, stream>>>(color, normal, position, out, W, H, t, it);
     return cudaGetLastError();
 }
 
