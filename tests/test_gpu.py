@@ -505,3 +505,12 @@ def test_denoiser_iteration0_edge_blind_kernel_is_exact(gpu_ctx):
         got = out.cpu().numpy()
         assert np.array_equal(got, O.denoise(color, normal, pos, iterations=1, mode=mode)), mode
         assert np.array_equal(got, blind_blur(color, mode)), mode
+
+
+def test_degenerate_rotation_takes_the_ordered_host_flatten(gpu_ctx):
+    from vrtlib import degenerate_rotation_vox
+    data = degenerate_rotation_vox()
+    rc, vol, pal = O.load_vox(data)
+    gs = pyvrt.VoxelScene.from_vox_bytes(gpu_ctx, data)
+    assert np.array_equal(gs.download_volume(), vol) and np.array_equal(gs.palette(), pal)
+    gs.destroy()

@@ -230,3 +230,13 @@ def test_image_writers_round_trip(tmp_path):
         pass
     with pytest.raises(pyvrt.VrtError):
         pyvrt.image_write(str(tmp_path / "no_such_dir" / "x.png"), img)
+
+
+def test_vox_decode_degenerate_rotation_matches_oracle():
+    from vrtlib import degenerate_rotation_vox
+    data = degenerate_rotation_vox()
+    v, p = pyvrt.vox_decode(data)
+    rc, v2, p2 = O.load_vox(data)
+    assert rc == 0 and v.shape == v2.shape and np.array_equal(v, v2) and np.array_equal(p, p2)
+    good, _ = pyvrt.vox_decode(open(os.path.join(GOLD, "overlap9.vox"), "rb").read())
+    assert good.shape != v.shape or not np.array_equal(good, v)          # the patch really changed the scene

@@ -199,3 +199,14 @@ def blind_blur(color, mode):
         tot = f32(tot + k)
     v = np.clip(acc / tot, 0, 1).astype(f32)
     return np.rint(v * f32(255)).astype(np.uint8)
+
+
+def degenerate_rotation_vox() -> bytes:
+    """overlap9.vox with two instance rotations patched to packed values that name the same axis twice (_r = 0 and 21). The reference's
+    parser asserts on them in a debug build (ogt_vox.h:874) and leaves a zero row in a release build; oracle and product model the
+    release behaviour. Such an instance maps many voxels onto one cell: the flatten's loop order decides, so the product flattens it on
+    the host (vrt_api.cu scene_from_layout)."""
+    data = bytearray(open(os.path.join(ROOT, "tests", "golden", "overlap9.vox"), "rb").read())
+    assert data[6724:6726] == b"_r" and data[6730:6731] == b"4" and data[6926:6928] == b"_r" and data[6932:6934] == b"17"
+    data[6730:6731] = b"0"; data[6932:6934] = b"21"
+    return bytes(data)
