@@ -162,6 +162,12 @@ int vrt_scene_set_skybox(vrt_scene*, const float* rgba32f, uint32_t w, uint32_t 
 int vrt_scene_bounds(const vrt_scene*, uint32_t whd[3]);
 int vrt_scene_palette(const vrt_scene*, vrt_material palette[256]);
 int vrt_scene_download_volume(const vrt_scene*, uint8_t* dst, size_t bytes);
+/* Only the volume and the palette are resident for every scene; the safe-step fields of a traversal back-end are built the first
+ * time it is asked for. The default back-end is prepared by the loaders, so this is only needed before measuring another one
+ * (0 = default). Thread-safe per scene. */
+int vrt_scene_prepare(vrt_scene*, uint32_t traversal);
+/* device bytes of the scene: the dense volume, the fields built so far, the peak during their build; host wall time of load + builds */
+int vrt_scene_memory(const vrt_scene*, size_t* volume_bytes, size_t* field_bytes, size_t* peak_build_bytes, double* load_ms);
 int vrt_scene_accel_info(const vrt_scene*, size_t* dense_bytes, size_t* brick_mask_bytes, size_t* brick_dist_bytes);
 /* brick levels back to the host (tests): bmask = 8 B per 4x4x4 brick, bdist = 1 B per brick; either may be NULL */
 int vrt_scene_download_accel(const vrt_scene*, uint64_t* bmask_dst, uint8_t* bdist_dst);

@@ -240,3 +240,78 @@ def test_vox_decode_degenerate_rotation_matches_oracle():
     assert rc == 0 and v.shape == v2.shape and np.array_equal(v, v2) and np.array_equal(p, p2)
     good, _ = pyvrt.vox_decode(open(os.path.join(GOLD, "overlap9.vox"), "rb").read())
     assert good.shape != v.shape or not np.array_equal(good, v)          # the patch really changed the scene
+
+
+# ---- hostile .vox input: the C ABI must answer with a status code, never crash or throw ----
+def _vox_chunk(tag: bytes, body: bytes) -> bytes:
+    return tag + len(body).to_bytes(4, "little") + (0).to_bytes(4, "little") + body
+
+
+def _crafted_vox_files():
+    u32 = lambda *v: b"".join(int(x).to_bytes(4, "little") for x in v)
+    head = b"VOX " + u32(150) + _vox_chunk(b"MAIN", b"")
+    xyzi = _vox_chunk(b"XYZI", u32(1) + bytes([0, 0, 0, 7]))
+    return {
+        "size_product_wraps_to_zero": head + _vox_chunk(b"SIZE", u32(0x80000000, 0x80000000, 4)) + xyzi,
+        "size_product_wraps_small": head + _vox_chunk(b"SIZE", u32(0x10001, 0x10001, 0x10001)) + xyzi,
+        "size_huge": head + _vox_chunk(b"SIZE", u32(60000, 60000, 60000)) + xyzi,
+        "node_id_huge": head + _vox_chunk(b"SIZE", u32(2, 2, 2)) + xyzi + _vox_chunk(b"nTRN", u32(0xFFFFFFF0, 0, 1, 0xFFFFFFFF, 0, 1, 0)),
+        "group_fanout_lie": head + _vox_chunk(b"SIZE", u32(2, 2, 2)) + xyzi + _vox_chunk(b"nGRP", u32(0, 0, 0xFFFFFFFF)),
+        "self_referencing_group": head + _vox_chunk(b"SIZE", u32(2, 2, 2)) + xyzi + _vox_chunk(b"nGRP", u32(0, 0, 8, 0, 0, 0, 0, 0, 0, 0, 0)),
+    }
+
+
+_FUZZ_CHILD = r"""
+import sys, os, ctypes as C
+import numpy as np
+sys.path.insert(0, sys.argv[1])
+import pyvrt
+L = pyvrt.lib()
+mode = sys.argv[2]
+def decode(data):
+    buf = (C.c_uint8 * max(1, len(data))).from_buffer_copy(data or b"\0")
+    vol = C.c_void_p(); whd = (C.c_uint32 * 3)(); pal = np.zeros((256, 8), np.float32)
+    rc = L.vrt_vox_decode(buf, C.c_size_t(len(data)), C.byref(vol), whd, pal.ctypes.data_as(C.c_void_p))
+    if rc == 0:
+        L.vrt_host_free(vol)
+    return rc
+if mode == "crafted":
+    import pickle
+    files = pickle.load(open(sys.argv[3], "rb"))
+    for name, data in files.items():
+        rc = decode(data)
+        assert rc in (-4, -9, -3), (name, rc)        # PARSE, OOM or NO_INSTANCE: a status code, not a crash
+        print(name, rc)
+else:
+    rng = np.random.default_rng(int(sys.argv[4]))
+    seeds = [open(os.path.join(sys.argv[3], f), "rb").read() for f in sorted(os.listdir(sys.argv[3])) if f.endswith(".vox")]
+    n = int(sys.argv[5]); ok = 0
+    for it in range(n):
+        d = bytearray(seeds[it % len(seeds)])
+        for _ in range(int(rng.integers(1, 7))):
+            d[int(rng.integers(0, len(d)))] = int(rng.integers(0, 256))
+        rc = decode(bytes(d))
+        assert rc in (0, -2, -3, -4, -9), rc
+        ok += rc == 0
+    print("fuzz", n, "decoded", ok)
+"""
+
+
+def _run_child(args):
+    import subprocess, sys
+    p = subprocess.run([sys.executable, "-c", _FUZZ_CHILD, os.path.join(ROOT, "voxel-raytracing_b200")] + args, capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, f"child exited {p.returncode} (139 = segfault, 134 = abort)\n{p.stdout[-2000:]}\n{p.stderr[-2000:]}"
+    return p.stdout
+
+
+def test_vox_decode_survives_crafted_files(tmp_path):
+    import pickle
+    f = tmp_path / "crafted.pkl"
+    pickle.dump(_crafted_vox_files(), open(f, "wb"))
+    out = _run_child(["crafted", str(f)])
+    assert "size_product_wraps_to_zero -4" in out and "node_id_huge -4" in out
+
+
+def test_vox_decode_survives_mutation_fuzz():
+    out = _run_child(["fuzz", GOLD, "1234", "2000"])
+    assert "fuzz 2000" in out

@@ -60,7 +60,7 @@ cudaError_t launch_build_accel(const uint8_t* vol, uint32_t W, uint32_t H, uint3
         dist_pass_kernel<2><<<grid, block, 0, stream>>>(tmpB, bdist, (int)Bx, (int)By, (int)Bz);
         n += 3;
     }
-    if (launches) *launches = n;
+    if (launches) *launches += n;
     return cudaGetLastError();
 }
 
@@ -114,17 +114,18 @@ __global__ void fine_merge_kernel(const uint8_t* __restrict__ fine, const uint8_
     uint32_t n = f;
     if (f != 0 && d != 0) n = max(f, (d - 1u) * 4u + 1u);
     n = min(n, VRT_SAFE_MAX);
-    fdist[b * 64u + ((x & 3u) | ((y & 3u) << 2) | ((z & 3u) << 4))] = (uint8_t)n;
-    ldist[(size_t)(x + 1u) + (size_t)(y + 1u) * (W + 2u) + (size_t)(z + 1u) * (W + 2u) * (H + 2u)] = (uint8_t)n;
+    if (fdist) fdist[b * 64u + ((x & 3u) | ((y & 3u) << 2) | ((z & 3u) << 4))] = (uint8_t)n;
+    if (ldist) ldist[(size_t)(x + 1u) + (size_t)(y + 1u) * (W + 2u) + (size_t)(z + 1u) * (W + 2u) * (H + 2u)] = (uint8_t)n;
 }
 
 cudaError_t launch_build_fdist(const uint8_t* vol, const uint8_t* bdist, uint32_t W, uint32_t H, uint32_t D, uint8_t* fdist, uint8_t* ldist,
                                uint8_t* a, uint8_t* t1, uint8_t* t2, cudaStream_t stream, int* launches) {
     const size_t n = (size_t)W * H * D;
     const uint32_t Bx = (W + 3) / 4, By = (H + 3) / 4, Bz = (D + 3) / 4;
-    cudaError_t e = cudaMemsetAsync(fdist, 0, (size_t)Bx * By * Bz * 64u, stream);   // padding voxels of edge bricks
+    // either output may be null (only the field of the back-end asked for is built)
+    cudaError_t e = fdist ? cudaMemsetAsync(fdist, 0, (size_t)Bx * By * Bz * 64u, stream) : cudaSuccess;   // padding voxels of edge bricks
     if (e != cudaSuccess) return e;
-    e = cudaMemsetAsync(ldist, (int)VRT_LIN_OOB, (size_t)(W + 2u) * (H + 2u) * (D + 2u), stream);               // apron
+    e = ldist ? cudaMemsetAsync(ldist, (int)VRT_LIN_OOB, (size_t)(W + 2u) * (H + 2u) * (D + 2u), stream) : cudaSuccess;   // apron
     if (e != cudaSuccess) return e;
     fine_init_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(vol, a, n);
     int cnt = 1;

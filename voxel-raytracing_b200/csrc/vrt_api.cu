@@ -3,10 +3,13 @@
 // VoxelRenderer::recordCommands (voxel_renderer.cpp:55-105): geometry pass, then optional denoiser passes.
 // There is NO CPU fallback: without a CUDA device context creation fails with VRT_E_NO_DEVICE.
 #include <cuda_runtime.h>
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <cstdlib>
+#include <chrono>
+#include <mutex>
 #include <new>
 #include <string>
 #include <vector>
@@ -29,14 +32,21 @@ struct vrt_context {
     std::vector<struct vrt_frame*> frames;
 };
 
+// Only the dense volume and the palette are resident for every scene. The fields of a traversal back-end are built when that
+// back-end is first asked for (vrt_scene_prepare, or the first vrt_render that names it), under the scene's mutex: the default
+// back-end (OCTANT) is prepared at load time so that no frame pays for it.
 struct vrt_scene {
     vrt_context* ctx = nullptr;
     uint32_t w = 0, h = 0, d = 0, Bx = 0, By = 0, Bz = 0;
     uint8_t* vol = nullptr; unsigned long long* bmask = nullptr; uint8_t* bdist = nullptr; uint8_t* fdist = nullptr; uint8_t* ldist = nullptr;
-    uint8_t* odist[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // built on first use (scene_ensure_octant)
+    uint8_t* odist[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     vrt_material* palette = nullptr; vrt_material hostPalette[256];
     uint8_t* noise = nullptr; float* sky = nullptr; uint32_t skyW = 0, skyH = 0;
     int accelLaunches = 0;
+    std::mutex fieldMutex;               // guards the lazy field builds below
+    size_t fieldBytes = 0;               // safe-step fields resident now
+    size_t peakBuildBytes = 0;           // largest scratch + fields footprint seen during a build
+    double loadMs = 0.0;                 // host wall time of upload / generate / flatten + field builds so far
 };
 
 static const int kPlaneBpp[VRT_PLANE_COUNT] = {4, 4, 4, 8, 1, 16, 4, 8, 1, 12, 4, 4};
@@ -68,6 +78,7 @@ struct vrt_frame {
 extern "C" const char* vrt_last_error(void) { return g_err.c_str(); }
 extern "C" const char* vrt_version(void) { return "vrt 0.1 (sm_100a)"; }
 
+extern "C" void vrt_context_destroy(vrt_context* c);
 extern "C" int vrt_context_create(int device, vrt_context** out) {
     if (!out) return fail(VRT_E_INVALID, "out is null");
     int n = 0;
@@ -78,14 +89,15 @@ extern "C" int vrt_context_create(int device, vrt_context** out) {
     vrt_context* c = new (std::nothrow) vrt_context();
     if (!c) return fail(VRT_E_OOM, "host allocation failed");
     c->device = device;
-    CU(cudaGetDeviceProperties(&c->prop, device));
     int prLow = 0, prHigh = 0;
-    CU(cudaDeviceGetStreamPriorityRange(&prLow, &prHigh));
-    CU(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prHigh));
-    CU(cudaStreamCreateWithPriority(&c->side.stream, cudaStreamNonBlocking, prLow));
-    CU(cudaEventCreateWithFlags(&c->side.fork, cudaEventDisableTiming));
-    CU(cudaEventCreateWithFlags(&c->side.join, cudaEventDisableTiming));
-    CU(cudaStreamCreateWithFlags(&c->copyStream, cudaStreamNonBlocking));
+    e = cudaGetDeviceProperties(&c->prop, device);
+    if (e == cudaSuccess) e = cudaDeviceGetStreamPriorityRange(&prLow, &prHigh);
+    if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prHigh);
+    if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&c->side.stream, cudaStreamNonBlocking, prLow);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->side.fork, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->side.join, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copyStream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) { vrt_context_destroy(c); return fail(VRT_E_CUDA, cudaGetErrorString(e)); }   // frees whatever was created
     *out = c;
     return VRT_OK;
 }
@@ -170,53 +182,130 @@ static int scene_alloc(vrt_context* c, uint32_t w, uint32_t h, uint32_t d, vrt_s
     if (!s) return fail(VRT_E_OOM, "host allocation failed");
     s->ctx = c; s->w = w; s->h = h; s->d = d;
     s->Bx = (w + 3) / 4; s->By = (h + 3) / 4; s->Bz = (d + 3) / 4;
-    const size_t nb = (size_t)s->Bx * s->By * s->Bz;
     cudaError_t e = cudaMalloc(&s->vol, (size_t)w * h * d);
-    if (e == cudaSuccess) e = cudaMalloc(&s->bmask, nb * 8);
-    if (e == cudaSuccess) e = cudaMalloc(&s->bdist, nb);
-    if (e == cudaSuccess) e = cudaMalloc(&s->fdist, nb * 64);
-    if (e == cudaSuccess) e = cudaMalloc(&s->ldist, (size_t)(w + 2) * (h + 2) * (d + 2));
     if (e == cudaSuccess) e = cudaMalloc(&s->palette, sizeof(vrt_material) * 256);
     if (e != cudaSuccess) { vrt_scene_destroy(s); return fail(e == cudaErrorMemoryAllocation ? VRT_E_OOM : VRT_E_CUDA, cudaGetErrorString(e)); }
     *out = s;
     return VRT_OK;
 }
 
-static int scene_finish(vrt_scene* s, const vrt_material palette[256]) {
+static double now_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+static int cuda_fail(cudaError_t e) { return fail(e == cudaErrorMemoryAllocation ? VRT_E_OOM : VRT_E_CUDA, cudaGetErrorString(e)); }
+
+// brick occupancy + brick distance (back-end BRICK; far-field term of FINE / LINEAR). Caller holds fieldMutex.
+static int scene_ensure_bricks(vrt_scene* s) {
+    if (s->bmask) return VRT_OK;
+    vrt_context* c = s->ctx;
+    const size_t nb = (size_t)s->Bx * s->By * s->Bz;
+    uint8_t *tmpA = nullptr, *tmpB = nullptr;
+    cudaError_t e = cudaMalloc(&s->bmask, nb * 8);
+    if (e == cudaSuccess) e = cudaMalloc(&s->bdist, nb);
+    if (e == cudaSuccess) e = cudaMalloc(&tmpA, nb);
+    if (e == cudaSuccess) e = cudaMalloc(&tmpB, nb);
+    if (e == cudaSuccess) e = launch_build_accel(s->vol, s->w, s->h, s->d, s->bmask, s->bdist, tmpA, tmpB, c->stream, &s->accelLaunches);
+    const cudaError_t e2 = cudaStreamSynchronize(c->stream);
+    cudaFree(tmpA); cudaFree(tmpB);
+    if (e == cudaSuccess) e = e2;
+    if (e != cudaSuccess) { cudaFree(s->bmask); cudaFree(s->bdist); s->bmask = nullptr; s->bdist = nullptr; return cuda_fail(e); }
+    s->peakBuildBytes = std::max(s->peakBuildBytes, s->fieldBytes + nb * 11);
+    s->fieldBytes += nb * 9;
+    return VRT_OK;
+}
+// per-voxel isotropic safe-step field: bricked (FINE) and / or aproned linear (LINEAR); three volume-sized scratch buffers
+static int scene_ensure_iso(vrt_scene* s, bool wantFine, bool wantLinear) {
+    wantFine = wantFine && !s->fdist; wantLinear = wantLinear && !s->ldist;
+    if (!wantFine && !wantLinear) return VRT_OK;
+    int rc = scene_ensure_bricks(s);
+    if (rc) return rc;
+    vrt_context* c = s->ctx;
+    const size_t nv = (size_t)s->w * s->h * s->d, nb = (size_t)s->Bx * s->By * s->Bz, nl = (size_t)(s->w + 2) * (s->h + 2) * (s->d + 2);
+    uint8_t *a = nullptr, *t1 = nullptr, *t2 = nullptr, *fd = nullptr, *ld = nullptr;
+    cudaError_t e = cudaMalloc(&a, nv);
+    if (e == cudaSuccess) e = cudaMalloc(&t1, nv);
+    if (e == cudaSuccess) e = cudaMalloc(&t2, nv);
+    if (e == cudaSuccess && wantFine) e = cudaMalloc(&fd, nb * 64);
+    if (e == cudaSuccess && wantLinear) e = cudaMalloc(&ld, nl);
+    if (e == cudaSuccess) e = launch_build_fdist(s->vol, s->bdist, s->w, s->h, s->d, fd, ld, a, t1, t2, c->stream, &s->accelLaunches);
+    const cudaError_t e2 = cudaStreamSynchronize(c->stream);
+    cudaFree(a); cudaFree(t1); cudaFree(t2);
+    if (e == cudaSuccess) e = e2;
+    if (e != cudaSuccess) { cudaFree(fd); cudaFree(ld); return cuda_fail(e); }
+    const size_t add = (fd ? nb * 64 : 0) + (ld ? nl : 0);
+    s->peakBuildBytes = std::max(s->peakBuildBytes, s->fieldBytes + add + 3 * nv);
+    s->fieldBytes += add;
+    if (fd) s->fdist = fd;
+    if (ld) s->ldist = ld;
+    return VRT_OK;
+}
+// directional safe-step fields (OCTANT): 8 fields of one byte per voxel
+static int scene_ensure_octant(vrt_scene* s) {
+    if (s->odist[0]) return VRT_OK;
+    vrt_context* c = s->ctx;
+    const size_t fieldBytes = (size_t)(s->w + 2) * (s->h + 2) * (s->d + 2), scratchBytes = octant_scratch_bytes(s->w, s->h, s->d);
+    uint32_t* scratch = nullptr;
+    cudaError_t e = cudaMalloc(&scratch, scratchBytes);
+    for (int o = 0; o < 8 && e == cudaSuccess; o++) e = cudaMalloc(&s->odist[o], fieldBytes);
+    if (e == cudaSuccess) e = launch_build_odist(s->vol, s->w, s->h, s->d, s->odist, scratch, c->stream, &s->accelLaunches);
+    const cudaError_t e2 = cudaStreamSynchronize(c->stream);
+    cudaFree(scratch);
+    if (e == cudaSuccess) e = e2;
+    if (e != cudaSuccess) {
+        for (uint8_t*& p : s->odist) { cudaFree(p); p = nullptr; }
+        return cuda_fail(e);
+    }
+    s->peakBuildBytes = std::max(s->peakBuildBytes, s->fieldBytes + 8 * fieldBytes + scratchBytes);
+    s->fieldBytes += 8 * fieldBytes;
+    return VRT_OK;
+}
+static int scene_ensure(vrt_scene* s, uint32_t traversal) {
+    std::lock_guard<std::mutex> lock(s->fieldMutex);
+    const double t0 = now_ms();
+    int rc = VRT_OK;
+    switch (traversal == VRT_TRAVERSAL_DEFAULT ? (uint32_t)VRT_TRAVERSAL_OCTANT : traversal) {
+        case VRT_TRAVERSAL_DENSE_U8: break;
+        case VRT_TRAVERSAL_BRICK: rc = scene_ensure_bricks(s); break;
+        case VRT_TRAVERSAL_FINE: rc = scene_ensure_iso(s, true, false); break;
+        case VRT_TRAVERSAL_LINEAR: rc = scene_ensure_iso(s, false, true); break;
+        case VRT_TRAVERSAL_OCTANT: rc = scene_ensure_octant(s); break;
+        default: rc = fail(VRT_E_INVALID, "unknown traversal");
+    }
+    s->loadMs += now_ms() - t0;
+    return rc;
+}
+extern "C" int vrt_scene_prepare(vrt_scene* s, uint32_t traversal) {
+    if (!s) return fail(VRT_E_INVALID, "null argument");
+    CU(cudaSetDevice(s->ctx->device));
+    return scene_ensure(s, traversal);
+}
+extern "C" int vrt_scene_memory(const vrt_scene* s, size_t* volume_bytes, size_t* field_bytes, size_t* peak_build_bytes, double* load_ms) {
+    if (!s) return fail(VRT_E_INVALID, "null argument");
+    if (volume_bytes) *volume_bytes = (size_t)s->w * s->h * s->d;
+    if (field_bytes) *field_bytes = s->fieldBytes;
+    if (peak_build_bytes) *peak_build_bytes = s->peakBuildBytes + (size_t)s->w * s->h * s->d;
+    if (load_ms) *load_ms = s->loadMs;
+    return VRT_OK;
+}
+
+// palette upload + the default back-end's fields (so that no frame pays for them)
+static int scene_finish(vrt_scene* s, const vrt_material palette[256], double t0) {
     vrt_context* c = s->ctx;
     memcpy(s->hostPalette, palette, sizeof(vrt_material) * 256);
     CU(cudaMemcpyAsync(s->palette, palette, sizeof(vrt_material) * 256, cudaMemcpyHostToDevice, c->stream));
-    const size_t nb = (size_t)s->Bx * s->By * s->Bz;
-    uint8_t *tmpA = nullptr, *tmpB = nullptr;
-    CU(cudaMalloc(&tmpA, nb)); CU(cudaMalloc(&tmpB, nb));
-    cudaError_t e = launch_build_accel(s->vol, s->w, s->h, s->d, s->bmask, s->bdist, tmpA, tmpB, c->stream, &s->accelLaunches);
-    cudaError_t e2 = cudaStreamSynchronize(c->stream);
-    cudaFree(tmpA); cudaFree(tmpB);
-    if (e != cudaSuccess) return fail(VRT_E_CUDA, cudaGetErrorString(e));
-    if (e2 != cudaSuccess) return fail(VRT_E_CUDA, cudaGetErrorString(e2));
-    // per-voxel safe-step field: three volume-sized scratch buffers, freed after the build
-    const size_t nv = (size_t)s->w * s->h * s->d;
-    uint8_t *a = nullptr, *t1 = nullptr, *t2 = nullptr;
-    e = cudaMalloc(&a, nv);
-    if (e == cudaSuccess) e = cudaMalloc(&t1, nv);
-    if (e == cudaSuccess) e = cudaMalloc(&t2, nv);
-    if (e == cudaSuccess) e = launch_build_fdist(s->vol, s->bdist, s->w, s->h, s->d, s->fdist, s->ldist, a, t1, t2, c->stream, &s->accelLaunches);
-    e2 = cudaStreamSynchronize(c->stream);
-    cudaFree(a); cudaFree(t1); cudaFree(t2);
-    if (e != cudaSuccess) return fail(e == cudaErrorMemoryAllocation ? VRT_E_OOM : VRT_E_CUDA, cudaGetErrorString(e));
-    if (e2 != cudaSuccess) return fail(VRT_E_CUDA, cudaGetErrorString(e2));
-    return VRT_OK;
+    CU(cudaStreamSynchronize(c->stream));
+    s->loadMs += now_ms() - t0;
+    return scene_ensure(s, VRT_TRAVERSAL_DEFAULT);
 }
 
 extern "C" int vrt_scene_from_dense(vrt_context* c, const uint8_t* volume, uint32_t w, uint32_t h, uint32_t d,
                                     const vrt_material palette[256], vrt_scene** out) {
     if (!volume || !palette) return fail(VRT_E_INVALID, "null argument");
     vrt_scene* s = nullptr;
+    const double t0 = now_ms();
     int rc = scene_alloc(c, w, h, d, &s);
     if (rc) return rc;
     cudaError_t e = cudaMemcpyAsync(s->vol, volume, (size_t)w * h * d, cudaMemcpyHostToDevice, c->stream);
     if (e != cudaSuccess) { vrt_scene_destroy(s); return fail(VRT_E_CUDA, cudaGetErrorString(e)); }
-    rc = scene_finish(s, palette);
+    rc = scene_finish(s, palette, t0);
     if (rc) { vrt_scene_destroy(s); return rc; }
     *out = s;
     return VRT_OK;
@@ -227,6 +316,7 @@ extern "C" int vrt_scene_from_dense(vrt_context* c, const uint8_t* volume, uint3
 // as in the reference's parser) can collide inside one instance, where the reference's sequential loop order decides: such a scene
 // is flattened by the host loop and uploaded, like vrt_scene_from_dense.
 static int scene_from_layout(vrt_context* c, const VoxLayout& lay, vrt_scene** out) {
+    const double t0 = now_ms();
     bool device = true;
     for (const VoxLayout::Instance& in : lay.instances) device = device && in.permutation;
     if (!device) {
@@ -253,37 +343,44 @@ static int scene_from_layout(vrt_context* c, const VoxLayout& lay, vrt_scene** o
     const cudaError_t e2 = cudaStreamSynchronize(c->stream);   // lay's host buffers are pageable: the copies must be done before they go away
     for (uint8_t* p : dmodels) cudaFree(p);
     if (e != cudaSuccess || e2 != cudaSuccess) { vrt_scene_destroy(s); return fail(e == cudaErrorMemoryAllocation ? VRT_E_OOM : VRT_E_CUDA, cudaGetErrorString(e != cudaSuccess ? e : e2)); }
-    rc = scene_finish(s, lay.palette);
+    rc = scene_finish(s, lay.palette, t0);
     if (rc) { vrt_scene_destroy(s); return rc; }
     *out = s;
     return VRT_OK;
 }
 
+// Nothing throws across the ABI: host containers sized from the file can (bad_alloc, length_error).
+#define VRT_NOTHROW(body) try { body } catch (const std::bad_alloc&) { return fail(VRT_E_OOM, "out of host memory"); } catch (const std::exception& ex) { return fail(VRT_E_PARSE, ex.what()); }
 extern "C" int vrt_scene_load_vox_memory(vrt_context* c, const uint8_t* bytes, size_t n, vrt_scene** out) {
     if (!c || !out) return fail(VRT_E_INVALID, "null argument");
-    VoxLayout lay; std::string err;
-    int rc = parse_vox_bytes(bytes, n, lay, err);
-    if (rc) return fail(rc, err);
-    return scene_from_layout(c, lay, out);
+    VRT_NOTHROW(
+        VoxLayout lay; std::string err;
+        int rc = parse_vox_bytes(bytes, n, lay, err);
+        if (rc) return fail(rc, err);
+        return scene_from_layout(c, lay, out);
+    )
 }
 extern "C" int vrt_scene_load_vox(vrt_context* c, const char* path, vrt_scene** out) {
     if (!c || !out) return fail(VRT_E_INVALID, "null argument");
-    VoxLayout lay; std::string err;
-    int rc = parse_vox_file(path, lay, err);
-    if (rc) return fail(rc, err);
-    return scene_from_layout(c, lay, out);
+    VRT_NOTHROW(
+        VoxLayout lay; std::string err;
+        int rc = parse_vox_file(path, lay, err);
+        if (rc) return fail(rc, err);
+        return scene_from_layout(c, lay, out);
+    )
 }
 
 extern "C" int vrt_scene_generate(vrt_context* c, int generator, uint64_t seed, uint32_t w, uint32_t h, uint32_t d, vrt_scene** out) {
     if (generator != 1 && generator != 2) return fail(VRT_E_INVALID, "unknown generator");
     vrt_scene* s = nullptr;
+    const double t0 = now_ms();
     int rc = scene_alloc(c, w, h, d, &s);
     if (rc) return rc;
     cudaError_t e = launch_generate(generator, (uint32_t)seed, s->vol, w, h, d, c->stream);
     if (e != cudaSuccess) { vrt_scene_destroy(s); return fail(VRT_E_CUDA, cudaGetErrorString(e)); }
     vrt_material pal[256];
     generator_palette(generator, (uint32_t)seed, pal);
-    rc = scene_finish(s, pal);
+    rc = scene_finish(s, pal, t0);
     if (rc) { vrt_scene_destroy(s); return rc; }
     *out = s;
     return VRT_OK;
@@ -326,8 +423,8 @@ extern "C" int vrt_scene_accel_info(const vrt_scene* s, size_t* dense_bytes, siz
     if (!s) return fail(VRT_E_INVALID, "null argument");
     const size_t nb = (size_t)s->Bx * s->By * s->Bz;
     if (dense_bytes) *dense_bytes = (size_t)s->w * s->h * s->d;
-    if (brick_mask_bytes) *brick_mask_bytes = nb * 8;
-    if (brick_dist_bytes) *brick_dist_bytes = nb + nb * 64 + (size_t)(s->w + 2) * (s->h + 2) * (s->d + 2);   // bdist + fdist + ldist
+    if (brick_mask_bytes) *brick_mask_bytes = s->bmask ? nb * 8 : 0;
+    if (brick_dist_bytes) *brick_dist_bytes = (s->bdist ? nb : 0) + (s->fdist ? nb * 64 : 0) + (s->ldist ? (size_t)(s->w + 2) * (s->h + 2) * (s->d + 2) : 0);
     return VRT_OK;
 }
 
@@ -335,6 +432,7 @@ extern "C" int vrt_scene_download_accel(const vrt_scene* s, uint64_t* bmask_dst,
     if (!s) return fail(VRT_E_INVALID, "null argument");
     const size_t nb = (size_t)s->Bx * s->By * s->Bz;
     CU(cudaSetDevice(s->ctx->device));
+    { const int rc = scene_ensure(const_cast<vrt_scene*>(s), VRT_TRAVERSAL_BRICK); if (rc) return rc; }
     if (bmask_dst) CU(cudaMemcpy(bmask_dst, s->bmask, nb * 8, cudaMemcpyDeviceToHost));
     if (bdist_dst) CU(cudaMemcpy(bdist_dst, s->bdist, nb, cudaMemcpyDeviceToHost));
     return VRT_OK;
@@ -343,33 +441,15 @@ extern "C" int vrt_scene_download_accel(const vrt_scene* s, uint64_t* bmask_dst,
 extern "C" int vrt_scene_download_fdist(const vrt_scene* s, uint8_t* dst, size_t bytes) {
     if (!s || !dst || bytes != (size_t)s->Bx * s->By * s->Bz * 64u) return fail(VRT_E_INVALID, "bad size");
     CU(cudaSetDevice(s->ctx->device));
+    { const int rc = scene_ensure(const_cast<vrt_scene*>(s), VRT_TRAVERSAL_FINE); if (rc) return rc; }
     CU(cudaMemcpy(dst, s->fdist, bytes, cudaMemcpyDeviceToHost));
-    return VRT_OK;
-}
-
-// Directional safe-step fields, built the first time a frame asks for VRT_TRAVERSAL_OCTANT (8 fields of one byte per voxel).
-static int scene_ensure_octant(vrt_scene* s) {
-    if (s->odist[0]) return VRT_OK;
-    vrt_context* c = s->ctx;
-    const size_t fieldBytes = (size_t)(s->w + 2) * (s->h + 2) * (s->d + 2);
-    uint32_t* scratch = nullptr;
-    cudaError_t e = cudaMalloc(&scratch, octant_scratch_bytes(s->w, s->h, s->d));
-    for (int o = 0; o < 8 && e == cudaSuccess; o++) e = cudaMalloc(&s->odist[o], fieldBytes);
-    if (e == cudaSuccess) e = launch_build_odist(s->vol, s->w, s->h, s->d, s->odist, scratch, c->stream, &s->accelLaunches);
-    const cudaError_t e2 = cudaStreamSynchronize(c->stream);
-    cudaFree(scratch);
-    if (e == cudaSuccess) e = e2;
-    if (e != cudaSuccess) {
-        for (uint8_t*& p : s->odist) { cudaFree(p); p = nullptr; }
-        return fail(e == cudaErrorMemoryAllocation ? VRT_E_OOM : VRT_E_CUDA, cudaGetErrorString(e));
-    }
     return VRT_OK;
 }
 
 extern "C" int vrt_scene_download_odist(const vrt_scene* s, int octant, uint8_t* dst, size_t bytes) {
     if (!s || !dst || octant < 0 || octant > 7 || bytes != (size_t)(s->w + 2) * (s->h + 2) * (s->d + 2)) return fail(VRT_E_INVALID, "bad argument");
     CU(cudaSetDevice(s->ctx->device));
-    const int rc = scene_ensure_octant(const_cast<vrt_scene*>(s));
+    const int rc = scene_ensure(const_cast<vrt_scene*>(s), VRT_TRAVERSAL_OCTANT);
     if (rc) return rc;
     CU(cudaMemcpy(dst, s->odist[octant], bytes, cudaMemcpyDeviceToHost));
     return VRT_OK;
@@ -532,7 +612,8 @@ extern "C" int vrt_render(vrt_context* c, const vrt_scene* s, const vrt_camera* 
     if (rc) { if (!*frame) vrt_frame_release(f); return rc; }
 
     const uint32_t traversal = st->traversal == VRT_TRAVERSAL_DEFAULT ? VRT_TRAVERSAL_OCTANT : st->traversal;
-    if (traversal == VRT_TRAVERSAL_OCTANT) { rc = scene_ensure_octant(const_cast<vrt_scene*>(s)); if (rc) { if (!*frame) vrt_frame_release(f); return rc; } }
+    rc = scene_ensure(const_cast<vrt_scene*>(s), traversal);   // a no-op once the back-end's fields exist (vrt_scene_prepare / load time)
+    if (rc) { if (!*frame) vrt_frame_release(f); return rc; }
     SceneDev sc{};
     for (int o = 0; o < 8; o++) sc.odist[o] = s->odist[o];
     sc.vol = s->vol; sc.bmask = s->bmask; sc.bdist = s->bdist; sc.fdist = s->fdist; sc.ldist = s->ldist; sc.W = s->w; sc.H = s->h; sc.D = s->d; sc.Bx = s->Bx; sc.By = s->By; sc.Bz = s->Bz;
@@ -656,6 +737,7 @@ extern "C" int vrt_frame_stats_get(vrt_frame* f, vrt_frame_stats* out) {
 extern "C" int vrt_denoise(vrt_context* c, const void* d_color, const void* d_normal, const void* d_position, int w, int h,
                            const vrt_denoiser_settings* ds, void* d_out) {
     if (!c || !d_color || !d_normal || !d_position || !ds || !d_out || w <= 0 || h <= 0) return fail(VRT_E_INVALID, "null argument");
+    if (d_out == d_color) return fail(VRT_E_INVALID, "d_out must not alias d_color (iteration 0 reads neighbours while it writes)");
     CU(cudaSetDevice(c->device));
     void* ping[2] = {d_out, nullptr};
     if (ds->iterations > 1) CU(cudaMalloc(&ping[1], (size_t)w * h * 4));
@@ -746,14 +828,16 @@ extern "C" void vrt_default_settings(vrt_render_settings* s) {
 // Host-only .vox decode (no GPU needed): what vrt_scene_load_vox_memory uploads. Free *volume_out with vrt_host_free.
 extern "C" int vrt_vox_decode(const uint8_t* bytes, size_t n, uint8_t** volume_out, uint32_t whd[3], vrt_material palette[256]) {
     if (!volume_out || !whd || !palette) return fail(VRT_E_INVALID, "null argument");
-    DenseScene ds; std::string err;
-    int rc = load_vox_bytes(bytes, n, ds, err);
-    if (rc) return fail(rc, err);
-    uint8_t* v = (uint8_t*)malloc(ds.volume.size());
-    if (!v) return fail(VRT_E_OOM, "host allocation failed");
-    memcpy(v, ds.volume.data(), ds.volume.size());
-    memcpy(palette, ds.palette, sizeof(vrt_material) * 256);
-    *volume_out = v; whd[0] = ds.w; whd[1] = ds.h; whd[2] = ds.d;
-    return VRT_OK;
+    VRT_NOTHROW(
+        DenseScene ds; std::string err;
+        int rc = load_vox_bytes(bytes, n, ds, err);
+        if (rc) return fail(rc, err);
+        uint8_t* v = (uint8_t*)malloc(ds.volume.size());
+        if (!v) return fail(VRT_E_OOM, "host allocation failed");
+        memcpy(v, ds.volume.data(), ds.volume.size());
+        memcpy(palette, ds.palette, sizeof(vrt_material) * 256);
+        *volume_out = v; whd[0] = ds.w; whd[1] = ds.h; whd[2] = ds.d;
+        return VRT_OK;
+    )
 }
 extern "C" void vrt_host_free(void* p) { free(p); }

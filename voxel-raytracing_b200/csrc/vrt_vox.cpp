@@ -8,6 +8,8 @@
 #include <cstring>
 #include <algorithm>
 #include <map>
+#include <new>
+#include <stdexcept>
 
 namespace vrt {
 namespace {
@@ -66,17 +68,21 @@ Mat4 frame_transform(const Props& p) {
     return t;
 }
 
+// A crafted graph (a group listing itself, or the same child many times) would otherwise fan out exponentially: the walk visits at
+// most kMaxVisits nodes and then stops (a real scene has a few thousand nodes).
+constexpr uint32_t kMaxNodeId = 1u << 20, kMaxVisits = 1u << 22;
+constexpr size_t kMaxModelCells = (size_t)1 << 31;
 void walk(const std::vector<GraphNode>& g, uint32_t id, std::vector<const GraphNode*>& path, const std::vector<VoxModel>& models,
-          std::vector<std::pair<Mat4, int>>& groups, int group, std::vector<Placed>& out, int depth) {
-    if (id >= g.size() || depth > 256) return;
+          std::vector<std::pair<Mat4, int>>& groups, int group, std::vector<Placed>& out, int depth, uint32_t& visits) {
+    if (id >= g.size() || depth > 256 || ++visits > kMaxVisits) return;
     const GraphNode& n = g[id];
     if (n.kind == 1) {
-        path.push_back(&n); walk(g, n.child, path, models, groups, group, out, depth + 1); path.pop_back();
+        path.push_back(&n); walk(g, n.child, path, models, groups, group, out, depth + 1, visits); path.pop_back();
     } else if (n.kind == 2) {
         const int mine = (int)groups.size();
         groups.emplace_back(path.empty() ? ident() : path.back()->xf, group);
         path.push_back(&n);
-        for (uint32_t k : n.kids) walk(g, k, path, models, groups, mine, out, depth + 1);
+        for (uint32_t k : n.kids) walk(g, k, path, models, groups, mine, out, depth + 1, visits);
         path.pop_back();
     } else if (n.kind == 3) {
         if (n.model < models.size() && models[n.model].present) {
@@ -105,7 +111,14 @@ constexpr uint32_t tag(char a, char b, char c, char d) { return (uint32_t)(uint8
 
 }  // namespace
 
+static int parse_vox_bytes_unchecked(const uint8_t* bytes, size_t n, VoxLayout& out, std::string& err);
+// Nothing may throw across the C ABI: sizes taken from the file can make the containers throw (bad_alloc / length_error).
 int parse_vox_bytes(const uint8_t* bytes, size_t n, VoxLayout& out, std::string& err) {
+    try { return parse_vox_bytes_unchecked(bytes, n, out, err); }
+    catch (const std::bad_alloc&) { err = "out of host memory while parsing the voxel scene"; return VRT_E_OOM; }
+    catch (const std::exception&) { err = "Could not parse voxel scene"; return VRT_E_PARSE; }
+}
+static int parse_vox_bytes_unchecked(const uint8_t* bytes, size_t n, VoxLayout& out, std::string& err) {
     static const char lfs[] = "version https://git-lfs";
     if (bytes && n >= sizeof(lfs) - 1 && memcmp(bytes, lfs, sizeof(lfs) - 1) == 0) {
         err = "file is a git-LFS pointer stub, not .vox data"; return VRT_E_LFS_POINTER;
@@ -121,7 +134,9 @@ int parse_vox_bytes(const uint8_t* bytes, size_t n, VoxLayout& out, std::string&
     uint8_t imap[256]; bool haveImap = false;
     uint32_t nx = 0, ny = 0, nz = 0;
     Props props;
-    auto node = [&](uint32_t id) -> GraphNode& { if (id >= graph.size()) graph.resize((size_t)id + 1); return graph[id]; };
+    bool badNode = false;
+    GraphNode scrap;
+    auto node = [&](uint32_t id) -> GraphNode& { if (id > kMaxNodeId) { badNode = true; return scrap; } if (id >= graph.size()) graph.resize((size_t)id + 1); return graph[id]; };
 
     // (1) chunk scan. Like the reference parser, structured chunks are consumed field by field (their declared
     // size is not used to re-seek) and unknown chunks are skipped by their declared size.
@@ -134,8 +149,11 @@ int parse_vox_bytes(const uint8_t* bytes, size_t n, VoxLayout& out, std::string&
                 const uint32_t count = c.word();
                 VoxModel m;
                 if (count) {
+                    // the sizes come from the file: the product must neither wrap nor ask for an absurd allocation
+                    const unsigned __int128 cells = (unsigned __int128)nx * ny * nz;
+                    if (cells == 0 || cells > kMaxModelCells) { err = "Could not parse voxel scene (model size)"; return VRT_E_PARSE; }
                     m.present = true; m.nx = nx; m.ny = ny; m.nz = nz;
-                    m.cells.assign((size_t)nx * ny * nz, 0);
+                    m.cells.assign((size_t)cells, 0);
                     const uint32_t readable = (uint32_t)std::min<size_t>(c.left() / 4, count);
                     const uint8_t* q = bytes + c.at;
                     for (uint32_t i = 0; i < readable; i++, q += 4)
@@ -158,6 +176,7 @@ int parse_vox_bytes(const uint8_t* bytes, size_t n, VoxLayout& out, std::string&
             case tag('n', 'G', 'R', 'P'): {
                 const uint32_t nid = c.word(); props.read(c);
                 const uint32_t kids = c.word();
+                if (kids > c.left() / 4) { err = "Could not parse voxel scene (group size)"; return VRT_E_PARSE; }
                 std::vector<uint32_t> ids; for (uint32_t i = 0; i < kids && !c.bad; i++) ids.push_back(c.word());
                 GraphNode& g = node(nid); g.kind = 2; g.kids.swap(ids);
                 break;
@@ -188,11 +207,14 @@ int parse_vox_bytes(const uint8_t* bytes, size_t n, VoxLayout& out, std::string&
         }
     }
 
+    if (badNode) { err = "Could not parse voxel scene (node id)"; return VRT_E_PARSE; }
     // (2) instances
     std::vector<Placed> placed;
     if (!graph.empty()) {
         std::vector<const GraphNode*> path; std::vector<std::pair<Mat4, int>> groups;
-        walk(graph, 0, path, models, groups, -1, placed, 0);
+        uint32_t visits = 0;
+        walk(graph, 0, path, models, groups, -1, placed, 0, visits);
+        if (visits > kMaxVisits) { err = "Could not parse voxel scene (scene graph too large)"; return VRT_E_PARSE; }
     } else if (models.size() == 1) {
         placed.push_back({0, ident()});
     }
@@ -237,7 +259,11 @@ int parse_vox_bytes(const uint8_t* bytes, size_t n, VoxLayout& out, std::string&
         for (int k = 0; k < 3; k++) { lo[k] = std::min(lo[k], std::min(a[k], b[k])); hi[k] = std::max(hi[k], std::max(a[k], b[k])); }
         out.instances.push_back(in);
     }
-    for (int k = 0; k < 3; k++) out.lo[k] = lo[k];
+    for (int k = 0; k < 3; k++) {
+        out.lo[k] = lo[k];
+        const long long ext = (long long)hi[k] - (long long)lo[k];
+        if (ext <= 0 || ext > 32767) { err = "degenerate scene bounds"; return VRT_E_PARSE; }   // vrt_scene bounds are 1..32767 per axis
+    }
     out.w = (uint32_t)(hi[0] - lo[0]); out.h = (uint32_t)(hi[2] - lo[2]); out.d = (uint32_t)(hi[1] - lo[1]);
     const size_t total = (size_t)out.w * out.h * out.d;
     if (total == 0 || total > ((size_t)1 << 34)) { err = "degenerate scene bounds"; return VRT_E_PARSE; }
@@ -275,14 +301,17 @@ void flatten_host(const VoxLayout& lay, uint8_t* volume) {
 }
 
 int load_vox_bytes(const uint8_t* bytes, size_t n, DenseScene& out, std::string& err) {
-    VoxLayout lay;
-    const int rc = parse_vox_bytes(bytes, n, lay, err);
-    if (rc) return rc;
-    out.w = lay.w; out.h = lay.h; out.d = lay.d;
-    out.volume.resize((size_t)lay.w * lay.h * lay.d);
-    flatten_host(lay, out.volume.data());
-    memcpy(out.palette, lay.palette, sizeof(out.palette));
-    return VRT_OK;
+    try {
+        VoxLayout lay;
+        const int rc = parse_vox_bytes(bytes, n, lay, err);
+        if (rc) return rc;
+        out.w = lay.w; out.h = lay.h; out.d = lay.d;
+        out.volume.resize((size_t)lay.w * lay.h * lay.d);
+        flatten_host(lay, out.volume.data());
+        memcpy(out.palette, lay.palette, sizeof(out.palette));
+        return VRT_OK;
+    } catch (const std::bad_alloc&) { err = "out of host memory while flattening the voxel scene"; return VRT_E_OOM; }
+    catch (const std::exception&) { err = "Could not parse voxel scene"; return VRT_E_PARSE; }
 }
 
 static int read_file(const char* path, std::vector<uint8_t>& buf, std::string& err) {
@@ -290,7 +319,7 @@ static int read_file(const char* path, std::vector<uint8_t>& buf, std::string& e
     if (!f) { err = "Failed to read voxel scene"; return VRT_E_IO; }
     fseek(f, 0, SEEK_END); long sz = ftell(f); fseek(f, 0, SEEK_SET);
     if (sz < 0) { fclose(f); err = "Failed to read voxel scene"; return VRT_E_IO; }
-    buf.resize((size_t)sz);
+    try { buf.resize((size_t)sz); } catch (const std::exception&) { fclose(f); err = "out of host memory"; return VRT_E_OOM; }
     const size_t got = sz ? fread(buf.data(), 1, (size_t)sz, f) : 0;
     fclose(f);
     if (got != (size_t)sz) { err = "Failed to read voxel scene"; return VRT_E_IO; }

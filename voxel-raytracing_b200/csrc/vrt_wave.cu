@@ -9,6 +9,7 @@
 // because sky pixels / non-metallic pixels / finished pixels do not occupy lanes in the secondary waves.
 #include <cuda_runtime.h>
 #include <stdlib.h>
+#include <mutex>
 #include "vrt_wave.cuh"
 #include "vrt_engine.cuh"
 #include "vrt_launch.h"
@@ -256,7 +257,7 @@ __global__ void __launch_bounds__(ENGINE_WARPS * 32, 4) wave_anyhit_engine_kerne
     // lane state
     EngRay er; er.rem = 0; er.left = 0;
     er.l.sx = er.l.sy = er.l.sz = er.l.dx = er.l.dy = er.l.dz = er.l.sx0 = er.l.sy0 = er.l.sz0 = er.l.ax = er.l.ay = er.l.az = 0.0f;
-    er.l.p0 = sc.ldist; er.l.SX = er.l.SY = er.l.SZ = er.l.T0 = 0; er.l.maxSteps = 0;
+    er.l.p0 = sc.vol; er.l.SX = er.l.SY = er.l.SZ = er.l.T0 = 0; er.l.maxSteps = 0;
     bool alive = false, pending = false, hitRes = false;
     uint32_t idx = 0, kind = 0, fetchRes = 0;
     unsigned rays = 0, fetches = 0;
@@ -378,8 +379,7 @@ __global__ void __launch_bounds__(256) wave_resolve_kernel(const SceneDev sc, co
 
 // refill threshold of the ray engine (idle lanes that trigger a refill); VRT_ENGINE_T=0 selects the run-to-completion kernels
 static int engineT() {
-    static int t = -1;
-    if (t < 0) { const char* e = getenv("VRT_ENGINE_T"); t = e ? atoi(e) : 8; if (t > 32) t = 32; }
+    static const int t = [] { const char* e = getenv("VRT_ENGINE_T"); const int v = e ? atoi(e) : 8; return v > 32 ? 32 : v; }();
     return t;
 }
 
@@ -389,14 +389,15 @@ static cudaError_t launch_wave_t(const SceneDev& sc, const FrameParams& fp, cons
     cudaError_t e = cudaMemsetAsync(wb.ctr, 0, sizeof(WaveCtr), stream);
     if (e != cudaSuccess) return e;
     static int occAny = 0, occBounce = 0, occEngine = 0;
-    if (!occAny) {
+    static std::once_flag occOnce;                        // contexts on different host threads may render at the same time
+    std::call_once(occOnce, [] {
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occAny, wave_anyhit_kernel<T>, 256, 0);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occBounce, wave_bounce_kernel<T>, 128, 0);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occEngine, wave_anyhit_engine_kernel<T, ENGINE_NEAR_TOP, ENGINE_FAR_TOP>, ENGINE_WARPS * 32, 0);
         if (occAny < 1) occAny = 1;
         if (occBounce < 1) occBounce = 1;
         if (occEngine < 1) occEngine = 1;
-    }
+    });
     static const uint32_t quota = getenv("VRT_ENGINE_QUOTA") ? (uint32_t)atoi(getenv("VRT_ENGINE_QUOTA")) / ENGINE_CHUNK * ENGINE_CHUNK : ENGINE_BLOCK_QUOTA;
     // the wave from which the rest of every reflection chain runs in place (MAX_REFLECTIONS - 1: one launch per bounce)
     static const int bounceChain = getenv("VRT_BOUNCE_CHAIN") ? min(max(atoi(getenv("VRT_BOUNCE_CHAIN")), 0), MAX_REFLECTIONS - 1) : 2;

@@ -134,6 +134,11 @@ class Context:
         if world != 1:
             _ck(lib().vrt_context_set_shard(self.h, rank, world))
 
+    def set_shard(self, rank, world):
+        """Tile shard of the frames created from now on (vrt_context_set_shard)."""
+        _ck(lib().vrt_context_set_shard(self.h, int(rank), int(world)))
+        self.rank, self.world = int(rank), int(world)
+
     def device_info(self):
         sm = C.c_int(); l2 = C.c_size_t(); hbm = C.c_size_t()
         _ck(lib().vrt_device_info(self.h, C.byref(sm), C.byref(l2), C.byref(hbm)))
@@ -219,6 +224,15 @@ class VoxelScene:
     def download_odist(self, octant):
         f = np.zeros((self.depth + 2, self.height + 2, self.width + 2), np.uint8)   # aproned, [z+1][y+1][x+1]
         _ck(lib().vrt_scene_download_odist(self.h, int(octant), f.ctypes.data_as(C.c_void_p), C.c_size_t(f.size))); return f
+
+    def prepare(self, traversal=0):
+        """Build the safe-step fields of a traversal back-end now (the default back-end's are built at load time)."""
+        _ck(lib().vrt_scene_prepare(self.h, C.c_uint32(traversal)))
+
+    def memory(self):
+        v, f, pk, ms = C.c_size_t(), C.c_size_t(), C.c_size_t(), C.c_double()
+        _ck(lib().vrt_scene_memory(self.h, C.byref(v), C.byref(f), C.byref(pk), C.byref(ms)))
+        return dict(volume_bytes=v.value, field_bytes=f.value, peak_build_bytes=pk.value, load_ms=ms.value)
 
     def accel_info(self):
         a, b, c = C.c_size_t(), C.c_size_t(), C.c_size_t()
