@@ -3,22 +3,27 @@
 synthetic 1024^3 volume; 1/2/4/8 B200).
 
     python bench.py --gpus 1 --steps K --warmup W              # the CUDA path through the C ABI (libvrt.so)
-    torchrun --nproc-per-node N ... bench.py --gpus N ...      # image tiles sharded over N GPUs, frame gathered on rank 0
+    torchrun --nproc-per-node N ... bench.py --gpus N ...      # image tiles sharded over N GPUs, frame assembled on rank 0
     python bench.py --impl reference --steps K --warmup W      # the reference algorithm on the host cores (oracle port)
 
 A step = one frame of the camera path of the config (camera and noise frame index change every step).
-Prints ONE JSON line (rank 0). The product path never touches oracle/: only the cpu_baseline leg and the
---impl reference arm do."""
+Prints ONE JSON line (rank 0). The product path never touches oracle/: only the cpu_baseline / parity leg and the
+--impl reference arm do.
+
+N > 1: the exchange is the library's own (vrt_comm_* / vrt_frame_exchange in csrc/vrt_comm.cu): every rank stores its tiles straight
+into rank 0's frame over NVLink peer memory and, for the end-to-end number, into a pinned host frame shared by all ranks (every GPU's
+PCIe link carries its own tiles). torch.distributed (NCCL) is only used here for the barriers around the timed regions and for
+reducing the per-rank counters."""
 from __future__ import annotations
 
 import argparse
 import ctypes as C
 import json
+import math
 import os
 import subprocess
 import sys
 import tempfile
-import threading
 import time
 
 import numpy as np
@@ -27,6 +32,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.join(ROOT, "voxel-raytracing_b200"))
 
 METRIC, UNIT = "Mrays/s", "Mrays/s"
+STEP_INSTRUCTIONS = 7          # SASS instructions of one replayed DDA step (profiles/r2_sass_step.txt): FMNMX3, 3 FSETP, 3 predicated FADD
 
 
 def parse_args():
@@ -38,19 +44,18 @@ def parse_args():
     ap.add_argument("--config", default="cfg4")
     ap.add_argument("--whd", type=int, nargs=3, default=None, help="override the synthetic volume size (debug)")
     ap.add_argument("--size", type=int, nargs=2, default=None, help="override the resolution (debug)")
-    ap.add_argument("--traversal", type=int, default=0, help="0 default, 1 dense u8, 2 brick")
+    ap.add_argument("--traversal", type=int, default=0, help="0 default (octant fields), 1 dense u8, 2 brick, 3 fine, 4 linear, 5 octant")
     ap.add_argument("--pipeline", type=int, default=0, help="0 default (wavefront), 1 megakernel, 2 wavefront")
     ap.add_argument("--passes", type=int, default=None, help="override the pass mask (measurement of pass subsets)")
     ap.add_argument("--ao", type=int, default=None, help="override aoSamples")
     ap.add_argument("--no-gbuffer", action="store_true")
     ap.add_argument("--shard", type=int, nargs=2, default=None, metavar=("RANK", "WORLD"),
-                    help="debug: render only the tile shard RANK of WORLD on one GPU (what one rank of an N-GPU run does), no gather")
-    ap.add_argument("--no-cpu-baseline", action="store_true")
+                    help="debug: render only the tile shard RANK of WORLD on one GPU (what one rank of an N-GPU run does), no exchange")
+    ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the cpu_baseline + parity leg (N = 1)")
     ap.add_argument("--frames-in-flight", type=int, default=3, help="frame objects used round-robin (>= 2)")
-    ap.add_argument("--exchange", choices=["gather", "push"], default="gather",
-                    help="N>1: NCCL gather + de-tile on rank 0, or every rank stores its tiles straight into rank 0's frame over NVLink (symmetric memory)")
-    ap.add_argument("--serial-frames", action="store_true", help="one stream: frame k+1 starts when frame k has finished (default: two frames in flight on their own streams)")
+    ap.add_argument("--serial-frames", action="store_true", help="one stream: frame k+1 starts when frame k has finished (default: frames in flight on their own streams)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
+    ap.add_argument("--min-timed-ms", type=float, default=1500.0, help="the K-step region is repeated until this much GPU time has been measured; the median region is reported")
     return ap.parse_args()
 
 
@@ -63,15 +68,15 @@ class ClockSampler:
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         self.p = None
         try:
-            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(device)],
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "50", "-i", str(device)],
                                       stdout=self.f, stderr=subprocess.DEVNULL)
         except Exception:
             self.p = None
 
     def stop(self):
         if self.p is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"], "samples": 0}
+        time.sleep(0.1)
         self.p.terminate()
         try:
             self.p.wait(timeout=5)
@@ -96,8 +101,8 @@ class ClockSampler:
         except OSError:
             pass
         if not sm:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
-        # median over the upper half: samples taken between frames (idle) would drag a plain median down
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"], "samples": 0}
+        # median over the upper half: samples taken between regions (idle) would drag a plain median down
         busy = sorted(sm)[len(sm) // 2:]
         return {"sm_mhz": float(np.median(busy)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
 
@@ -125,18 +130,33 @@ def l2_block(primary_alg_bytes, primary_ms):
             "peak_source": "measured (tools/l2peak.cu, 64 MiB read-only stream, profiles/r1_l2_peak.json)"}
 
 
-def ncu_traffic(kernel="render_kernel"):
-    """Per-launch DRAM traffic of the dominant kernel from the committed ncu summary, if one exists."""
+def ncu_traffic(kernel, config, world, default_path):
+    """Per-launch DRAM traffic (dram__bytes_read + write) of the dominant kernel from the committed `ncu --set full` capture of the
+    N = 1 launch of THIS config; a rank of an N-GPU run traces 1/N of the rays over the same fields, so its launch is booked at 1/N of
+    it (stated in traffic_source). None when no capture exists for the config / code path."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(p):
-        try:
-            return json.load(open(p)).get(kernel.split(" ")[0] + "_dram_bytes_per_launch")
-        except Exception:
-            return None
-    return None
+    if not default_path or not os.path.exists(p):
+        return None, None
+    try:
+        t = json.load(open(p))
+    except Exception:
+        return None, None
+    v = t.get(f"{config}:{kernel.split(' ')[0]}_dram_bytes_per_launch")
+    if v is None:
+        return None, None
+    src = t.get("source", "profiles/traffic.json")
+    return (float(v) / world, src + (f"; N = 1 capture scaled by 1/{world} for the tile shard" if world > 1 else ""))
 
 
 # ----------------------------------------------------------------------------------------------- oracle legs
+def host_threads():
+    """torch.distributed.run exports OMP_NUM_THREADS=1: the oracle is told how many threads to use explicitly."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def oracle_scene_for(cfg, whd):
     """CPU-side inputs of the same workload (oracle leg only)."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
@@ -164,34 +184,66 @@ def oracle_camera(O, name, bounds, size, k):
     return O.make_camera(pos, d, r, u, bounds, size, frame)
 
 
-def oracle_timed(O, sc, cam, st, row_step, nthreads=0):
+def oracle_timed(O, sc, cam, st, row_step, nthreads, planes=("color", "rays", "fetches")):
     H = cam.screenSize[1]
     t0 = time.perf_counter()
-    out = O.render(sc, cam, st, rows=(0, H, row_step), nthreads=nthreads, planes=["color", "rays", "fetches"])
+    out = O.render(sc, cam, st, rows=(0, H, row_step), nthreads=nthreads, planes=list(planes) if planes else None)
     dt = time.perf_counter() - t0
-    return dt, int(out["rays"].sum()), int(out["fetches"].sum())
+    return dt, int(out["rays"].sum()), int(out["fetches"].sum()), out
 
 
-def cpu_baseline(cfg, name, whd, size, target_s):
+def cpu_baseline_and_parity(cfg, name, whd, size, target_s, gpu_frame0):
+    """The oracle port on all host cores over a bounded row sample of frame 0 of the workload; the same rows of the same frame as
+    rendered by the CUDA path (instrumented, outside every timed region) are then compared plane by plane: the parity block."""
     O, sc, keep, bounds = oracle_scene_for(cfg, whd)
     st = O.make_settings(pass_mask=cfg["passes"], ao=cfg["ao"])
     cam = oracle_camera(O, name, bounds, size, 0)
-    cores = O.lib().orc_num_threads()
-    dt, rays, _ = oracle_timed(O, sc, cam, st, 32)                       # calibration: every 32nd row
+    cores = host_threads()
+    dt, rays, _, _ = oracle_timed(O, sc, cam, st, 32, cores)                       # calibration: every 32nd row
     step = int(min(32, max(1, round(32 * dt / max(target_s, 1e-3)))))
-    if step < 32:
-        dt, rays, _ = oracle_timed(O, sc, cam, st, step)
-    return {"value": rays / dt / 1e6, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"frame 0 of the workload, every {step}th row ({size[1] // step} of {size[1]} rows), {dt:.1f} s, oracle port with OpenMP over rows"}
+    dt, rays, _, want = oracle_timed(O, sc, cam, st, step, cores, planes=None)     # the timed sample, all planes kept
+    base = {"value": rays / dt / 1e6, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"frame 0 of the workload, every {step}th row ({len(range(0, size[1], step))} of {size[1]} rows), {dt:.1f} s, oracle port with OpenMP over rows"}
+    rows = slice(0, size[1], step)
+    got = gpu_frame0()
+
+    def diff_bits(n):
+        a, b = np.ascontiguousarray(got[n][rows]), np.ascontiguousarray(want[n][rows])
+        if a.dtype.kind == "f":
+            same = (a.view(np.uint32) == b.view(np.uint32)) | (np.isnan(a) & np.isnan(b))
+        else:
+            same = a == b
+        return int((~same).sum())
+
+    def max_rel(n):
+        a, b = got[n][rows].astype(np.float64), want[n][rows].astype(np.float64)
+        ok = np.isfinite(a) & np.isfinite(b)
+        if not ok.any():
+            return 0.0
+        return float((np.abs(a - b)[ok] / np.maximum(np.abs(b[ok]), 1e-30)).max())
+
+    hit_bad = diff_bits("hit")
+    par = {"frame": 0, "rows_compared": len(range(0, size[1], step)), "pixels_compared": len(range(0, size[1], step)) * size[0],
+           "hit_xyz_steps_mismatch": hit_bad, "palette_mismatch": diff_bits("hit_palette"),
+           "rays_mismatch": diff_bits("rays"), "fetches_mismatch": diff_bits("fetches"), "mask_mismatch": diff_bits("mask"),
+           "depth_bits_mismatch": diff_bits("depth"), "position_bits_mismatch": diff_bits("position"), "normal_mismatch": diff_bits("normal"),
+           "depth_normal_max_rel": max(max_rel("depth"), max_rel("position")),
+           "color_max_abs_255": int(np.abs(got["color"][rows].astype(int) - want["color"][rows].astype(int)).max()),
+           "color_f32_bits_mismatch_pixels": int((~(((got["color_f32"][rows].view(np.uint32) == want["color_f32"][rows].view(np.uint32))
+                                                     | (np.isnan(got["color_f32"][rows]) & np.isnan(want["color_f32"][rows]))).all(axis=-1))).sum()),
+           "oracle": "oracle/orc_render.cpp (CPU restatement of shader/voxel_volume.frag; parity unpinned: the reference holds no vectors for this path)"}
+    par["ok"] = all(par[k] == 0 for k in ("hit_xyz_steps_mismatch", "palette_mismatch", "rays_mismatch", "fetches_mismatch", "mask_mismatch", "normal_mismatch")) \
+        and par["depth_normal_max_rel"] <= 1e-5 and par["color_max_abs_255"] <= 1
+    return base, par
 
 
-def config_blob(cfg, name, whd, size, extra):
+def config_blob(cfg, name, whd, size, world):
+    """Identical in both arms (the driver compares the two `config` objects)."""
     kind, what, kw = cfg["scene"]
-    blob = {"workload": f"{name}: {cfg['label']}", "volume": list(whd) if whd else list(kw.get("whd", [])) or what,
+    return {"workload": f"{name}: {cfg['label']}", "volume": list(whd) if whd else list(kw.get("whd", [])) or what,
             "resolution": list(size), "pass_mask": cfg["passes"], "aoSamples": cfg["ao"], "denoiser": bool(cfg["denoise"]),
-            "l2": "inputs larger than L2 (1 GiB volume + 144 MiB brick levels vs 126 MB); camera pose and noise frame index change every step"}
-    blob.update(extra)
-    return blob
+            "parallelism": f"tiles{world}" if world > 1 else "single",
+            "l2": "inputs larger than L2 (1 GiB volume + 8 GiB of directional safe-step fields vs 126 MB); camera pose and noise frame index change every step"}
 
 
 # ----------------------------------------------------------------------------------------------- reference arm
@@ -205,23 +257,24 @@ def run_reference(args):
     size = tuple(args.size) if args.size else cfg["size"]
     O, sc, keep, bounds = oracle_scene_for(cfg, args.whd)
     st = O.make_settings(pass_mask=cfg["passes"], ao=cfg["ao"])
-    cores = O.lib().orc_num_threads()
+    cores = host_threads()
     # calibrate the per-step sample to ~2 s of host work
-    dt, _, _ = oracle_timed(O, sc, oracle_camera(O, args.config, bounds, size, 0), st, 64)
+    dt, _, _, _ = oracle_timed(O, sc, oracle_camera(O, args.config, bounds, size, 0), st, 64, cores)
     step = int(min(64, max(1, round(64 * dt / 2.0))))
     for k in range(args.warmup):
-        oracle_timed(O, sc, oracle_camera(O, args.config, bounds, size, k), st, step)
+        oracle_timed(O, sc, oracle_camera(O, args.config, bounds, size, k), st, step, cores)
     rays = fetches = 0
     t = 0.0
     for k in range(args.steps):
-        dt, r, f = oracle_timed(O, sc, oracle_camera(O, args.config, bounds, size, k), st, step)
+        dt, r, f, _ = oracle_timed(O, sc, oracle_camera(O, args.config, bounds, size, k), st, step, cores)
         t += dt; rays += r; fetches += f
     val = rays / t / 1e6
-    sample = f"every {step}th row of each frame ({size[1] // step} of {size[1]} rows per step), {t:.1f} s total"
+    sample = f"every {step}th row of each frame ({len(range(0, size[1], step))} of {size[1]} rows per step), {t:.1f} s total"
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": config_blob(cfg, args.config, args.whd, size, {"note": "reference has no CPU implementation and its Vulkan path is unavailable on this box; "
-                                                                               "this is the CPU restatement of shader/voxel_volume.frag (oracle port), OpenMP over rows"}),
+            "config": config_blob(cfg, args.config, args.whd, size, args.gpus),
+            "note": "the reference has no CPU implementation and its Vulkan path is unavailable on this box; this is the CPU restatement of "
+                    "shader/voxel_volume.frag (oracle port), OpenMP over rows, on all host cores whatever --gpus says",
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "algorithmic_bytes_per_s": fetches / t}
@@ -229,13 +282,6 @@ def run_reference(args):
 
 
 # ----------------------------------------------------------------------------------------------- the CUDA arm
-class _DevBuf:
-    """Wraps a device pointer owned by libvrt so torch.distributed can move it (no copy)."""
-
-    def __init__(self, ptr, nbytes):
-        self.__cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
-
-
 def run_vrt(args):
     import torch
     import torch.distributed as dist
@@ -247,8 +293,9 @@ def run_vrt(args):
     if world != args.gpus:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch N>1 with torch.distributed.run")
     torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        dist.init_process_group("nccl", device_id=dev)
     cfg = dict(configs.CONFIGS[args.config])
     if args.passes is not None:
         cfg["passes"] = args.passes
@@ -256,108 +303,81 @@ def run_vrt(args):
         cfg["ao"] = args.ao
     size = tuple(args.size) if args.size else cfg["size"]
     W, H = size
+    denoise = bool(cfg["denoise"])
 
-    if args.shard and world == 1:
-        ctx = pyvrt.Context(local, rank=args.shard[0], world=args.shard[1])
-    else:
-        ctx = pyvrt.Context(local, rank=rank, world=world)   # raises without a GPU: there is no CPU fallback
+    ctx = pyvrt.Context(local)   # raises without a GPU: there is no CPU fallback
+    if world > 1:
+        key = [f"bench{os.getpid()}_{int(time.time())}" if rank == 0 else None]
+        dist.broadcast_object_list(key, src=0)
+        ctx.comm_create(rank, world, key[0])                 # the library's own exchange (csrc/vrt_comm.cu); also sets the tile shard
+    elif args.shard:
+        ctx.set_shard(args.shard[0], args.shard[1])
     scene = configs.build_scene(ctx, cfg, args.whd)
+    scene.prepare(args.traversal)
+    mem = scene.memory()
     bounds = scene.bounds
     st = configs.settings_for(cfg, gbuffer=not args.no_gbuffer)
     st.traversal = args.traversal
     st.pipeline = args.pipeline
-    # Two frames in flight (as in the reference, source/engine/engine.hpp:19): two render passes used alternately, each frame on
+    if world > 1:
+        st.denoise.enable = 0                               # sharded ranks trace; rank 0 denoises the assembled planes
+    # Frames in flight (the reference keeps two, source/engine/engine.hpp:19): F render passes used round-robin, each frame on
     # a stream of its own so that the kernels of frame k+1 fill the tails of frame k's (--serial-frames: one stream, back to back).
     if not args.serial_frames:
         ctx.set_concurrent_frames(True)
     F = max(2, args.frames_in_flight)
     passes = tuple(pyvrt.VoxelRenderPass(ctx, scene, st) for _ in range(F))
-    dev = torch.device("cuda", local)
     ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
-    final = "denoised" if cfg["denoise"] and world == 1 else "color"
+    final = "denoised" if denoise else "color"
     frame_bytes = W * H * 4
-    host2 = [torch.empty(frame_bytes, dtype=torch.uint8, pin_memory=True) for _ in range(F)] if rank == 0 else None
-    # N>1: the colour shards of frame k travel to rank 0 (NCCL gather) on a communication stream while the context stream already
-    # traces frame k+1; rank 0 assembles frame k (detile kernel, same communication stream) once its shards are in.
-    gathered, asm2, comm, copy_stream = [None] * F, None, None, None
-    sym = hdl = None
+    xplanes = ("color", "normal", "position") if denoise else ("color",)
+    xhost = () if denoise else ("color",)                    # e2e: every rank stores its tiles into the shared pinned host frame
+    host2 = dn_out = dn_scratch = cstream = None
+    ds = pyvrt.default_settings().denoise
     if world > 1:
-        comm = torch.cuda.Stream(device=dev, priority=-1)
-        if rank == 0:
-            copy_stream = torch.cuda.Stream(device=dev)
-        if args.exchange == "push":
-            # rank 0's buffer holds the F assembled frames; every rank maps it (peer memory over NVLink / NVSwitch)
-            import torch.distributed._symmetric_memory as symm_mem
-            sym = symm_mem.empty(F * frame_bytes, dtype=torch.uint8, device=dev)
-            hdl = symm_mem.rendezvous(sym, dist.group.WORLD)
-            frame0_ptr = int(hdl.buffer_ptrs[0])
-            if rank == 0:
-                asm2 = [sym[k * frame_bytes:(k + 1) * frame_bytes] for k in range(F)]
-        elif rank == 0:
-            asm2 = [torch.empty(frame_bytes, dtype=torch.uint8, device="cuda") for _ in range(F)]
-    ev_rendered = [torch.cuda.Event() for _ in range(F)]
-    ev_gathered = [torch.cuda.Event() for _ in range(F)]
-    ev_ready = [torch.cuda.Event() for _ in range(F)]
-    ev_copied = [torch.cuda.Event() for _ in range(F)]
-    sent, copied_pending = [False] * F, [False] * F
-    fstream = [None] * F                                   # the stream each frame object renders on
-    last_slot = None
+        ctx.comm_alloc_frames(size, F, xplanes, xhost)
+        if rank == 0 and denoise:
+            dn_out = [torch.empty(frame_bytes, dtype=torch.uint8, device=dev) for _ in range(F)]
+            dn_scratch = torch.empty(frame_bytes, dtype=torch.uint8, device=dev)
+            cstream = torch.cuda.ExternalStream(ctx.comm_stream, device=dev)
+    if rank == 0 and (world == 1 or denoise):
+        host2 = [torch.empty(frame_bytes, dtype=torch.uint8, pin_memory=True) for _ in range(F)]
+    ev_done = [torch.cuda.Event() for _ in range(F)]
+    pending = [False] * F
 
     def submit(k, readback=False):
-        """Queue frame k: render this rank's tiles (+ N>1: gather and assemble; + readback: copy the finished frame to pinned host
-        memory). Returns the frame and the kernels launched outside vrt_render (the library counts its own)."""
-        nonlocal last_slot
+        """Queue frame k: render this rank's tiles; N>1: store them into rank 0's frame (and the shared host frame when the frame is
+        read back); rank 0 orders its consumer (denoiser, read-back) behind the arrival of every rank's tiles. Returns the frame and
+        the kernels launched outside vrt_render / vrt_frame_exchange (the library counts its own)."""
         slot = k % F
         cam = configs.make_camera(args.config, bounds, size, k)
+        fr = passes[slot].record(cam)
         if world == 1:
-            fr = passes[slot].record(cam)
             if readback:
                 fr.download_async(final, host2[slot].numpy())
             return fr, 0
-        if sent[slot]:
-            fstream[slot].wait_event(ev_gathered[slot])      # this slot's shard buffer is still being sent
-        fr = passes[slot].record(cam)
-        if fstream[slot] is None:
-            fstream[slot] = torch.cuda.ExternalStream(fr.stream, device=dev)
-        ev_rendered[slot].record(fstream[slot])
-        ptr, n = fr.plane_ptr("color")
-        shard = torch.as_tensor(_DevBuf(ptr, n), device=dev)
-        launches = 0
-        comm.wait_event(ev_rendered[slot])
-        with torch.cuda.stream(comm):
-            if rank == 0 and copied_pending[slot]:
-                comm.wait_event(ev_copied[slot])             # asm2[slot] is still being read back
-            if args.exchange == "push":
+        fr.exchange(slot, xplanes, xhost if readback else ())
+        extra = 0
+        if rank == 0:
+            ctx.comm_wait(slot)                              # wait kernel on the communicator's stream
+            extra = 1
+            if denoise:
+                dc, _, _ = ctx.comm_frame_plane(slot, "color"); dn, _, _ = ctx.comm_frame_plane(slot, "normal"); dp, _, _ = ctx.comm_frame_plane(slot, "position")
+                pyvrt.denoise_device_on(ctx, dc, dn, dp, size, ds, dn_out[slot].data_ptr(), dn_scratch.data_ptr(), stream=ctx.comm_stream)
+                extra += ds.iterations
                 if readback:
-                    hdl.barrier(channel=0)                   # rank 0 has finished with what this slot held
-                fr.push_tiles("color", frame0_ptr + slot * frame_bytes, stream=comm.cuda_stream)
-                hdl.barrier(channel=1)                       # every rank's tiles of frame k are in rank 0's buffer
-                launches = 1
+                    with torch.cuda.stream(cstream):
+                        host2[slot].copy_(dn_out[slot], non_blocking=True)
+            if readback:
+                ev_done[slot].record(torch.cuda.ExternalStream(ctx.comm_stream, device=dev))
+                pending[slot] = True                         # released by wait_readback once the host has the frame
             else:
-                if rank == 0 and gathered[slot] is None:
-                    gathered[slot] = torch.empty((world, n), dtype=torch.uint8, device="cuda")
-                dist.gather(shard, list(gathered[slot].unbind(0)) if rank == 0 else None, dst=0)
-                if rank == 0:
-                    pyvrt.assemble(ctx, gathered[slot].data_ptr(), world, size, "color", asm2[slot].data_ptr(), stream=comm.cuda_stream)
-                    launches = 1
-            if rank == 0 and readback:
-                ev_ready[slot].record(comm)
-                copy_stream.wait_event(ev_ready[slot])
-                with torch.cuda.stream(copy_stream):
-                    host2[slot].copy_(asm2[slot], non_blocking=True)
-                    ev_copied[slot].record(copy_stream)
-                copied_pending[slot] = True
-            ev_gathered[slot].record(comm)                   # shards sent / frame assembled
-        sent[slot] = True
-        last_slot = slot
-        return fr, launches
+                ctx.comm_release(slot, on_stream=True)       # the ranks may overwrite the slot once the consumer got there
+        return fr, extra
 
     def drain():
-        """Join the frames' streams and the communication stream into the context stream (the timed region ends there)."""
+        """Join the frames' streams and the communicator's stream into the context stream (the timed region ends there)."""
         ctx.join()
-        if world > 1 and last_slot is not None:
-            ext.wait_event(ev_gathered[last_slot])
-        return 0
 
     def wait_readback(k):
         slot = k % F
@@ -365,97 +385,119 @@ def run_vrt(args):
             return
         if world == 1:
             passes[slot].frame.download_wait()
-        elif copied_pending[slot]:
-            ev_copied[slot].synchronize()
+        elif pending[slot]:
+            if not denoise:
+                ctx.comm_wait_host(slot)                     # every rank's tiles are in the shared pinned host frame
+            ev_done[slot].synchronize()
+            ctx.comm_release(slot)
+            pending[slot] = False
 
     def barrier():
         ctx.sync(); torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
 
-    if world > 1 and args.exchange == "push":
-        # self-check of the peer-memory plumbing (outside every timed region): frame 0 assembled by push must equal the same frame
-        # assembled by NCCL gather + de-tile
+    def checksum(ptr, nbytes):
+        t = torch.as_tensor(_DevBuf(ptr, nbytes), device=dev).to(torch.int64)
+        return torch.stack([t.sum(), (t * t).sum()])
+
+    # ---- self-check of the exchange (outside every timed region): the bytes of the assembled frame are the bytes of the shards
+    if world > 1:
         fr0, _ = submit(0)
         drain(); barrier()
         ptr, n = fr0.plane_ptr("color")
-        g = torch.empty((world, n), dtype=torch.uint8, device="cuda") if rank == 0 else None
-        dist.gather(torch.as_tensor(_DevBuf(ptr, n), device=dev), list(g.unbind(0)) if rank == 0 else None, dst=0)
+        mine = checksum(ptr, n)
+        dist.all_reduce(mine)
         if rank == 0:
-            ref = torch.empty(frame_bytes, dtype=torch.uint8, device="cuda")
-            pyvrt.assemble(ctx, g.data_ptr(), world, size, "color", ref.data_ptr(), stream=torch.cuda.current_stream().cuda_stream)
-            torch.cuda.synchronize()
-            if not torch.equal(ref, asm2[0]):
-                raise SystemExit("push exchange: assembled frame differs from the gathered one")
+            dptr, _, nb = ctx.comm_frame_plane(0, "color")
+            if not torch.equal(checksum(dptr, nb), mine):
+                raise SystemExit("exchange self-check failed: the assembled frame does not hold the ranks' tiles")
         barrier()
 
-    # ---- warm-up, then an untimed counting pass over the K timed poses (rays / voxel visits / kernel time per frame)
+    # ---- warm-up, then an untimed counting pass over the K timed poses, each frame ALONE on the GPU (rays / voxel visits / kernel
+    # times per frame; this is also the single-frame latency)
     for k in range(max(args.warmup, F)):
         submit(k)
     drain()
     barrier()
-    rays = fetches = pixels = lib_launches = 0
-    ms_kernel, ms_stage = [], []
+    rays = fetches = pixels = lib_launches = extra_launches = 0
+    ms_kernel, ms_stage, ms_alone = [], [], []
     stage_rays, stage_fetches = np.zeros(3), np.zeros(3)
+    a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     for k in range(args.steps):
-        fr, _ = submit(k)
+        barrier()
+        with torch.cuda.stream(ext):
+            a0.record()
+        fr, n = submit(k)
+        drain()
+        with torch.cuda.stream(ext):
+            a1.record()
         s = fr.stats()
+        ctx.sync()
+        ms_alone.append(a0.elapsed_time(a1))
         rays += s["rays"]; fetches += s["fetches"]; pixels += s["pixels"]; ms_kernel.append(s["ms_trace"] + s["ms_denoise"])
         ms_stage.append(s["ms_stage"]); stage_rays += s["stage_rays"]; stage_fetches += s["stage_fetches"]
-        lib_launches += s["kernel_launches"]
-    drain()
+        lib_launches += s["kernel_launches"]; extra_launches += n
     barrier()
 
     # ---- timed region 1: K frames, inputs resident, device time on the launching stream, max over ranks. The region ends when the
-    # last frame is assembled on rank 0 (every gather and detile kernel is inside it).
+    # last frame is assembled on rank 0 (every push, signal and wait kernel is inside it). The region is repeated until at least
+    # --min-timed-ms of GPU time has been measured; the median region is reported and the clocks are sampled over the whole span.
     sampler = ClockSampler(local) if rank == 0 else None
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    launches = lib_launches    # the timed region replays exactly the frames counted above
-    barrier()
-    with torch.cuda.stream(ext):
-        e0.record()
-    t_host = time.perf_counter()
-    for k in range(args.steps):
-        _, n = submit(k)
-        launches += n
-    launches += drain()
-    t_host = time.perf_counter() - t_host        # host time to QUEUE the K frames (must stay below the device time, else the GPU starves)
-    with torch.cuda.stream(ext):
-        e1.record()
-    barrier()
-    ms = e0.elapsed_time(e1)
+    region_ms, host_ms = [], []
+    repeats = 1
+    while len(region_ms) < repeats:
+        barrier()
+        with torch.cuda.stream(ext):
+            e0.record()
+        t_host = time.perf_counter()
+        for k in range(args.steps):
+            submit(k)
+        drain()
+        host_ms.append(1e3 * (time.perf_counter() - t_host))   # host time to QUEUE the K frames (must stay below the device time, else the GPU starves)
+        with torch.cuda.stream(ext):
+            e1.record()
+        barrier()
+        mx = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        region_ms.append(float(mx.item()))
+        if len(region_ms) == 1:
+            repeats = int(min(400, max(1, math.ceil(args.min_timed_ms / max(region_ms[0], 1e-3)))))
     clocks = sampler.stop() if sampler else None
+    ms = float(np.median(region_ms))
 
-    # ---- timed region 2 (e2e): the same K frames through the public API with the finished frame read back into pinned host
-    # memory EVERY step; per-step inputs (camera block + settings) travel as kernel parameters. The read-back of frame k runs on
-    # the copy stream beside the kernels of the following frames, and the host waits for frame k-(F-1) before it queues frame
-    # k+1 (F frame objects in flight). All K read-backs complete inside the timed region.
+    # ---- timed region 2 (e2e): the same K frames through the public API with the finished frame in pinned HOST memory EVERY step;
+    # per-step inputs (camera block + settings) travel as kernel parameters. N = 1: the read-back of frame k runs on the copy stream
+    # beside the kernels of the following frames. N > 1: every rank stores its own tiles into the shared pinned host frame over its
+    # own PCIe link (the denoised frame of cfg3 is produced on rank 0 and copied from there). The host waits for frame k-(F-1)
+    # before it queues frame k+1 (F frame objects in flight). All K frames are complete in host memory inside the timed region.
     if args.shard and world == 1:                           # debug mode: a shard is not a frame, there is nothing to read back
         t_e2e = ms * 1e-3
     else:
-        for k in range(F):
-            submit(k, True)
-        drain()
-        for k in range(F):
-            wait_readback(k)
-        barrier()
-        t0 = time.perf_counter()
-        for k in range(args.steps):
-            submit(k, True)
-            if k >= F - 1:
-                wait_readback(k - (F - 1))            # the host runs at most F-1 frames ahead of the finished read-backs
-        drain()
-        for k in range(max(0, args.steps - (F - 1)), args.steps):
-            wait_readback(k)
-        barrier()
-        t_e2e = time.perf_counter() - t0
+        def e2e_region():
+            barrier()
+            t0 = time.perf_counter()
+            for k in range(args.steps):
+                submit(k, True)
+                if k >= F - 1:
+                    wait_readback(k - (F - 1))            # the host runs at most F-1 frames ahead of the finished read-backs
+            drain()
+            for k in range(max(0, args.steps - (F - 1)), args.steps):
+                wait_readback(k)
+            barrier()
+            return time.perf_counter() - t0
+        e2e_region()                                       # warm-up of the read-back path
+        reps = int(min(200, max(1, math.ceil(0.5 * repeats))))
+        t_e2e = float(np.median([e2e_region() for _ in range(reps)]))
 
-    tot = torch.tensor([float(rays), float(fetches), float(pixels)], dtype=torch.float64, device="cuda")
-    mx = torch.tensor([ms, t_e2e], dtype=torch.float64, device="cuda")
+    tot = torch.tensor([float(rays), float(fetches), float(pixels)], dtype=torch.float64, device=dev)
+    mx = torch.tensor([t_e2e, float(np.median(ms_alone))], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tot); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
     rays_all, fetches_all, pixels_all = [float(x) for x in tot.tolist()]
-    ms, t_e2e = [float(x) for x in mx.tolist()]
+    t_e2e, latency_ms = [float(x) for x in mx.tolist()]
 
     if rank == 0:
         peak, peak_src = measured_peaks()
@@ -464,8 +506,9 @@ def run_vrt(args):
         k_ms = float(np.mean(ms_kernel))
         # dominant kernel of the pass: per-stage CUDA-event times and per-stage getVoxel counts from the library
         stage_ms = np.mean(np.array(ms_stage), axis=0)
+        default_path = args.traversal in (0, 5) and args.pipeline != 1 and os.environ.get("VRT_ENGINE_T", "8") != "0"
         engine = args.traversal in (0, 4, 5) and os.environ.get("VRT_ENGINE_T", "8") != "0"
-        names = ["wave_primary_kernel", "wave_bounce_kernel (x5)", "wave_anyhit_engine_kernel" if engine else "wave_anyhit_kernel",
+        names = ["wave_primary_kernel", "wave_bounce_kernel (x3)", "wave_anyhit_engine_kernel" if engine else "wave_anyhit_kernel",
                  "wave_resolve_kernel"] if args.pipeline != 1 else ["render_kernel"] * 4
         dom = int(np.argmax(stage_ms[:3]))
         # algorithmic bytes of that kernel: 1 B per reference getVoxel call + its outputs
@@ -474,42 +517,74 @@ def run_vrt(args):
         alg_bytes = (float(stage_fetches[dom]) + out_bytes) / args.steps
         dom_ms = float(stage_ms[dom])
         achieved = alg_bytes / (dom_ms * 1e-3) / 1e9
+        traffic, traffic_src = ncu_traffic(names[dom], args.config, world, default_path and not args.shard)
+        info = ctx.device_info()
+        f_sm = (clocks or {}).get("sm_max_mhz") or 1965.0
+        issue_peak = info["sm_count"] * 4 * 32 * f_sm * 1e6                  # lane-instructions per second the chip can issue
+        issue_ach = float(stage_fetches[dom]) / args.steps * STEP_INSTRUCTIONS / (dom_ms * 1e-3)
         line = {"metric": METRIC, "value": rays_all / (ms * 1e-3) / 1e6, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": config_blob(cfg, args.config, args.whd, size, {"parallelism": f"tiles{world}" if world > 1 else "single", "traversal": args.traversal, "pipeline": args.pipeline,
-                                                                         "gathered_plane": "color RGBA8" if world > 1 else None, "frames_in_flight": F, "frame_streams": "one" if args.serial_frames else "per frame",
-                                                                         "exchange": ("NCCL gather of frame k on a communication stream beside the tracing of the next frames, detile on rank 0" if args.exchange == "gather" else "every rank stores its tiles of frame k straight into rank 0's frame (symmetric memory over NVLink) on a communication stream; device-side barriers") if world > 1 else None}),
+                "config": config_blob(cfg, args.config, args.whd, size, world),
+                "run": {"traversal": args.traversal, "pipeline": args.pipeline, "frames_in_flight": F, "frame_streams": "one" if args.serial_frames else "per frame",
+                        "timed_regions": len(region_ms), "timed_ms_total": float(np.sum(region_ms)), "region_ms_min_median_max": [float(np.min(region_ms)), ms, float(np.max(region_ms))],
+                        "exchange": ("libvrt vrt_frame_exchange: every rank stores its tiles of " + "+".join(xplanes) + " into rank 0's frame (CUDA IPC peer memory over NVLink) "
+                                     "+ arrival flags; rank 0 consumes behind a wait kernel" + ("; rank 0 denoises the assembled planes" if denoise else "")) if world > 1 else None,
+                        "e2e_readback": ("every rank stores its tiles into a pinned host frame shared by all ranks (own PCIe link each)" if not denoise else "rank 0 copies the denoised frame to pinned host memory") if world > 1
+                                        else "vrt_frame_download_async on the copy stream, F frames in flight"},
+                "latency_ms_single_frame": latency_ms,
+                "scene_bytes": mem["volume_bytes"] + mem["field_bytes"], "scene": mem,
                 "rays_per_frame": rays_all / args.steps, "voxel_visits_per_frame": fetches_all / args.steps,
                 "Mrays_per_s_primary": pixels_all / (ms * 1e-3) / 1e6,
-                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(names[dom]),
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                              "kernel": names[dom], "kernel_ms": dom_ms, "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
+                             "limiter": "instruction issue (ALU pipe), not memory: see roofline.issue and DESIGN.md section 4",
+                             "issue": {"instr_per_step": STEP_INSTRUCTIONS, "steps_per_launch": float(stage_fetches[dom]) / args.steps, "achieved_lane_instr_per_s": issue_ach,
+                                       "peak_lane_instr_per_s": issue_peak, "frac": issue_ach / issue_peak,
+                                       "note": "reference getVoxel calls the kernel stands for x 7 SASS instructions per replayed DDA step / kernel time, against SMs x 4 schedulers x 32 lanes x max SM clock"},
                              "frame": {"achieved": frame_bytes_alg / (k_ms * 1e-3) / 1e9, "frac": frame_bytes_alg / (k_ms * 1e-3) / 1e9 / peak,
                                        "algorithmic_bytes": frame_bytes_alg, "ms": k_ms},
                              "l2": l2_block(float(stage_fetches[0]) / args.steps + pixels / args.steps * b_out, float(stage_ms[0])),
                              "stages_ms": {"primary": float(stage_ms[0]), "bounce": float(stage_ms[1]), "anyhit": float(stage_ms[2]), "resolve": float(stage_ms[3])},
                              "stages_Mrays": {"primary": float(stage_rays[0] / args.steps / 1e6), "bounce": float(stage_rays[1] / args.steps / 1e6), "anyhit": float(stage_rays[2] / args.steps / 1e6)},
                              "stages_Gvisits": {"primary": float(stage_fetches[0] / args.steps / 1e9), "bounce": float(stage_fetches[1] / args.steps / 1e9), "anyhit": float(stage_fetches[2] / args.steps / 1e9)},
-                             "note": "algorithmic bytes = getVoxel calls of the reference loop x 1 B + the kernel's outputs (primary: %d B/pixel; any-hit: 1 B/ray); the loop is issue-bound, not bandwidth-bound (DESIGN.md)" % b_out},
+                             "note": "stage times are of frames running ALONE; algorithmic bytes = getVoxel calls of the reference loop x 1 B + the kernel's outputs (primary: %d B/pixel; any-hit: 1 B/ray)" % b_out},
                 "e2e": {"value": rays_all / t_e2e / 1e6, "unit": UNIT, "h2d_bytes_per_step": C.sizeof(pyvrt.Camera) + C.sizeof(pyvrt.RenderSettings),
                         "d2h_bytes_per_step": frame_bytes, "ms_per_step": 1e3 * t_e2e / args.steps},
-                "gpu_launches": launches, "clocks": clocks, "host_submit_ms_per_step": 1e3 * t_host / args.steps}
-        if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline(cfg, args.config, args.whd, size, args.cpu_seconds)
+                "gpu_launches": lib_launches + extra_launches, "clocks": clocks, "host_submit_ms_per_step": float(np.median(host_ms)) / args.steps}
+        if world == 1 and not args.no_cpu_baseline and not args.shard:
+            def gpu_frame0():
+                sti = configs.settings_for(cfg, gbuffer=True, instrument=True)
+                sti.traversal, sti.pipeline, sti.denoise.enable = args.traversal, args.pipeline, 0
+                rp = pyvrt.VoxelRenderPass(ctx, scene, sti)
+                fr = rp.record(configs.make_camera(args.config, bounds, size, 0)); fr.sync()
+                out = {n: fr.download(n) for n in ("hit", "hit_palette", "depth", "position", "normal", "mask", "rays", "fetches", "color", "color_f32")}
+                fr.release()
+                return out
+            line["cpu_baseline"], line["parity"] = cpu_baseline_and_parity(cfg, args.config, args.whd, size, args.cpu_seconds, gpu_frame0)
         print(json.dumps(line), flush=True)
+        if "parity" in line and not line["parity"]["ok"]:
+            raise SystemExit("parity check failed: the CUDA path differs from the oracle (see the parity block)")
     barrier()
-    # tensors that were used on the context's stream must be returned to torch's allocator while that stream still exists
-    gathered = host2 = asm2 = sym = hdl = None
-    for p_ in passes[1:]:
+    # tensors that were used on the library's streams must be returned to torch's allocator while those streams still exist
+    host2 = dn_out = dn_scratch = cstream = None
+    for p_ in passes:
         p_.frame.release()
     del submit
     import gc
     gc.collect()
     torch.cuda.synchronize()
     torch.cuda.empty_cache()
+    scene.destroy(); ctx.close()                             # closes the communicator (collective)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
-    scene.destroy(); ctx.close()
+
+
+class _DevBuf:
+    """Wraps a device pointer owned by libvrt so torch can read it (no copy)."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
 
 
 if __name__ == "__main__":

@@ -43,7 +43,8 @@ typedef enum {
     VRT_E_CUDA = -6,          /* CUDA runtime error (message in vrt_last_error) */
     VRT_E_NO_DEVICE = -7,     /* no CUDA device: there is NO CPU fallback */
     VRT_E_UNSUPPORTED = -8,
-    VRT_E_OOM = -9
+    VRT_E_OOM = -9,
+    VRT_E_COMM = -10          /* multi-GPU exchange: rendezvous failed, a rank reported an error, or a wait timed out */
 } vrt_status;
 
 typedef struct vrt_context vrt_context;
@@ -201,6 +202,10 @@ void vrt_frame_release(vrt_frame*);
 /* Stand-alone denoiser on host planes already resident on device: DenoiserStage::record. */
 int vrt_denoise(vrt_context*, const void* d_color_rgba8, const void* d_normal_rgba8s, const void* d_position_rgba32f,
                 int w, int h, const vrt_denoiser_settings*, void* d_out_rgba8);
+/* The same without synchronising: on `stream` (NULL: the context stream), with a caller-owned scratch image of w*h*4 bytes
+ * (needed when iterations > 1). This is what rank 0 runs on the assembled planes of a sharded frame. */
+int vrt_denoise_on(vrt_context*, const void* d_color_rgba8, const void* d_normal_rgba8s, const void* d_position_rgba32f,
+                   int w, int h, const vrt_denoiser_settings*, void* d_out_rgba8, void* d_scratch_rgba8, void* stream);
 
 /* Multi-GPU assembly on the gathering rank: d_gathered holds `world` shard buffers back to back (rank-major), each
  * of vrt_frame_plane() size as produced under vrt_context_set_shard(rank, world); writes a row-major w x h plane. */
@@ -212,6 +217,31 @@ int vrt_assemble_on(vrt_context*, const void* d_gathered, int world, int w, int 
  * may be peer memory (another GPU's buffer mapped into this process over NVLink). On `stream` (NULL: the frame's own stream); the
  * caller orders the stores against the consumer (device-side barrier / signal). With world == 1 it is a plain de-tile copy. */
 int vrt_frame_push_tiles(vrt_frame*, int plane, void* d_frame, void* stream);
+
+/* ---- multi-GPU exchange inside the library: one process per GPU, every rank traces its interleaved tile shard,
+ * the frame is assembled on rank 0. No collective call on the data path: rank 0 owns the assembled planes of `slots` frames in flight
+ * and exports them (CUDA IPC); every other rank maps them as peer memory (NVLink / NVSwitch) and stores its tiles straight into the
+ * row-major frame, then an arrival flag; rank 0 orders its consumer behind a wait kernel on the flags. The same stores can go to a
+ * frame in pinned HOST memory shared by all ranks, so a read-back uses every GPU's PCIe link at once.
+ *   key: names the POSIX shared-memory rendezvous segment; the same on every rank, unique per job (rank 0 creates it).
+ *   vrt_comm_create also sets the tile shard (vrt_context_set_shard(rank, world)); call it before the first frame.
+ *   vrt_comm_alloc_frames is collective (same arguments on every rank); plane masks are bit (1 << vrt_plane).
+ *   Per frame, every rank: vrt_render, then vrt_frame_exchange(frame, slot, ...) — asynchronous on the frame's stream (or `stream`);
+ *   the call itself may block on the host until rank 0 has released what the slot held before.
+ *   Rank 0 then: vrt_comm_wait(slot, stream) [device-side], its own work on that stream (vrt_denoise_on, copies, ...),
+ *   vrt_comm_release_on(slot, stream); or vrt_comm_wait_host(slot) / vrt_comm_release(slot) for the host frame.
+ * Every wait has a time limit (VRT_COMM_TIMEOUT_S, default 120 s) and returns VRT_E_COMM instead of hanging when a rank is gone. */
+int vrt_comm_create(vrt_context*, int rank, int world, const char* key);
+int vrt_comm_destroy(vrt_context*);                       /* collective; vrt_context_destroy calls it */
+int vrt_comm_barrier(vrt_context*);                       /* host barrier over all ranks */
+int vrt_comm_alloc_frames(vrt_context*, int w, int h, int slots, uint32_t plane_mask, uint32_t host_plane_mask);
+int vrt_frame_exchange(vrt_frame*, int slot, uint32_t plane_mask, uint32_t host_plane_mask, void* stream);
+int vrt_comm_wait(vrt_context*, int slot, void* stream);  /* rank 0; stream NULL: vrt_comm_stream() */
+int vrt_comm_wait_host(vrt_context*, int slot);           /* rank 0 */
+int vrt_comm_release(vrt_context*, int slot);             /* rank 0 */
+int vrt_comm_release_on(vrt_context*, int slot, void* stream);
+int vrt_comm_frame_plane(vrt_context*, int slot, int plane, void** d_ptr, void** h_ptr, size_t* bytes);
+void* vrt_comm_stream(vrt_context*);                      /* rank 0's consumer stream; vrt_context_join / _sync include it */
 
 /* ---- output stage (the step downstream of the pass): BlitStage::record running blit.frag, headless ----
  * d_src: sw x sh RGBA8 on the device (the colour or denoised plane of a full frame, or any RGBA8 image); d_dst: tw x th RGBA8 device

@@ -177,9 +177,9 @@ def test_dense_and_brick_traversal_identical_at_4k(gpu_ctx):
     gs.destroy()
 
 
-def test_production_frames_early_termination(gpu_ctx):
-    """Frames without VRT_OUT_INSTRUMENT end rays as a miss as soon as the safe-step field shows no solid within reach (EARLY_ALWAYS):
-    colour and every G-buffer plane must still equal the oracle's / the instrumented frame's, on every pipeline."""
+def test_production_frames_equal_instrumented_frames(gpu_ctx):
+    """Frames without VRT_OUT_INSTRUMENT (what bench.py times): colour and every G-buffer plane equal the oracle's / the instrumented
+    frame's on every pipeline, and the ray and getVoxel totals of the frame statistics are the oracle's exactly."""
     gs = pyvrt.VoxelScene.generate(gpu_ctx, 1, 42, 256, 192, 256)
     noise, sky = assets.noise_standin(), assets.sky_standin(512, 256)
     gs.set_noise(noise); gs.set_skybox(sky)
@@ -199,7 +199,7 @@ def test_production_frames_early_termination(gpu_ctx):
                 ok, bad = bits_equal(got[n], want[n]); assert ok, (trav, pipe, n, bad)
             assert np.array_equal(got["color"], want["color"]) or np.abs(got["color"].astype(int) - want["color"].astype(int)).max() <= 1
             assert stats["rays"] == int(want["rays"].sum())
-            assert stats["fetches"] >= int(want["fetches"].sum())         # early-terminated rays are booked with their full budget
+            assert stats["fetches"] == int(want["fetches"].sum())
     # full resolution, sharp edge: production frame == instrumented frame, byte for byte
     big = pyvrt.VoxelScene.generate(gpu_ctx, 1, 42, 512, 256, 512)
     big.set_noise(noise); big.set_skybox(sky)

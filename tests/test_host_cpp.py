@@ -24,6 +24,44 @@ def build_check():
     return EXE
 
 
+COMM_SRC = os.path.join(ROOT, "tests", "host_cpp", "comm_check.cpp")
+COMM_EXE = os.path.join(ROOT, "tests", "host_cpp", "comm_check")
+
+
+def build_comm_check():
+    deps = [COMM_SRC, os.path.join(ROOT, "include", "vrt.h"), os.path.join(PKG, "libvrt.so")]
+    if not os.path.exists(COMM_EXE) or any(os.path.getmtime(d) > os.path.getmtime(COMM_EXE) for d in deps):
+        gxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+        subprocess.check_call([gxx, "-std=c++17", "-O1", "-Wall", "-Werror", "-I" + os.path.join(ROOT, "include"), COMM_SRC, "-o", COMM_EXE,
+                               "-L" + PKG, "-lvrt", "-Wl,-rpath," + PKG])
+    return COMM_EXE
+
+
+def test_cpp_comm_check_compiles_and_links():
+    """The multi-rank exchange driver is plain C++ over include/vrt.h (no torch, no NCCL): it must build and link on the CPU tier."""
+    assert os.path.exists(build_comm_check())
+
+
+@pytest.mark.skipif(os.path.exists("/dev/nvidia0"), reason="this is the no-GPU behaviour test")
+def test_cpp_comm_check_fails_loudly_without_gpu():
+    p = subprocess.run([build_comm_check(), "2", "64", "64", "1"], capture_output=True, text=True, timeout=120)
+    assert p.returncode == 10 and "no CPU fallback" in p.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world,size", [(2, (200, 150)), (3, (333, 217)), (4, (640, 360))])
+def test_cpp_ranks_assemble_a_frame_without_torch(world, size):
+    """a C++ host linking libvrt.so shards a frame over `world` processes and assembles it on rank 0 through
+    vrt_comm_* / vrt_frame_exchange alone (peer stores into rank 0's frame + shared pinned host frame), then denoises it there:
+    every plane and the denoised frame equal the single-rank frame byte for byte. Ranks share the GPUs that are present."""
+    import torch
+    ndev = max(1, torch.cuda.device_count())
+    env = dict(os.environ, VRT_COMM_TIMEOUT_S="60")
+    p = subprocess.run([build_comm_check(), str(world), str(size[0]), str(size[1]), str(ndev), "5"], capture_output=True, text=True, timeout=600, env=env)
+    assert p.returncode == 0, p.stdout + p.stderr
+    assert "identical to the single-rank frames" in p.stdout
+
+
 def test_cpp_host_compiles_and_links():
     out = subprocess.check_output([build_check(), "--link-only"], text=True)
     assert out.startswith("vrt ")

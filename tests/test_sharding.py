@@ -1,6 +1,8 @@
 """N>1 path on CPU (gloo, world size 2 and 3): every rank renders its interleaved tile shard with the product's own
 per-pixel code and layout functions (host-compiled: tests/host_harness), the colour shards are gathered on rank 0 with
-torch.distributed exactly as bench.py gathers them over NCCL, assembled, and must be byte-identical to the 1-rank frame."""
+torch.distributed, assembled with the product's index functions, and must be byte-identical to the 1-rank frame: tile
+ownership, compact tile-major indices and the inverse mapping, on the default traversal back-end and on FINE. (The
+GPU-side exchange itself — vrt_comm_* over CUDA IPC — needs a device: tests/test_host_cpp.py, GPU tier.)"""
 import ctypes as C
 import os
 import socket
@@ -11,7 +13,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from vrtlib import O, assets, harness, harness_render, look_at_camera, random_volume, random_palette, to_vrt_camera, to_vrt_settings, TRAV_FINE
+from vrtlib import O, assets, harness, harness_render, look_at_camera, random_volume, random_palette, to_vrt_camera, to_vrt_settings, TRAV_FINE, TRAV_OCTANT
 
 TILE = 32
 
@@ -24,7 +26,7 @@ def _inputs():
     return vol, pal, cam, O.make_settings(ao=2)
 
 
-def _worker(rank, world, port, outdir):
+def _worker(rank, world, port, outdir, trav):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
@@ -39,7 +41,7 @@ def _worker(rank, world, port, outdir):
         shard = np.zeros(shard_px * 4, np.uint8)
         vs, vc = to_vrt_settings(st), to_vrt_camera(cam)
         h.hh_render_shard.restype = C.c_int
-        rc = h.hh_render_shard(C.c_void_p(hs), C.byref(vc), C.byref(vs), TRAV_FINE, rank, world, shard.ctypes.data_as(C.c_void_p), C.c_size_t(shard_px))
+        rc = h.hh_render_shard(C.c_void_p(hs), C.byref(vc), C.byref(vs), trav, rank, world, shard.ctypes.data_as(C.c_void_p), C.c_size_t(shard_px))
         assert rc == 0
         t = torch.from_numpy(shard)
         if rank == 0:
@@ -57,14 +59,14 @@ def _worker(rank, world, port, outdir):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world", [2, 3])
-def test_gloo_sharded_frame_is_byte_identical(world, tmp_path):
+@pytest.mark.parametrize("world,trav", [(2, TRAV_OCTANT), (3, TRAV_OCTANT), (2, TRAV_FINE)])
+def test_gloo_sharded_frame_is_byte_identical(world, trav, tmp_path):
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]
-    mp.spawn(_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, port, str(tmp_path), trav), nprocs=world, join=True)
     got = np.load(tmp_path / "frame.npy")
     vol, pal, cam, st = _inputs()
     sc, keep = O.make_scene(vol, pal, assets.noise_standin(), assets.sky_standin(64, 32))
-    want = harness_render(sc, cam, st, traversal=TRAV_FINE)["color"]
+    want = harness_render(sc, cam, st, traversal=trav)["color"]
     assert np.array_equal(got, want)
     assert np.array_equal(want, O.render(sc, cam, st)["color"]) or np.abs(want.astype(int) - O.render(sc, cam, st)["color"].astype(int)).max() <= 1

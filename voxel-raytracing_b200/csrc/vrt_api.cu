@@ -13,69 +13,12 @@
 #include <new>
 #include <string>
 #include <vector>
-#include "vrt_launch.h"
+#include "vrt_internal.h"
 #include "vrt_vox.h"
 
-using namespace vrt;
+thread_local std::string g_vrt_err;
 
-static thread_local std::string g_err;
-static int fail(int code, const std::string& msg) { g_err = msg; return code; }
-#define CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(VRT_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
-
-struct vrt_context {
-    int device = 0, rank = 0, world = 1;
-    cudaStream_t stream = nullptr;
-    cudaStream_t copyStream = nullptr;   // asynchronous read-backs (vrt_frame_download_async)
-    WaveSide side{};                     // low-priority stream + fork/join events (launch_wavefront)
-    cudaDeviceProp prop{};
-    bool concurrent = false;             // frames created from now on render on their own streams (vrt_context_set_concurrent_frames)
-    std::vector<struct vrt_frame*> frames;
-};
-
-// Only the dense volume and the palette are resident for every scene. The fields of a traversal back-end are built when that
-// back-end is first asked for (vrt_scene_prepare, or the first vrt_render that names it), under the scene's mutex: the default
-// back-end (OCTANT) is prepared at load time so that no frame pays for it.
-struct vrt_scene {
-    vrt_context* ctx = nullptr;
-    uint32_t w = 0, h = 0, d = 0, Bx = 0, By = 0, Bz = 0;
-    uint8_t* vol = nullptr; unsigned long long* bmask = nullptr; uint8_t* bdist = nullptr; uint8_t* fdist = nullptr; uint8_t* ldist = nullptr;
-    uint8_t* odist[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    vrt_material* palette = nullptr; vrt_material hostPalette[256];
-    uint8_t* noise = nullptr; float* sky = nullptr; uint32_t skyW = 0, skyH = 0;
-    int accelLaunches = 0;
-    std::mutex fieldMutex;               // guards the lazy field builds below
-    size_t fieldBytes = 0;               // safe-step fields resident now
-    size_t peakBuildBytes = 0;           // largest scratch + fields footprint seen during a build
-    double loadMs = 0.0;                 // host wall time of upload / generate / flatten + field builds so far
-};
-
-static const int kPlaneBpp[VRT_PLANE_COUNT] = {4, 4, 4, 8, 1, 16, 4, 8, 1, 12, 4, 4};
-
-struct vrt_frame {
-    vrt_context* ctx = nullptr;
-    int W = 0, H = 0;
-    size_t pixels = 0;                 // pixels stored per plane on this rank (full frame, or localTiles*1024 when sharded)
-    int tilesX = 0, tilesY = 0, localTiles = 0;
-    void* planes[VRT_PLANE_COUNT] = {};
-    void* ping[2] = {nullptr, nullptr};
-    Counters* ctr = nullptr;
-    cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr;
-    cudaEvent_t es[3] = {nullptr, nullptr, nullptr};   // wavefront stage boundaries
-    cudaEvent_t rendered = nullptr, copied = nullptr;  // asynchronous read-back: frame complete on the main stream / copy complete
-    bool copyPending = false;
-    bool staged = false;
-    bool denoised = false;
-    uint32_t launches = 0, out_mask = 0;
-    cudaStream_t stream = nullptr;     // the stream this frame's work is queued on: the context's, or its own (concurrent frames)
-    WaveSide side{};
-    cudaEvent_t fork = nullptr;        // own stream: orders the frame after what the context stream held when vrt_render was called
-    cudaEvent_t joined = nullptr;      // own stream: vrt_context_join
-    bool own = false;
-    WaveBuf wb{};                      // wavefront pipeline buffers (allocated on first use)
-    uint32_t wbRays = 0;               // result planes allocated in wb.res
-};
-
-extern "C" const char* vrt_last_error(void) { return g_err.c_str(); }
+extern "C" const char* vrt_last_error(void) { return g_vrt_err.c_str(); }
 extern "C" const char* vrt_version(void) { return "vrt 0.1 (sm_100a)"; }
 
 extern "C" void vrt_context_destroy(vrt_context* c);
@@ -101,9 +44,13 @@ extern "C" int vrt_context_create(int device, vrt_context** out) {
     *out = c;
     return VRT_OK;
 }
+int vrt_comm_join_into(vrt_context* c);   // vrt_comm.cu
+int vrt_comm_sync(vrt_context* c);
+extern "C" int vrt_comm_destroy(vrt_context* c);
 extern "C" void vrt_context_destroy(vrt_context* c) {
     if (!c) return;
     cudaSetDevice(c->device);
+    vrt_comm_destroy(c);
     if (c->stream) cudaStreamDestroy(c->stream);
     if (c->copyStream) cudaStreamDestroy(c->copyStream);
     if (c->side.stream) cudaStreamDestroy(c->side.stream);
@@ -128,7 +75,7 @@ extern "C" int vrt_context_sync(vrt_context* c) {
     CU(cudaSetDevice(c->device));
     CU(cudaStreamSynchronize(c->stream));
     for (vrt_frame* f : c->frames) if (f->own) CU(cudaStreamSynchronize(f->stream));
-    return VRT_OK;
+    return vrt_comm_sync(c);
 }
 extern "C" void* vrt_context_stream(vrt_context* c) { return c ? (void*)c->stream : nullptr; }
 // Frames in flight: with this on, every frame object created afterwards renders on a stream of its own (forked from the context
@@ -143,7 +90,7 @@ extern "C" int vrt_context_join(vrt_context* c) {
     if (!c) return fail(VRT_E_INVALID, "ctx is null");
     CU(cudaSetDevice(c->device));
     for (vrt_frame* f : c->frames) if (f->own) { CU(cudaEventRecord(f->joined, f->stream)); CU(cudaStreamWaitEvent(c->stream, f->joined, 0)); }
-    return VRT_OK;
+    return vrt_comm_join_into(c);
 }
 
 // ------------------------------------------------------------------------------------------------ scene
@@ -593,7 +540,7 @@ extern "C" int vrt_render(vrt_context* c, const vrt_scene* s, const vrt_camera* 
     if (st->pipeline > VRT_PIPELINE_WAVEFRONT) return fail(VRT_E_INVALID, "unknown pipeline");
     if (st->vol.aoSamples > 255) return fail(VRT_E_INVALID, "aoSamples must be <= 255 (the reference GUI allows 0..16)");
     const bool wavefront = st->pipeline != VRT_PIPELINE_MEGAKERNEL;
-    if (st->denoise.enable && c->world != 1) return fail(VRT_E_UNSUPPORTED, "denoise runs on the assembled frame: call vrt_denoise on rank 0 after the gather");
+    if (st->denoise.enable && c->world != 1) return fail(VRT_E_UNSUPPORTED, "denoise runs on the assembled frame: exchange colour, normal and position (vrt_frame_exchange) and call vrt_denoise_on on rank 0");
     CU(cudaSetDevice(c->device));
     vrt_frame* f = *frame;
     if (f && (f->W != W || f->H != H || f->ctx != c)) return fail(VRT_E_INVALID, "frame does not match screenSize/context");
@@ -751,6 +698,18 @@ extern "C" int vrt_denoise(vrt_context* c, const void* d_color, const void* d_no
     if (rc) return rc;
     if (e != cudaSuccess) return fail(VRT_E_CUDA, cudaGetErrorString(e));
     return VRT_OK;
+}
+
+extern "C" int vrt_denoise_on(vrt_context* c, const void* d_color, const void* d_normal, const void* d_position, int w, int h,
+                              const vrt_denoiser_settings* ds, void* d_out, void* d_scratch, void* stream) {
+    if (!c || !d_color || !d_normal || !d_position || !ds || !d_out || w <= 0 || h <= 0) return fail(VRT_E_INVALID, "null argument");
+    if (d_out == d_color || d_scratch == d_color || d_out == d_scratch) return fail(VRT_E_INVALID, "d_out / d_scratch must not alias d_color or each other");
+    if (ds->iterations > 1 && !d_scratch) return fail(VRT_E_INVALID, "more than one iteration needs a scratch image");
+    CU(cudaSetDevice(c->device));
+    void* ping[2] = {d_out, d_scratch};
+    if (((ds->iterations - 1) % 2) == 1) { ping[0] = d_scratch; ping[1] = d_out; }   // the last iteration lands in d_out
+    int last = 0; uint32_t n = 0;
+    return run_denoise(c, stream ? (cudaStream_t)stream : c->stream, d_color, d_normal, d_position, w, h, ds, ping, &last, &n);
 }
 
 // BlitStage::record (blit_stage.cpp:25-57): source image -> "window" buffer through blit.frag. Asynchronous on the given stream.

@@ -1,0 +1,375 @@
+// vrt_comm.cu — the multi-GPU exchange, inside the library: one process per GPU, every rank traces its
+// interleaved tile shard, the frame is assembled on rank 0.
+//
+// There is no collective call on the data path. Rank 0 owns the assembled planes of `slots` frames in flight (one cudaMalloc block,
+// exported with cudaIpcGetMemHandle); every other rank maps that block (cudaIpcOpenMemHandle: peer memory, NVLink / NVSwitch on an
+// 8xB200 box) and its push kernel stores its tiles straight into the row-major frame — a tile row is 128 contiguous bytes in both
+// layouts, so the stores are full lines — followed by a one-word arrival flag. Rank 0 orders its consumer (denoiser, read-back,
+// present) behind a wait kernel that polls the `world` flags of the slot. The exchange therefore overlaps the tracing of the next
+// frames tile shard by tile shard, and the de-tile pass a gather would need on rank 0 does not exist.
+// The same kernel can store a rank's tiles into a frame in PINNED HOST memory shared by all ranks (POSIX shm, registered with CUDA in
+// every process): the read-back of a frame then runs over every GPU's PCIe link at once instead of funnelling through rank 0's.
+// Rendezvous, barrier and the slot hand-shake (a consumer releases a slot before the ranks may overwrite it) live in a small POSIX
+// shared-memory header; nothing on the data path touches the host.
+#include <cuda_runtime.h>
+#include <atomic>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+#include <fcntl.h>
+#include <sched.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+#include "vrt_internal.h"
+
+namespace {
+
+constexpr int kMaxWorld = 16, kMaxSlots = 8;
+constexpr uint32_t kMagic = 0x56525443u;   // "VRTC"
+
+struct CommShm {
+    std::atomic<uint32_t> magic;
+    uint32_t world;
+    std::atomic<uint32_t> joined;
+    std::atomic<uint32_t> barCount, barGen;
+    std::atomic<int32_t> error;                       // a rank that failed sets it; every wait gives up
+    // frame layout, written by rank 0 in vrt_comm_alloc_frames, valid once framesGen == the caller's generation
+    std::atomic<uint32_t> framesGen;
+    cudaIpcMemHandle_t devHandle;
+    uint64_t devBytes, hostBytes;
+    int32_t w, h, slots;
+    uint32_t planeMask, hostPlaneMask;
+    uint64_t planeOff[VRT_PLANE_COUNT], slotStride, arriveOff;
+    uint64_t hostPlaneOff[VRT_PLANE_COUNT], hostSlotStride;
+    std::atomic<uint64_t> released[kMaxSlots];        // generations of the slot the consumer on rank 0 is done with
+    volatile uint32_t hostArrive[kMaxSlots][kMaxWorld];   // generation whose tiles rank r has stored into the HOST frame (written by kernels)
+};
+
+double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+double timeout_s() { static const double t = getenv("VRT_COMM_TIMEOUT_S") ? atof(getenv("VRT_COMM_TIMEOUT_S")) : 120.0; return t; }
+
+}  // namespace
+
+struct vrt_comm {
+    int rank = 0, world = 1;
+    std::string key;
+    CommShm* shm = nullptr;                           // host mapping of the header
+    uint32_t* shmDevArrive = nullptr;                 // device view of shm->hostArrive
+    uint32_t framesGen = 0;
+    uint8_t* devBase = nullptr;                       // rank 0: its allocation; others: the peer mapping of it
+    uint8_t* hostBase = nullptr; uint8_t* hostBaseDev = nullptr; size_t hostBytes = 0;
+    uint64_t gen[kMaxSlots] = {};                     // exchanges issued on each slot (identical on every rank)
+    cudaStream_t stream = nullptr;                    // rank 0's consumer stream (wait kernel, caller's work, release)
+    cudaEvent_t joined = nullptr;
+    uint32_t* devError = nullptr;                     // set by a wait kernel that gave up
+    bool joinedOk = false;
+};
+
+// ---------------------------------------------------------------------------------------------------------------- kernels
+namespace vrt {
+
+// arrival flags of one exchange: generation g of slot s is complete for this rank (device frame on rank 0 and / or host frame).
+// A kernel of its own: it starts after the push kernels before it on the stream have completed, i.e. after their stores are performed.
+__global__ void comm_signal_kernel(volatile uint32_t* devFlag, volatile uint32_t* hostFlag, uint32_t g) {
+    __threadfence_system();
+    if (devFlag) *devFlag = g;
+    if (hostFlag) *hostFlag = g;
+}
+
+// rank 0: returns once the `world` arrival flags of the slot have reached generation g. Gives up after ~20 s (sets *err).
+__global__ void comm_wait_kernel(const volatile uint32_t* flags, int world, uint32_t g, uint32_t* err) {
+    const int r = threadIdx.x;
+    if (r < world) {
+        unsigned long long t0; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        for (;;) {
+            uint32_t v; asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + r) : "memory");
+            if ((int32_t)(v - g) >= 0) break;
+            __nanosleep(200);
+            unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            if (t - t0 > 20000000000ull) { *err = 1u; break; }
+        }
+    }
+    __threadfence_system();
+}
+
+}  // namespace vrt
+
+// ---------------------------------------------------------------------------------------------------------------- host
+static int comm_spin(vrt_comm* m, const char* what, bool (*done)(vrt_comm*, const void*), const void* arg, double limit = -1.0) {
+    const double t0 = now_s();
+    if (limit < 0) limit = timeout_s();
+    for (unsigned it = 0;; it++) {
+        if (done(m, arg)) return VRT_OK;
+        if (m->shm && m->shm->error.load(std::memory_order_relaxed)) return fail(VRT_E_COMM, std::string("another rank reported an error while this rank waited for ") + what);
+        if ((it & 63u) == 63u) { sched_yield(); if (now_s() - t0 > limit) { if (m->shm) m->shm->error.store(1); return fail(VRT_E_COMM, std::string("timed out waiting for ") + what); } }
+    }
+}
+
+static int comm_barrier(vrt_comm* m, double limit = -1.0) {
+    CommShm* h = m->shm;
+    const uint32_t gen = h->barGen.load();
+    if (h->barCount.fetch_add(1) + 1 == (uint32_t)m->world) { h->barCount.store(0); h->barGen.store(gen + 1); return VRT_OK; }
+    return comm_spin(m, "the barrier", [](vrt_comm* mm, const void* g) { return mm->shm->barGen.load() != *(const uint32_t*)g; }, &gen, limit);
+}
+
+static void comm_unmap_frames(vrt_comm* m) {
+    if (m->devBase) { if (m->rank == 0) cudaFree(m->devBase); else cudaIpcCloseMemHandle(m->devBase); m->devBase = nullptr; }
+    if (m->hostBase) { cudaHostUnregister(m->hostBase); munmap(m->hostBase, m->hostBytes); m->hostBase = nullptr; m->hostBaseDev = nullptr; }
+    if (m->rank == 0 && m->hostBytes) shm_unlink(("/vrt_" + m->key + "_f" + std::to_string(m->framesGen)).c_str());
+    m->hostBytes = 0;
+}
+
+extern "C" int vrt_comm_destroy(vrt_context* c) {
+    if (!c || !c->comm) return VRT_OK;
+    vrt_comm* m = c->comm;
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    if (m->shm && m->joinedOk && !m->shm->error.load()) comm_barrier(m, 15.0);   // nobody unmaps memory a peer may still be storing into
+    comm_unmap_frames(m);
+    if (m->stream) cudaStreamDestroy(m->stream);
+    if (m->joined) cudaEventDestroy(m->joined);
+    cudaFree(m->devError);
+    if (m->shm) { cudaHostUnregister(m->shm); munmap(m->shm, sizeof(CommShm)); }
+    if (m->rank == 0) shm_unlink(("/vrt_" + m->key).c_str());
+    delete m;
+    c->comm = nullptr;
+    return VRT_OK;
+}
+
+extern "C" int vrt_comm_create(vrt_context* c, int rank, int world, const char* key) {
+    if (!c || !key || !*key || world < 1 || world > kMaxWorld || rank < 0 || rank >= world) return fail(VRT_E_INVALID, "bad communicator arguments (world <= 16)");
+    if (c->comm) return fail(VRT_E_INVALID, "the context already has a communicator");
+    if (!c->frames.empty()) return fail(VRT_E_INVALID, "create the communicator before the first frame (it sets the tile shard)");
+    CU(cudaSetDevice(c->device));
+    vrt_comm* m = new (std::nothrow) vrt_comm();
+    if (!m) return fail(VRT_E_OOM, "host allocation failed");
+    m->rank = rank; m->world = world; m->key = key;
+    const std::string name = "/vrt_" + m->key;
+    int fd = -1;
+    if (rank == 0) {
+        shm_unlink(name.c_str());                                          // a stale segment of a crashed run with the same key
+        fd = shm_open(name.c_str(), O_CREAT | O_EXCL | O_RDWR, 0600);
+        if (fd >= 0 && ftruncate(fd, sizeof(CommShm)) != 0) { close(fd); fd = -1; }
+    } else {
+        const double t0 = now_s();
+        while ((fd = shm_open(name.c_str(), O_RDWR, 0600)) < 0 && now_s() - t0 < timeout_s()) usleep(1000);
+        struct stat st{};
+        while (fd >= 0 && (fstat(fd, &st) != 0 || (size_t)st.st_size < sizeof(CommShm)) && now_s() - t0 < timeout_s()) usleep(1000);
+    }
+    if (fd < 0) { delete m; return fail(VRT_E_COMM, "cannot open the shared-memory rendezvous segment " + name); }
+    void* p = mmap(nullptr, sizeof(CommShm), PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+    close(fd);
+    if (p == MAP_FAILED) { delete m; return fail(VRT_E_COMM, "mmap of the rendezvous segment failed"); }
+    m->shm = (CommShm*)p;
+    c->comm = m;
+    if (rank == 0) {
+        memset((void*)m->shm, 0, sizeof(CommShm));
+        m->shm->world = (uint32_t)world;
+        m->shm->magic.store(kMagic, std::memory_order_release);
+    } else {
+        int rc = comm_spin(m, "rank 0 to publish the rendezvous segment", [](vrt_comm* mm, const void*) { return mm->shm->magic.load(std::memory_order_acquire) == kMagic; }, nullptr);
+        if (rc == VRT_OK && m->shm->world != (uint32_t)world) { m->shm->error.store(1); rc = fail(VRT_E_COMM, "world size differs from rank 0's"); }
+        if (rc) { const std::string msg = g_vrt_err; vrt_comm_destroy(c); return fail(rc, msg); }
+    }
+    // the arrival flags of the host frames are written by kernels: the header is mapped into the device's address space
+    cudaError_t e = cudaHostRegister(m->shm, sizeof(CommShm), cudaHostRegisterMapped | cudaHostRegisterPortable);
+    void* dv = nullptr;
+    if (e == cudaSuccess) e = cudaHostGetDevicePointer(&dv, (void*)&m->shm->hostArrive[0][0], 0);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&m->joined, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaMalloc(&m->devError, sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaMemset(m->devError, 0, sizeof(uint32_t));
+    if (e != cudaSuccess) { m->shm->error.store(1); const std::string msg = cudaGetErrorString(e); vrt_comm_destroy(c); return fail(VRT_E_CUDA, msg); }
+    m->shmDevArrive = (uint32_t*)dv;
+    m->shm->joined.fetch_add(1);
+    const int rc = comm_barrier(m);
+    if (rc) { const std::string msg = g_vrt_err; vrt_comm_destroy(c); return fail(rc, msg); }
+    m->joinedOk = true;
+    c->rank = rank; c->world = world;
+    return VRT_OK;
+}
+
+extern "C" int vrt_comm_barrier(vrt_context* c) {
+    if (!c || !c->comm) return fail(VRT_E_INVALID, "no communicator");
+    return comm_barrier(c->comm);
+}
+extern "C" void* vrt_comm_stream(vrt_context* c) { return c && c->comm ? (void*)c->comm->stream : nullptr; }
+
+// Collective: every rank calls it with the same arguments. Rank 0 allocates the assembled planes of `slots` frames in flight on its
+// GPU (plane_mask) and in shared pinned host memory (host_plane_mask); the others map both.
+extern "C" int vrt_comm_alloc_frames(vrt_context* c, int w, int h, int slots, uint32_t plane_mask, uint32_t host_plane_mask) {
+    if (!c || !c->comm) return fail(VRT_E_INVALID, "no communicator");
+    if (w <= 0 || h <= 0 || slots < 1 || slots > kMaxSlots || (plane_mask | host_plane_mask) >> VRT_PLANE_COUNT || ((plane_mask | host_plane_mask) & (1u << VRT_PLANE_DENOISED_RGBA8)))
+        return fail(VRT_E_INVALID, "bad frame layout (slots <= 8; the denoised plane is produced on rank 0, not exchanged)");
+    vrt_comm* m = c->comm; CommShm* sh = m->shm;
+    CU(cudaSetDevice(c->device));
+    CU(cudaDeviceSynchronize());
+    int rc = comm_barrier(m);                                              // nobody is still storing into the old frames
+    if (rc) return rc;
+    comm_unmap_frames(m);
+    m->framesGen++;
+    memset(m->gen, 0, sizeof(m->gen));
+    const std::string hname = "/vrt_" + m->key + "_f" + std::to_string(m->framesGen);
+    cudaError_t e = cudaSuccess;
+    if (m->rank == 0) {
+        uint64_t off = 0, hoff = 0;
+        for (int p = 0; p < VRT_PLANE_COUNT; p++) {
+            sh->planeOff[p] = off; sh->hostPlaneOff[p] = hoff;
+            const uint64_t bytes = ((uint64_t)w * h * kPlaneBpp[p] + 255u) & ~(uint64_t)255u;
+            if (plane_mask >> p & 1u) off += bytes;
+            if (host_plane_mask >> p & 1u) hoff += bytes;
+        }
+        sh->slotStride = off; sh->hostSlotStride = hoff;
+        sh->arriveOff = off * slots;
+        sh->devBytes = sh->arriveOff + sizeof(uint32_t) * kMaxSlots * kMaxWorld;
+        sh->hostBytes = hoff * slots;
+        sh->w = w; sh->h = h; sh->slots = slots; sh->planeMask = plane_mask; sh->hostPlaneMask = host_plane_mask;
+        for (int s = 0; s < kMaxSlots; s++) { sh->released[s].store(0); for (int r = 0; r < kMaxWorld; r++) sh->hostArrive[s][r] = 0; }
+        e = cudaMalloc(&m->devBase, sh->devBytes);
+        if (e == cudaSuccess) e = cudaMemset(m->devBase, 0, sh->devBytes);
+        if (e == cudaSuccess && m->world > 1) e = cudaIpcGetMemHandle(&sh->devHandle, m->devBase);
+        if (e == cudaSuccess && sh->hostBytes) {
+            shm_unlink(hname.c_str());
+            const int fd = shm_open(hname.c_str(), O_CREAT | O_EXCL | O_RDWR, 0600);
+            if (fd < 0 || ftruncate(fd, (off_t)sh->hostBytes) != 0) { if (fd >= 0) close(fd); sh->error.store(1); return fail(VRT_E_COMM, "cannot create the shared host frame segment"); }
+            close(fd);
+        }
+        if (e != cudaSuccess) { sh->error.store(1); return fail(e == cudaErrorMemoryAllocation ? VRT_E_OOM : VRT_E_CUDA, cudaGetErrorString(e)); }
+        sh->framesGen.store(m->framesGen, std::memory_order_release);
+    } else {
+        rc = comm_spin(m, "rank 0 to allocate the frames", [](vrt_comm* mm, const void*) { return mm->shm->framesGen.load(std::memory_order_acquire) == mm->framesGen; }, nullptr);
+        if (rc) return rc;
+        if (sh->w != w || sh->h != h || sh->slots != slots || sh->planeMask != plane_mask || sh->hostPlaneMask != host_plane_mask) { sh->error.store(1); return fail(VRT_E_COMM, "frame layout differs from rank 0's"); }
+        void* base = nullptr;
+        e = cudaIpcOpenMemHandle(&base, sh->devHandle, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) { sh->error.store(1); return fail(VRT_E_CUDA, std::string("cudaIpcOpenMemHandle: ") + cudaGetErrorString(e)); }
+        m->devBase = (uint8_t*)base;
+    }
+    if (sh->hostBytes) {
+        const int fd = shm_open(hname.c_str(), O_RDWR, 0600);
+        void* p = fd >= 0 ? mmap(nullptr, sh->hostBytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0) : MAP_FAILED;
+        if (fd >= 0) close(fd);
+        if (p == MAP_FAILED) { sh->error.store(1); return fail(VRT_E_COMM, "cannot map the shared host frame segment"); }
+        m->hostBase = (uint8_t*)p; m->hostBytes = sh->hostBytes;
+        if (m->rank == 0) memset(p, 0, sh->hostBytes);                     // touch every page once, before the timed use
+        void* dv = nullptr;
+        e = cudaHostRegister(p, sh->hostBytes, cudaHostRegisterMapped | cudaHostRegisterPortable);
+        if (e == cudaSuccess) e = cudaHostGetDevicePointer(&dv, p, 0);
+        if (e != cudaSuccess) { sh->error.store(1); return fail(VRT_E_CUDA, std::string("cudaHostRegister of the shared host frames: ") + cudaGetErrorString(e)); }
+        m->hostBaseDev = (uint8_t*)dv;
+    }
+    return comm_barrier(m);
+}
+
+// This rank's tiles of the planes in plane_mask (device frame on rank 0) and host_plane_mask (shared host frame) of `slot`, then the
+// arrival flags. Asynchronous on the frame's stream (or `stream`); the call itself may wait on the HOST until rank 0 has released
+// what the slot held before (vrt_comm_release): with F slots the ranks run at most F-1 frames ahead of the consumer.
+extern "C" int vrt_frame_exchange(vrt_frame* f, int slot, uint32_t plane_mask, uint32_t host_plane_mask, void* stream) {
+    if (!f || !f->ctx->comm) return fail(VRT_E_INVALID, "no communicator");
+    vrt_context* c = f->ctx; vrt_comm* m = c->comm; CommShm* sh = m->shm;
+    if (!m->devBase) return fail(VRT_E_INVALID, "call vrt_comm_alloc_frames first");
+    if (slot < 0 || slot >= sh->slots || f->W != sh->w || f->H != sh->h) return fail(VRT_E_INVALID, "slot or frame size does not match vrt_comm_alloc_frames");
+    if ((plane_mask & ~sh->planeMask) || (host_plane_mask & ~sh->hostPlaneMask)) return fail(VRT_E_INVALID, "plane was not allocated by vrt_comm_alloc_frames");
+    for (int p = 0; p < VRT_PLANE_COUNT; p++) if (((plane_mask | host_plane_mask) >> p & 1u) && !f->planes[p]) return fail(VRT_E_INVALID, "plane was not produced for this frame");
+    CU(cudaSetDevice(c->device));
+    const uint64_t g = ++m->gen[slot];
+    struct Arg { int slot; uint64_t g; } a{slot, g};
+    int rc = comm_spin(m, "rank 0 to release the slot", [](vrt_comm* mm, const void* q) { const Arg* x = (const Arg*)q; return mm->shm->released[x->slot].load(std::memory_order_acquire) + 1 >= x->g; }, &a);
+    if (rc) return rc;
+    const cudaStream_t s = stream ? (cudaStream_t)stream : f->stream;
+    cudaError_t e = cudaSuccess;
+    for (int p = 0; p < VRT_PLANE_COUNT && e == cudaSuccess; p++) {
+        if (plane_mask >> p & 1u)
+            e = launch_push_tiles(f->planes[p], m->devBase + (uint64_t)slot * sh->slotStride + sh->planeOff[p], f->W, f->H, c->rank, c->world, f->localTiles, kPlaneBpp[p], s);
+        if (e == cudaSuccess && (host_plane_mask >> p & 1u))
+            e = launch_push_tiles(f->planes[p], m->hostBaseDev + (uint64_t)slot * sh->hostSlotStride + sh->hostPlaneOff[p], f->W, f->H, c->rank, c->world, f->localTiles, kPlaneBpp[p], s);
+        if (f->localTiles > 0) f->launches += (plane_mask >> p & 1u) + (host_plane_mask >> p & 1u);
+    }
+    if (e == cudaSuccess) {
+        uint32_t* devFlag = plane_mask ? (uint32_t*)(m->devBase + sh->arriveOff) + slot * kMaxWorld + c->rank : nullptr;
+        uint32_t* hostFlag = host_plane_mask ? m->shmDevArrive + slot * kMaxWorld + c->rank : nullptr;
+        comm_signal_kernel<<<1, 1, 0, s>>>(devFlag, hostFlag, (uint32_t)g);
+        f->launches++;
+        e = cudaGetLastError();
+    }
+    if (e != cudaSuccess) { sh->error.store(1); return fail(VRT_E_CUDA, cudaGetErrorString(e)); }
+    return VRT_OK;
+}
+
+// Rank 0: everything queued on `stream` (null: the communicator's stream) after this call runs once every rank's tiles of the latest
+// exchange on `slot` are in the device frame.
+extern "C" int vrt_comm_wait(vrt_context* c, int slot, void* stream) {
+    if (!c || !c->comm || !c->comm->devBase) return fail(VRT_E_INVALID, "no communicator / frames");
+    vrt_comm* m = c->comm; CommShm* sh = m->shm;
+    if (m->rank != 0) return fail(VRT_E_INVALID, "the frame is assembled on rank 0");
+    if (slot < 0 || slot >= sh->slots || m->gen[slot] == 0) return fail(VRT_E_INVALID, "nothing was exchanged on this slot");
+    CU(cudaSetDevice(c->device));
+    comm_wait_kernel<<<1, 32, 0, stream ? (cudaStream_t)stream : m->stream>>>((const uint32_t*)(m->devBase + sh->arriveOff) + slot * kMaxWorld, m->world, (uint32_t)m->gen[slot], m->devError);
+    CU(cudaGetLastError());
+    return VRT_OK;
+}
+
+// Rank 0: the HOST waits until every rank's tiles of the latest exchange on `slot` are in the shared host frame.
+extern "C" int vrt_comm_wait_host(vrt_context* c, int slot) {
+    if (!c || !c->comm || !c->comm->hostBase) return fail(VRT_E_INVALID, "no communicator / host frames");
+    vrt_comm* m = c->comm;
+    if (m->rank != 0) return fail(VRT_E_INVALID, "the frame is assembled on rank 0");
+    if (slot < 0 || slot >= m->shm->slots || m->gen[slot] == 0) return fail(VRT_E_INVALID, "nothing was exchanged on this slot");
+    struct Arg { int slot; uint32_t g; } a{slot, (uint32_t)m->gen[slot]};
+    return comm_spin(m, "the ranks' tiles in the host frame", [](vrt_comm* mm, const void* q) {
+        const Arg* x = (const Arg*)q;
+        for (int r = 0; r < mm->world; r++) if ((int32_t)(mm->shm->hostArrive[x->slot][r] - x->g) < 0) return false;
+        std::atomic_thread_fence(std::memory_order_acquire);
+        return true; }, &a);
+}
+
+// Rank 0: the consumer is done with what `slot` holds; the ranks may store the next frame into it. _on: when `stream` gets there.
+extern "C" int vrt_comm_release(vrt_context* c, int slot) {
+    if (!c || !c->comm || c->comm->rank != 0 || slot < 0 || slot >= kMaxSlots) return fail(VRT_E_INVALID, "bad argument");
+    c->comm->shm->released[slot].store(c->comm->gen[slot], std::memory_order_release);
+    return VRT_OK;
+}
+namespace { struct ReleaseNote { std::atomic<uint64_t>* word; uint64_t g; }; }
+extern "C" int vrt_comm_release_on(vrt_context* c, int slot, void* stream) {
+    if (!c || !c->comm || c->comm->rank != 0 || slot < 0 || slot >= kMaxSlots) return fail(VRT_E_INVALID, "bad argument");
+    vrt_comm* m = c->comm;
+    CU(cudaSetDevice(c->device));
+    ReleaseNote* n = new (std::nothrow) ReleaseNote{&m->shm->released[slot], m->gen[slot]};
+    if (!n) return fail(VRT_E_OOM, "host allocation failed");
+    CU(cudaLaunchHostFunc(stream ? (cudaStream_t)stream : m->stream, [](void* q) { ReleaseNote* x = (ReleaseNote*)q; x->word->store(x->g, std::memory_order_release); delete x; }, n));
+    return VRT_OK;
+}
+
+// The assembled plane of a slot as this process sees it: device pointer (rank 0: its memory; others: the peer mapping) and the
+// host pointer into the shared pinned frame (null if the plane has none).
+extern "C" int vrt_comm_frame_plane(vrt_context* c, int slot, int plane, void** d_ptr, void** h_ptr, size_t* bytes) {
+    if (!c || !c->comm || !c->comm->devBase) return fail(VRT_E_INVALID, "no communicator / frames");
+    vrt_comm* m = c->comm; CommShm* sh = m->shm;
+    if (slot < 0 || slot >= sh->slots || plane < 0 || plane >= VRT_PLANE_COUNT) return fail(VRT_E_INVALID, "bad slot / plane");
+    if (d_ptr) *d_ptr = (sh->planeMask >> plane & 1u) ? m->devBase + (uint64_t)slot * sh->slotStride + sh->planeOff[plane] : nullptr;
+    if (h_ptr) *h_ptr = (sh->hostPlaneMask >> plane & 1u) && m->hostBase ? m->hostBase + (uint64_t)slot * sh->hostSlotStride + sh->hostPlaneOff[plane] : nullptr;
+    if (bytes) *bytes = (size_t)sh->w * sh->h * kPlaneBpp[plane];
+    return VRT_OK;
+}
+
+// the context stream waits for everything queued on the communicator's stream so far (the end of a timed region on rank 0)
+int vrt_comm_join_into(vrt_context* c) {
+    vrt_comm* m = c->comm;
+    if (!m) return VRT_OK;
+    CU(cudaEventRecord(m->joined, m->stream));
+    CU(cudaStreamWaitEvent(c->stream, m->joined, 0));
+    return VRT_OK;
+}
+int vrt_comm_sync(vrt_context* c) {
+    vrt_comm* m = c->comm;
+    if (!m) return VRT_OK;
+    CU(cudaStreamSynchronize(m->stream));
+    uint32_t err = 0;
+    CU(cudaMemcpy(&err, m->devError, sizeof(err), cudaMemcpyDeviceToHost));
+    if (err) { m->shm->error.store(1); return fail(VRT_E_COMM, "a wait kernel gave up: a rank's tiles never arrived"); }
+    return VRT_OK;
+}

@@ -18,7 +18,7 @@ OUT_GBUFFER, OUT_INSTRUMENT = 1, 2
 TRAVERSAL_DEFAULT, TRAVERSAL_DENSE_U8, TRAVERSAL_BRICK, TRAVERSAL_FINE, TRAVERSAL_LINEAR, TRAVERSAL_OCTANT = 0, 1, 2, 3, 4, 5
 PIPELINE_DEFAULT, PIPELINE_MEGAKERNEL, PIPELINE_WAVEFRONT = 0, 1, 2
 DENOISE_AS_EXECUTED, DENOISE_AS_INTENDED = 0, 1
-E_LFS_POINTER, E_NO_INSTANCE, E_PARSE, E_IO, E_CUDA, E_NO_DEVICE = -2, -3, -4, -5, -6, -7
+E_LFS_POINTER, E_NO_INSTANCE, E_PARSE, E_IO, E_CUDA, E_NO_DEVICE, E_UNSUPPORTED, E_OOM, E_COMM = -2, -3, -4, -5, -6, -7, -8, -9, -10
 
 # plane id -> (name, dtype, channels)
 PLANES = {0: ("color", np.uint8, 4), 1: ("denoised", np.uint8, 4), 2: ("depth", np.float32, 1), 3: ("motion", np.float32, 2),
@@ -76,6 +76,7 @@ def lib():
         L.vrt_version.restype = C.c_char_p
         L.vrt_context_stream.restype = C.c_void_p
         L.vrt_frame_stream.restype = C.c_void_p
+        L.vrt_comm_stream.restype = C.c_void_p
         for fn in ("vrt_context_destroy", "vrt_scene_destroy", "vrt_frame_release", "vrt_host_free", "vrt_camera_vectors", "vrt_default_settings", "vrt_render_resolution"):
             getattr(L, fn).restype = None
         _lib = L
@@ -158,6 +159,44 @@ class Context:
     def join(self):
         """The context stream waits for everything queued on the frames' own streams so far."""
         _ck(lib().vrt_context_join(self.h))
+
+    # ---- multi-GPU exchange (vrt_comm_*): one process per GPU, frame assembled on rank 0 ----
+    def comm_create(self, rank, world, key: str):
+        _ck(lib().vrt_comm_create(self.h, int(rank), int(world), key.encode()))
+        self.rank, self.world = int(rank), int(world)
+
+    def comm_alloc_frames(self, size, slots, planes=("color",), host_planes=()):
+        pm = sum(1 << PLANE_ID[n] for n in planes); hm = sum(1 << PLANE_ID[n] for n in host_planes)
+        _ck(lib().vrt_comm_alloc_frames(self.h, int(size[0]), int(size[1]), int(slots), C.c_uint32(pm), C.c_uint32(hm)))
+
+    def comm_wait(self, slot, stream=None):
+        _ck(lib().vrt_comm_wait(self.h, int(slot), C.c_void_p(stream) if stream else None))
+
+    def comm_wait_host(self, slot):
+        _ck(lib().vrt_comm_wait_host(self.h, int(slot)))
+
+    def comm_release(self, slot, stream=None, on_stream=False):
+        if on_stream:
+            _ck(lib().vrt_comm_release_on(self.h, int(slot), C.c_void_p(stream) if stream else None))
+        else:
+            _ck(lib().vrt_comm_release(self.h, int(slot)))
+
+    def comm_barrier(self):
+        _ck(lib().vrt_comm_barrier(self.h))
+
+    @property
+    def comm_stream(self):
+        return lib().vrt_comm_stream(self.h)
+
+    def comm_frame_plane(self, slot, name):
+        """(device pointer, host numpy view or None, bytes) of an assembled plane of a slot as this process sees it."""
+        d, h, n = C.c_void_p(), C.c_void_p(), C.c_size_t()
+        _ck(lib().vrt_comm_frame_plane(self.h, int(slot), PLANE_ID[name], C.byref(d), C.byref(h), C.byref(n)))
+        host = np.ctypeslib.as_array(C.cast(h, C.POINTER(C.c_uint8)), shape=(n.value,)) if h.value else None
+        return d.value, host, n.value
+
+    def comm_destroy(self):
+        _ck(lib().vrt_comm_destroy(self.h))
 
     def close(self):
         if self.h:
@@ -261,6 +300,11 @@ class Frame:
     def push_tiles(self, name, d_frame_ptr, stream=None):
         """Store this rank's tiles of a plane into a row-major frame that may be peer memory (vrt_frame_push_tiles)."""
         _ck(lib().vrt_frame_push_tiles(self.h, PLANE_ID[name], C.c_void_p(d_frame_ptr), C.c_void_p(stream) if stream else None))
+
+    def exchange(self, slot, planes=("color",), host_planes=(), stream=None):
+        """This rank's tiles of the planes into rank 0's assembled frame `slot` (peer memory) and / or the shared host frame."""
+        pm = sum(1 << PLANE_ID[n] for n in planes); hm = sum(1 << PLANE_ID[n] for n in host_planes)
+        _ck(lib().vrt_frame_exchange(self.h, int(slot), C.c_uint32(pm), C.c_uint32(hm), C.c_void_p(stream) if stream else None))
 
     def download_async(self, name, out):
         """Queue the read-back behind this frame's kernels on the copy stream (out: pinned uint8 buffer); pair with download_wait()."""
@@ -368,6 +412,12 @@ class UpscalerStage:
         fc, x, y = C.c_int(self.frameCount), C.c_float(), C.c_float()
         _ck(lib().vrt_upscaler_update(self.render_width, self.target_width, C.byref(fc), C.byref(x), C.byref(y)))
         self.frameCount, self.jitterX, self.jitterY = fc.value, np.float32(x.value), np.float32(y.value)
+
+
+def denoise_device_on(ctx: Context, d_color, d_normal, d_position, size, ds: DenoiserSettings, d_out, d_scratch, stream=None):
+    """vrt_denoise_on: asynchronous, caller-owned scratch (rank 0 on the assembled planes of a sharded frame)."""
+    _ck(lib().vrt_denoise_on(ctx.h, C.c_void_p(d_color), C.c_void_p(d_normal), C.c_void_p(d_position), size[0], size[1], C.byref(ds),
+                             C.c_void_p(d_out), C.c_void_p(d_scratch), C.c_void_p(stream) if stream else None))
 
 
 def denoise_device(ctx: Context, d_color, d_normal, d_position, size, ds: DenoiserSettings, d_out):
