@@ -237,13 +237,19 @@ def cpu_baseline_and_parity(cfg, name, whd, size, target_s, gpu_frame0):
     return base, par
 
 
-def config_blob(cfg, name, whd, size, world):
+def config_blob(cfg, name, whd, size, world, bounds):
     """Identical in both arms (the driver compares the two `config` objects)."""
     kind, what, kw = cfg["scene"]
+    vol_mib = bounds[0] * bounds[1] * bounds[2] / 2 ** 20
+    fld_mib = 8 * (bounds[0] + 2) * (bounds[1] + 2) * (bounds[2] + 2) / 2 ** 20
+    big = vol_mib + fld_mib > 126
+    l2 = (f"inputs {'larger' if big else 'SMALLER'} than the 126 MB L2: volume {vol_mib:.0f} MiB + 8 directional safe-step fields {fld_mib:.0f} MiB"
+          + ("" if big else f"; the scene is L2-resident by construction, the {size[0] * size[1] * 37 / 2 ** 20:.0f} MiB of frame planes written per step are not")
+          + "; camera pose and noise frame index change every step")
     return {"workload": f"{name}: {cfg['label']}", "volume": list(whd) if whd else list(kw.get("whd", [])) or what,
             "resolution": list(size), "pass_mask": cfg["passes"], "aoSamples": cfg["ao"], "denoiser": bool(cfg["denoise"]),
             "parallelism": f"tiles{world}" if world > 1 else "single",
-            "l2": "inputs larger than L2 (1 GiB volume + 8 GiB of directional safe-step fields vs 126 MB); camera pose and noise frame index change every step"}
+            "l2": l2}
 
 
 # ----------------------------------------------------------------------------------------------- reference arm
@@ -272,7 +278,7 @@ def run_reference(args):
     sample = f"every {step}th row of each frame ({len(range(0, size[1], step))} of {size[1]} rows per step), {t:.1f} s total"
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": config_blob(cfg, args.config, args.whd, size, args.gpus),
+            "config": config_blob(cfg, args.config, args.whd, size, args.gpus, bounds),
             "note": "the reference has no CPU implementation and its Vulkan path is unavailable on this box; this is the CPU restatement of "
                     "shader/voxel_volume.frag (oracle port), OpenMP over rows, on all host cores whatever --gpus says",
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
@@ -339,6 +345,7 @@ def run_vrt(args):
         if rank == 0 and denoise:
             dn_out = [torch.empty(frame_bytes, dtype=torch.uint8, device=dev) for _ in range(F)]
             dn_scratch = torch.empty(frame_bytes, dtype=torch.uint8, device=dev)
+        if rank == 0:
             cstream = torch.cuda.ExternalStream(ctx.comm_stream, device=dev)
     if rank == 0 and (world == 1 or denoise):
         host2 = [torch.empty(frame_bytes, dtype=torch.uint8, pin_memory=True) for _ in range(F)]
@@ -369,7 +376,7 @@ def run_vrt(args):
                     with torch.cuda.stream(cstream):
                         host2[slot].copy_(dn_out[slot], non_blocking=True)
             if readback:
-                ev_done[slot].record(torch.cuda.ExternalStream(ctx.comm_stream, device=dev))
+                ev_done[slot].record(cstream)
                 pending[slot] = True                         # released by wait_readback once the host has the frame
             else:
                 ctx.comm_release(slot, on_stream=True)       # the ranks may overwrite the slot once the consumer got there
@@ -524,7 +531,7 @@ def run_vrt(args):
         issue_ach = float(stage_fetches[dom]) / args.steps * STEP_INSTRUCTIONS / (dom_ms * 1e-3)
         line = {"metric": METRIC, "value": rays_all / (ms * 1e-3) / 1e6, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": config_blob(cfg, args.config, args.whd, size, world),
+                "config": config_blob(cfg, args.config, args.whd, size, world, bounds),
                 "run": {"traversal": args.traversal, "pipeline": args.pipeline, "frames_in_flight": F, "frame_streams": "one" if args.serial_frames else "per frame",
                         "timed_regions": len(region_ms), "timed_ms_total": float(np.sum(region_ms)), "region_ms_min_median_max": [float(np.min(region_ms)), ms, float(np.max(region_ms))],
                         "exchange": ("libvrt vrt_frame_exchange: every rank stores its tiles of " + "+".join(xplanes) + " into rank 0's frame (CUDA IPC peer memory over NVLink) "

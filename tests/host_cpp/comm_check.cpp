@@ -121,7 +121,7 @@ int main(int argc, char** argv) {
     std::vector<pid_t> kids;
     for (int r = 0; r < world; r++) {                        // fork BEFORE any CUDA call: a CUDA context does not survive fork
         const pid_t p = fork();
-        if (p == 0) _exit(run_rank(r, world, W, H, ndev, frames, key));
+        if (p == 0) { const int rc = run_rank(r, world, W, H, ndev, frames, key); fflush(nullptr); _exit(rc); }
         kids.push_back(p);
     }
     int worst = 0;

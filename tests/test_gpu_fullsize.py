@@ -139,7 +139,7 @@ def test_cfg5_sparse_2048_orbit_8k_sampled_rows_world1_and_world8(gpu_ctx):
         assert np.abs(got["color"].astype(int) - want["color"].astype(int)).max() <= 1
         same = (got["color_f32"].view(np.uint32) == want["color_f32"].view(np.uint32)) | (np.isnan(got["color_f32"]) & np.isnan(want["color_f32"]))
         assert 1.0 - same.all(axis=-1).mean() <= 1e-4
-        assert want["hit"][..., :3].max() > 1500 and (want["hit_palette"] != 0).mean() > 0.03
+        assert want["hit"][..., :3].max() > 1200 and (want["hit_palette"] != 0).mean() > 0.03
         # ---- world = 8: the eight shards of an 8-GPU run, one after another, assembled by direct tile stores (vrt_frame_push_tiles)
         planes = ("color", "depth", "normal", "hit", "hit_palette", "position")
         bpp = {"color": 4, "depth": 4, "normal": 4, "hit": 8, "hit_palette": 1, "position": 16}

@@ -1,6 +1,6 @@
 """Summarise an .ncu-rep for profiles/: per kernel launch the counters BASELINE.json asks for (L2 hit rate, achieved L2 / HBM GB/s,
 warp execution efficiency, issue-slot utilisation) plus occupancy, stall reasons and DRAM traffic.
-usage: ncu_summary.py file.ncu-rep [--json traffic.json]"""
+usage: ncu_summary.py file.ncu-rep [--json traffic.json [--config cfg4] [--source "text"]]"""
 import csv, json, subprocess, sys
 
 out = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "raw", "--csv"], capture_output=True, text=True).stdout
@@ -56,9 +56,15 @@ for r in rows[2:]:
     print("   " + "  ".join(f"{k}={v:.4g}" if isinstance(v, float) else f"{k}={v}" for k, v in d.items()))
 if "--json" in sys.argv:
     # per-launch DRAM traffic of each kernel (mean over the captured launches; reflection waves: the first = largest wave)
-    tr = {}
+    cfgname = sys.argv[sys.argv.index("--config") + 1] if "--config" in sys.argv else "cfg4"
+    jpath = sys.argv[sys.argv.index("--json") + 1]
+    try:
+        tr = json.load(open(jpath))
+    except Exception:
+        tr = {}
+    tr["source"] = sys.argv[sys.argv.index("--source") + 1] if "--source" in sys.argv else "ncu --set full capture: " + sys.argv[1]
     for name, ds in per.items():
         key = name.split("<")[0]
         big = ds if "bounce" not in key else ds[:1]
-        tr[key + "_dram_bytes_per_launch"] = sum((d["dram_read_bytes"] or 0) + (d["dram_write_bytes"] or 0) for d in big) / len(big)
-    json.dump(tr, open(sys.argv[sys.argv.index("--json") + 1], "w"), indent=1)
+        tr[cfgname + ":" + key + "_dram_bytes_per_launch"] = sum((d["dram_read_bytes"] or 0) + (d["dram_write_bytes"] or 0) for d in big) / len(big)
+    json.dump(tr, open(jpath, "w"), indent=1)
