@@ -160,6 +160,12 @@ int vrt_scene_from_dense(vrt_context*, const uint8_t* volume, uint32_t w, uint32
 int vrt_scene_generate(vrt_context*, int generator, uint64_t seed, uint32_t w, uint32_t h, uint32_t d, vrt_scene** out);
 int vrt_scene_set_noise(vrt_scene*, const uint8_t* rgba8, uint32_t w, uint32_t h);      /* must be 512x512 */
 int vrt_scene_set_skybox(vrt_scene*, const float* rgba32f, uint32_t w, uint32_t h);
+/* The reference's file inputs (VoxelScene(engine, voxPath, skyboxFilename): voxel_scene.cpp:33,132; VoxelRenderer's noise texture:
+ * voxel_renderer.cpp:22; both through Texture2D = stbi_loadf / stbi_load with 4 channels, texture_2d.cpp:22-38):
+ * skybox = Radiance RGBE .hdr -> RGBA32F (flat and run-length scanlines), noise = PNG -> RGBA8 (must be 512 x 512).
+ * VRT_E_LFS_POINTER when the file is a git-LFS pointer stub, VRT_E_IO / VRT_E_PARSE like "Could not load image". */
+int vrt_scene_load_skybox(vrt_scene*, const char* hdr_path);
+int vrt_scene_load_noise(vrt_scene*, const char* png_path);
 int vrt_scene_bounds(const vrt_scene*, uint32_t whd[3]);
 int vrt_scene_palette(const vrt_scene*, vrt_material palette[256]);
 int vrt_scene_download_volume(const vrt_scene*, uint8_t* dst, size_t bytes);
@@ -255,6 +261,18 @@ int vrt_blit_on(vrt_context*, const void* d_src_rgba8, int sw, int sh, void* d_d
 /* image files for the headless path (host memory in, RGBA8 row-major): binary PPM (rgb), PNG rgb (tagged sRGB) or PNG rgba */
 enum { VRT_IMAGE_PPM = 0, VRT_IMAGE_PNG_RGB = 1, VRT_IMAGE_PNG_RGBA = 2 };
 int vrt_image_write(const char* path, const void* rgba8, int w, int h, int format);
+
+/* image decoders behind vrt_scene_load_skybox / vrt_scene_load_noise (host only; *out is malloc'ed, free with vrt_host_free) */
+int vrt_image_read_hdr(const char* path, float** rgba32f_out, uint32_t* w, uint32_t* h);
+int vrt_image_decode_hdr(const uint8_t* bytes, size_t n, float** rgba32f_out, uint32_t* w, uint32_t* h);
+int vrt_image_read_png(const char* path, uint8_t** rgba8_out, uint32_t* w, uint32_t* h);
+int vrt_image_decode_png(const uint8_t* bytes, size_t n, uint8_t** rgba8_out, uint32_t* w, uint32_t* h);
+/* Every bundled asset of the reference checkout is a git-LFS pointer stub. These decide whether a file that has been
+ * supplied IS the asset a stub names: sha256 and size must equal the pointer's oid and size. VRT_OK = use it instead of the stand-in. */
+int vrt_sha256(const void* data, size_t n, char hex[65]);
+int vrt_file_sha256(const char* path, char hex[65]);
+int vrt_lfs_pointer_info(const char* path, char oid_hex[65], uint64_t* size);   /* VRT_E_INVALID if `path` is not a pointer file */
+int vrt_asset_matches_pointer(const char* candidate_path, const char* pointer_path);
 
 /* ---- frame driver (the caller of the pass): jitter sequence and frame counter of UpscalerStage::update ----
  * Pure host functions, usable without a GPU. vrt_upscaler_update: jitter of this frame from *frameCount, then advances it the way the

@@ -106,9 +106,17 @@ private:
 class VoxelScene {
 public:
     uint32_t width = 0, height = 0, depth = 0;
-    // VoxelScene(engine, filename, skyboxFilename): the skybox/noise decoders (stb) are outside the path; pass pixels.
-    VoxelScene(const std::shared_ptr<Engine>& engine, const std::string& filename) : _engine(engine) {
+    // VoxelScene(engine, filename, skyboxFilename), voxel_scene.cpp:33: the .vox file and the Radiance .hdr skybox (stbi_loadf in the
+    // reference, voxel_scene.cpp:132 -> texture_2d.cpp:31-38). A git-LFS pointer stub in either place throws (VRT_E_LFS_POINTER).
+    VoxelScene(const std::shared_ptr<Engine>& engine, const std::string& filename, const std::string& skyboxFilename) : _engine(engine) {
         check(vrt_scene_load_vox(engine->handle(), filename.c_str(), &_scene), "VoxelScene");   // messages of voxel_scene.cpp:42,46,50
+        bounds();
+        const int rc = vrt_scene_load_skybox(_scene, skyboxFilename.c_str());
+        if (rc != VRT_OK) { destroy(); check(rc, "VoxelScene skybox"); }
+    }
+    // without a skybox file: pixels are passed with setSkybox (stand-ins, tests)
+    VoxelScene(const std::shared_ptr<Engine>& engine, const std::string& filename) : _engine(engine) {
+        check(vrt_scene_load_vox(engine->handle(), filename.c_str(), &_scene), "VoxelScene");
         bounds();
     }
     VoxelScene(const std::shared_ptr<Engine>& engine, const uint8_t* dense, uint32_t w, uint32_t h, uint32_t d, const vrt_material palette[256])
@@ -125,6 +133,7 @@ public:
     VoxelScene& operator=(const VoxelScene&) = delete;
     void destroy() { if (_scene) { vrt_scene_destroy(_scene); _scene = nullptr; } }   // == AResource::destroy()
     void setNoise(const uint8_t* rgba8, uint32_t w, uint32_t h) { check(vrt_scene_set_noise(_scene, rgba8, w, h), "setNoise"); }
+    void loadNoise(const std::string& pngPath) { check(vrt_scene_load_noise(_scene, pngPath.c_str()), "noise texture"); }   // voxel_renderer.cpp:22
     void setSkybox(const float* rgba32f, uint32_t w, uint32_t h) { check(vrt_scene_set_skybox(_scene, rgba32f, w, h), "setSkybox"); }
     vrt_scene* handle() const { return _scene; }
     const std::shared_ptr<Engine>& engine() const { return _engine; }

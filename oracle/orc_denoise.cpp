@@ -81,19 +81,31 @@ extern "C" int orc_denoise(const uint8_t* color_in, const int8_t* normal, const 
                 vec4 sampleColor = ldc(px, py), sampleNormal = ldn(px, py), samplePos = ldp(px, py);
                 float totalWeight = 0.0f;
                 for (int i = 0; i < 25; i++) {
-                    // uv = vScreenPos + offset*step*stepWidth sampled LINEAR/CLAMP (render_image.cpp:60-66):
-                    // pinned to the texel containing the sample point (exact texel centre for integral stepWidth).
-                    int tx = clampi(px + f2i(floorf(0.5f + taps.offset[i].x * stepWidth)), 0, w - 1);
-                    int ty = clampi(py + f2i(floorf(0.5f + taps.offset[i].y * stepWidth)), 0, h - 1);
-                    vec4 offsetColor = ldc(tx, ty);
+                    // uv = vScreenPos + offset*step*stepWidth sampled LINEAR / CLAMP_TO_EDGE (render_image.cpp:60-66). In texel space the
+                    // sample point is px + offset*stepWidth (+0.5 for the pixel centre, -0.5 for the texel centre): on a texel centre when
+                    // offset*stepWidth is integral (the filter then returns that texel), between four texels otherwise (stepWidth is a
+                    // float slider in the reference GUI, voxel_settings_gui.cpp:106). Pinned: the texel-space coordinate is evaluated as
+                    // float(px) + offset*stepWidth in binary32; weights per the Vulkan texel-filtering equations in binary32, products
+                    // first, sums left to right (as in orc_blit); all three inputs are filtered the same way, after their UNORM / SNORM decode.
+                    const float ux = (float)px + taps.offset[i].x * stepWidth, uy = (float)py + taps.offset[i].y * stepWidth;
+                    const float fi = floorf(ux), fj = floorf(uy);
+                    const float a = ux - fi, b = uy - fj;
+                    const int i0 = clampi(f2i(fi), 0, w - 1), i1 = clampi(f2i(fi) + 1, 0, w - 1);
+                    const int j0 = clampi(f2i(fj), 0, h - 1), j1 = clampi(f2i(fj) + 1, 0, h - 1);
+                    const bool onTexel = a == 0.0f && b == 0.0f;
+                    const float w00 = (1.0f - a) * (1.0f - b), w10 = a * (1.0f - b), w01 = (1.0f - a) * b, w11 = a * b;
+                    auto mix4 = [&](const vec4& t00, const vec4& t10, const vec4& t01, const vec4& t11) {
+                        return vec4{((w00 * t00.x + w10 * t10.x) + w01 * t01.x) + w11 * t11.x, ((w00 * t00.y + w10 * t10.y) + w01 * t01.y) + w11 * t11.y,
+                                    ((w00 * t00.z + w10 * t10.z) + w01 * t01.z) + w11 * t11.z, ((w00 * t00.w + w10 * t10.w) + w01 * t01.w) + w11 * t11.w}; };
+                    vec4 offsetColor = onTexel ? ldc(i0, j0) : mix4(ldc(i0, j0), ldc(i1, j0), ldc(i0, j1), ldc(i1, j1));
                     vec4 t = sampleColor - offsetColor;
                     float dist2 = dot(t, t);
                     float colorWeight = gmin(expf(-(dist2) / phiColor), 1.0f);
-                    vec4 offsetNormal = ldn(tx, ty);
+                    vec4 offsetNormal = onTexel ? ldn(i0, j0) : mix4(ldn(i0, j0), ldn(i1, j0), ldn(i0, j1), ldn(i1, j1));
                     t = sampleNormal - offsetNormal;
                     dist2 = gmax(dot(t, t) / (stepWidth * stepWidth), 0.0f);
                     float normalWeight = gmin(expf(-(dist2) / phiNormal), 1.0f);
-                    vec4 offsetPos = ldp(tx, ty);
+                    vec4 offsetPos = onTexel ? ldp(i0, j0) : mix4(ldp(i0, j0), ldp(i1, j0), ldp(i0, j1), ldp(i1, j1));
                     t = samplePos - offsetPos;
                     dist2 = dot(t, t);
                     float posWeight = gmin(expf(-(dist2) / phiPos), 1.0f);

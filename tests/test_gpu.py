@@ -514,3 +514,27 @@ def test_degenerate_rotation_takes_the_ordered_host_flatten(gpu_ctx):
     gs = pyvrt.VoxelScene.from_vox_bytes(gpu_ctx, data)
     assert np.array_equal(gs.download_volume(), vol) and np.array_equal(gs.palette(), pal)
     gs.destroy()
+
+
+@pytest.mark.parametrize("step_width", [1.5, 0.7, 2.25])
+def test_standalone_denoise_fractional_step_width(gpu_ctx, step_width):
+    """Non-integral stepWidth (a float slider in the reference GUI): the taps fall between texels and the LINEAR sampler of the
+    reference blends four of them (render_image.cpp:60-66). Kernel vs oracle, both modes, within 1/255 (expf is not shared)."""
+    import torch
+    rng = np.random.default_rng(17)
+    h, w = 271, 483
+    color = rng.integers(0, 256, (h, w, 4), dtype=np.uint8); color[..., 3] = 0
+    normal = np.zeros((h, w, 4), np.int8); normal[..., :3] = rng.choice([-127, 0, 127], (h, w, 3))
+    pos = (rng.random((h, w, 4), dtype=np.float32) * 3); pos[..., 3] = 0
+    tc, tn, tp = torch.from_numpy(color).cuda(), torch.from_numpy(normal).cuda(), torch.from_numpy(pos).cuda()
+    for mode in (0, 1):
+        for iters in (2, 3):
+            ds = pyvrt.DenoiserSettings(1, iters, 20.4, 1e-2, 1e-1, step_width, mode)
+            out = torch.empty_like(tc)
+            torch.cuda.synchronize()
+            pyvrt.denoise_device(gpu_ctx, tc.data_ptr(), tn.data_ptr(), tp.data_ptr(), (w, h), ds, out.data_ptr())
+            gpu_ctx.sync()
+            want = O.denoise(color, normal, pos, iterations=iters, step_width=step_width, mode=mode)
+            d = np.abs(out.cpu().numpy().astype(int) - want.astype(int))
+            assert d.max() <= 1 and (d != 0).mean() < 2e-3, (mode, iters, d.max(), (d != 0).mean())
+    assert not np.array_equal(want, O.denoise(color, normal, pos, iterations=3, step_width=float(round(step_width)) or 1.0, mode=1))

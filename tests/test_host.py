@@ -315,3 +315,106 @@ def test_vox_decode_survives_crafted_files(tmp_path):
 def test_vox_decode_survives_mutation_fuzz():
     out = _run_child(["fuzz", GOLD, "1234", "2000"])
     assert "fuzz 2000" in out
+
+
+# ---- file inputs of the operator surface: Radiance .hdr skybox, PNG noise texture, LFS pointers (host code, no GPU) ----
+def _rgbe_encode(img):
+    """float32 [h, w, 3] -> RGBE bytes [h, w, 4] (the standard frexp encoding)."""
+    m = img.max(axis=-1)
+    e = np.zeros(m.shape, np.int32); mant = np.zeros(m.shape)
+    nz = m > 1e-32
+    mant[nz], e[nz] = np.frexp(m[nz])
+    scale = np.where(nz, mant * 256.0 / np.where(nz, m, 1), 0)
+    out = np.zeros(img.shape[:2] + (4,), np.uint8)
+    out[..., :3] = np.clip(img * scale[..., None], 0, 255).astype(np.uint8)
+    out[..., 3] = np.where(nz, e + 128, 0)
+    return out
+
+
+def _rgbe_decode(rgbe):
+    f = np.ldexp(np.float32(1.0), rgbe[..., 3].astype(np.int32) - 136).astype(np.float32)
+    out = np.ones(rgbe.shape[:2] + (4,), np.float32)
+    out[..., :3] = rgbe[..., :3].astype(np.float32) * f[..., None]
+    out[..., :3][rgbe[..., 3] == 0] = 0
+    return out
+
+
+def test_hdr_reader_flat_and_rle_scanlines(tmp_path):
+    import cv2
+    rng = np.random.default_rng(3)
+    img = (rng.random((37, 64, 3)) ** 4 * 50).astype(np.float32); img[5, 7] = 0; img[0, :20] = img[0, 0]   # a run for the RLE coder
+    rgbe = _rgbe_encode(img)
+    want = _rgbe_decode(rgbe)
+    # flat scanlines, written by hand
+    head = b"#?RADIANCE\nFORMAT=32-bit_rle_rgbe\n\n-Y 37 +X 64\n"
+    got = pyvrt.read_hdr(head + rgbe.tobytes())
+    assert got.shape == (37, 64, 4) and np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    # run-length scanlines: OpenCV's writer; OpenCV's own reader as the second opinion (BGR, no alpha)
+    p = str(tmp_path / "sky.hdr")
+    assert cv2.imwrite(p, want[..., 2::-1].copy())
+    data = open(p, "rb").read()
+    assert b"\x02\x02\x00\x40" in data                              # new-style RLE scanline marker for width 64
+    got = pyvrt.read_hdr(p)
+    ref = cv2.imread(p, cv2.IMREAD_UNCHANGED)
+    assert np.array_equal(got[..., :3].view(np.uint32), ref[..., ::-1].copy().view(np.uint32)) and (got[..., 3] == 1).all()
+    assert np.abs(got[..., :3] - want[..., :3]).max() <= np.abs(want[..., :3]).max() / 128
+    # narrow images are always flat (stb: width < 8)
+    small = _rgbe_encode(img[:3, :5])
+    assert np.array_equal(pyvrt.read_hdr(b"#?RGBE\nFORMAT=32-bit_rle_rgbe\n\n-Y 3 +X 5\n" + small.tobytes()), _rgbe_decode(small))
+    for bad_bytes, code in ((b"#?RADIANCE\nFORMAT=32-bit_rle_xyze\n\n-Y 1 +X 1\n\0\0\0\0", pyvrt.E_PARSE), (b"not an hdr", pyvrt.E_PARSE),
+                            (head + rgbe.tobytes()[:100], pyvrt.E_PARSE), (b"version https://git-lfs.github.com/spec/v1\noid sha256:" + b"e" * 64 + b"\nsize 4047254\n", pyvrt.E_LFS_POINTER)):
+        with pytest.raises(pyvrt.VrtError) as e:
+            pyvrt.read_hdr(bad_bytes)
+        assert e.value.code == code
+    with pytest.raises(pyvrt.VrtError) as e:
+        pyvrt.read_hdr("/nonexistent/sky.hdr")
+    assert e.value.code == pyvrt.E_IO and "Could not load image" in str(e.value)
+
+
+def test_png_reader_matches_pil(tmp_path):
+    from PIL import Image
+    rng = np.random.default_rng(4)
+    rgba = rng.integers(0, 256, (61, 47, 4), dtype=np.uint8)
+    cases = {"rgba": Image.fromarray(rgba, "RGBA"), "rgb": Image.fromarray(rgba[..., :3].copy(), "RGB"), "grey": Image.fromarray(rgba[..., 0].copy(), "L"),
+             "greya": Image.fromarray(rgba[..., :2].copy(), "LA"), "pal": Image.fromarray(rgba[..., :3].copy(), "RGB").quantize(37), "bit1": Image.fromarray(rgba[..., 0] > 127)}
+    for name, im in cases.items():
+        p = str(tmp_path / f"{name}.png")
+        im.save(p, optimize=(name == "rgb"))
+        want = np.asarray(Image.open(p).convert("RGBA"))
+        got = pyvrt.read_png(p)
+        assert got.shape == want.shape and np.array_equal(got, want), name
+    g16 = rng.integers(0, 65536, (9, 13), dtype=np.uint16)          # 16-bit: stb keeps the high byte
+    p = str(tmp_path / "g16.png"); Image.fromarray(g16).save(p)
+    got = pyvrt.read_png(p)
+    assert np.array_equal(got[..., 0], (g16 >> 8).astype(np.uint8)) and (got[..., 3] == 255).all()
+    big = rng.integers(0, 256, (512, 512, 4), dtype=np.uint8)          # the noise texture's size
+    p = str(tmp_path / "noise.png"); Image.fromarray(big, "RGBA").save(p)
+    assert np.array_equal(pyvrt.read_png(open(p, "rb").read()), big)
+    for bad_bytes, code in ((b"\x89PNG\r\n\x1a\n" + b"\0" * 20, pyvrt.E_PARSE), (b"GIF89a", pyvrt.E_PARSE),
+                            (b"version https://git-lfs.github.com/spec/v1\noid sha256:" + b"7" * 64 + b"\nsize 1049488\n", pyvrt.E_LFS_POINTER)):
+        with pytest.raises(pyvrt.VrtError) as e:
+            pyvrt.read_png(bad_bytes)
+        assert e.value.code == code
+
+
+def test_sha256_and_lfs_pointer_resolution(tmp_path):
+    """a supplied file replaces a stand-in only if its sha256 and size are those of the reference's LFS pointer."""
+    import hashlib
+    rng = np.random.default_rng(8)
+    for n in (0, 1, 55, 56, 63, 64, 65, 100000):
+        data = rng.integers(0, 256, n, dtype=np.uint8).tobytes()
+        p = str(tmp_path / f"blob{n}"); open(p, "wb").write(data)
+        assert pyvrt.file_sha256(p) == hashlib.sha256(data).hexdigest()
+    real = str(tmp_path / "blob100000")
+    oid = pyvrt.file_sha256(real)
+    ptr = str(tmp_path / "asset.ptr")
+    open(ptr, "w").write(f"version https://git-lfs.github.com/spec/v1\noid sha256:{oid}\nsize 100000\n")
+    assert pyvrt.lfs_pointer_info(ptr) == (oid, 100000) and pyvrt.lfs_pointer_info(real) is None
+    assert pyvrt.asset_matches_pointer(real, ptr)
+    assert not pyvrt.asset_matches_pointer(str(tmp_path / "blob65"), ptr) and not pyvrt.asset_matches_pointer(ptr, ptr)
+    ref = "/root/reference/resource/rustig_koppie.hdr"
+    if os.path.exists(ref):                                             # the reference's own stub: named in BASELINE.md section 2
+        assert pyvrt.lfs_pointer_info(ref) == ("e70bf97a44982db07fb952b1f74c07e818649c2bbdfeb6ad4f98af7b4431a38f", 4047254)
+        with pytest.raises(pyvrt.VrtError) as e:
+            pyvrt.read_hdr(ref)
+        assert e.value.code == pyvrt.E_LFS_POINTER

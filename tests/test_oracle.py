@@ -316,3 +316,59 @@ def test_iteration0_is_a_plain_blur_whatever_the_gbuffer_holds():
     for mode in (0, 1):
         got = O.denoise(color, normal, pos, iterations=1, mode=mode)
         assert np.array_equal(got, blind_blur(color, mode)), mode
+
+
+def test_denoiser_fractional_step_width_samples_between_texels():
+    """stepWidth is a float slider in the reference GUI (voxel_settings_gui.cpp:106) and the denoiser's inputs go through a LINEAR /
+    CLAMP_TO_EDGE sampler (render_image.cpp:60-66): for a non-integral offset*stepWidth the taps blend four texels. An independent
+    numpy statement of the same equations (AS_INTENDED, 2 iterations, stepWidth0 = 1.5 -> tap distance 2.5 in iteration 1)."""
+    f32 = np.float32
+    rng = np.random.default_rng(5)
+    h, w = 37, 53
+    color = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+    normal = rng.integers(-127, 128, (h, w, 4)).astype(np.int8)
+    pos = (rng.random((h, w, 4), dtype=f32) * 4).astype(f32)
+    got = O.denoise(color, normal, pos, iterations=2, step_width=1.5, mode=1)
+    assert not np.array_equal(got, O.denoise(color, normal, pos, iterations=2, step_width=2.0, mode=1))
+
+    import ctypes as C
+    libm = C.CDLL("libm.so.6"); libm.expf.restype = C.c_float; libm.expf.argtypes = [C.c_float]
+    expf = np.vectorize(lambda v: f32(libm.expf(float(v))), otypes=[f32])
+    ys, xs = np.mgrid[0:h, 0:w]
+
+    def sample(img, ox, oy):
+        ux, uy = (xs.astype(f32) + f32(ox)).astype(f32), (ys.astype(f32) + f32(oy)).astype(f32)
+        fi, fj = np.floor(ux), np.floor(uy)
+        a, b = (ux - fi).astype(f32)[..., None], (uy - fj).astype(f32)[..., None]
+        i0, i1 = np.clip(fi.astype(int), 0, w - 1), np.clip(fi.astype(int) + 1, 0, w - 1)
+        j0, j1 = np.clip(fj.astype(int), 0, h - 1), np.clip(fj.astype(int) + 1, 0, h - 1)
+        one = f32(1)
+        w00, w10, w01, w11 = (one - a) * (one - b), a * (one - b), (one - a) * b, a * b
+        mix = (((w00 * img[j0, i0] + w10 * img[j0, i1]).astype(f32) + w01 * img[j1, i0]).astype(f32) + w11 * img[j1, i1]).astype(f32)
+        return np.where((a == 0) & (b == 0), img[j0, i0], mix)
+
+    def dot4(t):
+        return (((t[..., 0] * t[..., 0] + t[..., 1] * t[..., 1]).astype(f32) + t[..., 2] * t[..., 2]).astype(f32) + t[..., 3] * t[..., 3]).astype(f32)
+
+    n = np.maximum(normal.astype(f32) / f32(127), f32(-1)).astype(f32)
+    src = color
+    for it in range(2):
+        with np.errstate(divide="ignore", invalid="ignore"):
+            phi = [f32(f32(1) / f32(it)) * f32(v) for v in (20.4, 1e-2, 1e-1)]
+        sw = f32(f32(it) * f32(1.5) + f32(1))
+        c = (src.astype(f32) / f32(255)).astype(f32)
+        acc = np.zeros((h, w, 4), f32); tot = np.zeros((h, w), f32)
+        for oy in (-1, 0, 1):
+            for ox in (-1, 0, 1):
+                k = f32(libm.expf(float(f32(-(f32(ox * ox) / f32(8) + f32(oy * oy) / f32(8))))))
+                oc, on, op = sample(c, f32(ox) * sw, f32(oy) * sw), sample(n, f32(ox) * sw, f32(oy) * sw), sample(pos, f32(ox) * sw, f32(oy) * sw)
+                with np.errstate(divide="ignore", invalid="ignore", over="ignore"):
+                    cw = np.fmin(expf(-dot4(c - oc) / phi[0]), f32(1))
+                    nw = np.fmin(expf(-np.fmax(dot4(n - on) / f32(sw * sw), f32(0)) / phi[1]), f32(1))
+                    pw = np.fmin(expf(-dot4(pos - op) / phi[2]), f32(1))
+                wgt = ((cw * nw).astype(f32) * pw).astype(f32)
+                acc = (acc + ((oc * wgt[..., None]).astype(f32) * k).astype(f32)).astype(f32)
+                tot = (tot + (wgt * k).astype(f32)).astype(f32)
+        v = (acc / tot[..., None]).astype(f32)
+        src = np.rint(np.clip(np.nan_to_num(v, nan=0.0), 0, 1).astype(f32) * f32(255)).astype(np.uint8)
+    assert np.array_equal(src, got)

@@ -29,7 +29,29 @@ __device__ __forceinline__ float dot4d(float4 a, float4 b) {   // t = a - b; dot
 // NaN for x = inf / NaN, exp gives 1 or NaN, and min(NaN, 1) = 1 — so the iteration is a plain weighted blur of the colour plane:
 // normals and positions are not read, no exp, no division (the IEEE divisions by inf all took the slow path). The sums are the same
 // float operations in the same order ((c * 1) * k == c * k, 1 * k == k), so the bytes are those of the general kernel.
-template <bool BLIND>
+// LINEAR: some tap offset*stepWidth of this iteration is not integral (stepWidth is a float slider in the reference GUI,
+// voxel_settings_gui.cpp:106): the inputs are then sampled between four texels, as the reference's LINEAR / CLAMP_TO_EDGE sampler does
+// (render_image.cpp:60-66). Texel-space coordinate float(px) + offset*stepWidth, weights per the Vulkan texel-filtering equations in
+// binary32, products first, sums left to right: the same float operations as oracle/orc_denoise.cpp. Integral offsets keep the
+// one-texel path (the filter returns the texel itself there).
+struct Bilin { int i0, i1, j0, j1; float w00, w10, w01, w11; bool onTexel; };
+__device__ __forceinline__ Bilin bilin_setup(int px, int py, float ox, float oy, int W, int H) {
+    Bilin q;
+    const float ux = (float)px + ox, uy = (float)py + oy;
+    const float fi = floorf(ux), fj = floorf(uy);
+    const float a = ux - fi, b = uy - fj;
+    q.i0 = min(max(f2i(fi), 0), W - 1); q.i1 = min(max(f2i(fi) + 1, 0), W - 1);
+    q.j0 = min(max(f2i(fj), 0), H - 1); q.j1 = min(max(f2i(fj) + 1, 0), H - 1);
+    q.onTexel = a == 0.0f && b == 0.0f;
+    q.w00 = (1.0f - a) * (1.0f - b); q.w10 = a * (1.0f - b); q.w01 = (1.0f - a) * b; q.w11 = a * b;
+    return q;
+}
+__device__ __forceinline__ float4 bilin_mix(const Bilin& q, float4 t00, float4 t10, float4 t01, float4 t11) {
+    return make_float4(((q.w00 * t00.x + q.w10 * t10.x) + q.w01 * t01.x) + q.w11 * t11.x, ((q.w00 * t00.y + q.w10 * t10.y) + q.w01 * t01.y) + q.w11 * t11.y,
+                       ((q.w00 * t00.z + q.w10 * t10.z) + q.w01 * t01.z) + q.w11 * t11.z, ((q.w00 * t00.w + q.w10 * t10.w) + q.w01 * t01.w) + q.w11 * t11.w);
+}
+
+template <bool BLIND, bool LINEAR>
 __global__ void __launch_bounds__(256) denoise_kernel(const uint8_t* __restrict__ color, const int8_t* __restrict__ normal,
                                                       const float* __restrict__ position, uint8_t* __restrict__ out, int W, int H,
                                                       const DenoiseTaps taps, const DenoiseIter it) {
@@ -58,13 +80,25 @@ __global__ void __launch_bounds__(256) denoise_kernel(const uint8_t* __restrict_
         for (int i = 0; i < taps.n; i++) {
             // uv = vScreenPos + offset*step*stepWidth under LINEAR/CLAMP = the texel holding the sample point; the texel offsets
             // floor(0.5 + offset*stepWidth) are per-iteration constants (taps.dx / dy, computed on the host with the same float operations)
-            const int tx = min(max(px + taps.dx[i], 0), W - 1), ty = min(max(py + taps.dy[i], 0), H - 1);
-            const size_t q = (size_t)ty * W + tx;
-            const float4 oc = ld_color(color, q, lutU);
+            float4 oc, on, op;
+            if (LINEAR) {
+                const Bilin b = bilin_setup(px, py, taps.fx[i], taps.fy[i], W, H);
+                const size_t q00 = (size_t)b.j0 * W + b.i0, q10 = (size_t)b.j0 * W + b.i1, q01 = (size_t)b.j1 * W + b.i0, q11 = (size_t)b.j1 * W + b.i1;
+                if (b.onTexel) {
+                    oc = ld_color(color, q00, lutU); on = ld_normal(normal, q00, lutS); op = reinterpret_cast<const float4*>(position)[q00];
+                } else {
+                    oc = bilin_mix(b, ld_color(color, q00, lutU), ld_color(color, q10, lutU), ld_color(color, q01, lutU), ld_color(color, q11, lutU));
+                    on = bilin_mix(b, ld_normal(normal, q00, lutS), ld_normal(normal, q10, lutS), ld_normal(normal, q01, lutS), ld_normal(normal, q11, lutS));
+                    const float4* pp = reinterpret_cast<const float4*>(position);
+                    op = bilin_mix(b, pp[q00], pp[q10], pp[q01], pp[q11]);
+                }
+            } else {
+                const int tx = min(max(px + taps.dx[i], 0), W - 1), ty = min(max(py + taps.dy[i], 0), H - 1);
+                const size_t q = (size_t)ty * W + tx;
+                oc = ld_color(color, q, lutU); on = ld_normal(normal, q, lutS); op = reinterpret_cast<const float4*>(position)[q];
+            }
             const float cw = fminf(expf(-(dot4d(sc, oc)) / it.phiColor), 1.0f);
-            const float4 on = ld_normal(normal, q, lutS);
             const float nw = fminf(expf(-(fmaxf(dot4d(sn, on) / sw2, 0.0f)) / it.phiNormal), 1.0f);
-            const float4 op = reinterpret_cast<const float4*>(position)[q];
             const float pw = fminf(expf(-(dot4d(sp, op)) / it.phiPos), 1.0f);
             const float weight = (cw * nw) * pw;
             const float k = taps.k[i];
@@ -78,14 +112,18 @@ __global__ void __launch_bounds__(256) denoise_kernel(const uint8_t* __restrict_
 cudaError_t launch_denoise(const uint8_t* color, const int8_t* normal, const float* position, uint8_t* out, int W, int H,
                            const DenoiseTaps& taps, const DenoiseIter& it, cudaStream_t stream) {
     DenoiseTaps t = taps;
-    for (int i = 0; i < t.n; i++) {   // the texel offsets of this iteration (the kernel used to compute them per tap and pixel)
-        t.dx[i] = f2i(floorf(0.5f + (float)t.ox[i] * it.stepWidth));
-        t.dy[i] = f2i(floorf(0.5f + (float)t.oy[i] * it.stepWidth));
+    bool integral = true;
+    for (int i = 0; i < t.n; i++) {   // the tap offsets of this iteration in texels: offset * stepWidth, the product the shader forms
+        t.fx[i] = (float)t.ox[i] * it.stepWidth; t.fy[i] = (float)t.oy[i] * it.stepWidth;
+        integral = integral && t.fx[i] == floorf(t.fx[i]) && t.fy[i] == floorf(t.fy[i]) && fabsf(t.fx[i]) < 1.0e6f && fabsf(t.fy[i]) < 1.0e6f;
+        t.dx[i] = f2i(t.fx[i]); t.dy[i] = f2i(t.fy[i]);
     }
     const float inf = INFINITY;
     const dim3 grid((W + 31) / 32, (H + 7) / 8);
-    if (it.phiColor == inf && it.phiNormal == inf && it.phiPos == inf) denoise_kernel<true><<<grid, 256, 0, stream>>>(color, normal, position, out, W, H, t, it);
-    else denoise_kernel<false><<<grid, 256, 0, stream>>>(color, normal, position, out, W, H, t, it);
+    const bool blind = it.phiColor == inf && it.phiNormal == inf && it.phiPos == inf;
+    if (blind && integral) denoise_kernel<true, false><<<grid, 256, 0, stream>>>(color, normal, position, out, W, H, t, it);
+    else if (integral) denoise_kernel<false, false><<<grid, 256, 0, stream>>>(color, normal, position, out, W, H, t, it);
+    else denoise_kernel<false, true><<<grid, 256, 0, stream>>>(color, normal, position, out, W, H, t, it);   // (a blind iteration has stepWidth 1: always integral)
     return cudaGetLastError();
 }
 

@@ -28,6 +28,9 @@ constexpr uint32_t ENGINE_BLOCK_QUOTA = ENGINE_WARPS * 256u;   // rays per block
 #ifndef ENGINE_FAR_TOP
 #define ENGINE_FAR_TOP 16              // far round: up to 31 steps (blocks 16,8,4,2,1)
 #endif
+#ifndef ENGINE_MIN_BLOCKS
+#define ENGINE_MIN_BLOCKS 4             // blocks per SM the register allocation aims at (64 registers)
+#endif
 constexpr int ENGINE_STASH = 64;         // prepared rays per warp (a refill asks for <= 32 more while < 32 are left)
 
 // Traversal state of one ray: LinRay (vrt_core.cuh) + the step budget
@@ -39,14 +42,16 @@ struct EngRay {
 
 // SoA of 16-byte quads: lanes popping consecutive entries read consecutive quads
 struct alignas(16) EngineStash {
-    float4 s[ENGINE_STASH];              // sideDist at entry (== sideDist0);  w: flags = maxSteps << 8 | sign bits (1: step -1) x,y,z
+    float4 s[ENGINE_STASH];              // sideDist at entry (== sideDist0);  w: flags = first budget << 20 | maxSteps << 8 | sign bits (1: step -1) x,y,z
     float4 d[ENGINE_STASH];              // deltaDist;                         w: user word 0
     float4 a[ENGINE_STASH];              // |dir|;                             w: user word 1
     uint2 p[ENGINE_STASH];               // entry pointer into the ray's safe-step field
 };
 
-__device__ __forceinline__ void engine_push(EngineStash& st, uint32_t slot, const LinRay& r, uint32_t u0, uint32_t u1) {
-    const uint32_t flags = (r.maxSteps << 8) | (r.SX < 0 ? 1u : 0u) | (r.SY < 0 ? 2u : 0u) | (r.SZ < 0 ? 4u : 0u);
+// rem: the budget the ray's FIRST look-up granted (the set-up code does that look-up with all 32 lanes: a ray that ends there —
+// more than half of the AO rays exhaust their 64 steps at once — never enters the stash or occupies a lane of the step rounds)
+__device__ __forceinline__ void engine_push(EngineStash& st, uint32_t slot, const LinRay& r, uint32_t u0, uint32_t u1, uint32_t rem) {
+    const uint32_t flags = (rem << 20) | (r.maxSteps << 8) | (r.SX < 0 ? 1u : 0u) | (r.SY < 0 ? 2u : 0u) | (r.SZ < 0 ? 4u : 0u);
     st.s[slot] = make_float4(r.sx, r.sy, r.sz, __uint_as_float(flags));
     st.d[slot] = make_float4(r.dx, r.dy, r.dz, __uint_as_float(u0));
     st.a[slot] = make_float4(r.ax, r.ay, r.az, __uint_as_float(u1));
@@ -63,11 +68,11 @@ __device__ __forceinline__ void engine_pop(const EngineStash& st, uint32_t slot,
     r.dx = d.x; r.dy = d.y; r.dz = d.z;
     r.ax = a.x; r.ay = a.y; r.az = a.z;
     u0 = __float_as_uint(d.w); u1 = __float_as_uint(a.w);
-    r.maxSteps = flags >> 8;
+    r.maxSteps = (flags >> 8) & 0xfffu;
     r.SX = (flags & 1u) ? -1 : 1; r.SY = (flags & 2u) ? -LW : LW; r.SZ = (flags & 4u) ? -LWH : LWH;
     r.T0 = (int)(0u - (uint32_t)VRT_LIN_MAGIC_BITS * (uint32_t)(r.SX + r.SY));
     r.p0 = reinterpret_cast<const uint8_t*>((unsigned long long)p.x | ((unsigned long long)p.y << 32));
-    e.rem = 0; e.left = r.maxSteps;
+    e.rem = (int)(flags >> 20); e.left = r.maxSteps - (flags >> 20);
 }
 
 enum { ENG_GO = 0, ENG_HIT = 1, ENG_OOB = 2, ENG_EXHAUSTED = 3 };

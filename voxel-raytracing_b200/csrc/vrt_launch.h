@@ -36,7 +36,7 @@ cudaError_t launch_generate(int generator, uint32_t seed, uint8_t* vol, uint32_t
 void generator_palette(int generator, uint32_t seed, vrt_material palette[256]);   // host
 
 // denoiser (vrt_denoise.cu)
-struct DenoiseTaps { int n; int ox[9], oy[9]; float k[9]; int dx[9], dy[9]; };   // taps with non-zero kernel weight, in loop order; dx/dy: texel offsets of one iteration (launch_denoise)
+struct DenoiseTaps { int n; int ox[9], oy[9]; float k[9]; int dx[9], dy[9]; float fx[9], fy[9]; };   // taps with non-zero kernel weight, in loop order; per iteration (launch_denoise): fx/fy = offset*stepWidth, dx/dy the same as integers when all are integral
 struct DenoiseIter { float phiColor, phiNormal, phiPos, stepWidth; };
 cudaError_t launch_denoise(const uint8_t* color, const int8_t* normal, const float* position, uint8_t* out, int W, int H,
                            const DenoiseTaps& taps, const DenoiseIter& it, cudaStream_t stream);

@@ -229,7 +229,7 @@ __global__ void __launch_bounds__(256) wave_anyhit_kernel(const SceneDev sc, con
 
 // ---- any-hit wave on the ray engine (vrt_engine.cuh): LINEAR (isotropic field) or OCTANT (directional fields) ----
 template <int TRAVERSAL, int NEAR_TOP, int FAR_TOP>
-__global__ void __launch_bounds__(ENGINE_WARPS * 32, 4) wave_anyhit_engine_kernel(const SceneDev sc, const FrameParams fp, const PlanesDev pl, const WaveBuf wb,
+__global__ void __launch_bounds__(ENGINE_WARPS * 32, ENGINE_MIN_BLOCKS) wave_anyhit_engine_kernel(const SceneDev sc, const FrameParams fp, const PlanesDev pl, const WaveBuf wb,
                                                                                 Counters* __restrict__ ctr, const uint32_t refillT, const uint32_t farShare, const int part, const uint32_t quota) {
     __shared__ EngineStash stashAll[ENGINE_WARPS];
     __shared__ uint32_t blockChunk;
@@ -302,7 +302,7 @@ __global__ void __launch_bounds__(ENGINE_WARPS * 32, 4) wave_anyhit_engine_kerne
                 const bool valid = cur + lane < end;
                 bool push = false;
                 LinRay nr = er.l;
-                uint32_t nIdx = 0, i = ci;
+                uint32_t nIdx = 0, i = ci, firstRem = 0;
                 if (valid) {
                     unsigned long long qq = (unsigned long long)cq + lane;
                     while (qq >= S) { qq -= S; i++; }
@@ -316,10 +316,17 @@ __global__ void __launch_bounds__(ENGINE_WARPS * 32, 4) wave_anyhit_engine_kerne
                         retire(nIdx, i, hit, f);
                     } else if (lin_begin(sc, TRAVERSAL == VRT_TRAVERSAL_OCTANT ? octant_field(sc, s) : sc.ldist, s, rd, maxSteps, nr) == LIN_OOB)
                         retire(nIdx, i, false, 0u);
-                    else push = true;
+                    else {
+                        // the first look-up, with the whole warp: a ray it ends (exhausted at once / starts in a solid voxel) is retired here
+                        EngRay t; t.l = nr; t.rem = 0; t.left = maxSteps;
+                        const int stt = engine_lookup(t);
+                        ENG_STAT(17, 1); ENG_STAT(18, stt != ENG_GO);
+                        if (stt != ENG_GO) retire(nIdx, i, stt == ENG_HIT, engine_steps_taken(t) + (stt == ENG_HIT ? 1u : 0u));
+                        else { push = true; firstRem = (uint32_t)t.rem; }
+                    }
                 }
                 const unsigned pm = __ballot_sync(0xffffffffu, push);
-                if (push) engine_push(st, stashN + __popc(pm & ltMask), nr, nIdx, i);
+                if (push) engine_push(st, stashN + __popc(pm & ltMask), nr, nIdx, i, firstRem);
                 stashN += __popc(pm);
                 cur += 32u; cq += 32u;
                 while (cq >= S) { cq -= S; ci++; }

@@ -116,6 +116,49 @@ def make_camera(pos, yaw, pitch, bounds_whd, size, frame=0, jitter=(0.0, 0.0), f
     return c
 
 
+def _read_image(fn, arg, dtype, by_path):
+    out = C.c_void_p(); w, h = C.c_uint32(), C.c_uint32()
+    if by_path:
+        _ck(fn(arg.encode(), C.byref(out), C.byref(w), C.byref(h)))
+    else:
+        buf = (C.c_uint8 * max(1, len(arg))).from_buffer_copy(arg or b"\0")
+        _ck(fn(buf, C.c_size_t(len(arg)), C.byref(out), C.byref(w), C.byref(h)))
+    ct = C.c_float if dtype == np.float32 else C.c_uint8
+    a = np.ctypeslib.as_array(C.cast(out, C.POINTER(ct)), shape=(h.value, w.value, 4)).copy()
+    lib().vrt_host_free(out)
+    return a
+
+
+def read_hdr(path_or_bytes):
+    """Radiance RGBE -> float32 [h, w, 4] (alpha 1), host only."""
+    by_path = isinstance(path_or_bytes, str)
+    return _read_image(lib().vrt_image_read_hdr if by_path else lib().vrt_image_decode_hdr, path_or_bytes, np.float32, by_path)
+
+
+def read_png(path_or_bytes):
+    """PNG -> uint8 [h, w, 4], host only."""
+    by_path = isinstance(path_or_bytes, str)
+    return _read_image(lib().vrt_image_read_png if by_path else lib().vrt_image_decode_png, path_or_bytes, np.uint8, by_path)
+
+
+def file_sha256(path) -> str:
+    hexbuf = C.create_string_buffer(65)
+    _ck(lib().vrt_file_sha256(path.encode(), hexbuf))
+    return hexbuf.value.decode()
+
+
+def lfs_pointer_info(path):
+    """(oid, size) if the file is a git-LFS pointer stub, else None."""
+    oid = C.create_string_buffer(65); size = C.c_uint64()
+    rc = lib().vrt_lfs_pointer_info(path.encode(), oid, C.byref(size))
+    return (oid.value.decode(), size.value) if rc == 0 else None
+
+
+def asset_matches_pointer(candidate, pointer) -> bool:
+    """True when `candidate` is the real file the LFS pointer at `pointer` names (sha256 and size equal)."""
+    return lib().vrt_asset_matches_pointer(candidate.encode(), pointer.encode()) == 0
+
+
 def vox_decode(data: bytes):
     """Host-only decode of .vox bytes -> (volume[D,H,W] uint8, palette[256,8] float32). No GPU involved."""
     buf = (C.c_uint8 * len(data)).from_buffer_copy(data)
@@ -242,6 +285,14 @@ class VoxelScene:
 
     def set_skybox(self, rgba32f):
         a = np.ascontiguousarray(rgba32f, np.float32); _ck(lib().vrt_scene_set_skybox(self.h, a.ctypes.data_as(C.c_void_p), a.shape[1], a.shape[0]))
+
+    def load_skybox(self, path):
+        """Radiance .hdr -> RGBA32F skybox (stbi_loadf in the reference, voxel_scene.cpp:132)."""
+        _ck(lib().vrt_scene_load_skybox(self.h, path.encode()))
+
+    def load_noise(self, path):
+        """PNG -> RGBA8 512x512 noise texture (stbi_load in the reference, voxel_renderer.cpp:22)."""
+        _ck(lib().vrt_scene_load_noise(self.h, path.encode()))
 
     def palette(self):
         p = np.zeros((256, 8), np.float32); _ck(lib().vrt_scene_palette(self.h, p.ctypes.data_as(C.c_void_p))); return p
