@@ -332,6 +332,7 @@ def run_vrt(args):
     if not args.serial_frames:
         ctx.set_concurrent_frames(True)
     F = max(2, args.frames_in_flight)
+    S = F if world == 1 else min(8, 2 * F)                  # exchange slots on rank 0: more than frames in flight, so that no rank waits for a slot
     passes = tuple(pyvrt.VoxelRenderPass(ctx, scene, st) for _ in range(F))
     ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
     final = "denoised" if denoise else "color"
@@ -341,29 +342,33 @@ def run_vrt(args):
     host2 = dn_out = dn_scratch = cstream = None
     ds = pyvrt.default_settings().denoise
     if world > 1:
-        ctx.comm_alloc_frames(size, F, xplanes, xhost)
+        ctx.comm_alloc_frames(size, S, xplanes, xhost)
         if rank == 0 and denoise:
-            dn_out = [torch.empty(frame_bytes, dtype=torch.uint8, device=dev) for _ in range(F)]
+            dn_out = [torch.empty(frame_bytes, dtype=torch.uint8, device=dev) for _ in range(S)]
             dn_scratch = torch.empty(frame_bytes, dtype=torch.uint8, device=dev)
         if rank == 0:
             cstream = torch.cuda.ExternalStream(ctx.comm_stream, device=dev)
     if rank == 0 and (world == 1 or denoise):
-        host2 = [torch.empty(frame_bytes, dtype=torch.uint8, pin_memory=True) for _ in range(F)]
-    ev_done = [torch.cuda.Event() for _ in range(F)]
-    pending = [False] * F
+        host2 = [torch.empty(frame_bytes, dtype=torch.uint8, pin_memory=True) for _ in range(S)]
+    ev_done = [torch.cuda.Event() for _ in range(S)]
+    pending = [False] * S
 
     def submit(k, readback=False):
         """Queue frame k: render this rank's tiles; N>1: store them into rank 0's frame (and the shared host frame when the frame is
         read back); rank 0 orders its consumer (denoiser, read-back) behind the arrival of every rank's tiles. Returns the frame and
         the kernels launched outside vrt_render / vrt_frame_exchange (the library counts its own)."""
-        slot = k % F
+        slot = k % S                                         # exchange slot (N > 1) / read-back buffer
         cam = configs.make_camera(args.config, bounds, size, k)
-        fr = passes[slot].record(cam)
-        if world == 1:
-            if readback:
+        if world == 1 or os.environ.get("VRT_BENCH_NOEXCHANGE"):   # (the env knob: what the ranks would do with a free exchange)
+            fr = passes[k % F].record(cam)
+            if readback and world == 1:
                 fr.download_async(final, host2[slot].numpy())
             return fr, 0
-        fr.exchange(slot, xplanes, xhost if readback else ())
+        if os.environ.get("VRT_BENCH_UNFUSED"):               # measurement only: separate push kernels after the pass
+            fr = passes[k % F].record(cam)
+            fr.exchange(slot, xplanes, xhost if readback else ())
+        else:                                                 # the pass's own kernels store into rank 0's frame
+            fr = passes[k % F].record_exchange(cam, slot, xplanes, xhost if readback else ())
         extra = 0
         if rank == 0:
             ctx.comm_wait(slot)                              # wait kernel on the communicator's stream
@@ -387,11 +392,11 @@ def run_vrt(args):
         ctx.join()
 
     def wait_readback(k):
-        slot = k % F
+        slot = k % S
         if rank != 0:
             return
         if world == 1:
-            passes[slot].frame.download_wait()
+            passes[k % F].frame.download_wait()
         elif pending[slot]:
             if not denoise:
                 ctx.comm_wait_host(slot)                     # every rank's tiles are in the shared pinned host frame
@@ -409,7 +414,7 @@ def run_vrt(args):
         return torch.stack([t.sum(), (t * t).sum()])
 
     # ---- self-check of the exchange (outside every timed region): the bytes of the assembled frame are the bytes of the shards
-    if world > 1:
+    if world > 1 and not os.environ.get("VRT_BENCH_NOEXCHANGE"):
         fr0, _ = submit(0)
         drain(); barrier()
         ptr, n = fr0.plane_ptr("color")
@@ -532,10 +537,10 @@ def run_vrt(args):
         line = {"metric": METRIC, "value": rays_all / (ms * 1e-3) / 1e6, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": config_blob(cfg, args.config, args.whd, size, world, bounds),
-                "run": {"traversal": args.traversal, "pipeline": args.pipeline, "frames_in_flight": F, "frame_streams": "one" if args.serial_frames else "per frame",
+                "run": {"traversal": args.traversal, "pipeline": args.pipeline, "frames_in_flight": F, "exchange_slots": S if world > 1 else None, "frame_streams": "one" if args.serial_frames else "per frame",
                         "timed_regions": len(region_ms), "timed_ms_total": float(np.sum(region_ms)), "region_ms_min_median_max": [float(np.min(region_ms)), ms, float(np.max(region_ms))],
-                        "exchange": ("libvrt vrt_frame_exchange: every rank stores its tiles of " + "+".join(xplanes) + " into rank 0's frame (CUDA IPC peer memory over NVLink) "
-                                     "+ arrival flags; rank 0 consumes behind a wait kernel" + ("; rank 0 denoises the assembled planes" if denoise else "")) if world > 1 else None,
+                        "exchange": ("libvrt vrt_render_exchange: the pass's own kernels store " + "+".join(xplanes) + " of every rank's tiles straight into rank 0's frame (CUDA IPC peer memory over NVLink), "
+                                     "arrival flags and rank 0's wait are stream memory operations (no kernel)" + ("; rank 0 denoises the assembled planes" if denoise else "")) if world > 1 else None,
                         "e2e_readback": ("every rank stores its tiles into a pinned host frame shared by all ranks (own PCIe link each)" if not denoise else "rank 0 copies the denoised frame to pinned host memory") if world > 1
                                         else "vrt_frame_download_async on the copy stream, F frames in flight"},
                 "latency_ms_single_frame": latency_ms,

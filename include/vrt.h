@@ -232,8 +232,9 @@ int vrt_frame_push_tiles(vrt_frame*, int plane, void* d_frame, void* stream);
  *   key: names the POSIX shared-memory rendezvous segment; the same on every rank, unique per job (rank 0 creates it).
  *   vrt_comm_create also sets the tile shard (vrt_context_set_shard(rank, world)); call it before the first frame.
  *   vrt_comm_alloc_frames is collective (same arguments on every rank); plane masks are bit (1 << vrt_plane).
- *   Per frame, every rank: vrt_render, then vrt_frame_exchange(frame, slot, ...) — asynchronous on the frame's stream (or `stream`);
- *   the call itself may block on the host until rank 0 has released what the slot held before.
+ *   Per frame, every rank: vrt_render_exchange(..., slot, ...) (fused), or vrt_render then vrt_frame_exchange(frame, slot, ...) —
+ *   asynchronous; the call itself may block on the host until rank 0 has released what the slot held before (use more slots than
+ *   frames in flight and it never does).
  *   Rank 0 then: vrt_comm_wait(slot, stream) [device-side], its own work on that stream (vrt_denoise_on, copies, ...),
  *   vrt_comm_release_on(slot, stream); or vrt_comm_wait_host(slot) / vrt_comm_release(slot) for the host frame.
  * Every wait has a time limit (VRT_COMM_TIMEOUT_S, default 120 s) and returns VRT_E_COMM instead of hanging when a rank is gone. */
@@ -242,6 +243,11 @@ int vrt_comm_destroy(vrt_context*);                       /* collective; vrt_con
 int vrt_comm_barrier(vrt_context*);                       /* host barrier over all ranks */
 int vrt_comm_alloc_frames(vrt_context*, int w, int h, int slots, uint32_t plane_mask, uint32_t host_plane_mask);
 int vrt_frame_exchange(vrt_frame*, int slot, uint32_t plane_mask, uint32_t host_plane_mask, void* stream);
+/* vrt_render + vrt_frame_exchange in one call with the exchange FUSED into the pass: the colour / G-buffer planes of plane_mask are
+ * stored by the pass's own kernels straight into rank 0's frame (peer stores over NVLink beside the local ones) and the arrival flag
+ * follows the last kernel as a stream memory operation: no push kernel, the last kernel of every rank is the collective. */
+int vrt_render_exchange(vrt_context*, const vrt_scene*, const vrt_camera*, const vrt_render_settings*, int slot,
+                        uint32_t plane_mask, uint32_t host_plane_mask, vrt_frame** frame);
 int vrt_comm_wait(vrt_context*, int slot, void* stream);  /* rank 0; stream NULL: vrt_comm_stream() */
 int vrt_comm_wait_host(vrt_context*, int slot);           /* rank 0 */
 int vrt_comm_release(vrt_context*, int slot);             /* rank 0 */

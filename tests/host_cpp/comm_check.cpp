@@ -73,8 +73,12 @@ static int run_rank(int rank, int world, int W, int H, int ndev, int frames, con
     for (int k = 0; k < frames; k++) {
         const int slot = k % slots;
         const vrt_camera cam = make_camera(whd, W, H, k);
-        CK(vrt_render(ctx, scene, &cam, &st, &fr[slot]));
-        CK(vrt_frame_exchange(fr[slot], slot, planes, 1u << VRT_PLANE_COLOR_RGBA8, nullptr));
+        if (k & 1) {                                          // fused: the pass's own kernels store into rank 0's frame
+            CK(vrt_render_exchange(ctx, scene, &cam, &st, slot, planes, 1u << VRT_PLANE_COLOR_RGBA8, &fr[slot]));
+        } else {                                              // separate: push kernels after the pass
+            CK(vrt_render(ctx, scene, &cam, &st, &fr[slot]));
+            CK(vrt_frame_exchange(fr[slot], slot, planes, 1u << VRT_PLANE_COLOR_RGBA8, nullptr));
+        }
         if (rank != 0) continue;
         void* cs = vrt_comm_stream(ctx);
         void *dc, *dn, *dp, *hc; size_t nb;

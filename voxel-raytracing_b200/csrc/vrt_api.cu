@@ -529,6 +529,10 @@ static int run_denoise(vrt_context* c, cudaStream_t stream, const void* color, c
 }
 
 extern "C" int vrt_render(vrt_context* c, const vrt_scene* s, const vrt_camera* cam, const vrt_render_settings* st, vrt_frame** frame) {
+    return vrt_render_impl(c, s, cam, st, frame, nullptr);
+}
+// x: planes of the assembled frame the pass's kernels store into as well (vrt_render_exchange), or null
+int vrt_render_impl(vrt_context* c, const vrt_scene* s, const vrt_camera* cam, const vrt_render_settings* st, vrt_frame** frame, const XPlanes* x) {
     if (!c || !s || !cam || !st || !frame) return fail(VRT_E_INVALID, "null argument");
     if (s->ctx != c) return fail(VRT_E_INVALID, "scene belongs to another context");
     const int W = cam->screenSize[0], H = cam->screenSize[1];
@@ -566,6 +570,7 @@ extern "C" int vrt_render(vrt_context* c, const vrt_scene* s, const vrt_camera* 
     sc.vol = s->vol; sc.bmask = s->bmask; sc.bdist = s->bdist; sc.fdist = s->fdist; sc.ldist = s->ldist; sc.W = s->w; sc.H = s->h; sc.D = s->d; sc.Bx = s->Bx; sc.By = s->By; sc.Bz = s->Bz;
     sc.palette = s->palette; sc.noise = s->noise; sc.sky = s->sky; sc.skyW = s->skyW; sc.skyH = s->skyH;
     FrameParams fp{};
+    if (x) fp.x = *x;
     fp.cam = *cam; fp.pass_mask = st->pass_mask; fp.out_mask = out_mask;
     fp.traversal = traversal;
     fp.aoSamples = st->vol.aoSamples; fp.ambientIntensity = st->vol.ambientIntensity;

@@ -45,9 +45,28 @@ struct CommShm {
     uint32_t planeMask, hostPlaneMask;
     uint64_t planeOff[VRT_PLANE_COUNT], slotStride, arriveOff;
     uint64_t hostPlaneOff[VRT_PLANE_COUNT], hostSlotStride;
-    std::atomic<uint64_t> released[kMaxSlots];        // generations of the slot the consumer on rank 0 is done with
+    std::atomic<uint64_t> released[kMaxSlots];        // generations of the slot the consumer on rank 0 is done with (host store / host function)
+    volatile uint32_t releasedOp[kMaxSlots];          // the same, written by a stream memory operation of rank 0's consumer stream
     volatile uint32_t hostArrive[kMaxSlots][kMaxWorld];   // generation whose tiles rank r has stored into the HOST frame (written by kernels)
 };
+
+// Stream memory operations (cuStreamWaitValue32 / cuStreamWriteValue32), fetched through the runtime so that libvrt has no link-time
+// dependency on libcuda (it must load on a machine without a driver). A wait on a memory word needs no SM: the persistent kernels
+// of the frames in flight own every block slot, and a one-warp wait KERNEL would queue behind them (measured: the exchange then adds a
+// frame time of latency and throttles every rank through the slot hand-shake).
+typedef int (*StreamValue32Fn)(cudaStream_t, unsigned long long, uint32_t, unsigned int);
+StreamValue32Fn g_waitValue32 = nullptr, g_writeValue32 = nullptr;
+void load_stream_memops() {
+    static bool done = false;
+    if (done) return;
+    done = true;
+    if (getenv("VRT_COMM_NO_MEMOPS")) return;
+    void* fn = nullptr; cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &fn, cudaEnableDefault, &qr) == cudaSuccess && qr == cudaDriverEntryPointSuccess) g_waitValue32 = (StreamValue32Fn)fn;
+    fn = nullptr;
+    if (cudaGetDriverEntryPoint("cuStreamWriteValue32", &fn, cudaEnableDefault, &qr) == cudaSuccess && qr == cudaDriverEntryPointSuccess) g_writeValue32 = (StreamValue32Fn)fn;
+    cudaGetLastError();
+}
 
 double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 double timeout_s() { static const double t = getenv("VRT_COMM_TIMEOUT_S") ? atof(getenv("VRT_COMM_TIMEOUT_S")) : 120.0; return t; }
@@ -59,11 +78,13 @@ struct vrt_comm {
     std::string key;
     CommShm* shm = nullptr;                           // host mapping of the header
     uint32_t* shmDevArrive = nullptr;                 // device view of shm->hostArrive
+    uint32_t* shmDevReleased = nullptr;               // device view of shm->releasedOp
     uint32_t framesGen = 0;
     uint8_t* devBase = nullptr;                       // rank 0: its allocation; others: the peer mapping of it
     uint8_t* hostBase = nullptr; uint8_t* hostBaseDev = nullptr; size_t hostBytes = 0;
     uint64_t gen[kMaxSlots] = {};                     // exchanges issued on each slot (identical on every rank)
-    cudaStream_t stream = nullptr;                    // rank 0's consumer stream (wait kernel, caller's work, release)
+    cudaStream_t stream = nullptr;                    // rank 0's consumer stream (arrival wait, caller's work, release)
+    cudaStream_t pushStream = nullptr;                // highest priority: the tile stores of a finished frame never queue behind the next frame's kernels
     cudaEvent_t joined = nullptr;
     uint32_t* devError = nullptr;                     // set by a wait kernel that gave up
     bool joinedOk = false;
@@ -131,6 +152,7 @@ extern "C" int vrt_comm_destroy(vrt_context* c) {
     if (m->shm && m->joinedOk && !m->shm->error.load()) comm_barrier(m, 15.0);   // nobody unmaps memory a peer may still be storing into
     comm_unmap_frames(m);
     if (m->stream) cudaStreamDestroy(m->stream);
+    if (m->pushStream) cudaStreamDestroy(m->pushStream);
     if (m->joined) cudaEventDestroy(m->joined);
     cudaFree(m->devError);
     if (m->shm) { cudaHostUnregister(m->shm); munmap(m->shm, sizeof(CommShm)); }
@@ -179,12 +201,17 @@ extern "C" int vrt_comm_create(vrt_context* c, int rank, int world, const char* 
     cudaError_t e = cudaHostRegister(m->shm, sizeof(CommShm), cudaHostRegisterMapped | cudaHostRegisterPortable);
     void* dv = nullptr;
     if (e == cudaSuccess) e = cudaHostGetDevicePointer(&dv, (void*)&m->shm->hostArrive[0][0], 0);
-    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking);
+    int prLow = 0, prHigh = 0;
+    if (e == cudaSuccess) e = cudaDeviceGetStreamPriorityRange(&prLow, &prHigh);
+    if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&m->stream, cudaStreamNonBlocking, prHigh);
+    if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&m->pushStream, cudaStreamNonBlocking, prHigh);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&m->joined, cudaEventDisableTiming);
+    load_stream_memops();
     if (e == cudaSuccess) e = cudaMalloc(&m->devError, sizeof(uint32_t));
     if (e == cudaSuccess) e = cudaMemset(m->devError, 0, sizeof(uint32_t));
     if (e != cudaSuccess) { m->shm->error.store(1); const std::string msg = cudaGetErrorString(e); vrt_comm_destroy(c); return fail(VRT_E_CUDA, msg); }
     m->shmDevArrive = (uint32_t*)dv;
+    if (cudaHostGetDevicePointer(&dv, (void*)&m->shm->releasedOp[0], 0) == cudaSuccess) m->shmDevReleased = (uint32_t*)dv;
     m->shm->joined.fetch_add(1);
     const int rc = comm_barrier(m);
     if (rc) { const std::string msg = g_vrt_err; vrt_comm_destroy(c); return fail(rc, msg); }
@@ -228,7 +255,7 @@ extern "C" int vrt_comm_alloc_frames(vrt_context* c, int w, int h, int slots, ui
         sh->devBytes = sh->arriveOff + sizeof(uint32_t) * kMaxSlots * kMaxWorld;
         sh->hostBytes = hoff * slots;
         sh->w = w; sh->h = h; sh->slots = slots; sh->planeMask = plane_mask; sh->hostPlaneMask = host_plane_mask;
-        for (int s = 0; s < kMaxSlots; s++) { sh->released[s].store(0); for (int r = 0; r < kMaxWorld; r++) sh->hostArrive[s][r] = 0; }
+        for (int s = 0; s < kMaxSlots; s++) { sh->released[s].store(0); sh->releasedOp[s] = 0; for (int r = 0; r < kMaxWorld; r++) sh->hostArrive[s][r] = 0; }
         e = cudaMalloc(&m->devBase, sh->devBytes);
         if (e == cudaSuccess) e = cudaMemset(m->devBase, 0, sh->devBytes);
         if (e == cudaSuccess && m->world > 1) e = cudaIpcGetMemHandle(&sh->devHandle, m->devBase);
@@ -265,23 +292,37 @@ extern "C" int vrt_comm_alloc_frames(vrt_context* c, int w, int h, int slots, ui
     return comm_barrier(m);
 }
 
-// This rank's tiles of the planes in plane_mask (device frame on rank 0) and host_plane_mask (shared host frame) of `slot`, then the
-// arrival flags. Asynchronous on the frame's stream (or `stream`); the call itself may wait on the HOST until rank 0 has released
-// what the slot held before (vrt_comm_release): with F slots the ranks run at most F-1 frames ahead of the consumer.
-extern "C" int vrt_frame_exchange(vrt_frame* f, int slot, uint32_t plane_mask, uint32_t host_plane_mask, void* stream) {
-    if (!f || !f->ctx->comm) return fail(VRT_E_INVALID, "no communicator");
-    vrt_context* c = f->ctx; vrt_comm* m = c->comm; CommShm* sh = m->shm;
+// ---- one exchange = begin (slot hand-shake on the host) + the stores (push kernels, or the pass's own kernels) + finish (arrival flags)
+static int exchange_begin(vrt_context* c, int W, int H, int slot, uint32_t plane_mask, uint32_t host_plane_mask, uint64_t* gOut) {
+    if (!c || !c->comm) return fail(VRT_E_INVALID, "no communicator");
+    vrt_comm* m = c->comm; CommShm* sh = m->shm;
     if (!m->devBase) return fail(VRT_E_INVALID, "call vrt_comm_alloc_frames first");
-    if (slot < 0 || slot >= sh->slots || f->W != sh->w || f->H != sh->h) return fail(VRT_E_INVALID, "slot or frame size does not match vrt_comm_alloc_frames");
+    if (slot < 0 || slot >= sh->slots || W != sh->w || H != sh->h) return fail(VRT_E_INVALID, "slot or frame size does not match vrt_comm_alloc_frames");
     if ((plane_mask & ~sh->planeMask) || (host_plane_mask & ~sh->hostPlaneMask)) return fail(VRT_E_INVALID, "plane was not allocated by vrt_comm_alloc_frames");
-    for (int p = 0; p < VRT_PLANE_COUNT; p++) if (((plane_mask | host_plane_mask) >> p & 1u) && !f->planes[p]) return fail(VRT_E_INVALID, "plane was not produced for this frame");
     CU(cudaSetDevice(c->device));
     const uint64_t g = ++m->gen[slot];
     struct Arg { int slot; uint64_t g; } a{slot, g};
-    int rc = comm_spin(m, "rank 0 to release the slot", [](vrt_comm* mm, const void* q) { const Arg* x = (const Arg*)q; return mm->shm->released[x->slot].load(std::memory_order_acquire) + 1 >= x->g; }, &a);
-    if (rc) return rc;
-    const cudaStream_t s = stream ? (cudaStream_t)stream : f->stream;
+    const int rc = comm_spin(m, "rank 0 to release the slot", [](vrt_comm* mm, const void* q) { const Arg* x = (const Arg*)q;
+        const uint64_t r = mm->shm->released[x->slot].load(std::memory_order_acquire), r2 = mm->shm->releasedOp[x->slot];
+        return (r > r2 ? r : r2) + 1 >= x->g; }, &a);
+    *gOut = g;
+    return rc;
+}
+// push kernels for the planes in plane_mask / host_plane_mask (none: the pass's kernels stored them already), then the arrival flags
+static int exchange_finish(vrt_frame* f, int slot, uint64_t g, uint32_t plane_mask, uint32_t host_plane_mask, bool devFlagWanted, void* stream) {
+    vrt_context* c = f->ctx; vrt_comm* m = c->comm; CommShm* sh = m->shm;
+    for (int p = 0; p < VRT_PLANE_COUNT; p++) if (((plane_mask | host_plane_mask) >> p & 1u) && !f->planes[p]) return fail(VRT_E_INVALID, "plane was not produced for this frame");
+    // Push kernels run on the communicator's high-priority stream behind the frame's kernels; the frame's next render waits for
+    // them (f->copied), as it does for an asynchronous read-back. Without push kernels the flags follow the pass on its own stream.
+    static const bool ownStream = !getenv("VRT_COMM_PUSH_ON_FRAME_STREAM");
+    cudaStream_t s = stream ? (cudaStream_t)stream : f->stream;
     cudaError_t e = cudaSuccess;
+    const bool hop = !stream && ownStream && (plane_mask | host_plane_mask) != 0 && f->localTiles > 0;
+    if (hop) {
+        e = cudaEventRecord(f->rendered, f->stream);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(m->pushStream, f->rendered, 0);
+        s = m->pushStream;
+    }
     for (int p = 0; p < VRT_PLANE_COUNT && e == cudaSuccess; p++) {
         if (plane_mask >> p & 1u)
             e = launch_push_tiles(f->planes[p], m->devBase + (uint64_t)slot * sh->slotStride + sh->planeOff[p], f->W, f->H, c->rank, c->world, f->localTiles, kPlaneBpp[p], s);
@@ -290,14 +331,66 @@ extern "C" int vrt_frame_exchange(vrt_frame* f, int slot, uint32_t plane_mask, u
         if (f->localTiles > 0) f->launches += (plane_mask >> p & 1u) + (host_plane_mask >> p & 1u);
     }
     if (e == cudaSuccess) {
-        uint32_t* devFlag = plane_mask ? (uint32_t*)(m->devBase + sh->arriveOff) + slot * kMaxWorld + c->rank : nullptr;
+        uint32_t* devFlag = devFlagWanted ? (uint32_t*)(m->devBase + sh->arriveOff) + slot * kMaxWorld + c->rank : nullptr;
         uint32_t* hostFlag = host_plane_mask ? m->shmDevArrive + slot * kMaxWorld + c->rank : nullptr;
-        comm_signal_kernel<<<1, 1, 0, s>>>(devFlag, hostFlag, (uint32_t)g);
-        f->launches++;
-        e = cudaGetLastError();
+        // arrival flags: stream memory operations where the driver has them (no kernel, no SM), else the one-thread kernel
+        bool done = false;
+        if (g_writeValue32 && !getenv("VRT_COMM_SIGNAL_KERNEL")) {
+            int rc = 0;
+            if (devFlag) rc = g_writeValue32(s, (unsigned long long)devFlag, (uint32_t)g, 0);
+            if (rc == 0 && hostFlag) rc = g_writeValue32(s, (unsigned long long)hostFlag, (uint32_t)g, 0);
+            done = rc == 0;
+            if (!done) { g_writeValue32 = nullptr; cudaGetLastError(); }
+        }
+        if (!done) { comm_signal_kernel<<<1, 1, 0, s>>>(devFlag, hostFlag, (uint32_t)g); f->launches++; e = cudaGetLastError(); }
+    }
+    if (e == cudaSuccess && hop) {
+        e = cudaEventRecord(f->copied, m->pushStream);
+        f->copyPending = true;
     }
     if (e != cudaSuccess) { sh->error.store(1); return fail(VRT_E_CUDA, cudaGetErrorString(e)); }
     return VRT_OK;
+}
+
+// This rank's tiles of the planes in plane_mask (device frame on rank 0) and host_plane_mask (shared host frame) of `slot`, then the
+// arrival flags. Asynchronous (on `stream`, or behind the frame's kernels); the call itself may wait on the HOST until rank 0 has
+// released what the slot held before (vrt_comm_release): with S slots the ranks run at most S-1 frames ahead of the consumer.
+extern "C" int vrt_frame_exchange(vrt_frame* f, int slot, uint32_t plane_mask, uint32_t host_plane_mask, void* stream) {
+    if (!f) return fail(VRT_E_INVALID, "null frame");
+    uint64_t g = 0;
+    const int rc = exchange_begin(f->ctx, f->W, f->H, slot, plane_mask, host_plane_mask, &g);
+    if (rc) return rc;
+    return exchange_finish(f, slot, g, plane_mask, host_plane_mask, plane_mask != 0, stream);
+}
+
+// vrt_render + vrt_frame_exchange in one call, with the exchange FUSED into the pass where it can be: the colour and G-buffer planes
+// named in plane_mask are stored by the pass's own kernels (primary / resolve) straight into rank 0's frame as they are produced —
+// peer stores over NVLink beside the local ones — and the arrival flag follows the last kernel on the frame's stream as a stream
+// memory operation. No push kernel, no extra pass over the tiles: the last kernel of every rank is the collective.
+// Instrumentation planes and the host frame (host_plane_mask) still go through push kernels.
+extern "C" int vrt_render_exchange(vrt_context* c, const vrt_scene* sc, const vrt_camera* cam, const vrt_render_settings* st, int slot,
+                                   uint32_t plane_mask, uint32_t host_plane_mask, vrt_frame** frame) {
+    if (!c || !cam || !st) return fail(VRT_E_INVALID, "null argument");
+    uint64_t g = 0;
+    int rc = exchange_begin(c, cam->screenSize[0], cam->screenSize[1], slot, plane_mask, host_plane_mask, &g);
+    if (rc) return rc;
+    vrt_comm* m = c->comm; CommShm* sh = m->shm;
+    XPlanes x{};
+    uint32_t fused = 0;
+    static const bool noFuse = getenv("VRT_COMM_NO_FUSE") != nullptr;
+    if (!noFuse) {
+        auto at = [&](int p) { return m->devBase + (uint64_t)slot * sh->slotStride + sh->planeOff[p]; };
+        const bool gb = (st->out_mask & VRT_OUT_GBUFFER) != 0;
+        if (plane_mask >> VRT_PLANE_COLOR_RGBA8 & 1u) { x.color = at(VRT_PLANE_COLOR_RGBA8); fused |= 1u << VRT_PLANE_COLOR_RGBA8; }
+        if (gb && (plane_mask >> VRT_PLANE_DEPTH_R32F & 1u)) { x.depth = (float*)at(VRT_PLANE_DEPTH_R32F); fused |= 1u << VRT_PLANE_DEPTH_R32F; }
+        if (gb && (plane_mask >> VRT_PLANE_MOTION_RG32F & 1u)) { x.motion = (float*)at(VRT_PLANE_MOTION_RG32F); fused |= 1u << VRT_PLANE_MOTION_RG32F; }
+        if (gb && (plane_mask >> VRT_PLANE_MASK_R8 & 1u)) { x.mask = at(VRT_PLANE_MASK_R8); fused |= 1u << VRT_PLANE_MASK_R8; }
+        if (gb && (plane_mask >> VRT_PLANE_POSITION_RGBA32F & 1u)) { x.position = (float*)at(VRT_PLANE_POSITION_RGBA32F); fused |= 1u << VRT_PLANE_POSITION_RGBA32F; }
+        if (gb && (plane_mask >> VRT_PLANE_NORMAL_RGBA8S & 1u)) { x.normal = (int8_t*)at(VRT_PLANE_NORMAL_RGBA8S); fused |= 1u << VRT_PLANE_NORMAL_RGBA8S; }
+    }
+    rc = vrt_render_impl(c, sc, cam, st, frame, fused ? &x : nullptr);
+    if (rc) { sh->error.store(1); return rc; }
+    return exchange_finish(*frame, slot, g, plane_mask & ~fused, host_plane_mask, plane_mask != 0, nullptr);
 }
 
 // Rank 0: everything queued on `stream` (null: the communicator's stream) after this call runs once every rank's tiles of the latest
@@ -308,7 +401,15 @@ extern "C" int vrt_comm_wait(vrt_context* c, int slot, void* stream) {
     if (m->rank != 0) return fail(VRT_E_INVALID, "the frame is assembled on rank 0");
     if (slot < 0 || slot >= sh->slots || m->gen[slot] == 0) return fail(VRT_E_INVALID, "nothing was exchanged on this slot");
     CU(cudaSetDevice(c->device));
-    comm_wait_kernel<<<1, 32, 0, stream ? (cudaStream_t)stream : m->stream>>>((const uint32_t*)(m->devBase + sh->arriveOff) + slot * kMaxWorld, m->world, (uint32_t)m->gen[slot], m->devError);
+    const cudaStream_t s = stream ? (cudaStream_t)stream : m->stream;
+    const uint32_t* flags = (const uint32_t*)(m->devBase + sh->arriveOff) + slot * kMaxWorld;
+    if (g_waitValue32) {
+        bool ok = true;
+        for (int r = 0; r < m->world && ok; r++) ok = g_waitValue32(s, (unsigned long long)(flags + r), (uint32_t)m->gen[slot], 0x0 /* CU_STREAM_WAIT_VALUE_GEQ */) == 0;
+        if (ok) return VRT_OK;
+        g_waitValue32 = nullptr; cudaGetLastError();
+    }
+    comm_wait_kernel<<<1, 32, 0, s>>>(flags, m->world, (uint32_t)m->gen[slot], m->devError);
     CU(cudaGetLastError());
     return VRT_OK;
 }
@@ -338,6 +439,11 @@ extern "C" int vrt_comm_release_on(vrt_context* c, int slot, void* stream) {
     if (!c || !c->comm || c->comm->rank != 0 || slot < 0 || slot >= kMaxSlots) return fail(VRT_E_INVALID, "bad argument");
     vrt_comm* m = c->comm;
     CU(cudaSetDevice(c->device));
+    // a stream memory operation into the (mapped) rendezvous segment where the driver has them: no host callback thread in the loop
+    if (g_writeValue32 && m->shmDevReleased && !getenv("VRT_COMM_RELEASE_HOSTFUNC")) {
+        if (g_writeValue32(stream ? (cudaStream_t)stream : m->stream, (unsigned long long)(m->shmDevReleased + slot), (uint32_t)m->gen[slot], 0) == 0) return VRT_OK;
+        cudaGetLastError();
+    }
     ReleaseNote* n = new (std::nothrow) ReleaseNote{&m->shm->released[slot], m->gen[slot]};
     if (!n) return fail(VRT_E_OOM, "host allocation failed");
     CU(cudaLaunchHostFunc(stream ? (cudaStream_t)stream : m->stream, [](void* q) { ReleaseNote* x = (ReleaseNote*)q; x->word->store(x->g, std::memory_order_release); delete x; }, n));

@@ -69,3 +69,6 @@ struct vrt_frame {
     uint32_t wbRays = 0;               // result planes allocated in wb.res
 };
 
+
+// vrt_render with the fused exchange targets (vrt_api.cu; used by vrt_render_exchange in vrt_comm.cu)
+int vrt_render_impl(vrt_context* c, const vrt_scene* s, const vrt_camera* cam, const vrt_render_settings* st, vrt_frame** frame, const XPlanes* x);

@@ -31,13 +31,23 @@ __global__ void __launch_bounds__(128, VRT_MIN_BLOCKS) render_kernel(const Scene
         render_pixel<TRAVERSAL>(sc, fp, px, py, o);
         rays = o.rays; fetches = o.fetches;
         const size_t p = fp.world == 1 ? (size_t)py * W + px : (size_t)j * (VRT_TILE * VRT_TILE) + ly * VRT_TILE + lx;
-        reinterpret_cast<uchar4*>(pl.color)[p] = make_uchar4(to_unorm8(o.color.x), to_unorm8(o.color.y), to_unorm8(o.color.z), 0);
+        const uchar4 c4 = make_uchar4(to_unorm8(o.color.x), to_unorm8(o.color.y), to_unorm8(o.color.z), 0);
+        const size_t xp = (size_t)py * W + px;                      // fused exchange (XPlanes): the pixel in rank 0's row-major planes
+        reinterpret_cast<uchar4*>(pl.color)[p] = c4;
+        if (fp.x.color) reinterpret_cast<uchar4*>(fp.x.color)[xp] = c4;
         if (fp.out_mask & VRT_OUT_GBUFFER) {
+            const float4 pos4 = make_float4(o.pos.x, o.pos.y, o.pos.z, 0.0f);
+            const char4 n4 = make_char4(to_snorm8(o.normal.x), to_snorm8(o.normal.y), to_snorm8(o.normal.z), 0);
             pl.depth[p] = o.depth;
             reinterpret_cast<float2*>(pl.motion)[p] = make_float2(0.0f, 0.0f);
             pl.mask[p] = to_unorm8(o.mask);
-            reinterpret_cast<float4*>(pl.position)[p] = make_float4(o.pos.x, o.pos.y, o.pos.z, 0.0f);
-            reinterpret_cast<char4*>(pl.normal)[p] = make_char4(to_snorm8(o.normal.x), to_snorm8(o.normal.y), to_snorm8(o.normal.z), 0);
+            reinterpret_cast<float4*>(pl.position)[p] = pos4;
+            reinterpret_cast<char4*>(pl.normal)[p] = n4;
+            if (fp.x.depth) fp.x.depth[xp] = o.depth;
+            if (fp.x.motion) reinterpret_cast<float2*>(fp.x.motion)[xp] = make_float2(0.0f, 0.0f);
+            if (fp.x.mask) fp.x.mask[xp] = to_unorm8(o.mask);
+            if (fp.x.position) reinterpret_cast<float4*>(fp.x.position)[xp] = pos4;
+            if (fp.x.normal) reinterpret_cast<char4*>(fp.x.normal)[xp] = n4;
         }
         if (fp.out_mask & VRT_OUT_INSTRUMENT) {
             auto sat = [](int v) { return (short)(v < -32768 ? -32768 : (v > 32767 ? 32767 : v)); };

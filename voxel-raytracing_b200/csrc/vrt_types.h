@@ -78,8 +78,14 @@ struct PlanesDev {
 // tiles compactly, tile-major (local tile j = t / world, TILE*TILE pixels each, row-major inside the tile).
 constexpr int VRT_TILE = 32;
 
+// Fused exchange (vrt_render_exchange, multi-GPU): row-major W x H planes of the assembled frame on rank 0 (peer memory over NVLink for
+// the other ranks). A kernel that stores a pixel of one of these planes stores it there as well: the pass's own kernels are the
+// "collective", no push kernel runs afterwards. Null = the plane is not exchanged in-kernel.
+struct XPlanes { uint8_t* color; float* depth; float* motion; uint8_t* mask; float* position; int8_t* normal; };
+
 struct FrameParams {
     vrt_camera cam;
+    XPlanes x;
     uint32_t pass_mask, out_mask, traversal;
     uint32_t aoSamples;
     float ambientIntensity;

@@ -38,8 +38,10 @@ __device__ __forceinline__ void add_totals(Counters* ctr, int stage, unsigned ra
     }
 }
 
-__device__ __forceinline__ void store_color(const FrameParams& fp, const PlanesDev& pl, size_t p, V3 c) {
-    reinterpret_cast<uchar4*>(pl.color)[p] = make_uchar4(to_unorm8(c.x), to_unorm8(c.y), to_unorm8(c.z), 0);
+__device__ __forceinline__ void store_color(const FrameParams& fp, const PlanesDev& pl, size_t p, V3 c, int px, int py) {
+    const uchar4 q = make_uchar4(to_unorm8(c.x), to_unorm8(c.y), to_unorm8(c.z), 0);
+    reinterpret_cast<uchar4*>(pl.color)[p] = q;
+    if (fp.x.color) reinterpret_cast<uchar4*>(fp.x.color)[(size_t)py * fp.cam.screenSize[0] + px] = q;   // fused exchange: rank 0's frame
     if (fp.out_mask & VRT_OUT_INSTRUMENT) { pl.color_f32[3 * p + 0] = c.x; pl.color_f32[3 * p + 1] = c.y; pl.color_f32[3 * p + 2] = c.z; }
 }
 
@@ -63,13 +65,21 @@ __global__ void __launch_bounds__(128) wave_primary_kernel(const SceneDev sc, co
     if (active) {
         action = wave_primary<TRAVERSAL>(sc, fp, px, py, o, rayDir);
         p = fp.world == 1 ? (size_t)py * W + px : (size_t)j * (VRT_TILE * VRT_TILE) + ly * VRT_TILE + lx;
-        if (action == WAVE_PIXEL_FINAL) store_color(fp, pl, p, o.color);
+        if (action == WAVE_PIXEL_FINAL) store_color(fp, pl, p, o.color, px, py);
         if (fp.out_mask & VRT_OUT_GBUFFER) {
+            const float4 pos4 = make_float4(o.pos.x, o.pos.y, o.pos.z, 0.0f);
+            const char4 n4 = make_char4(to_snorm8(o.normal.x), to_snorm8(o.normal.y), to_snorm8(o.normal.z), 0);
             pl.depth[p] = o.depth;
             reinterpret_cast<float2*>(pl.motion)[p] = make_float2(0.0f, 0.0f);
             pl.mask[p] = to_unorm8(o.mask);
-            reinterpret_cast<float4*>(pl.position)[p] = make_float4(o.pos.x, o.pos.y, o.pos.z, 0.0f);
-            reinterpret_cast<char4*>(pl.normal)[p] = make_char4(to_snorm8(o.normal.x), to_snorm8(o.normal.y), to_snorm8(o.normal.z), 0);
+            reinterpret_cast<float4*>(pl.position)[p] = pos4;
+            reinterpret_cast<char4*>(pl.normal)[p] = n4;
+            const size_t xp = (size_t)py * W + px;                  // fused exchange: the same pixel of rank 0's row-major planes
+            if (fp.x.depth) fp.x.depth[xp] = o.depth;
+            if (fp.x.motion) reinterpret_cast<float2*>(fp.x.motion)[xp] = make_float2(0.0f, 0.0f);
+            if (fp.x.mask) fp.x.mask[xp] = to_unorm8(o.mask);
+            if (fp.x.position) reinterpret_cast<float4*>(fp.x.position)[xp] = pos4;
+            if (fp.x.normal) reinterpret_cast<char4*>(fp.x.normal)[xp] = n4;
         }
         if (fp.out_mask & VRT_OUT_INSTRUMENT) {
             auto sat = [](int v) { return (short)(v < -32768 ? -32768 : (v > 32767 ? 32767 : v)); };
@@ -380,7 +390,7 @@ __global__ void __launch_bounds__(256) wave_resolve_kernel(const SceneDev sc, co
     for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n0; idx += gridDim.x * blockDim.x) {
         const uint32_t pxy = wb.rec[3 * (size_t)idx].w;
         const V3 c = wave_resolve(sc, fp, wb, idx, aoN, skyTab);
-        store_color(fp, pl, plane_index(fp, (int)(pxy & 0xffffu), (int)(pxy >> 16)), c);
+        store_color(fp, pl, plane_index(fp, (int)(pxy & 0xffffu), (int)(pxy >> 16)), c, (int)(pxy & 0xffffu), (int)(pxy >> 16));
     }
 }
 

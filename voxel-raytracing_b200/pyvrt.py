@@ -400,6 +400,16 @@ class VoxelRenderPass:
         self.settings = settings if settings is not None else default_settings()
         self.frame = Frame(ctx)
 
+    def record_exchange(self, camera: Camera, slot, planes=("color",), host_planes=()) -> Frame:
+        """record() + Frame.exchange() in one call, the exchange fused into the pass's kernels (vrt_render_exchange)."""
+        size = (camera.screenSize[0], camera.screenSize[1])
+        if self.frame.size not in (None, size):
+            self.frame.release()
+        pm = sum(1 << PLANE_ID[n] for n in planes); hm = sum(1 << PLANE_ID[n] for n in host_planes)
+        _ck(lib().vrt_render_exchange(self.ctx.h, self.scene.h, C.byref(camera), C.byref(self.settings), int(slot), C.c_uint32(pm), C.c_uint32(hm), C.byref(self.frame.h)))
+        self.frame.size = size
+        return self.frame
+
     def record(self, camera: Camera) -> Frame:
         size = (camera.screenSize[0], camera.screenSize[1])
         if self.frame.size not in (None, size):
