@@ -309,7 +309,7 @@ static int exchange_begin(vrt_context* c, int W, int H, int slot, uint32_t plane
     return rc;
 }
 // push kernels for the planes in plane_mask / host_plane_mask (none: the pass's kernels stored them already), then the arrival flags
-static int exchange_finish(vrt_frame* f, int slot, uint64_t g, uint32_t plane_mask, uint32_t host_plane_mask, bool devFlagWanted, void* stream) {
+static int exchange_finish(vrt_frame* f, int slot, uint64_t g, uint32_t plane_mask, uint32_t host_plane_mask, bool devFlagWanted, bool hostFlagWanted, void* stream) {
     vrt_context* c = f->ctx; vrt_comm* m = c->comm; CommShm* sh = m->shm;
     for (int p = 0; p < VRT_PLANE_COUNT; p++) if (((plane_mask | host_plane_mask) >> p & 1u) && !f->planes[p]) return fail(VRT_E_INVALID, "plane was not produced for this frame");
     // Push kernels run on the communicator's high-priority stream behind the frame's kernels; the frame's next render waits for
@@ -332,7 +332,7 @@ static int exchange_finish(vrt_frame* f, int slot, uint64_t g, uint32_t plane_ma
     }
     if (e == cudaSuccess) {
         uint32_t* devFlag = devFlagWanted ? (uint32_t*)(m->devBase + sh->arriveOff) + slot * kMaxWorld + c->rank : nullptr;
-        uint32_t* hostFlag = host_plane_mask ? m->shmDevArrive + slot * kMaxWorld + c->rank : nullptr;
+        uint32_t* hostFlag = hostFlagWanted ? m->shmDevArrive + slot * kMaxWorld + c->rank : nullptr;
         // arrival flags: stream memory operations where the driver has them (no kernel, no SM), else the one-thread kernel
         bool done = false;
         if (g_writeValue32 && !getenv("VRT_COMM_SIGNAL_KERNEL")) {
@@ -360,7 +360,7 @@ extern "C" int vrt_frame_exchange(vrt_frame* f, int slot, uint32_t plane_mask, u
     uint64_t g = 0;
     const int rc = exchange_begin(f->ctx, f->W, f->H, slot, plane_mask, host_plane_mask, &g);
     if (rc) return rc;
-    return exchange_finish(f, slot, g, plane_mask, host_plane_mask, plane_mask != 0, stream);
+    return exchange_finish(f, slot, g, plane_mask, host_plane_mask, plane_mask != 0, host_plane_mask != 0, stream);
 }
 
 // vrt_render + vrt_frame_exchange in one call, with the exchange FUSED into the pass where it can be: the colour and G-buffer planes
@@ -376,8 +376,12 @@ extern "C" int vrt_render_exchange(vrt_context* c, const vrt_scene* sc, const vr
     if (rc) return rc;
     vrt_comm* m = c->comm; CommShm* sh = m->shm;
     XPlanes x{};
-    uint32_t fused = 0;
-    static const bool noFuse = getenv("VRT_COMM_NO_FUSE") != nullptr;
+    uint32_t fused = 0, fusedHost = 0;
+    static const bool noFuse = getenv("VRT_COMM_NO_FUSE") != nullptr, fuseHost = getenv("VRT_COMM_FUSE_HOST") != nullptr;
+    if (!noFuse && fuseHost && (host_plane_mask >> VRT_PLANE_COLOR_RGBA8 & 1u)) {
+        x.colorHost = m->hostBaseDev + (uint64_t)slot * sh->hostSlotStride + sh->hostPlaneOff[VRT_PLANE_COLOR_RGBA8];
+        fusedHost = 1u << VRT_PLANE_COLOR_RGBA8;
+    }
     if (!noFuse) {
         auto at = [&](int p) { return m->devBase + (uint64_t)slot * sh->slotStride + sh->planeOff[p]; };
         const bool gb = (st->out_mask & VRT_OUT_GBUFFER) != 0;
@@ -388,9 +392,9 @@ extern "C" int vrt_render_exchange(vrt_context* c, const vrt_scene* sc, const vr
         if (gb && (plane_mask >> VRT_PLANE_POSITION_RGBA32F & 1u)) { x.position = (float*)at(VRT_PLANE_POSITION_RGBA32F); fused |= 1u << VRT_PLANE_POSITION_RGBA32F; }
         if (gb && (plane_mask >> VRT_PLANE_NORMAL_RGBA8S & 1u)) { x.normal = (int8_t*)at(VRT_PLANE_NORMAL_RGBA8S); fused |= 1u << VRT_PLANE_NORMAL_RGBA8S; }
     }
-    rc = vrt_render_impl(c, sc, cam, st, frame, fused ? &x : nullptr);
+    rc = vrt_render_impl(c, sc, cam, st, frame, (fused | fusedHost) ? &x : nullptr);
     if (rc) { sh->error.store(1); return rc; }
-    return exchange_finish(*frame, slot, g, plane_mask & ~fused, host_plane_mask, plane_mask != 0, nullptr);
+    return exchange_finish(*frame, slot, g, plane_mask & ~fused, host_plane_mask & ~fusedHost, plane_mask != 0, host_plane_mask != 0, nullptr);
 }
 
 // Rank 0: everything queued on `stream` (null: the communicator's stream) after this call runs once every rank's tiles of the latest

@@ -35,6 +35,7 @@ __global__ void __launch_bounds__(128, VRT_MIN_BLOCKS) render_kernel(const Scene
         const size_t xp = (size_t)py * W + px;                      // fused exchange (XPlanes): the pixel in rank 0's row-major planes
         reinterpret_cast<uchar4*>(pl.color)[p] = c4;
         if (fp.x.color) reinterpret_cast<uchar4*>(fp.x.color)[xp] = c4;
+        if (fp.x.colorHost) reinterpret_cast<uchar4*>(fp.x.colorHost)[xp] = c4;
         if (fp.out_mask & VRT_OUT_GBUFFER) {
             const float4 pos4 = make_float4(o.pos.x, o.pos.y, o.pos.z, 0.0f);
             const char4 n4 = make_char4(to_snorm8(o.normal.x), to_snorm8(o.normal.y), to_snorm8(o.normal.z), 0);

@@ -81,7 +81,7 @@ constexpr int VRT_TILE = 32;
 // Fused exchange (vrt_render_exchange, multi-GPU): row-major W x H planes of the assembled frame on rank 0 (peer memory over NVLink for
 // the other ranks). A kernel that stores a pixel of one of these planes stores it there as well: the pass's own kernels are the
 // "collective", no push kernel runs afterwards. Null = the plane is not exchanged in-kernel.
-struct XPlanes { uint8_t* color; float* depth; float* motion; uint8_t* mask; float* position; int8_t* normal; };
+struct XPlanes { uint8_t* color; float* depth; float* motion; uint8_t* mask; float* position; int8_t* normal; uint8_t* colorHost; /* the same pixel of the shared pinned HOST frame (zero-copy over this GPU's PCIe link) */ };
 
 struct FrameParams {
     vrt_camera cam;

@@ -42,6 +42,7 @@ __device__ __forceinline__ void store_color(const FrameParams& fp, const PlanesD
     const uchar4 q = make_uchar4(to_unorm8(c.x), to_unorm8(c.y), to_unorm8(c.z), 0);
     reinterpret_cast<uchar4*>(pl.color)[p] = q;
     if (fp.x.color) reinterpret_cast<uchar4*>(fp.x.color)[(size_t)py * fp.cam.screenSize[0] + px] = q;   // fused exchange: rank 0's frame
+    if (fp.x.colorHost) reinterpret_cast<uchar4*>(fp.x.colorHost)[(size_t)py * fp.cam.screenSize[0] + px] = q;
     if (fp.out_mask & VRT_OUT_INSTRUMENT) { pl.color_f32[3 * p + 0] = c.x; pl.color_f32[3 * p + 1] = c.y; pl.color_f32[3 * p + 2] = c.z; }
 }
 
