@@ -50,6 +50,7 @@ typedef enum {
 typedef struct vrt_context vrt_context;
 typedef struct vrt_scene vrt_scene;
 typedef struct vrt_frame vrt_frame;
+typedef struct vrt_upscaler vrt_upscaler;
 
 /* == ScreenQuadPush: 96 bytes, offsets 0,16,32,48,64,76,80,88 */
 typedef struct {
@@ -80,7 +81,7 @@ enum {
     VRT_OUT_INSTRUMENT = 2,   /* hit voxel + step count, palette index, float colour, per-pixel ray / fetch counts */
 };
 /* traversal back-ends (all bit-identical; for measurement). 0 = library default. */
-enum { VRT_TRAVERSAL_DEFAULT = 0, VRT_TRAVERSAL_DENSE_U8 = 1, VRT_TRAVERSAL_BRICK = 2, VRT_TRAVERSAL_FINE = 3, VRT_TRAVERSAL_LINEAR = 4, VRT_TRAVERSAL_OCTANT = 5 };
+enum { VRT_TRAVERSAL_DEFAULT = 0, VRT_TRAVERSAL_DENSE_U8 = 1, VRT_TRAVERSAL_BRICK = 2, VRT_TRAVERSAL_FINE = 3, VRT_TRAVERSAL_LINEAR = 4, VRT_TRAVERSAL_OCTANT = 5, VRT_TRAVERSAL_SPARSE = 6 };
 
 /* how the pass is scheduled on the GPU (all bit-identical; for measurement). 0 = library default (wavefront).
  *   MEGAKERNEL: one thread runs a pixel's whole ray tree (the shader's own shape).
@@ -182,6 +183,8 @@ int vrt_scene_download_accel(const vrt_scene*, uint64_t* bmask_dst, uint8_t* bdi
 int vrt_scene_download_fdist(const vrt_scene*, uint8_t* dst, size_t bytes);
 /* directional safe-step field of one direction octant (0..7), aproned linear: (w+2)*(h+2)*(d+2) bytes; built on first use */
 int vrt_scene_download_odist(const vrt_scene*, int octant, uint8_t* dst, size_t bytes);
+/* the two-level (sparse) directional field of one octant, expanded to the same aproned linear layout (tests; built on first use) */
+int vrt_scene_download_sdist(const vrt_scene*, int octant, uint8_t* dst, size_t bytes);
 void vrt_scene_destroy(vrt_scene*);
 /* Host-only .vox decode (no GPU involved): the dense volume + palette vrt_scene_load_vox_memory would upload.
  * *volume_out is malloc'ed (x + y*w + z*w*h); free it with vrt_host_free. */
@@ -254,6 +257,18 @@ int vrt_comm_release(vrt_context*, int slot);             /* rank 0 */
 int vrt_comm_release_on(vrt_context*, int slot, void* stream);
 int vrt_comm_frame_plane(vrt_context*, int slot, int plane, void** d_ptr, void** h_ptr, size_t* bytes);
 void* vrt_comm_stream(vrt_context*);                      /* rank 0's consumer stream; vrt_context_join / _sync include it */
+
+/* ---- temporal upscaler: the stage after the denoiser, UpscalerStage::record -> ffxFsr2ContextDispatch
+ * (source/voxels/stages/upscaler_stage.cpp:78-172). FSR2 is closed source in the reference checkout, so this is an OWN DEFINITION of
+ * the same interface (PARITY UNPINNED): jittered temporal accumulation with neighbourhood rectification, documented in
+ * csrc/vrt_upscale.cu. Inputs are row-major device planes of the render resolution (what vrt_frame_plane returns on an unsharded
+ * frame, or rank 0's assembled planes): colour RGBA8, depth R32F, motion RG32F (may be NULL), reactive mask R8 (may be NULL); jitter
+ * as UpscalerStage::update / vrt_upscaler_update produced it for this frame; reset: ignore the history. Output: target-resolution RGBA8.
+ * Deterministic; exact pass-through at scale 1 with jitter (0, 0). Asynchronous on `stream` (NULL: the context stream). */
+int vrt_upscaler_create(vrt_context*, int renderW, int renderH, int targetW, int targetH, vrt_upscaler** out);
+int vrt_upscaler_dispatch(vrt_upscaler*, const void* d_color_rgba8, const void* d_depth_r32f, const void* d_motion_rg32f, const void* d_mask_r8,
+                          float jitterX, float jitterY, float mvScaleX, float mvScaleY, int reset, void* d_out_rgba8, void* stream);
+void vrt_upscaler_destroy(vrt_upscaler*);
 
 /* ---- output stage (the step downstream of the pass): BlitStage::record running blit.frag, headless ----
  * d_src: sw x sh RGBA8 on the device (the colour or denoised plane of a full frame, or any RGBA8 image); d_dst: tw x th RGBA8 device

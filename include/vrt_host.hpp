@@ -271,12 +271,41 @@ public:
     float jitterX = 0.0f, jitterY = 0.0f;
     int frameCount = 0;
     explicit UpscalerStage(const std::shared_ptr<VoxelRenderSettings>& settings) : _settings(settings) {}
+    // UpscalerStage(engine, settings), upscaler_stage.cpp:18: with an engine the stage can also record() its pass
+    UpscalerStage(const std::shared_ptr<Engine>& engine, const std::shared_ptr<VoxelRenderSettings>& settings) : _settings(settings), _engine(engine) {}
+    ~UpscalerStage() { if (_up) vrt_upscaler_destroy(_up); if (_engine && _target.devicePtr) vrt_buffer_free(_engine->handle(), _target.devicePtr); }
+    UpscalerStage(const UpscalerStage&) = delete;
+    UpscalerStage& operator=(const UpscalerStage&) = delete;
     void update(float /*delta*/) {
         check(vrt_upscaler_update((int)_settings->renderResolution()[0], (int)_settings->targetResolution[0], &frameCount, &jitterX, &jitterY),
               "UpscalerStage::update");
     }
+    // UpscalerStage::record (upscaler_stage.cpp:78-172): colour, depth, motion and the reactive mask of the render resolution in, the
+    // target-resolution image out. The reference dispatches FSR2 here (closed source); this is libvrt's own temporal upscaler.
+    const RenderImage& record(const RenderImage& color, const RenderImage& depth, const RenderImage& motion, const RenderImage& mask) {
+        if (!_engine) throw std::runtime_error("UpscalerStage::record needs the engine constructor");
+        const int rw = (int)_settings->renderResolution()[0], rh = (int)_settings->renderResolution()[1];
+        const int tw = (int)_settings->targetResolution[0], th = (int)_settings->targetResolution[1];
+        if (!_up || _rw != rw || _rh != rh || _tw != tw || _th != th) {   // RENDER_RESIZE / TARGET_RESIZE
+            if (_up) { vrt_upscaler_destroy(_up); _up = nullptr; }
+            if (_target.devicePtr) { vrt_buffer_free(_engine->handle(), _target.devicePtr); _target.devicePtr = nullptr; }
+            check(vrt_upscaler_create(_engine->handle(), rw, rh, tw, th, &_up), "UpscalerStage");
+            _target.bytes = (size_t)tw * th * 4; _tw = tw; _th = th;
+            check(vrt_buffer_alloc(_engine->handle(), _target.bytes, &_target.devicePtr), "UpscalerStage target");
+            _rw = rw; _rh = rh; _first = true;
+        }
+        check(vrt_upscaler_dispatch(_up, color.devicePtr, depth.devicePtr, motion.devicePtr, mask.devicePtr, jitterX, jitterY, 1.0f, 1.0f, _first ? 1 : 0,
+                                    _target.devicePtr, nullptr), "UpscalerStage::record");
+        _first = false;
+        return _target;
+    }
 private:
     std::shared_ptr<VoxelRenderSettings> _settings;
+    std::shared_ptr<Engine> _engine;
+    vrt_upscaler* _up = nullptr;
+    RenderImage _target{};
+    int _rw = 0, _rh = 0, _tw = 0, _th = 0;
+    bool _first = true;
 };
 
 // BlitStage::record (blit_stage.cpp:25-57): the final image, sampled LINEAR / CLAMP_TO_EDGE, scaled to fill the window and centre-cropped

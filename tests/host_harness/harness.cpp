@@ -105,10 +105,32 @@ static void build_odist(const uint8_t* vol, int W, int H, int D, std::vector<uin
     }
 }
 
+// CPU restatement of the two-level layout (csrc/vrt_octant.cu sp_classify_kernel / sp_fill_kernel) from an octant's linear field
+static void build_sdist(const std::vector<uint8_t>& lin, int W, int H, int D, const uint32_t tb[3], std::vector<uint32_t>& top, std::vector<uint8_t>& fine) {
+    auto code = [&](int x, int y, int z) -> uint32_t {
+        if (x < -1 || y < -1 || z < -1 || x > W || y > H || z > D) return VRT_LIN_OOB;
+        return lin[(size_t)(x + 1) + (size_t)(y + 1) * (W + 2) + (size_t)(z + 1) * (W + 2) * (H + 2)]; };
+    top.assign((size_t)tb[0] * tb[1] * tb[2], 0u); fine.clear();
+    for (uint32_t bz = 0; bz < tb[2]; bz++) for (uint32_t by = 0; by < tb[1]; by++) for (uint32_t bx = 0; bx < tb[0]; bx++) {
+        uint8_t c[512]; uint32_t mn = 0xffffffffu; bool same = true, special = false;
+        for (int k = 0; k < 512; k++) {
+            c[k] = (uint8_t)code((int)bx * 8 - 8 + (k & 7), (int)by * 8 - 8 + ((k >> 3) & 7), (int)bz * 8 - 8 + (k >> 6));
+            same = same && c[k] == c[0]; special = special || c[k] == 0 || c[k] == VRT_LIN_OOB;
+            mn = std::min(mn, safe_decode(c[k]));
+        }
+        uint32_t e;
+        if (same) e = c[0];
+        else if (!special && mn >= VRT_SP_UNIFORM_MIN) e = safe_encode(mn);
+        else { e = VRT_SP_FINE | (uint32_t)(fine.size() / 512); fine.insert(fine.end(), c, c + 512); }
+        top[bx + (by + (size_t)bz * tb[1]) * tb[0]] = e;
+    }
+}
+
 struct HScene {
     SceneDev dev;
     std::vector<unsigned long long> bmask;
-    std::vector<uint8_t> bdist, fdist, ldist, odist[8];
+    std::vector<uint8_t> bdist, fdist, ldist, odist[8], sfine[8];
+    std::vector<uint32_t> stop[8];
 };
 
 extern "C" void* hh_scene_create(const uint8_t* vol, uint32_t W, uint32_t H, uint32_t D, const float* palette,
@@ -121,6 +143,12 @@ extern "C" void* hh_scene_create(const uint8_t* vol, uint32_t W, uint32_t H, uin
     s->dev.bmask = s->bmask.data(); s->dev.bdist = s->bdist.data(); s->dev.fdist = s->fdist.data(); s->dev.ldist = s->ldist.data();
     build_odist(vol, (int)W, (int)H, (int)D, s->odist);
     for (int o = 0; o < 8; o++) s->dev.odist[o] = s->odist[o].data();
+    uint32_t tb[3] = {((W + 8u) >> 3) + 1u, ((H + 8u) >> 3) + 1u, ((D + 8u) >> 3) + 1u};
+    s->dev.TBx = tb[0]; s->dev.TBy = tb[1]; s->dev.TBz = tb[2];
+    for (int o = 0; o < 8; o++) {
+        build_sdist(s->odist[o], (int)W, (int)H, (int)D, tb, s->stop[o], s->sfine[o]);
+        s->dev.sdist[o].top = s->stop[o].data(); s->dev.sdist[o].fine = s->sfine[o].data();
+    }
     s->dev.palette = reinterpret_cast<const vrt_material*>(palette);
     s->dev.noise = noise; s->dev.sky = sky; s->dev.skyW = skyW; s->dev.skyH = skyH;
     return s;
@@ -148,6 +176,7 @@ extern "C" int hh_render(void* scene, const vrt_camera* cam, const vrt_render_se
             else if (traversal == VRT_TRAVERSAL_FINE) render_pixel<VRT_TRAVERSAL_FINE>(s->dev, fp, px, py, o);
             else if (traversal == VRT_TRAVERSAL_LINEAR) render_pixel<VRT_TRAVERSAL_LINEAR>(s->dev, fp, px, py, o);
             else if (traversal == VRT_TRAVERSAL_OCTANT) render_pixel<VRT_TRAVERSAL_OCTANT>(s->dev, fp, px, py, o);
+            else if (traversal == VRT_TRAVERSAL_SPARSE) render_pixel<VRT_TRAVERSAL_SPARSE>(s->dev, fp, px, py, o);
             else render_pixel<VRT_TRAVERSAL_BRICK>(s->dev, fp, px, py, o);
             size_t p = (size_t)py * W + px;
             auto sat = [](int v) { return (int16_t)(v < -32768 ? -32768 : (v > 32767 ? 32767 : v)); };
@@ -249,6 +278,7 @@ extern "C" int hh_render_wave(void* scene, const vrt_camera* cam, const vrt_rend
     else if (traversal == VRT_TRAVERSAL_FINE) render_wave<VRT_TRAVERSAL_FINE>(s->dev, fp, pl, row_begin, row_end, row_step);
     else if (traversal == VRT_TRAVERSAL_LINEAR) render_wave<VRT_TRAVERSAL_LINEAR>(s->dev, fp, pl, row_begin, row_end, row_step);
     else if (traversal == VRT_TRAVERSAL_OCTANT) render_wave<VRT_TRAVERSAL_OCTANT>(s->dev, fp, pl, row_begin, row_end, row_step);
+    else if (traversal == VRT_TRAVERSAL_SPARSE) render_wave<VRT_TRAVERSAL_SPARSE>(s->dev, fp, pl, row_begin, row_end, row_step);
     else render_wave<VRT_TRAVERSAL_BRICK>(s->dev, fp, pl, row_begin, row_end, row_step);
     return 0;
 }
@@ -278,6 +308,8 @@ extern "C" int hh_render_shard(void* scene, const vrt_camera* cam, const vrt_ren
                 PixelOut o; memset(&o, 0, sizeof(o));
                 if (traversal == VRT_TRAVERSAL_LINEAR) render_pixel<VRT_TRAVERSAL_LINEAR>(s->dev, fp, px, py, o);
                 else if (traversal == VRT_TRAVERSAL_OCTANT) render_pixel<VRT_TRAVERSAL_OCTANT>(s->dev, fp, px, py, o);
+                else if (traversal == VRT_TRAVERSAL_SPARSE) render_pixel<VRT_TRAVERSAL_SPARSE>(s->dev, fp, px, py, o);
+            else if (traversal == VRT_TRAVERSAL_SPARSE) render_pixel<VRT_TRAVERSAL_SPARSE>(s->dev, fp, px, py, o);
                 else render_pixel<VRT_TRAVERSAL_FINE>(s->dev, fp, px, py, o);
                 uint8_t* q = color_tiles + 4 * plane_index(fp, px, py);
                 q[0] = to_unorm8(o.color.x); q[1] = to_unorm8(o.color.y); q[2] = to_unorm8(o.color.z); q[3] = 0;
@@ -292,6 +324,13 @@ extern "C" void hh_assemble(const uint8_t* gathered, int world, int W, int H, si
             memcpy(out + 4 * ((size_t)py * W + px), gathered + 4 * gathered_index(px, py, tilesX, world, shard_pixels), 4);
 }
 
+// the sparse field of an octant expanded to the aproned linear layout (what vrt_scene_download_sdist returns)
+extern "C" void hh_scene_sdist(void* p, int octant, uint8_t* out) {
+    HScene* s = (HScene*)p;
+    const int W = (int)s->dev.W, H = (int)s->dev.H, D = (int)s->dev.D;
+    for (int z = -1; z <= D; z++) for (int y = -1; y <= H; y++) for (int x = -1; x <= W; x++)
+        out[(size_t)(x + 1) + (size_t)(y + 1) * (W + 2) + (size_t)(z + 1) * (W + 2) * (H + 2)] = (uint8_t)sparse_fetch(s->dev, s->dev.sdist[octant], x, y, z);
+}
 extern "C" void hh_scene_odist(void* p, int octant, uint8_t* out) { HScene* s = (HScene*)p; memcpy(out, s->odist[octant].data(), s->odist[octant].size()); }
 
 // the output stage's per-pixel code (csrc/vrt_output.cuh) in the loop structure of blit_kernel

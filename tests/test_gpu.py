@@ -151,6 +151,13 @@ def test_brick_levels_match_cpu_builder(gpu_ctx):
             o2 = np.zeros((whd[2] + 2, whd[1] + 2, whd[0] + 2), np.uint8)
             h.hh_scene_odist(C.c_void_p(hs), o, o2.ctypes.data_as(C.c_void_p))
             assert np.array_equal(gs.download_odist(o), o2), f"odist octant {o} differs for {whd}"
+            s2 = np.zeros_like(o2)                            # two-level layout: the GPU's classification + fill == the CPU restatement
+            h.hh_scene_sdist(C.c_void_p(hs), o, s2.ctypes.data_as(C.c_void_p))
+            sd = gs.download_sdist(o)
+            assert np.array_equal(sd, s2), f"sparse field octant {o} differs for {whd}"
+            dec = lambda a: np.where(a < 128, a.astype(np.int32), a.astype(np.int32) * 4 - 384)
+            inside = (o2 != 0) & (o2 != 255)
+            assert np.array_equal(sd == 0, o2 == 0) and np.array_equal(sd == 255, o2 == 255) and (dec(sd)[inside] <= dec(o2)[inside]).all() and (dec(sd)[inside] >= 1).all()
         h.hh_scene_destroy(C.c_void_p(hs))
         gs.destroy()
 
@@ -163,7 +170,8 @@ def test_dense_and_brick_traversal_identical_at_4k(gpu_ctx):
     st = O.make_settings()
     a = gpu_render(gpu_ctx, gs, cam, st, TRAV_DENSE, pipeline=pyvrt.PIPELINE_MEGAKERNEL)
     for trav, pipe in ((TRAV_BRICK, pyvrt.PIPELINE_MEGAKERNEL), (TRAV_FINE, pyvrt.PIPELINE_MEGAKERNEL), (TRAV_FINE, pyvrt.PIPELINE_WAVEFRONT),
-                       (TRAV_DENSE, pyvrt.PIPELINE_WAVEFRONT), (4, pyvrt.PIPELINE_WAVEFRONT), (5, pyvrt.PIPELINE_WAVEFRONT), (5, pyvrt.PIPELINE_MEGAKERNEL)):
+                       (TRAV_DENSE, pyvrt.PIPELINE_WAVEFRONT), (4, pyvrt.PIPELINE_WAVEFRONT), (5, pyvrt.PIPELINE_WAVEFRONT), (5, pyvrt.PIPELINE_MEGAKERNEL),
+                       (6, pyvrt.PIPELINE_WAVEFRONT), (6, pyvrt.PIPELINE_MEGAKERNEL)):
         b = gpu_render(gpu_ctx, gs, cam, st, trav, pipeline=pipe)
         for n, _, _ in O.PLANE_SPECS:
             ok, bad = bits_equal(a[n], b[n]); assert ok, (trav, pipe, n, bad)
@@ -189,7 +197,7 @@ def test_production_frames_equal_instrumented_frames(gpu_ctx):
     st = O.make_settings()
     want = O.render(sc, cam, st)
     names = ["color", "depth", "motion", "mask", "position", "normal"]
-    for trav in (4, 5):
+    for trav in (4, 5, 6):
         for pipe in PIPELINES:
             rp = pyvrt.VoxelRenderPass(gpu_ctx, gs, vrt_settings(st, trav, out_mask=pyvrt.OUT_GBUFFER, pipeline=pipe))
             fr = rp.record(cam_to_py(cam)); fr.sync()
@@ -538,3 +546,62 @@ def test_standalone_denoise_fractional_step_width(gpu_ctx, step_width):
             d = np.abs(out.cpu().numpy().astype(int) - want.astype(int))
             assert d.max() <= 1 and (d != 0).mean() < 2e-3, (mode, iters, d.max(), (d != 0).mean())
     assert not np.array_equal(want, O.denoise(color, normal, pos, iterations=3, step_width=float(round(step_width)) or 1.0, mode=1))
+
+
+def test_temporal_upscaler_own_definition_properties(gpu_ctx):
+    """SURVEY 8(f) N4, parity unpinned (FSR2 is closed source: own definition, csrc/vrt_upscale.cu). Tested properties: exact pass-through
+    at scale 1 / jitter (0, 0) (first frame and steady state); determinism; with the Halton jitter of the frame driver a static scene
+    rendered at half resolution converges towards the full-resolution image (better than a single bilinear frame); reset drops the history."""
+    import torch
+    rng = np.random.default_rng(5)
+    w, h = 321, 187
+    img = rng.integers(0, 256, (h, w, 4), dtype=np.uint8); img[..., 3] = 0
+    t = torch.from_numpy(img).cuda()
+    up = pyvrt.TemporalUpscaler(gpu_ctx, (w, h), (w, h))
+    out = torch.zeros_like(t)
+    torch.cuda.synchronize()
+    for k in range(3):                                     # pass-through, first frame and with history
+        up.dispatch(t.data_ptr(), out.data_ptr(), reset=(k == 0)); gpu_ctx.sync()
+        assert np.array_equal(out.cpu().numpy(), img), k
+    up.destroy()
+
+    # a static analytic scene "rendered" at half resolution with the frame driver's jitter, upscaled 2x
+    TW, TH, RW, RH = 512, 288, 256, 144
+    def scene(x, y):                                        # continuous position in target pixels -> rgb in [0, 1]
+        return np.stack([0.5 + 0.5 * np.sin(x * 0.11) * np.cos(y * 0.07), 0.5 + 0.5 * np.sin((x + y) * 0.05), ((np.floor(x / 16) + np.floor(y / 16)) % 2) * 0.8 + 0.1], axis=-1)
+    ty, tx = np.mgrid[0:TH, 0:TW]
+    truth = scene(tx + 0.5, ty + 0.5)
+    def render(jx, jy):
+        ry, rx = np.mgrid[0:RH, 0:RW]
+        c = scene((rx + 0.5 - jx) * (TW / RW), (ry + 0.5 + jy) * (TH / RH))          # sample (i, j) sits at (i + 0.5 - jx, j + 0.5 + jy)
+        a = np.zeros((RH, RW, 4), np.uint8); a[..., :3] = np.rint(c * 255).astype(np.uint8)
+        return a
+    def run(frames):
+        u = pyvrt.TemporalUpscaler(gpu_ctx, (RW, RH), (TW, TH))
+        stage = pyvrt.UpscalerStage(RW, TW)
+        o = torch.zeros((TH, TW, 4), dtype=torch.uint8, device="cuda")
+        outs = []
+        for k in range(frames):
+            stage.update(0.016)
+            src = torch.from_numpy(render(float(stage.jitterX), float(stage.jitterY))).cuda()
+            torch.cuda.synchronize()
+            u.dispatch(src.data_ptr(), o.data_ptr(), jitter=(float(stage.jitterX), float(stage.jitterY)), reset=(k == 0)); gpu_ctx.sync()
+            outs.append(o.cpu().numpy().copy())
+        u.destroy()
+        return outs
+    a, b = run(24), run(24)
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)                          # deterministic
+    err = [np.abs(x[..., :3] / 255.0 - truth).mean() for x in a]
+    assert err[-1] < 0.6 * err[0] and err[-1] < err[4]        # accumulation of jittered frames beats the single first frame
+    # reset: the first frame of a new sequence does not depend on the history
+    u = pyvrt.TemporalUpscaler(gpu_ctx, (RW, RH), (TW, TH))
+    o = torch.zeros((TH, TW, 4), dtype=torch.uint8, device="cuda")
+    src = torch.from_numpy(render(0.25, -0.125)).cuda()
+    other = torch.from_numpy(render(-0.3, 0.2)).cuda()
+    torch.cuda.synchronize()
+    u.dispatch(src.data_ptr(), o.data_ptr(), jitter=(0.25, -0.125), reset=True); gpu_ctx.sync(); first = o.cpu().numpy().copy()
+    u.dispatch(other.data_ptr(), o.data_ptr(), jitter=(-0.3, 0.2)); gpu_ctx.sync()
+    u.dispatch(src.data_ptr(), o.data_ptr(), jitter=(0.25, -0.125), reset=True); gpu_ctx.sync()
+    assert np.array_equal(o.cpu().numpy(), first)
+    u.destroy()

@@ -20,8 +20,8 @@ HARNESS_DIR = os.path.join(ROOT, "tests", "host_harness")
 HARNESS_LIB = os.path.join(HARNESS_DIR, "libvrt_hostharness.so")
 CACHE = os.environ.get("VRT_ASSET_CACHE", "/tmp/vrt_assets")
 
-TRAV_DENSE, TRAV_BRICK, TRAV_FINE, TRAV_LINEAR, TRAV_OCTANT = 1, 2, 3, 4, 5
-ALL_TRAVERSALS = (TRAV_DENSE, TRAV_BRICK, TRAV_FINE, TRAV_LINEAR, TRAV_OCTANT)
+TRAV_DENSE, TRAV_BRICK, TRAV_FINE, TRAV_LINEAR, TRAV_OCTANT, TRAV_SPARSE = 1, 2, 3, 4, 5, 6
+ALL_TRAVERSALS = (TRAV_DENSE, TRAV_BRICK, TRAV_FINE, TRAV_LINEAR, TRAV_OCTANT, TRAV_SPARSE)
 
 
 class VrtCamera(C.Structure):   # include/vrt.h vrt_camera

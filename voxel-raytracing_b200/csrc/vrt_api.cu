@@ -117,7 +117,7 @@ extern "C" int vrt_buffer_download(vrt_context* c, const void* d_src, void* host
 extern "C" void vrt_scene_destroy(vrt_scene* s) {
     if (!s) return;
     cudaSetDevice(s->ctx->device);
-    cudaFree(s->vol); cudaFree(s->bmask); cudaFree(s->bdist); cudaFree(s->fdist); cudaFree(s->ldist); for (uint8_t* p : s->odist) cudaFree(p); cudaFree(s->palette); cudaFree(s->noise); cudaFree(s->sky);
+    cudaFree(s->vol); cudaFree(s->bmask); cudaFree(s->bdist); cudaFree(s->fdist); cudaFree(s->ldist); for (uint8_t* p : s->odist) cudaFree(p); for (uint32_t* p : s->stop) cudaFree(p); for (uint8_t* p : s->sfine) cudaFree(p); cudaFree(s->palette); cudaFree(s->noise); cudaFree(s->sky);
     delete s;
 }
 
@@ -204,16 +204,68 @@ static int scene_ensure_octant(vrt_scene* s) {
     s->fieldBytes += 8 * fieldBytes;
     return VRT_OK;
 }
+// two-level (sparse) directional fields: every octant's linear field is built into ONE scratch buffer in turn and compacted
+// (top level + per-voxel bricks near surfaces only); what stays resident is a few per cent of the eight linear fields
+static int scene_ensure_sparse(vrt_scene* s) {
+    if (s->sparseReady) return VRT_OK;
+    vrt_context* c = s->ctx;
+    const size_t fieldBytes = (size_t)(s->w + 2) * (s->h + 2) * (s->d + 2), scratchBytes = octant_scratch_bytes(s->w, s->h, s->d);
+    sparse_top_dims(s->w, s->h, s->d, s->TB);
+    const size_t topWords = (size_t)s->TB[0] * s->TB[1] * s->TB[2];
+    uint32_t *scratch = nullptr, *counter = nullptr; uint8_t* lin = nullptr;
+    size_t added = 0;
+    cudaError_t e = cudaMalloc(&scratch, scratchBytes);
+    if (e == cudaSuccess) e = cudaMalloc(&lin, fieldBytes);
+    if (e == cudaSuccess) e = cudaMalloc(&counter, sizeof(uint32_t));
+    if (e == cudaSuccess) e = launch_odist_init(s->vol, s->w, s->h, s->d, scratch, c->stream, &s->accelLaunches);
+    for (int o = 0; o < 8 && e == cudaSuccess; o++) {
+        e = launch_odist_octant(s->w, s->h, s->d, o, lin, scratch, c->stream, &s->accelLaunches);
+        if (e == cudaSuccess) e = cudaMalloc(&s->stop[o], topWords * sizeof(uint32_t));
+        if (e == cudaSuccess) e = cudaMemsetAsync(counter, 0, sizeof(uint32_t), c->stream);
+        if (e == cudaSuccess) e = launch_sparse_classify(lin, s->w, s->h, s->d, s->stop[o], counter, c->stream);
+        uint32_t n = 0;
+        if (e == cudaSuccess) e = cudaMemcpyAsync(&n, counter, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+        if (e == cudaSuccess && n) e = cudaMalloc(&s->sfine[o], (size_t)n * 512u);
+        if (e == cudaSuccess && n) e = launch_sparse_fill(lin, s->w, s->h, s->d, s->stop[o], s->sfine[o], c->stream);
+        s->sfineBricks[o] = n;
+        s->accelLaunches += 2;
+        added += topWords * sizeof(uint32_t) + (size_t)n * 512u;
+    }
+    const cudaError_t e2 = cudaStreamSynchronize(c->stream);
+    cudaFree(scratch); cudaFree(lin); cudaFree(counter);
+    if (e == cudaSuccess) e = e2;
+    if (e != cudaSuccess) {
+        for (int o = 0; o < 8; o++) { cudaFree(s->stop[o]); cudaFree(s->sfine[o]); s->stop[o] = nullptr; s->sfine[o] = nullptr; s->sfineBricks[o] = 0; }
+        return cuda_fail(e);
+    }
+    s->peakBuildBytes = std::max(s->peakBuildBytes, s->fieldBytes + added + fieldBytes + scratchBytes);
+    s->fieldBytes += added;
+    s->sparseReady = true;
+    return VRT_OK;
+}
+// the library's choice when the caller says VRT_TRAVERSAL_DEFAULT: the linear directional fields while eight of them fit a budget,
+// the two-level layout beyond it (VRT_DEFAULT_TRAVERSAL / VRT_FIELD_BUDGET_GIB override, for measurement)
+static uint32_t resolve_traversal(const vrt_scene* s, uint32_t traversal) {
+    if (traversal != VRT_TRAVERSAL_DEFAULT) return traversal;
+    static const int forced = getenv("VRT_DEFAULT_TRAVERSAL") ? atoi(getenv("VRT_DEFAULT_TRAVERSAL")) : 0;
+    if (forced >= VRT_TRAVERSAL_DENSE_U8 && forced <= VRT_TRAVERSAL_SPARSE) return (uint32_t)forced;
+    static const double budgetGiB = getenv("VRT_FIELD_BUDGET_GIB") ? atof(getenv("VRT_FIELD_BUDGET_GIB")) : 16.0;
+    const double linearGiB = 8.0 * (double)(s->w + 2) * (double)(s->h + 2) * (double)(s->d + 2) / 1073741824.0;
+    return linearGiB <= budgetGiB ? (uint32_t)VRT_TRAVERSAL_OCTANT : (uint32_t)VRT_TRAVERSAL_SPARSE;
+}
+
 static int scene_ensure(vrt_scene* s, uint32_t traversal) {
     std::lock_guard<std::mutex> lock(s->fieldMutex);
     const double t0 = now_ms();
     int rc = VRT_OK;
-    switch (traversal == VRT_TRAVERSAL_DEFAULT ? (uint32_t)VRT_TRAVERSAL_OCTANT : traversal) {
+    switch (resolve_traversal(s, traversal)) {
         case VRT_TRAVERSAL_DENSE_U8: break;
         case VRT_TRAVERSAL_BRICK: rc = scene_ensure_bricks(s); break;
         case VRT_TRAVERSAL_FINE: rc = scene_ensure_iso(s, true, false); break;
         case VRT_TRAVERSAL_LINEAR: rc = scene_ensure_iso(s, false, true); break;
         case VRT_TRAVERSAL_OCTANT: rc = scene_ensure_octant(s); break;
+        case VRT_TRAVERSAL_SPARSE: rc = scene_ensure_sparse(s); break;
         default: rc = fail(VRT_E_INVALID, "unknown traversal");
     }
     s->loadMs += now_ms() - t0;
@@ -402,6 +454,21 @@ extern "C" int vrt_scene_download_odist(const vrt_scene* s, int octant, uint8_t*
     return VRT_OK;
 }
 
+extern "C" int vrt_scene_download_sdist(const vrt_scene* s, int octant, uint8_t* dst, size_t bytes) {
+    if (!s || !dst || octant < 0 || octant > 7 || bytes != (size_t)(s->w + 2) * (s->h + 2) * (s->d + 2)) return fail(VRT_E_INVALID, "bad argument");
+    CU(cudaSetDevice(s->ctx->device));
+    const int rc = scene_ensure(const_cast<vrt_scene*>(s), VRT_TRAVERSAL_SPARSE);
+    if (rc) return rc;
+    uint8_t* tmp = nullptr;
+    CU(cudaMalloc(&tmp, bytes));
+    cudaError_t e = launch_sparse_expand(s->stop[octant], s->sfine[octant], s->w, s->h, s->d, tmp, s->ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dst, tmp, bytes, cudaMemcpyDeviceToHost, s->ctx->stream);
+    const cudaError_t e2 = cudaStreamSynchronize(s->ctx->stream);
+    cudaFree(tmp);
+    if (e != cudaSuccess || e2 != cudaSuccess) return cuda_fail(e != cudaSuccess ? e : e2);
+    return VRT_OK;
+}
+
 // ------------------------------------------------------------------------------------------------ frames
 extern "C" void vrt_frame_release(vrt_frame* f) {
     if (!f) return;
@@ -540,7 +607,7 @@ int vrt_render_impl(vrt_context* c, const vrt_scene* s, const vrt_camera* cam, c
     if (cam->volumeBounds[0] != s->w || cam->volumeBounds[1] != s->h || cam->volumeBounds[2] != s->d)
         return fail(VRT_E_INVALID, "camera volumeBounds differ from the scene bounds");
     if (!(st->pass_mask & VRT_PASS_PRIMARY)) return fail(VRT_E_INVALID, "pass_mask must include VRT_PASS_PRIMARY");
-    if (st->traversal > VRT_TRAVERSAL_OCTANT) return fail(VRT_E_INVALID, "unknown traversal");
+    if (st->traversal > VRT_TRAVERSAL_SPARSE) return fail(VRT_E_INVALID, "unknown traversal");
     if (st->pipeline > VRT_PIPELINE_WAVEFRONT) return fail(VRT_E_INVALID, "unknown pipeline");
     if (st->vol.aoSamples > 255) return fail(VRT_E_INVALID, "aoSamples must be <= 255 (the reference GUI allows 0..16)");
     const bool wavefront = st->pipeline != VRT_PIPELINE_MEGAKERNEL;
@@ -562,11 +629,12 @@ int vrt_render_impl(vrt_context* c, const vrt_scene* s, const vrt_camera* cam, c
         rc = frame_ensure_wave(f, (st->pass_mask & VRT_PASS_SHADE) ? ((st->pass_mask & VRT_PASS_AO) ? st->vol.aoSamples : 0u) + 1u : 0u);
     if (rc) { if (!*frame) vrt_frame_release(f); return rc; }
 
-    const uint32_t traversal = st->traversal == VRT_TRAVERSAL_DEFAULT ? VRT_TRAVERSAL_OCTANT : st->traversal;
+    const uint32_t traversal = resolve_traversal(s, st->traversal);
     rc = scene_ensure(const_cast<vrt_scene*>(s), traversal);   // a no-op once the back-end's fields exist (vrt_scene_prepare / load time)
     if (rc) { if (!*frame) vrt_frame_release(f); return rc; }
     SceneDev sc{};
-    for (int o = 0; o < 8; o++) sc.odist[o] = s->odist[o];
+    for (int o = 0; o < 8; o++) { sc.odist[o] = s->odist[o]; sc.sdist[o].top = s->stop[o]; sc.sdist[o].fine = s->sfine[o]; }
+    sc.TBx = s->TB[0]; sc.TBy = s->TB[1]; sc.TBz = s->TB[2];
     sc.vol = s->vol; sc.bmask = s->bmask; sc.bdist = s->bdist; sc.fdist = s->fdist; sc.ldist = s->ldist; sc.W = s->w; sc.H = s->h; sc.D = s->d; sc.Bx = s->Bx; sc.By = s->By; sc.Bz = s->Bz;
     sc.palette = s->palette; sc.noise = s->noise; sc.sky = s->sky; sc.skyW = s->skyW; sc.skyH = s->skyH;
     FrameParams fp{};

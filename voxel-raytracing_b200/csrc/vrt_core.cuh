@@ -226,6 +226,58 @@ VRT_HD void lin_map_pos(const LinRay& r, int& mx, int& my, int& mz) {
     mz = r.mz0 + lin_count(r.sz, r.sz0, r.az) * r.stz;
 }
 
+// ---- VRT_TRAVERSAL_SPARSE: the same resumable ray over the two-level directional fields (SceneDev::sdist) ----
+// The look-up needs the voxel itself (brick index + position inside the brick): per axis the entry coordinate plus the recovered step
+// count. One 4-byte load of the top level (L2-resident), and a second, dependent byte load only for bricks near a surface.
+VRT_HD uint32_t sparse_fetch(const SceneDev& sc, const SparseField& f, int x, int y, int z) {   // x in [-1, W], y in [-1, H], z in [-1, D]
+    const uint32_t X = (uint32_t)(x + 8), Y = (uint32_t)(y + 8), Z = (uint32_t)(z + 8);
+    const uint32_t e = f.top[(X >> 3) + ((Y >> 3) + (Z >> 3) * sc.TBy) * sc.TBx];
+    if (!(e & VRT_SP_FINE)) return e;
+    return f.fine[(size_t)(e & ~VRT_SP_FINE) * 512u + ((X & 7u) | ((Y & 7u) << 3) | ((Z & 7u) << 6))];
+}
+VRT_HD SparseField sparse_octant_field(const SceneDev& sc, const Dda& s) {
+    return sc.sdist[(s.stx < 0 ? 1 : 0) | (s.sty < 0 ? 2 : 0) | (s.stz < 0 ? 4 : 0)];
+}
+struct SpRay {
+    float sx, sy, sz, dx, dy, dz, sx0, sy0, sz0, ax, ay, az;   // as LinRay
+    SparseField f;
+    int mx0, my0, mz0, stx, sty, stz;
+    uint32_t i, maxSteps, mask;
+};
+VRT_HD int sp_begin(const SceneDev& sc, const Dda& s, V3 dir, uint32_t maxSteps, SpRay& r) {
+    r.sx = r.sx0 = s.sx; r.sy = r.sy0 = s.sy; r.sz = r.sz0 = s.sz;
+    r.dx = s.dx; r.dy = s.dy; r.dz = s.dz;
+    r.ax = fabsf(dir.x); r.ay = fabsf(dir.y); r.az = fabsf(dir.z);
+    r.mx0 = s.mx; r.my0 = s.my; r.mz0 = s.mz; r.stx = s.stx; r.sty = s.sty; r.stz = s.stz;
+    r.i = 0; r.maxSteps = maxSteps; r.mask = 0;
+    if (!in_bounds(sc, s)) return LIN_OOB;
+    r.f = sparse_octant_field(sc, s);
+    return LIN_CONTINUE;
+}
+VRT_HD void sp_map_pos(const SpRay& r, int& mx, int& my, int& mz) {
+    mx = r.mx0 + lin_count(r.sx, r.sx0, r.ax) * r.stx;
+    my = r.my0 + lin_count(r.sy, r.sy0, r.ay) * r.sty;
+    mz = r.mz0 + lin_count(r.sz, r.sz0, r.az) * r.stz;
+}
+template <bool STEP_REC>
+VRT_HD int sp_round(const SceneDev& sc, SpRay& r, const bool ANYHIT = false, const uint32_t roundCap = 512u) {
+    int x, y, z; sp_map_pos(r, x, y, z);
+    uint32_t n = sparse_fetch(sc, r.f, x, y, z);
+    if (n == 0) return LIN_HIT;
+    if (n == VRT_LIN_OOB) return LIN_OOB;
+    n = safe_decode(n);
+    const uint32_t left = r.maxSteps - r.i;
+    if (ANYHIT && n >= left) { r.i = r.maxSteps; return LIN_EXHAUSTED; }
+    n = n < left ? n : left;
+    n = n < roundCap ? n : roundCap;
+    r.i += n;
+    Dda d; d.sx = r.sx; d.sy = r.sy; d.sz = r.sz; d.dx = r.dx; d.dy = r.dy; d.dz = r.dz;
+    for (uint32_t k = n - 1; k > 0; k--) dda_step_f(d);
+    if (STEP_REC) r.mask = dda_step_f_rec(d); else dda_step_f(d);
+    r.sx = d.sx; r.sy = d.sy; r.sz = d.sz;
+    return r.i >= r.maxSteps ? LIN_EXHAUSTED : LIN_CONTINUE;
+}
+
 // traceRayInt + traceRay (:127-196). TRAVERSAL selects how voxel emptiness is learned; the float/int DDA state
 // evolves identically in every variant (one dda_step per reference iteration).
 // DDA set-up of traceRayInt (:131-150). Returns whether the fast select-form step may be used (finite deltaDist).
@@ -254,7 +306,7 @@ VRT_HD TraceRes trace_ray(const SceneDev& sc, V3 start, V3 dir, uint32_t maxStep
     uint32_t i = 0, mask = 0, material = 0;
     bool hit = false, oob = false;
     // a NaN / infinite start (origin built from a NaN normal) never moves: the literal loop replays that too
-    if (TRAVERSAL == VRT_TRAVERSAL_LINEAR || TRAVERSAL == VRT_TRAVERSAL_OCTANT) fast = lin_usable(fast, s);
+    if (TRAVERSAL == VRT_TRAVERSAL_LINEAR || TRAVERSAL == VRT_TRAVERSAL_OCTANT || TRAVERSAL == VRT_TRAVERSAL_SPARSE) fast = lin_usable(fast, s);
     if (!fast) {
         // literal loop: rays with a zero / denormal / NaN direction component
         for (; i < maxSteps; i++) {
@@ -277,6 +329,15 @@ VRT_HD TraceRes trace_ray(const SceneDev& sc, V3 start, V3 dir, uint32_t maxStep
         lin_map_pos(lr, s.mx, s.my, s.mz);
         s.sx = lr.sx; s.sy = lr.sy; s.sz = lr.sz;
         i = lr.i; mask = lr.mask;
+        if (st == LIN_HIT) { material = fetch_voxel(sc, s); hit = true; }
+        else if (st == LIN_OOB) oob = true;
+    } else if (TRAVERSAL == VRT_TRAVERSAL_SPARSE) {
+        SpRay sr;
+        int st = sp_begin(sc, s, dir, maxSteps, sr);
+        while (st == LIN_CONTINUE) st = sp_round<true>(sc, sr, anyhit, roundCap);
+        sp_map_pos(sr, s.mx, s.my, s.mz);
+        s.sx = sr.sx; s.sy = sr.sy; s.sz = sr.sz;
+        i = sr.i; mask = sr.mask;
         if (st == LIN_HIT) { material = fetch_voxel(sc, s); hit = true; }
         else if (st == LIN_OOB) oob = true;
     } else if (TRAVERSAL == VRT_TRAVERSAL_FINE) {

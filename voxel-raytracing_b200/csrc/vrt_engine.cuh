@@ -38,7 +38,24 @@ struct EngRay {
     LinRay l;                            // l.i is not used here
     int rem;                             // steps that may still run before the field must be looked at again
     uint32_t left;                       // maxSteps - steps taken - rem
+    SparseField f;                       // VRT_TRAVERSAL_SPARSE: the two-level field of the ray's octant (l.p0 / l.SX.. are unused then)
 };
+// VRT_TRAVERSAL_SPARSE keeps the entry voxel and the octant instead of a pointer into a linear field: packed into the stash's pointer slot
+__device__ __forceinline__ const uint8_t* engine_pack_entry(int mx, int my, int mz, uint32_t oct) {
+    return reinterpret_cast<const uint8_t*>((unsigned long long)(uint32_t)mx | ((unsigned long long)(uint32_t)my << 16) | ((unsigned long long)(uint32_t)mz << 32) | ((unsigned long long)oct << 48));
+}
+// entry state of a ray for the sparse back-end in LinRay form (SX/SY/SZ carry only the step signs); LIN_OOB when it starts outside
+__device__ __forceinline__ int engine_begin_sparse(const SceneDev& sc, const Dda& s, V3 dir, uint32_t maxSteps, LinRay& r) {
+    r.sx = r.sx0 = s.sx; r.sy = r.sy0 = s.sy; r.sz = r.sz0 = s.sz;
+    r.dx = s.dx; r.dy = s.dy; r.dz = s.dz;
+    r.ax = fabsf(dir.x); r.ay = fabsf(dir.y); r.az = fabsf(dir.z);
+    r.mx0 = s.mx; r.my0 = s.my; r.mz0 = s.mz; r.stx = s.stx; r.sty = s.sty; r.stz = s.stz;
+    r.SX = s.stx; r.SY = s.sty; r.SZ = s.stz; r.T0 = 0;
+    r.i = 0; r.maxSteps = maxSteps; r.mask = 0;
+    if (!in_bounds(sc, s)) return LIN_OOB;
+    r.p0 = engine_pack_entry(s.mx, s.my, s.mz, (s.stx < 0 ? 1u : 0u) | (s.sty < 0 ? 2u : 0u) | (s.stz < 0 ? 4u : 0u));
+    return LIN_CONTINUE;
+}
 
 // SoA of 16-byte quads: lanes popping consecutive entries read consecutive quads
 struct alignas(16) EngineStash {
@@ -59,7 +76,8 @@ __device__ __forceinline__ void engine_push(EngineStash& st, uint32_t slot, cons
     st.p[slot] = make_uint2((uint32_t)p, (uint32_t)(p >> 32));
 }
 
-__device__ __forceinline__ void engine_pop(const EngineStash& st, uint32_t slot, EngRay& e, int LW, int LWH, uint32_t& u0, uint32_t& u1) {
+template <bool SPARSE>
+__device__ __forceinline__ void engine_pop(const EngineStash& st, uint32_t slot, EngRay& e, int LW, int LWH, uint32_t& u0, uint32_t& u1, const SparseField* octFields) {
     const float4 s = st.s[slot], d = st.d[slot], a = st.a[slot];
     const uint2 p = st.p[slot];
     const uint32_t flags = __float_as_uint(s.w);
@@ -69,9 +87,15 @@ __device__ __forceinline__ void engine_pop(const EngineStash& st, uint32_t slot,
     r.ax = a.x; r.ay = a.y; r.az = a.z;
     u0 = __float_as_uint(d.w); u1 = __float_as_uint(a.w);
     r.maxSteps = (flags >> 8) & 0xfffu;
-    r.SX = (flags & 1u) ? -1 : 1; r.SY = (flags & 2u) ? -LW : LW; r.SZ = (flags & 4u) ? -LWH : LWH;
-    r.T0 = (int)(0u - (uint32_t)VRT_LIN_MAGIC_BITS * (uint32_t)(r.SX + r.SY));
-    r.p0 = reinterpret_cast<const uint8_t*>((unsigned long long)p.x | ((unsigned long long)p.y << 32));
+    if (SPARSE) {
+        r.stx = (flags & 1u) ? -1 : 1; r.sty = (flags & 2u) ? -1 : 1; r.stz = (flags & 4u) ? -1 : 1;
+        r.mx0 = (int)(p.x & 0xffffu); r.my0 = (int)(p.x >> 16); r.mz0 = (int)(p.y & 0xffffu);
+        e.f = octFields[(p.y >> 16) & 7u];
+    } else {
+        r.SX = (flags & 1u) ? -1 : 1; r.SY = (flags & 2u) ? -LW : LW; r.SZ = (flags & 4u) ? -LWH : LWH;
+        r.T0 = (int)(0u - (uint32_t)VRT_LIN_MAGIC_BITS * (uint32_t)(r.SX + r.SY));
+        r.p0 = reinterpret_cast<const uint8_t*>((unsigned long long)p.x | ((unsigned long long)p.y << 32));
+    }
     e.rem = (int)(flags >> 20); e.left = r.maxSteps - (flags >> 20);
 }
 
@@ -79,14 +103,20 @@ enum { ENG_GO = 0, ENG_HIT = 1, ENG_OOB = 2, ENG_EXHAUSTED = 3 };
 
 // Look-up for a lane whose budget is spent (rem == 0). Mirrors the loop head of traceRayInt (:152-162): i < maxSteps, bounds
 // test, getVoxel != 0. On ENG_GO the budget is re-armed with min(safe steps, steps left).
-__device__ __forceinline__ int engine_lookup(EngRay& e) {
+template <bool SPARSE>
+__device__ __forceinline__ int engine_lookup(EngRay& e, const SceneDev& sc) {
     if (e.left == 0u) return ENG_EXHAUSTED;
     const LinRay& r = e.l;
-    const int bx = lin_bits(r.sx, r.sx0, r.ax), by = lin_bits(r.sy, r.sy0, r.ay), bz = lin_bits(r.sz, r.sz0, r.az);
-    const int t = (int)((uint32_t)bx * (uint32_t)r.SX + (uint32_t)by * (uint32_t)r.SY + (uint32_t)r.T0);
-    const long long off = (long long)(bz - VRT_LIN_MAGIC_BITS) * (long long)r.SZ + (long long)t;
     uint32_t n;
-    asm("ld.global.nc.u8 %0, [%1];" : "=r"(n) : "l"(r.p0 + off));
+    if (SPARSE) {
+        const int x = r.mx0 + lin_count(r.sx, r.sx0, r.ax) * r.stx, y = r.my0 + lin_count(r.sy, r.sy0, r.ay) * r.sty, z = r.mz0 + lin_count(r.sz, r.sz0, r.az) * r.stz;
+        n = sparse_fetch(sc, e.f, x, y, z);
+    } else {
+        const int bx = lin_bits(r.sx, r.sx0, r.ax), by = lin_bits(r.sy, r.sy0, r.ay), bz = lin_bits(r.sz, r.sz0, r.az);
+        const int t = (int)((uint32_t)bx * (uint32_t)r.SX + (uint32_t)by * (uint32_t)r.SY + (uint32_t)r.T0);
+        const long long off = (long long)(bz - VRT_LIN_MAGIC_BITS) * (long long)r.SZ + (long long)t;
+        asm("ld.global.nc.u8 %0, [%1];" : "=r"(n) : "l"(r.p0 + off));
+    }
     if (n - 1u >= 254u) return n == 0u ? ENG_HIT : ENG_OOB;
     n = safe_decode(n);
     // any-hit: a budget that covers all remaining steps ends the ray as a miss after maxSteps getVoxel calls (see lin_round)

@@ -34,6 +34,11 @@ struct vrt_scene {
     uint32_t w = 0, h = 0, d = 0, Bx = 0, By = 0, Bz = 0;
     uint8_t* vol = nullptr; unsigned long long* bmask = nullptr; uint8_t* bdist = nullptr; uint8_t* fdist = nullptr; uint8_t* ldist = nullptr;
     uint8_t* odist[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    uint32_t* stop[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // two-level directional fields: top level
+    uint8_t* sfine[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   //   per-voxel bricks (512 B each)
+    uint32_t sfineBricks[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    uint32_t TB[3] = {0, 0, 0};
+    bool sparseReady = false;
     vrt_material* palette = nullptr; vrt_material hostPalette[256];
     uint8_t* noise = nullptr; float* sky = nullptr; uint32_t skyW = 0, skyH = 0;
     int accelLaunches = 0;

@@ -31,6 +31,14 @@ size_t octant_scratch_bytes(uint32_t W, uint32_t H, uint32_t D);
 cudaError_t launch_build_odist(const uint8_t* vol, uint32_t W, uint32_t H, uint32_t D, uint8_t* const odist[8], uint32_t* scratch,
                                cudaStream_t stream, int* launches);
 
+// the same build one octant at a time, and the two-level (sparse) layout made from an octant's linear field (SceneDev::sdist)
+cudaError_t launch_odist_init(const uint8_t* vol, uint32_t W, uint32_t H, uint32_t D, uint32_t* scratch, cudaStream_t stream, int* launches);
+cudaError_t launch_odist_octant(uint32_t W, uint32_t H, uint32_t D, int octant, uint8_t* out, uint32_t* scratch, cudaStream_t stream, int* launches);
+void sparse_top_dims(uint32_t W, uint32_t H, uint32_t D, uint32_t tb[3]);
+cudaError_t launch_sparse_classify(const uint8_t* lin, uint32_t W, uint32_t H, uint32_t D, uint32_t* top, uint32_t* fineCount, cudaStream_t stream);
+cudaError_t launch_sparse_fill(const uint8_t* lin, uint32_t W, uint32_t H, uint32_t D, const uint32_t* top, uint8_t* fine, cudaStream_t stream);
+cudaError_t launch_sparse_expand(const uint32_t* top, const uint8_t* fine, uint32_t W, uint32_t H, uint32_t D, uint8_t* out, cudaStream_t stream);
+
 // procedural volumes (vrt_generate.cu)
 cudaError_t launch_generate(int generator, uint32_t seed, uint8_t* vol, uint32_t W, uint32_t H, uint32_t D, cudaStream_t stream);
 void generator_palette(int generator, uint32_t seed, vrt_material palette[256]);   // host

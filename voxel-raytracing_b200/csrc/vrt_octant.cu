@@ -93,34 +93,122 @@ size_t octant_scratch_bytes(uint32_t W, uint32_t H, uint32_t D) {
     return (size_t)VRT_OCT_NLEVELS * WW * H * D * sizeof(uint32_t);
 }
 
-// odist[0..7]: (W+2)(H+2)(D+2) bytes each; scratch: octant_scratch_bytes()
-cudaError_t launch_build_odist(const uint8_t* vol, uint32_t W, uint32_t H, uint32_t D, uint8_t* const odist[8], uint32_t* scratch,
-                               cudaStream_t stream, int* launches) {
+static cudaError_t upload_level_table(cudaStream_t stream) {
     static const int lv[VRT_OCT_NLEVELS] = VRT_OCT_LEVEL_LIST;
     uint8_t table[VRT_OCT_NLEVELS + 1];
     table[0] = 0;
     for (int l = 0; l < VRT_OCT_NLEVELS; l++) table[l + 1] = (uint8_t)safe_encode((uint32_t)lv[l]);
-    cudaError_t e = cudaMemcpyToSymbolAsync(c_octLevels, table, sizeof(table), 0, cudaMemcpyHostToDevice, stream);
+    return cudaMemcpyToSymbolAsync(c_octLevels, table, sizeof(table), 0, cudaMemcpyHostToDevice, stream);
+}
+
+// level 0 of the scratch (emptiness bits), shared by the eight octants
+cudaError_t launch_odist_init(const uint8_t* vol, uint32_t W, uint32_t H, uint32_t D, uint32_t* scratch, cudaStream_t stream, int* launches) {
+    cudaError_t e = upload_level_table(stream);
     if (e != cudaSuccess) return e;
+    const uint32_t WW = (W + 31u) / 32u;
+    const dim3 block(32, 8), grid((WW + 31u) / 32u, (H + 7u) / 8u, D);
+    oct_init_kernel<<<grid, block, 0, stream>>>(vol, scratch, W, H, WW);
+    if (launches) *launches += 1;
+    return cudaGetLastError();
+}
+// the aproned linear field of ONE octant from the scratch prepared by launch_odist_init
+cudaError_t launch_odist_octant(uint32_t W, uint32_t H, uint32_t D, int o, uint8_t* out, uint32_t* scratch, cudaStream_t stream, int* launches) {
+    static const int lv[VRT_OCT_NLEVELS] = VRT_OCT_LEVEL_LIST;
     const uint32_t WW = (W + 31u) / 32u;
     const size_t levelWords = (size_t)WW * H * D;
     const dim3 block(32, 8), grid((WW + 31u) / 32u, (H + 7u) / 8u, D);
-    oct_init_kernel<<<grid, block, 0, stream>>>(vol, scratch, W, H, WW);
-    int cnt = 1;
-    for (int o = 0; o < 8; o++) {
-        const int sx = (o & 1) ? -1 : 1, sy = (o & 2) ? -1 : 1, sz = (o & 4) ? -1 : 1;
-        e = cudaMemsetAsync(odist[o], (int)VRT_LIN_OOB, (size_t)(W + 2u) * (H + 2u) * (D + 2u), stream);   // apron
-        if (e != cudaSuccess) return e;
-        for (int l = 1; l < VRT_OCT_NLEVELS; l++) {
-            oct_level_kernel<<<grid, block, 0, stream>>>(scratch + (size_t)(l - 1) * levelWords, scratch + (size_t)l * levelWords, (int)WW, (int)H, (int)D,
-                                                         lv[l] - lv[l - 1], sx, sy, sz);
-            cnt++;
-        }
-        oct_final_kernel<<<grid, block, 0, stream>>>(scratch, levelWords, odist[o], W, H, WW);
-        cnt++;
-    }
-    if (launches) *launches += cnt;
+    const int sx = (o & 1) ? -1 : 1, sy = (o & 2) ? -1 : 1, sz = (o & 4) ? -1 : 1;
+    cudaError_t e = cudaMemsetAsync(out, (int)VRT_LIN_OOB, (size_t)(W + 2u) * (H + 2u) * (D + 2u), stream);   // apron
+    if (e != cudaSuccess) return e;
+    for (int l = 1; l < VRT_OCT_NLEVELS; l++)
+        oct_level_kernel<<<grid, block, 0, stream>>>(scratch + (size_t)(l - 1) * levelWords, scratch + (size_t)l * levelWords, (int)WW, (int)H, (int)D,
+                                                     lv[l] - lv[l - 1], sx, sy, sz);
+    oct_final_kernel<<<grid, block, 0, stream>>>(scratch, levelWords, out, W, H, WW);
+    if (launches) *launches += VRT_OCT_NLEVELS;
     return cudaGetLastError();
+}
+
+// ---- two-level (sparse) layout of one octant's field: SceneDev::sdist (vrt_types.h) ----
+// One block of 64 threads per 8x8x8 brick; thread t owns the 8 voxels of row (y, z) = (t & 7, t >> 3). `lin` is the aproned linear
+// field; brick coordinates are shifted by one brick (voxel x of brick bx: bx*8 - 8 + i), voxels beyond the apron count as outside.
+__device__ __forceinline__ uint32_t sp_code_at(const uint8_t* __restrict__ lin, int x, int y, int z, int W, int H, int D) {
+    if (x < -1 || y < -1 || z < -1 || x > W || y > H || z > D) return VRT_LIN_OOB;
+    return lin[(size_t)(x + 1) + (size_t)(y + 1) * (size_t)(W + 2) + (size_t)(z + 1) * (size_t)(W + 2) * (size_t)(H + 2)];
+}
+// pass 1: classify every brick; bricks that need per-voxel codes get a slot of the pool (atomic counter)
+__global__ void __launch_bounds__(64) sp_classify_kernel(const uint8_t* __restrict__ lin, int W, int H, int D, uint32_t TBx, uint32_t TBy, uint32_t* __restrict__ top,
+                                                         uint32_t* __restrict__ fineCount) {
+    const uint32_t bx = blockIdx.x, by = blockIdx.y, bz = blockIdx.z, t = threadIdx.x;
+    const int y = (int)by * 8 - 8 + (int)(t & 7u), z = (int)bz * 8 - 8 + (int)(t >> 3);
+    uint32_t mn = 0xffffffffu, first = 0, same = 1, special = 0;
+    for (int i = 0; i < 8; i++) {
+        const uint32_t c = sp_code_at(lin, (int)bx * 8 - 8 + i, y, z, W, H, D);
+        if (i == 0) first = c;
+        same &= c == first ? 1u : 0u;
+        special |= (c == 0u || c == VRT_LIN_OOB) ? 1u : 0u;
+        mn = min(mn, safe_decode(c));
+    }
+    __shared__ uint32_t sFirst[64], sMin[2], sFlags[2];
+    sFirst[t] = first;
+    const uint32_t wmin = __reduce_min_sync(0xffffffffu, mn), wsame = __reduce_and_sync(0xffffffffu, same), wspecial = __reduce_or_sync(0xffffffffu, special);
+    if ((t & 31u) == 0) { sMin[t >> 5] = wmin; sFlags[t >> 5] = wsame | (wspecial << 1); }
+    __syncthreads();
+    if (t == 0) {
+        bool allSame = (sFlags[0] & 1u) && (sFlags[1] & 1u);
+        for (int k = 1; k < 64 && allSame; k++) allSame = sFirst[k] == sFirst[0];
+        const bool anySpecial = ((sFlags[0] | sFlags[1]) >> 1) != 0;
+        const uint32_t m = min(sMin[0], sMin[1]);
+        uint32_t e;
+        if (allSame) e = sFirst[0];
+        else if (!anySpecial && m >= VRT_SP_UNIFORM_MIN) e = safe_encode(m);       // the minimum is a valid lower bound for every voxel of the brick
+        else e = VRT_SP_FINE | atomicAdd(fineCount, 1u);
+        top[bx + (by + (size_t)bz * TBy) * TBx] = e;
+    }
+}
+// pass 2: per-voxel codes of the bricks that were given a slot
+__global__ void __launch_bounds__(64) sp_fill_kernel(const uint8_t* __restrict__ lin, int W, int H, int D, uint32_t TBx, uint32_t TBy, const uint32_t* __restrict__ top,
+                                                     uint8_t* __restrict__ fine) {
+    const uint32_t bx = blockIdx.x, by = blockIdx.y, bz = blockIdx.z, t = threadIdx.x;
+    const uint32_t e = top[bx + (by + (size_t)bz * TBy) * TBx];
+    if (!(e & VRT_SP_FINE)) return;
+    const int y = (int)by * 8 - 8 + (int)(t & 7u), z = (int)bz * 8 - 8 + (int)(t >> 3);
+    unsigned long long row = 0ull;
+    for (int i = 0; i < 8; i++) row |= (unsigned long long)sp_code_at(lin, (int)bx * 8 - 8 + i, y, z, W, H, D) << (8 * i);
+    reinterpret_cast<unsigned long long*>(fine + (size_t)(e & ~VRT_SP_FINE) * 512u)[t] = row;   // (x&7) | (y&7)<<3 | (z&7)<<6
+}
+// expand a sparse field back to the aproned linear layout (tests)
+__global__ void sp_expand_kernel(const uint32_t* __restrict__ top, const uint8_t* __restrict__ fine, uint32_t TBx, uint32_t TBy, uint8_t* __restrict__ out, int W, int H, int D) {
+    const int x = (int)(blockIdx.x * blockDim.x + threadIdx.x) - 1, y = (int)blockIdx.y - 1, z = (int)blockIdx.z - 1;
+    if (x > W) return;
+    const uint32_t X = (uint32_t)(x + 8), Y = (uint32_t)(y + 8), Z = (uint32_t)(z + 8);
+    const uint32_t e = top[(X >> 3) + ((Y >> 3) + (size_t)(Z >> 3) * TBy) * TBx];
+    const uint32_t c = (e & VRT_SP_FINE) ? fine[(size_t)(e & ~VRT_SP_FINE) * 512u + ((X & 7u) | ((Y & 7u) << 3) | ((Z & 7u) << 6))] : e;
+    out[(size_t)(x + 1) + (size_t)(y + 1) * (size_t)(W + 2) + (size_t)(z + 1) * (size_t)(W + 2) * (size_t)(H + 2)] = (uint8_t)c;
+}
+
+void sparse_top_dims(uint32_t W, uint32_t H, uint32_t D, uint32_t tb[3]) { tb[0] = ((W + 8u) >> 3) + 1u; tb[1] = ((H + 8u) >> 3) + 1u; tb[2] = ((D + 8u) >> 3) + 1u; }
+cudaError_t launch_sparse_classify(const uint8_t* lin, uint32_t W, uint32_t H, uint32_t D, uint32_t* top, uint32_t* fineCount, cudaStream_t stream) {
+    uint32_t tb[3]; sparse_top_dims(W, H, D, tb);
+    sp_classify_kernel<<<dim3(tb[0], tb[1], tb[2]), 64, 0, stream>>>(lin, (int)W, (int)H, (int)D, tb[0], tb[1], top, fineCount);
+    return cudaGetLastError();
+}
+cudaError_t launch_sparse_fill(const uint8_t* lin, uint32_t W, uint32_t H, uint32_t D, const uint32_t* top, uint8_t* fine, cudaStream_t stream) {
+    uint32_t tb[3]; sparse_top_dims(W, H, D, tb);
+    sp_fill_kernel<<<dim3(tb[0], tb[1], tb[2]), 64, 0, stream>>>(lin, (int)W, (int)H, (int)D, tb[0], tb[1], top, fine);
+    return cudaGetLastError();
+}
+cudaError_t launch_sparse_expand(const uint32_t* top, const uint8_t* fine, uint32_t W, uint32_t H, uint32_t D, uint8_t* out, cudaStream_t stream) {
+    uint32_t tb[3]; sparse_top_dims(W, H, D, tb);
+    sp_expand_kernel<<<dim3((W + 2u + 127u) / 128u, H + 2u, D + 2u), 128, 0, stream>>>(top, fine, tb[0], tb[1], out, (int)W, (int)H, (int)D);
+    return cudaGetLastError();
+}
+
+// odist[0..7]: (W+2)(H+2)(D+2) bytes each; scratch: octant_scratch_bytes()
+cudaError_t launch_build_odist(const uint8_t* vol, uint32_t W, uint32_t H, uint32_t D, uint8_t* const odist[8], uint32_t* scratch,
+                               cudaStream_t stream, int* launches) {
+    cudaError_t e = launch_odist_init(vol, W, H, D, scratch, stream, launches);
+    for (int o = 0; o < 8 && e == cudaSuccess; o++) e = launch_odist_octant(W, H, D, o, odist[o], scratch, stream, launches);
+    return e;
 }
 
 }  // namespace vrt

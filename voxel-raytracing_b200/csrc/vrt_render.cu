@@ -77,6 +77,7 @@ cudaError_t launch_render(const SceneDev& sc, const FrameParams& fp, const Plane
     else if (fp.traversal == VRT_TRAVERSAL_FINE) render_kernel<VRT_TRAVERSAL_FINE><<<grid, block, 0, stream>>>(sc, fp, pl, ctr);
     else if (fp.traversal == VRT_TRAVERSAL_LINEAR) render_kernel<VRT_TRAVERSAL_LINEAR><<<grid, block, 0, stream>>>(sc, fp, pl, ctr);
     else if (fp.traversal == VRT_TRAVERSAL_OCTANT) render_kernel<VRT_TRAVERSAL_OCTANT><<<grid, block, 0, stream>>>(sc, fp, pl, ctr);
+    else if (fp.traversal == VRT_TRAVERSAL_SPARSE) render_kernel<VRT_TRAVERSAL_SPARSE><<<grid, block, 0, stream>>>(sc, fp, pl, ctr);
     else render_kernel<VRT_TRAVERSAL_BRICK><<<grid, block, 0, stream>>>(sc, fp, pl, ctr);
     return cudaGetLastError();
 }

@@ -44,6 +44,20 @@ constexpr int VRT_OCT_NLEVELS = 31;
 VRT_HD uint32_t safe_decode(uint32_t code) { return code < 128u ? code : code * 4u - 384u; }
 VRT_HD uint32_t safe_encode(uint32_t n) { return n < 128u ? n : (n + 384u) / 4u; }
 
+//   sdist[o]    : the SAME directional safe-step values in a two-level (sparse) layout, VRT_TRAVERSAL_SPARSE. The volume is cut into
+//              8x8x8 bricks (coordinates shifted by one brick so that the one-voxel apron needs no special case); `top` holds one word
+//              per brick: either the one byte code that stands for the whole brick (a solid brick: 0; a brick outside the volume:
+//              255; a brick whose every voxel has at least VRT_SP_UNIFORM_MIN safe steps: the code of their MINIMUM, which is a valid
+//              lower bound for each of them) or VRT_SP_FINE | index of a 512-byte block of per-voxel codes in `fine`. Only bricks near
+//              a surface are stored per voxel: 8 x 8.6 GiB of linear fields for a 2048^3 scene become ~1 GiB, the top levels
+//              (8 x 8.6 MB for 1024^3) stay resident in the 126 MB L2.
+constexpr uint32_t VRT_SP_FINE = 0x80000000u;
+#ifndef VRT_SP_UNIFORM_MIN_V
+#define VRT_SP_UNIFORM_MIN_V 16
+#endif
+constexpr uint32_t VRT_SP_UNIFORM_MIN = VRT_SP_UNIFORM_MIN_V;
+struct SparseField { const uint32_t* top; const uint8_t* fine; };
+
 struct SceneDev {
     const uint8_t* vol;               // dense u8[W*H*D], x fastest (voxel_scene.cpp:99)
     const unsigned long long* bmask;  // [Bz][By][Bx]
@@ -51,6 +65,8 @@ struct SceneDev {
     const uint8_t* fdist;             // [Bz][By][Bx][4][4][4]
     const uint8_t* ldist;             // [D+2][H+2][W+2]
     const uint8_t* odist[8];          // per direction octant, [D+2][H+2][W+2] each
+    SparseField sdist[8];             // per direction octant, two-level
+    uint32_t TBx, TBy, TBz;           // bricks of the top level per axis: ((dim + 8) >> 3) + 1
     uint32_t W, H, D;
     uint32_t Bx, By, Bz;
     const vrt_material* palette;      // 256 entries

@@ -244,6 +244,9 @@ __global__ void __launch_bounds__(ENGINE_WARPS * 32, ENGINE_MIN_BLOCKS) wave_any
                                                                                 Counters* __restrict__ ctr, const uint32_t refillT, const uint32_t farShare, const int part, const uint32_t quota) {
     __shared__ EngineStash stashAll[ENGINE_WARPS];
     __shared__ uint32_t blockChunk;
+    __shared__ SparseField octFields[8];             // VRT_TRAVERSAL_SPARSE: the per-octant fields, indexed by a ray's octant
+    constexpr bool SPARSE = TRAVERSAL == VRT_TRAVERSAL_SPARSE;
+    if (SPARSE) { if (threadIdx.x < 8) octFields[threadIdx.x] = sc.sdist[threadIdx.x]; __syncthreads(); }
     EngineStash& st = stashAll[threadIdx.x >> 5];
     const uint32_t lane = threadIdx.x & 31, ltMask = (1u << lane) - 1u;
     // part 0: the rays of every shaded record, persistent grid, chunks from a global counter
@@ -269,6 +272,8 @@ __global__ void __launch_bounds__(ENGINE_WARPS * 32, ENGINE_MIN_BLOCKS) wave_any
     EngRay er; er.rem = 0; er.left = 0;
     er.l.sx = er.l.sy = er.l.sz = er.l.dx = er.l.dy = er.l.dz = er.l.sx0 = er.l.sy0 = er.l.sz0 = er.l.ax = er.l.ay = er.l.az = 0.0f;
     er.l.p0 = sc.vol; er.l.SX = er.l.SY = er.l.SZ = er.l.T0 = 0; er.l.maxSteps = 0;
+    er.l.mx0 = er.l.my0 = er.l.mz0 = 0; er.l.stx = er.l.sty = er.l.stz = 1; er.l.i = 0; er.l.mask = 0;
+    er.f.top = nullptr; er.f.fine = nullptr;
     bool alive = false, pending = false, hitRes = false;
     uint32_t idx = 0, kind = 0, fetchRes = 0;
     unsigned rays = 0, fetches = 0;
@@ -325,12 +330,13 @@ __global__ void __launch_bounds__(ENGINE_WARPS * 32, ENGINE_MIN_BLOCKS) wave_any
                     if (!lin_usable(dda_begin(sc, rs, rd, pos, s), s)) {
                         uint32_t f; const bool hit = engine_anyhit_literal(sc, s, maxSteps, f);
                         retire(nIdx, i, hit, f);
-                    } else if (lin_begin(sc, TRAVERSAL == VRT_TRAVERSAL_OCTANT ? octant_field(sc, s) : sc.ldist, s, rd, maxSteps, nr) == LIN_OOB)
+                    } else if ((SPARSE ? engine_begin_sparse(sc, s, rd, maxSteps, nr) : lin_begin(sc, TRAVERSAL == VRT_TRAVERSAL_OCTANT ? octant_field(sc, s) : sc.ldist, s, rd, maxSteps, nr)) == LIN_OOB)
                         retire(nIdx, i, false, 0u);
                     else {
                         // the first look-up, with the whole warp: a ray it ends (exhausted at once / starts in a solid voxel) is retired here
                         EngRay t; t.l = nr; t.rem = 0; t.left = maxSteps;
-                        const int stt = engine_lookup(t);
+                        if (SPARSE) t.f = octFields[(s.stx < 0 ? 1 : 0) | (s.sty < 0 ? 2 : 0) | (s.stz < 0 ? 4 : 0)];
+                        const int stt = engine_lookup<SPARSE>(t, sc);
                         ENG_STAT(17, 1); ENG_STAT(18, stt != ENG_GO);
                         if (stt != ENG_GO) retire(nIdx, i, stt == ENG_HIT, engine_steps_taken(t) + (stt == ENG_HIT ? 1u : 0u));
                         else { push = true; firstRem = (uint32_t)t.rem; }
@@ -345,13 +351,13 @@ __global__ void __launch_bounds__(ENGINE_WARPS * 32, ENGINE_MIN_BLOCKS) wave_any
             __syncwarp();
             const uint32_t take = nIdle < stashN ? nIdle : stashN;
             const uint32_t r = __popc(idleMask & ltMask);
-            if (!alive && r < take) { engine_pop(st, stashN - 1u - r, er, LW, LWH, idx, kind); alive = true; }
+            if (!alive && r < take) { engine_pop<SPARSE>(st, stashN - 1u - r, er, LW, LWH, idx, kind, octFields); alive = true; }
             stashN -= take;
             __syncwarp();
         }
         // ---- look-up for lanes whose budget is spent
         if (alive && er.rem == 0) {
-            const int stt = engine_lookup(er);
+            const int stt = engine_lookup<SPARSE>(er, sc);
             ENG_STAT(6, 1);
             ENG_STAT(8, stt == ENG_EXHAUSTED);
 #ifdef VRT_ENGINE_STATS
@@ -434,7 +440,7 @@ static cudaError_t launch_wave_t(const SceneDev& sc, const FrameParams& fp, cons
     const uint32_t R = aoN + ((fp.pass_mask & VRT_PASS_SHADOW) ? 1u : 0u);
     const bool anyhit = shade && R;
     // the ray engine needs a linear safe-step field; the other back-ends keep the run-to-completion kernel (VRT_ENGINE_T=0 forces it)
-    const bool engine = (T == VRT_TRAVERSAL_LINEAR || T == VRT_TRAVERSAL_OCTANT) && engineT() > 0;
+    const bool engine = (T == VRT_TRAVERSAL_LINEAR || T == VRT_TRAVERSAL_OCTANT || T == VRT_TRAVERSAL_SPARSE) && engineT() > 0;
     const bool overlap = anyhit && reflect && engine && side && (overlapEnv < 0 ? smallFrame : overlapEnv != 0);
     auto launch_engine = [&](cudaStream_t s, int part, unsigned grid) {
         // part 1 shares the SMs with the reflection waves: padding its shared memory caps its blocks per SM so that the waves'
@@ -476,6 +482,7 @@ cudaError_t launch_wavefront(const SceneDev& sc, const FrameParams& fp, const Pl
     if (fp.traversal == VRT_TRAVERSAL_FINE) return launch_wave_t<VRT_TRAVERSAL_FINE>(sc, fp, pl, ctr, wb, sms, stream, side, launches, ev);
     if (fp.traversal == VRT_TRAVERSAL_LINEAR) return launch_wave_t<VRT_TRAVERSAL_LINEAR>(sc, fp, pl, ctr, wb, sms, stream, side, launches, ev);
     if (fp.traversal == VRT_TRAVERSAL_OCTANT) return launch_wave_t<VRT_TRAVERSAL_OCTANT>(sc, fp, pl, ctr, wb, sms, stream, side, launches, ev);
+    if (fp.traversal == VRT_TRAVERSAL_SPARSE) return launch_wave_t<VRT_TRAVERSAL_SPARSE>(sc, fp, pl, ctr, wb, sms, stream, side, launches, ev);
     return launch_wave_t<VRT_TRAVERSAL_BRICK>(sc, fp, pl, ctr, wb, sms, stream, side, launches, ev);
 }
 

@@ -15,7 +15,7 @@ LIB_PATH = os.environ.get("VRT_LIB", os.path.join(HERE, "libvrt.so"))   # VRT_LI
 
 PASS_PRIMARY, PASS_SHADOW, PASS_AO, PASS_REFLECT, PASS_SHADE, PASS_ALL = 1, 2, 4, 8, 16, 31
 OUT_GBUFFER, OUT_INSTRUMENT = 1, 2
-TRAVERSAL_DEFAULT, TRAVERSAL_DENSE_U8, TRAVERSAL_BRICK, TRAVERSAL_FINE, TRAVERSAL_LINEAR, TRAVERSAL_OCTANT = 0, 1, 2, 3, 4, 5
+TRAVERSAL_DEFAULT, TRAVERSAL_DENSE_U8, TRAVERSAL_BRICK, TRAVERSAL_FINE, TRAVERSAL_LINEAR, TRAVERSAL_OCTANT, TRAVERSAL_SPARSE = 0, 1, 2, 3, 4, 5, 6
 PIPELINE_DEFAULT, PIPELINE_MEGAKERNEL, PIPELINE_WAVEFRONT = 0, 1, 2
 DENOISE_AS_EXECUTED, DENOISE_AS_INTENDED = 0, 1
 E_LFS_POINTER, E_NO_INSTANCE, E_PARSE, E_IO, E_CUDA, E_NO_DEVICE, E_UNSUPPORTED, E_OOM, E_COMM = -2, -3, -4, -5, -6, -7, -8, -9, -10
@@ -77,7 +77,7 @@ def lib():
         L.vrt_context_stream.restype = C.c_void_p
         L.vrt_frame_stream.restype = C.c_void_p
         L.vrt_comm_stream.restype = C.c_void_p
-        for fn in ("vrt_context_destroy", "vrt_scene_destroy", "vrt_frame_release", "vrt_host_free", "vrt_camera_vectors", "vrt_default_settings", "vrt_render_resolution"):
+        for fn in ("vrt_context_destroy", "vrt_scene_destroy", "vrt_frame_release", "vrt_host_free", "vrt_upscaler_destroy", "vrt_camera_vectors", "vrt_default_settings", "vrt_render_resolution"):
             getattr(L, fn).restype = None
         _lib = L
     return _lib
@@ -324,6 +324,11 @@ class VoxelScene:
         _ck(lib().vrt_scene_memory(self.h, C.byref(v), C.byref(f), C.byref(pk), C.byref(ms)))
         return dict(volume_bytes=v.value, field_bytes=f.value, peak_build_bytes=pk.value, load_ms=ms.value)
 
+    def download_sdist(self, octant):
+        """The two-level (sparse) field of an octant, expanded to the aproned linear layout of download_odist."""
+        f = np.zeros((self.depth + 2, self.height + 2, self.width + 2), np.uint8)
+        _ck(lib().vrt_scene_download_sdist(self.h, int(octant), f.ctypes.data_as(C.c_void_p), C.c_size_t(f.size))); return f
+
     def accel_info(self):
         a, b, c = C.c_size_t(), C.c_size_t(), C.c_size_t()
         _ck(lib().vrt_scene_accel_info(self.h, C.byref(a), C.byref(b), C.byref(c)))
@@ -473,6 +478,23 @@ class UpscalerStage:
         fc, x, y = C.c_int(self.frameCount), C.c_float(), C.c_float()
         _ck(lib().vrt_upscaler_update(self.render_width, self.target_width, C.byref(fc), C.byref(x), C.byref(y)))
         self.frameCount, self.jitterX, self.jitterY = fc.value, np.float32(x.value), np.float32(y.value)
+
+
+class TemporalUpscaler:
+    """The stage after the denoiser (UpscalerStage::record): an own-definition temporal upscaler (csrc/vrt_upscale.cu); device pointers in."""
+
+    def __init__(self, ctx: Context, render_size, target_size):
+        self.ctx, self.h = ctx, C.c_void_p()
+        _ck(lib().vrt_upscaler_create(ctx.h, int(render_size[0]), int(render_size[1]), int(target_size[0]), int(target_size[1]), C.byref(self.h)))
+
+    def dispatch(self, d_color, d_out, d_depth=None, d_motion=None, d_mask=None, jitter=(0.0, 0.0), mv_scale=(1.0, 1.0), reset=False, stream=None):
+        p = lambda v: C.c_void_p(v) if v else None
+        _ck(lib().vrt_upscaler_dispatch(self.h, p(d_color), p(d_depth), p(d_motion), p(d_mask), C.c_float(jitter[0]), C.c_float(jitter[1]),
+                                        C.c_float(mv_scale[0]), C.c_float(mv_scale[1]), 1 if reset else 0, p(d_out), p(stream)))
+
+    def destroy(self):
+        if self.h:
+            lib().vrt_upscaler_destroy(self.h); self.h = C.c_void_p()
 
 
 def denoise_device_on(ctx: Context, d_color, d_normal, d_position, size, ds: DenoiserSettings, d_out, d_scratch, stream=None):
