@@ -7,12 +7,15 @@
 // scale) and the class of algorithm (jittered temporal accumulation with neighbourhood rectification). Defined here as:
 //   1. r = centre of the output pixel in render-pixel units. Pixel (i, j) of this frame was sampled at (i + 0.5 - jx, j + 0.5 + jy): the
 //      shader adds cameraJitter / screenSize * (-2, 2) to the ray direction (voxel_volume.frag:322), i.e. -jx / +jy pixels.
-//   2. current colour = tent-weighted mean of the (up to) four samples around r, w = max(0, 1-|dx|) * max(0, 1-|dy|); W = sum of w.
+//   2. current colour = tent-weighted mean of the (up to) four samples around r, the tent HALF an output pixel in radius: w = max(0,
+//      1 - 2|dx| tw/rw) * max(0, 1 - 2|dy| th/rh), dx, dy in render pixels; W = sum of w (a frame whose samples miss the pixel contributes
+//      nothing: W = 0). A wider tent, or a floor under alpha, was measured to converge to a blurred / noisy image (profiles/r2_upscaler.txt).
+//      When nothing better exists (first frame, reset) the pixel starts from the plain bilinear value with a token weight.
 //   3. history (target resolution, RGBA32F: colour + accumulated weight) is fetched at the output pixel moved back by the motion vector
 //      of the nearest sample (x motionVectorScale x target/render), nearest texel; rejected when that falls outside the image.
 //   4. the history colour is clamped to the min / max of the 3x3 render pixels around the nearest sample (rectification).
-//   5. alpha = max(W / (W + history weight), reactive mask of the nearest sample, 1/16); out = history + (current - history) * alpha;
-//      new weight = min(history weight + W, 15). reset, or no valid history: out = current (nearest sample when W = 0).
+//   5. W > 0: alpha = max(W / (W + history weight), W * reactive mask of the nearest sample); out = history + (current - history) * alpha;
+//      new weight = min(history weight + W, 15) (the cap keeps alpha >= W / (W + 15): the history never freezes). W = 0: the (rectified) history is kept. reset, or no valid history: out = current.
 // Properties tested (tests/test_gpu.py): deterministic; exact pass-through at scale 1, jitter (0, 0); a static scene converges.
 // Sharpening (the reference asks FSR2 for RCAS at 1.0) is not part of this definition.
 #include <cuda_runtime.h>
@@ -53,24 +56,29 @@ __global__ void __launch_bounds__(256) upscale_kernel(const uint8_t* __restrict_
     const float ax = ux - fx, ay = uy - fy;
     const int i0 = f2i(fx), j0 = f2i(fy);
     // 2. tent-weighted current colour over the samples that exist
-    float4 cur = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    float W = 0.0f;
+    const float kx = 2.0f * (float)p.tw / (float)p.rw, ky = 2.0f * (float)p.th / (float)p.rh;   // tent of half an output pixel in radius
+    float4 cur = make_float4(0.0f, 0.0f, 0.0f, 0.0f), wide = cur;
+    float W = 0.0f, Wwide = 0.0f;
 #pragma unroll
     for (int dy = 0; dy < 2; dy++)
 #pragma unroll
         for (int dx = 0; dx < 2; dx++) {
             const int i = i0 + dx, j = j0 + dy;
-            const float w = (dx ? ax : 1.0f - ax) * (dy ? ay : 1.0f - ay);
-            if (i < 0 || j < 0 || i >= p.rw || j >= p.rh || w <= 0.0f) continue;
+            if (i < 0 || j < 0 || i >= p.rw || j >= p.rh) continue;
+            const float ddx = dx ? 1.0f - ax : ax, ddy = dy ? 1.0f - ay : ay;             // distance to the sample, render pixels
+            const float wb = (1.0f - ddx) * (1.0f - ddy);
+            const float w = fmaxf(1.0f - ddx * kx, 0.0f) * fmaxf(1.0f - ddy * ky, 0.0f);
+            if (wb <= 0.0f) continue;
             const float4 c = up_color(color, i, j, p.rw, lut);
-            cur.x += c.x * w; cur.y += c.y * w; cur.z += c.z * w; cur.w += c.w * w;
-            W += w;
+            wide.x += c.x * wb; wide.y += c.y * wb; wide.z += c.z * wb; wide.w += c.w * wb; Wwide += wb;
+            if (w > 0.0f) { cur.x += c.x * w; cur.y += c.y * w; cur.z += c.z * w; cur.w += c.w * w; W += w; }
         }
     const int ni = min(max(f2i(floorf(ux + 0.5f)), 0), p.rw - 1), nj = min(max(f2i(floorf(uy + 0.5f)), 0), p.rh - 1);   // nearest sample
     const float4 nearest = up_color(color, ni, nj, p.rw, lut);
-    if (W > 0.0f) { cur.x /= W; cur.y /= W; cur.z /= W; cur.w /= W; } else cur = nearest;
+    if (Wwide > 0.0f) { wide.x /= Wwide; wide.y /= Wwide; wide.z /= Wwide; wide.w /= Wwide; } else wide = nearest;
+    if (W > 0.0f) { cur.x /= W; cur.y /= W; cur.z /= W; cur.w /= W; } else cur = wide;
     float4 o = cur;
-    float weight = W;
+    float weight = W > 0.0f ? W : 0.015625f;                 // a pixel no sample reached starts from the bilinear value with a token weight
     if (p.useHistory) {
         // 3. history at the output pixel moved back by the nearest sample's motion vector
         const float2 mv = motion ? reinterpret_cast<const float2*>(motion)[(size_t)nj * p.rw + ni] : make_float2(0.0f, 0.0f);
@@ -89,7 +97,7 @@ __global__ void __launch_bounds__(256) upscale_kernel(const uint8_t* __restrict_
                 h.x = fminf(fmaxf(h.x, lo.x), hi.x); h.y = fminf(fmaxf(h.y, lo.y), hi.y); h.z = fminf(fmaxf(h.z, lo.z), hi.z);
                 // 5. blend
                 const float reactive = mask ? lut[mask[(size_t)nj * p.rw + ni]] : 0.0f;
-                const float alpha = fmaxf(fmaxf(W / (W + h.w), reactive), 0.0625f);
+                const float alpha = W > 0.0f ? fmaxf(W / (W + h.w), W * reactive) : 0.0f;
                 o.x = h.x + (cur.x - h.x) * alpha; o.y = h.y + (cur.y - h.y) * alpha; o.z = h.z + (cur.z - h.z) * alpha;
                 weight = fminf(h.w + W, 15.0f);
             }
