@@ -24,6 +24,22 @@ __device__ __forceinline__ float dot4d(float4 a, float4 b) {   // t = a - b; dot
     return ((x * x + y * y) + z * z) + w * w;
 }
 
+// a / b for a divisor that is a per-launch constant, rb = 1.0f / b (IEEE, computed once on the host): two Markstein corrections of a * rb.
+// With rb the correctly rounded reciprocal, the first correction leaves the quotient within half an ulp and the second makes it the
+// correctly rounded a / b — the value the oracle's division produces — in 5 FMA-pipe instructions and WITHOUT the slow path the
+// compiler's IEEE division takes for a zero numerator (a tap on the pixel itself, or a neighbour with the same colour / normal /
+// position: the common case; ncu r2p1 had 32 % of the kernel's instructions in those subroutines). Quotients that are not finite or
+// so small that the corrections would work on denormals take the plain division (rare, and exact by construction).
+__device__ __forceinline__ float div_const(float a, float b, float rb) {
+    const float q0 = a * rb;
+    const float q1 = __fmaf_rn(__fmaf_rn(-b, q0, a), rb, q0);
+    const float q2 = __fmaf_rn(__fmaf_rn(-b, q1, a), rb, q1);
+    const float m = fabsf(q2);
+    if (a == 0.0f) return q0;                                   // +-0 / b: the product already has the right sign (b > 0 or b < 0 alike)
+    if (!(m <= 3.0e38f) || m < 1.0e-30f || fabsf(a) < 1.0e-30f) return a / b;
+    return q2;
+}
+
 // BLIND: all three phi are +inf, which is what the reference's host code produces for iteration 0 (1.0f / float(0) * phi0,
 // denoiser_stage.cpp:143-154). Then every edge-stopping weight is exactly 1 whatever the inputs are — x / inf is +-0 for finite x and
 // NaN for x = inf / NaN, exp gives 1 or NaN, and min(NaN, 1) = 1 — so the iteration is a plain weighted blur of the colour plane:
@@ -76,6 +92,7 @@ __global__ void __launch_bounds__(256) denoise_kernel(const uint8_t* __restrict_
     } else {
         const float4 sc = ld_color(color, p, lutU), sn = ld_normal(normal, p, lutS), sp = reinterpret_cast<const float4*>(position)[p];
         const float sw2 = it.stepWidth * it.stepWidth;
+        const float rPhiC = 1.0f / it.phiColor, rPhiN = 1.0f / it.phiNormal, rPhiP = 1.0f / it.phiPos, rSw2 = 1.0f / sw2;   // once per thread (IEEE)
 #pragma unroll 1
         for (int i = 0; i < taps.n; i++) {
             // uv = vScreenPos + offset*step*stepWidth under LINEAR/CLAMP = the texel holding the sample point; the texel offsets
@@ -97,9 +114,9 @@ __global__ void __launch_bounds__(256) denoise_kernel(const uint8_t* __restrict_
                 const size_t q = (size_t)ty * W + tx;
                 oc = ld_color(color, q, lutU); on = ld_normal(normal, q, lutS); op = reinterpret_cast<const float4*>(position)[q];
             }
-            const float cw = fminf(expf(-(dot4d(sc, oc)) / it.phiColor), 1.0f);
-            const float nw = fminf(expf(-(fmaxf(dot4d(sn, on) / sw2, 0.0f)) / it.phiNormal), 1.0f);
-            const float pw = fminf(expf(-(dot4d(sp, op)) / it.phiPos), 1.0f);
+            const float cw = fminf(expf(div_const(-(dot4d(sc, oc)), it.phiColor, rPhiC)), 1.0f);
+            const float nw = fminf(expf(div_const(-(fmaxf(div_const(dot4d(sn, on), sw2, rSw2), 0.0f)), it.phiNormal, rPhiN)), 1.0f);
+            const float pw = fminf(expf(div_const(-(dot4d(sp, op)), it.phiPos, rPhiP)), 1.0f);
             const float weight = (cw * nw) * pw;
             const float k = taps.k[i];
             sum.x += (oc.x * weight) * k; sum.y += (oc.y * weight) * k; sum.z += (oc.z * weight) * k; sum.w += (oc.w * weight) * k;

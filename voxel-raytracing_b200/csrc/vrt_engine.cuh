@@ -103,9 +103,13 @@ enum { ENG_GO = 0, ENG_HIT = 1, ENG_OOB = 2, ENG_EXHAUSTED = 3 };
 
 // Look-up for a lane whose budget is spent (rem == 0). Mirrors the loop head of traceRayInt (:152-162): i < maxSteps, bounds
 // test, getVoxel != 0. On ENG_GO the budget is re-armed with min(safe steps, steps left).
+// TOP-UP: the field may be looked at BEFORE the budget is spent (rem > 0): the ray's current voxel lies inside the region its last
+// look-up cleared, so the value there is a plain budget (never solid / outside), valid from here, and the larger of the two budgets
+// stands. The look-up code is issued for the whole warp anyway whenever one lane needs it; lanes whose budget would run out inside
+// the coming round join it for free (one more byte load) instead of idling through the rest of that round.
 template <bool SPARSE>
 __device__ __forceinline__ int engine_lookup(EngRay& e, const SceneDev& sc) {
-    if (e.left == 0u) return ENG_EXHAUSTED;
+    if (e.left == 0u && e.rem == 0) return ENG_EXHAUSTED;
     const LinRay& r = e.l;
     uint32_t n;
     if (SPARSE) {
@@ -120,9 +124,9 @@ __device__ __forceinline__ int engine_lookup(EngRay& e, const SceneDev& sc) {
     if (n - 1u >= 254u) return n == 0u ? ENG_HIT : ENG_OOB;
     n = safe_decode(n);
     // any-hit: a budget that covers all remaining steps ends the ray as a miss after maxSteps getVoxel calls (see lin_round)
-    if (n >= e.left) { e.left = 0u; return ENG_EXHAUSTED; }
-    e.rem = (int)n;
-    e.left -= n;
+    const uint32_t total = e.left + (uint32_t)e.rem;          // steps the ray may still take, its current budget included
+    if (n >= total) { e.left = 0u; e.rem = 0; return ENG_EXHAUSTED; }
+    if (n > (uint32_t)e.rem) { e.rem = (int)n; e.left = total - n; }
     return ENG_GO;
 }
 

@@ -241,7 +241,7 @@ __global__ void __launch_bounds__(256) wave_anyhit_kernel(const SceneDev sc, con
 // ---- any-hit wave on the ray engine (vrt_engine.cuh): LINEAR (isotropic field) or OCTANT (directional fields) ----
 template <int TRAVERSAL, int NEAR_TOP, int FAR_TOP>
 __global__ void __launch_bounds__(ENGINE_WARPS * 32, ENGINE_MIN_BLOCKS) wave_anyhit_engine_kernel(const SceneDev sc, const FrameParams fp, const PlanesDev pl, const WaveBuf wb,
-                                                                                Counters* __restrict__ ctr, const uint32_t refillT, const uint32_t farShare, const int part, const uint32_t quota) {
+                                                                                Counters* __restrict__ ctr, const uint32_t refillT, const uint32_t farShare, const int part, const uint32_t quota, const int topup) {
     __shared__ EngineStash stashAll[ENGINE_WARPS];
     __shared__ uint32_t blockChunk;
     __shared__ SparseField octFields[8];             // VRT_TRAVERSAL_SPARSE: the per-octant fields, indexed by a ray's octant
@@ -355,8 +355,8 @@ __global__ void __launch_bounds__(ENGINE_WARPS * 32, ENGINE_MIN_BLOCKS) wave_any
             stashN -= take;
             __syncwarp();
         }
-        // ---- look-up for lanes whose budget is spent
-        if (alive && er.rem == 0) {
+        // ---- look-up for lanes whose budget is spent or would run out inside the coming round (top-up, see engine_lookup)
+        if (alive && er.rem < topup) {
             const int stt = engine_lookup<SPARSE>(er, sc);
             ENG_STAT(6, 1);
             ENG_STAT(8, stt == ENG_EXHAUSTED);
@@ -446,9 +446,13 @@ static cudaError_t launch_wave_t(const SceneDev& sc, const FrameParams& fp, cons
         // part 1 shares the SMs with the reflection waves: padding its shared memory caps its blocks per SM so that the waves'
         // blocks find registers at once instead of waiting for a side block to retire
         static const int sidePad = getenv("VRT_SIDE_PAD_KB") ? atoi(getenv("VRT_SIDE_PAD_KB")) * 1024 : 0;
-        const size_t dyn = part == 1 ? (size_t)sidePad : 0;
+        static const int mainPad = getenv("VRT_ENGINE_PAD_KB") ? atoi(getenv("VRT_ENGINE_PAD_KB")) * 1024 : 0;   // measurement: caps the blocks per SM
+        const size_t dyn = part == 1 ? (size_t)sidePad : (size_t)mainPad;
         if (dyn) cudaFuncSetAttribute(wave_anyhit_engine_kernel<T, ENGINE_NEAR_TOP, ENGINE_FAR_TOP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
-        wave_anyhit_engine_kernel<T, ENGINE_NEAR_TOP, ENGINE_FAR_TOP><<<grid, ENGINE_WARPS * 32, dyn, s>>>(sc, fp, pl, wb, ctr, (uint32_t)engineT(), (uint32_t)farShare, part, quota);
+        // look-ups join in when a lane's budget would run out inside a near round (engine_lookup); 1 = only when it is spent. Measured on
+        // cfg4: 1 -> 3.48 ms, 3 -> 3.45, 7 -> 3.40, 12 -> 3.42, 31 -> 3.46 (profiles/r2_engine_experiments.txt)
+        static const int topup = getenv("VRT_ENGINE_TOPUP") ? max(1, atoi(getenv("VRT_ENGINE_TOPUP"))) : 2 * ENGINE_NEAR_TOP - 1;
+        wave_anyhit_engine_kernel<T, ENGINE_NEAR_TOP, ENGINE_FAR_TOP><<<grid, ENGINE_WARPS * 32, dyn, s>>>(sc, fp, pl, wb, ctr, (uint32_t)engineT(), (uint32_t)farShare, part, quota, topup);
         n++;
     };
     if (overlap) {
