@@ -163,6 +163,6 @@ def test_cfg5_sparse_2048_orbit_8k_sampled_rows_world1_and_world8(gpu_ctx):
             else:
                 ok, bad = bits_equal(a, want[n]); assert ok, (k, "world8", n, bad)
         del full
-    mem = gs.memory()
-    assert mem["field_bytes"] == 8 * 2050 ** 3
+    mem = gs.memory()                                                     # the two-level fields, not 8 x 8.6 GiB of linear ones
+    assert mem["field_bytes"] < 8 * 2 ** 30 and mem["volume_bytes"] + mem["field_bytes"] < 40 * 2 ** 30, mem
     gs.destroy()
