@@ -470,7 +470,13 @@ static cudaError_t launch_wave_t(const SceneDev& sc, const FrameParams& fp, cons
     if (ev) cudaEventRecord(ev[1], stream);
     if (anyhit) {
         if (overlap) { launch_engine(stream, 2, (unsigned)(sms * occEngine)); cudaStreamWaitEvent(stream, side->join, 0); }
-        else if (engine) launch_engine(stream, 0, (unsigned)(sms * occEngine));
+        else if (engine) {
+            // The persistent grid owns every block slot of the GPU until its work counter runs dry; a few slots are left free so
+            // that the small kernels of OTHER frames in flight (tile pushes of the exchange, blits, the next frame's first blocks) are
+            // not held back for the length of this kernel (VRT_ENGINE_GRID_SLACK, measured in profiles/r2_engine_experiments.txt)
+            static const int slack = getenv("VRT_ENGINE_GRID_SLACK") ? max(0, atoi(getenv("VRT_ENGINE_GRID_SLACK"))) : 0;
+            launch_engine(stream, 0, (unsigned)max(sms * occEngine - slack, sms));
+        }
         else { wave_anyhit_kernel<T><<<(unsigned)(sms * occAny), 256, 0, stream>>>(sc, fp, pl, wb, ctr); n++; }
     }
     if (ev) cudaEventRecord(ev[2], stream);
