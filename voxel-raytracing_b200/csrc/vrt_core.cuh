@@ -107,6 +107,17 @@ VRT_HD void dda_step_f(Dda& s) {
     if (s.sy <= m) s.sy += s.dy;
     if (s.sz <= m) s.sz += s.dz;
 }
+// k float-only steps. Unrolled by eight with a binary remainder: the plain `for` loop spent 2 of every 9 issued instructions on its
+// counter and branch (ncu r2p1: 16 % of wave_primary_kernel), and the step is bound by instruction issue.
+VRT_HD void dda_steps_f(Dda& s, uint32_t k) {
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
+    for (; k >= 8u; k -= 8u) { dda_step_f(s); dda_step_f(s); dda_step_f(s); dda_step_f(s); dda_step_f(s); dda_step_f(s); dda_step_f(s); dda_step_f(s); }
+    if (k & 4u) { dda_step_f(s); dda_step_f(s); dda_step_f(s); dda_step_f(s); }
+    if (k & 2u) { dda_step_f(s); dda_step_f(s); }
+    if (k & 1u) dda_step_f(s);
+}
 VRT_HD uint32_t dda_step_f_rec(Dda& s) {
     float m = min3f(s.sx, s.sy, s.sz);
     bool bx = s.sx <= m, by = s.sy <= m, bz = s.sz <= m;
@@ -214,7 +225,7 @@ VRT_HD int lin_round(const SceneDev& sc, LinRay& r, const bool ANYHIT = false, c
     n = n < roundCap ? n : roundCap;
     r.i += n;
     Dda d; d.sx = r.sx; d.sy = r.sy; d.sz = r.sz; d.dx = r.dx; d.dy = r.dy; d.dz = r.dz;
-    for (uint32_t k = n - 1; k > 0; k--) dda_step_f(d);
+    dda_steps_f(d, n - 1u);
     if (STEP_REC) r.mask = dda_step_f_rec(d); else dda_step_f(d);
     r.sx = d.sx; r.sy = d.sy; r.sz = d.sz;
     return r.i >= r.maxSteps ? LIN_EXHAUSTED : LIN_CONTINUE;
@@ -272,7 +283,7 @@ VRT_HD int sp_round(const SceneDev& sc, SpRay& r, const bool ANYHIT = false, con
     n = n < roundCap ? n : roundCap;
     r.i += n;
     Dda d; d.sx = r.sx; d.sy = r.sy; d.sz = r.sz; d.dx = r.dx; d.dy = r.dy; d.dz = r.dz;
-    for (uint32_t k = n - 1; k > 0; k--) dda_step_f(d);
+    dda_steps_f(d, n - 1u);
     if (STEP_REC) r.mask = dda_step_f_rec(d); else dda_step_f(d);
     r.sx = d.sx; r.sy = d.sy; r.sz = d.sz;
     return r.i >= r.maxSteps ? LIN_EXHAUSTED : LIN_CONTINUE;

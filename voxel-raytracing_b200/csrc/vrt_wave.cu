@@ -14,6 +14,14 @@
 #include "vrt_engine.cuh"
 #include "vrt_launch.h"
 
+// blocks per SM the register allocation of the run-to-completion kernels aims at (48 / 64 registers, no spills; 12 / 10 spill and lose)
+#ifndef WAVE_PRIMARY_MIN_BLOCKS
+#define WAVE_PRIMARY_MIN_BLOCKS 10
+#endif
+#ifndef WAVE_BOUNCE_MIN_BLOCKS
+#define WAVE_BOUNCE_MIN_BLOCKS 8
+#endif
+
 namespace vrt {
 
 // Warp-aggregated slot allocation; must be called by all 32 lanes.
@@ -47,7 +55,7 @@ __device__ __forceinline__ void store_color(const FrameParams& fp, const PlanesD
 }
 
 template <int TRAVERSAL>
-__global__ void __launch_bounds__(128) wave_primary_kernel(const SceneDev sc, const FrameParams fp, const PlanesDev pl, const WaveBuf wb,
+__global__ void __launch_bounds__(128, WAVE_PRIMARY_MIN_BLOCKS) wave_primary_kernel(const SceneDev sc, const FrameParams fp, const PlanesDev pl, const WaveBuf wb,
                                                            Counters* __restrict__ ctr) {
     const int W = fp.cam.screenSize[0], H = fp.cam.screenSize[1];
     const int j = blockIdx.x >> 3, sub = blockIdx.x & 7;           // local tile, 16x8 sub-block of the tile
@@ -107,7 +115,7 @@ __global__ void __launch_bounds__(128) wave_primary_kernel(const SceneDev sc, co
 // place (the lanes whose chain goes on keep going, the others idle): the last waves hold a few thousand rays each and cost a
 // launch + a latency-bound tail apiece, which is more than their idle lanes cost.
 template <int TRAVERSAL>
-__global__ void __launch_bounds__(128) wave_bounce_kernel(const SceneDev sc, const FrameParams fp, const PlanesDev pl, const WaveBuf wb,
+__global__ void __launch_bounds__(128, WAVE_BOUNCE_MIN_BLOCKS) wave_bounce_kernel(const SceneDev sc, const FrameParams fp, const PlanesDev pl, const WaveBuf wb,
                                                           Counters* __restrict__ ctr, const int w, const bool chain, const uint32_t roundCap) {
     const uint32_t n = wb.ctr->qn[w];
     const BounceEnt* __restrict__ qin = wb.bq[w & 1];
