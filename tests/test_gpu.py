@@ -605,3 +605,43 @@ def test_temporal_upscaler_own_definition_properties(gpu_ctx):
     u.dispatch(src.data_ptr(), o.data_ptr(), jitter=(0.25, -0.125), reset=True); gpu_ctx.sync()
     assert np.array_equal(o.cpu().numpy(), first)
     u.destroy()
+
+
+def test_two_level_volume_is_byte_identical(gpu_ctx, monkeypatch):
+    """SURVEY 8(f) N1: scenes over the dense budget keep the palette volume two-level as well (bricks of one value + 512-byte bricks);
+    a generated scene is then never materialised densely. Forced here on small scenes: the stored volume expands to the generator's /
+    the uploaded bytes, every plane equals the oracle's, and the measurement back-ends that need the dense volume refuse politely."""
+    monkeypatch.setenv("VRT_VOLUME_DENSE_MAX_GIB", "0")
+    noise, sky = assets.noise_standin(), assets.sky_standin(128, 64)
+    whd = (100, 72, 90)
+    gs = pyvrt.VoxelScene.generate(gpu_ctx, 2, 1234, *whd)
+    vol = synth.GENERATORS[2](1234, *whd)
+    assert np.array_equal(gs.download_volume(), vol)
+    mem = gs.memory()
+    assert mem["volume_bytes"] < vol.size                              # top level + the bricks that hold a shape
+    gs.set_noise(noise); gs.set_skybox(sky)
+    sc, keep = O.make_scene(vol, synth.generator_palette(2, 1234), noise, sky)
+    cam = look_at_camera(whd, (320, 200), (-20.5, 90.7, -30.2), (50, 36, 45), frame=3)
+    st = O.make_settings()
+    want = O.render(sc, cam, st)
+    for pipe in PIPELINES:
+        check(gpu_render(gpu_ctx, gs, cam, st, 0, pipeline=pipe), want)                       # default resolves to the two-level fields
+    check(gpu_render(gpu_ctx, gs, cam, st, TRAV_DENSE), want)                                  # one fetch per step through the two-level volume
+    with pytest.raises(pyvrt.VrtError) as e:
+        gpu_render(gpu_ctx, gs, cam, st, 5)
+    assert e.value.code == pyvrt.E_UNSUPPORTED
+    gs.destroy()
+    rng = np.random.default_rng(3)                                      # uploaded volumes are compacted after the upload
+    v2 = random_volume(rng, (37, 50, 41), 0.02); pal = random_palette(rng)
+    g2 = pyvrt.VoxelScene.from_dense(gpu_ctx, v2, pal); g2.set_noise(noise); g2.set_skybox(sky)
+    assert np.array_equal(g2.download_volume(), v2)
+    sc2, keep2 = O.make_scene(v2, pal, noise, sky)
+    cam2 = look_at_camera((37, 50, 41), (160, 120), (-12, 60, -15), (18, 25, 20))
+    check(gpu_render(gpu_ctx, g2, cam2, st), O.render(sc2, cam2, st))
+    g2.destroy()
+    monkeypatch.delenv("VRT_VOLUME_DENSE_MAX_GIB")
+    g1 = pyvrt.VoxelScene.generate(gpu_ctx, 1, 42, 96, 64, 80)          # generator 1 through the per-voxel function == the dense kernel
+    monkeypatch.setenv("VRT_VOLUME_DENSE_MAX_GIB", "0")
+    g1s = pyvrt.VoxelScene.generate(gpu_ctx, 1, 42, 96, 64, 80)
+    assert np.array_equal(g1.download_volume(), g1s.download_volume())
+    g1.destroy(); g1s.destroy()

@@ -117,11 +117,18 @@ extern "C" int vrt_buffer_download(vrt_context* c, const void* d_src, void* host
 extern "C" void vrt_scene_destroy(vrt_scene* s) {
     if (!s) return;
     cudaSetDevice(s->ctx->device);
-    cudaFree(s->vol); cudaFree(s->bmask); cudaFree(s->bdist); cudaFree(s->fdist); cudaFree(s->ldist); for (uint8_t* p : s->odist) cudaFree(p); for (uint32_t* p : s->stop) cudaFree(p); for (uint8_t* p : s->sfine) cudaFree(p); cudaFree(s->palette); cudaFree(s->noise); cudaFree(s->sky);
+    cudaFree(s->vol); cudaFree(s->bmask); cudaFree(s->bdist); cudaFree(s->fdist); cudaFree(s->ldist); for (uint8_t* p : s->odist) cudaFree(p); for (uint32_t* p : s->stop) cudaFree(p); for (uint8_t* p : s->sfine) cudaFree(p); cudaFree(s->vtop); cudaFree(s->vfine); cudaFree(s->palette); cudaFree(s->noise); cudaFree(s->sky);
     delete s;
 }
 
-static int scene_alloc(vrt_context* c, uint32_t w, uint32_t h, uint32_t d, vrt_scene** out) {
+// A volume larger than this stays two-level (bricks of one value + 512-byte bricks, like the sparse fields): cfg5's 8 GiB dense
+// volume is then never materialised by vrt_scene_generate. VRT_VOLUME_DENSE_MAX_GIB overrides (0: every scene two-level; tests).
+static bool volume_wants_sparse(uint32_t w, uint32_t h, uint32_t d) {
+    const char* e = getenv("VRT_VOLUME_DENSE_MAX_GIB");
+    const double maxGiB = e ? atof(e) : 4.0;
+    return (double)w * (double)h * (double)d / 1073741824.0 > maxGiB;
+}
+static int scene_alloc(vrt_context* c, uint32_t w, uint32_t h, uint32_t d, vrt_scene** out, bool dense = true) {
     if (!c || !out) return fail(VRT_E_INVALID, "null argument");
     if (!w || !h || !d || w > 32767 || h > 32767 || d > 32767) return fail(VRT_E_INVALID, "volume bounds must be 1..32767 per axis");
     CU(cudaSetDevice(c->device));
@@ -129,10 +136,35 @@ static int scene_alloc(vrt_context* c, uint32_t w, uint32_t h, uint32_t d, vrt_s
     if (!s) return fail(VRT_E_OOM, "host allocation failed");
     s->ctx = c; s->w = w; s->h = h; s->d = d;
     s->Bx = (w + 3) / 4; s->By = (h + 3) / 4; s->Bz = (d + 3) / 4;
-    cudaError_t e = cudaMalloc(&s->vol, (size_t)w * h * d);
+    sparse_top_dims(w, h, d, s->TB);
+    cudaError_t e = dense ? cudaMalloc(&s->vol, (size_t)w * h * d) : cudaSuccess;
+    if (dense) s->volumeBytes = (size_t)w * h * d;
     if (e == cudaSuccess) e = cudaMalloc(&s->palette, sizeof(vrt_material) * 256);
     if (e != cudaSuccess) { vrt_scene_destroy(s); return fail(e == cudaErrorMemoryAllocation ? VRT_E_OOM : VRT_E_CUDA, cudaGetErrorString(e)); }
     *out = s;
+    return VRT_OK;
+}
+// The palette volume in the two-level layout: from the dense volume the scene holds (which is then freed) or, with generator != 0,
+// straight from the procedural function (no dense volume ever exists).
+static int scene_make_sparse_volume(vrt_scene* s, int generator, uint32_t seed) {
+    vrt_context* c = s->ctx;
+    const size_t topWords = (size_t)s->TB[0] * s->TB[1] * s->TB[2];
+    uint32_t* counter = nullptr; uint32_t n = 0;
+    cudaError_t e = cudaMalloc(&s->vtop, topWords * sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaMalloc(&counter, sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaMemsetAsync(counter, 0, sizeof(uint32_t), c->stream);
+    if (e == cudaSuccess) e = launch_sparse_volume_classify(s->vol, generator, seed, s->w, s->h, s->d, s->vtop, counter, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&n, counter, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    if (e == cudaSuccess && n) e = cudaMalloc(&s->vfine, (size_t)n * 512u);
+    if (e == cudaSuccess && n) e = launch_sparse_volume_fill(s->vol, generator, seed, s->w, s->h, s->d, s->vtop, s->vfine, c->stream);
+    const cudaError_t e2 = cudaStreamSynchronize(c->stream);
+    cudaFree(counter);
+    if (e == cudaSuccess) e = e2;
+    if (e != cudaSuccess) return fail(e == cudaErrorMemoryAllocation ? VRT_E_OOM : VRT_E_CUDA, cudaGetErrorString(e));
+    s->vfineBricks = n; s->accelLaunches += 2;
+    if (s->vol) { s->peakBuildBytes = std::max(s->peakBuildBytes, (size_t)s->w * s->h * s->d); cudaFree(s->vol); s->vol = nullptr; }
+    s->volumeBytes = topWords * sizeof(uint32_t) + (size_t)n * 512u;
     return VRT_OK;
 }
 
@@ -140,8 +172,12 @@ static double now_ms() { return std::chrono::duration<double, std::milli>(std::c
 static int cuda_fail(cudaError_t e) { return fail(e == cudaErrorMemoryAllocation ? VRT_E_OOM : VRT_E_CUDA, cudaGetErrorString(e)); }
 
 // brick occupancy + brick distance (back-end BRICK; far-field term of FINE / LINEAR). Caller holds fieldMutex.
+static int dense_only(const vrt_scene* s) {
+    return s->vol ? VRT_OK : fail(VRT_E_UNSUPPORTED, "this traversal back-end is kept for measurement and needs the dense volume; the scene is over the dense budget and stored two-level (use the default back-end)");
+}
 static int scene_ensure_bricks(vrt_scene* s) {
     if (s->bmask) return VRT_OK;
+    { const int rc = dense_only(s); if (rc) return rc; }
     vrt_context* c = s->ctx;
     const size_t nb = (size_t)s->Bx * s->By * s->Bz;
     uint8_t *tmpA = nullptr, *tmpB = nullptr;
@@ -187,6 +223,7 @@ static int scene_ensure_iso(vrt_scene* s, bool wantFine, bool wantLinear) {
 // directional safe-step fields (OCTANT): 8 fields of one byte per voxel
 static int scene_ensure_octant(vrt_scene* s) {
     if (s->odist[0]) return VRT_OK;
+    { const int rc = dense_only(s); if (rc) return rc; }
     vrt_context* c = s->ctx;
     const size_t fieldBytes = (size_t)(s->w + 2) * (s->h + 2) * (s->d + 2), scratchBytes = octant_scratch_bytes(s->w, s->h, s->d);
     uint32_t* scratch = nullptr;
@@ -217,7 +254,8 @@ static int scene_ensure_sparse(vrt_scene* s) {
     cudaError_t e = cudaMalloc(&scratch, scratchBytes);
     if (e == cudaSuccess) e = cudaMalloc(&lin, fieldBytes);
     if (e == cudaSuccess) e = cudaMalloc(&counter, sizeof(uint32_t));
-    if (e == cudaSuccess) e = launch_odist_init(s->vol, s->w, s->h, s->d, scratch, c->stream, &s->accelLaunches);
+    if (e == cudaSuccess) e = s->vol ? launch_odist_init(s->vol, s->w, s->h, s->d, scratch, c->stream, &s->accelLaunches)
+                                     : launch_odist_init_sparse(s->vtop, s->vfine, s->w, s->h, s->d, scratch, c->stream, &s->accelLaunches);
     for (int o = 0; o < 8 && e == cudaSuccess; o++) {
         e = launch_odist_octant(s->w, s->h, s->d, o, lin, scratch, c->stream, &s->accelLaunches);
         if (e == cudaSuccess) e = cudaMalloc(&s->stop[o], topWords * sizeof(uint32_t));
@@ -248,6 +286,7 @@ static int scene_ensure_sparse(vrt_scene* s) {
 // the two-level layout beyond it (VRT_DEFAULT_TRAVERSAL / VRT_FIELD_BUDGET_GIB override, for measurement)
 static uint32_t resolve_traversal(const vrt_scene* s, uint32_t traversal) {
     if (traversal != VRT_TRAVERSAL_DEFAULT) return traversal;
+    if (!s->vol) return (uint32_t)VRT_TRAVERSAL_SPARSE;            // two-level volume: two-level fields
     static const int forced = getenv("VRT_DEFAULT_TRAVERSAL") ? atoi(getenv("VRT_DEFAULT_TRAVERSAL")) : 0;
     if (forced >= VRT_TRAVERSAL_DENSE_U8 && forced <= VRT_TRAVERSAL_SPARSE) return (uint32_t)forced;
     static const double budgetGiB = getenv("VRT_FIELD_BUDGET_GIB") ? atof(getenv("VRT_FIELD_BUDGET_GIB")) : 16.0;
@@ -278,9 +317,9 @@ extern "C" int vrt_scene_prepare(vrt_scene* s, uint32_t traversal) {
 }
 extern "C" int vrt_scene_memory(const vrt_scene* s, size_t* volume_bytes, size_t* field_bytes, size_t* peak_build_bytes, double* load_ms) {
     if (!s) return fail(VRT_E_INVALID, "null argument");
-    if (volume_bytes) *volume_bytes = (size_t)s->w * s->h * s->d;
+    if (volume_bytes) *volume_bytes = s->volumeBytes;
     if (field_bytes) *field_bytes = s->fieldBytes;
-    if (peak_build_bytes) *peak_build_bytes = s->peakBuildBytes + (size_t)s->w * s->h * s->d;
+    if (peak_build_bytes) *peak_build_bytes = s->peakBuildBytes + s->volumeBytes;
     if (load_ms) *load_ms = s->loadMs;
     return VRT_OK;
 }
@@ -304,6 +343,7 @@ extern "C" int vrt_scene_from_dense(vrt_context* c, const uint8_t* volume, uint3
     if (rc) return rc;
     cudaError_t e = cudaMemcpyAsync(s->vol, volume, (size_t)w * h * d, cudaMemcpyHostToDevice, c->stream);
     if (e != cudaSuccess) { vrt_scene_destroy(s); return fail(VRT_E_CUDA, cudaGetErrorString(e)); }
+    if (volume_wants_sparse(w, h, d)) { rc = scene_make_sparse_volume(s, 0, 0); if (rc) { vrt_scene_destroy(s); return rc; } }
     rc = scene_finish(s, palette, t0);
     if (rc) { vrt_scene_destroy(s); return rc; }
     *out = s;
@@ -342,6 +382,7 @@ static int scene_from_layout(vrt_context* c, const VoxLayout& lay, vrt_scene** o
     const cudaError_t e2 = cudaStreamSynchronize(c->stream);   // lay's host buffers are pageable: the copies must be done before they go away
     for (uint8_t* p : dmodels) cudaFree(p);
     if (e != cudaSuccess || e2 != cudaSuccess) { vrt_scene_destroy(s); return fail(e == cudaErrorMemoryAllocation ? VRT_E_OOM : VRT_E_CUDA, cudaGetErrorString(e != cudaSuccess ? e : e2)); }
+    if (volume_wants_sparse(lay.w, lay.h, lay.d)) { rc = scene_make_sparse_volume(s, 0, 0); if (rc) { vrt_scene_destroy(s); return rc; } }
     rc = scene_finish(s, lay.palette, t0);
     if (rc) { vrt_scene_destroy(s); return rc; }
     *out = s;
@@ -373,10 +414,16 @@ extern "C" int vrt_scene_generate(vrt_context* c, int generator, uint64_t seed, 
     if (generator != 1 && generator != 2) return fail(VRT_E_INVALID, "unknown generator");
     vrt_scene* s = nullptr;
     const double t0 = now_ms();
-    int rc = scene_alloc(c, w, h, d, &s);
+    const bool sparse = volume_wants_sparse(w, h, d);
+    int rc = scene_alloc(c, w, h, d, &s, !sparse);
     if (rc) return rc;
-    cudaError_t e = launch_generate(generator, (uint32_t)seed, s->vol, w, h, d, c->stream);
-    if (e != cudaSuccess) { vrt_scene_destroy(s); return fail(VRT_E_CUDA, cudaGetErrorString(e)); }
+    if (sparse) {                                                   // brick by brick from the generator: no dense volume, ever
+        rc = scene_make_sparse_volume(s, generator, (uint32_t)seed);
+        if (rc) { vrt_scene_destroy(s); return rc; }
+    } else {
+        cudaError_t e = launch_generate(generator, (uint32_t)seed, s->vol, w, h, d, c->stream);
+        if (e != cudaSuccess) { vrt_scene_destroy(s); return fail(VRT_E_CUDA, cudaGetErrorString(e)); }
+    }
     vrt_material pal[256];
     generator_palette(generator, (uint32_t)seed, pal);
     rc = scene_finish(s, pal, t0);
@@ -415,7 +462,21 @@ extern "C" int vrt_scene_palette(const vrt_scene* s, vrt_material palette[256]) 
 extern "C" int vrt_scene_download_volume(const vrt_scene* s, uint8_t* dst, size_t bytes) {
     if (!s || !dst || bytes != (size_t)s->w * s->h * s->d) return fail(VRT_E_INVALID, "bad size");
     CU(cudaSetDevice(s->ctx->device));
-    CU(cudaMemcpy(dst, s->vol, bytes, cudaMemcpyDeviceToHost));
+    if (s->vol) { CU(cudaMemcpy(dst, s->vol, bytes, cudaMemcpyDeviceToHost)); return VRT_OK; }
+    // two-level volume: expanded slab by slab through a bounded device buffer (tests only)
+    const size_t slice = (size_t)s->w * s->h;
+    const uint32_t slabD = (uint32_t)std::max<size_t>(1, std::min<size_t>(s->d, ((size_t)256 << 20) / slice));
+    uint8_t* tmp = nullptr;
+    CU(cudaMalloc(&tmp, slice * slabD));
+    cudaError_t e = cudaSuccess;
+    for (uint32_t z0 = 0; z0 < s->d && e == cudaSuccess; z0 += slabD) {
+        const uint32_t nz = std::min(slabD, s->d - z0);
+        e = launch_sparse_volume_expand(s->vtop, s->vfine, s->w, s->h, s->d, z0, nz, tmp, s->ctx->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(dst + slice * z0, tmp, slice * nz, cudaMemcpyDeviceToHost, s->ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s->ctx->stream);
+    }
+    cudaFree(tmp);
+    if (e != cudaSuccess) return cuda_fail(e);
     return VRT_OK;
 }
 extern "C" int vrt_scene_accel_info(const vrt_scene* s, size_t* dense_bytes, size_t* brick_mask_bytes, size_t* brick_dist_bytes) {
@@ -635,6 +696,7 @@ int vrt_render_impl(vrt_context* c, const vrt_scene* s, const vrt_camera* cam, c
     SceneDev sc{};
     for (int o = 0; o < 8; o++) { sc.odist[o] = s->odist[o]; sc.sdist[o].top = s->stop[o]; sc.sdist[o].fine = s->sfine[o]; }
     sc.TBx = s->TB[0]; sc.TBy = s->TB[1]; sc.TBz = s->TB[2];
+    sc.svol.top = s->vtop; sc.svol.fine = s->vfine;
     sc.vol = s->vol; sc.bmask = s->bmask; sc.bdist = s->bdist; sc.fdist = s->fdist; sc.ldist = s->ldist; sc.W = s->w; sc.H = s->h; sc.D = s->d; sc.Bx = s->Bx; sc.By = s->By; sc.Bz = s->Bz;
     sc.palette = s->palette; sc.noise = s->noise; sc.sky = s->sky; sc.skyW = s->skyW; sc.skyH = s->skyH;
     FrameParams fp{};

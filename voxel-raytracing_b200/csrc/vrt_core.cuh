@@ -137,8 +137,16 @@ VRT_HD uint32_t dda_step_literal(Dda& s) {   // exactly as written in the shader
 VRT_HD bool in_bounds(const SceneDev& sc, const Dda& s) {
     return (unsigned)s.mx < sc.W && (unsigned)s.my < sc.H && (unsigned)s.mz < sc.D;
 }
+// one byte of a two-level field / volume (SceneDev::sdist, ::svol): the brick's word, then the per-voxel byte only for bricks that have one
+VRT_HD uint32_t sparse_fetch(const SceneDev& sc, const SparseField& f, int x, int y, int z) {   // x in [-1, W], y in [-1, H], z in [-1, D]
+    const uint32_t X = (uint32_t)(x + 8), Y = (uint32_t)(y + 8), Z = (uint32_t)(z + 8);
+    const uint32_t e = f.top[(X >> 3) + ((Y >> 3) + (Z >> 3) * sc.TBy) * sc.TBx];
+    if (!(e & VRT_SP_FINE)) return e;
+    return f.fine[(size_t)(e & ~VRT_SP_FINE) * 512u + ((X & 7u) | ((Y & 7u) << 3) | ((Z & 7u) << 6))];
+}
 VRT_HD uint32_t fetch_voxel(const SceneDev& sc, const Dda& s) {   // getVoxel :73-77 as an integer fetch
-    return sc.vol[(size_t)s.mx + (size_t)s.my * sc.W + (size_t)s.mz * sc.W * (size_t)sc.H];
+    if (sc.vol) return sc.vol[(size_t)s.mx + (size_t)s.my * sc.W + (size_t)s.mz * sc.W * (size_t)sc.H];
+    return sparse_fetch(sc, sc.svol, s.mx, s.my, s.mz);           // scenes over the dense budget: the volume is two-level too
 }
 
 // ---- VRT_TRAVERSAL_LINEAR: resumable ray over the aproned linear safe-step field (ldist) ----
@@ -240,12 +248,6 @@ VRT_HD void lin_map_pos(const LinRay& r, int& mx, int& my, int& mz) {
 // ---- VRT_TRAVERSAL_SPARSE: the same resumable ray over the two-level directional fields (SceneDev::sdist) ----
 // The look-up needs the voxel itself (brick index + position inside the brick): per axis the entry coordinate plus the recovered step
 // count. One 4-byte load of the top level (L2-resident), and a second, dependent byte load only for bricks near a surface.
-VRT_HD uint32_t sparse_fetch(const SceneDev& sc, const SparseField& f, int x, int y, int z) {   // x in [-1, W], y in [-1, H], z in [-1, D]
-    const uint32_t X = (uint32_t)(x + 8), Y = (uint32_t)(y + 8), Z = (uint32_t)(z + 8);
-    const uint32_t e = f.top[(X >> 3) + ((Y >> 3) + (Z >> 3) * sc.TBy) * sc.TBx];
-    if (!(e & VRT_SP_FINE)) return e;
-    return f.fine[(size_t)(e & ~VRT_SP_FINE) * 512u + ((X & 7u) | ((Y & 7u) << 3) | ((Z & 7u) << 6))];
-}
 VRT_HD SparseField sparse_octant_field(const SceneDev& sc, const Dda& s) {
     return sc.sdist[(s.stx < 0 ? 1 : 0) | (s.sty < 0 ? 2 : 0) | (s.stz < 0 ? 4 : 0)];
 }

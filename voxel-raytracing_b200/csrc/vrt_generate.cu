@@ -4,29 +4,9 @@
 // index = x + y*W + z*W*H with +y up (what voxel_scene.cpp:99 produces from MagicaVoxel's z-up models).
 #include <cuda_runtime.h>
 #include "vrt_launch.h"
+#include "vrt_generate.cuh"
 
 namespace vrt {
-
-__host__ __device__ inline uint32_t lowbias32(uint32_t x) {   // Chris Wellons' lowbias32 (public domain)
-    x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16; return x;
-}
-__host__ __device__ inline uint32_t mixh(uint32_t h, uint32_t v) { return lowbias32(h ^ (v + 0x9e3779b9u + (h << 6) + (h >> 2))); }
-__host__ __device__ inline uint32_t hash3(uint32_t seed, uint32_t a, uint32_t b, uint32_t c) { return mixh(mixh(mixh(lowbias32(seed), a), b), c); }
-
-// ---- generator 1: noise terrain (5 octaves of bilinear value noise on hashed lattices, cells 256..16) + pillars ----
-__device__ inline uint32_t terrain_height(uint32_t seed, uint32_t x, uint32_t z, uint32_t H) {
-    uint32_t acc = 0;
-    for (uint32_t o = 0; o < 5; o++) {
-        const uint32_t sh = 8 - o, cell = 1u << sh;
-        const uint32_t ix = x >> sh, fx = x & (cell - 1), iz = z >> sh, fz = z & (cell - 1);
-        const uint32_t v00 = hash3(seed + o, ix, iz, 0x5EEDu) & 0xFFFFu, v10 = hash3(seed + o, ix + 1, iz, 0x5EEDu) & 0xFFFFu;
-        const uint32_t v01 = hash3(seed + o, ix, iz + 1, 0x5EEDu) & 0xFFFFu, v11 = hash3(seed + o, ix + 1, iz + 1, 0x5EEDu) & 0xFFFFu;
-        const uint32_t top = v00 * (cell - fx) + v10 * fx, bot = v01 * (cell - fx) + v11 * fx;   // < 2^24
-        const uint32_t val = (top * (cell - fz) + bot * fz) >> (2 * sh);                          // < 2^32 before the shift
-        acc += val >> o;
-    }
-    return H * 3 / 8 + ((acc * (H / 4)) >> 17);
-}
 
 __global__ void gen_terrain_kernel(uint32_t seed, uint8_t* __restrict__ vol, uint32_t W, uint32_t H, uint32_t D) {
     const uint32_t x = blockIdx.x * blockDim.x + threadIdx.x, z = blockIdx.y;

@@ -39,6 +39,8 @@ struct vrt_scene {
     uint32_t sfineBricks[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     uint32_t TB[3] = {0, 0, 0};
     bool sparseReady = false;
+    uint32_t* vtop = nullptr; uint8_t* vfine = nullptr; uint32_t vfineBricks = 0;   // the palette volume, two-level (vol == nullptr then)
+    size_t volumeBytes = 0;              // device bytes of the volume as stored (dense, or top + bricks)
     vrt_material* palette = nullptr; vrt_material hostPalette[256];
     uint8_t* noise = nullptr; float* sky = nullptr; uint32_t skyW = 0, skyH = 0;
     int accelLaunches = 0;

@@ -37,6 +37,10 @@ cudaError_t launch_odist_octant(uint32_t W, uint32_t H, uint32_t D, int octant, 
 void sparse_top_dims(uint32_t W, uint32_t H, uint32_t D, uint32_t tb[3]);
 cudaError_t launch_sparse_classify(const uint8_t* lin, uint32_t W, uint32_t H, uint32_t D, uint32_t* top, uint32_t* fineCount, cudaStream_t stream);
 cudaError_t launch_sparse_fill(const uint8_t* lin, uint32_t W, uint32_t H, uint32_t D, const uint32_t* top, uint8_t* fine, cudaStream_t stream);
+cudaError_t launch_sparse_volume_classify(const uint8_t* vol, int generator, uint32_t seed, uint32_t W, uint32_t H, uint32_t D, uint32_t* top, uint32_t* fineCount, cudaStream_t stream);
+cudaError_t launch_sparse_volume_fill(const uint8_t* vol, int generator, uint32_t seed, uint32_t W, uint32_t H, uint32_t D, const uint32_t* top, uint8_t* fine, cudaStream_t stream);
+cudaError_t launch_sparse_volume_expand(const uint32_t* top, const uint8_t* fine, uint32_t W, uint32_t H, uint32_t D, uint32_t zBase, uint32_t slabD, uint8_t* out, cudaStream_t stream);
+cudaError_t launch_odist_init_sparse(const uint32_t* top, const uint8_t* fine, uint32_t W, uint32_t H, uint32_t D, uint32_t* scratch, cudaStream_t stream, int* launches);
 cudaError_t launch_sparse_expand(const uint32_t* top, const uint8_t* fine, uint32_t W, uint32_t H, uint32_t D, uint8_t* out, cudaStream_t stream);
 
 // procedural volumes (vrt_generate.cu)

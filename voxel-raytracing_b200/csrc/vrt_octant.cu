@@ -9,6 +9,7 @@
 // voxel satisfies (bit-sliced adder) and writes the byte field. Load-time only: HBM-streaming, ~200 launches per scene.
 #include <cuda_runtime.h>
 #include "vrt_launch.h"
+#include "vrt_generate.cuh"
 
 namespace vrt {
 
@@ -131,18 +132,38 @@ cudaError_t launch_odist_octant(uint32_t W, uint32_t H, uint32_t D, int o, uint8
 // ---- two-level (sparse) layout of one octant's field: SceneDev::sdist (vrt_types.h) ----
 // One block of 64 threads per 8x8x8 brick; thread t owns the 8 voxels of row (y, z) = (t & 7, t >> 3). `lin` is the aproned linear
 // field; brick coordinates are shifted by one brick (voxel x of brick bx: bx*8 - 8 + i), voxels beyond the apron count as outside.
-__device__ __forceinline__ uint32_t sp_code_at(const uint8_t* __restrict__ lin, int x, int y, int z, int W, int H, int D) {
-    if (x < -1 || y < -1 || z < -1 || x > W || y > H || z > D) return VRT_LIN_OOB;
-    return lin[(size_t)(x + 1) + (size_t)(y + 1) * (size_t)(W + 2) + (size_t)(z + 1) * (size_t)(W + 2) * (size_t)(H + 2)];
-}
-// pass 1: classify every brick; bricks that need per-voxel codes get a slot of the pool (atomic counter)
-__global__ void __launch_bounds__(64) sp_classify_kernel(const uint8_t* __restrict__ lin, int W, int H, int D, uint32_t TBx, uint32_t TBy, uint32_t* __restrict__ top,
-                                                         uint32_t* __restrict__ fineCount) {
+// where a brick's 512 byte codes come from
+struct SrcField {     // an octant's aproned linear safe-step field; beyond the apron = outside
+    const uint8_t* lin; int W, H, D;
+    __device__ __forceinline__ uint32_t operator()(int x, int y, int z) const {
+        if (x < -1 || y < -1 || z < -1 || x > W || y > H || z > D) return VRT_LIN_OOB;
+        return lin[(size_t)(x + 1) + (size_t)(y + 1) * (size_t)(W + 2) + (size_t)(z + 1) * (size_t)(W + 2) * (size_t)(H + 2)];
+    }
+};
+struct SrcDenseVol {  // the dense palette volume; outside = 0 (empty)
+    const uint8_t* vol; int W, H, D;
+    __device__ __forceinline__ uint32_t operator()(int x, int y, int z) const {
+        if (x < 0 || y < 0 || z < 0 || x >= W || y >= H || z >= D) return 0u;
+        return vol[(size_t)x + (size_t)y * (size_t)W + (size_t)z * (size_t)W * (size_t)H];
+    }
+};
+struct SrcGenerator { // a procedural volume, evaluated in place: the dense volume is never materialised
+    int generator; uint32_t seed; int W, H, D;
+    __device__ __forceinline__ uint32_t operator()(int x, int y, int z) const {
+        if (x < 0 || y < 0 || z < 0 || x >= W || y >= H || z >= D) return 0u;
+        return gen_voxel(generator, seed, (uint32_t)x, (uint32_t)y, (uint32_t)z, (uint32_t)W, (uint32_t)H, (uint32_t)D);
+    }
+};
+// pass 1: classify every brick; bricks that need per-voxel codes get a slot of the pool (atomic counter). FIELD: the codes are safe-step
+// budgets, so a brick without solid / outside voxels whose minimum is at least VRT_SP_UNIFORM_MIN may stand for all of its voxels;
+// a volume brick (palette indices) is uniform only if all 512 values are equal.
+template <class SRC, bool FIELD>
+__global__ void __launch_bounds__(64) sp_classify_kernel(const SRC src, uint32_t TBx, uint32_t TBy, uint32_t* __restrict__ top, uint32_t* __restrict__ fineCount) {
     const uint32_t bx = blockIdx.x, by = blockIdx.y, bz = blockIdx.z, t = threadIdx.x;
     const int y = (int)by * 8 - 8 + (int)(t & 7u), z = (int)bz * 8 - 8 + (int)(t >> 3);
     uint32_t mn = 0xffffffffu, first = 0, same = 1, special = 0;
     for (int i = 0; i < 8; i++) {
-        const uint32_t c = sp_code_at(lin, (int)bx * 8 - 8 + i, y, z, W, H, D);
+        const uint32_t c = src((int)bx * 8 - 8 + i, y, z);
         if (i == 0) first = c;
         same &= c == first ? 1u : 0u;
         special |= (c == 0u || c == VRT_LIN_OOB) ? 1u : 0u;
@@ -160,21 +181,41 @@ __global__ void __launch_bounds__(64) sp_classify_kernel(const uint8_t* __restri
         const uint32_t m = min(sMin[0], sMin[1]);
         uint32_t e;
         if (allSame) e = sFirst[0];
-        else if (!anySpecial && m >= VRT_SP_UNIFORM_MIN) e = safe_encode(m);       // the minimum is a valid lower bound for every voxel of the brick
+        else if (FIELD && !anySpecial && m >= VRT_SP_UNIFORM_MIN) e = safe_encode(m);   // the minimum is a valid lower bound for every voxel of the brick
         else e = VRT_SP_FINE | atomicAdd(fineCount, 1u);
         top[bx + (by + (size_t)bz * TBy) * TBx] = e;
     }
 }
 // pass 2: per-voxel codes of the bricks that were given a slot
-__global__ void __launch_bounds__(64) sp_fill_kernel(const uint8_t* __restrict__ lin, int W, int H, int D, uint32_t TBx, uint32_t TBy, const uint32_t* __restrict__ top,
-                                                     uint8_t* __restrict__ fine) {
+template <class SRC>
+__global__ void __launch_bounds__(64) sp_fill_kernel(const SRC src, uint32_t TBx, uint32_t TBy, const uint32_t* __restrict__ top, uint8_t* __restrict__ fine) {
     const uint32_t bx = blockIdx.x, by = blockIdx.y, bz = blockIdx.z, t = threadIdx.x;
     const uint32_t e = top[bx + (by + (size_t)bz * TBy) * TBx];
     if (!(e & VRT_SP_FINE)) return;
     const int y = (int)by * 8 - 8 + (int)(t & 7u), z = (int)bz * 8 - 8 + (int)(t >> 3);
     unsigned long long row = 0ull;
-    for (int i = 0; i < 8; i++) row |= (unsigned long long)sp_code_at(lin, (int)bx * 8 - 8 + i, y, z, W, H, D) << (8 * i);
+    for (int i = 0; i < 8; i++) row |= (unsigned long long)src((int)bx * 8 - 8 + i, y, z) << (8 * i);
     reinterpret_cast<unsigned long long*>(fine + (size_t)(e & ~VRT_SP_FINE) * 512u)[t] = row;   // (x&7) | (y&7)<<3 | (z&7)<<6
+}
+__device__ __forceinline__ uint32_t sp_fetch(const uint32_t* __restrict__ top, const uint8_t* __restrict__ fine, uint32_t TBx, uint32_t TBy, int x, int y, int z) {
+    const uint32_t X = (uint32_t)(x + 8), Y = (uint32_t)(y + 8), Z = (uint32_t)(z + 8);
+    const uint32_t e = top[(X >> 3) + ((Y >> 3) + (size_t)(Z >> 3) * TBy) * TBx];
+    return (e & VRT_SP_FINE) ? fine[(size_t)(e & ~VRT_SP_FINE) * 512u + ((X & 7u) | ((Y & 7u) << 3) | ((Z & 7u) << 6))] : e;
+}
+// emptiness bits (level 0 of the octant build) and a dense copy (tests) from a two-level volume
+__global__ void oct_init_sparse_kernel(const uint32_t* __restrict__ top, const uint8_t* __restrict__ fine, uint32_t TBx, uint32_t TBy, uint32_t* __restrict__ bits,
+                                       uint32_t W, uint32_t H, uint32_t WW) {
+    const uint32_t wx = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y, z = blockIdx.z;
+    if (wx >= WW || y >= H) return;
+    uint32_t m = 0;
+    for (uint32_t b = 0; b < 32u && wx * 32u + b < W; b++) if (sp_fetch(top, fine, TBx, TBy, (int)(wx * 32u + b), (int)y, (int)z) == 0u) m |= 1u << b;
+    bits[(size_t)wx + (size_t)y * WW + (size_t)z * WW * H] = m;
+}
+__global__ void sp_expand_volume_kernel(const uint32_t* __restrict__ top, const uint8_t* __restrict__ fine, uint32_t TBx, uint32_t TBy, uint8_t* __restrict__ out,
+                                        uint32_t W, uint32_t H, uint32_t zBase) {
+    const uint32_t x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, z = blockIdx.z;
+    if (x >= W) return;
+    out[(size_t)x + (size_t)y * W + (size_t)z * W * H] = (uint8_t)sp_fetch(top, fine, TBx, TBy, (int)x, (int)y, (int)(z + zBase));
 }
 // expand a sparse field back to the aproned linear layout (tests)
 __global__ void sp_expand_kernel(const uint32_t* __restrict__ top, const uint8_t* __restrict__ fine, uint32_t TBx, uint32_t TBy, uint8_t* __restrict__ out, int W, int H, int D) {
@@ -189,12 +230,44 @@ __global__ void sp_expand_kernel(const uint32_t* __restrict__ top, const uint8_t
 void sparse_top_dims(uint32_t W, uint32_t H, uint32_t D, uint32_t tb[3]) { tb[0] = ((W + 8u) >> 3) + 1u; tb[1] = ((H + 8u) >> 3) + 1u; tb[2] = ((D + 8u) >> 3) + 1u; }
 cudaError_t launch_sparse_classify(const uint8_t* lin, uint32_t W, uint32_t H, uint32_t D, uint32_t* top, uint32_t* fineCount, cudaStream_t stream) {
     uint32_t tb[3]; sparse_top_dims(W, H, D, tb);
-    sp_classify_kernel<<<dim3(tb[0], tb[1], tb[2]), 64, 0, stream>>>(lin, (int)W, (int)H, (int)D, tb[0], tb[1], top, fineCount);
+    sp_classify_kernel<SrcField, true><<<dim3(tb[0], tb[1], tb[2]), 64, 0, stream>>>(SrcField{lin, (int)W, (int)H, (int)D}, tb[0], tb[1], top, fineCount);
     return cudaGetLastError();
 }
 cudaError_t launch_sparse_fill(const uint8_t* lin, uint32_t W, uint32_t H, uint32_t D, const uint32_t* top, uint8_t* fine, cudaStream_t stream) {
     uint32_t tb[3]; sparse_top_dims(W, H, D, tb);
-    sp_fill_kernel<<<dim3(tb[0], tb[1], tb[2]), 64, 0, stream>>>(lin, (int)W, (int)H, (int)D, tb[0], tb[1], top, fine);
+    sp_fill_kernel<SrcField><<<dim3(tb[0], tb[1], tb[2]), 64, 0, stream>>>(SrcField{lin, (int)W, (int)H, (int)D}, tb[0], tb[1], top, fine);
+    return cudaGetLastError();
+}
+// the palette volume itself in the two-level layout: from a dense volume (vol != null) or straight from a generator (vol == null)
+cudaError_t launch_sparse_volume_classify(const uint8_t* vol, int generator, uint32_t seed, uint32_t W, uint32_t H, uint32_t D, uint32_t* top, uint32_t* fineCount, cudaStream_t stream) {
+    uint32_t tb[3]; sparse_top_dims(W, H, D, tb);
+    const dim3 grid(tb[0], tb[1], tb[2]);
+    if (vol) sp_classify_kernel<SrcDenseVol, false><<<grid, 64, 0, stream>>>(SrcDenseVol{vol, (int)W, (int)H, (int)D}, tb[0], tb[1], top, fineCount);
+    else sp_classify_kernel<SrcGenerator, false><<<grid, 64, 0, stream>>>(SrcGenerator{generator, seed, (int)W, (int)H, (int)D}, tb[0], tb[1], top, fineCount);
+    return cudaGetLastError();
+}
+cudaError_t launch_sparse_volume_fill(const uint8_t* vol, int generator, uint32_t seed, uint32_t W, uint32_t H, uint32_t D, const uint32_t* top, uint8_t* fine, cudaStream_t stream) {
+    uint32_t tb[3]; sparse_top_dims(W, H, D, tb);
+    const dim3 grid(tb[0], tb[1], tb[2]);
+    if (vol) sp_fill_kernel<SrcDenseVol><<<grid, 64, 0, stream>>>(SrcDenseVol{vol, (int)W, (int)H, (int)D}, tb[0], tb[1], top, fine);
+    else sp_fill_kernel<SrcGenerator><<<grid, 64, 0, stream>>>(SrcGenerator{generator, seed, (int)W, (int)H, (int)D}, tb[0], tb[1], top, fine);
+    return cudaGetLastError();
+}
+// z-slab [zBase, zBase + slabD) of a two-level volume as dense bytes (vrt_scene_download_volume)
+cudaError_t launch_sparse_volume_expand(const uint32_t* top, const uint8_t* fine, uint32_t W, uint32_t H, uint32_t D, uint32_t zBase, uint32_t slabD, uint8_t* out, cudaStream_t stream) {
+    uint32_t tb[3]; sparse_top_dims(W, H, D, tb);
+    sp_expand_volume_kernel<<<dim3((W + 127u) / 128u, H, slabD), 128, 0, stream>>>(top, fine, tb[0], tb[1], out, W, H, zBase);
+    return cudaGetLastError();
+}
+// level 0 of the octant build from a two-level volume
+cudaError_t launch_odist_init_sparse(const uint32_t* top, const uint8_t* fine, uint32_t W, uint32_t H, uint32_t D, uint32_t* scratch, cudaStream_t stream, int* launches) {
+    cudaError_t e = upload_level_table(stream);
+    if (e != cudaSuccess) return e;
+    uint32_t tb[3]; sparse_top_dims(W, H, D, tb);
+    const uint32_t WW = (W + 31u) / 32u;
+    const dim3 block(32, 8), grid((WW + 31u) / 32u, (H + 7u) / 8u, D);
+    oct_init_sparse_kernel<<<grid, block, 0, stream>>>(top, fine, tb[0], tb[1], scratch, W, H, WW);
+    if (launches) *launches += 1;
     return cudaGetLastError();
 }
 cudaError_t launch_sparse_expand(const uint32_t* top, const uint8_t* fine, uint32_t W, uint32_t H, uint32_t D, uint8_t* out, cudaStream_t stream) {

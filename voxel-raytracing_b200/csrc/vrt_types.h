@@ -59,7 +59,8 @@ constexpr uint32_t VRT_SP_UNIFORM_MIN = VRT_SP_UNIFORM_MIN_V;
 struct SparseField { const uint32_t* top; const uint8_t* fine; };
 
 struct SceneDev {
-    const uint8_t* vol;               // dense u8[W*H*D], x fastest (voxel_scene.cpp:99)
+    const uint8_t* vol;               // dense u8[W*H*D], x fastest (voxel_scene.cpp:99); null when the volume is kept two-level (svol)
+    SparseField svol;                 // the palette volume in the two-level layout of sdist (bricks of one value + 512-byte bricks), scenes over the dense budget
     const unsigned long long* bmask;  // [Bz][By][Bx]
     const uint8_t* bdist;             // [Bz][By][Bx]
     const uint8_t* fdist;             // [Bz][By][Bx][4][4][4]
