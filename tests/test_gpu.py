@@ -627,8 +627,9 @@ def test_two_level_volume_is_byte_identical(gpu_ctx, monkeypatch):
     for pipe in PIPELINES:
         check(gpu_render(gpu_ctx, gs, cam, st, 0, pipeline=pipe), want)                       # default resolves to the two-level fields
     check(gpu_render(gpu_ctx, gs, cam, st, TRAV_DENSE), want)                                  # one fetch per step through the two-level volume
+    check(gpu_render(gpu_ctx, gs, cam, st, 5), want)                                           # linear fields built from the two-level volume
     with pytest.raises(pyvrt.VrtError) as e:
-        gpu_render(gpu_ctx, gs, cam, st, 5)
+        gpu_render(gpu_ctx, gs, cam, st, 4)
     assert e.value.code == pyvrt.E_UNSUPPORTED
     gs.destroy()
     rng = np.random.default_rng(3)                                      # uploaded volumes are compacted after the upload

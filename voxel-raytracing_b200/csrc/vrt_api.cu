@@ -223,13 +223,14 @@ static int scene_ensure_iso(vrt_scene* s, bool wantFine, bool wantLinear) {
 // directional safe-step fields (OCTANT): 8 fields of one byte per voxel
 static int scene_ensure_octant(vrt_scene* s) {
     if (s->odist[0]) return VRT_OK;
-    { const int rc = dense_only(s); if (rc) return rc; }
     vrt_context* c = s->ctx;
     const size_t fieldBytes = (size_t)(s->w + 2) * (s->h + 2) * (s->d + 2), scratchBytes = octant_scratch_bytes(s->w, s->h, s->d);
     uint32_t* scratch = nullptr;
     cudaError_t e = cudaMalloc(&scratch, scratchBytes);
     for (int o = 0; o < 8 && e == cudaSuccess; o++) e = cudaMalloc(&s->odist[o], fieldBytes);
-    if (e == cudaSuccess) e = launch_build_odist(s->vol, s->w, s->h, s->d, s->odist, scratch, c->stream, &s->accelLaunches);
+    if (e == cudaSuccess) e = s->vol ? launch_odist_init(s->vol, s->w, s->h, s->d, scratch, c->stream, &s->accelLaunches)
+                                     : launch_odist_init_sparse(s->vtop, s->vfine, s->w, s->h, s->d, scratch, c->stream, &s->accelLaunches);
+    for (int o = 0; o < 8 && e == cudaSuccess; o++) e = launch_odist_octant(s->w, s->h, s->d, o, s->odist[o], scratch, c->stream, &s->accelLaunches);
     const cudaError_t e2 = cudaStreamSynchronize(c->stream);
     cudaFree(scratch);
     if (e == cudaSuccess) e = e2;
@@ -286,7 +287,6 @@ static int scene_ensure_sparse(vrt_scene* s) {
 // the two-level layout beyond it (VRT_DEFAULT_TRAVERSAL / VRT_FIELD_BUDGET_GIB override, for measurement)
 static uint32_t resolve_traversal(const vrt_scene* s, uint32_t traversal) {
     if (traversal != VRT_TRAVERSAL_DEFAULT) return traversal;
-    if (!s->vol) return (uint32_t)VRT_TRAVERSAL_SPARSE;            // two-level volume: two-level fields
     static const int forced = getenv("VRT_DEFAULT_TRAVERSAL") ? atoi(getenv("VRT_DEFAULT_TRAVERSAL")) : 0;
     if (forced >= VRT_TRAVERSAL_DENSE_U8 && forced <= VRT_TRAVERSAL_SPARSE) return (uint32_t)forced;
     static const double budgetGiB = getenv("VRT_FIELD_BUDGET_GIB") ? atof(getenv("VRT_FIELD_BUDGET_GIB")) : 16.0;
