@@ -215,6 +215,21 @@ int vrt_denoise(vrt_context*, const void* d_color_rgba8, const void* d_normal_rg
  * (needed when iterations > 1). This is what rank 0 runs on the assembled planes of a sharded frame. */
 int vrt_denoise_on(vrt_context*, const void* d_color_rgba8, const void* d_normal_rgba8s, const void* d_position_rgba32f,
                    int w, int h, const vrt_denoiser_settings*, void* d_out_rgba8, void* d_scratch_rgba8, void* stream);
+/* vrt_denoise_on for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc). NO COUNTERPART IN THE REFERENCE. Same inputs, output, stream meaning
+ * and results as vrt_denoise_on, but the intermediate image the iterations ping-pong through lives in a file-scope __device__
+ * array of the library (csrc/vrt_denoise.cu) instead of caller memory, and the call performs no cudaMalloc / cudaFree or any
+ * other allocating routine. Limits and rules:
+ *   - w * h <= VRT_DENOISE_STATIC_MAX_PIXELS (one 3840 x 2160 image: 33 177 600 B, held by every GPU that loads the library
+ *     until the process exits); larger images are rejected with VRT_E_INVALID and a message naming the limit.
+ *   - every call on a device shares the one array and it keeps the last call's contents. Nothing in it has to start at zero
+ *     (each iteration writes every pixel of its target before the next one reads it), so nothing is cleared; but two calls
+ *     that overlap on the GPU (different streams, no ordering between them) race on it: order them.
+ *   - the first call on each device resolves the array's device address (cudaGetSymbolAddress, once per device): make one
+ *     call before starting a capture. */
+#define VRT_DENOISE_STATIC_MAX_PIXELS (3840 * 2160)
+int vrt_denoise_static(vrt_context*, const void* d_color_rgba8, const void* d_normal_rgba8s, const void* d_position_rgba32f,
+                       int w, int h, const vrt_denoiser_settings*, void* d_out_rgba8, void* stream);
 
 /* Multi-GPU assembly on the gathering rank: d_gathered holds `world` shard buffers back to back (rank-major), each
  * of vrt_frame_plane() size as produced under vrt_context_set_shard(rank, world); writes a row-major w x h plane. */

@@ -633,7 +633,7 @@ static void denoise_taps(int mode, DenoiseTaps& t) {
     }
 }
 
-static int run_denoise(vrt_context* c, cudaStream_t stream, const void* color, const void* normal, const void* position, int W, int H,
+int run_denoise(vrt_context* c, cudaStream_t stream, const void* color, const void* normal, const void* position, int W, int H,
                        const vrt_denoiser_settings* ds, void* ping[2], int* lastOut, uint32_t* launches) {
     if (ds->iterations < 1 || ds->iterations > 10) return fail(VRT_E_INVALID, "denoiser iterations must be 1..10 (MAX_DENOISER_PASSES)");
     if (ds->mode != VRT_DENOISE_AS_EXECUTED && ds->mode != VRT_DENOISE_AS_INTENDED) return fail(VRT_E_INVALID, "bad denoise mode");

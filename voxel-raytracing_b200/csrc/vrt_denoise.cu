@@ -156,3 +156,46 @@ cudaError_t launch_denoise(const uint8_t* color, const int8_t* normal, const flo
 }
 
 }  // namespace vrt
+
+// ---- vrt_denoise_static: the denoiser without any allocation (include/vrt.h; no counterpart in the reference).
+// The intermediate image of the ping-pong is this file-scope array. In HOST code `g_denoise_scratch` is only a
+// stand-in for the symbol, not a device address: the address is resolved once per device with cudaGetSymbolAddress (that device
+// current) and it is that pointer the kernels are given. All calls on a device share the array; see the header for the rules.
+#include <mutex>
+#include "vrt_internal.h"
+
+static __device__ __align__(256) unsigned char g_denoise_scratch[(size_t)VRT_DENOISE_STATIC_MAX_PIXELS * 4];
+
+static constexpr int kScratchMaxDevices = 64;
+static std::mutex g_scratchMutex;
+static void* g_scratchPtr[kScratchMaxDevices] = {};   // device address of g_denoise_scratch on each device, resolved on first use
+
+// the current device must be `device`
+static int denoise_scratch_address(int device, void** out) {
+    if (device < 0 || device >= kScratchMaxDevices) return fail(VRT_E_UNSUPPORTED, "vrt_denoise_static: device ordinal beyond 63");
+    std::lock_guard<std::mutex> lock(g_scratchMutex);
+    if (!g_scratchPtr[device]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_denoise_scratch);
+        if (e != cudaSuccess || !p) return fail(VRT_E_CUDA, std::string("cudaGetSymbolAddress(g_denoise_scratch): ") + cudaGetErrorString(e));
+        g_scratchPtr[device] = p;
+    }
+    *out = g_scratchPtr[device];
+    return VRT_OK;
+}
+
+extern "C" int vrt_denoise_static(vrt_context* c, const void* d_color, const void* d_normal, const void* d_position, int w, int h,
+                                  const vrt_denoiser_settings* ds, void* d_out, void* stream) {
+    if (!c || !d_color || !d_normal || !d_position || !ds || !d_out || w <= 0 || h <= 0) return fail(VRT_E_INVALID, "null argument");
+    if (d_out == d_color) return fail(VRT_E_INVALID, "d_out must not alias d_color (iteration 0 reads neighbours while it writes)");
+    if ((long long)w * (long long)h > (long long)VRT_DENOISE_STATIC_MAX_PIXELS)
+        return fail(VRT_E_INVALID, "vrt_denoise_static: w * h = " + std::to_string((long long)w * h) + " pixels exceeds VRT_DENOISE_STATIC_MAX_PIXELS = " +
+                                       std::to_string((long long)VRT_DENOISE_STATIC_MAX_PIXELS) + " (the built-in scratch image); use vrt_denoise_on with a scratch image of your own");
+    CU(cudaSetDevice(c->device));
+    void* scratch = nullptr;
+    if (int rc = denoise_scratch_address(c->device, &scratch)) return rc;
+    void* ping[2] = {d_out, scratch};
+    if (((ds->iterations - 1) % 2) == 1) { ping[0] = scratch; ping[1] = d_out; }   // the last iteration lands in d_out
+    int last = 0; uint32_t n = 0;
+    return run_denoise(c, stream ? (cudaStream_t)stream : c->stream, d_color, d_normal, d_position, w, h, ds, ping, &last, &n);
+}

@@ -79,3 +79,6 @@ struct vrt_frame {
 
 // vrt_render with the fused exchange targets (vrt_api.cu; used by vrt_render_exchange in vrt_comm.cu)
 int vrt_render_impl(vrt_context* c, const vrt_scene* s, const vrt_camera* cam, const vrt_render_settings* st, vrt_frame** frame, const XPlanes* x);
+// the denoiser's iteration loop (vrt_api.cu): iteration i writes ping[i % 2]; used by vrt_denoise, vrt_denoise_on and vrt_denoise_static
+int run_denoise(vrt_context* c, cudaStream_t stream, const void* color, const void* normal, const void* position, int W, int H,
+                const vrt_denoiser_settings* ds, void* ping[2], int* lastOut, uint32_t* launches);

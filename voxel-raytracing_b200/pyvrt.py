@@ -18,6 +18,7 @@ OUT_GBUFFER, OUT_INSTRUMENT = 1, 2
 TRAVERSAL_DEFAULT, TRAVERSAL_DENSE_U8, TRAVERSAL_BRICK, TRAVERSAL_FINE, TRAVERSAL_LINEAR, TRAVERSAL_OCTANT, TRAVERSAL_SPARSE = 0, 1, 2, 3, 4, 5, 6
 PIPELINE_DEFAULT, PIPELINE_MEGAKERNEL, PIPELINE_WAVEFRONT = 0, 1, 2
 DENOISE_AS_EXECUTED, DENOISE_AS_INTENDED = 0, 1
+E_INVALID = -1
 E_LFS_POINTER, E_NO_INSTANCE, E_PARSE, E_IO, E_CUDA, E_NO_DEVICE, E_UNSUPPORTED, E_OOM, E_COMM = -2, -3, -4, -5, -6, -7, -8, -9, -10
 
 # plane id -> (name, dtype, channels)
@@ -501,6 +502,16 @@ def denoise_device_on(ctx: Context, d_color, d_normal, d_position, size, ds: Den
     """vrt_denoise_on: asynchronous, caller-owned scratch (rank 0 on the assembled planes of a sharded frame)."""
     _ck(lib().vrt_denoise_on(ctx.h, C.c_void_p(d_color), C.c_void_p(d_normal), C.c_void_p(d_position), size[0], size[1], C.byref(ds),
                              C.c_void_p(d_out), C.c_void_p(d_scratch), C.c_void_p(stream) if stream else None))
+
+
+DENOISE_STATIC_MAX_PIXELS = 3840 * 2160   # include/vrt.h VRT_DENOISE_STATIC_MAX_PIXELS
+
+
+def denoise_device_static(ctx: Context, d_color, d_normal, d_position, size, ds: DenoiserSettings, d_out, stream=None):
+    """vrt_denoise_static: vrt_denoise_on without a scratch argument and without any allocation (the intermediate image is a
+    __device__ array of the library, at most DENOISE_STATIC_MAX_PIXELS; calls that overlap on the GPU race on it)."""
+    _ck(lib().vrt_denoise_static(ctx.h, C.c_void_p(d_color), C.c_void_p(d_normal), C.c_void_p(d_position), size[0], size[1], C.byref(ds),
+                                 C.c_void_p(d_out), C.c_void_p(stream) if stream else None))
 
 
 def denoise_device(ctx: Context, d_color, d_normal, d_position, size, ds: DenoiserSettings, d_out):
