@@ -341,8 +341,20 @@ def run_vrt(args):
     xhost = () if denoise else ("color",)                    # e2e: every rank stores its tiles into the shared pinned host frame
     host2 = dn_out = dn_scratch = cstream = None
     ds = pyvrt.default_settings().denoise
+    # cfg3 on N > 1 GPUs: the denoiser is distributed ("strips": every rank denoises the rows it owns, vrt_render_denoise_exchange);
+    # VRT_BENCH_ROUTE_A=1 measures route (a) instead (all three planes to rank 0, denoiser there).
+    strips = False
     if world > 1:
-        ctx.comm_alloc_frames(size, S, xplanes, xhost)
+        if denoise and not os.environ.get("VRT_BENCH_ROUTE_A"):
+            ctx.comm_alloc_frames(size, S, xplanes + ("denoised",), ("denoised",))
+            try:
+                ctx.comm_alloc_strips(ds)
+                strips = True
+            except pyvrt.VrtError as e:                       # strips thinner than the denoiser's reach (tiny frames): route (a)
+                if e.code != pyvrt.E_UNSUPPORTED:
+                    raise
+        else:
+            ctx.comm_alloc_frames(size, S, xplanes, xhost)
         if rank == 0 and denoise:
             dn_out = [torch.empty(frame_bytes, dtype=torch.uint8, device=dev) for _ in range(S)]
             dn_scratch = torch.empty(frame_bytes, dtype=torch.uint8, device=dev)
@@ -353,7 +365,7 @@ def run_vrt(args):
     ev_done = [torch.cuda.Event() for _ in range(S)]
     pending = [False] * S
 
-    def submit(k, readback=False):
+    def submit(k, readback=False, route_a=False):
         """Queue frame k: render this rank's tiles; N>1: store them into rank 0's frame (and the shared host frame when the frame is
         read back); rank 0 orders its consumer (denoiser, read-back) behind the arrival of every rank's tiles. Returns the frame and
         the kernels launched outside vrt_render / vrt_frame_exchange (the library counts its own)."""
@@ -364,6 +376,15 @@ def run_vrt(args):
             if readback and world == 1:
                 fr.download_async(final, host2[slot].numpy())
             return fr, 0
+        if strips and not route_a:
+            fr = passes[k % F].record_denoise_exchange(cam, slot, to_host=readback)
+            if rank == 0:
+                ctx.comm_wait(slot)                          # every rank's denoised rows are in the slot's denoised plane
+                if readback:
+                    pending[slot] = True
+                else:
+                    ctx.comm_release(slot, on_stream=True)
+            return fr, 1 if rank == 0 else 0
         if os.environ.get("VRT_BENCH_UNFUSED"):               # measurement only: separate push kernels after the pass
             fr = passes[k % F].record(cam)
             fr.exchange(slot, xplanes, xhost if readback else ())
@@ -398,9 +419,10 @@ def run_vrt(args):
         if world == 1:
             passes[k % F].frame.download_wait()
         elif pending[slot]:
-            if not denoise:
-                ctx.comm_wait_host(slot)                     # every rank's tiles are in the shared pinned host frame
-            ev_done[slot].synchronize()
+            if not denoise or strips:
+                ctx.comm_wait_host(slot)                     # every rank's tiles (strips: denoised rows) are in the shared pinned host frame
+            if not strips:
+                ev_done[slot].synchronize()
             ctx.comm_release(slot)
             pending[slot] = False
 
@@ -415,7 +437,7 @@ def run_vrt(args):
 
     # ---- self-check of the exchange (outside every timed region): the bytes of the assembled frame are the bytes of the shards
     if world > 1 and not os.environ.get("VRT_BENCH_NOEXCHANGE"):
-        fr0, _ = submit(0)
+        fr0, _ = submit(0, route_a=True)
         drain(); barrier()
         ptr, n = fr0.plane_ptr("color")
         mine = checksum(ptr, n)
@@ -425,6 +447,20 @@ def run_vrt(args):
             if not torch.equal(checksum(dptr, nb), mine):
                 raise SystemExit("exchange self-check failed: the assembled frame does not hold the ranks' tiles")
         barrier()
+        if strips:
+            # the distributed denoiser against route (a) on the same frame: rank 0 denoised the assembled planes of slot 0 just now
+            # (submit(0, route_a=True) above); the strips deliver the same frame into slot 1; the two denoised frames must be the same bytes
+            cam0 = configs.make_camera(args.config, bounds, size, 0)
+            passes[1 % F].record_denoise_exchange(cam0, 1, to_host=False)
+            if rank == 0:
+                ctx.comm_wait(1)
+            drain(); barrier()
+            if rank == 0:
+                dptr, _, nb = ctx.comm_frame_plane(1, "denoised")
+                if not torch.equal(torch.as_tensor(_DevBuf(dptr, nb), device=dev), dn_out[0]):
+                    raise SystemExit("strips self-check failed: the distributed denoiser's frame differs from rank 0's denoise of the assembled planes")
+                ctx.comm_release(1)
+            barrier()
 
     # ---- warm-up, then an untimed counting pass over the K timed poses, each frame ALONE on the GPU (rays / voxel visits / kernel
     # times per frame; this is also the single-frame latency)
@@ -540,8 +576,10 @@ def run_vrt(args):
                 "run": {"traversal": args.traversal, "pipeline": args.pipeline, "frames_in_flight": F, "exchange_slots": S if world > 1 else None, "frame_streams": "one" if args.serial_frames else "per frame",
                         "timed_regions": len(region_ms), "timed_ms_total": float(np.sum(region_ms)), "region_ms_min_median_max": [float(np.min(region_ms)), ms, float(np.max(region_ms))],
                         "exchange": ("libvrt vrt_render_exchange: the pass's own kernels store " + "+".join(xplanes) + " of every rank's tiles straight into rank 0's frame (CUDA IPC peer memory over NVLink), "
-                                     "arrival flags and rank 0's wait are stream memory operations (no kernel)" + ("; rank 0 denoises the assembled planes" if denoise else "")) if world > 1 else None,
-                        "e2e_readback": ("every rank stores its tiles into a pinned host frame shared by all ranks (own PCIe link each)" if not denoise else "rank 0 copies the denoised frame to pinned host memory") if world > 1
+                                     "arrival flags and rank 0's wait are stream memory operations (no kernel)" + ("; rank 0 denoises the assembled planes" if denoise else "")) if world > 1 and not strips else
+                                    ("libvrt vrt_render_denoise_exchange (strips): the pass's own kernels store colour+normal+position of every rank's tiles into the buffer of the rank that owns their rows "
+                                     "(CUDA IPC peer memory over NVLink); every rank denoises its rows (+ halo) and copies them into rank 0's denoised plane; flags and waits are stream memory operations") if world > 1 else None,
+                        "e2e_readback": ("every rank stores its tiles into a pinned host frame shared by all ranks (own PCIe link each)" if not denoise else ("every rank copies its denoised rows into a pinned host frame shared by all ranks (own PCIe link each)" if strips else "rank 0 copies the denoised frame to pinned host memory")) if world > 1
                                         else "vrt_frame_download_async on the copy stream, F frames in flight"},
                 "latency_ms_single_frame": latency_ms,
                 "scene_bytes": mem["volume_bytes"] + mem["field_bytes"], "scene": mem,

@@ -266,6 +266,19 @@ int vrt_frame_exchange(vrt_frame*, int slot, uint32_t plane_mask, uint32_t host_
  * follows the last kernel as a stream memory operation: no push kernel, the last kernel of every rank is the collective. */
 int vrt_render_exchange(vrt_context*, const vrt_scene*, const vrt_camera*, const vrt_render_settings*, int slot,
                         uint32_t plane_mask, uint32_t host_plane_mask, vrt_frame** frame);
+/* The denoiser of a sharded frame, distributed over the ranks ("strips"; SURVEY.md 8(e), in place of route (a) — all inputs to rank 0,
+ * denoiser there — which stays available through vrt_render_exchange + vrt_denoise_on). Replaces VoxelRenderer::recordCommands'
+ * geometry + denoiser stages (source/voxels/voxel_renderer.cpp:85-88) for world > 1.
+ *   vrt_comm_alloc_strips: collective, after vrt_comm_alloc_frames with VRT_PLANE_DENOISED_RGBA8 in plane_mask (and in host_plane_mask
+ *     if to_host will be used). Rank q will denoise rows [q * ceil(h / world), ...) and holds those rows plus a halo (the summed reach
+ *     of the iterations' taps) of colour, normal and position for every slot. VRT_E_UNSUPPORTED if a strip is thinner than the halo.
+ *   vrt_render_denoise_exchange: every rank, per frame. The pass's kernels store this rank's pixels into the strips of the ranks that
+ *     own their rows (NVLink peer stores); each rank denoises its rows once all contributions are in (settings: those given to
+ *     vrt_comm_alloc_strips; st->denoise is ignored) and copies them into the denoised plane of `slot` on rank 0 (to_host != 0: and of
+ *     the shared host frame). Rank 0 then uses vrt_comm_wait / vrt_comm_wait_host / vrt_comm_release as for any exchange. The assembled
+ *     plane is byte-identical to the single-GPU denoised frame. Wavefront pipeline only. */
+int vrt_comm_alloc_strips(vrt_context*, const vrt_denoiser_settings*);
+int vrt_render_denoise_exchange(vrt_context*, const vrt_scene*, const vrt_camera*, const vrt_render_settings*, int slot, int to_host, vrt_frame** frame);
 int vrt_comm_wait(vrt_context*, int slot, void* stream);  /* rank 0; stream NULL: vrt_comm_stream() */
 int vrt_comm_wait_host(vrt_context*, int slot);           /* rank 0 */
 int vrt_comm_release(vrt_context*, int slot);             /* rank 0 */

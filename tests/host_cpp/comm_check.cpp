@@ -2,6 +2,7 @@
 // one per rank (rank r on GPU r % ndev, so it also runs on a single GPU), each renders its interleaved tile shard of a few frames
 // and exchanges colour + normal + position into rank 0's frame (peer memory) and colour into the shared pinned host frame. Rank 0
 // denoises the assembled planes and compares everything, byte for byte, with the same frames rendered by a single-rank context.
+// Second part: the same frames through vrt_render_denoise_exchange (every rank denoises its own rows), compared the same way.
 //   usage: comm_check <world> <W> <H> <ndev> [frames]      exit code 0 = identical
 #include <cstdio>
 #include <cstdlib>
@@ -51,7 +52,8 @@ static int run_rank(int rank, int world, int W, int H, int ndev, int frames, con
     uint32_t whd[3]; CK(vrt_scene_bounds(scene, whd));
     const uint32_t planes = (1u << VRT_PLANE_COLOR_RGBA8) | (1u << VRT_PLANE_NORMAL_RGBA8S) | (1u << VRT_PLANE_POSITION_RGBA32F);
     const int slots = 2;
-    CK(vrt_comm_alloc_frames(ctx, W, H, slots, planes, 1u << VRT_PLANE_COLOR_RGBA8));
+    const uint32_t dnPlane = 1u << VRT_PLANE_DENOISED_RGBA8;     // filled by the distributed denoiser (strips) in the second part
+    CK(vrt_comm_alloc_frames(ctx, W, H, slots, planes | dnPlane, (1u << VRT_PLANE_COLOR_RGBA8) | dnPlane));
     vrt_render_settings st; vrt_default_settings(&st);
     st.denoise.enable = 0;                                   // sharded ranks do not denoise: rank 0 does, on the assembled planes
     vrt_render_settings st1 = st; st1.denoise.enable = 1;
@@ -107,9 +109,41 @@ static int run_rank(int rank, int world, int W, int H, int ndev, int frames, con
     }
     CK(vrt_context_sync(ctx));
     CK(vrt_comm_barrier(ctx));
+    // second part: the denoiser distributed over the ranks (strips). Every rank denoises the rows it owns; rank 0 finds the finished
+    // denoised plane in the slot (device frame and shared host frame) and compares it with the single-rank denoised frame.
+    int stripsState = 0;                                     // 1 ran, 2 unsupported for this size (strips thinner than the denoiser's reach)
+    {
+        const int rc = vrt_comm_alloc_strips(ctx, &st1.denoise);
+        if (rc == VRT_E_UNSUPPORTED) stripsState = 2;
+        else if (rc != VRT_OK) { fprintf(stderr, "[rank %d] vrt_comm_alloc_strips -> %d: %s\n", rank, rc, vrt_last_error()); return 10; }
+        else stripsState = 1;
+    }
+    for (int k = 0; stripsState == 1 && k < frames; k++) {
+        const int slot = k % slots;
+        const vrt_camera cam = make_camera(whd, W, H, k + 3);
+        CK(vrt_render_denoise_exchange(ctx, scene, &cam, &st, slot, 1, &fr[slot]));
+        if (rank != 0) continue;
+        void *dd, *hd; size_t nb;
+        CK(vrt_comm_frame_plane(ctx, slot, VRT_PLANE_DENOISED_RGBA8, &dd, &hd, &nb));
+        CK(vrt_comm_wait(ctx, slot, nullptr));
+        CK(vrt_context_join(ctx)); CK(vrt_context_sync(ctx));
+        CK(vrt_render(solo, soloScene, &cam, &st1, &soloFrame));
+        CK(vrt_frame_download(soloFrame, VRT_PLANE_DENOISED_RGBA8, wantDn.data(), wantDn.size()));
+        CK(vrt_buffer_download(ctx, dd, got.data(), got.size()));
+        if (memcmp(got.data(), wantDn.data(), got.size())) {
+            size_t first = 0; while (first < got.size() && got[first] == wantDn[first]) first++;
+            fprintf(stderr, "strips, frame %d: denoised frame differs (first at row %zu)\n", k, first / 4 / (size_t)W); bad++;
+        }
+        CK(vrt_comm_wait_host(ctx, slot));
+        if (memcmp(hd, wantDn.data(), wantDn.size())) { fprintf(stderr, "strips, frame %d: shared host denoised frame differs\n", k); bad++; }
+        CK(vrt_comm_release(ctx, slot));
+    }
+    CK(vrt_context_sync(ctx));
+    CK(vrt_comm_barrier(ctx));
     for (vrt_frame* f : fr) if (f) vrt_frame_release(f);
     if (rank == 0) {
         printf("comm_check: world %d, %dx%d, %d frames: %s\n", world, W, H, frames, bad ? "MISMATCH" : "assembled colour / normal / position, denoised and host frames identical to the single-rank frames");
+        printf("comm_check: strips (denoiser distributed over the ranks): %s\n", stripsState == 2 ? "unsupported at this size (strips thinner than the denoiser's reach)" : bad ? "MISMATCH" : "denoised frame identical");
         vrt_frame_release(soloFrame); vrt_scene_destroy(soloScene); vrt_context_destroy(solo);
         vrt_buffer_free(ctx, dOut); vrt_buffer_free(ctx, dScratch);
     }

@@ -49,7 +49,7 @@ def test_cpp_comm_check_fails_loudly_without_gpu():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("world,size", [(2, (200, 150)), (3, (333, 217)), (4, (640, 360))])
+@pytest.mark.parametrize("world,size", [(2, (200, 150)), (3, (333, 217)), (4, (640, 360)), (8, (256, 40))])
 def test_cpp_ranks_assemble_a_frame_without_torch(world, size):
     """a C++ host linking libvrt.so shards a frame over `world` processes and assembles it on rank 0 through
     vrt_comm_* / vrt_frame_exchange alone (peer stores into rank 0's frame + shared pinned host frame), then denoises it there:
@@ -60,6 +60,9 @@ def test_cpp_ranks_assemble_a_frame_without_torch(world, size):
     p = subprocess.run([build_comm_check(), str(world), str(size[0]), str(size[1]), str(ndev), "5"], capture_output=True, text=True, timeout=600, env=env)
     assert p.returncode == 0, p.stdout + p.stderr
     assert "identical to the single-rank frames" in p.stdout
+    # the denoiser distributed over the ranks (vrt_comm_alloc_strips / vrt_render_denoise_exchange); 8 ranks x 5 rows: refused, loudly
+    assert ("strips (denoiser distributed over the ranks): denoised frame identical" in p.stdout) == (world != 8), p.stdout
+    assert ("unsupported at this size" in p.stdout) == (world == 8), p.stdout
 
 
 def test_cpp_host_compiles_and_links():

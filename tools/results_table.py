@@ -11,9 +11,9 @@ def line(name):
 import sys
 T = sys.argv[1] if len(sys.argv) > 1 else "r2"      # round tag of the files under profiles/
 rows = [("1", "treehouse stand-in", f"{T}_bench_cfg1.json", "1"), ("2", "mandelbulb stand-in", f"{T}_bench_cfg2.json", "1"),
-        ("3", "floatingcolored stand-in", f"{T}_bench_cfg3.json", "1"), ("3", "floatingcolored stand-in (denoiser on rank 0)", f"scale/{T}_scale_cfg3_N2.json", "2"),
-        ("3", "floatingcolored stand-in (denoiser on rank 0)", f"scale/{T}_scale_cfg3_N4.json", "4"),
-        ("3", "floatingcolored stand-in (denoiser on rank 0)", f"scale/{T}_scale_cfg3_N8.json", "8"), ("4", "synthetic 1024^3 terrain", f"{T}_bench_cfg4.json", "1"),
+        ("3", "floatingcolored stand-in", f"{T}_bench_cfg3.json", "1"), ("3", "floatingcolored stand-in (denoiser distributed: strips)", f"scale/{T}_scale_cfg3_N2.json", "2"),
+        ("3", "floatingcolored stand-in (denoiser distributed: strips)", f"scale/{T}_scale_cfg3_N4.json", "4"),
+        ("3", "floatingcolored stand-in (denoiser distributed: strips)", f"scale/{T}_scale_cfg3_N8.json", "8"), ("4", "synthetic 1024^3 terrain", f"{T}_bench_cfg4.json", "1"),
         ("4", "synthetic 1024^3 terrain", f"scale/{T}_scale_cfg4_N2.json", "2"), ("4", "synthetic 1024^3 terrain", f"scale/{T}_scale_cfg4_N4.json", "4"),
         ("4", "synthetic 1024^3 terrain", f"scale/{T}_scale_cfg4_N8.json", "8"), ("5", "synthetic 2048^3 sparse", f"{T}_bench_cfg5_1gpu.json", "1"),
         ("5", "synthetic 2048^3 sparse, orbit", f"scale/{T}_scale_cfg5_N8.json", "8")]

@@ -17,6 +17,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <cmath>
 #include <new>
 #include <string>
 #include <fcntl.h>
@@ -48,7 +49,10 @@ struct CommShm {
     std::atomic<uint64_t> released[kMaxSlots];        // generations of the slot the consumer on rank 0 is done with (host store / host function)
     volatile uint32_t releasedOp[kMaxSlots];          // the same, written by a stream memory operation of rank 0's consumer stream
     volatile uint32_t hostArrive[kMaxSlots][kMaxWorld];   // generation whose tiles rank r has stored into the HOST frame (written by kernels)
+    // strips (vrt_comm_alloc_strips): every rank's buffer of the denoiser inputs of its rows, exported to all ranks
+    cudaIpcMemHandle_t stripHandle[kMaxWorld];
 };
+static_assert(kMaxWorld == VRT_MAX_WORLD, "StripTable and the rendezvous header are sized for the same world");
 
 // Stream memory operations (cuStreamWaitValue32 / cuStreamWriteValue32), fetched through the runtime so that libvrt has no link-time
 // dependency on libcuda (it must load on a machine without a driver). A wait on a memory word needs no SM: the persistent kernels
@@ -85,9 +89,17 @@ struct vrt_comm {
     uint64_t gen[kMaxSlots] = {};                     // exchanges issued on each slot (identical on every rank)
     cudaStream_t stream = nullptr;                    // rank 0's consumer stream (arrival wait, caller's work, release)
     cudaStream_t pushStream = nullptr;                // highest priority: the tile stores of a finished frame never queue behind the next frame's kernels
+    cudaStream_t stripStream = nullptr;               // highest priority: this rank's share of the denoiser (strips)
     cudaEvent_t joined = nullptr;
     uint32_t* devError = nullptr;                     // set by a wait kernel that gave up
     bool joinedOk = false;
+    // strips: the denoiser runs on every rank, on the rows it owns (vrt_render_denoise_exchange)
+    uint8_t* stripBase[kMaxWorld] = {};               // [rank]: own allocation, the others' as peer mappings
+    StripTable* stripTables = nullptr;                // device, one per slot
+    uint8_t* dnOut = nullptr; uint8_t* dnScratch = nullptr;   // the denoiser's ping-pong images of this rank's strip (+ halo)
+    int stripRows = 0, stripHalo = 0, stripBufRows = 0;
+    uint64_t stripSlotBytes = 0, stripFlagsOff = 0;
+    vrt_denoiser_settings stripDs{};
 };
 
 // ---------------------------------------------------------------------------------------------------------------- kernels
@@ -137,7 +149,14 @@ static int comm_barrier(vrt_comm* m, double limit = -1.0) {
     return comm_spin(m, "the barrier", [](vrt_comm* mm, const void* g) { return mm->shm->barGen.load() != *(const uint32_t*)g; }, &gen, limit);
 }
 
+static void comm_unmap_strips(vrt_comm* m) {
+    for (int r = 0; r < m->world; r++)
+        if (m->stripBase[r]) { if (r == m->rank) cudaFree(m->stripBase[r]); else cudaIpcCloseMemHandle(m->stripBase[r]); m->stripBase[r] = nullptr; }
+    cudaFree(m->stripTables); cudaFree(m->dnOut); cudaFree(m->dnScratch);
+    m->stripTables = nullptr; m->dnOut = m->dnScratch = nullptr; m->stripRows = 0;
+}
 static void comm_unmap_frames(vrt_comm* m) {
+    comm_unmap_strips(m);
     if (m->devBase) { if (m->rank == 0) cudaFree(m->devBase); else cudaIpcCloseMemHandle(m->devBase); m->devBase = nullptr; }
     if (m->hostBase) { cudaHostUnregister(m->hostBase); munmap(m->hostBase, m->hostBytes); m->hostBase = nullptr; m->hostBaseDev = nullptr; }
     if (m->rank == 0 && m->hostBytes) shm_unlink(("/vrt_" + m->key + "_f" + std::to_string(m->framesGen)).c_str());
@@ -153,6 +172,7 @@ extern "C" int vrt_comm_destroy(vrt_context* c) {
     comm_unmap_frames(m);
     if (m->stream) cudaStreamDestroy(m->stream);
     if (m->pushStream) cudaStreamDestroy(m->pushStream);
+    if (m->stripStream) cudaStreamDestroy(m->stripStream);
     if (m->joined) cudaEventDestroy(m->joined);
     cudaFree(m->devError);
     if (m->shm) { cudaHostUnregister(m->shm); munmap(m->shm, sizeof(CommShm)); }
@@ -205,6 +225,7 @@ extern "C" int vrt_comm_create(vrt_context* c, int rank, int world, const char* 
     if (e == cudaSuccess) e = cudaDeviceGetStreamPriorityRange(&prLow, &prHigh);
     if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&m->stream, cudaStreamNonBlocking, prHigh);
     if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&m->pushStream, cudaStreamNonBlocking, prHigh);
+    if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&m->stripStream, cudaStreamNonBlocking, prHigh);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&m->joined, cudaEventDisableTiming);
     load_stream_memops();
     if (e == cudaSuccess) e = cudaMalloc(&m->devError, sizeof(uint32_t));
@@ -230,8 +251,8 @@ extern "C" void* vrt_comm_stream(vrt_context* c) { return c && c->comm ? (void*)
 // GPU (plane_mask) and in shared pinned host memory (host_plane_mask); the others map both.
 extern "C" int vrt_comm_alloc_frames(vrt_context* c, int w, int h, int slots, uint32_t plane_mask, uint32_t host_plane_mask) {
     if (!c || !c->comm) return fail(VRT_E_INVALID, "no communicator");
-    if (w <= 0 || h <= 0 || slots < 1 || slots > kMaxSlots || (plane_mask | host_plane_mask) >> VRT_PLANE_COUNT || ((plane_mask | host_plane_mask) & (1u << VRT_PLANE_DENOISED_RGBA8)))
-        return fail(VRT_E_INVALID, "bad frame layout (slots <= 8; the denoised plane is produced on rank 0, not exchanged)");
+    if (w <= 0 || h <= 0 || slots < 1 || slots > kMaxSlots || (plane_mask | host_plane_mask) >> VRT_PLANE_COUNT)
+        return fail(VRT_E_INVALID, "bad frame layout (slots <= 8)");   // (the denoised plane of a slot is filled by vrt_render_denoise_exchange only)
     vrt_comm* m = c->comm; CommShm* sh = m->shm;
     CU(cudaSetDevice(c->device));
     CU(cudaDeviceSynchronize());
@@ -395,6 +416,158 @@ extern "C" int vrt_render_exchange(vrt_context* c, const vrt_scene* sc, const vr
     rc = vrt_render_impl(c, sc, cam, st, frame, (fused | fusedHost) ? &x : nullptr);
     if (rc) { sh->error.store(1); return rc; }
     return exchange_finish(*frame, slot, g, plane_mask & ~fused, host_plane_mask & ~fusedHost, plane_mask != 0, host_plane_mask != 0, nullptr);
+}
+
+// ---- strips: the denoiser of a sharded frame, distributed (SURVEY.md 8e "denoiser under sharding"; neither route (a) nor (b)) ----------
+// Route (a) — all three input planes to rank 0, denoiser there — makes rank 0 the serial part (cfg3 at 8 GPUs: 3.4x). Route (b) — every
+// rank re-traces a halo around its tiles — re-traces 56 % more pixels with 32x32 interleaved tiles. Here the pixels are traced once, by the
+// rank that owns their tile, and the denoiser's inputs are stored (by the pass's own kernels, over NVLink peer memory) into the buffer of
+// the rank that owns their ROWS: rank q denoises rows [q * stripRows, (q + 1) * stripRows) of the frame from a buffer that also holds
+// `halo` rows either side, halo = the summed reach of all iterations' taps, so its rows come out byte-identical to the single-GPU
+// frame (the rows of the halo itself come out wrong and are dropped; at the image's top and bottom the buffer ends where the image does,
+// and the sampler's clamp is the reference's). Each rank then copies its rows into rank 0's denoised plane of the slot (and into the
+// shared host frame) with plain row-range copies on the copy engines, and sets its arrival flag: vrt_comm_wait / _wait_host / _release
+// on rank 0 work as for any exchange. Per frame every rank receives 24 B x (1 / world + halo share) of the pixels instead of rank 0
+// receiving all of them.
+static int denoise_reach_rows(const vrt_denoiser_settings* ds) {
+    int h = 0;
+    for (int i = 0; i < ds->iterations; i++) {
+        const float sw = fabsf((float)i * ds->stepWidth + 1.0f);           // denoiser_stage.cpp:143-154; tap offsets are -1, 0, 1
+        if (!(sw < 4096.0f)) return -1;
+        h += (int)ceilf(sw) + 1;                                           // + 1: a fractional tap position blends the texel beyond it
+    }
+    return h;
+}
+// `word` := g when `s` gets there: a stream memory operation where the driver has them (no SM), else the one-thread kernel
+static cudaError_t stream_signal(cudaStream_t s, uint32_t* devFlag, uint32_t* hostFlag, uint32_t g, uint32_t* launches) {
+    if (g_writeValue32 && !getenv("VRT_COMM_SIGNAL_KERNEL")) {
+        int rc = 0;
+        if (devFlag) rc = g_writeValue32(s, (unsigned long long)devFlag, g, 0);
+        if (rc == 0 && hostFlag) rc = g_writeValue32(s, (unsigned long long)hostFlag, g, 0);
+        if (rc == 0) return cudaSuccess;
+        g_writeValue32 = nullptr; cudaGetLastError();
+    }
+    vrt::comm_signal_kernel<<<1, 1, 0, s>>>(devFlag, hostFlag, g);
+    if (launches) (*launches)++;
+    return cudaGetLastError();
+}
+static cudaError_t stream_wait_flags(vrt_comm* m, cudaStream_t s, const uint32_t* flags, int n, uint32_t g) {
+    if (g_waitValue32) {
+        bool ok = true;
+        for (int r = 0; r < n && ok; r++) ok = g_waitValue32(s, (unsigned long long)(flags + r), g, 0x0 /* CU_STREAM_WAIT_VALUE_GEQ */) == 0;
+        if (ok) return cudaSuccess;
+        g_waitValue32 = nullptr; cudaGetLastError();
+    }
+    vrt::comm_wait_kernel<<<1, 32, 0, s>>>(flags, n, g, m->devError);
+    return cudaGetLastError();
+}
+
+// Collective (same arguments on every rank), after vrt_comm_alloc_frames with VRT_PLANE_DENOISED_RGBA8 in plane_mask: every rank
+// allocates the strip buffers of its rows for all slots and maps everybody else's. The denoiser settings fix the halo; they are the
+// ones vrt_render_denoise_exchange runs. VRT_E_UNSUPPORTED when a strip is thinner than the denoiser's reach (use route (a) then).
+extern "C" int vrt_comm_alloc_strips(vrt_context* c, const vrt_denoiser_settings* ds) {
+    if (!c || !c->comm || !ds) return fail(VRT_E_INVALID, "no communicator / settings");
+    vrt_comm* m = c->comm; CommShm* sh = m->shm;
+    if (!m->devBase || !(sh->planeMask >> VRT_PLANE_DENOISED_RGBA8 & 1u)) return fail(VRT_E_INVALID, "call vrt_comm_alloc_frames with the denoised plane in plane_mask first");
+    if (ds->iterations < 1 || ds->iterations > 10) return fail(VRT_E_INVALID, "denoiser iterations must be 1..10 (MAX_DENOISER_PASSES)");
+    if (ds->mode != VRT_DENOISE_AS_EXECUTED && ds->mode != VRT_DENOISE_AS_INTENDED) return fail(VRT_E_INVALID, "bad denoise mode");
+    const int W = sh->w, H = sh->h, slots = sh->slots, world = m->world;
+    const int SR = (H + world - 1) / world, halo = denoise_reach_rows(ds);
+    if (halo < 0 || halo > SR) return fail(VRT_E_UNSUPPORTED, "a strip of " + std::to_string(SR) + " rows is thinner than the denoiser's reach: exchange the planes and denoise on rank 0 (vrt_denoise_on)");
+    CU(cudaSetDevice(c->device));
+    CU(cudaDeviceSynchronize());
+    int rc = comm_barrier(m);                                              // nobody is still storing into the old strips
+    if (rc) return rc;
+    comm_unmap_strips(m);
+    const int bufRows = SR + 2 * halo;
+    auto up = [](uint64_t v) { return (v + 255u) & ~(uint64_t)255u; };
+    const uint64_t colorBytes = up((uint64_t)bufRows * W * 4), normalBytes = colorBytes, positionBytes = up((uint64_t)bufRows * W * 16);
+    m->stripSlotBytes = colorBytes + normalBytes + positionBytes;
+    m->stripFlagsOff = m->stripSlotBytes * slots;
+    const uint64_t total = m->stripFlagsOff + sizeof(uint32_t) * kMaxSlots * kMaxWorld;
+    cudaError_t e = cudaMalloc(&m->stripBase[m->rank], total);
+    if (e == cudaSuccess) e = cudaMemset(m->stripBase[m->rank], 0, total);
+    if (e == cudaSuccess && world > 1) e = cudaIpcGetMemHandle(&sh->stripHandle[m->rank], m->stripBase[m->rank]);
+    if (e == cudaSuccess) e = cudaMalloc(&m->dnOut, (size_t)bufRows * W * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&m->dnScratch, (size_t)bufRows * W * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&m->stripTables, sizeof(StripTable) * slots);
+    if (e != cudaSuccess) { sh->error.store(1); return fail(e == cudaErrorMemoryAllocation ? VRT_E_OOM : VRT_E_CUDA, cudaGetErrorString(e)); }
+    rc = comm_barrier(m);                                                  // every handle is published
+    if (rc) return rc;
+    for (int r = 0; r < world; r++) {
+        if (r == m->rank) continue;
+        void* base = nullptr;
+        e = cudaIpcOpenMemHandle(&base, sh->stripHandle[r], cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) { sh->error.store(1); return fail(VRT_E_CUDA, std::string("cudaIpcOpenMemHandle (strips): ") + cudaGetErrorString(e)); }
+        m->stripBase[r] = (uint8_t*)base;
+    }
+    StripTable tables[kMaxSlots];
+    memset(tables, 0, sizeof(tables));
+    for (int s = 0; s < slots; s++) {
+        StripTable& t = tables[s];
+        for (int r = 0; r < world; r++) {
+            uint8_t* b = m->stripBase[r] + (uint64_t)s * m->stripSlotBytes;
+            t.color[r] = b; t.normal[r] = (int8_t*)(b + colorBytes); t.position[r] = (float*)(b + colorBytes + normalBytes);
+        }
+        t.world = world; t.stripRows = SR; t.halo = halo; t.W = W; t.H = H;
+    }
+    e = cudaMemcpy(m->stripTables, tables, sizeof(StripTable) * slots, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) { sh->error.store(1); return fail(VRT_E_CUDA, cudaGetErrorString(e)); }
+    m->stripRows = SR; m->stripHalo = halo; m->stripBufRows = bufRows; m->stripDs = *ds;
+    return comm_barrier(m);
+}
+
+// vrt_render + the distributed denoiser in one call (every rank, same arguments): the pass's kernels store colour, normal and position
+// of this rank's tiles into the strips of the ranks that own their rows; this rank then denoises its own rows as soon as every rank's
+// contribution has arrived and copies them into the denoised plane of `slot` on rank 0 (to_host: and of the shared host frame, which
+// must have been allocated with the denoised plane in host_plane_mask). st->denoise is ignored (the settings are those of
+// vrt_comm_alloc_strips); the frame's own G-buffer planes are produced as usual. Asynchronous, like vrt_render_exchange.
+extern "C" int vrt_render_denoise_exchange(vrt_context* c, const vrt_scene* sc, const vrt_camera* cam, const vrt_render_settings* st, int slot,
+                                           int to_host, vrt_frame** frame) {
+    if (!c || !cam || !st || !frame) return fail(VRT_E_INVALID, "null argument");
+    if (!c->comm || !c->comm->stripRows) return fail(VRT_E_INVALID, "call vrt_comm_alloc_strips first");
+    if (st->pipeline == VRT_PIPELINE_MEGAKERNEL) return fail(VRT_E_UNSUPPORTED, "strips are stored by the wavefront kernels");
+    vrt_comm* m = c->comm; CommShm* sh = m->shm;
+    const int W = cam->screenSize[0], H = cam->screenSize[1];
+    const uint32_t dn = 1u << VRT_PLANE_DENOISED_RGBA8;
+    uint64_t g64 = 0;
+    int rc = exchange_begin(c, W, H, slot, dn, to_host ? dn : 0u, &g64);
+    if (rc) return rc;
+    const uint32_t g = (uint32_t)g64;
+    vrt_render_settings s2 = *st;
+    s2.denoise.enable = 0; s2.out_mask |= VRT_OUT_GBUFFER;
+    XPlanes x{};
+    x.strips = m->stripTables + slot;
+    rc = vrt_render_impl(c, sc, cam, &s2, frame, &x);
+    if (rc) { sh->error.store(1); return rc; }
+    vrt_frame* f = *frame;
+    cudaError_t e = cudaSuccess;
+    // every owner learns that this rank's pixels of generation g are in its strip (behind the pass's last kernel on the frame's stream)
+    for (int q = 0; q < m->world && e == cudaSuccess; q++)
+        e = stream_signal(f->stream, (uint32_t*)(m->stripBase[q] + m->stripFlagsOff) + slot * kMaxWorld + m->rank, nullptr, g, &f->launches);
+    // this rank's rows: wait for every rank, denoise, deliver
+    if (e == cudaSuccess) e = stream_wait_flags(m, m->stripStream, (const uint32_t*)(m->stripBase[m->rank] + m->stripFlagsOff) + slot * kMaxWorld, m->world, g);
+    const int SR = m->stripRows, y0 = m->rank * SR, y1 = y0 + SR < H ? y0 + SR : H;
+    if (e == cudaSuccess && y0 < y1) {
+        const int lo = strip_lo(m->rank, SR, m->stripHalo), hi = strip_hi(m->rank, SR, m->stripHalo, H);
+        uint8_t* b = m->stripBase[m->rank] + (uint64_t)slot * m->stripSlotBytes;
+        const uint64_t colorBytes = ((uint64_t)m->stripBufRows * W * 4 + 255u) & ~(uint64_t)255u;
+        void* ping[2] = {m->dnOut, m->dnScratch};
+        if (((m->stripDs.iterations - 1) % 2) == 1) { ping[0] = m->dnScratch; ping[1] = m->dnOut; }   // the last iteration lands in dnOut
+        int last = 0; uint32_t n = 0;
+        rc = run_denoise(c, m->stripStream, b, b + colorBytes, b + 2 * colorBytes, W, hi - lo, &m->stripDs, ping, &last, &n);
+        if (rc) { sh->error.store(1); return rc; }
+        f->launches += n;
+        const size_t rowBytes = (size_t)W * 4;
+        const uint8_t* src = m->dnOut + (size_t)(y0 - lo) * rowBytes;
+        e = cudaMemcpyAsync(m->devBase + (uint64_t)slot * sh->slotStride + sh->planeOff[VRT_PLANE_DENOISED_RGBA8] + (size_t)y0 * rowBytes, src, (size_t)(y1 - y0) * rowBytes, cudaMemcpyDefault, m->stripStream);
+        if (e == cudaSuccess && to_host)
+            e = cudaMemcpyAsync(m->hostBase + (uint64_t)slot * sh->hostSlotStride + sh->hostPlaneOff[VRT_PLANE_DENOISED_RGBA8] + (size_t)y0 * rowBytes, src, (size_t)(y1 - y0) * rowBytes, cudaMemcpyDefault, m->stripStream);
+    }
+    if (e == cudaSuccess)
+        e = stream_signal(m->stripStream, (uint32_t*)(m->devBase + sh->arriveOff) + slot * kMaxWorld + m->rank, to_host ? m->shmDevArrive + slot * kMaxWorld + m->rank : nullptr, g, &f->launches);
+    if (e != cudaSuccess) { sh->error.store(1); return fail(VRT_E_CUDA, cudaGetErrorString(e)); }
+    return VRT_OK;
 }
 
 // Rank 0: everything queued on `stream` (null: the communicator's stream) after this call runs once every rank's tiles of the latest

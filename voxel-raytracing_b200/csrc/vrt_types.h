@@ -98,7 +98,20 @@ constexpr int VRT_TILE = 32;
 // Fused exchange (vrt_render_exchange, multi-GPU): row-major W x H planes of the assembled frame on rank 0 (peer memory over NVLink for
 // the other ranks). A kernel that stores a pixel of one of these planes stores it there as well: the pass's own kernels are the
 // "collective", no push kernel runs afterwards. Null = the plane is not exchanged in-kernel.
-struct XPlanes { uint8_t* color; float* depth; float* motion; uint8_t* mask; float* position; int8_t* normal; uint8_t* colorHost; /* the same pixel of the shared pinned HOST frame (zero-copy over this GPU's PCIe link) */ };
+// Strips (vrt_render_denoise_exchange, multi-GPU with the denoiser): the three planes the denoiser reads do not go to rank 0 but to the
+// rank that DENOISES their rows. Rank q owns rows [q * stripRows, (q + 1) * stripRows) and holds, per slot, row-major buffers of the rows
+// [lo_q, hi_q) = its own rows plus `halo` rows either side (clipped to the image): a pixel is stored into the buffer of every rank whose
+// range holds its row (at most three). The table lives in device memory (one per slot), pointers as THIS rank sees them (own memory or
+// CUDA-IPC peer mappings).
+constexpr int VRT_MAX_WORLD = 16;
+struct StripTable {
+    uint8_t* color[VRT_MAX_WORLD]; int8_t* normal[VRT_MAX_WORLD]; float* position[VRT_MAX_WORLD];
+    int world, stripRows, halo, W, H;
+};
+VRT_HD int strip_lo(int q, int stripRows, int halo) { const int v = q * stripRows - halo; return v < 0 ? 0 : v; }
+VRT_HD int strip_hi(int q, int stripRows, int halo, int H) { const int v = (q + 1) * stripRows + halo; return v > H ? H : v; }
+struct XPlanes { uint8_t* color; float* depth; float* motion; uint8_t* mask; float* position; int8_t* normal; uint8_t* colorHost; /* the same pixel of the shared pinned HOST frame (zero-copy over this GPU's PCIe link) */
+                 const StripTable* strips; /* or null */ };
 
 struct FrameParams {
     vrt_camera cam;

@@ -46,9 +46,23 @@ __device__ __forceinline__ void add_totals(Counters* ctr, int stage, unsigned ra
     }
 }
 
+// pixel (px, py) of a denoiser input plane into the strip buffer of every rank whose row range holds py (StripTable, vrt_types.h)
+template <class T, class B>
+__device__ __forceinline__ void strip_store(const StripTable* __restrict__ t, B* const* bases, int px, int py, T v) {
+    const int o = py / t->stripRows;
+#pragma unroll
+    for (int d = -1; d <= 1; d++) {
+        const int q = o + d;
+        if (q < 0 || q >= t->world) continue;
+        const int lo = strip_lo(q, t->stripRows, t->halo);
+        if (py >= lo && py < strip_hi(q, t->stripRows, t->halo, t->H)) reinterpret_cast<T*>(bases[q])[(size_t)(py - lo) * t->W + px] = v;
+    }
+}
+
 __device__ __forceinline__ void store_color(const FrameParams& fp, const PlanesDev& pl, size_t p, V3 c, int px, int py) {
     const uchar4 q = make_uchar4(to_unorm8(c.x), to_unorm8(c.y), to_unorm8(c.z), 0);
     reinterpret_cast<uchar4*>(pl.color)[p] = q;
+    if (fp.x.strips) strip_store<uchar4>(fp.x.strips, fp.x.strips->color, px, py, q);
     if (fp.x.color) reinterpret_cast<uchar4*>(fp.x.color)[(size_t)py * fp.cam.screenSize[0] + px] = q;   // fused exchange: rank 0's frame
     if (fp.x.colorHost) reinterpret_cast<uchar4*>(fp.x.colorHost)[(size_t)py * fp.cam.screenSize[0] + px] = q;
     if (fp.out_mask & VRT_OUT_INSTRUMENT) { pl.color_f32[3 * p + 0] = c.x; pl.color_f32[3 * p + 1] = c.y; pl.color_f32[3 * p + 2] = c.z; }
@@ -89,6 +103,7 @@ __global__ void __launch_bounds__(128, WAVE_PRIMARY_MIN_BLOCKS) wave_primary_ker
             if (fp.x.mask) fp.x.mask[xp] = to_unorm8(o.mask);
             if (fp.x.position) reinterpret_cast<float4*>(fp.x.position)[xp] = pos4;
             if (fp.x.normal) reinterpret_cast<char4*>(fp.x.normal)[xp] = n4;
+            if (fp.x.strips) { strip_store<float4>(fp.x.strips, fp.x.strips->position, px, py, pos4); strip_store<char4>(fp.x.strips, fp.x.strips->normal, px, py, n4); }
         }
         if (fp.out_mask & VRT_OUT_INSTRUMENT) {
             auto sat = [](int v) { return (short)(v < -32768 ? -32768 : (v > 32767 ? 32767 : v)); };

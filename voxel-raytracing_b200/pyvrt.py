@@ -213,6 +213,11 @@ class Context:
         pm = sum(1 << PLANE_ID[n] for n in planes); hm = sum(1 << PLANE_ID[n] for n in host_planes)
         _ck(lib().vrt_comm_alloc_frames(self.h, int(size[0]), int(size[1]), int(slots), C.c_uint32(pm), C.c_uint32(hm)))
 
+    def comm_alloc_strips(self, ds: "DenoiserSettings"):
+        """vrt_comm_alloc_strips: the denoiser distributed over the ranks (every rank denoises the rows it owns). Raises VrtError with
+        code E_UNSUPPORTED when a strip would be thinner than the denoiser's reach."""
+        _ck(lib().vrt_comm_alloc_strips(self.h, C.byref(ds)))
+
     def comm_wait(self, slot, stream=None):
         _ck(lib().vrt_comm_wait(self.h, int(slot), C.c_void_p(stream) if stream else None))
 
@@ -413,6 +418,15 @@ class VoxelRenderPass:
             self.frame.release()
         pm = sum(1 << PLANE_ID[n] for n in planes); hm = sum(1 << PLANE_ID[n] for n in host_planes)
         _ck(lib().vrt_render_exchange(self.ctx.h, self.scene.h, C.byref(camera), C.byref(self.settings), int(slot), C.c_uint32(pm), C.c_uint32(hm), C.byref(self.frame.h)))
+        self.frame.size = size
+        return self.frame
+
+    def record_denoise_exchange(self, camera: Camera, slot, to_host=False) -> Frame:
+        """vrt_render_denoise_exchange: the pass + the distributed denoiser; the denoised plane of `slot` on rank 0 is the result."""
+        size = (camera.screenSize[0], camera.screenSize[1])
+        if self.frame.size not in (None, size):
+            self.frame.release()
+        _ck(lib().vrt_render_denoise_exchange(self.ctx.h, self.scene.h, C.byref(camera), C.byref(self.settings), int(slot), int(bool(to_host)), C.byref(self.frame.h)))
         self.frame.size = size
         return self.frame
 
