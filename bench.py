@@ -343,7 +343,7 @@ def run_vrt(args):
     ds = pyvrt.default_settings().denoise
     # cfg3 on N > 1 GPUs: the denoiser is distributed ("strips": every rank denoises the rows it owns, vrt_render_denoise_exchange);
     # VRT_BENCH_ROUTE_A=1 measures route (a) instead (all three planes to rank 0, denoiser there).
-    strips = False
+    strips = plain_strips = False
     if world > 1:
         if denoise and not os.environ.get("VRT_BENCH_ROUTE_A"):
             ctx.comm_alloc_frames(size, S, xplanes + ("denoised",), ("denoised",))
@@ -355,6 +355,11 @@ def run_vrt(args):
                     raise
         else:
             ctx.comm_alloc_frames(size, S, xplanes, xhost)
+            # read-back path (e2e) of a frame without a denoiser: strips carrying the colour plane alone — tiles cross NVLink into row
+            # strips, every rank's copy engine writes whole rows into the shared host frame (VRT_BENCH_PUSH_HOST=1: the push kernels instead)
+            if not denoise and not os.environ.get("VRT_BENCH_PUSH_HOST"):
+                ctx.comm_alloc_strips(None)
+                plain_strips = True
         if rank == 0 and denoise:
             dn_out = [torch.empty(frame_bytes, dtype=torch.uint8, device=dev) for _ in range(S)]
             dn_scratch = torch.empty(frame_bytes, dtype=torch.uint8, device=dev)
@@ -385,6 +390,11 @@ def run_vrt(args):
                 else:
                     ctx.comm_release(slot, on_stream=True)
             return fr, 1 if rank == 0 else 0
+        if plain_strips and readback:
+            fr = passes[k % F].record_denoise_exchange(cam, slot, to_host=2)
+            if rank == 0:
+                pending[slot] = True
+            return fr, 0
         if os.environ.get("VRT_BENCH_UNFUSED"):               # measurement only: separate push kernels after the pass
             fr = passes[k % F].record(cam)
             fr.exchange(slot, xplanes, xhost if readback else ())
@@ -421,7 +431,7 @@ def run_vrt(args):
         elif pending[slot]:
             if not denoise or strips:
                 ctx.comm_wait_host(slot)                     # every rank's tiles (strips: denoised rows) are in the shared pinned host frame
-            if not strips:
+            if not strips and not plain_strips:
                 ev_done[slot].synchronize()
             ctx.comm_release(slot)
             pending[slot] = False
@@ -521,22 +531,58 @@ def run_vrt(args):
     # beside the kernels of the following frames. N > 1: every rank stores its own tiles into the shared pinned host frame over its
     # own PCIe link (the denoised frame of cfg3 is produced on rank 0 and copied from there). The host waits for frame k-(F-1)
     # before it queues frame k+1 (F frame objects in flight). All K frames are complete in host memory inside the timed region.
+    e2e_probe = None
     if args.shard and world == 1:                           # debug mode: a shard is not a frame, there is nothing to read back
         t_e2e = ms * 1e-3
     else:
+        # N = 1: a frame object's planes are the source of its read-back, so the host runs F-1 frames ahead. N > 1: the read-back leaves
+        # from the exchange slots (S of them, guarded by the slot hand-shake), so the host may run S-2 frames ahead of the finished ones.
+        depth = F - 1 if world == 1 else max(F - 1, S - 2)
+
         def e2e_region():
             barrier()
             t0 = time.perf_counter()
             for k in range(args.steps):
                 submit(k, True)
-                if k >= F - 1:
-                    wait_readback(k - (F - 1))            # the host runs at most F-1 frames ahead of the finished read-backs
+                if k >= depth:
+                    wait_readback(k - depth)              # the host runs at most `depth` frames ahead of the finished read-backs
             drain()
-            for k in range(max(0, args.steps - (F - 1)), args.steps):
+            for k in range(max(0, args.steps - depth), args.steps):
                 wait_readback(k)
             barrier()
             return time.perf_counter() - t0
         e2e_region()                                       # warm-up of the read-back path
+        if plain_strips and not os.environ.get("VRT_BENCH_STRIPS_HOST"):
+            # two read-back paths exist for a frame without a denoiser (row strips + copy engines, or push kernels into the host frame);
+            # which one is faster depends on N: both are warmed up and timed once here, outside the timed regions, and the faster one runs
+            t_strips = e2e_region()
+            plain_strips = False
+            e2e_region()
+            t_push = e2e_region()
+            tt = torch.tensor([t_strips, t_push], dtype=torch.float64, device=dev)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            plain_strips = bool(tt[0] <= tt[1])
+            e2e_probe = {"strips_ms_per_step": float(tt[0]) * 1e3 / args.steps, "push_ms_per_step": float(tt[1]) * 1e3 / args.steps}
+            e2e_region()
+        if world > 1 and not os.environ.get("VRT_BENCH_NOEXCHANGE"):
+            # self-check of the read-back path (outside the timed regions): the host frame of the last step holds the ranks' bytes.
+            # Without a denoiser: byte sums of the ranks' shards of that frame; with the strips' denoiser: the slot's device plane.
+            kl = args.steps - 1
+            if denoise:
+                if rank == 0 and strips:
+                    dptr, hview, nb = ctx.comm_frame_plane(kl % S, "denoised")
+                    if not np.array_equal(torch.as_tensor(_DevBuf(dptr, nb), device=dev).cpu().numpy(), hview):
+                        raise SystemExit("read-back self-check failed: the shared host frame differs from the assembled denoised frame")
+            else:
+                ptr, n = passes[kl % F].frame.plane_ptr("color")
+                mine = checksum(ptr, n)
+                dist.all_reduce(mine)
+                if rank == 0:
+                    _, hview, _ = ctx.comm_frame_plane(kl % S, "color")
+                    hv = hview.astype(np.int64)
+                    if [int(hv.sum()), int((hv * hv).sum())] != [int(x) for x in mine.tolist()]:
+                        raise SystemExit("read-back self-check failed: the shared host frame does not hold the ranks' tiles")
+            barrier()
         reps = int(min(200, max(1, math.ceil(0.5 * repeats))))
         t_e2e = float(np.median([e2e_region() for _ in range(reps)]))
 
@@ -579,7 +625,9 @@ def run_vrt(args):
                                      "arrival flags and rank 0's wait are stream memory operations (no kernel)" + ("; rank 0 denoises the assembled planes" if denoise else "")) if world > 1 and not strips else
                                     ("libvrt vrt_render_denoise_exchange (strips): the pass's own kernels store colour+normal+position of every rank's tiles into the buffer of the rank that owns their rows "
                                      "(CUDA IPC peer memory over NVLink); every rank denoises its rows (+ halo) and copies them into rank 0's denoised plane; flags and waits are stream memory operations") if world > 1 else None,
-                        "e2e_readback": ("every rank stores its tiles into a pinned host frame shared by all ranks (own PCIe link each)" if not denoise else ("every rank copies its denoised rows into a pinned host frame shared by all ranks (own PCIe link each)" if strips else "rank 0 copies the denoised frame to pinned host memory")) if world > 1
+                        "e2e_readback_probe": e2e_probe,
+                        "e2e_readback": (("the colour plane crosses NVLink into row strips; every rank's copy engine writes its rows into a pinned host frame shared by all ranks (own PCIe link each, no push kernel)" if plain_strips else
+                                          "every rank stores its tiles into a pinned host frame shared by all ranks (own PCIe link each)") if not denoise else ("every rank copies its denoised rows into a pinned host frame shared by all ranks (own PCIe link each)" if strips else "rank 0 copies the denoised frame to pinned host memory")) if world > 1
                                         else "vrt_frame_download_async on the copy stream, F frames in flight"},
                 "latency_ms_single_frame": latency_ms,
                 "scene_bytes": mem["volume_bytes"] + mem["field_bytes"], "scene": mem,

@@ -276,7 +276,12 @@ int vrt_render_exchange(vrt_context*, const vrt_scene*, const vrt_camera*, const
  *     own their rows (NVLink peer stores); each rank denoises its rows once all contributions are in (settings: those given to
  *     vrt_comm_alloc_strips; st->denoise is ignored) and copies them into the denoised plane of `slot` on rank 0 (to_host != 0: and of
  *     the shared host frame). Rank 0 then uses vrt_comm_wait / vrt_comm_wait_host / vrt_comm_release as for any exchange. The assembled
- *     plane is byte-identical to the single-GPU denoised frame. Wavefront pipeline only. */
+ *     plane is byte-identical to the single-GPU denoised frame. Wavefront pipeline only.
+ *     to_host: 0 = into rank 0's device frame, 1 = there and into the shared host frame, 2 = into the shared host frame only (then only
+ *     vrt_comm_wait_host sees the frame arrive).
+ *   Without a denoiser (vrt_comm_alloc_strips(ctx, NULL)) the strips carry the colour plane alone and deliver it unchanged: the read-back
+ *     path of a sharded frame — tiles cross NVLink into row strips, every rank's copy engine writes whole rows into the shared host frame
+ *     over its own PCIe link, and no push kernel occupies an SM. The frames then need VRT_PLANE_COLOR_RGBA8 in the masks used. */
 int vrt_comm_alloc_strips(vrt_context*, const vrt_denoiser_settings*);
 int vrt_render_denoise_exchange(vrt_context*, const vrt_scene*, const vrt_camera*, const vrt_render_settings*, int slot, int to_host, vrt_frame** frame);
 int vrt_comm_wait(vrt_context*, int slot, void* stream);  /* rank 0; stream NULL: vrt_comm_stream() */

@@ -140,9 +140,34 @@ static int run_rank(int rank, int world, int W, int H, int ndev, int frames, con
     }
     CK(vrt_context_sync(ctx));
     CK(vrt_comm_barrier(ctx));
+    // third part: strips without a denoiser — the colour plane crosses into row strips and every rank copies its rows into rank 0's
+    // frame / the shared host frame (the read-back path): alternately both targets and the host frame alone
+    CK(vrt_comm_alloc_strips(ctx, nullptr));
+    for (int k = 0; k < frames; k++) {
+        const int slot = k % slots, mode = (k & 1) ? 2 : 1;
+        const vrt_camera cam = make_camera(whd, W, H, k + 7);
+        CK(vrt_render_denoise_exchange(ctx, scene, &cam, &st, slot, mode, &fr[slot]));
+        if (rank != 0) continue;
+        void *dc, *hc; size_t nb;
+        CK(vrt_comm_frame_plane(ctx, slot, VRT_PLANE_COLOR_RGBA8, &dc, &hc, &nb));
+        CK(vrt_render(solo, soloScene, &cam, &st, &soloFrame));
+        CK(vrt_frame_download(soloFrame, VRT_PLANE_COLOR_RGBA8, want.data(), want.size()));
+        if (mode == 1) {
+            CK(vrt_comm_wait(ctx, slot, nullptr));
+            CK(vrt_context_join(ctx)); CK(vrt_context_sync(ctx));
+            CK(vrt_buffer_download(ctx, dc, got.data(), got.size()));
+            if (memcmp(got.data(), want.data(), got.size())) { fprintf(stderr, "plain strips, frame %d: colour frame differs\n", k); bad++; }
+        }
+        CK(vrt_comm_wait_host(ctx, slot));
+        if (memcmp(hc, want.data(), want.size())) { fprintf(stderr, "plain strips, frame %d: shared host colour frame differs\n", k); bad++; }
+        CK(vrt_comm_release(ctx, slot));
+    }
+    CK(vrt_context_sync(ctx));
+    CK(vrt_comm_barrier(ctx));
     for (vrt_frame* f : fr) if (f) vrt_frame_release(f);
     if (rank == 0) {
         printf("comm_check: world %d, %dx%d, %d frames: %s\n", world, W, H, frames, bad ? "MISMATCH" : "assembled colour / normal / position, denoised and host frames identical to the single-rank frames");
+        printf("comm_check: strips without a denoiser (colour rows to rank 0 / the host frame): %s\n", bad ? "MISMATCH" : "colour frame identical");
         printf("comm_check: strips (denoiser distributed over the ranks): %s\n", stripsState == 2 ? "unsupported at this size (strips thinner than the denoiser's reach)" : bad ? "MISMATCH" : "denoised frame identical");
         vrt_frame_release(soloFrame); vrt_scene_destroy(soloScene); vrt_context_destroy(solo);
         vrt_buffer_free(ctx, dOut); vrt_buffer_free(ctx, dScratch);

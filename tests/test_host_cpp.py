@@ -63,6 +63,7 @@ def test_cpp_ranks_assemble_a_frame_without_torch(world, size):
     # the denoiser distributed over the ranks (vrt_comm_alloc_strips / vrt_render_denoise_exchange); 8 ranks x 5 rows: refused, loudly
     assert ("strips (denoiser distributed over the ranks): denoised frame identical" in p.stdout) == (world != 8), p.stdout
     assert ("unsupported at this size" in p.stdout) == (world == 8), p.stdout
+    assert "strips without a denoiser (colour rows to rank 0 / the host frame): colour frame identical" in p.stdout
 
 
 def test_cpp_host_compiles_and_links():

@@ -100,6 +100,7 @@ struct vrt_comm {
     int stripRows = 0, stripHalo = 0, stripBufRows = 0;
     uint64_t stripSlotBytes = 0, stripFlagsOff = 0;
     vrt_denoiser_settings stripDs{};
+    bool stripPlain = false;                          // strips without a denoiser: only the colour plane is transposed (read-back path)
 };
 
 // ---------------------------------------------------------------------------------------------------------------- kernels
@@ -466,13 +467,15 @@ static cudaError_t stream_wait_flags(vrt_comm* m, cudaStream_t s, const uint32_t
 // allocates the strip buffers of its rows for all slots and maps everybody else's. The denoiser settings fix the halo; they are the
 // ones vrt_render_denoise_exchange runs. VRT_E_UNSUPPORTED when a strip is thinner than the denoiser's reach (use route (a) then).
 extern "C" int vrt_comm_alloc_strips(vrt_context* c, const vrt_denoiser_settings* ds) {
-    if (!c || !c->comm || !ds) return fail(VRT_E_INVALID, "no communicator / settings");
+    if (!c || !c->comm) return fail(VRT_E_INVALID, "no communicator");
     vrt_comm* m = c->comm; CommShm* sh = m->shm;
-    if (!m->devBase || !(sh->planeMask >> VRT_PLANE_DENOISED_RGBA8 & 1u)) return fail(VRT_E_INVALID, "call vrt_comm_alloc_frames with the denoised plane in plane_mask first");
-    if (ds->iterations < 1 || ds->iterations > 10) return fail(VRT_E_INVALID, "denoiser iterations must be 1..10 (MAX_DENOISER_PASSES)");
-    if (ds->mode != VRT_DENOISE_AS_EXECUTED && ds->mode != VRT_DENOISE_AS_INTENDED) return fail(VRT_E_INVALID, "bad denoise mode");
+    const bool plain = ds == nullptr;                                      // no denoiser: the colour plane alone goes through the strips
+    const uint32_t need = 1u << (plain ? VRT_PLANE_COLOR_RGBA8 : VRT_PLANE_DENOISED_RGBA8);
+    if (!m->devBase || !((sh->planeMask | sh->hostPlaneMask) & need)) return fail(VRT_E_INVALID, "call vrt_comm_alloc_frames with the plane the strips deliver (denoised, or colour without a denoiser) first");
+    if (!plain && (ds->iterations < 1 || ds->iterations > 10)) return fail(VRT_E_INVALID, "denoiser iterations must be 1..10 (MAX_DENOISER_PASSES)");
+    if (!plain && ds->mode != VRT_DENOISE_AS_EXECUTED && ds->mode != VRT_DENOISE_AS_INTENDED) return fail(VRT_E_INVALID, "bad denoise mode");
     const int W = sh->w, H = sh->h, slots = sh->slots, world = m->world;
-    const int SR = (H + world - 1) / world, halo = denoise_reach_rows(ds);
+    const int SR = (H + world - 1) / world, halo = plain ? 0 : denoise_reach_rows(ds);
     if (halo < 0 || halo > SR) return fail(VRT_E_UNSUPPORTED, "a strip of " + std::to_string(SR) + " rows is thinner than the denoiser's reach: exchange the planes and denoise on rank 0 (vrt_denoise_on)");
     CU(cudaSetDevice(c->device));
     CU(cudaDeviceSynchronize());
@@ -481,15 +484,15 @@ extern "C" int vrt_comm_alloc_strips(vrt_context* c, const vrt_denoiser_settings
     comm_unmap_strips(m);
     const int bufRows = SR + 2 * halo;
     auto up = [](uint64_t v) { return (v + 255u) & ~(uint64_t)255u; };
-    const uint64_t colorBytes = up((uint64_t)bufRows * W * 4), normalBytes = colorBytes, positionBytes = up((uint64_t)bufRows * W * 16);
+    const uint64_t colorBytes = up((uint64_t)bufRows * W * 4), normalBytes = plain ? 0 : colorBytes, positionBytes = plain ? 0 : up((uint64_t)bufRows * W * 16);
     m->stripSlotBytes = colorBytes + normalBytes + positionBytes;
     m->stripFlagsOff = m->stripSlotBytes * slots;
     const uint64_t total = m->stripFlagsOff + sizeof(uint32_t) * kMaxSlots * kMaxWorld;
     cudaError_t e = cudaMalloc(&m->stripBase[m->rank], total);
     if (e == cudaSuccess) e = cudaMemset(m->stripBase[m->rank], 0, total);
     if (e == cudaSuccess && world > 1) e = cudaIpcGetMemHandle(&sh->stripHandle[m->rank], m->stripBase[m->rank]);
-    if (e == cudaSuccess) e = cudaMalloc(&m->dnOut, (size_t)bufRows * W * 4);
-    if (e == cudaSuccess) e = cudaMalloc(&m->dnScratch, (size_t)bufRows * W * 4);
+    if (e == cudaSuccess && !plain) e = cudaMalloc(&m->dnOut, (size_t)bufRows * W * 4);
+    if (e == cudaSuccess && !plain) e = cudaMalloc(&m->dnScratch, (size_t)bufRows * W * 4);
     if (e == cudaSuccess) e = cudaMalloc(&m->stripTables, sizeof(StripTable) * slots);
     if (e != cudaSuccess) { sh->error.store(1); return fail(e == cudaErrorMemoryAllocation ? VRT_E_OOM : VRT_E_CUDA, cudaGetErrorString(e)); }
     rc = comm_barrier(m);                                                  // every handle is published
@@ -507,13 +510,15 @@ extern "C" int vrt_comm_alloc_strips(vrt_context* c, const vrt_denoiser_settings
         StripTable& t = tables[s];
         for (int r = 0; r < world; r++) {
             uint8_t* b = m->stripBase[r] + (uint64_t)s * m->stripSlotBytes;
-            t.color[r] = b; t.normal[r] = (int8_t*)(b + colorBytes); t.position[r] = (float*)(b + colorBytes + normalBytes);
+            t.color[r] = b;
+            if (!plain) { t.normal[r] = (int8_t*)(b + colorBytes); t.position[r] = (float*)(b + colorBytes + normalBytes); }
         }
         t.world = world; t.stripRows = SR; t.halo = halo; t.W = W; t.H = H;
     }
     e = cudaMemcpy(m->stripTables, tables, sizeof(StripTable) * slots, cudaMemcpyHostToDevice);
     if (e != cudaSuccess) { sh->error.store(1); return fail(VRT_E_CUDA, cudaGetErrorString(e)); }
-    m->stripRows = SR; m->stripHalo = halo; m->stripBufRows = bufRows; m->stripDs = *ds;
+    m->stripRows = SR; m->stripHalo = halo; m->stripBufRows = bufRows; m->stripPlain = plain;
+    if (!plain) m->stripDs = *ds;
     return comm_barrier(m);
 }
 
@@ -529,13 +534,16 @@ extern "C" int vrt_render_denoise_exchange(vrt_context* c, const vrt_scene* sc, 
     if (st->pipeline == VRT_PIPELINE_MEGAKERNEL) return fail(VRT_E_UNSUPPORTED, "strips are stored by the wavefront kernels");
     vrt_comm* m = c->comm; CommShm* sh = m->shm;
     const int W = cam->screenSize[0], H = cam->screenSize[1];
-    const uint32_t dn = 1u << VRT_PLANE_DENOISED_RGBA8;
+    const int outPlane = m->stripPlain ? VRT_PLANE_COLOR_RGBA8 : VRT_PLANE_DENOISED_RGBA8;
+    const uint32_t dn = 1u << outPlane;
+    const bool toDev = to_host != 2, toHost = to_host != 0;                // to_host: 0 rank 0's device frame, 1 both, 2 the shared host frame only
     uint64_t g64 = 0;
-    int rc = exchange_begin(c, W, H, slot, dn, to_host ? dn : 0u, &g64);
+    int rc = exchange_begin(c, W, H, slot, toDev ? dn : 0u, toHost ? dn : 0u, &g64);
     if (rc) return rc;
     const uint32_t g = (uint32_t)g64;
     vrt_render_settings s2 = *st;
-    s2.denoise.enable = 0; s2.out_mask |= VRT_OUT_GBUFFER;
+    s2.denoise.enable = 0;
+    if (!m->stripPlain) s2.out_mask |= VRT_OUT_GBUFFER;
     XPlanes x{};
     x.strips = m->stripTables + slot;
     rc = vrt_render_impl(c, sc, cam, &s2, frame, &x);
@@ -552,20 +560,24 @@ extern "C" int vrt_render_denoise_exchange(vrt_context* c, const vrt_scene* sc, 
         const int lo = strip_lo(m->rank, SR, m->stripHalo), hi = strip_hi(m->rank, SR, m->stripHalo, H);
         uint8_t* b = m->stripBase[m->rank] + (uint64_t)slot * m->stripSlotBytes;
         const uint64_t colorBytes = ((uint64_t)m->stripBufRows * W * 4 + 255u) & ~(uint64_t)255u;
-        void* ping[2] = {m->dnOut, m->dnScratch};
-        if (((m->stripDs.iterations - 1) % 2) == 1) { ping[0] = m->dnScratch; ping[1] = m->dnOut; }   // the last iteration lands in dnOut
-        int last = 0; uint32_t n = 0;
-        rc = run_denoise(c, m->stripStream, b, b + colorBytes, b + 2 * colorBytes, W, hi - lo, &m->stripDs, ping, &last, &n);
-        if (rc) { sh->error.store(1); return rc; }
-        f->launches += n;
         const size_t rowBytes = (size_t)W * 4;
-        const uint8_t* src = m->dnOut + (size_t)(y0 - lo) * rowBytes;
-        e = cudaMemcpyAsync(m->devBase + (uint64_t)slot * sh->slotStride + sh->planeOff[VRT_PLANE_DENOISED_RGBA8] + (size_t)y0 * rowBytes, src, (size_t)(y1 - y0) * rowBytes, cudaMemcpyDefault, m->stripStream);
-        if (e == cudaSuccess && to_host)
-            e = cudaMemcpyAsync(m->hostBase + (uint64_t)slot * sh->hostSlotStride + sh->hostPlaneOff[VRT_PLANE_DENOISED_RGBA8] + (size_t)y0 * rowBytes, src, (size_t)(y1 - y0) * rowBytes, cudaMemcpyDefault, m->stripStream);
+        const uint8_t* src = b + (size_t)(y0 - lo) * rowBytes;             // without a denoiser: the rows as they arrived
+        if (!m->stripPlain) {
+            void* ping[2] = {m->dnOut, m->dnScratch};
+            if (((m->stripDs.iterations - 1) % 2) == 1) { ping[0] = m->dnScratch; ping[1] = m->dnOut; }   // the last iteration lands in dnOut
+            int last = 0; uint32_t n = 0;
+            rc = run_denoise(c, m->stripStream, b, b + colorBytes, b + 2 * colorBytes, W, hi - lo, &m->stripDs, ping, &last, &n);
+            if (rc) { sh->error.store(1); return rc; }
+            f->launches += n;
+            src = m->dnOut + (size_t)(y0 - lo) * rowBytes;
+        }
+        if (toDev)
+            e = cudaMemcpyAsync(m->devBase + (uint64_t)slot * sh->slotStride + sh->planeOff[outPlane] + (size_t)y0 * rowBytes, src, (size_t)(y1 - y0) * rowBytes, cudaMemcpyDefault, m->stripStream);
+        if (e == cudaSuccess && toHost)
+            e = cudaMemcpyAsync(m->hostBase + (uint64_t)slot * sh->hostSlotStride + sh->hostPlaneOff[outPlane] + (size_t)y0 * rowBytes, src, (size_t)(y1 - y0) * rowBytes, cudaMemcpyDefault, m->stripStream);
     }
     if (e == cudaSuccess)
-        e = stream_signal(m->stripStream, (uint32_t*)(m->devBase + sh->arriveOff) + slot * kMaxWorld + m->rank, to_host ? m->shmDevArrive + slot * kMaxWorld + m->rank : nullptr, g, &f->launches);
+        e = stream_signal(m->stripStream, toDev ? (uint32_t*)(m->devBase + sh->arriveOff) + slot * kMaxWorld + m->rank : nullptr, toHost ? m->shmDevArrive + slot * kMaxWorld + m->rank : nullptr, g, &f->launches);
     if (e != cudaSuccess) { sh->error.store(1); return fail(VRT_E_CUDA, cudaGetErrorString(e)); }
     return VRT_OK;
 }

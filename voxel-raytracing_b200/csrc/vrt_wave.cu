@@ -103,7 +103,7 @@ __global__ void __launch_bounds__(128, WAVE_PRIMARY_MIN_BLOCKS) wave_primary_ker
             if (fp.x.mask) fp.x.mask[xp] = to_unorm8(o.mask);
             if (fp.x.position) reinterpret_cast<float4*>(fp.x.position)[xp] = pos4;
             if (fp.x.normal) reinterpret_cast<char4*>(fp.x.normal)[xp] = n4;
-            if (fp.x.strips) { strip_store<float4>(fp.x.strips, fp.x.strips->position, px, py, pos4); strip_store<char4>(fp.x.strips, fp.x.strips->normal, px, py, n4); }
+            if (fp.x.strips && fp.x.strips->position[0]) { strip_store<float4>(fp.x.strips, fp.x.strips->position, px, py, pos4); strip_store<char4>(fp.x.strips, fp.x.strips->normal, px, py, n4); }
         }
         if (fp.out_mask & VRT_OUT_INSTRUMENT) {
             auto sat = [](int v) { return (short)(v < -32768 ? -32768 : (v > 32767 ? 32767 : v)); };

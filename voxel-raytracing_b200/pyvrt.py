@@ -213,10 +213,11 @@ class Context:
         pm = sum(1 << PLANE_ID[n] for n in planes); hm = sum(1 << PLANE_ID[n] for n in host_planes)
         _ck(lib().vrt_comm_alloc_frames(self.h, int(size[0]), int(size[1]), int(slots), C.c_uint32(pm), C.c_uint32(hm)))
 
-    def comm_alloc_strips(self, ds: "DenoiserSettings"):
+    def comm_alloc_strips(self, ds: "DenoiserSettings | None"):
         """vrt_comm_alloc_strips: the denoiser distributed over the ranks (every rank denoises the rows it owns). Raises VrtError with
-        code E_UNSUPPORTED when a strip would be thinner than the denoiser's reach."""
-        _ck(lib().vrt_comm_alloc_strips(self.h, C.byref(ds)))
+        code E_UNSUPPORTED when a strip would be thinner than the denoiser's reach. ds=None: no denoiser, the strips carry the colour
+        plane alone (the read-back path of a sharded frame)."""
+        _ck(lib().vrt_comm_alloc_strips(self.h, C.byref(ds) if ds is not None else None))
 
     def comm_wait(self, slot, stream=None):
         _ck(lib().vrt_comm_wait(self.h, int(slot), C.c_void_p(stream) if stream else None))
@@ -422,11 +423,12 @@ class VoxelRenderPass:
         return self.frame
 
     def record_denoise_exchange(self, camera: Camera, slot, to_host=False) -> Frame:
-        """vrt_render_denoise_exchange: the pass + the distributed denoiser; the denoised plane of `slot` on rank 0 is the result."""
+        """vrt_render_denoise_exchange: the pass + the distributed denoiser; the denoised plane of `slot` on rank 0 is the result
+        (strips without a denoiser: the colour plane). to_host: 0 device frame, 1 device + shared host frame, 2 host frame only."""
         size = (camera.screenSize[0], camera.screenSize[1])
         if self.frame.size not in (None, size):
             self.frame.release()
-        _ck(lib().vrt_render_denoise_exchange(self.ctx.h, self.scene.h, C.byref(camera), C.byref(self.settings), int(slot), int(bool(to_host)), C.byref(self.frame.h)))
+        _ck(lib().vrt_render_denoise_exchange(self.ctx.h, self.scene.h, C.byref(camera), C.byref(self.settings), int(slot), int(to_host), C.byref(self.frame.h)))
         self.frame.size = size
         return self.frame
 
