@@ -356,3 +356,11 @@ extern "C" void hh_blit(const uint8_t* src, int sw, int sh, uint8_t* dst, int tw
         }
     }
 }
+
+// the strip layout of the distributed denoiser (csrc/vrt_types.h, used by the kernels' strip_store): for image row py, the ranks whose
+// buffer holds it and the row's index there; returns how many (out arrays of 4)
+extern "C" int hh_strip_holders(int py, int world, int stripRows, int halo, int H, int* q_out, int* row_out) {
+    int n = 0;
+    strip_for_each_holder(py, world, stripRows, halo, H, [&](int q, int row) { if (n < 4) { q_out[n] = q; row_out[n] = row; } n++; });
+    return n;
+}

@@ -70,3 +70,38 @@ def test_gloo_sharded_frame_is_byte_identical(world, trav, tmp_path):
     want = harness_render(sc, cam, st, traversal=trav)["color"]
     assert np.array_equal(got, want)
     assert np.array_equal(want, O.render(sc, cam, st)["color"]) or np.abs(want.astype(int) - O.render(sc, cam, st)["color"].astype(int)).max() <= 1
+
+
+def test_strip_layout_of_the_distributed_denoiser():
+    """vrt_comm_alloc_strips / vrt_render_denoise_exchange: rank q denoises rows [q*SR, (q+1)*SR) and holds rows [q*SR - halo, (q+1)*SR + halo)
+    clipped to the image. The kernels store a row into the buffers found by strip_for_each_holder (csrc/vrt_types.h), which only looks at
+    the row's owner and its neighbours: for every halo <= SR that must be exactly the set of ALL ranks whose range holds the row, with the
+    right row index, every buffer row must be written exactly once, and no index may leave the buffer (SR + 2*halo rows)."""
+    import ctypes as C
+    from vrtlib import harness
+    h = harness()
+    q, r = (C.c_int * 4)(), (C.c_int * 4)()
+    for H, world in [(2160, 8), (2160, 2), (217, 3), (40, 8), (360, 4), (1, 1), (7, 16), (4320, 8), (150, 2)]:
+        SR = (H + world - 1) // world
+        for halo in sorted({0, 1, 6, SR // 2, SR}):
+            if halo > SR:
+                continue
+            seen = {}
+            for py in range(H):
+                n = h.hh_strip_holders(py, world, SR, halo, H, q, r)
+                assert 1 <= n <= 3
+                got = {(q[i], r[i]) for i in range(n)}
+                want = set()
+                for k in range(world):
+                    lo, hi = max(0, k * SR - halo), min(H, (k + 1) * SR + halo)
+                    if lo <= py < hi:
+                        want.add((k, py - lo))
+                assert got == want, (H, world, halo, py, got, want)
+                for k, row in got:
+                    assert 0 <= row < SR + 2 * halo
+                    assert (k, row) not in seen
+                    seen[(k, row)] = py
+            # every rank that owns rows got all the rows of its range
+            for k in range(world):
+                lo, hi = max(0, k * SR - halo), min(H, (k + 1) * SR + halo)
+                assert sum(1 for (kk, _) in seen if kk == k) == max(0, hi - lo)

@@ -110,6 +110,19 @@ struct StripTable {
 };
 VRT_HD int strip_lo(int q, int stripRows, int halo) { const int v = q * stripRows - halo; return v < 0 ? 0 : v; }
 VRT_HD int strip_hi(int q, int stripRows, int halo, int H) { const int v = (q + 1) * stripRows + halo; return v > H ? H : v; }
+// f(q, row) for every rank q whose buffer holds image row py (row = its index in that buffer). With halo <= stripRows these can only be
+// the owner of the row and its two neighbours (vrt_comm_alloc_strips refuses thinner strips); tests/test_host.py checks the window
+// against all ranks.
+template <class F>
+VRT_HD void strip_for_each_holder(int py, int world, int stripRows, int halo, int H, F f) {
+    const int o = py / stripRows;
+    for (int d = -1; d <= 1; d++) {
+        const int q = o + d;
+        if (q < 0 || q >= world) continue;
+        const int lo = strip_lo(q, stripRows, halo);
+        if (py >= lo && py < strip_hi(q, stripRows, halo, H)) f(q, py - lo);
+    }
+}
 struct XPlanes { uint8_t* color; float* depth; float* motion; uint8_t* mask; float* position; int8_t* normal; uint8_t* colorHost; /* the same pixel of the shared pinned HOST frame (zero-copy over this GPU's PCIe link) */
                  const StripTable* strips; /* or null */ };
 

@@ -49,14 +49,8 @@ __device__ __forceinline__ void add_totals(Counters* ctr, int stage, unsigned ra
 // pixel (px, py) of a denoiser input plane into the strip buffer of every rank whose row range holds py (StripTable, vrt_types.h)
 template <class T, class B>
 __device__ __forceinline__ void strip_store(const StripTable* __restrict__ t, B* const* bases, int px, int py, T v) {
-    const int o = py / t->stripRows;
-#pragma unroll
-    for (int d = -1; d <= 1; d++) {
-        const int q = o + d;
-        if (q < 0 || q >= t->world) continue;
-        const int lo = strip_lo(q, t->stripRows, t->halo);
-        if (py >= lo && py < strip_hi(q, t->stripRows, t->halo, t->H)) reinterpret_cast<T*>(bases[q])[(size_t)(py - lo) * t->W + px] = v;
-    }
+    const int W = t->W;
+    strip_for_each_holder(py, t->world, t->stripRows, t->halo, t->H, [&](int q, int row) { reinterpret_cast<T*>(bases[q])[(size_t)row * W + px] = v; });
 }
 
 __device__ __forceinline__ void store_color(const FrameParams& fp, const PlanesDev& pl, size_t p, V3 c, int px, int py) {
