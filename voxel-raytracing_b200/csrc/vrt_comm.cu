@@ -530,6 +530,7 @@ extern "C" int vrt_comm_alloc_strips(vrt_context* c, const vrt_denoiser_settings
 extern "C" int vrt_render_denoise_exchange(vrt_context* c, const vrt_scene* sc, const vrt_camera* cam, const vrt_render_settings* st, int slot,
                                            int to_host, vrt_frame** frame) {
     if (!c || !cam || !st || !frame) return fail(VRT_E_INVALID, "null argument");
+    if (to_host < 0 || to_host > 2) return fail(VRT_E_INVALID, "to_host is 0 (device frame), 1 (device + host frame) or 2 (host frame only)");
     if (!c->comm || !c->comm->stripRows) return fail(VRT_E_INVALID, "call vrt_comm_alloc_strips first");
     if (st->pipeline == VRT_PIPELINE_MEGAKERNEL) return fail(VRT_E_UNSUPPORTED, "strips are stored by the wavefront kernels");
     vrt_comm* m = c->comm; CommShm* sh = m->shm;
