@@ -145,7 +145,8 @@ def test_noise_constants_match_double_folding():
 @pytest.mark.parametrize("wave", [False, True])
 def test_harness_production_mode_early_termination(trav, wave):
     """Frames without VRT_OUT_INSTRUMENT let rays stop as a miss as soon as the safe-step field shows no solid within reach
-    (EARLY_ALWAYS, vrt_core.cuh): every reference output (colour + G-buffer) must still equal the oracle's."""
+    (the any-hit exhaustion claim of lin_round / engine_lookup, vrt_core.cuh / vrt_engine.cuh): every reference output (colour + G-buffer)
+    must still equal the oracle's."""
     rng = np.random.default_rng(5)
     whd = (70, 40, 55)
     vol, pal = random_volume(rng, whd, 0.004), random_palette(rng, metallic_every=3)
