@@ -282,6 +282,10 @@ int vrt_render_exchange(vrt_context*, const vrt_scene*, const vrt_camera*, const
  *   Without a denoiser (vrt_comm_alloc_strips(ctx, NULL)) the strips carry the colour plane alone and deliver it unchanged: the read-back
  *     path of a sharded frame — tiles cross NVLink into row strips, every rank's copy engine writes whole rows into the shared host frame
  *     over its own PCIe link, and no push kernel occupies an SM. The frames then need VRT_PLANE_COLOR_RGBA8 in the masks used. */
+/* rows above and below a range of rows that the denoiser's output for that range depends on (the summed reach of all iterations' taps): the
+ * halo of a strip. -1: unbounded / bad settings. Pure host arithmetic (no device needed). New; derived from the per-iteration stepWidth
+ * of DenoiserStage (source/voxels/stages/denoiser_stage.cpp:143-154) and the 3x3 tap offsets (:37-61). */
+int vrt_denoise_reach_rows(const vrt_denoiser_settings*);
 int vrt_comm_alloc_strips(vrt_context*, const vrt_denoiser_settings*);
 int vrt_render_denoise_exchange(vrt_context*, const vrt_scene*, const vrt_camera*, const vrt_render_settings*, int slot, int to_host, vrt_frame** frame);
 int vrt_comm_wait(vrt_context*, int slot, void* stream);  /* rank 0; stream NULL: vrt_comm_stream() */

@@ -105,3 +105,30 @@ def test_strip_layout_of_the_distributed_denoiser():
             for k in range(world):
                 lo, hi = max(0, k * SR - halo), min(H, (k + 1) * SR + halo)
                 assert sum(1 for (kk, _) in seen if kk == k) == max(0, hi - lo)
+
+
+@pytest.mark.parametrize("iterations,step_width,mode", [(1, 2.0, 0), (2, 2.0, 0), (2, 2.0, 1), (3, 1.5, 1), (3, 0.5, 0), (4, 2.5, 1), (2, 5.0, 0), (3, 0.0, 1)])
+def test_strip_halo_is_enough_for_the_denoiser(iterations, step_width, mode):
+    """The distributed denoiser (strips) runs the denoiser on rows [y0 - halo, y1 + halo) of the inputs and keeps rows [y0, y1): with
+    halo = vrt_denoise_reach_rows(settings) those rows must be the rows of the whole-frame result, exactly — here with the oracle's
+    denoiser on random planes, for strips inside the image and at its top and bottom (where the buffer ends with the image)."""
+    import pyvrt
+    import oracle as O
+    ds = pyvrt.DenoiserSettings(1, iterations, 20.4, 1e-2, 1e-1, step_width, mode)
+    halo = pyvrt.denoise_reach_rows(ds)
+    assert 0 < halo <= 64
+    rng = np.random.default_rng(11)
+    H, W = 3 * 23 + 2 * 40, 57
+    color = rng.integers(0, 256, (H, W, 4), dtype=np.uint8); color[..., 3] = 0
+    normal = np.zeros((H, W, 4), np.int8); normal[..., :3] = rng.choice([-127, 0, 127], (H, W, 3))
+    pos = (rng.random((H, W, 4), dtype=np.float32) * 3).astype(np.float32); pos[..., 3] = 0
+    kw = dict(iterations=iterations, step_width=step_width, mode=mode)
+    full = O.denoise(color, normal, pos, **kw)
+    for y0, y1 in [(0, 23), (60, 83), (H - 23, H), (40, 41)]:
+        lo, hi = max(0, y0 - halo), min(H, y1 + halo)
+        part = O.denoise(color[lo:hi], normal[lo:hi], pos[lo:hi], **kw)
+        assert np.array_equal(part[y0 - lo:y1 - lo], full[y0:y1]), (y0, y1, halo)
+    # and it is not a wild over-estimate: one row less than the taps' plain reach breaks it somewhere (integral step widths)
+    if float(step_width).is_integer() and step_width > 0:
+        reach = int(sum(i * step_width + 1 for i in range(iterations)))
+        assert reach <= halo <= reach + iterations

@@ -431,6 +431,7 @@ extern "C" int vrt_render_exchange(vrt_context* c, const vrt_scene* sc, const vr
 // on rank 0 work as for any exchange. Per frame every rank receives 24 B x (1 / world + halo share) of the pixels instead of rank 0
 // receiving all of them.
 static int denoise_reach_rows(const vrt_denoiser_settings* ds) {
+    if (!ds || ds->iterations < 1 || ds->iterations > 10) return -1;
     int h = 0;
     for (int i = 0; i < ds->iterations; i++) {
         const float sw = fabsf((float)i * ds->stepWidth + 1.0f);           // denoiser_stage.cpp:143-154; tap offsets are -1, 0, 1
@@ -439,6 +440,8 @@ static int denoise_reach_rows(const vrt_denoiser_settings* ds) {
     }
     return h;
 }
+// the same as a utility of the ABI (pure host arithmetic: callable without a GPU): tests/test_sharding.py checks it against the oracle
+extern "C" int vrt_denoise_reach_rows(const vrt_denoiser_settings* ds) { return denoise_reach_rows(ds); }
 // `word` := g when `s` gets there: a stream memory operation where the driver has them (no SM), else the one-thread kernel
 static cudaError_t stream_signal(cudaStream_t s, uint32_t* devFlag, uint32_t* hostFlag, uint32_t g, uint32_t* launches) {
     if (g_writeValue32 && !getenv("VRT_COMM_SIGNAL_KERNEL")) {

@@ -520,6 +520,11 @@ def denoise_device_on(ctx: Context, d_color, d_normal, d_position, size, ds: Den
                              C.c_void_p(d_out), C.c_void_p(d_scratch), C.c_void_p(stream) if stream else None))
 
 
+def denoise_reach_rows(ds: DenoiserSettings) -> int:
+    """vrt_denoise_reach_rows: the halo (rows either side) the denoiser's output for a range of rows depends on. No device needed."""
+    return int(lib().vrt_denoise_reach_rows(C.byref(ds)))
+
+
 DENOISE_STATIC_MAX_PIXELS = 3840 * 2160   # include/vrt.h VRT_DENOISE_STATIC_MAX_PIXELS
 
 
