@@ -40,6 +40,21 @@ def test_no_gpu_fails_loudly_no_cpu_fallback():
     assert e.value.code == pyvrt.E_NO_DEVICE and "no CPU fallback" in str(e.value)
 
 
+def test_entry_points_added_in_round_2_reject_bad_arguments_without_a_device():
+    """Argument checks come before any CUDA call: null handles / sizes beyond the limits are answered with VRT_E_INVALID and a message,
+    on a machine without a GPU too (no compute happens here)."""
+    L = pyvrt.lib()
+    ds = pyvrt.default_settings().denoise
+    assert L.vrt_denoise_static(None, None, None, None, 4, 4, C.byref(ds), None, None) == pyvrt.E_INVALID
+    assert L.vrt_comm_alloc_strips(None, C.byref(ds)) == pyvrt.E_INVALID
+    assert L.vrt_render_denoise_exchange(None, None, None, None, 0, 0, None) == pyvrt.E_INVALID
+    assert L.vrt_last_error().decode() != ""
+    assert pyvrt.denoise_reach_rows(ds) == 6                      # defaults: 2 iterations, step widths 1 and 3, +1 row each for LINEAR taps
+    bad = pyvrt.DenoiserSettings(1, 11, 20.4, 1e-2, 1e-1, 2.0, 0)
+    assert pyvrt.denoise_reach_rows(bad) == -1
+    assert pyvrt.DENOISE_STATIC_MAX_PIXELS == 3840 * 2160
+
+
 @pytest.mark.parametrize("name", ["lshape", "twoinst", "nopalette", "overlap9"])
 def test_vox_decode_matches_reference_golden(name):
     data = open(os.path.join(GOLD, name + ".vox"), "rb").read()
