@@ -41,3 +41,17 @@ def test_product_parsers_are_clean_under_asan_and_ubsan_on_damaged_files():
     assert p.returncode == 0 and "parser sanitize ok" in p.stdout, p.stdout[-2000:] + p.stderr[-4000:]
     accepted, rejected = [int(x) for x in p.stdout.split("ok:")[1].replace("inputs accepted,", "").replace("rejected", "").split()]
     assert accepted > 1000 and rejected > 1000          # the damage is neither harmless nor always fatal: both paths of the parsers ran
+
+
+def test_shared_traversal_core_is_clean_under_ubsan():
+    """csrc/vrt_core.cuh & co. are compiled for the device by nvcc and for the host by the test harness: the same C++. Here the harness
+    is built with UBSan and renders three poses through every back-end and both pipelines (tests/sanitize/harness_ubsan.py)."""
+    src = os.path.join(ROOT, "tests", "host_harness", "harness.cpp")
+    lib = os.path.join(SAN, "libhh_ubsan.so")
+    deps = [src] + glob.glob(os.path.join(ROOT, "voxel-raytracing_b200", "csrc", "*.cuh")) + glob.glob(os.path.join(ROOT, "voxel-raytracing_b200", "csrc", "*.h"))
+    if not os.path.exists(lib) or any(os.path.getmtime(d) > os.path.getmtime(lib) for d in deps):
+        subprocess.check_call([GXX, "-std=c++17", "-O1", "-g", "-ffp-contract=off", "-fno-fast-math", "-fopenmp", "-fPIC", "-shared",
+                               "-fsanitize=undefined", "-fno-sanitize-recover=undefined", "-x", "c++", src, "-o", lib])
+    env = dict(os.environ, UBSAN_OPTIONS="print_stacktrace=1")
+    p = subprocess.run([os.sys.executable, os.path.join(SAN, "harness_ubsan.py"), lib], capture_output=True, text=True, timeout=900, env=env)
+    assert p.returncode == 0 and "harness under UBSan: ok" in p.stdout, p.stdout[-2000:] + p.stderr[-4000:]
